@@ -1,0 +1,224 @@
+/* orbx.h — C ABI of the B200-native ORB front end (liborbx.so).
+ *
+ * This is the drop-in boundary for ONE hot path of carry4985/ORB_SLAM2_MAP: the per-frame ORB
+ * front end.  The reference has no FFI of its own (its boundary is the C++ class API), so every
+ * entry point below names the reference function it replaces; the C++ classes in
+ * orb_slam2_map_b200/host/ re-create the reference's signatures on top of these calls.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; no C++/torch types; never throws, never aborts.
+ *  - every function returns ORBX_OK (0) or a negative orbx_status; orbx_last_error() gives the
+ *    message of the calling thread's last failure.
+ *  - there is NO CPU fallback: without a CUDA device every compute entry point fails with
+ *    ORBX_E_CUDA.
+ *  - a handle owns one CUDA stream (or borrows the caller's), a device workspace and a result
+ *    store; it must be used by one thread at a time (same rule as one ORBextractor object,
+ *    reference src/Frame.cc:78-79 uses two objects for two threads).
+ *  - "slot" = index of a frame inside the handle's device-resident result store.
+ */
+#ifndef ORBX_H
+#define ORBX_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum orbx_status {
+    ORBX_OK = 0,
+    ORBX_E_INVALID = -1,   /* bad argument */
+    ORBX_E_CUDA = -2,      /* CUDA runtime failure (incl. no device) */
+    ORBX_E_CAPACITY = -3,  /* caller buffer / handle capacity too small */
+    ORBX_E_STATE = -4      /* call sequence error (e.g. slot not extracted yet) */
+} orbx_status;
+
+/* Same 28-byte layout as cv::KeyPoint (pt.x, pt.y, size, angle, response, octave, class_id),
+ * which is what ORBextractor::operator() fills (reference src/ORBextractor.cc:1043-1105). */
+typedef struct orbx_keypoint {
+    float x, y, size, angle, response;
+    int32_t octave, class_id;
+} orbx_keypoint;
+
+/* ORBextractor constructor arguments (reference include/ORBextractor.h:51-52). */
+typedef struct orbx_params {
+    int32_t nfeatures;
+    float scale_factor;
+    int32_t nlevels;
+    int32_t ini_th_fast;
+    int32_t min_th_fast;
+} orbx_params;
+
+typedef struct orbx_handle orbx_handle;
+
+const char* orbx_last_error(void);
+/* number of CUDA devices visible; <0 on failure (lets a caller fail loudly up front). */
+int orbx_device_count(void);
+
+/* ---- extractor: replaces ORBextractor::ORBextractor / ~ORBextractor ------------------------
+ * max_width/max_height: largest image the handle will see; chunk_frames: frames in flight per
+ * kernel wave (workspace size); result_slots: frames whose keypoints/descriptors stay resident
+ * on the device; stream: a cudaStream_t to borrow, or NULL to create one. */
+int orbx_create(const orbx_params* params, int max_width, int max_height, int chunk_frames,
+                int result_slots, int device, void* stream, orbx_handle** out);
+int orbx_destroy(orbx_handle* h);
+int orbx_sync(orbx_handle* h);
+
+/* scale tables computed exactly as the reference ctor does (src/ORBextractor.cc:410-446);
+ * arrays of nlevels entries, any pointer may be NULL.  Replaces GetScaleFactors & friends. */
+int orbx_get_tables(const orbx_handle* h, float* scale, float* inv_scale, float* sigma2,
+                    float* inv_sigma2, int32_t* features_per_level);
+/* upper bound of keypoints per frame (sum over levels of max(N_l+3, 4*nIni)). */
+int orbx_keypoint_capacity(const orbx_handle* h);
+
+/* ---- ORBextractor::operator() (src/ORBextractor.cc:1043), single frame, host buffers --------
+ * image: 8UC1 host pointer.  kps/desc: host buffers with room for `capacity` keypoints
+ * (desc = capacity*32 bytes).  *n receives the count.  width*height==0 -> *n untouched (the
+ * reference returns silently on an empty image). */
+int orbx_extract(orbx_handle* h, const uint8_t* image, int width, int height, size_t row_stride,
+                 orbx_keypoint* kps, uint8_t* desc, int capacity, int* n);
+
+/* Batched form of the same operator: nframes images of one shape, `images` either a host
+ * pointer (pinned or pageable) or a device pointer (images_on_device!=0); frame i starts at
+ * images + i*frame_stride.  Results land in slots first_slot .. first_slot+nframes-1 and stay
+ * on the device; asynchronous on the handle's stream when images are on the device. */
+int orbx_extract_batch(orbx_handle* h, const uint8_t* images, size_t frame_stride,
+                       size_t row_stride, int width, int height, int nframes,
+                       int images_on_device, int first_slot);
+
+/* Copy results of slots [first_slot, first_slot+nframes) to host: kps[nframes][capacity],
+ * desc[nframes][capacity][32], counts[nframes].  Synchronises. Any of kps/desc may be NULL. */
+int orbx_download(orbx_handle* h, int first_slot, int nframes, orbx_keypoint* kps, uint8_t* desc,
+                  int32_t* counts, int capacity);
+
+/* ORBextractor::mvImagePyramid[level] of the LAST single-frame/batch chunk (src/ORBextractor.h:85,
+ * read by Frame::ComputeStereoMatches).  frame = index inside the last chunk.  blurred=0 gives the
+ * raw level, 1 the 7x7 Gaussian-blurred working copy (src/ORBextractor.cc:1085-1086).
+ * border>0 adds a BORDER_REFLECT_101 margin of that many pixels (the reference keeps 19). */
+int orbx_get_level(orbx_handle* h, int frame, int level, int blurred, int border, uint8_t* dst,
+                   size_t dst_stride, int* width, int* height);
+
+/* test/diagnostic taps (device -> host), same chunk addressing as orbx_get_level:
+ * FAST candidates handed to DistributeOctTree for one level, in the reference's order
+ * (src/ORBextractor.cc:789-829): xyr[3*i] = x, y (window-relative), response. */
+int orbx_get_candidates(orbx_handle* h, int frame, int level, float* xyr, int capacity, int* n);
+
+/* ---- Frame grid + ORBmatcher on device-resident slots ----------------------------------------
+ * Consecutive-frame ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:405-520) for pairs
+ * (first_slot+i, first_slot+i+1), i<npairs, with vbPrevMatched = F1's keypoint positions
+ * (Tracking.cc:862-866) and the frame grid of Frame::AssignFeaturesToGrid (src/Frame.cc:230) on
+ * bounds [0,width]x[0,height].  matches12: host [npairs][capacity] (may be NULL), nmatches: host
+ * [npairs] (may be NULL); with both NULL the call is asynchronous and results stay on device.
+ * ncompares (host, may be NULL): number of DescriptorDistance evaluations performed. */
+int orbx_search_init_pairs(orbx_handle* h, int first_slot, int npairs, int window_size,
+                           float nnratio, int check_orientation, int32_t* matches12,
+                           int32_t* nmatches, int capacity, uint64_t* ncompares);
+
+/* Stereo: extract left+right (two ORBextractor objects in the reference, src/Frame.cc:78-81) and
+ * run Frame::ComputeStereoMatches (src/Frame.cc:466-638) per pair while the pyramids are still on
+ * the device.  Left frame i -> slot first_slot+2*i, right -> first_slot+2*i+1.
+ * u_right/depth: host [npairs][capacity] (mvuRight / mvDepth), may be NULL (async). */
+int orbx_extract_stereo_batch(orbx_handle* h, const uint8_t* left, const uint8_t* right,
+                              size_t frame_stride, size_t row_stride, int width, int height,
+                              int npairs, int images_on_device, int first_slot, float bf, float fx,
+                              float* u_right, float* depth, int capacity, uint64_t* ncompares);
+
+/* ---- stateless matchers on caller-provided (host) arrays --------------------------------------
+ * A frame as the matchers see it: undistorted keypoints (Frame::mvKeysUn), descriptors
+ * (Frame::mDescriptors, n x 32), image bounds (mnMinX..mnMaxY) from which the 64x48 grid is
+ * built exactly as Frame.cc:97-98,230-245,382-392 do. */
+typedef struct orbm_frame {
+    int32_t n;
+    const orbx_keypoint* keys_un;
+    const uint8_t* descriptors;
+    float min_x, max_x, min_y, max_y;
+    const float* u_right;     /* Frame::mvuRight (n) or NULL (= all -1) */
+    const float* scale_factors; /* Frame::mvScaleFactors (nlevels) or NULL */
+    int32_t nlevels;
+} orbm_frame;
+
+/* ORBmatcher::DescriptorDistance (src/ORBmatcher.cc:1647-1663) for `count` row pairs on the
+ * device: dist[i] = hamming(a[i], b[i]).  Host pointers. */
+int orbm_descriptor_distance(const uint8_t* a, const uint8_t* b, int count, int32_t* dist);
+
+/* ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:405-520).  prev_matched: in/out
+ * [f1->n][2] floats (vbPrevMatched); matches12: out [f1->n].  Returns match count in *nmatches. */
+int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, float* prev_matched,
+                                   int32_t* matches12, int window_size, float nnratio,
+                                   int check_orientation, int32_t* nmatches);
+
+/* The four ORBmatcher::SearchByProjection variants share one device skeleton.  The C++ wrapper
+ * flattens MapPoints into queries (projection stays on the host, src/ORBmatcher.cc:1340-1376):
+ * per query: window centre (u,v), radius, level window [min_level,max_level] passed to
+ * GetFeaturesInArea (src/Frame.cc:327-380), descriptor, and per-variant extras. */
+typedef struct orbm_proj_query {
+    float u, v, radius;
+    int32_t min_level, max_level;
+    float u_right;        /* predicted right coordinate (mTrackProjXR / u - mbf*invz)          */
+    float max_right_err;  /* stereo gate for keypoints with mvuRight>0:
+                             |u_right - mvuRight[idx]| > max_right_err -> skip; <0 = gate off   */
+    float angle;          /* keypoint angle of the source observation (rotation histogram)     */
+    int32_t level_lo, level_hi; /* extra per-candidate octave filter applied after the area query
+                                   (KeyFrame/Sim3 variant, src/ORBmatcher.cc:374-377); -1 = off */
+} orbm_proj_query;
+
+enum {
+    ORBM_PROJ_LOCALMAP = 0,  /* (Frame&, vector<MapPoint*>&, th)      src/ORBmatcher.cc:45-129   */
+    ORBM_PROJ_LASTFRAME = 1, /* (Frame&, const Frame&, th, bMono)     src/ORBmatcher.cc:1328-1470 */
+    ORBM_PROJ_KEYFRAME = 2,  /* (Frame&, KeyFrame*, set&, th, ORBdist) src/ORBmatcher.cc:1472-1599 */
+    ORBM_PROJ_SIM3 = 3       /* (KeyFrame*, Scw, vpPoints, vpMatched, th) src/ORBmatcher.cc:290-403 */
+};
+
+/* occupied: in/out [frame->n] bytes. in: 1 if the keypoint already holds a map point that blocks
+ * new matches (Observations()>0 for LOCALMAP/LASTFRAME, non-NULL for KEYFRAME/SIM3);
+ * assigned: out [frame->n], index of the query that finally owns keypoint i, or -1 (the
+ * reference overwrites F.mvpMapPoints[bestIdx] in query order; rotation-culled ones are -1).
+ * query_blocks: [nq] bytes, 1 if a keypoint taken by this query blocks later queries
+ * (pMP->Observations()>0); ignored for KEYFRAME/SIM3 (always blocks).
+ * best_idx/best_dist: out [nq] per-query chosen keypoint (-1 if none) and distance.
+ * th_dist: TH_HIGH(100) / ORBdist / TH_LOW(50) per variant. */
+int orbm_search_by_projection(int variant, const orbm_frame* frame, const orbm_proj_query* queries,
+                              const uint8_t* query_desc, int nq, const uint8_t* query_blocks,
+                              uint8_t* occupied, int32_t* assigned, int32_t* best_idx,
+                              int32_t* best_dist, int th_dist, float nnratio,
+                              int check_orientation, int32_t* nmatches);
+
+/* Frame::ComputeStereoMatches (src/Frame.cc:466-638) on caller-provided data: keypoints and
+ * descriptors of both eyes plus both raw pyramids (mvImagePyramid of the two extractors; level l
+ * of eye e at pyr[e][l] with row stride pyr_stride[e][l], WITHOUT the 19-px border). */
+typedef struct orbm_stereo_input {
+    int32_t n_left, n_right;
+    const orbx_keypoint* keys_left;
+    const orbx_keypoint* keys_right;
+    const uint8_t* desc_left;
+    const uint8_t* desc_right;
+    int32_t nlevels;
+    const float* scale_factors;
+    const float* inv_scale_factors;
+    const uint8_t* const* pyr_left;   /* nlevels pointers */
+    const uint8_t* const* pyr_right;
+    const int32_t* level_width;       /* nlevels */
+    const int32_t* level_height;
+    const int64_t* pyr_stride_left;   /* nlevels */
+    const int64_t* pyr_stride_right;
+    float bf, fx;                     /* mbf and fx: mb = mbf/fx, maxD = mbf/mb */
+} orbm_stereo_input;
+int orbm_compute_stereo_matches(const orbm_stereo_input* in, float* u_right, float* depth,
+                                uint64_t* ncompares);
+
+/* Brute-force 2-nearest-neighbour Hamming search (BASELINE.json config 5): for every query the
+ * best and second-best database rows under DescriptorDistance; ties -> lower database index.
+ * Pointers are DEVICE pointers (the bench keeps 1M x 16M resident); out_dist: [nq][2] uint16,
+ * out_idx: [nq][2] int32 (global index = db_index_offset + local row).  Asynchronous on
+ * `stream` (cudaStream_t or NULL = default stream). */
+int orbm_knn2_device(const uint8_t* queries, int64_t nq, const uint8_t* database, int64_t ndb,
+                     int32_t db_index_offset, uint16_t* out_dist, int32_t* out_idx, void* stream);
+/* Merge `nparts` per-shard results (each [nq][2]) into one, same tie rule; device pointers. */
+int orbm_knn2_merge_device(const uint16_t* part_dist, const int32_t* part_idx, int nparts,
+                           int64_t nq, uint16_t* out_dist, int32_t* out_idx, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBX_H */

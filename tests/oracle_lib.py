@@ -1,0 +1,287 @@
+"""ctypes bindings for oracle/liborb_oracle.so (TEST INFRASTRUCTURE ONLY — never imported by the
+product package).  Builds the oracle with its Makefile on first use."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+_LIB = None
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+
+class Params(C.Structure):
+    _fields_ = [("nfeatures", C.c_int32), ("scale_factor", C.c_float), ("nlevels", C.c_int32),
+                ("ini_th_fast", C.c_int32), ("min_th_fast", C.c_int32)]
+
+
+class Frame(C.Structure):
+    _fields_ = [("n", C.c_int32), ("keys_un", C.c_void_p), ("descriptors", C.c_void_p),
+                ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float), ("max_y", C.c_float),
+                ("u_right", C.c_void_p), ("scale_factors", C.c_void_p), ("nlevels", C.c_int32)]
+
+
+class ProjQuery(C.Structure):
+    _fields_ = [("u", C.c_float), ("v", C.c_float), ("radius", C.c_float),
+                ("min_level", C.c_int32), ("max_level", C.c_int32),
+                ("u_right", C.c_float), ("max_right_err", C.c_float), ("angle", C.c_float),
+                ("level_lo", C.c_int32), ("level_hi", C.c_int32)]
+
+
+PROJ_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("radius", "<f4"), ("min_level", "<i4"),
+                       ("max_level", "<i4"), ("u_right", "<f4"), ("max_right_err", "<f4"),
+                       ("angle", "<f4"), ("level_lo", "<i4"), ("level_hi", "<i4")])
+assert PROJ_DTYPE.itemsize == C.sizeof(ProjQuery)
+
+
+class StereoInput(C.Structure):
+    _fields_ = [("n_left", C.c_int32), ("n_right", C.c_int32),
+                ("keys_left", C.c_void_p), ("keys_right", C.c_void_p),
+                ("desc_left", C.c_void_p), ("desc_right", C.c_void_p),
+                ("nlevels", C.c_int32),
+                ("scale_factors", C.c_void_p), ("inv_scale_factors", C.c_void_p),
+                ("pyr_left", C.c_void_p), ("pyr_right", C.c_void_p),
+                ("level_width", C.c_void_p), ("level_height", C.c_void_p),
+                ("pyr_stride_left", C.c_void_p), ("pyr_stride_right", C.c_void_p),
+                ("bf", C.c_float), ("fx", C.c_float)]
+
+
+def build_oracle(force: bool = False) -> str:
+    so = os.path.join(ORACLE_DIR, "liborb_oracle.so")
+    src = os.path.join(ORACLE_DIR, "orb_oracle.cpp")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", ORACLE_DIR, "liborb_oracle.so"], stdout=subprocess.DEVNULL)
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        L = C.CDLL(build_oracle())
+        L.oracle_fast_atan2.restype = C.c_float
+        L.oracle_fast_atan2.argtypes = [C.c_float, C.c_float]
+        L.oracle_extractor_create.restype = C.c_void_p
+        L.oracle_extractor_create.argtypes = [C.POINTER(Params)]
+        L.oracle_extractor_destroy.argtypes = [C.c_void_p]
+        L.oracle_extract_many.restype = C.c_int64
+        L.oracle_cv_round.argtypes = [C.c_double]
+        _LIB = L
+    return _LIB
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def resize(src: np.ndarray, dw: int, dh: int) -> np.ndarray:
+    src = np.ascontiguousarray(src)
+    dst = np.empty((dh, dw), np.uint8)
+    lib().oracle_resize_linear_u8(_p(src), C.c_int(src.shape[1]), C.c_int(src.shape[0]), C.c_size_t(src.strides[0]),
+                                  _p(dst), C.c_int(dw), C.c_int(dh), C.c_size_t(dw))
+    return dst
+
+
+def blur(src: np.ndarray) -> np.ndarray:
+    src = np.ascontiguousarray(src)
+    dst = np.empty_like(src)
+    lib().oracle_gaussian_blur7_u8(_p(src), C.c_int(src.shape[1]), C.c_int(src.shape[0]), C.c_size_t(src.strides[0]),
+                                   _p(dst), C.c_size_t(dst.strides[0]))
+    return dst
+
+
+def border101(src: np.ndarray, b: int) -> np.ndarray:
+    src = np.ascontiguousarray(src)
+    dst = np.empty((src.shape[0] + 2 * b, src.shape[1] + 2 * b), np.uint8)
+    lib().oracle_copy_make_border101(_p(src), C.c_int(src.shape[1]), C.c_int(src.shape[0]), C.c_size_t(src.strides[0]),
+                                     _p(dst), C.c_size_t(dst.strides[0]), C.c_int(b))
+    return dst
+
+
+def fast(img: np.ndarray, th: int, nms: bool = True) -> np.ndarray:
+    """-> float32 [n,3] (x, y, response); img may be a non-contiguous view (row stride honoured)."""
+    assert img.strides[1] == 1
+    cap = img.shape[0] * img.shape[1]
+    out = np.empty((cap, 3), np.float32)
+    n = lib().oracle_fast9_16(C.c_void_p(img.ctypes.data), C.c_int(img.shape[1]), C.c_int(img.shape[0]),
+                              C.c_size_t(img.strides[0]), C.c_int(th), C.c_int(int(nms)), _p(out), C.c_int(cap))
+    return out[:n].copy()
+
+
+def fast_atan2(y: float, x: float) -> float:
+    return float(lib().oracle_fast_atan2(C.c_float(y), C.c_float(x)))
+
+
+def sincos(x: float, use_libm: bool = False):
+    s, c = C.c_float(), C.c_float()
+    lib().oracle_sincos(C.c_float(x), C.byref(s), C.byref(c), C.c_int(int(use_libm)))
+    return s.value, c.value
+
+
+class Extractor:
+    def __init__(self, nfeatures=1000, scale=1.2, nlevels=8, ini_th=20, min_th=7):
+        self.params = Params(nfeatures, scale, nlevels, ini_th, min_th)
+        self.h = C.c_void_p(lib().oracle_extractor_create(C.byref(self.params)))
+        self.nlevels = nlevels
+        self.cap = nfeatures + 64 * nlevels + 64
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().oracle_extractor_destroy(self.h)
+            self.h = None
+
+    def tables(self):
+        n = self.nlevels
+        sc, isc, s2, is2 = (np.empty(n, np.float32) for _ in range(4))
+        fpl = np.empty(n, np.int32)
+        umax = np.empty(16, np.int32)
+        lib().oracle_extractor_tables(self.h, _p(sc), _p(isc), _p(s2), _p(is2), _p(fpl), _p(umax))
+        return dict(scale=sc, inv_scale=isc, sigma2=s2, inv_sigma2=is2, features_per_level=fpl, umax=umax)
+
+    def extract(self, img: np.ndarray, use_libm: bool = False):
+        img = np.ascontiguousarray(img)
+        kps = np.zeros(self.cap, KP_DTYPE)
+        desc = np.zeros((self.cap, 32), np.uint8)
+        n = lib().oracle_extract(self.h, _p(img), C.c_int(img.shape[1]), C.c_int(img.shape[0]),
+                                 C.c_size_t(img.strides[0]), _p(kps), _p(desc), C.c_int(self.cap),
+                                 C.c_int(int(use_libm)))
+        assert n >= 0, "oracle capacity"
+        return kps[:n].copy(), desc[:n].copy()
+
+    def level(self, level: int, blurred: bool = False) -> np.ndarray:
+        w, h = C.c_int(), C.c_int()
+        assert lib().oracle_level_size(self.h, C.c_int(level), C.byref(w), C.byref(h)) == 0
+        out = np.empty((h.value, w.value), np.uint8)
+        assert lib().oracle_get_level(self.h, C.c_int(level), C.c_int(int(blurred)), _p(out), C.c_size_t(w.value)) == 0
+        return out
+
+    def candidates(self, level: int) -> np.ndarray:
+        n = lib().oracle_get_candidates(self.h, C.c_int(level), None, C.c_int(0))
+        out = np.empty((max(n, 1), 3), np.float32)
+        lib().oracle_get_candidates(self.h, C.c_int(level), _p(out), C.c_int(n))
+        return out[:n]
+
+    def level_keypoints(self, level: int) -> np.ndarray:
+        out = np.zeros(self.cap, KP_DTYPE)
+        n = lib().oracle_get_level_keypoints(self.h, C.c_int(level), _p(out), C.c_int(self.cap))
+        return out[:n].copy()
+
+
+def distribute_octtree(xyr: np.ndarray, minX, maxX, minY, maxY, N) -> np.ndarray:
+    xyr = np.ascontiguousarray(xyr, np.float32)
+    n = len(xyr)
+    out = np.empty(max(n, 1), np.int32)
+    m = lib().oracle_distribute_octtree(_p(xyr), C.c_int(n), C.c_int(minX), C.c_int(maxX), C.c_int(minY),
+                                        C.c_int(maxY), C.c_int(N), _p(out), C.c_int(n))
+    return out[:m].copy()
+
+
+def descriptor_distance(a: np.ndarray, b: np.ndarray) -> int:
+    a = np.ascontiguousarray(a)
+    b = np.ascontiguousarray(b)
+    return int(lib().oracle_descriptor_distance(_p(a), _p(b)))
+
+
+class FrameData:
+    """Keeps numpy arrays alive behind an orbm_frame struct."""
+
+    def __init__(self, kps, desc, width, height, u_right=None, scale_factors=None, bounds=None):
+        self.kps = np.ascontiguousarray(kps, KP_DTYPE)
+        self.desc = np.ascontiguousarray(desc, np.uint8)
+        self.u_right = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+        self.sf = None if scale_factors is None else np.ascontiguousarray(scale_factors, np.float32)
+        b = bounds if bounds is not None else (0.0, float(width), 0.0, float(height))
+        self.bounds = b
+        self.c = Frame(len(self.kps), self.kps.ctypes.data, self.desc.ctypes.data, b[0], b[1], b[2], b[3],
+                       None if self.u_right is None else self.u_right.ctypes.data,
+                       None if self.sf is None else self.sf.ctypes.data,
+                       0 if self.sf is None else len(self.sf))
+
+
+def features_in_area(f: FrameData, x, y, r, min_level=-1, max_level=-1) -> np.ndarray:
+    out = np.empty(max(f.c.n, 1), np.int32)
+    n = lib().oracle_features_in_area(C.byref(f.c), C.c_float(x), C.c_float(y), C.c_float(r), C.c_int(min_level),
+                                      C.c_int(max_level), _p(out), C.c_int(f.c.n))
+    return out[:n].copy()
+
+
+def search_for_initialization(f1: FrameData, f2: FrameData, prev_matched: np.ndarray, window=100, nnratio=0.9,
+                              check_ori=True):
+    pm = np.ascontiguousarray(prev_matched, np.float32).copy()
+    m12 = np.empty(max(f1.c.n, 1), np.int32)
+    ncmp = C.c_uint64()
+    n = lib().oracle_search_for_initialization(C.byref(f1.c), C.byref(f2.c), _p(pm), _p(m12), C.c_int(window),
+                                               C.c_float(nnratio), C.c_int(int(check_ori)), C.byref(ncmp))
+    return n, m12[:f1.c.n].copy(), pm, ncmp.value
+
+
+def search_by_projection(variant, f: FrameData, queries: np.ndarray, qdesc: np.ndarray, blocks, occupied, th_dist,
+                         nnratio=0.6, check_ori=True):
+    q = np.ascontiguousarray(queries, PROJ_DTYPE)
+    qd = np.ascontiguousarray(qdesc, np.uint8)
+    nq = len(q)
+    occ = np.ascontiguousarray(occupied, np.uint8).copy()
+    blk = None if blocks is None else np.ascontiguousarray(blocks, np.uint8)
+    assigned = np.empty(max(f.c.n, 1), np.int32)
+    bi = np.empty(max(nq, 1), np.int32)
+    bd = np.empty(max(nq, 1), np.int32)
+    n = lib().oracle_search_by_projection(C.c_int(variant), C.byref(f.c), _p(q), _p(qd), C.c_int(nq), _p(blk),
+                                          _p(occ), _p(assigned), _p(bi), _p(bd), C.c_int(th_dist), C.c_float(nnratio),
+                                          C.c_int(int(check_ori)))
+    return n, assigned[:f.c.n].copy(), bi[:nq].copy(), bd[:nq].copy(), occ
+
+
+def make_stereo_input(kl, dl, kr, dr, pyr_l, pyr_r, scale, inv_scale, bf, fx):
+    """pyr_l / pyr_r: lists of contiguous uint8 level images.  Returns (struct, keepalive)."""
+    nl = len(pyr_l)
+    kl = np.ascontiguousarray(kl, KP_DTYPE)
+    kr = np.ascontiguousarray(kr, KP_DTYPE)
+    dl = np.ascontiguousarray(dl, np.uint8)
+    dr = np.ascontiguousarray(dr, np.uint8)
+    pyr_l = [np.ascontiguousarray(p) for p in pyr_l]
+    pyr_r = [np.ascontiguousarray(p) for p in pyr_r]
+    pl = (C.c_void_p * nl)(*[p.ctypes.data for p in pyr_l])
+    pr = (C.c_void_p * nl)(*[p.ctypes.data for p in pyr_r])
+    lw = np.array([p.shape[1] for p in pyr_l], np.int32)
+    lh = np.array([p.shape[0] for p in pyr_l], np.int32)
+    sl = np.array([p.strides[0] for p in pyr_l], np.int64)
+    sr = np.array([p.strides[0] for p in pyr_r], np.int64)
+    sc = np.ascontiguousarray(scale, np.float32)
+    isc = np.ascontiguousarray(inv_scale, np.float32)
+    s = StereoInput(len(kl), len(kr), kl.ctypes.data, kr.ctypes.data, dl.ctypes.data, dr.ctypes.data, nl,
+                    sc.ctypes.data, isc.ctypes.data, C.cast(pl, C.c_void_p), C.cast(pr, C.c_void_p),
+                    lw.ctypes.data, lh.ctypes.data, sl.ctypes.data, sr.ctypes.data, bf, fx)
+    keep = (kl, kr, dl, dr, pyr_l, pyr_r, pl, pr, lw, lh, sl, sr, sc, isc)
+    return s, keep
+
+
+def compute_stereo_matches(kl, dl, kr, dr, pyr_l, pyr_r, scale, inv_scale, bf, fx):
+    s, keep = make_stereo_input(kl, dl, kr, dr, pyr_l, pyr_r, scale, inv_scale, bf, fx)
+    ur = np.empty(max(len(kl), 1), np.float32)
+    dp = np.empty(max(len(kl), 1), np.float32)
+    ncmp = C.c_uint64()
+    lib().oracle_compute_stereo_matches(C.byref(s), _p(ur), _p(dp), C.byref(ncmp))
+    return ur[:len(kl)].copy(), dp[:len(kl)].copy(), ncmp.value
+
+
+def knn2(queries: np.ndarray, database: np.ndarray, offset=0, nthreads=1):
+    q = np.ascontiguousarray(queries, np.uint8)
+    d = np.ascontiguousarray(database, np.uint8)
+    od = np.empty((len(q), 2), np.uint16)
+    oi = np.empty((len(q), 2), np.int32)
+    lib().oracle_knn2(_p(q), C.c_int64(len(q)), _p(d), C.c_int64(len(d)), C.c_int32(offset), _p(od), _p(oi),
+                      C.c_int(nthreads))
+    return od, oi
+
+
+def extract_many(params: Params, imgs: np.ndarray, nthreads: int) -> int:
+    imgs = np.ascontiguousarray(imgs)
+    n, h, w = imgs.shape
+    return int(lib().oracle_extract_many(C.byref(params), _p(imgs), C.c_size_t(imgs.strides[0]), C.c_int(w),
+                                         C.c_int(h), C.c_size_t(imgs.strides[1]), C.c_int(n), C.c_int(nthreads)))
