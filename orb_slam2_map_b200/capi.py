@@ -1,0 +1,327 @@
+"""ctypes view of liborbx.so (the C ABI in include/orbx.h).
+
+This is plumbing for tests and bench.py: the product is the shared library and the C++ wrapper
+classes in orb_slam2_map_b200/host/.  There is no CPU fallback — if the library is missing or no
+CUDA device is present, calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG_DIR, "liborbx.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"),
+                     ("response", "<f4"), ("octave", "<i4"), ("class_id", "<i4")])
+PROJ_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("radius", "<f4"), ("min_level", "<i4"),
+                       ("max_level", "<i4"), ("u_right", "<f4"), ("max_right_err", "<f4"),
+                       ("angle", "<f4"), ("level_lo", "<i4"), ("level_hi", "<i4")])
+
+PROJ_LOCALMAP, PROJ_LASTFRAME, PROJ_KEYFRAME, PROJ_SIM3 = 0, 1, 2, 3
+
+
+class OrbxError(RuntimeError):
+    pass
+
+
+class Params(C.Structure):
+    _fields_ = [("nfeatures", C.c_int32), ("scale_factor", C.c_float), ("nlevels", C.c_int32),
+                ("ini_th_fast", C.c_int32), ("min_th_fast", C.c_int32)]
+
+
+class FrameStruct(C.Structure):
+    _fields_ = [("n", C.c_int32), ("keys_un", C.c_void_p), ("descriptors", C.c_void_p),
+                ("min_x", C.c_float), ("max_x", C.c_float), ("min_y", C.c_float), ("max_y", C.c_float),
+                ("u_right", C.c_void_p), ("scale_factors", C.c_void_p), ("nlevels", C.c_int32)]
+
+
+class StereoInput(C.Structure):
+    _fields_ = [("n_left", C.c_int32), ("n_right", C.c_int32),
+                ("keys_left", C.c_void_p), ("keys_right", C.c_void_p),
+                ("desc_left", C.c_void_p), ("desc_right", C.c_void_p),
+                ("nlevels", C.c_int32),
+                ("scale_factors", C.c_void_p), ("inv_scale_factors", C.c_void_p),
+                ("pyr_left", C.c_void_p), ("pyr_right", C.c_void_p),
+                ("level_width", C.c_void_p), ("level_height", C.c_void_p),
+                ("pyr_stride_left", C.c_void_p), ("pyr_stride_right", C.c_void_p),
+                ("bf", C.c_float), ("fx", C.c_float)]
+
+
+EXPORTS = [
+    "orbx_last_error", "orbx_device_count", "orbx_create", "orbx_destroy", "orbx_sync", "orbx_get_tables",
+    "orbx_keypoint_capacity", "orbx_extract", "orbx_extract_batch", "orbx_download", "orbx_get_level",
+    "orbx_get_candidates", "orbx_search_init_pairs", "orbx_extract_stereo_batch",
+    "orbm_descriptor_distance", "orbm_search_for_initialization", "orbm_search_by_projection",
+    "orbm_compute_stereo_matches", "orbm_knn2_device", "orbm_knn2_merge_device",
+]
+
+_LIB = None
+
+
+def build(verbose: bool = False) -> str:
+    """Compile liborbx.so in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    out = None if verbose else subprocess.DEVNULL
+    subprocess.check_call(["make", "-C", os.path.join(PKG_DIR, "csrc"), "-j4"], stdout=out)
+    return LIB_PATH
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise OrbxError(f"{LIB_PATH} is missing: build it with `make -C orb_slam2_map_b200/csrc` "
+                            "(there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        L.orbx_last_error.restype = C.c_char_p
+        L.orbx_create.argtypes = [C.POINTER(Params), C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                  C.POINTER(C.c_void_p)]
+        L.orbx_destroy.argtypes = [C.c_void_p]
+        L.orbx_sync.argtypes = [C.c_void_p]
+        L.orbx_get_tables.argtypes = [C.c_void_p] + [C.c_void_p] * 5
+        L.orbx_keypoint_capacity.argtypes = [C.c_void_p]
+        L.orbx_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_void_p, C.c_void_p,
+                                   C.c_int, C.POINTER(C.c_int)]
+        L.orbx_extract_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int,
+                                         C.c_int, C.c_int]
+        L.orbx_download.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.orbx_get_level.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t,
+                                     C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.orbx_get_candidates.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+        L.orbx_search_init_pairs.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_void_p,
+                                             C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
+        L.orbx_extract_stereo_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int,
+                                                C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p,
+                                                C.c_void_p, C.c_int, C.POINTER(C.c_uint64)]
+        L.orbm_descriptor_distance.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.orbm_search_for_initialization.argtypes = [C.POINTER(FrameStruct), C.POINTER(FrameStruct), C.c_void_p,
+                                                     C.c_void_p, C.c_int, C.c_float, C.c_int, C.POINTER(C.c_int32)]
+        L.orbm_search_by_projection.argtypes = [C.c_int, C.POINTER(FrameStruct), C.c_void_p, C.c_void_p, C.c_int,
+                                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                                C.c_float, C.c_int, C.POINTER(C.c_int32)]
+        L.orbm_compute_stereo_matches.argtypes = [C.POINTER(StereoInput), C.c_void_p, C.c_void_p,
+                                                  C.POINTER(C.c_uint64)]
+        L.orbm_knn2_device.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p,
+                                       C.c_void_p, C.c_void_p]
+        L.orbm_knn2_merge_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p,
+                                             C.c_void_p]
+        _LIB = L
+    return _LIB
+
+
+def check(rc: int):
+    if rc != 0:
+        raise OrbxError(f"liborbx error {rc}: {lib().orbx_last_error().decode()}")
+
+
+def _p(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data_as(C.c_void_p)
+    return C.c_void_p(int(a))
+
+
+class Extractor:
+    """Owns one orbx_handle.  Mirrors ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)
+    (reference include/ORBextractor.h:51) plus the batch / device-resident entry points."""
+
+    def __init__(self, nfeatures=1000, scale=1.2, nlevels=8, ini_th=20, min_th=7, max_width=640, max_height=480,
+                 chunk_frames=1, result_slots=2, device=0, stream=None):
+        self.params = Params(nfeatures, scale, nlevels, ini_th, min_th)
+        self.h = C.c_void_p()
+        self.nlevels = nlevels
+        check(lib().orbx_create(C.byref(self.params), max_width, max_height, chunk_frames, result_slots, device,
+                                C.c_void_p(stream) if stream else None, C.byref(self.h)))
+        self.cap = lib().orbx_keypoint_capacity(self.h)
+        self.result_slots = result_slots
+
+    def close(self):
+        if getattr(self, "h", None) and self.h.value:
+            lib().orbx_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def sync(self):
+        check(lib().orbx_sync(self.h))
+
+    def tables(self):
+        n = self.nlevels
+        sc, isc, s2, is2 = (np.empty(n, np.float32) for _ in range(4))
+        fpl = np.empty(n, np.int32)
+        check(lib().orbx_get_tables(self.h, _p(sc), _p(isc), _p(s2), _p(is2), _p(fpl)))
+        return dict(scale=sc, inv_scale=isc, sigma2=s2, inv_sigma2=is2, features_per_level=fpl)
+
+    def extract(self, img: np.ndarray):
+        """ORBextractor::operator() on one host image -> (keypoints[KP_DTYPE], descriptors[n,32])."""
+        img = np.ascontiguousarray(img, np.uint8)
+        kps = np.zeros(self.cap, KP_DTYPE)
+        desc = np.zeros((self.cap, 32), np.uint8)
+        n = C.c_int(0)
+        check(lib().orbx_extract(self.h, _p(img), img.shape[1], img.shape[0], img.strides[0], _p(kps), _p(desc),
+                                 self.cap, C.byref(n)))
+        return kps[:n.value].copy(), desc[:n.value].copy()
+
+    def extract_batch(self, images, nframes=None, width=None, height=None, frame_stride=None, row_stride=None,
+                      on_device=False, first_slot=0):
+        """images: numpy [n,h,w] (host) or a raw device pointer (int) with explicit geometry."""
+        if isinstance(images, np.ndarray):
+            assert images.ndim == 3 and images.dtype == np.uint8 and images.strides[2] == 1
+            nframes, height, width = images.shape
+            frame_stride, row_stride = images.strides[0], images.strides[1]
+            ptr = images.ctypes.data
+        else:
+            ptr = int(images)
+        check(lib().orbx_extract_batch(self.h, C.c_void_p(ptr), frame_stride, row_stride, width, height, nframes,
+                                       int(on_device), first_slot))
+
+    def download(self, first_slot, nframes, want_kps=True, want_desc=True, out=None):
+        counts = np.zeros(nframes, np.int32)
+        if out is not None:
+            kps, desc = out
+        else:
+            kps = np.zeros((nframes, self.cap), KP_DTYPE) if want_kps else None
+            desc = np.zeros((nframes, self.cap, 32), np.uint8) if want_desc else None
+        check(lib().orbx_download(self.h, first_slot, nframes, _p(kps), _p(desc), _p(counts), self.cap))
+        return kps, desc, counts
+
+    def level(self, frame, level, blurred=False, border=0):
+        w, h = C.c_int(), C.c_int()
+        check(lib().orbx_get_level(self.h, frame, level, int(blurred), border, None, 0, C.byref(w), C.byref(h)))
+        out = np.empty((h.value + 2 * border, w.value + 2 * border), np.uint8)
+        check(lib().orbx_get_level(self.h, frame, level, int(blurred), border, _p(out), out.strides[0], C.byref(w),
+                                   C.byref(h)))
+        return out
+
+    def candidates(self, frame, level, cap=1 << 18):
+        out = np.empty((cap, 3), np.float32)
+        n = C.c_int()
+        check(lib().orbx_get_candidates(self.h, frame, level, _p(out), cap, C.byref(n)))
+        assert n.value <= cap
+        return out[:n.value].copy()
+
+    def search_init_pairs(self, first_slot, npairs, window=100, nnratio=0.9, check_ori=True, fetch=True):
+        ncmp = C.c_uint64()
+        if fetch:
+            m12 = np.full((npairs, self.cap), -1, np.int32)
+            nm = np.zeros(npairs, np.int32)
+            check(lib().orbx_search_init_pairs(self.h, first_slot, npairs, window, nnratio, int(check_ori), _p(m12),
+                                               _p(nm), self.cap, C.byref(ncmp)))
+            return m12, nm, ncmp.value
+        check(lib().orbx_search_init_pairs(self.h, first_slot, npairs, window, nnratio, int(check_ori), None, None,
+                                           self.cap, None))
+        return None
+
+    def extract_stereo_batch(self, left, right, bf, fx, nframes=None, width=None, height=None, frame_stride=None,
+                             row_stride=None, on_device=False, first_slot=0, fetch=True):
+        if isinstance(left, np.ndarray):
+            assert left.shape == right.shape and left.strides == right.strides
+            nframes, height, width = left.shape
+            frame_stride, row_stride = left.strides[0], left.strides[1]
+            lp, rp = left.ctypes.data, right.ctypes.data
+        else:
+            lp, rp = int(left), int(right)
+        ncmp = C.c_uint64()
+        if fetch:
+            ur = np.zeros((nframes, self.cap), np.float32)
+            dp = np.zeros((nframes, self.cap), np.float32)
+            check(lib().orbx_extract_stereo_batch(self.h, C.c_void_p(lp), C.c_void_p(rp), frame_stride, row_stride,
+                                                  width, height, nframes, int(on_device), first_slot, bf, fx, _p(ur),
+                                                  _p(dp), self.cap, C.byref(ncmp)))
+            return ur, dp, ncmp.value
+        check(lib().orbx_extract_stereo_batch(self.h, C.c_void_p(lp), C.c_void_p(rp), frame_stride, row_stride, width,
+                                              height, nframes, int(on_device), first_slot, bf, fx, None, None,
+                                              self.cap, None))
+        return None
+
+
+class FrameData:
+    """numpy arrays behind an orbm_frame."""
+
+    def __init__(self, kps, desc, width, height, u_right=None, scale_factors=None, bounds=None):
+        self.kps = np.ascontiguousarray(kps, KP_DTYPE)
+        self.desc = np.ascontiguousarray(desc, np.uint8)
+        self.u_right = None if u_right is None else np.ascontiguousarray(u_right, np.float32)
+        self.sf = None if scale_factors is None else np.ascontiguousarray(scale_factors, np.float32)
+        b = bounds if bounds is not None else (0.0, float(width), 0.0, float(height))
+        self.c = FrameStruct(len(self.kps), self.kps.ctypes.data, self.desc.ctypes.data, b[0], b[1], b[2], b[3],
+                             None if self.u_right is None else self.u_right.ctypes.data,
+                             None if self.sf is None else self.sf.ctypes.data,
+                             0 if self.sf is None else len(self.sf))
+
+
+def descriptor_distance(a: np.ndarray, b: np.ndarray) -> np.ndarray:
+    a = np.ascontiguousarray(a, np.uint8).reshape(-1, 32)
+    b = np.ascontiguousarray(b, np.uint8).reshape(-1, 32)
+    out = np.empty(len(a), np.int32)
+    check(lib().orbm_descriptor_distance(_p(a), _p(b), len(a), _p(out)))
+    return out
+
+
+def search_for_initialization(f1: FrameData, f2: FrameData, prev_matched, window=100, nnratio=0.9, check_ori=True):
+    pm = np.ascontiguousarray(prev_matched, np.float32).copy()
+    m12 = np.empty(max(f1.c.n, 1), np.int32)
+    nm = C.c_int32()
+    check(lib().orbm_search_for_initialization(C.byref(f1.c), C.byref(f2.c), _p(pm), _p(m12), window, nnratio,
+                                               int(check_ori), C.byref(nm)))
+    return nm.value, m12[:f1.c.n].copy(), pm
+
+
+def search_by_projection(variant, f: FrameData, queries, qdesc, blocks, occupied, th_dist, nnratio=0.6,
+                         check_ori=True):
+    q = np.ascontiguousarray(queries, PROJ_DTYPE)
+    qd = np.ascontiguousarray(qdesc, np.uint8)
+    nq = len(q)
+    occ = np.ascontiguousarray(occupied, np.uint8).copy()
+    blk = None if blocks is None else np.ascontiguousarray(blocks, np.uint8)
+    assigned = np.empty(max(f.c.n, 1), np.int32)
+    bi = np.empty(max(nq, 1), np.int32)
+    bd = np.empty(max(nq, 1), np.int32)
+    nm = C.c_int32()
+    check(lib().orbm_search_by_projection(variant, C.byref(f.c), _p(q), _p(qd), nq, _p(blk), _p(occ), _p(assigned),
+                                          _p(bi), _p(bd), th_dist, nnratio, int(check_ori), C.byref(nm)))
+    return nm.value, assigned[:f.c.n].copy(), bi[:nq].copy(), bd[:nq].copy(), occ
+
+
+def compute_stereo_matches(kl, dl, kr, dr, pyr_l, pyr_r, scale, inv_scale, bf, fx):
+    nl = len(pyr_l)
+    kl = np.ascontiguousarray(kl, KP_DTYPE)
+    kr = np.ascontiguousarray(kr, KP_DTYPE)
+    dl = np.ascontiguousarray(dl, np.uint8)
+    dr = np.ascontiguousarray(dr, np.uint8)
+    pyr_l = [np.ascontiguousarray(p) for p in pyr_l]
+    pyr_r = [np.ascontiguousarray(p) for p in pyr_r]
+    pl = (C.c_void_p * nl)(*[p.ctypes.data for p in pyr_l])
+    pr = (C.c_void_p * nl)(*[p.ctypes.data for p in pyr_r])
+    lw = np.array([p.shape[1] for p in pyr_l], np.int32)
+    lh = np.array([p.shape[0] for p in pyr_l], np.int32)
+    sl = np.array([p.strides[0] for p in pyr_l], np.int64)
+    sr = np.array([p.strides[0] for p in pyr_r], np.int64)
+    sc = np.ascontiguousarray(scale, np.float32)
+    isc = np.ascontiguousarray(inv_scale, np.float32)
+    s = StereoInput(len(kl), len(kr), kl.ctypes.data, kr.ctypes.data, dl.ctypes.data, dr.ctypes.data, nl,
+                    sc.ctypes.data, isc.ctypes.data, C.cast(pl, C.c_void_p), C.cast(pr, C.c_void_p),
+                    lw.ctypes.data, lh.ctypes.data, sl.ctypes.data, sr.ctypes.data, bf, fx)
+    ur = np.empty(max(len(kl), 1), np.float32)
+    dp = np.empty(max(len(kl), 1), np.float32)
+    ncmp = C.c_uint64()
+    check(lib().orbm_compute_stereo_matches(C.byref(s), _p(ur), _p(dp), C.byref(ncmp)))
+    return ur[:len(kl)].copy(), dp[:len(kl)].copy(), ncmp.value
+
+
+def knn2_device(q_ptr, nq, db_ptr, ndb, offset, out_dist_ptr, out_idx_ptr, stream=None):
+    check(lib().orbm_knn2_device(C.c_void_p(q_ptr), nq, C.c_void_p(db_ptr), ndb, offset, C.c_void_p(out_dist_ptr),
+                                 C.c_void_p(out_idx_ptr), C.c_void_p(stream) if stream else None))
+
+
+def knn2_merge_device(pd_ptr, pi_ptr, nparts, nq, od_ptr, oi_ptr, stream=None):
+    check(lib().orbm_knn2_merge_device(C.c_void_p(pd_ptr), C.c_void_p(pi_ptr), nparts, nq, C.c_void_p(od_ptr),
+                                       C.c_void_p(oi_ptr), C.c_void_p(stream) if stream else None))

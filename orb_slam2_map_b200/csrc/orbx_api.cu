@@ -1,0 +1,340 @@
+// orbx_api.cu — C ABI of liborbx.so: handle life cycle and the extractor entry points
+// (declared in include/orbx.h; each cites the reference function it stands in for).
+
+#include "orbx_internal.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+static thread_local char g_err[512] = "";
+
+void orbx_set_error(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+static inline int cv_roundf(float v) { return (int)lrintf(v); }
+static inline int cv_round(double v) { return (int)lrint(v); }
+
+// ORBextractor::ORBextractor tables (reference src/ORBextractor.cc:410-470)
+static void compute_tables(orbx_handle* h)
+{
+    const int nl = h->params.nlevels;
+    const double scaleFactor = (double)h->params.scale_factor;   // member is a double holding a float
+    h->scale.assign(nl, 1.f); h->sigma2.assign(nl, 1.f);
+    for (int i = 1; i < nl; ++i) {
+        h->scale[i] = (float)(h->scale[i - 1] * scaleFactor);
+        h->sigma2[i] = h->scale[i] * h->scale[i];
+    }
+    h->invScale.resize(nl); h->invSigma2.resize(nl);
+    for (int i = 0; i < nl; ++i) { h->invScale[i] = 1.0f / h->scale[i]; h->invSigma2[i] = 1.0f / h->sigma2[i]; }
+    h->perLevel.assign(nl, 0);
+    const float factor = (float)(1.0f / scaleFactor);
+    float nDesired = h->params.nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)nl));
+    int sum = 0;
+    for (int l = 0; l < nl - 1; ++l) {
+        h->perLevel[l] = cv_roundf(nDesired);
+        sum += h->perLevel[l];
+        nDesired *= factor;
+    }
+    h->perLevel[nl - 1] = std::max(h->params.nfeatures - sum, 0);
+    // umax: end of each row of the circular patch (src/ORBextractor.cc:452-469)
+    const int HALF = 15;
+    int v, v0;
+    const int vmax = (int)floorf(HALF * sqrtf(2.f) / 2 + 1);
+    const int vmin = (int)ceilf(HALF * sqrtf(2.f) / 2);
+    const double hp2 = HALF * HALF;
+    for (v = 0; v < 16; ++v) h->umax[v] = 0;
+    for (v = 0; v <= vmax; ++v) h->umax[v] = cv_round(sqrt(hp2 - v * v));
+    for (v = HALF, v0 = 0; v >= vmin; --v) {
+        while (h->umax[v0] == h->umax[v0 + 1]) ++v0;
+        h->umax[v] = v0;
+        ++v0;
+    }
+}
+
+extern "C" {
+
+const char* orbx_last_error(void) { return g_err; }
+
+int orbx_device_count(void)
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) { orbx_set_error("cudaGetDeviceCount: %s", cudaGetErrorString(e)); return ORBX_E_CUDA; }
+    return n;
+}
+
+int orbx_create(const orbx_params* params, int max_width, int max_height, int chunk_frames,
+                int result_slots, int device, void* stream, orbx_handle** out)
+{
+    if (!params || !out) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
+    if (params->nlevels < 1 || params->nlevels > ORBX_MAX_LEVELS || params->nfeatures < 1 ||
+        params->scale_factor <= 1.0f || params->min_th_fast < 1 || params->ini_th_fast < params->min_th_fast ||
+        params->ini_th_fast > 254) {
+        orbx_set_error("unsupported ORBextractor parameters (nlevels 1..%d, scale>1, 1<=minTh<=iniTh<255)", ORBX_MAX_LEVELS);
+        return ORBX_E_INVALID;
+    }
+    if (max_width < 64 || max_height < 64 || max_width > 4000 || max_height > 4000 || chunk_frames < 1 || result_slots < 1) {
+        orbx_set_error("bad handle dimensions");
+        return ORBX_E_INVALID;
+    }
+    int ndev = 0;
+    ORBX_CUDA(cudaGetDeviceCount(&ndev));
+    if (ndev <= 0 || device < 0 || device >= ndev) { orbx_set_error("CUDA device %d not available (%d devices); no CPU fallback", device, ndev); return ORBX_E_CUDA; }
+    ORBX_CUDA(cudaSetDevice(device));
+    orbx_handle* h = new orbx_handle();
+    h->params = *params;
+    h->device = device;
+    h->maxW = max_width; h->maxH = max_height;
+    h->chunkFrames = chunk_frames; h->resultSlots = result_slots;
+    h->curW = h->curH = 0;
+    h->dCells = nullptr; h->dCoef = nullptr; h->dBlurTiles = nullptr; h->dKpMap = nullptr; h->nBlurTiles = 0;
+    h->dLevel0 = h->dRaw = h->dBlur = nullptr;
+    h->dCand = h->dKeysA = h->dKeysB = nullptr; h->dCellSeg = nullptr; h->dLevelCandCount = nullptr;
+    h->dLevelKps = nullptr; h->dLevelKpCount = nullptr; h->dStatus = nullptr;
+    h->dKps = nullptr; h->dDesc = nullptr; h->dCount = nullptr; h->dSlotLevelCount = nullptr;
+    h->dGridStart = nullptr; h->dGridIdx = nullptr; h->dMatches12 = nullptr; h->dNMatches = nullptr;
+    h->dNCompares = nullptr; h->dURight = nullptr; h->dDepth = nullptr; h->dMatchScratch = nullptr;
+    h->matchScratchPerPair = 0;
+    h->hStage = nullptr; h->hStageBytes = 0;
+    h->lastChunkFrames = 0;
+    if (stream) { h->stream = (cudaStream_t)stream; h->ownStream = false; }
+    else { ORBX_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)); h->ownStream = true; }
+    compute_tables(h);
+    // per-frame keypoint capacity for the largest shape: sum_l max(N_l+3, 4*nIni)+1, nIni from the
+    // aspect ratio of the maximum image (per-level ratios differ by rounding; +8 slack per level)
+    {
+        int cap = 0;
+        for (int l = 0; l < params->nlevels; ++l) {
+            const int w = cv_roundf((float)max_width * h->invScale[l]) - 32, hh = cv_roundf((float)max_height * h->invScale[l]) - 32;
+            int nIni = (w > 0 && hh > 0) ? (int)roundf((float)w / hh) : 1;
+            if (nIni < 1) nIni = 1;
+            cap += std::max(h->perLevel[l] + 3, 4 * (nIni + 1)) + 1;
+        }
+        h->kpCap = (cap + 7) & ~7;
+    }
+    const size_t R = (size_t)result_slots;
+    ORBX_CUDA(cudaMalloc((void**)&h->dKps, R * h->kpCap * sizeof(orbx_keypoint)));
+    ORBX_CUDA(cudaMalloc((void**)&h->dDesc, R * h->kpCap * 32));
+    ORBX_CUDA(cudaMalloc((void**)&h->dCount, R * sizeof(int)));
+    ORBX_CUDA(cudaMalloc((void**)&h->dSlotLevelCount, R * ORBX_MAX_LEVELS * sizeof(int)));
+    ORBX_CUDA(cudaMalloc((void**)&h->dStatus, sizeof(int)));
+    ORBX_CUDA(cudaMemset(h->dCount, 0, R * sizeof(int)));
+    ORBX_CUDA(cudaMemset(h->dStatus, 0, sizeof(int)));
+    *out = h;
+    return ORBX_OK;
+}
+
+int orbx_destroy(orbx_handle* h)
+{
+    if (!h) return ORBX_OK;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    void* ptrs[] = {h->dCells, h->dCoef, h->dBlurTiles, h->dKpMap, h->dLevel0, h->dRaw, h->dBlur, h->dCand, h->dKeysA,
+                    h->dKeysB, h->dCellSeg, h->dLevelCandCount, h->dLevelKps, h->dLevelKpCount, h->dStatus, h->dKps,
+                    h->dDesc, h->dCount, h->dSlotLevelCount, h->dGridStart, h->dGridIdx, h->dMatches12, h->dNMatches,
+                    h->dNCompares, h->dURight, h->dDepth, h->dMatchScratch};
+    for (void* p : ptrs) if (p) cudaFree(p);
+    if (h->hStage) cudaFreeHost(h->hStage);
+    if (h->ownStream) cudaStreamDestroy(h->stream);
+    delete h;
+    return ORBX_OK;
+}
+
+int orbx_sync(orbx_handle* h)
+{
+    if (!h) { orbx_set_error("null handle"); return ORBX_E_INVALID; }
+    ORBX_CUDA(cudaSetDevice(h->device));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    int st = 0;
+    ORBX_CUDA(cudaMemcpy(&st, h->dStatus, sizeof(int), cudaMemcpyDeviceToHost));
+    if (st) {
+        cudaMemset(h->dStatus, 0, sizeof(int));
+        orbx_set_error("device-side capacity overflow (flags 0x%x): quadtree node/keypoint table too small", st);
+        return ORBX_E_CAPACITY;
+    }
+    return ORBX_OK;
+}
+
+int orbx_get_tables(const orbx_handle* h, float* scale, float* inv_scale, float* sigma2,
+                    float* inv_sigma2, int32_t* features_per_level)
+{
+    if (!h) { orbx_set_error("null handle"); return ORBX_E_INVALID; }
+    for (int i = 0; i < h->params.nlevels; ++i) {
+        if (scale) scale[i] = h->scale[i];
+        if (inv_scale) inv_scale[i] = h->invScale[i];
+        if (sigma2) sigma2[i] = h->sigma2[i];
+        if (inv_sigma2) inv_sigma2[i] = h->invSigma2[i];
+        if (features_per_level) features_per_level[i] = h->perLevel[i];
+    }
+    return ORBX_OK;
+}
+
+int orbx_keypoint_capacity(const orbx_handle* h) { return h ? h->kpCap : ORBX_E_INVALID; }
+
+static int ensure_stage(orbx_handle* h, size_t bytes)
+{
+    if (h->hStageBytes >= bytes) return ORBX_OK;
+    if (h->hStage) cudaFreeHost(h->hStage);
+    h->hStage = nullptr; h->hStageBytes = 0;
+    ORBX_CUDA(cudaMallocHost(&h->hStage, bytes));
+    h->hStageBytes = bytes;
+    return ORBX_OK;
+}
+
+int orbx_extract_batch(orbx_handle* h, const uint8_t* images, size_t frame_stride,
+                       size_t row_stride, int width, int height, int nframes,
+                       int images_on_device, int first_slot)
+{
+    if (!h || !images) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
+    if (width <= 0 || height <= 0 || nframes <= 0) return ORBX_OK;   // empty image: silent return
+    if (width < 64 || height < 64) { orbx_set_error("image smaller than 64x64 is outside the extractor's domain"); return ORBX_E_INVALID; }
+    if (row_stride < (size_t)width) { orbx_set_error("row_stride < width"); return ORBX_E_INVALID; }
+    if (first_slot < 0 || first_slot + nframes > h->resultSlots) { orbx_set_error("slots [%d,%d) exceed result store (%d)", first_slot, first_slot + nframes, h->resultSlots); return ORBX_E_CAPACITY; }
+    ORBX_CUDA(cudaSetDevice(h->device));
+    int rc = orbx_setup_shape(h, width, height);
+    if (rc) return rc;
+    const bool direct = images_on_device && (row_stride % 4 == 0) && (((uintptr_t)images) % 4 == 0) && (frame_stride % 4 == 0);
+    for (int f0 = 0; f0 < nframes; f0 += h->chunkFrames) {
+        const int nf = std::min(h->chunkFrames, nframes - f0);
+        const uint8_t* src = images + (size_t)f0 * frame_stride;
+        Level0 l0;
+        if (direct) { l0.base = src; l0.frameStride = (long long)frame_stride; l0.pitch = (int)row_stride; }
+        else {
+            const cudaMemcpyKind kind = images_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+            if (frame_stride == row_stride * (size_t)height) {
+                ORBX_CUDA(cudaMemcpy2DAsync(h->dLevel0, h->l0Pitch, src, row_stride, width, (size_t)height * nf, kind, h->stream));
+                // frames are row-contiguous: one tall 2-D copy; workspace frame stride follows
+                l0.frameStride = (long long)h->l0Pitch * height;
+            } else {
+                for (int f = 0; f < nf; ++f)
+                    ORBX_CUDA(cudaMemcpy2DAsync(h->dLevel0 + (size_t)f * h->l0FrameBytes, h->l0Pitch, src + (size_t)f * frame_stride,
+                                                row_stride, width, height, kind, h->stream));
+                l0.frameStride = h->l0FrameBytes;
+            }
+            l0.base = h->dLevel0; l0.pitch = h->l0Pitch;
+        }
+        rc = orbx_run_chunk(h, l0, nf, first_slot + f0);
+        if (rc) return rc;
+    }
+    return ORBX_OK;
+}
+
+int orbx_download(orbx_handle* h, int first_slot, int nframes, orbx_keypoint* kps, uint8_t* desc,
+                  int32_t* counts, int capacity)
+{
+    if (!h) { orbx_set_error("null handle"); return ORBX_E_INVALID; }
+    if (nframes <= 0) return ORBX_OK;
+    if (first_slot < 0 || first_slot + nframes > h->resultSlots) { orbx_set_error("slot range out of bounds"); return ORBX_E_INVALID; }
+    ORBX_CUDA(cudaSetDevice(h->device));
+    std::vector<int> cnt(nframes);
+    ORBX_CUDA(cudaMemcpyAsync(cnt.data(), h->dCount + first_slot, nframes * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    int rc = orbx_sync(h);
+    if (rc) return rc;
+    int maxc = 0;
+    for (int i = 0; i < nframes; ++i) { maxc = std::max(maxc, cnt[i]); if (counts) counts[i] = cnt[i]; }
+    if ((kps || desc) && maxc > capacity) { orbx_set_error("capacity %d < %d keypoints", capacity, maxc); return ORBX_E_CAPACITY; }
+    const int rows = std::min(capacity, h->kpCap);
+    if (kps)
+        ORBX_CUDA(cudaMemcpy2DAsync(kps, (size_t)capacity * sizeof(orbx_keypoint), h->dKps + (size_t)first_slot * h->kpCap,
+                                    (size_t)h->kpCap * sizeof(orbx_keypoint), (size_t)rows * sizeof(orbx_keypoint), nframes,
+                                    cudaMemcpyDeviceToHost, h->stream));
+    if (desc)
+        ORBX_CUDA(cudaMemcpy2DAsync(desc, (size_t)capacity * 32, h->dDesc + (size_t)first_slot * h->kpCap * 32,
+                                    (size_t)h->kpCap * 32, (size_t)rows * 32, nframes, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    return ORBX_OK;
+}
+
+int orbx_extract(orbx_handle* h, const uint8_t* image, int width, int height, size_t row_stride,
+                 orbx_keypoint* kps, uint8_t* desc, int capacity, int* n)
+{
+    if (!h) { orbx_set_error("null handle"); return ORBX_E_INVALID; }
+    if (width <= 0 || height <= 0 || !image) return ORBX_OK;     // _image.empty(): return, outputs untouched
+    int rc = orbx_extract_batch(h, image, row_stride * (size_t)height, row_stride, width, height, 1, 0, 0);
+    if (rc) return rc;
+    int32_t cnt = 0;
+    rc = orbx_download(h, 0, 1, nullptr, nullptr, &cnt, 0);
+    if (rc) return rc;
+    if (cnt > capacity) { orbx_set_error("capacity %d < %d keypoints", capacity, cnt); return ORBX_E_CAPACITY; }
+    if (cnt > 0) {
+        if (kps) ORBX_CUDA(cudaMemcpyAsync(kps, h->dKps, (size_t)cnt * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, h->stream));
+        if (desc) ORBX_CUDA(cudaMemcpyAsync(desc, h->dDesc, (size_t)cnt * 32, cudaMemcpyDeviceToHost, h->stream));
+        ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    }
+    if (n) *n = cnt;
+    return ORBX_OK;
+}
+
+int orbx_get_level(orbx_handle* h, int frame, int level, int blurred, int border, uint8_t* dst,
+                   size_t dst_stride, int* width, int* height)
+{
+    if (!h) { orbx_set_error("null handle"); return ORBX_E_INVALID; }
+    if (h->lastChunkFrames <= 0 || frame < 0 || frame >= h->lastChunkFrames || level < 0 || level >= h->geom.nlevels) {
+        orbx_set_error("no such frame/level in the last chunk"); return ORBX_E_STATE;
+    }
+    if (border < 0 || border > 64) { orbx_set_error("border out of range"); return ORBX_E_INVALID; }
+    ORBX_CUDA(cudaSetDevice(h->device));
+    const LevelGeom& L = h->geom.L[level];
+    if (width) *width = L.w;
+    if (height) *height = L.h;
+    if (!dst) return ORBX_OK;
+    if (dst_stride < (size_t)(L.w + 2 * border)) { orbx_set_error("dst_stride too small"); return ORBX_E_INVALID; }
+    const uint8_t* src; size_t sp;
+    if (blurred) { src = h->dBlur + (size_t)frame * h->geom.pyrFrameBytes + L.off; sp = L.pitch; }
+    else if (level == 0) { src = h->lastL0.base + (size_t)frame * h->lastL0.frameStride; sp = h->lastL0.pitch; }
+    else { src = h->dRaw + (size_t)frame * h->geom.pyrFrameBytes + L.off; sp = L.pitch; }
+    ORBX_CUDA(cudaMemcpy2DAsync(dst + (size_t)border * dst_stride + border, dst_stride, src, sp, L.w, L.h, cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    if (border > 0) {
+        // copyMakeBorder(..., BORDER_REFLECT_101) of the level (src/ORBextractor.cc:1122-1128), host side
+        auto refl = [](int i, int n) { if (n == 1) return 0; while (i < 0 || i >= n) i = (i < 0) ? -i : 2 * (n - 1) - i; return i; };
+        uint8_t* core = dst + (size_t)border * dst_stride + border;
+        for (int y = 0; y < L.h; ++y) {
+            uint8_t* row = core + (size_t)y * dst_stride;
+            for (int x = 1; x <= border; ++x) { row[-x] = row[refl(-x, L.w)]; row[L.w - 1 + x] = row[refl(L.w - 1 + x, L.w)]; }
+        }
+        for (int y = 1; y <= border; ++y) {
+            memcpy(dst + (size_t)(border - y) * dst_stride, dst + (size_t)(border + refl(-y, L.h)) * dst_stride, L.w + 2 * border);
+            memcpy(dst + (size_t)(border + L.h - 1 + y) * dst_stride, dst + (size_t)(border + refl(L.h - 1 + y, L.h)) * dst_stride, L.w + 2 * border);
+        }
+    }
+    return ORBX_OK;
+}
+
+int orbx_get_candidates(orbx_handle* h, int frame, int level, float* xyr, int capacity, int* n)
+{
+    if (!h || !n) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
+    if (h->lastChunkFrames <= 0 || frame < 0 || frame >= h->lastChunkFrames || level < 0 || level >= h->geom.nlevels) {
+        orbx_set_error("no such frame/level in the last chunk"); return ORBX_E_STATE;
+    }
+    ORBX_CUDA(cudaSetDevice(h->device));
+    const Geom& g = h->geom;
+    const LevelGeom& L = g.L[level];
+    std::vector<int2> seg(L.nCells);
+    ORBX_CUDA(cudaMemcpyAsync(seg.data(), h->dCellSeg + (size_t)frame * g.ncells + L.cellBeg, L.nCells * sizeof(int2), cudaMemcpyDeviceToHost, h->stream));
+    unsigned cnt = 0;
+    ORBX_CUDA(cudaMemcpyAsync(&cnt, h->dLevelCandCount + frame * g.nlevels + level, sizeof(unsigned), cudaMemcpyDeviceToHost, h->stream));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    std::vector<uint32_t> c(std::max<unsigned>(cnt, 1));
+    if (cnt) ORBX_CUDA(cudaMemcpy(c.data(), h->dCand + (size_t)frame * g.candTotal + L.candOff, cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    int k = 0;
+    for (int ci = 0; ci < L.nCells; ++ci)
+        for (int i = 0; i < seg[ci].y; ++i, ++k) {
+            if (k < capacity && xyr) {
+                const uint32_t p = c[seg[ci].x + i];
+                xyr[3 * k] = (float)(p & 0xfff); xyr[3 * k + 1] = (float)((p >> 12) & 0xfff); xyr[3 * k + 2] = (float)(p >> 24);
+            }
+        }
+    *n = k;
+    return ORBX_OK;
+}
+
+} // extern "C"

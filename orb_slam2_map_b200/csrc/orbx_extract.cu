@@ -1,0 +1,882 @@
+// orbx_extract.cu — sm_100a kernels for ORBextractor::operator() (reference src/ORBextractor.cc).
+//
+//   K1a pyr_resize_kernel   cv::resize INTER_LINEAR 8U fixed point      (ORBextractor.cc:1120)
+//   K1b blur7_kernel        GaussianBlur 7x7 s=2 REFLECT_101            (ORBextractor.cc:1085-1086)
+//   K2  fast_cells_kernel   per-cell FAST 9/16 + NMS + ini/min retry    (ORBextractor.cc:789-829)
+//   K3  octree_kernel       DistributeOctTree                           (ORBextractor.cc:539-763)
+//   K4  describe_kernel     IC_Angle + computeOrbDescriptor + output    (ORBextractor.cc:77-147,1076-1103)
+//
+// All kernels are batched over the frames of a chunk; every intermediate lives in the handle's
+// device workspace.  Integer arithmetic reproduces OpenCV 4.13 bit for bit;
+// float arithmetic uses explicit round-to-nearest intrinsics so nothing is contracted to FMA.
+
+#include "orbx_internal.h"
+#include "../../include/orbx_pattern.h"
+#include "../../include/orbx_sincos.h"
+
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstring>
+
+typedef uint8_t u8;
+
+// =============================================================================================
+// K1a: one level of the pyramid = bilinear 8U resize of the previous level (OpenCV fixed point:
+// 11-bit coefficients, horizontal sums kept as int, vertical blend ((b*(S>>4))>>16 ... +2)>>2).
+// One thread produces 4 horizontally adjacent pixels and stores them as one 32-bit word.
+// =============================================================================================
+__global__ void __launch_bounds__(256)
+pyr_resize_kernel(const u8* __restrict__ srcBase, long long srcFrameStride, int srcPitch,
+                  u8* __restrict__ dstBase, long long dstFrameStride, int dstPitch,
+                  int dw, int dh, const int2* __restrict__ cx, const int2* __restrict__ cy)
+{
+    const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
+    const int y = blockIdx.y * 8 + threadIdx.y;
+    if (x4 >= dw || y >= dh) return;
+    const u8* src = srcBase + (long long)blockIdx.z * srcFrameStride;
+    u8* dst = dstBase + (long long)blockIdx.z * dstFrameStride;
+    const int2 cyv = cy[y];
+    const u8* r0 = src + (long long)(cyv.x & 0xffff) * srcPitch;
+    const u8* r1 = src + (long long)(cyv.x >> 16) * srcPitch;
+    const int b0 = (short)(cyv.y & 0xffff), b1 = cyv.y >> 16;
+    uint32_t out = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int x = min(x4 + i, dw - 1);
+        const int2 c = cx[x];
+        const int s0 = c.x & 0xffff, s1 = c.x >> 16;
+        const int a0 = (short)(c.y & 0xffff), a1 = c.y >> 16;
+        const int S0 = r0[s0] * a0 + r0[s1] * a1;
+        const int S1 = r1[s0] * a0 + r1[s1] * a1;
+        const int v = (((b0 * (S0 >> 4)) >> 16) + ((b1 * (S1 >> 4)) >> 16) + 2) >> 2;
+        out |= (uint32_t)(v & 0xff) << (8 * i);
+    }
+    *reinterpret_cast<uint32_t*>(dst + (long long)y * dstPitch + x4) = out;
+}
+
+// =============================================================================================
+// K1b: 7x7 Gaussian blur, kernel [18 34 48 56 48 34 18]/256 per axis, exact integer, reflect-101
+// of the level itself.  Tile 128x32 per CTA, separable through shared memory.
+// =============================================================================================
+#define BL_TW 128
+#define BL_TH 32
+__device__ __forceinline__ int reflect101(int i, int n)
+{
+    if (n == 1) return 0;
+    while (i < 0 || i >= n) i = (i < 0) ? -i : 2 * (n - 1) - i;
+    return i;
+}
+
+__global__ void __launch_bounds__(256)
+blur7_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, u8* __restrict__ blurBase,
+             const int* __restrict__ tiles)
+{
+    __shared__ u8 sIn[BL_TH + 6][BL_TW + 8];
+    __shared__ unsigned short sH[BL_TH + 6][BL_TW];
+    const int t = tiles[blockIdx.x];
+    const int level = t >> 24, ty = (t >> 12) & 0xfff, tx = t & 0xfff;
+    const LevelGeom& L = g.L[level];
+    const int frame = blockIdx.y;
+    const u8* src;
+    int sp;
+    if (level == 0) { src = l0.base + (long long)frame * l0.frameStride; sp = l0.pitch; }
+    else { src = rawBase + (long long)frame * g.pyrFrameBytes + L.off; sp = L.pitch; }
+    u8* dst = blurBase + (long long)frame * g.pyrFrameBytes + L.off;
+    const int x0 = tx * BL_TW, y0 = ty * BL_TH;
+    const int tid = threadIdx.x;
+    // load (BL_TH+6) x (BL_TW+6) with reflection
+    for (int i = tid; i < (BL_TH + 6) * (BL_TW + 6); i += 256) {
+        const int r = i / (BL_TW + 6), c = i - r * (BL_TW + 6);
+        const int yy = reflect101(min(y0 + r - 3, L.h + 2), L.h);
+        const int xx = reflect101(min(x0 + c - 3, L.w + 2), L.w);
+        sIn[r][c] = src[(long long)yy * sp + xx];
+    }
+    __syncthreads();
+    for (int i = tid; i < (BL_TH + 6) * BL_TW; i += 256) {
+        const int r = i / BL_TW, c = i - r * BL_TW;
+        const u8* p = &sIn[r][c];
+        const int v = 18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3];
+        sH[r][c] = (unsigned short)v;
+    }
+    __syncthreads();
+    // vertical: thread -> 4 adjacent pixels, 4 rows
+    const int cx4 = (tid & 31) * 4;
+    for (int rr = tid >> 5; rr < BL_TH; rr += 8) {
+        const int y = y0 + rr;
+        if (y >= L.h || x0 + cx4 >= L.w) continue;
+        uint32_t out = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int c = cx4 + i;
+            const int v = 18 * (sH[rr][c] + sH[rr + 6][c]) + 34 * (sH[rr + 1][c] + sH[rr + 5][c]) +
+                          48 * (sH[rr + 2][c] + sH[rr + 4][c]) + 56 * sH[rr + 3][c];
+            out |= (uint32_t)((v + 32768) >> 16) << (8 * i);
+        }
+        *reinterpret_cast<uint32_t*>(dst + (long long)y * L.pitch + x0 + cx4) = out;
+    }
+}
+
+// =============================================================================================
+// K2: FAST per cell.  One warp = one cell = one cv::FAST(sub-image) call of the reference,
+// including its private 3x3 non-max suppression and the iniThFAST -> minThFAST retry.
+// A corner's strength S (largest t with a 9-arc all beyond t) does not depend on the threshold,
+// and NMS(th=ini) == NMS(th=min) restricted to S>ini, so one pass at minTh
+// serves both calls.  Candidates are packed x:12 | y:12 | (S-1):8 in window coordinates.
+// =============================================================================================
+#define FAST_WARPS 4
+
+__device__ __forceinline__ uint32_t vmaxu2(uint32_t a, uint32_t b) { return __vmaxu2(a, b); }
+__device__ __forceinline__ uint32_t vminu2(uint32_t a, uint32_t b) { return __vminu2(a, b); }
+
+// S for the pixel at p (row pitch tp): max over the 16 arcs of 9 contiguous ring pixels of
+// max(min(v - r), min(r - v)) = max(v - min_arcs(max r), max_arcs(min r) - v).
+__device__ __forceinline__ int fast_strength(const u8* p, int tp)
+{
+    const int v = p[0];
+    uint32_t P[8];
+    P[0] = p[3 * tp]      | (p[3 * tp + 1] << 16);
+    P[1] = p[2 * tp + 2]  | (p[tp + 3] << 16);
+    P[2] = p[3]           | (p[-tp + 3] << 16);
+    P[3] = p[-2 * tp + 2] | (p[-3 * tp + 1] << 16);
+    P[4] = p[-3 * tp]     | (p[-3 * tp - 1] << 16);
+    P[5] = p[-2 * tp - 2] | (p[-tp - 3] << 16);
+    P[6] = p[-3]          | (p[tp - 3] << 16);
+    P[7] = p[2 * tp - 2]  | (p[3 * tp - 1] << 16);
+    uint32_t mx[8], mn[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const uint32_t q = __byte_perm(P[j], P[(j + 1) & 7], 0x5432);   // elements 2j+1, 2j+2
+        mx[j] = vmaxu2(P[j], q);
+        mn[j] = vminu2(P[j], q);
+    }
+    uint32_t mx4[8], mn4[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { mx4[j] = vmaxu2(mx[j], mx[(j + 1) & 7]); mn4[j] = vminu2(mn[j], mn[(j + 1) & 7]); }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { mx[j] = vmaxu2(mx4[j], mx4[(j + 2) & 7]); mn[j] = vminu2(mn4[j], mn4[(j + 2) & 7]); }
+    uint32_t lo = 0xffffffffu, hi = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        lo = vminu2(lo, vmaxu2(mx[j], P[(j + 4) & 7]));   // min over arcs of (max over arc)
+        hi = vmaxu2(hi, vminu2(mn[j], P[(j + 4) & 7]));   // max over arcs of (min over arc)
+    }
+    const int minArcMax = min(lo & 0xffff, lo >> 16);
+    const int maxArcMin = max(hi & 0xffff, hi >> 16);
+    return max(v - minArcMax, maxArcMin - v);
+}
+
+__global__ void __launch_bounds__(FAST_WARPS * 32)
+fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* __restrict__ rawBase,
+                  int nframes, int minTh, int iniTh, uint32_t* __restrict__ cand,
+                  int2* __restrict__ cellSeg, unsigned* __restrict__ levelCandCount,
+                  int tilePitch, int scorePitch, int warpSmem)
+{
+    extern __shared__ __align__(16) u8 smem[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const long long gw = (long long)blockIdx.x * FAST_WARPS + wid;
+    if (gw >= (long long)nframes * g.ncells) return;
+    const int frame = (int)(gw / g.ncells), ci = (int)(gw - (long long)frame * g.ncells);
+    const Cell c = cells[ci];
+    const LevelGeom& L = g.L[c.level];
+    const u8* img;
+    int pitch;
+    if (c.level == 0) { img = l0.base + (long long)frame * l0.frameStride; pitch = l0.pitch; }
+    else { img = rawBase + (long long)frame * g.pyrFrameBytes + L.off; pitch = L.pitch; }
+
+    u8* tile = smem + (size_t)wid * warpSmem;
+    u8* score = tile + (size_t)tilePitch * g.chMax;
+    unsigned short* list = reinterpret_cast<unsigned short*>(score + (size_t)scorePitch * (g.chMax - 4));
+
+    const int cw = c.cw, ch = c.ch;
+    const int dw = cw - 6, dh = ch - 6;               // detectable interior
+    const unsigned FULL = 0xffffffffu;
+    int nOut = 0;
+    unsigned base = 0;
+    if (dw > 0 && dh > 0) {
+        // ---- load the sub-image with aligned 32-bit words -----------------------------------
+        const int xa = c.x0 & ~3, shift = c.x0 - xa;
+        const int nw = (shift + cw + 3) >> 2;
+        const int tw = tilePitch >> 2;
+        for (int i = lane; i < nw * ch; i += 32) {
+            const int y = i / nw, xw = i - y * nw;
+            reinterpret_cast<uint32_t*>(tile)[y * tw + xw] =
+                *reinterpret_cast<const uint32_t*>(img + (long long)(c.y0 + y) * pitch + xa + 4 * xw);
+        }
+        // zero the score tile ((dh+2) x scorePitch)
+        for (int i = lane; i < ((dh + 2) * scorePitch) >> 2; i += 32) reinterpret_cast<uint32_t*>(score)[i] = 0;
+        __syncwarp();
+        // ---- stage 1: compass pre-test (two adjacent compass pixels beyond minTh) ------------
+        int n1 = 0;
+        for (int y = 0; y < dh; ++y) {
+            for (int xb = 0; xb < dw; xb += 32) {
+                const int x = xb + lane;
+                bool pass = false;
+                if (x < dw) {
+                    const u8* p = tile + (y + 3) * tilePitch + shift + x + 3;
+                    const int v = p[0];
+                    const int hi = v + minTh, lo = v - minTh;
+                    const int r0 = p[3 * tilePitch], r4 = p[3], r8 = p[-3 * tilePitch], r12 = p[-3];
+                    const unsigned d = (r0 < lo) | ((r4 < lo) << 1) | ((r8 < lo) << 2) | ((r12 < lo) << 3);
+                    const unsigned b = (r0 > hi) | ((r4 > hi) << 1) | ((r8 > hi) << 2) | ((r12 > hi) << 3);
+                    const unsigned dd = d & ((d >> 1) | (d << 3)), bb = b & ((b >> 1) | (b << 3));
+                    pass = ((dd | bb) & 0xf) != 0;
+                }
+                const unsigned m = __ballot_sync(FULL, pass);
+                if (pass) list[n1 + __popc(m & ((1u << lane) - 1))] = (unsigned short)((y << 8) | x);
+                n1 += __popc(m);
+            }
+        }
+        __syncwarp();
+        // ---- stage 2: exact strength, keep corners (S > minTh) -------------------------------
+        int n2 = 0;
+        for (int i0 = 0; i0 < n1; i0 += 32) {
+            const int i = i0 + lane;
+            bool corner = false;
+            unsigned short e = 0;
+            if (i < n1) {
+                e = list[i];
+                const int y = e >> 8, x = e & 0xff;
+                const int S = fast_strength(tile + (y + 3) * tilePitch + shift + x + 3, tilePitch);
+                if (S > minTh) { corner = true; score[(y + 1) * scorePitch + x + 1] = (u8)S; }
+            }
+            __syncwarp();
+            const unsigned m = __ballot_sync(FULL, corner);
+            if (corner) list[n2 + __popc(m & ((1u << lane) - 1))] = e;
+            n2 += __popc(m);
+        }
+        __syncwarp();
+        // ---- stage 3: 3x3 non-max suppression inside the cell --------------------------------
+        int n3 = 0, nStrong = 0;
+        for (int i0 = 0; i0 < n2; i0 += 32) {
+            const int i = i0 + lane;
+            bool keep = false, strong = false;
+            unsigned short e = 0;
+            if (i < n2) {
+                e = list[i];
+                const int y = e >> 8, x = e & 0xff;
+                const u8* s = score + (y + 1) * scorePitch + x + 1;
+                const int v = s[0];
+                keep = v > s[-1] && v > s[1] && v > s[-scorePitch - 1] && v > s[-scorePitch] &&
+                       v > s[-scorePitch + 1] && v > s[scorePitch - 1] && v > s[scorePitch] &&
+                       v > s[scorePitch + 1];
+                strong = keep && v > iniTh;
+            }
+            __syncwarp();
+            const unsigned m = __ballot_sync(FULL, keep);
+            if (keep) list[n3 + __popc(m & ((1u << lane) - 1))] = e;
+            n3 += __popc(m);
+            nStrong += __popc(__ballot_sync(FULL, strong));
+        }
+        __syncwarp();
+        // ---- stage 4: emit (strong ones if any, else all), order = row-major ----------------
+        nOut = nStrong > 0 ? nStrong : n3;
+        if (nOut > 0) {
+            if (lane == 0) base = atomicAdd(&levelCandCount[frame * g.nlevels + c.level], (unsigned)nOut);
+            base = __shfl_sync(FULL, base, 0);
+            uint32_t* out = cand + (size_t)frame * g.candTotal + L.candOff + base;
+            int pos = 0;
+            for (int i0 = 0; i0 < n3; i0 += 32) {
+                const int i = i0 + lane;
+                bool emit = false;
+                uint32_t packed = 0;
+                if (i < n3) {
+                    const unsigned short e = list[i];
+                    const int y = e >> 8, x = e & 0xff;
+                    const int S = score[(y + 1) * scorePitch + x + 1];
+                    emit = nStrong > 0 ? (S > iniTh) : true;
+                    packed = (uint32_t)(x + 3 + c.offx) | ((uint32_t)(y + 3 + c.offy) << 12) | ((uint32_t)(S - 1) << 24);
+                }
+                const unsigned m = __ballot_sync(FULL, emit);
+                if (emit) out[pos + __popc(m & ((1u << lane) - 1))] = packed;
+                pos += __popc(m);
+            }
+        }
+    }
+    if (lane == 0) cellSeg[(size_t)frame * g.ncells + ci] = make_int2((int)base, nOut);
+}
+
+// =============================================================================================
+// K3: DistributeOctTree.  One warp per (frame, level) replays the reference's list algorithm:
+// the node list is kept REVERSED in shared memory (push_front == append), keys of a node are a
+// contiguous, order-preserving segment of a ping-pong key buffer.  Equal-size ties in the
+// "careful" phase are ordered by creation (array index) — DEVIATION-1 of the oracle.
+// =============================================================================================
+struct QNodes {
+    short* ulx; short* uly; short* urx; short* bry;
+    int* beg;            // bit31 = which key buffer
+    unsigned short* cnt; // 0 = dead
+};
+
+__device__ __forceinline__ int key_x(uint32_t k) { return k & 0xfff; }
+__device__ __forceinline__ int key_y(uint32_t k) { return (k >> 12) & 0xfff; }
+
+// Split node `ni` into up to four children appended at *top; returns growth (children - 1).
+__device__ int octree_split(QNodes q, int ni, int* top, uint32_t* keysA, uint32_t* keysB, int lane)
+{
+    const unsigned FULL = 0xffffffffu;
+    const int ulx = q.ulx[ni], uly = q.uly[ni], urx = q.urx[ni], bry = q.bry[ni];
+    const int begw = q.beg[ni];
+    const int beg = begw & 0x7fffffff, n = q.cnt[ni];
+    const uint32_t* src = (begw < 0) ? keysB : keysA;
+    uint32_t* dst = (begw < 0) ? keysA : keysB;
+    const int halfX = (urx - ulx + 1) >> 1;      // ceil((float)(UR.x-UL.x)/2), widths >= 0
+    const int halfY = (bry - uly + 1) >> 1;
+    const int mx = ulx + halfX, my = uly + halfY;
+    int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+    if (n <= 32) {
+        uint32_t k = 0;
+        int qd = 4;
+        if (lane < n) { k = src[beg + lane]; qd = (key_x(k) >= mx ? 1 : 0) | (key_y(k) >= my ? 2 : 0); }
+        const unsigned m0 = __ballot_sync(FULL, qd == 0), m1 = __ballot_sync(FULL, qd == 1);
+        const unsigned m2 = __ballot_sync(FULL, qd == 2), m3 = __ballot_sync(FULL, qd == 3);
+        c0 = __popc(m0); c1 = __popc(m1); c2 = __popc(m2); c3 = __popc(m3);
+        if (lane < n) {
+            const unsigned lt = (1u << lane) - 1;
+            int pos;
+            if (qd == 0) pos = __popc(m0 & lt);
+            else if (qd == 1) pos = c0 + __popc(m1 & lt);
+            else if (qd == 2) pos = c0 + c1 + __popc(m2 & lt);
+            else pos = c0 + c1 + c2 + __popc(m3 & lt);
+            dst[beg + pos] = k;
+        }
+    } else {
+        for (int i0 = 0; i0 < n; i0 += 32) {
+            int qd = 4;
+            if (i0 + lane < n) { const uint32_t k = src[beg + i0 + lane]; qd = (key_x(k) >= mx ? 1 : 0) | (key_y(k) >= my ? 2 : 0); }
+            c0 += __popc(__ballot_sync(FULL, qd == 0)); c1 += __popc(__ballot_sync(FULL, qd == 1));
+            c2 += __popc(__ballot_sync(FULL, qd == 2)); c3 += __popc(__ballot_sync(FULL, qd == 3));
+        }
+        int o0 = 0, o1 = c0, o2 = c0 + c1, o3 = c0 + c1 + c2;
+        for (int i0 = 0; i0 < n; i0 += 32) {
+            int qd = 4;
+            uint32_t k = 0;
+            if (i0 + lane < n) { k = src[beg + i0 + lane]; qd = (key_x(k) >= mx ? 1 : 0) | (key_y(k) >= my ? 2 : 0); }
+            const unsigned m0 = __ballot_sync(FULL, qd == 0), m1 = __ballot_sync(FULL, qd == 1);
+            const unsigned m2 = __ballot_sync(FULL, qd == 2), m3 = __ballot_sync(FULL, qd == 3);
+            const unsigned lt = (1u << lane) - 1;
+            if (qd == 0) dst[beg + o0 + __popc(m0 & lt)] = k;
+            else if (qd == 1) dst[beg + o1 + __popc(m1 & lt)] = k;
+            else if (qd == 2) dst[beg + o2 + __popc(m2 & lt)] = k;
+            else if (qd == 3) dst[beg + o3 + __popc(m3 & lt)] = k;
+            o0 += __popc(m0); o1 += __popc(m1); o2 += __popc(m2); o3 += __popc(m3);
+        }
+    }
+    __syncwarp();
+    // children in creation order n1 (UL), n2 (UR), n3 (BL), n4 (BR)
+    const int t = *top;
+    const int flip = (begw < 0) ? 0 : (int)0x80000000;
+    int nch = 0;
+    if (lane == 0) {
+        int o = beg, w = t;
+        if (c0) { q.ulx[w] = ulx; q.uly[w] = uly; q.urx[w] = mx;  q.bry[w] = my;  q.beg[w] = o | flip; q.cnt[w] = c0; ++w; } o += c0;
+        if (c1) { q.ulx[w] = mx;  q.uly[w] = uly; q.urx[w] = urx; q.bry[w] = my;  q.beg[w] = o | flip; q.cnt[w] = c1; ++w; } o += c1;
+        if (c2) { q.ulx[w] = ulx; q.uly[w] = my;  q.urx[w] = mx;  q.bry[w] = bry; q.beg[w] = o | flip; q.cnt[w] = c2; ++w; } o += c2;
+        if (c3) { q.ulx[w] = mx;  q.uly[w] = my;  q.urx[w] = urx; q.bry[w] = bry; q.beg[w] = o | flip; q.cnt[w] = c3; ++w; }
+        q.cnt[ni] = 0;   // parent erased
+    }
+    nch = (c0 != 0) + (c1 != 0) + (c2 != 0) + (c3 != 0);
+    *top = t + nch;
+    __syncwarp();
+    return nch - 1;
+}
+
+// remove dead nodes, keep order; returns new length
+__device__ int octree_compact(QNodes q, int len, int lane)
+{
+    const unsigned FULL = 0xffffffffu;
+    int w = 0;
+    for (int i0 = 0; i0 < len; i0 += 32) {
+        const int i = i0 + lane;
+        short a = 0, b = 0, c = 0, d = 0; int bg = 0; unsigned short cn = 0;
+        if (i < len) { cn = q.cnt[i]; a = q.ulx[i]; b = q.uly[i]; c = q.urx[i]; d = q.bry[i]; bg = q.beg[i]; }
+        const unsigned m = __ballot_sync(FULL, cn != 0);
+        __syncwarp();
+        if (cn != 0) {
+            const int p = w + __popc(m & ((1u << lane) - 1));
+            q.cnt[p] = cn; q.ulx[p] = a; q.uly[p] = b; q.urx[p] = c; q.bry[p] = d; q.beg[p] = bg;
+        }
+        w += __popc(m);
+        __syncwarp();
+    }
+    return w;
+}
+
+// warp bitonic sort (ascending) of n (<= cap, cap power of two) 32-bit keys in shared memory
+__device__ void warp_bitonic_sort(uint32_t* a, int n, int cap, int lane)
+{
+    for (int i = n + lane; i < cap; i += 32) a[i] = 0xffffffffu;
+    __syncwarp();
+    for (int k = 2; k <= cap; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = lane; i < cap; i += 32) {
+                const int l = i ^ j;
+                if (l > i) {
+                    const uint32_t x = a[i], y = a[l];
+                    const bool up = (i & k) == 0;
+                    if ((x > y) == up) { a[i] = y; a[l] = x; }
+                }
+            }
+            __syncwarp();
+        }
+}
+
+__global__ void __launch_bounds__(32)
+octree_kernel(Geom g, int nframes, const uint32_t* __restrict__ cand, const int2* __restrict__ cellSeg,
+              const unsigned* __restrict__ levelCandCount, uint32_t* __restrict__ keysAbase,
+              uint32_t* __restrict__ keysBbase, uint32_t* __restrict__ levelKps,
+              int* __restrict__ levelKpCount, int nodeCap, int sortCap, int* __restrict__ status)
+{
+    extern __shared__ __align__(16) u8 smem[];
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x;
+    const int level = blockIdx.x % g.nlevels, frame = blockIdx.x / g.nlevels;
+    const LevelGeom& L = g.L[level];
+    QNodes q;
+    q.beg = reinterpret_cast<int*>(smem);
+    q.ulx = reinterpret_cast<short*>(q.beg + nodeCap);
+    q.uly = q.ulx + nodeCap; q.urx = q.uly + nodeCap; q.bry = q.urx + nodeCap;
+    q.cnt = reinterpret_cast<unsigned short*>(q.bry + nodeCap);
+    uint32_t* sortbuf = reinterpret_cast<uint32_t*>(q.cnt + nodeCap + (nodeCap & 1));
+
+    const int n = (int)levelCandCount[frame * g.nlevels + level];
+    uint32_t* keysA = keysAbase + (size_t)frame * g.candTotal + L.candOff;
+    uint32_t* keysB = keysBbase + (size_t)frame * g.candTotal + L.candOff;
+    const uint32_t* csrc = cand + (size_t)frame * g.candTotal + L.candOff;
+    uint32_t* outKps = levelKps + (size_t)frame * g.kpTotal + L.kpOff;
+    int* outCount = levelKpCount + frame * g.nlevels + level;
+    if (n == 0 || L.nIni <= 0) { if (lane == 0) *outCount = 0; return; }
+
+    // ---- gather the per-cell segments into reference order (cell-row-major) into keysB --------
+    {
+        int pos = 0;
+        const int2* seg = cellSeg + (size_t)frame * g.ncells + L.cellBeg;
+        for (int c0 = 0; c0 < L.nCells; c0 += 32) {
+            int2 s = make_int2(0, 0);
+            if (c0 + lane < L.nCells) s = seg[c0 + lane];
+            int incl = s.y;
+            for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += v; }
+            const int excl = incl - s.y;
+            const int m = min(32, L.nCells - c0);
+            for (int j = 0; j < m; ++j) {
+                const int so = __shfl_sync(FULL, s.x, j), sc = __shfl_sync(FULL, s.y, j);
+                const int dp = pos + __shfl_sync(FULL, excl, j);
+                for (int i = lane; i < sc; i += 32) keysB[dp + i] = csrc[so + i];
+            }
+            pos += __shfl_sync(FULL, incl, 31);
+        }
+    }
+    __syncwarp();
+    // ---- roots: vpIniNodes[kp.pt.x / hX], stable partition keysB -> keysA ----------------------
+    int top = 0;
+    {
+        int o = 0;
+        // reversed list: root nIni-1 first ... root 0 last
+        for (int r = L.nIni - 1; r >= 0; --r) {
+            const int rb = o;
+            for (int i0 = 0; i0 < n; i0 += 32) {
+                bool sel = false; uint32_t k = 0;
+                if (i0 + lane < n) { k = keysB[i0 + lane]; sel = __float2int_rz(__fdiv_rn((float)key_x(k), L.hX)) == r; }
+                const unsigned m = __ballot_sync(FULL, sel);
+                if (sel) keysA[o + __popc(m & ((1u << lane) - 1))] = k;
+                o += __popc(m);
+            }
+            const int cnt = o - rb;
+            if (cnt > 0) {
+                if (lane == 0) {
+                    q.ulx[top] = (short)__float2int_rz(__fmul_rn(L.hX, (float)r));
+                    q.urx[top] = (short)__float2int_rz(__fmul_rn(L.hX, (float)(r + 1)));
+                    q.uly[top] = 0; q.bry[top] = (short)L.winH;
+                    q.beg[top] = rb; q.cnt[top] = (unsigned short)cnt;
+                }
+                ++top;
+            }
+        }
+    }
+    __syncwarp();
+    const int N = L.N;
+    int size = top;
+    bool finish = false;
+    bool overflow = false;
+    while (!finish) {
+        // full pass: split every node with more than one key, list order = from the end
+        const int len = octree_compact(q, top, lane);
+        top = len;
+        const int prevSize = size;
+        if (len + 4 * len > nodeCap) { overflow = true; break; }
+        for (int i = len - 1; i >= 0; --i) {
+            if (q.cnt[i] <= 1) continue;
+            size += octree_split(q, i, &top, keysA, keysB, lane);
+        }
+        int nToExpand = 0;
+        for (int i0 = len; i0 < top; i0 += 32) nToExpand += __popc(__ballot_sync(FULL, i0 + lane < top && q.cnt[i0 + lane] > 1));
+        if (size >= N || size == prevSize) { finish = true; }
+        else if (size + nToExpand * 3 > N) {
+            while (!finish) {
+                const int len2 = octree_compact(q, top, lane);
+                top = len2;
+                const int prev2 = size;
+                // candidates: alive nodes with > 1 key; sort by (nKeys, creation index)
+                int nc = 0;
+                for (int i0 = 0; i0 < len2; i0 += 32) {
+                    const int i = i0 + lane;
+                    const bool e = i < len2 && q.cnt[i] > 1;
+                    const unsigned m = __ballot_sync(FULL, e);
+                    if (e) {
+                        const int p = nc + __popc(m & ((1u << lane) - 1));
+                        if (p < sortCap) sortbuf[p] = ((uint32_t)q.cnt[i] << 16) | (uint32_t)i;
+                    }
+                    nc += __popc(m);
+                }
+                if (nc > sortCap || len2 + 4 * nc > nodeCap || len2 > 0xffff) { overflow = true; finish = true; break; }
+                __syncwarp();
+                int cap2 = 32; while (cap2 < nc) cap2 <<= 1;
+                warp_bitonic_sort(sortbuf, nc, cap2, lane);
+                for (int j = nc - 1; j >= 0; --j) {
+                    const int ni = (int)(sortbuf[j] & 0xffff);
+                    size += octree_split(q, ni, &top, keysA, keysB, lane);
+                    if (size >= N) break;
+                }
+                if (size >= N || size == prev2) finish = true;
+            }
+        }
+    }
+    if (overflow) { if (lane == 0) { atomicOr(status, 1); *outCount = 0; } return; }
+    // ---- retain the best key of every node, list order = reversed array -----------------------
+    const int len = octree_compact(q, top, lane);
+    if (len > L.kpCap) { if (lane == 0) { atomicOr(status, 2); *outCount = 0; } return; }
+    for (int i0 = 0; i0 < len; i0 += 32) {
+        const int i = i0 + lane;
+        if (i < len) {
+            const int begw = q.beg[i];
+            const uint32_t* src = (begw < 0) ? keysB : keysA;
+            const int b = begw & 0x7fffffff, c = q.cnt[i];
+            uint32_t best = src[b];
+            for (int k = 1; k < c; ++k) { const uint32_t kk = src[b + k]; if ((kk >> 24) > (best >> 24)) best = kk; }
+            outKps[len - 1 - i] = best;
+        }
+    }
+    if (lane == 0) *outCount = len;
+}
+
+// =============================================================================================
+// K4: orientation (IC_Angle) + rotated BRIEF + final keypoint record.  One warp per keypoint.
+// =============================================================================================
+__constant__ int c_umax[16];
+
+__device__ __forceinline__ float fast_atan2_deg(float y, float x)
+{
+    // cv::fastAtan2 scalar path; every op individually rounded
+    const float scale = (float)(180.0 / 3.14159265358979323846);
+    const float p1 = 0.9997878412794807f * scale, p3 = -0.3258083974640975f * scale;
+    const float p5 = 0.1555786518463281f * scale, p7 = -0.04432655554792128f * scale;
+    const float ax = fabsf(x), ay = fabsf(y);
+    float a, c, c2;
+    if (ax >= ay) {
+        c = __fdiv_rn(ay, __fadd_rn(ax, (float)DBL_EPSILON));
+        c2 = __fmul_rn(c, c);
+        a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+    } else {
+        c = __fdiv_rn(ax, __fadd_rn(ay, (float)DBL_EPSILON));
+        c2 = __fmul_rn(c, c);
+        a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+    }
+    if (x < 0) a = __fsub_rn(180.f, a);
+    if (y < 0) a = __fsub_rn(360.f, a);
+    return a;
+}
+
+#define DESC_WARPS 8
+__global__ void __launch_bounds__(DESC_WARPS * 32)
+describe_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, const u8* __restrict__ blurBase,
+                int nframes, const uint32_t* __restrict__ levelKps, const int* __restrict__ levelKpCount,
+                const int* __restrict__ kpMap, const signed char* __restrict__ pattern,
+                orbx_keypoint* __restrict__ outKps, u8* __restrict__ outDesc, int* __restrict__ outCount,
+                int* __restrict__ outLevelCount, int firstSlot, int kpCapOut)
+{
+    __shared__ __align__(16) signed char sPat[ORBX_PATTERN_LEN];
+    for (int i = threadIdx.x; i < ORBX_PATTERN_LEN / 4; i += blockDim.x)
+        reinterpret_cast<int*>(sPat)[i] = reinterpret_cast<const int*>(pattern)[i];
+    __syncthreads();
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const long long gw = (long long)blockIdx.x * DESC_WARPS + (threadIdx.x >> 5);
+    if (gw >= (long long)nframes * g.kpTotal) return;
+    const int frame = (int)(gw / g.kpTotal), slotk = (int)(gw - (long long)frame * g.kpTotal);
+    const int level = kpMap[slotk];
+    const LevelGeom& L = g.L[level];
+    const int k = slotk - L.kpOff;
+    const int* counts = levelKpCount + frame * g.nlevels;
+    int offset = 0, total = 0;
+    for (int l = 0; l < g.nlevels; ++l) { const int c = counts[l]; if (l < level) offset += c; total += c; }
+    if (slotk == 0 && lane == 0) {
+        outCount[firstSlot + frame] = total;
+        for (int l = 0; l < g.nlevels; ++l) outLevelCount[(firstSlot + frame) * ORBX_MAX_LEVELS + l] = counts[l];
+    }
+    if (k >= counts[level]) return;
+    const uint32_t packed = levelKps[(size_t)frame * g.kpTotal + slotk];
+    const int px = key_x(packed) + 16, py = key_y(packed) + 16;     // + minBorderX/Y (EDGE_THRESHOLD-3)
+    const u8* raw;
+    int rp;
+    if (level == 0) { raw = l0.base + (long long)frame * l0.frameStride; rp = l0.pitch; }
+    else { raw = rawBase + (long long)frame * g.pyrFrameBytes + L.off; rp = L.pitch; }
+    // ---- IC_Angle: lanes = u in [-15,15], loop over the 31 rows of the disc --------------------
+    const int u = lane - 15;
+    int m10 = 0, m01 = 0;
+    if (lane < 31) {
+        const u8* center = raw + (long long)py * rp + px;
+        const int au = abs(u);
+#pragma unroll 1
+        for (int v = -15; v <= 15; ++v) {
+            if (au <= c_umax[abs(v)]) {
+                const int val = center[v * rp + u];
+                m10 += u * val;
+                m01 += v * val;
+            }
+        }
+    }
+    for (int d = 16; d > 0; d >>= 1) { m10 += __shfl_xor_sync(FULL, m10, d); m01 += __shfl_xor_sync(FULL, m01, d); }
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+    // ---- rotated BRIEF on the blurred level: lane i -> descriptor byte i -----------------------
+    const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
+    float sa, ca;
+    orbx_sincosf(__fmul_rn(angle, factorPI), &sa, &ca);
+    const u8* bl = blurBase + (long long)frame * g.pyrFrameBytes + L.off;
+    const u8* bc = bl + (long long)py * L.pitch + px;
+    const signed char* pat = sPat + lane * 32;
+    int val = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const float x0 = (float)pat[4 * j], y0 = (float)pat[4 * j + 1], x1 = (float)pat[4 * j + 2], y1 = (float)pat[4 * j + 3];
+        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sa), __fmul_rn(y0, ca)));
+        const int q0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sa)));
+        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sa), __fmul_rn(y1, ca)));
+        const int q1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, ca), __fmul_rn(y1, sa)));
+        const int t0 = bc[r0 * L.pitch + q0], t1 = bc[r1 * L.pitch + q1];
+        val |= (t0 < t1) << j;
+    }
+    const size_t o = (size_t)(firstSlot + frame) * kpCapOut + offset + k;
+    outDesc[o * 32 + lane] = (u8)val;
+    if (lane == 0) {
+        orbx_keypoint kp;
+        kp.x = (float)px; kp.y = (float)py;
+        if (level != 0) { kp.x = __fmul_rn(kp.x, L.scale); kp.y = __fmul_rn(kp.y, L.scale); }
+        kp.size = L.kpSize;
+        kp.angle = angle;
+        kp.response = (float)(packed >> 24);
+        kp.octave = level;
+        kp.class_id = -1;
+        outKps[o] = kp;
+    }
+}
+
+// =============================================================================================
+// host side: geometry for an image shape, and the per-chunk launch sequence
+// =============================================================================================
+static inline int cv_roundf(float v) { return (int)lrintf(v); }
+
+static void linear_coeffs(int sn, int dn, std::vector<int2>& out)
+{
+    // cv::resize INTER_LINEAR coefficient rule
+    const double scale = (double)sn / dn;
+    for (int d = 0; d < dn; ++d) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)floorf(f);
+        f -= s;
+        if (s < 0) { s = 0; f = 0.f; }
+        if (s >= sn - 1) { s = sn - 1; f = 0.f; }
+        const int s1 = std::min(s + 1, sn - 1);
+        const int a0 = cv_roundf((1.f - f) * 2048.f), a1 = cv_roundf(f * 2048.f);
+        out.push_back(make_int2(s | (s1 << 16), (a0 & 0xffff) | (a1 << 16)));
+    }
+}
+
+int orbx_setup_shape(orbx_handle* h, int w, int hgt)
+{
+    if (h->curW == w && h->curH == hgt) return ORBX_OK;
+    if (w > h->maxW || hgt > h->maxH) { orbx_set_error("image %dx%d exceeds handle maximum %dx%d", w, hgt, h->maxW, h->maxH); return ORBX_E_CAPACITY; }
+    const int nl = h->params.nlevels;
+    Geom& g = h->geom;
+    memset(&g, 0, sizeof(g));
+    g.nlevels = nl;
+    std::vector<Cell> cells;
+    std::vector<int2> coef;
+    std::vector<int> tiles, kpMap;
+    long long off = 0;
+    int candOff = 0, kpOff = 0;
+    for (int l = 0; l < nl; ++l) {
+        LevelGeom& L = g.L[l];
+        L.w = cv_roundf((float)w * h->invScale[l]);
+        L.h = cv_roundf((float)hgt * h->invScale[l]);
+        L.pitch = (L.w + 15) & ~15;
+        L.off = (int)off;
+        off += (long long)L.pitch * L.h;
+        off = (off + 255) & ~255LL;
+        L.scale = h->scale[l];
+        L.kpSize = (float)(int)(31 * h->scale[l]);
+        L.N = h->perLevel[l];
+        if (l > 0) {
+            L.coefX = (int)coef.size(); linear_coeffs(g.L[l - 1].w, L.w, coef);
+            L.coefY = (int)coef.size(); linear_coeffs(g.L[l - 1].h, L.h, coef);
+        }
+        for (int ty = 0; ty * BL_TH < L.h; ++ty)
+            for (int tx = 0; tx * BL_TW < L.w; ++tx) tiles.push_back((l << 24) | (ty << 12) | tx);
+        // FAST cell grid (src/ORBextractor.cc:773-806)
+        const int minBX = 16, minBY = 16, maxBX = L.w - 16, maxBY = L.h - 16;
+        L.winW = maxBX - minBX; L.winH = maxBY - minBY;
+        L.cellBeg = (int)cells.size();
+        L.candOff = candOff;
+        int cap = 0;
+        const float width = (float)(maxBX - minBX), height = (float)(maxBY - minBY);
+        const int nCols = (int)(width / 30.f), nRows = (int)(height / 30.f);
+        if (L.winW > 0 && L.winH > 0 && nCols > 0 && nRows > 0) {
+            const int wCell = (int)ceilf(width / nCols), hCell = (int)ceilf(height / nRows);
+            for (int i = 0; i < nRows; ++i) {
+                const float iniY = (float)(minBY + i * hCell);
+                float maxY = iniY + hCell + 6;
+                if (iniY >= maxBY - 3) continue;
+                if (maxY > maxBY) maxY = (float)maxBY;
+                for (int j = 0; j < nCols; ++j) {
+                    const float iniX = (float)(minBX + j * wCell);
+                    float maxX = iniX + wCell + 6;
+                    if (iniX >= maxBX - 6) continue;
+                    if (maxX > maxBX) maxX = (float)maxBX;
+                    Cell c;
+                    c.x0 = (unsigned short)iniX; c.y0 = (unsigned short)iniY;
+                    c.cw = (unsigned short)((int)maxX - (int)iniX); c.ch = (unsigned short)((int)maxY - (int)iniY);
+                    c.offx = (unsigned short)(j * wCell); c.offy = (unsigned short)(i * hCell);
+                    c.level = (unsigned short)l; c.pad = 0;
+                    if (c.cw > 250 || c.ch > 250) { orbx_set_error("FAST cell too large (%dx%d)", c.cw, c.ch); return ORBX_E_INVALID; }
+                    cells.push_back(c);
+                    g.cwMax = std::max<int>(g.cwMax, c.cw); g.chMax = std::max<int>(g.chMax, c.ch);
+                    const int dw = c.cw - 6, dh = c.ch - 6;
+                    if (dw > 0 && dh > 0) cap += ((dw + 1) / 2) * ((dh + 1) / 2);
+                }
+            }
+            // quadtree roots (src/ORBextractor.cc:543-546)
+            L.nIni = (int)roundf((float)(maxBX - minBX) / (maxBY - minBY));
+            L.hX = L.nIni > 0 ? (float)(maxBX - minBX) / L.nIni : 0.f;
+        }
+        L.nCells = (int)cells.size() - L.cellBeg;
+        L.candCap = (cap + 31) & ~31;
+        candOff += L.candCap;
+        L.kpOff = kpOff;
+        L.kpCap = std::max(L.N + 3, 4 * std::max(L.nIni, 1)) + 1;
+        for (int k = 0; k < L.kpCap; ++k) kpMap.push_back(l);
+        kpOff += L.kpCap;
+    }
+    if (w > 4000 || hgt > 4000) { orbx_set_error("image larger than 4000 px per side is unsupported"); return ORBX_E_INVALID; }
+    g.ncells = (int)cells.size();
+    g.candTotal = candOff;
+    g.kpTotal = kpOff;
+    g.pyrFrameBytes = off;
+    if (g.cwMax < 7) g.cwMax = 7;
+    if (g.chMax < 7) g.chMax = 7;
+    // (re)allocate shape-dependent device buffers
+    cudaStream_t st = h->stream;
+    ORBX_CUDA(cudaStreamSynchronize(st));
+    auto re = [&](void** p, size_t bytes) -> cudaError_t { if (*p) cudaFree(*p); *p = nullptr; return cudaMalloc(p, std::max<size_t>(bytes, 256)); };
+    const size_t C = (size_t)h->chunkFrames;
+    ORBX_CUDA(re((void**)&h->dCells, cells.size() * sizeof(Cell)));
+    ORBX_CUDA(re((void**)&h->dCoef, coef.size() * sizeof(int2)));
+    ORBX_CUDA(re((void**)&h->dBlurTiles, tiles.size() * sizeof(int)));
+    ORBX_CUDA(re((void**)&h->dKpMap, kpMap.size() * sizeof(int)));
+    h->nBlurTiles = (int)tiles.size();
+    h->l0Pitch = (w + 15) & ~15;
+    h->l0FrameBytes = (((long long)h->l0Pitch * hgt) + 255) & ~255LL;
+    ORBX_CUDA(re((void**)&h->dLevel0, C * h->l0FrameBytes));
+    ORBX_CUDA(re((void**)&h->dRaw, C * g.pyrFrameBytes));
+    ORBX_CUDA(re((void**)&h->dBlur, C * g.pyrFrameBytes));
+    ORBX_CUDA(re((void**)&h->dCand, C * g.candTotal * sizeof(uint32_t)));
+    ORBX_CUDA(re((void**)&h->dKeysA, C * g.candTotal * sizeof(uint32_t)));
+    ORBX_CUDA(re((void**)&h->dKeysB, C * g.candTotal * sizeof(uint32_t)));
+    ORBX_CUDA(re((void**)&h->dCellSeg, C * g.ncells * sizeof(int2)));
+    ORBX_CUDA(re((void**)&h->dLevelCandCount, C * nl * sizeof(unsigned)));
+    ORBX_CUDA(re((void**)&h->dLevelKps, C * g.kpTotal * sizeof(uint32_t)));
+    ORBX_CUDA(re((void**)&h->dLevelKpCount, C * nl * sizeof(int)));
+    if (g.kpTotal > h->kpCap) { orbx_set_error("internal: keypoint capacity %d < %d", h->kpCap, g.kpTotal); return ORBX_E_CAPACITY; }
+    ORBX_CUDA(cudaMemcpyAsync(h->dCells, cells.data(), cells.size() * sizeof(Cell), cudaMemcpyHostToDevice, st));
+    if (!coef.empty()) ORBX_CUDA(cudaMemcpyAsync(h->dCoef, coef.data(), coef.size() * sizeof(int2), cudaMemcpyHostToDevice, st));
+    ORBX_CUDA(cudaMemcpyAsync(h->dBlurTiles, tiles.data(), tiles.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+    ORBX_CUDA(cudaMemcpyAsync(h->dKpMap, kpMap.data(), kpMap.size() * sizeof(int), cudaMemcpyHostToDevice, st));
+    ORBX_CUDA(cudaMemcpyToSymbolAsync(c_umax, h->umax, sizeof(int) * 16, 0, cudaMemcpyHostToDevice, st));
+    ORBX_CUDA(cudaStreamSynchronize(st));
+    h->curW = w; h->curH = hgt;
+    h->lastChunkFrames = 0;
+    return ORBX_OK;
+}
+
+static signed char* g_dPattern[16] = {nullptr};
+
+static int get_pattern(int device, const signed char** out)
+{
+    if (device < 0 || device >= 16) { orbx_set_error("device index %d unsupported", device); return ORBX_E_INVALID; }
+    if (!g_dPattern[device]) {
+        static const signed char pat[ORBX_PATTERN_LEN] = {ORBX_PATTERN_VALUES};
+        ORBX_CUDA(cudaMalloc((void**)&g_dPattern[device], ORBX_PATTERN_LEN));
+        ORBX_CUDA(cudaMemcpy(g_dPattern[device], pat, ORBX_PATTERN_LEN, cudaMemcpyHostToDevice));
+    }
+    *out = g_dPattern[device];
+    return ORBX_OK;
+}
+
+int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
+{
+    const Geom& g = h->geom;
+    cudaStream_t st = h->stream;
+    const int nl = g.nlevels;
+    const signed char* dPat = nullptr;
+    int rc = get_pattern(h->device, &dPat);
+    if (rc) return rc;
+    // K1a: levels 1..n-1, each from the previous one
+    for (int l = 1; l < nl; ++l) {
+        const LevelGeom& S = g.L[l - 1];
+        const LevelGeom& D = g.L[l];
+        const u8* src; long long sfs; int sp;
+        if (l == 1) { src = l0.base; sfs = l0.frameStride; sp = l0.pitch; }
+        else { src = h->dRaw + S.off; sfs = g.pyrFrameBytes; sp = S.pitch; }
+        dim3 grid((D.w + 127) / 128, (D.h + 7) / 8, nframes), block(32, 8);
+        pyr_resize_kernel<<<grid, block, 0, st>>>(src, sfs, sp, h->dRaw + D.off, g.pyrFrameBytes, D.pitch, D.w, D.h,
+                                                  h->dCoef + D.coefX, h->dCoef + D.coefY);
+    }
+    // K1b: blur of all levels
+    blur7_kernel<<<dim3(h->nBlurTiles, nframes), 256, 0, st>>>(g, l0, h->dRaw, h->dBlur, h->dBlurTiles);
+    // K2: FAST
+    ORBX_CUDA(cudaMemsetAsync(h->dLevelCandCount, 0, (size_t)nframes * nl * sizeof(unsigned), st));
+    {
+        const int tilePitch = (g.cwMax + 3 + 3) & ~3;
+        const int scorePitch = (g.cwMax - 4 + 3) & ~3;
+        int warpSmem = tilePitch * g.chMax + scorePitch * (g.chMax - 4) + 2 * (g.cwMax - 6) * (g.chMax - 6);
+        warpSmem = (warpSmem + 15) & ~15;
+        const int smem = warpSmem * FAST_WARPS;
+        if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        const long long warps = (long long)nframes * g.ncells;
+        const int blocks = (int)((warps + FAST_WARPS - 1) / FAST_WARPS);
+        fast_cells_kernel<<<blocks, FAST_WARPS * 32, smem, st>>>(g, h->dCells, l0, h->dRaw, nframes, h->params.min_th_fast,
+                                                                  h->params.ini_th_fast, h->dCand, h->dCellSeg, h->dLevelCandCount,
+                                                                  tilePitch, scorePitch, warpSmem);
+    }
+    // K3: quadtree
+    {
+        int maxN = 1;
+        for (int l = 0; l < nl; ++l) maxN = std::max(maxN, std::max(g.L[l].N, 4 * g.L[l].nIni));
+        const int nodeCap = 5 * (maxN + 4) + 32;
+        int sortCap = 32; while (sortCap < maxN + 4) sortCap <<= 1;
+        const int smem = nodeCap * (4 + 8 + 2) + 4 + sortCap * 4;
+        if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        octree_kernel<<<nframes * nl, 32, smem, st>>>(g, nframes, h->dCand, h->dCellSeg, h->dLevelCandCount, h->dKeysA, h->dKeysB,
+                                                       h->dLevelKps, h->dLevelKpCount, nodeCap, sortCap, h->dStatus);
+    }
+    // K4: orientation + descriptors + output records
+    {
+        const long long warps = (long long)nframes * g.kpTotal;
+        const int blocks = (int)((warps + DESC_WARPS - 1) / DESC_WARPS);
+        describe_kernel<<<blocks, DESC_WARPS * 32, 0, st>>>(g, l0, h->dRaw, h->dBlur, nframes, h->dLevelKps, h->dLevelKpCount,
+                                                             h->dKpMap, dPat, h->dKps, h->dDesc, h->dCount, h->dSlotLevelCount,
+                                                             firstSlot, h->kpCap);
+    }
+    ORBX_CUDA(cudaGetLastError());
+    h->lastL0 = l0;
+    h->lastChunkFrames = nframes;
+    return ORBX_OK;
+}

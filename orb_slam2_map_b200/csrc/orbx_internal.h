@@ -1,0 +1,134 @@
+// orbx_internal.h — shared declarations of liborbx.so (not part of the public C ABI).
+#ifndef ORBX_INTERNAL_H
+#define ORBX_INTERNAL_H
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/orbx.h"
+
+#define ORBX_MAX_LEVELS 16
+#define ORBX_GRID_COLS 64     // FRAME_GRID_COLS, reference include/Frame.h:38
+#define ORBX_GRID_ROWS 48     // FRAME_GRID_ROWS, reference include/Frame.h:37
+#define ORBX_GRID_CELLS (ORBX_GRID_COLS * ORBX_GRID_ROWS)
+#define ORBX_TH_HIGH 100      // reference src/ORBmatcher.cc:37
+#define ORBX_TH_LOW 50        // reference src/ORBmatcher.cc:38
+#define ORBX_HISTO_LENGTH 30  // reference src/ORBmatcher.cc:39
+
+void orbx_set_error(const char* fmt, ...);
+
+#define ORBX_CUDA(call)                                                                         \
+    do {                                                                                        \
+        cudaError_t e__ = (call);                                                               \
+        if (e__ != cudaSuccess) {                                                               \
+            orbx_set_error("%s failed at %s:%d: %s", #call, __FILE__, __LINE__,                 \
+                           cudaGetErrorString(e__));                                            \
+            return ORBX_E_CUDA;                                                                 \
+        }                                                                                       \
+    } while (0)
+
+// ---- per-level geometry (host-computed, passed to kernels by value) -------------------------
+struct LevelGeom {
+    int w, h, pitch;        // level size, row pitch in bytes (multiple of 16)
+    int off;                // byte offset of the level inside one frame's pyramid block
+    int cellBeg, nCells;    // range of this level's FAST cells in the cell table
+    int candOff, candCap;   // candidate region (entries) inside one frame's candidate block
+    int kpOff, kpCap;       // culled-keypoint region inside one frame's keypoint block
+    int N;                  // mnFeaturesPerLevel[level]
+    int nIni;               // quadtree roots
+    float hX;               // root width (float, as the reference computes it)
+    int winW, winH;         // maxBorderX-minBorderX, maxBorderY-minBorderY
+    int coefX, coefY;       // offsets into the resize coefficient table (levels >= 1)
+    float scale;            // mvScaleFactor[level]
+    float kpSize;           // (float)(int)(31*scale)
+};
+
+struct Geom {
+    int nlevels, ncells, candTotal, kpTotal;
+    int cwMax, chMax;            // largest FAST cell sub-image
+    long long pyrFrameBytes;     // bytes of one frame's pyramid block (all levels, pitched)
+    LevelGeom L[ORBX_MAX_LEVELS];
+};
+
+// one FAST cell = one cv::FAST call of the reference (src/ORBextractor.cc:789-829)
+struct Cell {
+    unsigned short x0, y0;      // iniX, iniY (level coordinates)
+    unsigned short cw, ch;      // sub-image size (maxX-iniX, maxY-iniY)
+    unsigned short offx, offy;  // j*wCell, i*hCell added to cell-local coordinates
+    unsigned short level, pad;
+};
+
+// where level 0 of each frame of the current chunk lives (caller's device images or the
+// workspace copy)
+struct Level0 {
+    const uint8_t* base;
+    long long frameStride;
+    int pitch;
+};
+
+struct orbx_handle {
+    orbx_params params;
+    int device;
+    cudaStream_t stream;
+    bool ownStream;
+    int maxW, maxH, chunkFrames, resultSlots;
+    // tables as the reference ctor computes them
+    std::vector<float> scale, invScale, sigma2, invSigma2;
+    std::vector<int> perLevel;
+    int umax[16];
+    // geometry of the current image shape
+    int curW, curH;
+    Geom geom;
+    // device tables
+    Cell* dCells;
+    int2* dCoef;        // resize coefficients
+    int* dBlurTiles;
+    int nBlurTiles;
+    int* dKpMap;        // keypoint-slot -> level map for the describe kernel
+    // workspace (chunkFrames deep)
+    uint8_t* dLevel0;   // pitched copy of the input images (when needed)
+    int l0Pitch;
+    long long l0FrameBytes;
+    uint8_t* dRaw;      // pyramid levels >= 1
+    uint8_t* dBlur;     // blurred levels (all)
+    uint32_t* dCand;    // FAST candidates, per-cell segments
+    uint32_t* dKeysA;   // quadtree key buffers
+    uint32_t* dKeysB;
+    int2* dCellSeg;
+    unsigned* dLevelCandCount;
+    uint32_t* dLevelKps;    // culled keypoints per level (packed)
+    int* dLevelKpCount;
+    int* dStatus;           // device-side error flags
+    Level0 lastL0;
+    int lastChunkFrames;
+    // result store (resultSlots deep)
+    int kpCap;              // per-frame keypoint capacity (= geom.kpTotal at creation shape)
+    orbx_keypoint* dKps;
+    uint8_t* dDesc;
+    int* dCount;
+    int* dSlotLevelCount;
+    // frame grid (per slot)
+    unsigned short* dGridStart;   // [slot][GRID_CELLS+1]
+    unsigned short* dGridIdx;     // [slot][kpCap]
+    // matcher outputs (per slot = pair index)
+    int* dMatches12;
+    int* dNMatches;
+    unsigned long long* dNCompares;
+    float* dURight;
+    float* dDepth;
+    uint32_t* dMatchScratch;
+    long long matchScratchPerPair;
+    // pinned staging
+    void* hStage;
+    size_t hStageBytes;
+};
+
+// orbx_extract.cu
+int orbx_setup_shape(orbx_handle* h, int w, int hgt);
+int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot);
+
+// orbx_match.cu
+int orbx_build_grids(orbx_handle* h, int firstSlot, int nframes, int width, int height);
+
+#endif
