@@ -1,0 +1,113 @@
+"""GPU parity: liborbx.so (through the C ABI) vs the CPU oracle, stage by stage and end to end.
+Bit-exact for pyramid bytes, FAST candidates, culled keypoints (x, y, octave, order), descriptors;
+angle/response are compared exactly too (the tolerance north_star allows is 1e-5 relative)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from orb_slam2_map_b200 import capi, synth
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(640, 480, 1000), (1241, 376, 2000), (752, 480, 1200), (333, 251, 500), (1920, 1080, 5000)]
+
+
+def _image(w, h, seed):
+    return synth.textured_canvas(w, h, seed=seed)
+
+
+def _compare_full(kg, dg, ko, do):
+    assert len(kg) == len(ko), (len(kg), len(ko))
+    for f in ("x", "y", "size", "octave", "class_id", "response"):
+        assert np.array_equal(kg[f], ko[f]), f
+    assert np.array_equal(kg["angle"], ko["angle"]), np.abs(kg["angle"] - ko["angle"]).max()
+    assert np.array_equal(dg, do), int((dg != do).any(axis=1).sum())
+
+
+@pytest.mark.parametrize("w,h,nf", SHAPES)
+def test_stages_and_full(w, h, nf):
+    img = _image(w, h, seed=w + h)
+    ex = capi.Extractor(nfeatures=nf, max_width=w, max_height=h)
+    orc = O.Extractor(nfeatures=nf)
+    ko, do = orc.extract(img)
+    kg, dg = ex.extract(img)
+    # tables
+    tg, to = ex.tables(), orc.tables()
+    for k in tg:
+        assert np.array_equal(tg[k], to[k]), k
+    # pyramid + blur bytes
+    for l in range(8):
+        assert np.array_equal(ex.level(0, l), orc.level(l)), f"raw level {l}"
+        assert np.array_equal(ex.level(0, l, blurred=True), orc.level(l, blurred=True)), f"blur level {l}"
+    assert np.array_equal(ex.level(0, 2, border=19), O.border101(orc.level(2), 19))
+    # FAST candidates in reference order
+    for l in range(8):
+        cg, co = ex.candidates(0, l), orc.candidates(l)
+        assert cg.shape == co.shape, (l, cg.shape, co.shape)
+        assert np.array_equal(cg, co), f"candidates level {l}"
+    _compare_full(kg, dg, ko, do)
+    ex.close()
+
+
+@pytest.mark.parametrize("kind", ["noise", "flat", "checker", "gradient", "sparse"])
+def test_odd_content(kind):
+    w, h = 640, 480
+    rng = np.random.default_rng(5)
+    if kind == "noise":
+        img = rng.integers(0, 256, (h, w), dtype=np.uint8)
+    elif kind == "flat":
+        img = np.full((h, w), 77, np.uint8)
+    elif kind == "checker":
+        yy, xx = np.mgrid[0:h, 0:w]
+        img = (((yy // 9 + xx // 7) % 2) * 200 + 20).astype(np.uint8)
+    elif kind == "gradient":
+        yy, xx = np.mgrid[0:h, 0:w]
+        img = ((xx * 255) // w).astype(np.uint8)
+    else:
+        img = np.full((h, w), 128, np.uint8)
+        pts = rng.integers(30, 450, (40, 2))
+        for (y, x) in pts:
+            img[y:y + 5, x:x + 5] = 255
+    ex = capi.Extractor(max_width=w, max_height=h)
+    orc = O.Extractor()
+    ko, do = orc.extract(img)
+    kg, dg = ex.extract(img)
+    for l in range(8):
+        assert np.array_equal(ex.candidates(0, l), orc.candidates(l)), f"candidates level {l}"
+    _compare_full(kg, dg, ko, do)
+    ex.close()
+
+
+def test_batch_matches_single_and_oracle():
+    w, h, n = 640, 480, 12
+    frames = synth.frame_sequence(n, w, h, seed=3)
+    ex = capi.Extractor(max_width=w, max_height=h, chunk_frames=5, result_slots=n)
+    ex.extract_batch(frames)
+    kps, desc, counts = ex.download(0, n)
+    orc = O.Extractor()
+    for i in range(n):
+        ko, do = orc.extract(frames[i])
+        _compare_full(kps[i, :counts[i]], desc[i, :counts[i]], ko, do)
+    ex.close()
+
+
+def test_params_variants():
+    img = _image(640, 480, seed=11)
+    for (nf, sc, nl, it, mt) in [(500, 1.2, 8, 20, 7), (1500, 1.3, 6, 30, 10), (300, 1.5, 4, 15, 5),
+                                 (2000, 1.1, 10, 20, 7)]:
+        ex = capi.Extractor(nf, sc, nl, it, mt, max_width=640, max_height=480)
+        orc = O.Extractor(nf, sc, nl, it, mt)
+        ko, do = orc.extract(img)
+        kg, dg = ex.extract(img)
+        _compare_full(kg, dg, ko, do)
+        ex.close()
+
+
+def test_empty_image_is_silent():
+    ex = capi.Extractor()
+    n = C.c_int(-7)
+    rc = capi.lib().orbx_extract(ex.h, None, 0, 0, 0, None, None, 0, C.byref(n))
+    assert rc == 0 and n.value == -7
+    ex.close()
