@@ -1,0 +1,347 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200-native ORB front end.
+
+Workload (BASELINE.json configs[1]): a batch of 4096 synthetic 640x480 frames; one "step" =
+ORBextractor::operator() on every frame (nFeatures 1000, 8 levels, 1.2, FAST 20/7) + consecutive-
+frame ORBmatcher::SearchForInitialization (window 100, nnratio 0.9, orientation check) on the
+4095 pairs.  Metric: frames/s.
+
+  value     device-resident: frames already in HBM, results left in HBM, CUDA events on the
+            stream the kernels run on.
+  e2e       same step through the C ABI with HOST (pinned) images in and HOST results out:
+            H2D of the frames and D2H of keypoints, descriptors, counts and matches are inside the
+            timed region.
+  roofline  dominant kernel (largest share of device time, measured live with CUDA events placed
+            around every stage by liborbx), algorithmic bytes / its time vs MEASURED_PEAKS.json.
+  cpu_baseline  the CPU oracle (restatement of the reference's CPU path) on the box's host cores,
+            bounded sample of the same frames.
+
+`--impl reference` times the reference's CPU path (oracle/_ref when built from the reference's own
+ORBextractor.cc, else the oracle port) with all host threads on the same workload.
+Multi-GPU: one process per GPU (torchrun), frames sharded by rank, no data-path collective
+(weak scaling: every rank processes its own 4096-frame batch).
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W, H = 640, 480
+PARAMS = dict(nfeatures=1000, scale=1.2, nlevels=8, ini_th=20, min_th=7)
+WINDOW, NNRATIO = 100, 0.9
+METRIC = "ORB frames/s (640x480, 1000 kp, extract+match)"
+
+# algorithmic bytes per 640x480 frame (DESIGN.md "Roofline")
+def level_sizes(w, h, nlevels=8, scale=1.2):
+    sf = np.float32(1.0)
+    out = []
+    for l in range(nlevels):
+        inv = np.float32(1.0) / sf
+        out.append((int(np.rint(np.float32(w) * inv)), int(np.rint(np.float32(h) * inv))))
+        sf = np.float32(np.float64(sf) * np.float64(np.float32(scale)))
+    return out
+
+
+def algorithmic_bytes(w, h, nkp):
+    px = [a * b for a, b in level_sizes(w, h)]
+    b_resize = sum(px[:-1]) + sum(px[1:])             # level l reads raw_{l-1}, writes raw_l
+    b_blur = 2 * sum(px)                              # reads raw_l, writes blur_l
+    b_pyr = px[0] + sum(px[:-1]) + px[0] + 2 * sum(px[1:])   # fused formulation (the graded figure)
+    b_fast = sum(px)
+    b_desc = nkp * (749 + 512 + 32 + 28)
+    return dict(resize=b_resize, blur=b_blur, fast=b_fast, describe=b_desc, pyr_fused=b_pyr,
+                total=b_pyr + b_fast + b_desc)
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons during the timed region."""
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def oracle_mod():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib  # test infrastructure: only the cpu_baseline / reference legs use it
+    return oracle_lib
+
+
+def ref_lib():
+    """oracle/_ref: the UNMODIFIED reference ORBextractor.cc over the cv shim, if it was built."""
+    p = os.path.join(ROOT, "oracle", "_ref", "libref_orbextractor.so")
+    if not os.path.exists(p):
+        return None
+    L = C.CDLL(p)
+    L.ref_extract_match_many.restype = C.c_int64
+    return L
+
+
+def cpu_extract_match(frames: np.ndarray, nthreads: int, use_ref: bool):
+    """-> (seconds, kind). frames: [n,h,w] uint8 host."""
+    O = oracle_mod()
+    p = O.Params(PARAMS["nfeatures"], PARAMS["scale"], PARAMS["nlevels"], PARAMS["ini_th"], PARAMS["min_th"])
+    L = ref_lib() if use_ref else None
+    frames = np.ascontiguousarray(frames)
+    n, h, w = frames.shape
+    tm, nc = C.c_int64(), C.c_uint64()
+    fn = L.ref_extract_match_many if L is not None else O.lib().oracle_extract_match_many
+    t0 = time.perf_counter()
+    fn(C.byref(p), frames.ctypes.data_as(C.c_void_p), C.c_size_t(frames.strides[0]), C.c_int(w), C.c_int(h),
+       C.c_size_t(frames.strides[1]), C.c_int(n), C.c_int(nthreads), C.c_int(WINDOW), C.c_float(NNRATIO), C.c_int(1),
+       C.byref(tm), C.byref(nc))
+    return time.perf_counter() - t0, ("reference" if L is not None else "port")
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from orb_slam2_map_b200 import synth
+    cores = os.cpu_count() or 1
+    sample = max(2 * cores, 32)
+    frames = synth.frame_sequence(sample, W, H, seed=0)
+    for _ in range(args.warmup):
+        cpu_extract_match(frames[:max(cores, 8)], cores, True)
+    t, kind = 0.0, "port"
+    for _ in range(args.steps):
+        dt, kind = cpu_extract_match(frames, cores, True)
+        t += dt
+    fps = sample * args.steps / t
+    line = {
+        "impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "configs[1]: 640x480 frames, nFeatures 1000, extract + consecutive-frame "
+                               "SearchForInitialization", "frames_per_step": sample},
+        "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind,
+                         "sample": f"{sample} frames + {sample - 1} pairs per step, one frame per thread"},
+        "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--frames", type=int, default=4096)
+    ap.add_argument("--chunk", type=int, default=64)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from orb_slam2_map_b200 import capi, synth
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+    F = args.frames
+    frames = synth.frame_sequence_torch(F, W, H, seed=rank, device=dev)
+    stream = torch.cuda.current_stream()
+    ex = capi.Extractor(**PARAMS, max_width=W, max_height=H, chunk_frames=args.chunk, result_slots=F, device=local,
+                        stream=stream.cuda_stream)
+
+    def step_device():
+        ex.extract_batch(frames.data_ptr(), nframes=F, width=W, height=H, frame_stride=W * H, row_stride=W,
+                         on_device=True, first_slot=0)
+        ex.search_init_pairs(0, F - 1, WINDOW, NNRATIO, True, fetch=False)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step_device()
+    ex.sync()
+    ex.profile()
+    ex.set_profiling(True)
+    clocks = ClockSampler(local)
+    barrier()
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_device()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    stage_ms, stage_launches = ex.profile()
+    ex.set_profiling(False)
+    clk = clocks.stop()
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    value = world * F * args.steps / (ms * 1e-3)
+
+    # mean keypoints per frame (for the algorithmic byte count)
+    _, _, counts = ex.download(0, min(F, 64), want_kps=False, want_desc=False)
+    nkp = float(counts.mean())
+
+    # ---- e2e: host pinned images in, host results out, through the C ABI ------------------------
+    host = torch.empty((F, H, W), dtype=torch.uint8, pin_memory=True)
+    host.copy_(frames)
+    torch.cuda.synchronize()
+    cap = ex.cap
+    kp_out = torch.empty((F, cap, 28), dtype=torch.uint8, pin_memory=True).numpy().view(capi.KP_DTYPE).reshape(F, cap)
+    de_out = torch.empty((F, cap, 32), dtype=torch.uint8, pin_memory=True).numpy()
+    m12_out = torch.empty((F - 1, cap), dtype=torch.int32, pin_memory=True).numpy()
+    nm_out = torch.empty((F - 1,), dtype=torch.int32, pin_memory=True).numpy()
+    hnp = host.numpy()
+    ncmp = C.c_uint64()
+
+    def step_e2e():
+        ex.extract_batch(hnp)
+        capi.check(capi.lib().orbx_search_init_pairs(ex.h, 0, F - 1, WINDOW, NNRATIO, 1, m12_out.ctypes.data_as(C.c_void_p),
+                                                     nm_out.ctypes.data_as(C.c_void_p), cap, C.byref(ncmp)))
+        return ex.download(0, F, out=(kp_out, de_out))
+
+    _, _, cnts = step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    t = torch.tensor([dt], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * F * args.steps / float(t.item())
+    h2d = F * W * H
+    d2h = kp_out.nbytes + de_out.nbytes + m12_out.nbytes + nm_out.nbytes + 4 * F + 8
+
+    # ---- roofline of the dominant kernel ----------------------------------------------------------
+    peak, peak_src = measured_peaks()
+    ab = algorithmic_bytes(W, H, nkp)
+    frames_total = F * args.steps
+    ext_stages = {k: v for k, v in stage_ms.items() if v > 0}
+    dom = max(ext_stages, key=ext_stages.get) if ext_stages else "fast"
+    dom_bytes = {"resize": ab["resize"], "blur": ab["blur"], "fast": ab["fast"], "describe": ab["describe"]}.get(dom, ab["fast"])
+    dom_launches = max(1, stage_launches.get(dom, 1))
+    dom_ms = stage_ms.get(dom, 0.0)
+    achieved = (dom_bytes * frames_total / dom_launches) / (dom_ms / dom_launches * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_frame": dom_bytes,
+                "share_of_device_time": dom_ms / max(sum(stage_ms.values()), 1e-9)}
+    path_gbs = ab["total"] * value / world / 1e9
+    stages = {k: {"ms_per_step": v / args.steps, "launches_per_step": stage_launches[k] / args.steps}
+              for k, v in stage_ms.items() if stage_launches[k]}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "configs[1]: batch of 4096 synthetic 640x480 frames, ORBextractor(1000,1.2,8,20,7) + "
+                               "consecutive-frame SearchForInitialization(window 100, nnratio 0.9)",
+                   "frames_per_step_per_gpu": F, "chunk_frames": args.chunk, "keypoints_per_frame": nkp,
+                   "l2_policy": "inputs (1.26 GB per step) larger than L2", "sharding": "frames by rank, no collective"},
+        "clocks": clk,
+        "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": int(sum(stage_launches.values())),
+        "roofline": roofline,
+        "path_roofline": {"algorithmic_bytes_per_frame": ab["total"], "achieved": path_gbs, "peak": peak,
+                          "frac": path_gbs / peak, "unit": "GB/s"},
+        "stages": stages,
+        "matches_per_pair": float(nm_out.mean()), "hamming_compares_per_step": int(ncmp.value),
+    }
+
+    # ---- CPU baseline (rank 0, N=1 only): bounded sample of the same frames ----------------------
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        s1 = 16
+        t1, kind = cpu_extract_match(hnp[:s1], 1, False)
+        sN = max(2 * cores, 32)
+        tN, _ = cpu_extract_match(hnp[:sN], cores, False)
+        line["cpu_baseline"] = {"value": sN / tN, "unit": "frames/s", "cores": cores, "kind": kind,
+                                "sample": f"first {sN} frames (+{sN - 1} pairs), one frame per thread on {cores} threads; "
+                                          f"single-thread on {s1} frames: {s1 / t1:.2f} frames/s",
+                                "single_thread_value": s1 / t1}
+    if rank == 0:
+        print(json.dumps(line))
+    ex.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -65,6 +65,14 @@ int orbx_create(const orbx_params* params, int max_width, int max_height, int ch
 int orbx_destroy(orbx_handle* h);
 int orbx_sync(orbx_handle* h);
 
+/* ---- measurement hooks (bench.py): per-stage device time via CUDA events recorded on the
+ * handle's stream around each stage, and the number of kernels launched per stage. */
+enum { ORBX_STAGE_RESIZE = 0, ORBX_STAGE_BLUR, ORBX_STAGE_FAST, ORBX_STAGE_OCTREE, ORBX_STAGE_DESCRIBE,
+       ORBX_STAGE_GRID, ORBX_STAGE_SEARCH_INIT, ORBX_STAGE_STEREO, ORBX_NSTAGES };
+int orbx_set_profiling(orbx_handle* h, int enable);
+/* accumulated since the previous call (synchronises); either pointer may be NULL */
+int orbx_get_profile(orbx_handle* h, double* stage_ms, int64_t* stage_launches);
+
 /* scale tables computed exactly as the reference ctor does (src/ORBextractor.cc:410-446);
  * arrays of nlevels entries, any pointer may be NULL.  Replaces GetScaleFactors & friends. */
 int orbx_get_tables(const orbx_handle* h, float* scale, float* inv_scale, float* sigma2,

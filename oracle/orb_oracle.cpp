@@ -1061,4 +1061,62 @@ int64_t oracle_extract_many(const orbx_params* p, const uint8_t* imgs, size_t fr
     return total;
 }
 
+// CPU baseline driver for BASELINE.json config 2: extract every frame (one frame per thread at a
+// time) and run SearchForInitialization on consecutive pairs with vbPrevMatched = F1 keypoints.
+int64_t oracle_extract_match_many(const orbx_params* p, const uint8_t* imgs, size_t frame_stride,
+                                  int w, int h, size_t stride, int nframes, int nthreads,
+                                  int window_size, float nnratio, int check_orientation,
+                                  int64_t* total_matches, uint64_t* ncompares)
+{
+    if (nthreads < 1) nthreads = 1;
+    const int cap = p->nfeatures + 64 * p->nlevels + 64;
+    std::vector<std::vector<orbx_keypoint>> K(nframes);
+    std::vector<std::vector<u8>> D(nframes);
+    std::atomic<int> next(0);
+    auto extract_work = [&]() {
+        Extractor ex(*p);
+        std::vector<orbx_keypoint> kps(cap);
+        std::vector<u8> desc((size_t)cap * 32);
+        for (;;) {
+            const int f = next.fetch_add(1);
+            if (f >= nframes) break;
+            const int n = std::max(0, ex.extract(imgs + (size_t)f * frame_stride, w, h, stride, kps.data(), desc.data(), cap, false));
+            K[f].assign(kps.begin(), kps.begin() + n);
+            D[f].assign(desc.begin(), desc.begin() + (size_t)n * 32);
+        }
+    };
+    std::atomic<int> nextPair(0);
+    std::atomic<int64_t> matches(0);
+    std::atomic<uint64_t> cmps(0);
+    auto match_work = [&]() {
+        std::vector<float> prev;
+        std::vector<int32_t> m12;
+        for (;;) {
+            const int i = nextPair.fetch_add(1);
+            if (i >= nframes - 1) break;
+            orbm_frame f1{(int32_t)K[i].size(), K[i].data(), D[i].data(), 0.f, (float)w, 0.f, (float)h, nullptr, nullptr, 0};
+            orbm_frame f2{(int32_t)K[i + 1].size(), K[i + 1].data(), D[i + 1].data(), 0.f, (float)w, 0.f, (float)h, nullptr, nullptr, 0};
+            prev.resize(2 * K[i].size() + 2);
+            m12.resize(K[i].size() + 1);
+            for (size_t k = 0; k < K[i].size(); ++k) { prev[2 * k] = K[i][k].x; prev[2 * k + 1] = K[i][k].y; }
+            uint64_t c = 0;
+            matches += oracle_search_for_initialization(&f1, &f2, prev.data(), m12.data(), window_size, nnratio, check_orientation, &c);
+            cmps += c;
+        }
+    };
+    auto run = [&](auto fn) {
+        if (nthreads == 1) { fn(); return; }
+        std::vector<std::thread> th;
+        for (int t = 0; t < nthreads; ++t) th.emplace_back(fn);
+        for (auto& t : th) t.join();
+    };
+    run(extract_work);
+    run(match_work);
+    int64_t total = 0;
+    for (int f = 0; f < nframes; ++f) total += (int64_t)K[f].size();
+    if (total_matches) *total_matches = matches;
+    if (ncompares) *ncompares = cmps;
+    return total;
+}
+
 } // extern "C"

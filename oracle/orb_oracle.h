@@ -75,6 +75,13 @@ void oracle_knn2(const uint8_t* queries, int64_t nq, const uint8_t* database, in
 int64_t oracle_extract_many(const orbx_params* p, const uint8_t* imgs, size_t frame_stride, int w,
                             int h, size_t stride, int nframes, int nthreads);
 
+/* config-2 CPU baseline: extraction of all frames + SearchForInitialization on consecutive pairs;
+ * returns total keypoints. */
+int64_t oracle_extract_match_many(const orbx_params* p, const uint8_t* imgs, size_t frame_stride,
+                                  int w, int h, size_t stride, int nframes, int nthreads,
+                                  int window_size, float nnratio, int check_orientation,
+                                  int64_t* total_matches, uint64_t* ncompares);
+
 #ifdef __cplusplus
 }
 #endif

@@ -51,7 +51,10 @@ class StereoInput(C.Structure):
                 ("bf", C.c_float), ("fx", C.c_float)]
 
 
+STAGES = ["resize", "blur", "fast", "octree", "describe", "grid", "search_init", "stereo"]
+
 EXPORTS = [
+    "orbx_set_profiling", "orbx_get_profile",
     "orbx_last_error", "orbx_device_count", "orbx_create", "orbx_destroy", "orbx_sync", "orbx_get_tables",
     "orbx_keypoint_capacity", "orbx_extract", "orbx_extract_batch", "orbx_download", "orbx_get_level",
     "orbx_get_candidates", "orbx_search_init_pairs", "orbx_extract_stereo_batch",
@@ -81,6 +84,8 @@ def lib():
                                   C.POINTER(C.c_void_p)]
         L.orbx_destroy.argtypes = [C.c_void_p]
         L.orbx_sync.argtypes = [C.c_void_p]
+        L.orbx_set_profiling.argtypes = [C.c_void_p, C.c_int]
+        L.orbx_get_profile.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.orbx_get_tables.argtypes = [C.c_void_p] + [C.c_void_p] * 5
         L.orbx_keypoint_capacity.argtypes = [C.c_void_p]
         L.orbx_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_void_p, C.c_void_p,
@@ -152,6 +157,16 @@ class Extractor:
 
     def sync(self):
         check(lib().orbx_sync(self.h))
+
+    def set_profiling(self, on: bool):
+        check(lib().orbx_set_profiling(self.h, int(on)))
+
+    def profile(self):
+        """-> ({stage: ms}, {stage: launches}) accumulated since the previous call."""
+        ms = np.zeros(len(STAGES), np.float64)
+        ln = np.zeros(len(STAGES), np.int64)
+        check(lib().orbx_get_profile(self.h, _p(ms), _p(ln)))
+        return dict(zip(STAGES, ms.tolist())), dict(zip(STAGES, ln.tolist()))
 
     def tables(self):
         n = self.nlevels

@@ -59,9 +59,51 @@ static void compute_tables(orbx_handle* h)
     }
 }
 
+void orbx_prof_mark(orbx_handle* h, int stage)
+{
+    if (!h->profiling) return;
+    if (h->evUsed == h->evPool.size()) {
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return;
+        h->evPool.push_back(e);
+        h->evStage.push_back(-1);
+    }
+    cudaEventRecord(h->evPool[h->evUsed], h->stream);
+    h->evStage[h->evUsed] = stage;
+    ++h->evUsed;
+}
+
 extern "C" {
 
 const char* orbx_last_error(void) { return g_err; }
+
+int orbx_set_profiling(orbx_handle* h, int enable)
+{
+    if (!h) { orbx_set_error("null handle"); return ORBX_E_INVALID; }
+    h->profiling = enable != 0;
+    return ORBX_OK;
+}
+
+int orbx_get_profile(orbx_handle* h, double* stage_ms, int64_t* stage_launches)
+{
+    if (!h) { orbx_set_error("null handle"); return ORBX_E_INVALID; }
+    ORBX_CUDA(cudaSetDevice(h->device));
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    for (size_t i = 1; i < h->evUsed; ++i) {
+        const int st = h->evStage[i];
+        if (st < 0) continue;
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, h->evPool[i - 1], h->evPool[i]) == cudaSuccess) h->stageMs[st] += ms;
+    }
+    h->evUsed = 0;
+    for (int s = 0; s < ORBX_NSTAGES; ++s) {
+        if (stage_ms) stage_ms[s] = h->stageMs[s];
+        if (stage_launches) stage_launches[s] = h->stageLaunches[s];
+        h->stageMs[s] = 0.0;
+        h->stageLaunches[s] = 0;
+    }
+    return ORBX_OK;
+}
 
 int orbx_device_count(void)
 {
@@ -105,6 +147,8 @@ int orbx_create(const orbx_params* params, int max_width, int max_height, int ch
     h->matchScratchPerPair = 0;
     h->hStage = nullptr; h->hStageBytes = 0;
     h->lastChunkFrames = 0;
+    h->profiling = false; h->evUsed = 0;
+    for (int s = 0; s < ORBX_NSTAGES; ++s) { h->stageMs[s] = 0.0; h->stageLaunches[s] = 0; }
     if (stream) { h->stream = (cudaStream_t)stream; h->ownStream = false; }
     else { ORBX_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)); h->ownStream = true; }
     compute_tables(h);
@@ -143,6 +187,7 @@ int orbx_destroy(orbx_handle* h)
                     h->dNCompares, h->dURight, h->dDepth, h->dMatchScratch};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->hStage) cudaFreeHost(h->hStage);
+    for (cudaEvent_t e : h->evPool) cudaEventDestroy(e);
     if (h->ownStream) cudaStreamDestroy(h->stream);
     delete h;
     return ORBX_OK;

@@ -828,6 +828,7 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
     const signed char* dPat = nullptr;
     int rc = get_pattern(h->device, &dPat);
     if (rc) return rc;
+    orbx_prof_mark(h, -1);
     // K1a: levels 1..n-1, each from the previous one
     for (int l = 1; l < nl; ++l) {
         const LevelGeom& S = g.L[l - 1];
@@ -839,8 +840,12 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
         pyr_resize_kernel<<<grid, block, 0, st>>>(src, sfs, sp, h->dRaw + D.off, g.pyrFrameBytes, D.pitch, D.w, D.h,
                                                   h->dCoef + D.coefX, h->dCoef + D.coefY);
     }
+    ORBX_COUNT(h, ORBX_STAGE_RESIZE, nl - 1);
+    orbx_prof_mark(h, ORBX_STAGE_RESIZE);
     // K1b: blur of all levels
     blur7_kernel<<<dim3(h->nBlurTiles, nframes), 256, 0, st>>>(g, l0, h->dRaw, h->dBlur, h->dBlurTiles);
+    ORBX_COUNT(h, ORBX_STAGE_BLUR, 1);
+    orbx_prof_mark(h, ORBX_STAGE_BLUR);
     // K2: FAST
     ORBX_CUDA(cudaMemsetAsync(h->dLevelCandCount, 0, (size_t)nframes * nl * sizeof(unsigned), st));
     {
@@ -855,6 +860,8 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
         fast_cells_kernel<<<blocks, FAST_WARPS * 32, smem, st>>>(g, h->dCells, l0, h->dRaw, nframes, h->params.min_th_fast,
                                                                   h->params.ini_th_fast, h->dCand, h->dCellSeg, h->dLevelCandCount,
                                                                   tilePitch, scorePitch, warpSmem);
+        ORBX_COUNT(h, ORBX_STAGE_FAST, 1);
+        orbx_prof_mark(h, ORBX_STAGE_FAST);
     }
     // K3: quadtree
     {
@@ -866,6 +873,8 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
         if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         octree_kernel<<<nframes * nl, 32, smem, st>>>(g, nframes, h->dCand, h->dCellSeg, h->dLevelCandCount, h->dKeysA, h->dKeysB,
                                                        h->dLevelKps, h->dLevelKpCount, nodeCap, sortCap, h->dStatus);
+        ORBX_COUNT(h, ORBX_STAGE_OCTREE, 1);
+        orbx_prof_mark(h, ORBX_STAGE_OCTREE);
     }
     // K4: orientation + descriptors + output records
     {
@@ -874,6 +883,8 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
         describe_kernel<<<blocks, DESC_WARPS * 32, 0, st>>>(g, l0, h->dRaw, h->dBlur, nframes, h->dLevelKps, h->dLevelKpCount,
                                                              h->dKpMap, dPat, h->dKps, h->dDesc, h->dCount, h->dSlotLevelCount,
                                                              firstSlot, h->kpCap);
+        ORBX_COUNT(h, ORBX_STAGE_DESCRIBE, 1);
+        orbx_prof_mark(h, ORBX_STAGE_DESCRIBE);
     }
     ORBX_CUDA(cudaGetLastError());
     h->lastL0 = l0;

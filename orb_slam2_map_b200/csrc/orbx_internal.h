@@ -122,7 +122,18 @@ struct orbx_handle {
     // pinned staging
     void* hStage;
     size_t hStageBytes;
+    // per-stage device timing (CUDA events on the handle's stream) and launch counting
+    bool profiling;
+    std::vector<cudaEvent_t> evPool;
+    std::vector<int> evStage;       // stage id of the interval that ENDS at event i (-1 = interval start)
+    size_t evUsed;
+    double stageMs[ORBX_NSTAGES];
+    long long stageLaunches[ORBX_NSTAGES];
 };
+
+// record an event closing the interval of `stage` (or opening one when stage < 0)
+void orbx_prof_mark(orbx_handle* h, int stage);
+#define ORBX_COUNT(h, stage, n) ((h)->stageLaunches[stage] += (n))
 
 // orbx_extract.cu
 int orbx_setup_shape(orbx_handle* h, int w, int hgt);

@@ -125,3 +125,37 @@ def plant_near_duplicates(queries: np.ndarray, database: np.ndarray, frac: float
         b = bit[use]
         q[rows, b // 8] ^= (1 << (b % 8)).astype(np.uint8)
     return q
+
+
+# ---- torch twin of frame_sequence (same bytes), used by bench.py to build big batches on the GPU ----
+def _lsr64(z, s):
+    return (z >> s) & ((1 << (64 - s)) - 1)
+
+
+def _splitmix64_torch(x):
+    """splitmix64 on int64 tensors holding uint64 bit patterns (two's-complement wrap-around)."""
+    z = x + (-7046029254386353131)                    # 0x9E3779B97F4A7C15
+    z = (z ^ _lsr64(z, 30)) * (-4658895280553007687)   # 0xBF58476D1CE4E5B9
+    z = (z ^ _lsr64(z, 27)) * (-7723592293110705685)   # 0x94D049BB133111EB
+    return z ^ _lsr64(z, 31)
+
+
+def frame_sequence_torch(nframes: int, width: int, height: int, seed: int = 0, span: int = 256,
+                         device="cuda", out=None, first: int = 0):
+    """[nframes, height, width] uint8 torch tensor, byte-identical to frame_sequence()[first:first+nframes]."""
+    import torch
+    canvas_np = textured_canvas(width + span, height + span // 2 + 1, seed)
+    canvas = torch.from_numpy(canvas_np).to(device)
+    H, W = canvas_np.shape
+    if out is None:
+        out = torch.empty((nframes, height, width), dtype=torch.uint8, device=device)
+    idx = torch.arange(width * height, dtype=torch.int64, device=device)
+    for i in range(nframes):
+        k = first + i
+        ox = k % (W - width + 1)
+        oy = (k // 2) % (H - height + 1)
+        z = _splitmix64_torch(idx + (((seed + 1) << 44) + (k << 24)))
+        m = torch.remainder(torch.remainder(z, 5) + (z < 0).to(torch.int64), 5).to(torch.int16) - 2
+        win = canvas[oy:oy + height, ox:ox + width].to(torch.int16) + m.view(height, width)
+        out[i] = win.clamp_(0, 255).to(torch.uint8)
+    return out

@@ -71,6 +71,7 @@ def lib():
         L.oracle_extractor_create.argtypes = [C.POINTER(Params)]
         L.oracle_extractor_destroy.argtypes = [C.c_void_p]
         L.oracle_extract_many.restype = C.c_int64
+        L.oracle_extract_match_many.restype = C.c_int64
         L.oracle_cv_round.argtypes = [C.c_double]
         _LIB = L
     return _LIB
@@ -285,3 +286,14 @@ def extract_many(params: Params, imgs: np.ndarray, nthreads: int) -> int:
     n, h, w = imgs.shape
     return int(lib().oracle_extract_many(C.byref(params), _p(imgs), C.c_size_t(imgs.strides[0]), C.c_int(w),
                                          C.c_int(h), C.c_size_t(imgs.strides[1]), C.c_int(n), C.c_int(nthreads)))
+
+
+def extract_match_many(params: Params, imgs: np.ndarray, nthreads: int, window=100, nnratio=0.9, check_ori=True):
+    """config-2 CPU baseline driver -> (total keypoints, total matches, descriptor compares)."""
+    imgs = np.ascontiguousarray(imgs)
+    n, h, w = imgs.shape
+    tm, nc = C.c_int64(), C.c_uint64()
+    tk = lib().oracle_extract_match_many(C.byref(params), _p(imgs), C.c_size_t(imgs.strides[0]), C.c_int(w), C.c_int(h),
+                                         C.c_size_t(imgs.strides[1]), C.c_int(n), C.c_int(nthreads), C.c_int(window),
+                                         C.c_float(nnratio), C.c_int(int(check_ori)), C.byref(tm), C.byref(nc))
+    return int(tk), tm.value, nc.value
