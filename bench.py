@@ -214,7 +214,10 @@ def main():
     dev = torch.device("cuda", local)
     F = args.frames
     frames = synth.frame_sequence_torch(F, W, H, seed=rank, device=dev)
-    stream = torch.cuda.current_stream()
+    # a real (non-default) stream: liborbx launches on it and the CUDA events below are recorded on it
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
     ex = capi.Extractor(**PARAMS, max_width=W, max_height=H, chunk_frames=args.chunk, result_slots=F, device=local,
                         stream=stream.cuda_stream)
 
