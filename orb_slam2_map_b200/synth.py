@@ -87,7 +87,7 @@ def frame_sequence(nframes: int, width: int, height: int, seed: int = 0, span: i
 
 def stereo_pair(width: int, height: int, seed: int = 0, k: int = 0):
     """(left, right): right(x) = left(x + d(y-band)), disparities 5..60 px in 8 horizontal bands."""
-    canvas = textured_canvas(width + 96, height, seed)
+    canvas = textured_canvas(width + 128, height, seed)
     left = canvas[:, 64:64 + width].copy()
     right = np.empty_like(left)
     nb = 8
