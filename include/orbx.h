@@ -222,6 +222,9 @@ int orbm_compute_stereo_matches(const orbm_stereo_input* in, float* u_right, flo
  * `stream` (cudaStream_t or NULL = default stream). */
 int orbm_knn2_device(const uint8_t* queries, int64_t nq, const uint8_t* database, int64_t ndb,
                      int32_t db_index_offset, uint16_t* out_dist, int32_t* out_idx, void* stream);
+/* Tuning hook: how the 256-bit popcount is evaluated (0 = 8 POPC, 1 = carry-save 5 POPC [default],
+ * 2 = Harley-Seal 4 POPC).  Results are identical; only the instruction mix changes. */
+int orbm_knn2_set_variant(int variant);
 /* Merge `nparts` per-shard results (each [nq][2]) into one, same tie rule; device pointers. */
 int orbm_knn2_merge_device(const uint16_t* part_dist, const int32_t* part_idx, int nparts,
                            int64_t nq, uint16_t* out_dist, int32_t* out_idx, void* stream);

@@ -59,7 +59,7 @@ EXPORTS = [
     "orbx_keypoint_capacity", "orbx_extract", "orbx_extract_batch", "orbx_download", "orbx_get_level",
     "orbx_get_candidates", "orbx_search_init_pairs", "orbx_extract_stereo_batch",
     "orbm_descriptor_distance", "orbm_search_for_initialization", "orbm_search_by_projection",
-    "orbm_compute_stereo_matches", "orbm_knn2_device", "orbm_knn2_merge_device",
+    "orbm_compute_stereo_matches", "orbm_knn2_device", "orbm_knn2_merge_device", "orbm_knn2_set_variant",
 ]
 
 _LIB = None

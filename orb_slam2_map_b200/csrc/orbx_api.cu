@@ -251,6 +251,7 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* images, size_t frame_strid
         const int nf = std::min(h->chunkFrames, nframes - f0);
         const uint8_t* src = images + (size_t)f0 * frame_stride;
         Level0 l0;
+        l0.base1 = nullptr; l0.stereo = 0;
         if (direct) { l0.base = src; l0.frameStride = (long long)frame_stride; l0.pitch = (int)row_stride; }
         else {
             const cudaMemcpyKind kind = images_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
@@ -334,7 +335,7 @@ int orbx_get_level(orbx_handle* h, int frame, int level, int blurred, int border
     if (dst_stride < (size_t)(L.w + 2 * border)) { orbx_set_error("dst_stride too small"); return ORBX_E_INVALID; }
     const uint8_t* src; size_t sp;
     if (blurred) { src = h->dBlur + (size_t)frame * h->geom.pyrFrameBytes + L.off; sp = L.pitch; }
-    else if (level == 0) { src = h->lastL0.base + (size_t)frame * h->lastL0.frameStride; sp = h->lastL0.pitch; }
+    else if (level == 0) { src = l0_frame(h->lastL0, frame); sp = h->lastL0.pitch; }
     else { src = h->dRaw + (size_t)frame * h->geom.pyrFrameBytes + L.off; sp = L.pitch; }
     ORBX_CUDA(cudaMemcpy2DAsync(dst + (size_t)border * dst_stride + border, dst_stride, src, sp, L.w, L.h, cudaMemcpyDeviceToHost, h->stream));
     ORBX_CUDA(cudaStreamSynchronize(h->stream));

@@ -27,14 +27,14 @@ typedef uint8_t u8;
 // One thread produces 4 horizontally adjacent pixels and stores them as one 32-bit word.
 // =============================================================================================
 __global__ void __launch_bounds__(256)
-pyr_resize_kernel(const u8* __restrict__ srcBase, long long srcFrameStride, int srcPitch,
+pyr_resize_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long long srcFrameStride, int srcPitch,
                   u8* __restrict__ dstBase, long long dstFrameStride, int dstPitch,
                   int dw, int dh, const int2* __restrict__ cx, const int2* __restrict__ cy)
 {
     const int x4 = (blockIdx.x * 32 + threadIdx.x) * 4;
     const int y = blockIdx.y * 8 + threadIdx.y;
     if (x4 >= dw || y >= dh) return;
-    const u8* src = srcBase + (long long)blockIdx.z * srcFrameStride;
+    const u8* src = fromL0 ? l0_frame(l0, blockIdx.z) : srcBase + (long long)blockIdx.z * srcFrameStride;
     u8* dst = dstBase + (long long)blockIdx.z * dstFrameStride;
     const int2 cyv = cy[y];
     const u8* r0 = src + (long long)(cyv.x & 0xffff) * srcPitch;
@@ -80,7 +80,7 @@ blur7_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, u8* __restrict__
     const int frame = blockIdx.y;
     const u8* src;
     int sp;
-    if (level == 0) { src = l0.base + (long long)frame * l0.frameStride; sp = l0.pitch; }
+    if (level == 0) { src = l0_frame(l0, frame); sp = l0.pitch; }
     else { src = rawBase + (long long)frame * g.pyrFrameBytes + L.off; sp = L.pitch; }
     u8* dst = blurBase + (long long)frame * g.pyrFrameBytes + L.off;
     const int x0 = tx * BL_TW, y0 = ty * BL_TH;
@@ -181,7 +181,7 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
     const LevelGeom& L = g.L[c.level];
     const u8* img;
     int pitch;
-    if (c.level == 0) { img = l0.base + (long long)frame * l0.frameStride; pitch = l0.pitch; }
+    if (c.level == 0) { img = l0_frame(l0, frame); pitch = l0.pitch; }
     else { img = rawBase + (long long)frame * g.pyrFrameBytes + L.off; pitch = L.pitch; }
 
     u8* tile = smem + (size_t)wid * warpSmem;
@@ -618,7 +618,7 @@ describe_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, const u8* __r
     const int px = key_x(packed) + 16, py = key_y(packed) + 16;     // + minBorderX/Y (EDGE_THRESHOLD-3)
     const u8* raw;
     int rp;
-    if (level == 0) { raw = l0.base + (long long)frame * l0.frameStride; rp = l0.pitch; }
+    if (level == 0) { raw = l0_frame(l0, frame); rp = l0.pitch; }
     else { raw = rawBase + (long long)frame * g.pyrFrameBytes + L.off; rp = L.pitch; }
     // ---- IC_Angle: lanes = u in [-15,15], loop over the 31 rows of the disc --------------------
     const int u = lane - 15;
@@ -837,7 +837,7 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
         if (l == 1) { src = l0.base; sfs = l0.frameStride; sp = l0.pitch; }
         else { src = h->dRaw + S.off; sfs = g.pyrFrameBytes; sp = S.pitch; }
         dim3 grid((D.w + 127) / 128, (D.h + 7) / 8, nframes), block(32, 8);
-        pyr_resize_kernel<<<grid, block, 0, st>>>(src, sfs, sp, h->dRaw + D.off, g.pyrFrameBytes, D.pitch, D.w, D.h,
+        pyr_resize_kernel<<<grid, block, 0, st>>>(l0, l == 1 ? 1 : 0, src, sfs, sp, h->dRaw + D.off, g.pyrFrameBytes, D.pitch, D.w, D.h,
                                                   h->dCoef + D.coefX, h->dCoef + D.coefY);
     }
     ORBX_COUNT(h, ORBX_STAGE_RESIZE, nl - 1);

@@ -63,9 +63,16 @@ struct Cell {
 // workspace copy)
 struct Level0 {
     const uint8_t* base;
+    const uint8_t* base1;     // stereo: right-eye images (chunk frame 2p = left p, 2p+1 = right p)
     long long frameStride;
     int pitch;
+    int stereo;
 };
+static __host__ __device__ __forceinline__ const uint8_t* l0_frame(const Level0& l0, int frame)
+{
+    if (l0.stereo) return ((frame & 1) ? l0.base1 : l0.base) + (long long)(frame >> 1) * l0.frameStride;
+    return l0.base + (long long)frame * l0.frameStride;
+}
 
 struct orbx_handle {
     orbx_params params;
@@ -141,5 +148,6 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot);
 
 // orbx_match.cu
 int orbx_build_grids(orbx_handle* h, int firstSlot, int nframes, int width, int height);
+int orbx_ensure_match_buffers(orbx_handle* h);
 
 #endif

@@ -1,0 +1,259 @@
+// orbx_knn.cu — brute-force 2-nearest-neighbour Hamming search over 256-bit ORB descriptors
+// (BASELINE.json config 5) and the cross-shard merge.
+//
+//   K10 knn2_kernel        every query against every database row with ORBmatcher::DescriptorDistance
+//                          (reference src/ORBmatcher.cc:1647-1663), best + second best.
+//   K11 knn2_merge_kernel  merge of per-shard (or per-split) partial results.
+//
+// Ordering rule (the oracle's ascending scan with strict '<'): the result is the two smallest
+// (distance, global index) pairs — ties go to the lower database index.
+//
+// Mapping to the machine: this is XOR/POPC work, not a dense FP contraction, so no tensor cores.
+// Each thread keeps KNN_QPT queries (8 registers each) and their running top-2 in registers; the
+// database streams through shared memory in 8 KB tiles fetched by TMA bulk copies
+// (cp.async.bulk + mbarrier, 4 stages); every lane of a warp reads the same row (broadcast
+// LDS.128), so the kernel is bound by the integer pipes.  The popcount of the 8 XOR words is
+// compressed with carry-save adders (LOP3) so that fewer POPC instructions are needed — POPC
+// issues at a quarter of the LOP3 rate.
+
+#include "orbx_internal.h"
+
+#include <algorithm>
+#include <cstdint>
+
+typedef uint8_t u8;
+
+#define KNN_THREADS 256
+#define KNN_QPT 4                       // queries per thread
+#define KNN_TILE_ROWS 256               // database rows per shared-memory stage (8 KB)
+#define KNN_STAGES 4
+#define KNN_QUERIES_PER_BLOCK (KNN_THREADS * KNN_QPT)
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    uint32_t done;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                     : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    } while (!done);
+}
+
+// popcount of 8 words.  V=0: 8 POPC.  V=1: three carry-save adders, 5 POPC.  V=2: Harley-Seal, 4 POPC.
+template <int V>
+__device__ __forceinline__ int popc8(uint32_t x0, uint32_t x1, uint32_t x2, uint32_t x3, uint32_t x4, uint32_t x5,
+                                     uint32_t x6, uint32_t x7)
+{
+    if (V == 0) {
+        return (__popc(x0) + __popc(x1) + __popc(x2)) + (__popc(x3) + __popc(x4) + __popc(x5)) + (__popc(x6) + __popc(x7));
+    } else {
+        const uint32_t l1 = x0 ^ x1 ^ x2, h1 = (x0 & x1) | (x2 & (x0 | x1));
+        const uint32_t l2 = x3 ^ x4 ^ x5, h2 = (x3 & x4) | (x5 & (x3 | x4));
+        const uint32_t l3 = l1 ^ l2 ^ x6, h3 = (l1 & l2) | (x6 & (l1 | l2));
+        if (V == 1) {
+            return (__popc(l3) + __popc(x7)) + 2 * (__popc(h1) + __popc(h2) + __popc(h3));
+        } else {
+            const uint32_t ones = l3 ^ x7, h4 = l3 & x7;
+            const uint32_t tl = h1 ^ h2 ^ h3, th = (h1 & h2) | (h3 & (h1 | h2));
+            const uint32_t twos = tl ^ h4, fh = tl & h4;
+            const uint32_t fours = th ^ fh, eights = th & fh;
+            return (__popc(ones) + 2 * __popc(twos)) + 4 * (__popc(fours) + 2 * __popc(eights));
+        }
+    }
+}
+
+struct Top2 { int d1, i1, d2, i2; };
+
+__device__ __forceinline__ void top2_push(Top2& t, int d, int j)
+{
+    if (d < t.d2) {
+        if (d < t.d1) { t.d2 = t.d1; t.i2 = t.i1; t.d1 = d; t.i1 = j; }
+        else { t.d2 = d; t.i2 = j; }
+    }
+}
+
+// grid = (query tiles, database splits).  Split s scans rows [s*rowsPerSplit, ...) and writes its
+// partial top-2 to part s of the outputs (outDist/outIdx hold gridDim.y parts of nq entries each).
+template <int V>
+__global__ void __launch_bounds__(KNN_THREADS)
+knn2_kernel(const u8* __restrict__ queries, long long nq, const u8* __restrict__ db, long long ndb,
+            long long rowsPerSplit, int dbIndexOffset, uint16_t* __restrict__ outDist, int* __restrict__ outIdx)
+{
+    __shared__ __align__(128) uint4 tile[KNN_STAGES][KNN_TILE_ROWS * 2];
+    __shared__ __align__(8) uint64_t full[KNN_STAGES];
+    const int tid = threadIdx.x;
+    const long long row0 = (long long)blockIdx.y * rowsPerSplit;
+    const long long rows = min(rowsPerSplit, ndb - row0);
+    const int ntiles = (int)((rows + KNN_TILE_ROWS - 1) / KNN_TILE_ROWS);
+    const u8* dbs = db + row0 * 32;
+    if (tid == 0) {
+        for (int s = 0; s < KNN_STAGES; ++s) mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto issue = [&](int t) {
+        const int s = t % KNN_STAGES;
+        const long long r0 = (long long)t * KNN_TILE_ROWS;
+        const uint32_t bytes = (uint32_t)(min((long long)KNN_TILE_ROWS, rows - r0) * 32);
+        mbar_expect_tx(&full[s], bytes);
+        bulk_g2s(&tile[s][0], dbs + r0 * 32, bytes, &full[s]);
+    };
+    if (tid == 0)
+        for (int t = 0; t < min(ntiles, KNN_STAGES); ++t) issue(t);
+
+    // queries of this thread: q = tileBase + k*KNN_THREADS + tid (coalesced 32-byte rows)
+    const long long qbase = (long long)blockIdx.x * KNN_QUERIES_PER_BLOCK;
+    uint32_t qw[KNN_QPT][8];
+    Top2 best[KNN_QPT];
+#pragma unroll
+    for (int k = 0; k < KNN_QPT; ++k) {
+        const long long q = qbase + (long long)k * KNN_THREADS + tid;
+        uint4 a = make_uint4(0, 0, 0, 0), b = a;
+        if (q < nq) {
+            a = *reinterpret_cast<const uint4*>(queries + q * 32);
+            b = *reinterpret_cast<const uint4*>(queries + q * 32 + 16);
+        }
+        qw[k][0] = a.x; qw[k][1] = a.y; qw[k][2] = a.z; qw[k][3] = a.w;
+        qw[k][4] = b.x; qw[k][5] = b.y; qw[k][6] = b.z; qw[k][7] = b.w;
+        best[k].d1 = best[k].d2 = 257; best[k].i1 = best[k].i2 = -1;
+    }
+    for (int t = 0; t < ntiles; ++t) {
+        const int s = t % KNN_STAGES;
+        mbar_wait(&full[s], (uint32_t)((t / KNN_STAGES) & 1));
+        const int nrow = (int)min((long long)KNN_TILE_ROWS, rows - (long long)t * KNN_TILE_ROWS);
+        const int jbase = (int)(row0 + (long long)t * KNN_TILE_ROWS);       // shard-local row index
+        const uint4* tp = &tile[s][0];
+#pragma unroll 2
+        for (int r = 0; r < nrow; ++r) {
+            const uint4 a = tp[2 * r], b = tp[2 * r + 1];
+#pragma unroll
+            for (int k = 0; k < KNN_QPT; ++k) {
+                const int d = popc8<V>(qw[k][0] ^ a.x, qw[k][1] ^ a.y, qw[k][2] ^ a.z, qw[k][3] ^ a.w,
+                                       qw[k][4] ^ b.x, qw[k][5] ^ b.y, qw[k][6] ^ b.z, qw[k][7] ^ b.w);
+                top2_push(best[k], d, jbase + r);
+            }
+        }
+        __syncthreads();                       // every thread is done with stage s
+        if (tid == 0 && t + KNN_STAGES < ntiles) issue(t + KNN_STAGES);
+    }
+    uint16_t* od = outDist + (long long)blockIdx.y * nq * 2;
+    int* oi = outIdx + (long long)blockIdx.y * nq * 2;
+#pragma unroll
+    for (int k = 0; k < KNN_QPT; ++k) {
+        const long long q = qbase + (long long)k * KNN_THREADS + tid;
+        if (q < nq) {
+            *reinterpret_cast<ushort2*>(od + 2 * q) = make_ushort2((unsigned short)best[k].d1, (unsigned short)best[k].d2);
+            *reinterpret_cast<int2*>(oi + 2 * q) = make_int2(best[k].i1 < 0 ? -1 : best[k].i1 + dbIndexOffset,
+                                                             best[k].i2 < 0 ? -1 : best[k].i2 + dbIndexOffset);
+        }
+    }
+}
+
+// K11: merge nparts partial results per query; order = (distance, global index), -1 = absent.
+__global__ void __launch_bounds__(256)
+knn2_merge_kernel(const uint16_t* __restrict__ partDist, const int* __restrict__ partIdx, int nparts, long long nq,
+                  uint16_t* __restrict__ outDist, int* __restrict__ outIdx)
+{
+    const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= nq) return;
+    unsigned long long k1 = ~0ull, k2 = ~0ull;
+    for (int p = 0; p < nparts; ++p) {
+        const ushort2 d = *reinterpret_cast<const ushort2*>(partDist + ((long long)p * nq + q) * 2);
+        const int2 i = *reinterpret_cast<const int2*>(partIdx + ((long long)p * nq + q) * 2);
+        const unsigned long long a = i.x < 0 ? ~0ull : (((unsigned long long)d.x << 32) | (unsigned)i.x);
+        const unsigned long long b = i.y < 0 ? ~0ull : (((unsigned long long)d.y << 32) | (unsigned)i.y);
+        if (a < k1) { k2 = k1; k1 = a; } else if (a < k2) k2 = a;
+        if (b < k1) { k2 = k1; k1 = b; } else if (b < k2) k2 = b;
+    }
+    *reinterpret_cast<ushort2*>(outDist + 2 * q) = make_ushort2(k1 == ~0ull ? 257 : (unsigned short)(k1 >> 32),
+                                                                k2 == ~0ull ? 257 : (unsigned short)(k2 >> 32));
+    *reinterpret_cast<int2*>(outIdx + 2 * q) = make_int2(k1 == ~0ull ? -1 : (int)(unsigned)k1, k2 == ~0ull ? -1 : (int)(unsigned)k2);
+}
+
+static int g_knn_variant = 1;
+
+extern "C" {
+
+// test/bench hook: 0 = 8 POPC, 1 = 5 POPC + 6 LOP3 (default), 2 = Harley-Seal 4 POPC
+int orbm_knn2_set_variant(int v)
+{
+    if (v < 0 || v > 2) { orbx_set_error("knn2 variant must be 0, 1 or 2"); return ORBX_E_INVALID; }
+    g_knn_variant = v;
+    return ORBX_OK;
+}
+
+int orbm_knn2_device(const uint8_t* queries, int64_t nq, const uint8_t* database, int64_t ndb,
+                     int32_t db_index_offset, uint16_t* out_dist, int32_t* out_idx, void* stream)
+{
+    if (nq <= 0) return ORBX_OK;
+    if (!queries || !out_dist || !out_idx || ndb < 0 || (ndb > 0 && !database)) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
+    if (((uintptr_t)queries | (uintptr_t)database) & 15) { orbx_set_error("descriptor arrays must be 16-byte aligned"); return ORBX_E_INVALID; }
+    if (((uintptr_t)out_dist & 3) || ((uintptr_t)out_idx & 7)) { orbx_set_error("output arrays must be 4/8-byte aligned"); return ORBX_E_INVALID; }
+    if (ndb > 0x7fffffffLL - 1 || (int64_t)db_index_offset + ndb > 0x7fffffffLL) { orbx_set_error("database index exceeds int32"); return ORBX_E_CAPACITY; }
+    int ndev = 0;
+    ORBX_CUDA(cudaGetDeviceCount(&ndev));
+    if (ndev <= 0) { orbx_set_error("no CUDA device; there is no CPU fallback"); return ORBX_E_CUDA; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const long long qtiles = (nq + KNN_QUERIES_PER_BLOCK - 1) / KNN_QUERIES_PER_BLOCK;
+    int dev = 0, sms = 148;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    ORBX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    // few query tiles: split the database so the grid still fills the machine (2 CTAs per SM)
+    long long splits = 1;
+    if (qtiles < 2LL * sms && ndb > 0) {
+        splits = (2LL * sms + qtiles - 1) / qtiles;
+        const long long maxSplits = std::max<long long>(1, ndb / 4096);
+        splits = std::min(splits, maxSplits);
+    }
+    long long rowsPerSplit = ndb > 0 ? (ndb + splits - 1) / splits : 1;
+    rowsPerSplit = (rowsPerSplit + KNN_TILE_ROWS - 1) / KNN_TILE_ROWS * KNN_TILE_ROWS;
+    splits = ndb > 0 ? (ndb + rowsPerSplit - 1) / rowsPerSplit : 1;
+    if (qtiles > 0x7fffffffLL || splits > 65535) { orbx_set_error("grid too large"); return ORBX_E_CAPACITY; }
+    uint16_t* pd = out_dist;
+    int* pi = out_idx;
+    void* scratch = nullptr;
+    if (splits > 1) {
+        ORBX_CUDA(cudaMallocAsync(&scratch, (size_t)splits * nq * 2 * (sizeof(uint16_t) + sizeof(int)), st));
+        pi = (int*)scratch;
+        pd = (uint16_t*)((char*)scratch + (size_t)splits * nq * 2 * sizeof(int));
+    }
+    const dim3 grid((unsigned)qtiles, (unsigned)splits);
+    switch (g_knn_variant) {
+    case 0: knn2_kernel<0><<<grid, KNN_THREADS, 0, st>>>(queries, nq, database, ndb, rowsPerSplit, db_index_offset, pd, pi); break;
+    case 2: knn2_kernel<2><<<grid, KNN_THREADS, 0, st>>>(queries, nq, database, ndb, rowsPerSplit, db_index_offset, pd, pi); break;
+    default: knn2_kernel<1><<<grid, KNN_THREADS, 0, st>>>(queries, nq, database, ndb, rowsPerSplit, db_index_offset, pd, pi); break;
+    }
+    ORBX_CUDA(cudaGetLastError());
+    if (splits > 1) {
+        knn2_merge_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(pd, pi, (int)splits, nq, out_dist, out_idx);
+        ORBX_CUDA(cudaGetLastError());
+        ORBX_CUDA(cudaFreeAsync(scratch, st));
+    }
+    return ORBX_OK;
+}
+
+int orbm_knn2_merge_device(const uint16_t* part_dist, const int32_t* part_idx, int nparts, int64_t nq,
+                           uint16_t* out_dist, int32_t* out_idx, void* stream)
+{
+    if (nq <= 0) return ORBX_OK;
+    if (!part_dist || !part_idx || !out_dist || !out_idx || nparts < 1) { orbx_set_error("bad argument"); return ORBX_E_INVALID; }
+    knn2_merge_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, (cudaStream_t)stream>>>(part_dist, part_idx, nparts, nq, out_dist, out_idx);
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+} // extern "C"

@@ -19,34 +19,7 @@
 #include <cstring>
 #include <vector>
 
-typedef uint8_t u8;
-#define FULL 0xffffffffu
-
-__device__ __forceinline__ int hamming256(const uint32_t a[8], const uint32_t* __restrict__ b)
-{
-    const uint4 b0 = *reinterpret_cast<const uint4*>(b), b1 = *reinterpret_cast<const uint4*>(b + 4);
-    return __popc(a[0] ^ b0.x) + __popc(a[1] ^ b0.y) + __popc(a[2] ^ b0.z) + __popc(a[3] ^ b0.w) +
-           __popc(a[4] ^ b1.x) + __popc(a[5] ^ b1.y) + __popc(a[6] ^ b1.z) + __popc(a[7] ^ b1.w);
-}
-
-__device__ __forceinline__ void load_desc(uint32_t a[8], const u8* __restrict__ p)
-{
-    const uint4 v0 = *reinterpret_cast<const uint4*>(p), v1 = *reinterpret_cast<const uint4*>(p + 16);
-    a[0] = v0.x; a[1] = v0.y; a[2] = v0.z; a[3] = v0.w; a[4] = v1.x; a[5] = v1.y; a[6] = v1.z; a[7] = v1.w;
-}
-
-struct GridParams { float minX, minY, invW, invH; };
-
-// frames live in a store: kps[slot*cap + i], desc[(slot*cap + i)*32], count[slot],
-// gridStart[slot*(CELLS+1) + c], gridIdx[slot*cap + j]
-struct FrameStore {
-    const orbx_keypoint* kps;
-    const u8* desc;
-    const int* count;
-    unsigned short* gridStart;
-    unsigned short* gridIdx;
-    int cap;
-};
+#include "orbx_match_common.cuh"
 
 // =============================================================================================
 // K6: frame grid.  One warp per frame: count -> exclusive scan -> stable fill (ascending keypoint
@@ -108,58 +81,6 @@ grid_build_kernel(FrameStore fs, int firstSlot, GridParams gp)
         }
         __syncwarp();
     }
-}
-
-// Frame::GetFeaturesInArea cell window (src/Frame.cc:332-346); returns false when empty.
-__device__ __forceinline__ bool area_cells(const GridParams& gp, float x, float y, float r, int& cx0, int& cx1,
-                                           int& cy0, int& cy1)
-{
-    cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, gp.minX), r), gp.invW)));
-    if (cx0 >= ORBX_GRID_COLS) return false;
-    cx1 = min(ORBX_GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, gp.minX), r), gp.invW)));
-    if (cx1 < 0) return false;
-    cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, gp.minY), r), gp.invH)));
-    if (cy0 >= ORBX_GRID_ROWS) return false;
-    cy1 = min(ORBX_GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, gp.minY), r), gp.invH)));
-    if (cy1 < 0) return false;
-    return true;
-}
-
-// top-2 merge across the warp: best = min (dist, key), second = second smallest distance
-__device__ __forceinline__ void warp_top2(int& best, unsigned& key, int& second)
-{
-    for (int d = 16; d > 0; d >>= 1) {
-        const int ob = __shfl_xor_sync(FULL, best, d);
-        const unsigned ok = __shfl_xor_sync(FULL, key, d);
-        const int os = __shfl_xor_sync(FULL, second, d);
-        if (ob < best || (ob == best && ok < key)) { second = min(min(second, os), best); best = ob; key = ok; }
-        else second = min(min(second, os), ob);
-    }
-}
-
-// ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:1601-1642)
-__device__ void three_maxima(const int* histo, int L, int& ind1, int& ind2, int& ind3)
-{
-    int max1 = 0, max2 = 0, max3 = 0;
-    ind1 = ind2 = ind3 = -1;
-    for (int i = 0; i < L; ++i) {
-        const int s = histo[i];
-        if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
-        else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
-        else if (s > max3) { max3 = s; ind3 = i; }
-    }
-    if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
-    else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
-}
-
-__device__ __forceinline__ int rot_bin(float a1, float a2)
-{
-    const float factor = 1.0f / ORBX_HISTO_LENGTH;
-    float rot = __fsub_rn(a1, a2);
-    if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
-    int bin = (int)roundf(__fmul_rn(rot, factor));
-    if (bin == ORBX_HISTO_LENGTH) bin = 0;
-    return bin;
 }
 
 // =============================================================================================
@@ -269,6 +190,307 @@ search_init_kernel(FrameStore fs, int firstSlot, int slotStride, GridParams gp, 
     }
 }
 
+// =============================================================================================
+// K9: the four ORBmatcher::SearchByProjection variants on flattened queries.  The reference loops
+// over map points in order and a match changes what later queries may take (occupied flags), so
+// one warp replays the query order; the candidates of one query (grid cells of
+// Frame::GetFeaturesInArea) are spread over the lanes.  "First minimum / second minimum in scan
+// order" (strict '<' updates, src/ORBmatcher.cc:100-114) = the two smallest 64-bit keys
+// dist | cell | idx | octave, because the scan order is (cell, idx) ascending.
+// =============================================================================================
+__device__ __forceinline__ void top2_insert(unsigned long long& k1, unsigned long long& k2, unsigned long long k)
+{
+    if (k < k1) { k2 = k1; k1 = k; }
+    else if (k < k2) k2 = k;
+}
+
+__global__ void __launch_bounds__(32)
+search_proj_kernel(FrameStore fs, int slot, GridParams gp, const float* __restrict__ uRight,
+                   const orbm_proj_query* __restrict__ queries, const u8* __restrict__ qdesc, int nq,
+                   const u8* __restrict__ queryBlocks, u8* __restrict__ occupied, int* __restrict__ assigned,
+                   int* __restrict__ bestIdxOut, int* __restrict__ bestDistOut, u8* __restrict__ binOf,
+                   int variant, int thDist, float nnratio, int checkOri, int* __restrict__ nmatchesOut)
+{
+    __shared__ int hist[ORBX_HISTO_LENGTH];
+    const int lane = threadIdx.x;
+    const int n = min(fs.count[slot], fs.cap);
+    const orbx_keypoint* kps = fs.kps + (size_t)slot * fs.cap;
+    const u8* desc = fs.desc + (size_t)slot * fs.cap * 32;
+    const unsigned short* gs = fs.gridStart + (size_t)slot * (ORBX_GRID_CELLS + 1);
+    const unsigned short* gi = fs.gridIdx + (size_t)slot * fs.cap;
+    if (lane < ORBX_HISTO_LENGTH) hist[lane] = 0;
+    for (int i = lane; i < n; i += 32) assigned[i] = -1;
+    __syncwarp();
+    const bool rot = checkOri && (variant == ORBM_PROJ_LASTFRAME || variant == ORBM_PROJ_KEYFRAME);
+    const bool gate = (variant == ORBM_PROJ_LOCALMAP || variant == ORBM_PROJ_LASTFRAME) && uRight != nullptr;
+    const unsigned long long NONE = ~0ull;
+    int nmatches = 0;
+    for (int q = 0; q < nq; ++q) {
+        const orbm_proj_query Q = queries[q];
+        int bIdx = -1, bDist = 256;
+        int cx0, cx1, cy0, cy1;
+        if (area_cells(gp, Q.u, Q.v, Q.radius, cx0, cx1, cy0, cy1)) {
+            uint32_t qd[8];
+            load_desc(qd, qdesc + (size_t)q * 32);
+            const bool checkLevels = (Q.min_level > 0) || (Q.max_level >= 0);
+            const int ncy = cy1 - cy0 + 1, nc = (cx1 - cx0 + 1) * ncy;
+            unsigned long long k1 = NONE, k2 = NONE;
+            for (int c = lane; c < nc; c += 32) {
+                const int ix = cx0 + c / ncy, iy = cy0 + c % ncy;
+                const int cell = ix * ORBX_GRID_ROWS + iy;
+                const int s = gs[cell], e = gs[cell + 1];
+                for (int j = s; j < e; ++j) {
+                    const int idx = gi[j];
+                    const orbx_keypoint kp = kps[idx];
+                    if (checkLevels) {
+                        if (kp.octave < Q.min_level) continue;
+                        if (Q.max_level >= 0 && kp.octave > Q.max_level) continue;
+                    }
+                    if (!(fabsf(__fsub_rn(kp.x, Q.u)) < Q.radius && fabsf(__fsub_rn(kp.y, Q.v)) < Q.radius)) continue;
+                    if (occupied[idx]) continue;
+                    if (gate) {
+                        const float ur = uRight[idx];
+                        if (ur > 0 && Q.max_right_err >= 0 && fabsf(__fsub_rn(Q.u_right, ur)) > Q.max_right_err) continue;
+                    }
+                    if (Q.level_lo >= 0 && (kp.octave < Q.level_lo || kp.octave > Q.level_hi)) continue;
+                    const int dist = hamming256(qd, reinterpret_cast<const uint32_t*>(desc + (size_t)idx * 32));
+                    const unsigned long long key = ((unsigned long long)dist << 40) | ((unsigned long long)cell << 24) |
+                                                   ((unsigned long long)idx << 8) | (unsigned long long)(kp.octave & 0xff);
+                    top2_insert(k1, k2, key);
+                }
+            }
+            for (int d = 16; d > 0; d >>= 1) {
+                const unsigned long long o1 = __shfl_xor_sync(FULL, k1, d), o2 = __shfl_xor_sync(FULL, k2, d);
+                top2_insert(k1, k2, o1);
+                top2_insert(k1, k2, o2);
+            }
+            if (k1 != NONE) {
+                const int bestDist = (int)(k1 >> 40), bestLevel = (int)(k1 & 0xff), bestIdx = (int)((k1 >> 8) & 0xffff);
+                // reference initial values: bestDist2 = 256, bestLevel2 = -1 (src/ORBmatcher.cc:73-77)
+                const int bestDist2 = (k2 != NONE && (int)(k2 >> 40) < 256) ? (int)(k2 >> 40) : 256;
+                const int bestLevel2 = (k2 != NONE && (int)(k2 >> 40) < 256) ? (int)(k2 & 0xff) : -1;
+                bool ok = bestDist < 256 && bestDist <= thDist;
+                if (ok && variant == ORBM_PROJ_LOCALMAP && bestLevel == bestLevel2 &&
+                    (float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) ok = false;
+                if (ok) { bIdx = bestIdx; bDist = bestDist; }
+            }
+        }
+        if (bIdx >= 0) {
+            ++nmatches;
+            if (lane == 0) {
+                assigned[bIdx] = q;
+                const bool blocks = (variant == ORBM_PROJ_KEYFRAME || variant == ORBM_PROJ_SIM3) ? true
+                                    : (queryBlocks ? queryBlocks[q] != 0 : true);
+                occupied[bIdx] = blocks ? 1 : 0;
+                if (rot) { const int bin = rot_bin(Q.angle, kps[bIdx].angle); binOf[q] = (u8)bin; hist[bin] += 1; }
+            }
+        }
+        if (lane == 0) { bestIdxOut[q] = bIdx; bestDistOut[q] = bDist; if (rot && bIdx < 0) binOf[q] = 0xff; }
+        __syncwarp();
+    }
+    __threadfence_block();
+    __syncwarp();
+    if (rot) {
+        int i1, i2, i3;
+        three_maxima(hist, ORBX_HISTO_LENGTH, i1, i2, i3);
+        for (int q0 = 0; q0 < nq; q0 += 32) {
+            const int q = q0 + lane;
+            bool cull = false;
+            if (q < nq) {
+                const int b = binOf[q];
+                cull = b != 0xff && b != i1 && b != i2 && b != i3;
+                if (cull) assigned[bestIdxOut[q]] = -1;
+            }
+            nmatches -= __popc(__ballot_sync(FULL, cull));
+        }
+    }
+    if (lane == 0) *nmatchesOut = nmatches;
+}
+
+// =============================================================================================
+// K8: Frame::ComputeStereoMatches (src/Frame.cc:466-638).  One CTA per stereo pair.
+//  phase 1  every right keypoint -> (minr, maxr, octave, x): the rows it is filed under (:480-491)
+//  phase 2  warp per left keypoint: lanes scan the right keypoints (ascending index = the order
+//           of vRowIndices[row]), Hamming argmin with strict '<' from TH_HIGH (:502-547), then the
+//           11x11 SAD over 11 shifts on the raw pyramids + parabola (:550-621); SAD is integer
+//           valued so int arithmetic equals the reference's float L1 norm.
+//  phase 3  median of the accepted SADs by bisection on the value, cull >= 1.5*1.4*median (:624-637)
+// =============================================================================================
+struct PyrView {
+    const u8* base[2][ORBX_MAX_LEVELS];        // [eye][level], pair p at base + p*pairStride
+    long long pairStride[2][ORBX_MAX_LEVELS];
+    int pitch[2][ORBX_MAX_LEVELS];
+    int w[ORBX_MAX_LEVELS], h[ORBX_MAX_LEVELS];
+    float scale[ORBX_MAX_LEVELS], invScale[ORBX_MAX_LEVELS];
+    int nlevels;
+};
+
+__device__ __forceinline__ int reflect101i(int i, int n)
+{
+    if (n == 1) return 0;
+    while (i < 0 || i >= n) i = (i < 0) ? -i : 2 * (n - 1) - i;
+    return i;
+}
+
+#define STEREO_THREADS 256
+__global__ void __launch_bounds__(STEREO_THREADS)
+stereo_match_kernel(FrameStore fs, int firstSlot, PyrView pv, float bf, float fx, int rightCap,
+                    float* __restrict__ uRightOut, float* __restrict__ depthOut, int* __restrict__ sadScratch,
+                    unsigned long long* __restrict__ ncompares)
+{
+    extern __shared__ __align__(16) unsigned char smraw[];
+    int* rRows = reinterpret_cast<int*>(smraw);                 // minr | maxr<<16 (biased by 4096)
+    float* rX = reinterpret_cast<float*>(rRows + rightCap);
+    u8* rOct = reinterpret_cast<u8*>(rX + rightCap);
+    __shared__ int sCount[2];
+    const int pair = blockIdx.x;
+    const int sL = firstSlot + 2 * pair, sR = sL + 1;
+    const int N = min(fs.count[sL], fs.cap), Nr = min(min(fs.count[sR], fs.cap), rightCap);
+    const orbx_keypoint* kL = fs.kps + (size_t)sL * fs.cap;
+    const orbx_keypoint* kR = fs.kps + (size_t)sR * fs.cap;
+    const u8* dL = fs.desc + (size_t)sL * fs.cap * 32;
+    const u8* dR = fs.desc + (size_t)sR * fs.cap * 32;
+    float* uOut = uRightOut + (size_t)pair * fs.cap;
+    float* zOut = depthOut + (size_t)pair * fs.cap;
+    int* sad = sadScratch + (size_t)pair * fs.cap;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int nRows = pv.h[0];
+    for (int i = tid; i < Nr; i += STEREO_THREADS) {
+        const orbx_keypoint kp = kR[i];
+        const float r = __fmul_rn(2.0f, pv.scale[kp.octave]);
+        const int maxr = (int)ceilf(__fadd_rn(kp.y, r)), minr = (int)floorf(__fsub_rn(kp.y, r));
+        rRows[i] = (min(max(minr, -4096), 28000) + 4096) | ((min(max(maxr, -4096), 28000) + 4096) << 16);
+        rX[i] = kp.x;
+        rOct[i] = (u8)kp.octave;
+    }
+    if (tid < 2) sCount[tid] = 0;
+    for (int i = N + tid; i < fs.cap; i += STEREO_THREADS) { uOut[i] = -1.f; zOut[i] = -1.f; }   // unused tail
+    __syncthreads();
+    const float mb = __fdiv_rn(bf, fx);
+    const float minD = -3.f, maxD = __fdiv_rn(bf, mb);
+    unsigned long long ncmp = 0;
+    for (int iL = wid; iL < N; iL += STEREO_THREADS / 32) {
+        const orbx_keypoint kp = kL[iL];
+        float uR = -1.f, z = -1.f;
+        int bestSad = -1;
+        const int row = (int)kp.y;
+        const float minU = __fsub_rn(kp.x, maxD), maxU = __fsub_rn(kp.x, minD);
+        if (row >= 0 && row < nRows && !(maxU < 0)) {
+            uint32_t q[8];
+            load_desc(q, dL + (size_t)iL * 32);
+            unsigned best = ((unsigned)ORBX_TH_HIGH << 16);
+            const int rowb = row + 4096;
+            for (int iR = lane; iR < Nr; iR += 32) {
+                const int rr = rRows[iR];
+                if (rowb < (rr & 0xffff) || rowb > (rr >> 16)) continue;
+                const int o = rOct[iR];
+                if (o < kp.octave - 1 || o > kp.octave + 1) continue;
+                const float x = rX[iR];
+                if (!(x >= minU && x <= maxU)) continue;
+                const unsigned dist = (unsigned)hamming256(q, reinterpret_cast<const uint32_t*>(dR + (size_t)iR * 32));
+                ++ncmp;
+                const unsigned key = (dist << 16) | (unsigned)iR;
+                if (key < best) best = key;        // dist < TH_HIGH, ties -> lowest iR
+            }
+            for (int d = 16; d > 0; d >>= 1) best = min(best, __shfl_xor_sync(FULL, best, d));
+            if ((best >> 16) < (unsigned)ORBX_TH_HIGH) {
+                const int bestIdxR = (int)(best & 0xffff);
+                const int lvl = kp.octave;
+                const float uR0 = rX[bestIdxR];
+                const float sf = pv.invScale[lvl];
+                const float scaleduL = roundf(__fmul_rn(kp.x, sf)), scaledvL = roundf(__fmul_rn(kp.y, sf));
+                const float scaleduR0 = roundf(__fmul_rn(uR0, sf));
+                const int w = 5, L = 5;
+                const float iniu = __fsub_rn(__fadd_rn(scaleduR0, (float)L), (float)w);
+                const float endu = __fadd_rn(__fadd_rn(__fadd_rn(scaleduR0, (float)L), (float)w), 1.f);
+                if (!(iniu < 0 || endu >= (float)pv.w[lvl])) {
+                    const int cuL = (int)scaleduL, cvL = (int)scaledvL, cuR = (int)scaleduR0;
+                    const int lw = pv.w[lvl], lh = pv.h[lvl];
+                    const u8* pl = pv.base[0][lvl] + (long long)pair * pv.pairStride[0][lvl];
+                    const u8* pr = pv.base[1][lvl] + (long long)pair * pv.pairStride[1][lvl];
+                    const int pitL = pv.pitch[0][lvl], pitR = pv.pitch[1][lvl];
+                    const int cL = pl[(long long)reflect101i(cvL, lh) * pitL + reflect101i(cuL, lw)];
+                    int cR[11];
+#pragma unroll
+                    for (int s = 0; s < 11; ++s) cR[s] = pr[(long long)reflect101i(cvL, lh) * pitR + reflect101i(cuR + s - L, lw)];
+                    int acc[11];
+#pragma unroll
+                    for (int s = 0; s < 11; ++s) acc[s] = 0;
+                    for (int p = lane; p < 121; p += 32) {
+                        const int dy = p / 11 - w, dx = p % 11 - w;
+                        const int yy = reflect101i(cvL + dy, lh);
+                        const int a = (int)pl[(long long)yy * pitL + reflect101i(cuL + dx, lw)] - cL;
+                        const u8* rrow = pr + (long long)yy * pitR;
+#pragma unroll
+                        for (int s = 0; s < 11; ++s) {
+                            const int b = (int)rrow[reflect101i(cuR + s - L + dx, lw)] - cR[s];
+                            acc[s] += abs(a - b);
+                        }
+                    }
+#pragma unroll
+                    for (int s = 0; s < 11; ++s)
+                        for (int d = 16; d > 0; d >>= 1) acc[s] += __shfl_xor_sync(FULL, acc[s], d);
+                    int bs = 0x7fffffff, binc = 0;
+#pragma unroll
+                    for (int s = 0; s < 11; ++s) if (acc[s] < bs) { bs = acc[s]; binc = s - L; }
+                    if (!(binc == -L || binc == L)) {
+                        float d1 = 0.f, d2 = 0.f, d3 = 0.f;
+#pragma unroll
+                        for (int s = 0; s < 11; ++s) {
+                            if (s == binc + L - 1) d1 = (float)acc[s];
+                            if (s == binc + L) d2 = (float)acc[s];
+                            if (s == binc + L + 1) d3 = (float)acc[s];
+                        }
+                        const float deltaR = __fdiv_rn(__fsub_rn(d1, d3),
+                                                       __fmul_rn(2.0f, __fsub_rn(__fadd_rn(d1, d3), __fmul_rn(2.0f, d2))));
+                        if (!(deltaR < -1 || deltaR > 1)) {
+                            float bestuR = __fmul_rn(pv.scale[lvl], __fadd_rn(__fadd_rn(scaleduR0, (float)binc), deltaR));
+                            float disparity = __fsub_rn(kp.x, bestuR);
+                            if (disparity >= 0 && disparity < maxD) {
+                                if (disparity <= 0) { disparity = (float)0.01; bestuR = (float)((double)kp.x - 0.01); }
+                                z = __fdiv_rn(bf, disparity);
+                                uR = bestuR;
+                                bestSad = bs;
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        if (lane == 0) { uOut[iL] = uR; zOut[iL] = z; sad[iL] = bestSad; }
+    }
+    for (int d = 16; d > 0; d >>= 1) ncmp += __shfl_xor_sync(FULL, ncmp, d);
+    if (lane == 0 && ncompares && ncmp) atomicAdd(ncompares, ncmp);
+    __syncthreads();
+    // ---- median of accepted SADs: k-th smallest, k = size/2 -----------------------------------------
+    int cnt = 0;
+    for (int i = tid; i < N; i += STEREO_THREADS) cnt += sad[i] >= 0;
+    for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(FULL, cnt, d);
+    if (lane == 0 && cnt) atomicAdd(&sCount[0], cnt);
+    __syncthreads();
+    const int nValid = sCount[0];
+    if (nValid == 0) return;
+    const int k = nValid / 2;
+    int lo = 0, hi = 121 * 510;          // smallest v with count(sad <= v) > k
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        __syncthreads();
+        if (tid == 0) sCount[1] = 0;
+        __syncthreads();
+        int c = 0;
+        for (int i = tid; i < N; i += STEREO_THREADS) { const int s = sad[i]; c += (s >= 0 && s <= mid); }
+        for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(FULL, c, d);
+        if (lane == 0 && c) atomicAdd(&sCount[1], c);
+        __syncthreads();
+        if (sCount[1] > k) hi = mid; else lo = mid + 1;
+    }
+    const float thDist = __fmul_rn(__fmul_rn(1.5f, 1.4f), (float)lo);
+    for (int i = tid; i < N; i += STEREO_THREADS) {
+        const int s = sad[i];
+        if (s >= 0 && !((float)s < thDist)) { uOut[i] = -1.f; zOut[i] = -1.f; }
+    }
+}
+
 __global__ void hamming_pairs_kernel(const u8* __restrict__ a, const u8* __restrict__ b, int n, int* __restrict__ out)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -281,7 +503,7 @@ __global__ void hamming_pairs_kernel(const u8* __restrict__ a, const u8* __restr
 // =============================================================================================
 // host side
 // =============================================================================================
-static int ensure_match_buffers(orbx_handle* h)
+int orbx_ensure_match_buffers(orbx_handle* h)
 {
     if (h->dGridStart) return ORBX_OK;
     const size_t R = (size_t)h->resultSlots;
@@ -332,10 +554,29 @@ static int launch_search_init(const FrameStore& fs, int firstSlot, int slotStrid
 
 int orbx_build_grids(orbx_handle* h, int firstSlot, int nframes, int width, int height)
 {
-    int rc = ensure_match_buffers(h);
+    int rc = orbx_ensure_match_buffers(h);
     if (rc) return rc;
     return launch_grid_build(store_of(h), firstSlot, nframes, grid_params(0.f, (float)width, 0.f, (float)height), h->stream);
 }
+
+static int launch_stereo(const FrameStore& fs, int firstSlot, int npairs, const PyrView& pv, float bf, float fx,
+                         int rightCap, float* uRight, float* depth, int* sadScratch, unsigned long long* ncmp,
+                         cudaStream_t st)
+{
+    const int smem = rightCap * 9 + 16;
+    if (smem > 200 * 1024) { orbx_set_error("more than %d right keypoints per frame unsupported by the stereo matcher", 200 * 1024 / 9); return ORBX_E_CAPACITY; }
+    if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(stereo_match_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    stereo_match_kernel<<<npairs, STEREO_THREADS, smem, st>>>(fs, firstSlot, pv, bf, fx, rightCap, uRight, depth, sadScratch, ncmp);
+    return ORBX_OK;
+}
+
+// device scratch that frees itself (the stateless entry points allocate per call)
+struct DevBuf {
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    int alloc(size_t bytes) { ORBX_CUDA(cudaMalloc(&p, bytes ? bytes : 4)); return ORBX_OK; }
+    template <typename T> T* as() { return (T*)p; }
+};
 
 extern "C" {
 
@@ -349,7 +590,7 @@ int orbx_search_init_pairs(orbx_handle* h, int first_slot, int npairs, int windo
     if (h->curW <= 0) { orbx_set_error("no frames extracted yet"); return ORBX_E_STATE; }
     if (matches12 && capacity < h->kpCap) { orbx_set_error("matches12 capacity %d < %d", capacity, h->kpCap); return ORBX_E_CAPACITY; }
     ORBX_CUDA(cudaSetDevice(h->device));
-    int rc = ensure_match_buffers(h);
+    int rc = orbx_ensure_match_buffers(h);
     if (rc) return rc;
     const FrameStore fs = store_of(h);
     const GridParams gp = grid_params(0.f, (float)h->curW, 0.f, (float)h->curH);
@@ -475,11 +716,184 @@ int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, f
     return ORBX_OK;
 }
 
-#define STUB { orbx_set_error("not implemented yet"); return ORBX_E_STATE; }
-int orbx_extract_stereo_batch(orbx_handle*, const uint8_t*, const uint8_t*, size_t, size_t, int, int, int, int, int, float, float, float*, float*, int, uint64_t*) STUB
-int orbm_search_by_projection(int, const orbm_frame*, const orbm_proj_query*, const uint8_t*, int, const uint8_t*, uint8_t*, int32_t*, int32_t*, int32_t*, int, float, int, int32_t*) STUB
-int orbm_compute_stereo_matches(const orbm_stereo_input*, float*, float*, uint64_t*) STUB
-int orbm_knn2_device(const uint8_t*, int64_t, const uint8_t*, int64_t, int32_t, uint16_t*, int32_t*, void*) STUB
-int orbm_knn2_merge_device(const uint16_t*, const int32_t*, int, int64_t, uint16_t*, int32_t*, void*) STUB
+int orbm_search_by_projection(int variant, const orbm_frame* frame, const orbm_proj_query* queries,
+                              const uint8_t* query_desc, int nq, const uint8_t* query_blocks,
+                              uint8_t* occupied, int32_t* assigned, int32_t* best_idx,
+                              int32_t* best_dist, int th_dist, float nnratio,
+                              int check_orientation, int32_t* nmatches)
+{
+    int rc = check_frame(frame); if (rc) return rc;
+    if (variant < ORBM_PROJ_LOCALMAP || variant > ORBM_PROJ_SIM3) { orbx_set_error("unknown SearchByProjection variant %d", variant); return ORBX_E_INVALID; }
+    if (nq < 0 || (nq > 0 && (!queries || !query_desc || !best_idx || !best_dist)) || (frame->n > 0 && (!occupied || !assigned))) {
+        orbx_set_error("null argument"); return ORBX_E_INVALID;
+    }
+    rc = require_device(); if (rc) return rc;
+    TempFrames tf;
+    rc = tf.alloc(1, frame->n); if (rc) return rc;
+    rc = tf.upload(0, frame); if (rc) return rc;
+    const GridParams gp = grid_params(frame->min_x, frame->max_x, frame->min_y, frame->max_y);
+    rc = launch_grid_build(tf.store(), 0, 1, gp, 0); if (rc) return rc;
+    DevBuf dQ, dQD, dQB, dOcc, dAsg, dBI, dBD, dBin, dNm, dUR;
+    const size_t n = (size_t)std::max(frame->n, 1), Q = (size_t)std::max(nq, 1);
+    if ((rc = dQ.alloc(Q * sizeof(orbm_proj_query))) || (rc = dQD.alloc(Q * 32)) || (rc = dQB.alloc(Q)) ||
+        (rc = dOcc.alloc(n)) || (rc = dAsg.alloc(n * 4)) || (rc = dBI.alloc(Q * 4)) || (rc = dBD.alloc(Q * 4)) ||
+        (rc = dBin.alloc(Q)) || (rc = dNm.alloc(4)) || (rc = dUR.alloc(n * 4))) return rc;
+    if (nq > 0) {
+        ORBX_CUDA(cudaMemcpy(dQ.p, queries, (size_t)nq * sizeof(orbm_proj_query), cudaMemcpyHostToDevice));
+        ORBX_CUDA(cudaMemcpy(dQD.p, query_desc, (size_t)nq * 32, cudaMemcpyHostToDevice));
+        if (query_blocks) ORBX_CUDA(cudaMemcpy(dQB.p, query_blocks, (size_t)nq, cudaMemcpyHostToDevice));
+    }
+    if (frame->n > 0) {
+        ORBX_CUDA(cudaMemcpy(dOcc.p, occupied, (size_t)frame->n, cudaMemcpyHostToDevice));
+        if (frame->u_right) ORBX_CUDA(cudaMemcpy(dUR.p, frame->u_right, (size_t)frame->n * 4, cudaMemcpyHostToDevice));
+    }
+    search_proj_kernel<<<1, 32>>>(tf.store(), 0, gp, frame->u_right ? dUR.as<float>() : nullptr, dQ.as<orbm_proj_query>(),
+                                  dQD.as<u8>(), nq, query_blocks ? dQB.as<u8>() : nullptr, dOcc.as<u8>(), dAsg.as<int>(),
+                                  dBI.as<int>(), dBD.as<int>(), dBin.as<u8>(), variant, th_dist, nnratio,
+                                  check_orientation, dNm.as<int>());
+    ORBX_CUDA(cudaGetLastError());
+    int nm = 0;
+    ORBX_CUDA(cudaMemcpy(&nm, dNm.p, 4, cudaMemcpyDeviceToHost));
+    if (frame->n > 0) {
+        ORBX_CUDA(cudaMemcpy(occupied, dOcc.p, (size_t)frame->n, cudaMemcpyDeviceToHost));
+        ORBX_CUDA(cudaMemcpy(assigned, dAsg.p, (size_t)frame->n * 4, cudaMemcpyDeviceToHost));
+    }
+    if (nq > 0) {
+        ORBX_CUDA(cudaMemcpy(best_idx, dBI.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+        ORBX_CUDA(cudaMemcpy(best_dist, dBD.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+    }
+    if (nmatches) *nmatches = nm;
+    return ORBX_OK;
+}
+int orbm_compute_stereo_matches(const orbm_stereo_input* in, float* u_right, float* depth,
+                                uint64_t* ncompares)
+{
+    if (!in || in->n_left < 0 || in->n_right < 0 || in->nlevels < 1 || in->nlevels > ORBX_MAX_LEVELS ||
+        !in->scale_factors || !in->inv_scale_factors || !in->pyr_left || !in->pyr_right || !in->level_width ||
+        !in->level_height || !in->pyr_stride_left || !in->pyr_stride_right ||
+        (in->n_left > 0 && (!in->keys_left || !in->desc_left || !u_right || !depth)) ||
+        (in->n_right > 0 && (!in->keys_right || !in->desc_right))) {
+        orbx_set_error("bad orbm_stereo_input"); return ORBX_E_INVALID;
+    }
+    if (in->n_left > 65000 || in->n_right > 22000) { orbx_set_error("too many keypoints for the stereo matcher"); return ORBX_E_CAPACITY; }
+    int rc = require_device(); if (rc) return rc;
+    for (int i = 0; i < in->n_left + in->n_right; ++i) {
+        const orbx_keypoint& k = i < in->n_left ? in->keys_left[i] : in->keys_right[i - in->n_left];
+        if (k.octave < 0 || k.octave >= in->nlevels) { orbx_set_error("keypoint octave outside [0,nlevels)"); return ORBX_E_INVALID; }
+    }
+    TempFrames tf;
+    rc = tf.alloc(2, std::max(in->n_left, in->n_right)); if (rc) return rc;
+    orbm_frame fl{in->n_left, in->keys_left, in->desc_left, 0.f, 1.f, 0.f, 1.f, nullptr, nullptr, 0};
+    orbm_frame fr{in->n_right, in->keys_right, in->desc_right, 0.f, 1.f, 0.f, 1.f, nullptr, nullptr, 0};
+    rc = tf.upload(0, &fl); if (rc) return rc;
+    rc = tf.upload(1, &fr); if (rc) return rc;
+    PyrView pv;
+    memset(&pv, 0, sizeof(pv));
+    pv.nlevels = in->nlevels;
+    std::vector<DevBuf> lv(2 * in->nlevels);
+    for (int l = 0; l < in->nlevels; ++l) {
+        pv.w[l] = in->level_width[l]; pv.h[l] = in->level_height[l];
+        pv.scale[l] = in->scale_factors[l]; pv.invScale[l] = in->inv_scale_factors[l];
+        if (pv.w[l] <= 0 || pv.h[l] <= 0) { orbx_set_error("empty pyramid level %d", l); return ORBX_E_INVALID; }
+        for (int e = 0; e < 2; ++e) {
+            const uint8_t* src = e ? in->pyr_right[l] : in->pyr_left[l];
+            const int64_t ss = e ? in->pyr_stride_right[l] : in->pyr_stride_left[l];
+            if (!src || ss < pv.w[l]) { orbx_set_error("bad pyramid level %d", l); return ORBX_E_INVALID; }
+            DevBuf& b = lv[2 * l + e];
+            const int pitch = (pv.w[l] + 15) & ~15;
+            rc = b.alloc((size_t)pitch * pv.h[l]); if (rc) return rc;
+            ORBX_CUDA(cudaMemcpy2D(b.p, pitch, src, (size_t)ss, pv.w[l], pv.h[l], cudaMemcpyHostToDevice));
+            pv.base[e][l] = b.as<u8>(); pv.pitch[e][l] = pitch; pv.pairStride[e][l] = 0;
+        }
+    }
+    DevBuf dU, dZ, dS, dC;
+    const size_t n = (size_t)tf.cap;
+    if ((rc = dU.alloc(n * 4)) || (rc = dZ.alloc(n * 4)) || (rc = dS.alloc(n * 4)) || (rc = dC.alloc(8))) return rc;
+    ORBX_CUDA(cudaMemset(dC.p, 0, 8));
+    rc = launch_stereo(tf.store(), 0, 1, pv, in->bf, in->fx, tf.cap, dU.as<float>(), dZ.as<float>(), dS.as<int>(),
+                       dC.as<unsigned long long>(), 0);
+    if (rc) return rc;
+    ORBX_CUDA(cudaGetLastError());
+    if (in->n_left > 0) {
+        ORBX_CUDA(cudaMemcpy(u_right, dU.p, (size_t)in->n_left * 4, cudaMemcpyDeviceToHost));
+        ORBX_CUDA(cudaMemcpy(depth, dZ.p, (size_t)in->n_left * 4, cudaMemcpyDeviceToHost));
+    }
+    unsigned long long c = 0;
+    ORBX_CUDA(cudaMemcpy(&c, dC.p, 8, cudaMemcpyDeviceToHost));
+    if (ncompares) *ncompares = c;
+    return ORBX_OK;
+}
+
+int orbx_extract_stereo_batch(orbx_handle* h, const uint8_t* left, const uint8_t* right,
+                              size_t frame_stride, size_t row_stride, int width, int height,
+                              int npairs, int images_on_device, int first_slot, float bf, float fx,
+                              float* u_right, float* depth, int capacity, uint64_t* ncompares)
+{
+    if (!h || !left || !right) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
+    if (width <= 0 || height <= 0 || npairs <= 0) return ORBX_OK;
+    if (width < 64 || height < 64) { orbx_set_error("image smaller than 64x64 is outside the extractor's domain"); return ORBX_E_INVALID; }
+    if (row_stride < (size_t)width) { orbx_set_error("row_stride < width"); return ORBX_E_INVALID; }
+    if (h->chunkFrames < 2) { orbx_set_error("stereo needs a handle with chunk_frames >= 2"); return ORBX_E_CAPACITY; }
+    if (first_slot < 0 || first_slot + 2 * npairs > h->resultSlots) { orbx_set_error("slots [%d,%d) exceed result store (%d)", first_slot, first_slot + 2 * npairs, h->resultSlots); return ORBX_E_CAPACITY; }
+    if ((u_right || depth) && capacity < h->kpCap) { orbx_set_error("output capacity %d < %d", capacity, h->kpCap); return ORBX_E_CAPACITY; }
+    if (!(fx > 0) || !(bf > 0)) { orbx_set_error("bf and fx must be positive"); return ORBX_E_INVALID; }
+    ORBX_CUDA(cudaSetDevice(h->device));
+    int rc = orbx_setup_shape(h, width, height); if (rc) return rc;
+    rc = orbx_ensure_match_buffers(h); if (rc) return rc;
+    const Geom& g = h->geom;
+    const bool direct = images_on_device && (row_stride % 4 == 0) && (frame_stride % 4 == 0) &&
+                        (((uintptr_t)left) % 4 == 0) && (((uintptr_t)right) % 4 == 0);
+    const int pairsPerChunk = h->chunkFrames / 2;
+    if (ncompares) ORBX_CUDA(cudaMemsetAsync(h->dNCompares, 0, sizeof(unsigned long long), h->stream));
+    for (int p0 = 0; p0 < npairs; p0 += pairsPerChunk) {
+        const int np = std::min(pairsPerChunk, npairs - p0);
+        Level0 l0;
+        l0.stereo = 1;
+        if (direct) {
+            l0.base = left + (size_t)p0 * frame_stride; l0.base1 = right + (size_t)p0 * frame_stride;
+            l0.frameStride = (long long)frame_stride; l0.pitch = (int)row_stride;
+        } else {
+            const cudaMemcpyKind kind = images_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+            uint8_t* dl = h->dLevel0;
+            uint8_t* dr = h->dLevel0 + (size_t)pairsPerChunk * h->l0FrameBytes;
+            for (int f = 0; f < np; ++f) {
+                ORBX_CUDA(cudaMemcpy2DAsync(dl + (size_t)f * h->l0FrameBytes, h->l0Pitch, left + (size_t)(p0 + f) * frame_stride, row_stride, width, height, kind, h->stream));
+                ORBX_CUDA(cudaMemcpy2DAsync(dr + (size_t)f * h->l0FrameBytes, h->l0Pitch, right + (size_t)(p0 + f) * frame_stride, row_stride, width, height, kind, h->stream));
+            }
+            l0.base = dl; l0.base1 = dr; l0.frameStride = h->l0FrameBytes; l0.pitch = h->l0Pitch;
+        }
+        const int slot0 = first_slot + 2 * p0;
+        rc = orbx_run_chunk(h, l0, 2 * np, slot0); if (rc) return rc;
+        PyrView pv;
+        memset(&pv, 0, sizeof(pv));
+        pv.nlevels = g.nlevels;
+        for (int l = 0; l < g.nlevels; ++l) {
+            const LevelGeom& L = g.L[l];
+            pv.w[l] = L.w; pv.h[l] = L.h; pv.scale[l] = h->scale[l]; pv.invScale[l] = h->invScale[l];
+            for (int e = 0; e < 2; ++e) {
+                if (l == 0) { pv.base[e][0] = e ? l0.base1 : l0.base; pv.pairStride[e][0] = l0.frameStride; pv.pitch[e][0] = l0.pitch; }
+                else { pv.base[e][l] = h->dRaw + (size_t)e * g.pyrFrameBytes + L.off; pv.pairStride[e][l] = 2 * g.pyrFrameBytes; pv.pitch[e][l] = L.pitch; }
+            }
+        }
+        orbx_prof_mark(h, -1);
+        // outputs indexed by pair: pair p of this call lives at row (first_slot/2 + p) of dURight/dDepth
+        const size_t row0 = (size_t)(first_slot / 2 + p0) * h->kpCap;
+        FrameStore fs = store_of(h);
+        // the kernel addresses outputs by blockIdx (pair inside the chunk): pass offset pointers
+        rc = launch_stereo(fs, slot0, np, pv, bf, fx, h->kpCap, h->dURight + row0, h->dDepth + row0,
+                           reinterpret_cast<int*>(h->dMatches12) + row0, ncompares ? h->dNCompares : nullptr, h->stream);
+        if (rc) return rc;
+        ORBX_COUNT(h, ORBX_STAGE_STEREO, 1);
+        orbx_prof_mark(h, ORBX_STAGE_STEREO);
+    }
+    ORBX_CUDA(cudaGetLastError());
+    const size_t row0 = (size_t)(first_slot / 2) * h->kpCap;
+    if (u_right) ORBX_CUDA(cudaMemcpy2DAsync(u_right, (size_t)capacity * 4, h->dURight + row0, (size_t)h->kpCap * 4, (size_t)h->kpCap * 4, npairs, cudaMemcpyDeviceToHost, h->stream));
+    if (depth) ORBX_CUDA(cudaMemcpy2DAsync(depth, (size_t)capacity * 4, h->dDepth + row0, (size_t)h->kpCap * 4, (size_t)h->kpCap * 4, npairs, cudaMemcpyDeviceToHost, h->stream));
+    if (ncompares) ORBX_CUDA(cudaMemcpyAsync(ncompares, h->dNCompares, sizeof(unsigned long long), cudaMemcpyDeviceToHost, h->stream));
+    if (u_right || depth || ncompares) return orbx_sync(h);
+    return ORBX_OK;
+}
+
 
 } // extern "C"

@@ -1,0 +1,5 @@
+# usage: bash scripts/gpu_tests.sh [pytest args]   (run under gpurun)
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -x -q "$@" > gpurun_out/pytest_gpu.log 2>&1
+echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
+tail -40 gpurun_out/pytest_gpu.log
