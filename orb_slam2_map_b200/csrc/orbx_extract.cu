@@ -57,10 +57,16 @@ pyr_resize_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long lo
 
 // =============================================================================================
 // K1b: 7x7 Gaussian blur, kernel [18 34 48 56 48 34 18]/256 per axis, exact integer, reflect-101
-// of the level itself.  Tile 128x32 per CTA, separable through shared memory.
+// of the level itself.  One warp owns a 128 x 32 strip: a lane owns 4 adjacent columns and walks
+// down the rows.  Per row it loads ONE aligned 32-bit word (the warp reads 128 contiguous bytes),
+// takes the neighbouring words from the adjacent lanes by shuffle, forms the horizontal 7-tap sums
+// with byte-permutes + IDP.4A dot products, and keeps the last 7 rows of sums in registers for the
+// vertical pass — no shared memory, every source byte is fetched once per strip (+6 halo rows).
 // =============================================================================================
-#define BL_TW 128
-#define BL_TH 32
+#define BL_TW 120                       // output columns per strip: lanes 1..30 (lanes 0, 31 are halo)
+#define BL_GROUPS 9                     // 7-row groups per strip
+#define BL_TH (7 * BL_GROUPS - 6)       // 57 output rows per strip (+6 halo rows)
+#define BL_WARPS 4
 __device__ __forceinline__ int reflect101(int i, int n)
 {
     if (n == 1) return 0;
@@ -68,13 +74,84 @@ __device__ __forceinline__ int reflect101(int i, int n)
     return i;
 }
 
-__global__ void __launch_bounds__(256)
-blur7_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, u8* __restrict__ blurBase,
-             const int* __restrict__ tiles)
+// bytes at columns x..x+3 (x % 4 == 0, x >= 0) of a row; BORDER_REFLECT_101 beyond column w-1
+template <bool EDGE>
+__device__ __forceinline__ uint32_t row_word(const u8* __restrict__ row, int x, int w)
 {
-    __shared__ u8 sIn[BL_TH + 6][BL_TW + 8];
-    __shared__ unsigned short sH[BL_TH + 6][BL_TW];
-    const int t = tiles[blockIdx.x];
+    if (!EDGE) return *reinterpret_cast<const uint32_t*>(row + x);
+    if (x + 3 < w) return *reinterpret_cast<const uint32_t*>(row + x);
+    if (x >= w + 4) return 0;                    // only feeds lanes whose own pixels are outside the image
+    uint32_t v = 0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) v |= (uint32_t)row[reflect101(min(x + i, w + 2), w)] << (8 * i);
+    return v;
+}
+
+__device__ __forceinline__ int reflect_row(int y, int h)
+{
+    y = y < 0 ? -y : (y >= h ? 2 * (h - 1) - y : y);
+    return max(0, min(y, h - 1));
+}
+
+template <bool EDGE>
+__device__ __forceinline__ void blur_strip(const u8* __restrict__ src, int sp, u8* __restrict__ dst, int dp,
+                                           int w, int h, int x, int y0, int lane)
+{
+    const unsigned FULL = 0xffffffffu;
+    const uint32_t c0 = 18u | (34u << 8) | (48u << 16) | (56u << 24), c1 = 48u | (34u << 8) | (18u << 16);
+    const int rowsOut = min(BL_TH, h - y0);
+    const int ngroups = (rowsOut + 6 + 6) / 7;
+    const int xl = max(x, 0);                    // lane 0 of the first strip sits at x = -4 (built by reflection)
+    uint32_t H[7][4];
+    uint32_t cur[7], nxt[7];
+#pragma unroll
+    for (int k = 0; k < 7; ++k) cur[k] = row_word<EDGE>(src + (long long)reflect_row(y0 - 3 + k, h) * sp, xl, w);
+#pragma unroll 1
+    for (int gi = 0; gi < ngroups; ++gi) {
+        if (gi + 1 < ngroups) {
+#pragma unroll
+            for (int k = 0; k < 7; ++k)
+                nxt[k] = row_word<EDGE>(src + (long long)reflect_row(y0 - 3 + (gi + 1) * 7 + k, h) * sp, xl, w);
+        }
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+            const int r = gi * 7 + k;
+            uint32_t w1 = cur[k];
+            const uint32_t d1 = __shfl_down_sync(FULL, w1, 1), d2 = __shfl_down_sync(FULL, w1, 2);
+            if (x < 0) w1 = __byte_perm(d1, d2, 0x1234);          // columns -4..-1 = columns 4,3,2,1
+            const uint32_t w0 = __shfl_up_sync(FULL, w1, 1), w2 = d1;   // lane+1 is never the patched lane
+            H[k][0] = __dp4a(__byte_perm(w0, w1, 0x4321), c0, __dp4a(__byte_perm(w1, w2, 0x4321), c1, 0u));
+            H[k][1] = __dp4a(__byte_perm(w0, w1, 0x5432), c0, __dp4a(__byte_perm(w1, w2, 0x5432), c1, 0u));
+            H[k][2] = __dp4a(__byte_perm(w0, w1, 0x6543), c0, __dp4a(__byte_perm(w1, w2, 0x6543), c1, 0u));
+            H[k][3] = __dp4a(w1, c0, __dp4a(w2, c1, 0u));
+            // rows r-6 .. r are in slots (k+1)%7 .. k ; output row y = y0 + r - 6
+            const int y = y0 + r - 6;
+            if (r >= 6 && y < h) {
+                uint32_t o[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const uint32_t s0 = H[(k + 1) % 7][j] + H[k][j];
+                    const uint32_t s1 = H[(k + 2) % 7][j] + H[(k + 6) % 7][j];
+                    const uint32_t s2 = H[(k + 3) % 7][j] + H[(k + 5) % 7][j];
+                    o[j] = 18u * s0 + 34u * s1 + 48u * s2 + 56u * H[(k + 4) % 7][j] + 32768u;   // result in bits 16..23
+                }
+                const uint32_t lo = __byte_perm(o[0], o[1], 0x0062), hi = __byte_perm(o[2], o[3], 0x0062);
+                if (lane >= 1 && lane <= 30 && x < w) *reinterpret_cast<uint32_t*>(dst + (long long)y * dp + x) = __byte_perm(lo, hi, 0x5410);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 7; ++k) cur[k] = nxt[k];
+    }
+}
+
+__global__ void __launch_bounds__(BL_WARPS * 32)
+blur7_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, u8* __restrict__ blurBase,
+             const int* __restrict__ tiles, int ntiles)
+{
+    const int lane = threadIdx.x & 31;
+    const int ti = blockIdx.x * BL_WARPS + (threadIdx.x >> 5);
+    if (ti >= ntiles) return;
+    const int t = tiles[ti];
     const int level = t >> 24, ty = (t >> 12) & 0xfff, tx = t & 0xfff;
     const LevelGeom& L = g.L[level];
     const int frame = blockIdx.y;
@@ -83,38 +160,10 @@ blur7_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, u8* __restrict__
     if (level == 0) { src = l0_frame(l0, frame); sp = l0.pitch; }
     else { src = rawBase + (long long)frame * g.pyrFrameBytes + L.off; sp = L.pitch; }
     u8* dst = blurBase + (long long)frame * g.pyrFrameBytes + L.off;
-    const int x0 = tx * BL_TW, y0 = ty * BL_TH;
-    const int tid = threadIdx.x;
-    // load (BL_TH+6) x (BL_TW+6) with reflection
-    for (int i = tid; i < (BL_TH + 6) * (BL_TW + 6); i += 256) {
-        const int r = i / (BL_TW + 6), c = i - r * (BL_TW + 6);
-        const int yy = reflect101(min(y0 + r - 3, L.h + 2), L.h);
-        const int xx = reflect101(min(x0 + c - 3, L.w + 2), L.w);
-        sIn[r][c] = src[(long long)yy * sp + xx];
-    }
-    __syncthreads();
-    for (int i = tid; i < (BL_TH + 6) * BL_TW; i += 256) {
-        const int r = i / BL_TW, c = i - r * BL_TW;
-        const u8* p = &sIn[r][c];
-        const int v = 18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3];
-        sH[r][c] = (unsigned short)v;
-    }
-    __syncthreads();
-    // vertical: thread -> 4 adjacent pixels, 4 rows
-    const int cx4 = (tid & 31) * 4;
-    for (int rr = tid >> 5; rr < BL_TH; rr += 8) {
-        const int y = y0 + rr;
-        if (y >= L.h || x0 + cx4 >= L.w) continue;
-        uint32_t out = 0;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            const int c = cx4 + i;
-            const int v = 18 * (sH[rr][c] + sH[rr + 6][c]) + 34 * (sH[rr + 1][c] + sH[rr + 5][c]) +
-                          48 * (sH[rr + 2][c] + sH[rr + 4][c]) + 56 * sH[rr + 3][c];
-            out |= (uint32_t)((v + 32768) >> 16) << (8 * i);
-        }
-        *reinterpret_cast<uint32_t*>(dst + (long long)y * L.pitch + x0 + cx4) = out;
-    }
+    const int x = tx * BL_TW - 4 + lane * 4;
+    // strips whose 32 words all lie left of column w need no reflection logic on their loads
+    if (tx * BL_TW - 4 + 128 <= L.w) blur_strip<false>(src, sp, dst, L.pitch, L.w, L.h, x, ty * BL_TH, lane);
+    else blur_strip<true>(src, sp, dst, L.pitch, L.w, L.h, x, ty * BL_TH, lane);
 }
 
 // =============================================================================================
@@ -843,7 +892,7 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
     ORBX_COUNT(h, ORBX_STAGE_RESIZE, nl - 1);
     orbx_prof_mark(h, ORBX_STAGE_RESIZE);
     // K1b: blur of all levels
-    blur7_kernel<<<dim3(h->nBlurTiles, nframes), 256, 0, st>>>(g, l0, h->dRaw, h->dBlur, h->dBlurTiles);
+    blur7_kernel<<<dim3((h->nBlurTiles + BL_WARPS - 1) / BL_WARPS, nframes), BL_WARPS * 32, 0, st>>>(g, l0, h->dRaw, h->dBlur, h->dBlurTiles, h->nBlurTiles);
     ORBX_COUNT(h, ORBX_STAGE_BLUR, 1);
     orbx_prof_mark(h, ORBX_STAGE_BLUR);
     // K2: FAST
