@@ -74,26 +74,32 @@ __device__ __forceinline__ int reflect101(int i, int n)
     return i;
 }
 
-// bytes at columns x..x+3 (x % 4 == 0, x >= 0) of a row; BORDER_REFLECT_101 beyond column w-1
-template <bool EDGE>
-__device__ __forceinline__ uint32_t row_word(const u8* __restrict__ row, int x, int w)
-{
-    if (!EDGE) return *reinterpret_cast<const uint32_t*>(row + x);
-    if (x + 3 < w) return *reinterpret_cast<const uint32_t*>(row + x);
-    if (x >= w + 4) return 0;                    // only feeds lanes whose own pixels are outside the image
-    uint32_t v = 0;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) v |= (uint32_t)row[reflect101(min(x + i, w + 2), w)] << (8 * i);
-    return v;
-}
-
 __device__ __forceinline__ int reflect_row(int y, int h)
 {
     y = y < 0 ? -y : (y >= h ? 2 * (h - 1) - y : y);
     return max(0, min(y, h - 1));
 }
 
-template <bool EDGE>
+// BORDER_REFLECT_101 of the columns is done in registers: the lane whose word holds the last
+// column e = w-1 (at byte be) and the lane after it rebuild their words from their left
+// neighbours' words with one byte-permute (selectors below); the lane at x = -4 mirrors columns
+// 4,3,2,1 out of its right neighbours.  mode: 0 none, 1 = holds e, 2 = lane after, 3 = x < 0.
+__device__ __forceinline__ void edge_mode(int x, int w, int& mode, uint32_t& sel)
+{
+    const int e = w - 1;
+    mode = 0; sel = 0x3210;
+    if (x < 0) { mode = 3; sel = 0x1234; }
+    else if (e >= x && e <= x + 3) {
+        const int be = e - x;
+        mode = be == 3 ? 0 : 1;
+        sel = be == 2 ? 0x5654u : (be == 1 ? 0x3454u : 0x1234u);       // source pair (left word, own word)
+    } else if (e >= x - 4 && e < x) {
+        const int be = e - (x - 4);
+        mode = be == 0 ? 0 : 2;
+        sel = be == 3 ? 0x3456u : (be == 2 ? 0x1234u : 0x0012u);       // source pair (2nd left word, left word)
+    }
+}
+
 __device__ __forceinline__ void blur_strip(const u8* __restrict__ src, int sp, u8* __restrict__ dst, int dp,
                                            int w, int h, int x, int y0, int lane)
 {
@@ -101,25 +107,30 @@ __device__ __forceinline__ void blur_strip(const u8* __restrict__ src, int sp, u
     const uint32_t c0 = 18u | (34u << 8) | (48u << 16) | (56u << 24), c1 = 48u | (34u << 8) | (18u << 16);
     const int rowsOut = min(BL_TH, h - y0);
     const int ngroups = (rowsOut + 6 + 6) / 7;
-    const int xl = max(x, 0);                    // lane 0 of the first strip sits at x = -4 (built by reflection)
+    const int xl = min(max(x, 0), (w - 1) & ~3);  // every lane loads an aligned word that lies inside the row
+    int mode; uint32_t sel;
+    edge_mode(x, w, mode, sel);
+    const bool store = lane >= 1 && lane <= 30 && x < w;
     uint32_t H[7][4];
     uint32_t cur[7], nxt[7];
 #pragma unroll
-    for (int k = 0; k < 7; ++k) cur[k] = row_word<EDGE>(src + (long long)reflect_row(y0 - 3 + k, h) * sp, xl, w);
+    for (int k = 0; k < 7; ++k) cur[k] = *reinterpret_cast<const uint32_t*>(src + (long long)reflect_row(y0 - 3 + k, h) * sp + xl);
 #pragma unroll 1
     for (int gi = 0; gi < ngroups; ++gi) {
         if (gi + 1 < ngroups) {
 #pragma unroll
             for (int k = 0; k < 7; ++k)
-                nxt[k] = row_word<EDGE>(src + (long long)reflect_row(y0 - 3 + (gi + 1) * 7 + k, h) * sp, xl, w);
+                nxt[k] = *reinterpret_cast<const uint32_t*>(src + (long long)reflect_row(y0 - 3 + (gi + 1) * 7 + k, h) * sp + xl);
         }
 #pragma unroll
         for (int k = 0; k < 7; ++k) {
             const int r = gi * 7 + k;
             uint32_t w1 = cur[k];
             const uint32_t d1 = __shfl_down_sync(FULL, w1, 1), d2 = __shfl_down_sync(FULL, w1, 2);
-            if (x < 0) w1 = __byte_perm(d1, d2, 0x1234);          // columns -4..-1 = columns 4,3,2,1
-            const uint32_t w0 = __shfl_up_sync(FULL, w1, 1), w2 = d1;   // lane+1 is never the patched lane
+            const uint32_t u1 = __shfl_up_sync(FULL, w1, 1), u2 = __shfl_up_sync(FULL, w1, 2);
+            const uint32_t pa = mode == 3 ? d1 : (mode == 2 ? u2 : u1), pb = mode == 3 ? d2 : (mode == 2 ? u1 : w1);
+            if (mode != 0) w1 = __byte_perm(pa, pb, sel);
+            const uint32_t w0 = __shfl_up_sync(FULL, w1, 1), w2 = __shfl_down_sync(FULL, w1, 1);
             H[k][0] = __dp4a(__byte_perm(w0, w1, 0x4321), c0, __dp4a(__byte_perm(w1, w2, 0x4321), c1, 0u));
             H[k][1] = __dp4a(__byte_perm(w0, w1, 0x5432), c0, __dp4a(__byte_perm(w1, w2, 0x5432), c1, 0u));
             H[k][2] = __dp4a(__byte_perm(w0, w1, 0x6543), c0, __dp4a(__byte_perm(w1, w2, 0x6543), c1, 0u));
@@ -136,7 +147,7 @@ __device__ __forceinline__ void blur_strip(const u8* __restrict__ src, int sp, u
                     o[j] = 18u * s0 + 34u * s1 + 48u * s2 + 56u * H[(k + 4) % 7][j] + 32768u;   // result in bits 16..23
                 }
                 const uint32_t lo = __byte_perm(o[0], o[1], 0x0062), hi = __byte_perm(o[2], o[3], 0x0062);
-                if (lane >= 1 && lane <= 30 && x < w) *reinterpret_cast<uint32_t*>(dst + (long long)y * dp + x) = __byte_perm(lo, hi, 0x5410);
+                if (store) *reinterpret_cast<uint32_t*>(dst + (unsigned)(y * dp + x)) = __byte_perm(lo, hi, 0x5410);
             }
         }
 #pragma unroll
@@ -160,10 +171,7 @@ blur7_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, u8* __restrict__
     if (level == 0) { src = l0_frame(l0, frame); sp = l0.pitch; }
     else { src = rawBase + (long long)frame * g.pyrFrameBytes + L.off; sp = L.pitch; }
     u8* dst = blurBase + (long long)frame * g.pyrFrameBytes + L.off;
-    const int x = tx * BL_TW - 4 + lane * 4;
-    // strips whose 32 words all lie left of column w need no reflection logic on their loads
-    if (tx * BL_TW - 4 + 128 <= L.w) blur_strip<false>(src, sp, dst, L.pitch, L.w, L.h, x, ty * BL_TH, lane);
-    else blur_strip<true>(src, sp, dst, L.pitch, L.w, L.h, x, ty * BL_TH, lane);
+    blur_strip(src, sp, dst, L.pitch, L.w, L.h, tx * BL_TW - 4 + lane * 4, ty * BL_TH, lane);
 }
 
 // =============================================================================================
