@@ -251,38 +251,101 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
     int nOut = 0;
     unsigned base = 0;
     if (dw > 0 && dh > 0) {
-        // ---- load the sub-image with aligned 32-bit words -----------------------------------
+        // ---- load the sub-image with aligned 32-bit words; lanes = (row, word) -----------------
         const int xa = c.x0 & ~3, shift = c.x0 - xa;
         const int nw = (shift + cw + 3) >> 2;
         const int tw = tilePitch >> 2;
-        for (int i = lane; i < nw * ch; i += 32) {
-            const int y = i / nw, xw = i - y * nw;
-            reinterpret_cast<uint32_t*>(tile)[y * tw + xw] =
-                *reinterpret_cast<const uint32_t*>(img + (long long)(c.y0 + y) * pitch + xa + 4 * xw);
+        {
+            const int wshift = nw <= 8 ? 3 : (nw <= 16 ? 4 : 5);
+            const int lw = lane & ((1 << wshift) - 1), lr = lane >> wshift, rstep = 32 >> wshift;
+            const u8* gp = img + (long long)(c.y0 + lr) * pitch + xa + 4 * lw;
+            for (int y = lr; y < ch; y += rstep, gp += (long long)rstep * pitch)
+                if (lw < nw) reinterpret_cast<uint32_t*>(tile)[y * tw + lw] = *reinterpret_cast<const uint32_t*>(gp);
         }
         // zero the score tile ((dh+2) x scorePitch)
         for (int i = lane; i < ((dh + 2) * scorePitch) >> 2; i += 32) reinterpret_cast<uint32_t*>(score)[i] = 0;
         __syncwarp();
-        // ---- stage 1: compass pre-test (two adjacent compass pixels beyond minTh) ------------
+        // ---- stage 1a: compass pre-test on 4 pixels per lane (byte-packed).  A 9-arc contains two
+        // adjacent compass points, so |v - r| > minTh must hold for one of {N,S} and one of {E,W}.
+        // |v-r| per byte = VABSDIFF4; "> t" per byte via the 7-bit carry trick (t < 127).
         int n1 = 0;
-        for (int y = 0; y < dh; ++y) {
-            for (int xb = 0; xb < dw; xb += 32) {
-                const int x = xb + lane;
-                bool pass = false;
-                if (x < dw) {
-                    const u8* p = tile + (y + 3) * tilePitch + shift + x + 3;
-                    const int v = p[0];
-                    const int hi = v + minTh, lo = v - minTh;
-                    const int r0 = p[3 * tilePitch], r4 = p[3], r8 = p[-3 * tilePitch], r12 = p[-3];
-                    const unsigned d = (r0 < lo) | ((r4 < lo) << 1) | ((r8 < lo) << 2) | ((r12 < lo) << 3);
-                    const unsigned b = (r0 > hi) | ((r4 > hi) << 1) | ((r8 > hi) << 2) | ((r12 > hi) << 3);
-                    const unsigned dd = d & ((d >> 1) | (d << 3)), bb = b & ((b >> 1) | (b << 3));
-                    pass = ((dd | bb) & 0xf) != 0;
+        {
+            const int ng = (dw + 3) >> 2;                       // 4-pixel groups per row
+            const int gshift = ng <= 8 ? 3 : (ng <= 16 ? 4 : 5);
+            const int lg = lane & ((1 << gshift) - 1), ly = lane >> gshift, rstep = 32 >> gshift;
+            const uint32_t T = (uint32_t)(0x7f - min(minTh, 0x7e)) * 0x01010101u;
+            const bool packedOk = minTh < 0x7f;
+            // byte column of pixel 0 of the group inside the tile: shift + 3 + 4*lg  -> word lg, byte (shift+3)
+            const int i1 = (shift + 3) >> 2, s1 = ((shift + 3) & 3) * 8;      // centre / N / S window
+            const int i4 = (shift + 6) >> 2, s4 = ((shift + 6) & 3) * 8;      // E window (x+3)
+            const int s12 = shift * 8;                                        // W window (x-3), word lg
+            uint32_t vmask = 0;                                               // valid pixels of this group
+#pragma unroll
+            for (int j = 0; j < 4; ++j) if (4 * lg + j < dw) vmask |= 0x80u << (8 * j);
+            for (int y0 = 0; y0 < dh; y0 += rstep) {
+                const int y = y0 + ly;
+                uint32_t pass = 0;
+                if (y < dh && lg < ng) {
+                    const uint32_t* rc = reinterpret_cast<const uint32_t*>(tile) + (y + 3) * tw + lg;
+                    const uint32_t t0 = rc[0], t1 = rc[1], t2 = rc[2], t3 = rc[3];
+                    const uint32_t* rn = rc + 3 * tw + i1;
+                    const uint32_t* rs = rc - 3 * tw + i1;
+                    const uint32_t V = __funnelshift_r(i1 ? t1 : t0, i1 ? t2 : t1, s1);
+                    const uint32_t R4 = __funnelshift_r(i4 == 1 ? t1 : t2, i4 == 1 ? t2 : t3, s4);
+                    const uint32_t R12 = __funnelshift_r(t0, t1, s12);
+                    const uint32_t R0 = __funnelshift_r(rn[0], rn[1], s1);
+                    const uint32_t R8 = __funnelshift_r(rs[0], rs[1], s1);
+                    if (packedOk) {
+                        const uint32_t d0 = __vabsdiffu4(R0, V), d4 = __vabsdiffu4(R4, V);
+                        const uint32_t d8 = __vabsdiffu4(R8, V), d12 = __vabsdiffu4(R12, V);
+                        const uint32_t e0 = ((d0 & 0x7f7f7f7fu) + T) | d0, e4 = ((d4 & 0x7f7f7f7fu) + T) | d4;
+                        const uint32_t e8 = ((d8 & 0x7f7f7f7fu) + T) | d8, e12 = ((d12 & 0x7f7f7f7fu) + T) | d12;
+                        pass = (e0 | e8) & (e4 | e12) & vmask;
+                    } else pass = vmask;
                 }
-                const unsigned m = __ballot_sync(FULL, pass);
-                if (pass) list[n1 + __popc(m & ((1u << lane) - 1))] = (unsigned short)((y << 8) | x);
-                n1 += __popc(m);
+                // append in (row, x) order: lanes are (ly, lg)-major, pixels of a lane ascending
+                const int cnt = __popc(pass);
+                int incl = cnt;
+#pragma unroll
+                for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += v; }
+                int pos = n1 + incl - cnt;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (pass & (0x80u << (8 * j))) list[pos++] = (unsigned short)((y << 8) | (4 * lg + j));
+                n1 += __shfl_sync(FULL, incl, 31);
             }
+        }
+        __syncwarp();
+        // ---- stage 1b: signed opposite-pair bound.  A 9-arc holds at least one pixel of every
+        // diameter (k, k+8), so S <= max(min_k max(r_k, r_k+8) - v, v - max_k min(r_k, r_k+8)).
+        {
+            int nb = 0;
+            for (int i0 = 0; i0 < n1; i0 += 32) {
+                const int i = i0 + lane;
+                bool keep = false;
+                unsigned short e = 0;
+                if (i < n1) {
+                    e = list[i];
+                    const int y = e >> 8, x = e & 0xff;
+                    const u8* p = tile + (y + 3) * tilePitch + shift + x + 3;
+                    const int tp = tilePitch;
+                    const int v = p[0];
+                    const uint32_t a0 = p[3 * tp] | (p[3 * tp + 1] << 16), b0 = p[-3 * tp] | (p[-3 * tp - 1] << 16);
+                    const uint32_t a1 = p[2 * tp + 2] | (p[tp + 3] << 16), b1 = p[-2 * tp - 2] | (p[-tp - 3] << 16);
+                    const uint32_t a2 = p[3] | (p[-tp + 3] << 16), b2 = p[-3] | (p[tp - 3] << 16);
+                    const uint32_t a3 = p[-2 * tp + 2] | (p[-3 * tp + 1] << 16), b3 = p[2 * tp - 2] | (p[3 * tp - 1] << 16);
+                    const uint32_t mx = vminu2(vminu2(vmaxu2(a0, b0), vmaxu2(a1, b1)), vminu2(vmaxu2(a2, b2), vmaxu2(a3, b3)));
+                    const uint32_t mn = vmaxu2(vmaxu2(vminu2(a0, b0), vminu2(a1, b1)), vmaxu2(vminu2(a2, b2), vminu2(a3, b3)));
+                    const int A = min(mx & 0xffff, mx >> 16), B = max(mn & 0xffff, mn >> 16);
+                    keep = max(A - v, v - B) > minTh;
+                }
+                const unsigned m = __ballot_sync(FULL, keep);
+                __syncwarp();
+                if (keep) list[nb + __popc(m & ((1u << lane) - 1))] = e;
+                nb += __popc(m);
+                __syncwarp();
+            }
+            n1 = nb;
         }
         __syncwarp();
         // ---- stage 2: exact strength, keep corners (S > minTh) -------------------------------
@@ -906,7 +969,7 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
     // K2: FAST
     ORBX_CUDA(cudaMemsetAsync(h->dLevelCandCount, 0, (size_t)nframes * nl * sizeof(unsigned), st));
     {
-        const int tilePitch = (g.cwMax + 3 + 3) & ~3;
+        const int tilePitch = ((g.cwMax + 3 + 3) & ~3) + 16;    // +16: the packed pre-test reads whole words past the cell
         const int scorePitch = (g.cwMax - 4 + 3) & ~3;
         int warpSmem = tilePitch * g.chMax + scorePitch * (g.chMax - 4) + 2 * (g.cwMax - 6) * (g.chMax - 6);
         warpSmem = (warpSmem + 15) & ~15;
