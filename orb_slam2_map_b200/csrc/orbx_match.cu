@@ -84,110 +84,249 @@ grid_build_kernel(FrameStore fs, int firstSlot, GridParams gp)
 }
 
 // =============================================================================================
-// K7: SearchForInitialization, one warp per frame pair (slotA -> slotB).
+// K7: SearchForInitialization, one CTA (4 warps) per frame pair (slotA -> slotB).
+// F2's keypoint positions, descriptors and grid are staged in shared memory once.  Queries are
+// processed in blocks of SI_QBLOCK:
+//   phase A (parallel, warp per query): enumerate the window's candidates, evaluate
+//     DescriptorDistance, keep (dist << 16 | grid position) for dist <= Dkeep.  The grid position
+//     (index into Frame::mGrid flattened cell-major) IS the reference's scan order, and a dropped
+//     candidate (dist > Dkeep >= TH_LOW / nnratio) can neither win nor fail the ratio test.
+//   phase B (warp 0, sequential in i1 like the reference): apply the vMatchedDistance skip
+//     (src/ORBmatcher.cc:444), take best / second best, steal-back bookkeeping (:463-471).
 // =============================================================================================
-__global__ void __launch_bounds__(32)
+#define SI_WARPS 8
+#define SI_QBLOCK 64
+#define SI_MAXC 32
+#define SI_DESC_SMEM 512            // F2 descriptors staged in shared memory (the octave-0 ones come first)
+
+struct SiSmem {
+    float* kx; float* ky;            // F2 positions (+inf for octave > 0: never inside a window)
+    unsigned short* gs; unsigned short* gi;
+    unsigned short* md; unsigned short* m21;
+    unsigned short* qlist;           // octave-0 keypoints of F1 in index order
+    u8* binOf;                       // per F1 keypoint
+    uint32_t* cand;                  // [2][SI_QBLOCK][SI_MAXC]
+    int* ccount;                     // [2][SI_QBLOCK] (> SI_MAXC = overflow)
+    int* hist;
+    u8* desc;                        // first SI_DESC_SMEM descriptors of F2
+};
+
+__device__ __forceinline__ SiSmem si_carve(unsigned char* base, int cap)
+{
+    SiSmem s;
+    unsigned char* p = base;
+    const size_t h = ((size_t)cap + 1) / 2 * 4;      // bytes of a u16[cap] array, 4-byte granular
+    s.desc = p; p += (size_t)min(cap, SI_DESC_SMEM) * 32;
+    s.kx = reinterpret_cast<float*>(p); p += (size_t)cap * 4;
+    s.ky = reinterpret_cast<float*>(p); p += (size_t)cap * 4;
+    s.cand = reinterpret_cast<uint32_t*>(p); p += 2 * SI_QBLOCK * SI_MAXC * 4;
+    s.ccount = reinterpret_cast<int*>(p); p += 2 * SI_QBLOCK * 4;
+    s.hist = reinterpret_cast<int*>(p); p += 32 * 4;
+    s.gs = reinterpret_cast<unsigned short*>(p); p += (ORBX_GRID_CELLS + 2) * 2;
+    s.gi = reinterpret_cast<unsigned short*>(p); p += h;
+    s.md = reinterpret_cast<unsigned short*>(p); p += h;
+    s.m21 = reinterpret_cast<unsigned short*>(p); p += h;
+    s.qlist = reinterpret_cast<unsigned short*>(p); p += h;
+    s.binOf = p;
+    return s;
+}
+static size_t si_smem_bytes(int cap)
+{
+    return (size_t)std::min(cap, SI_DESC_SMEM) * 32 + (size_t)cap * 8 + 2 * SI_QBLOCK * SI_MAXC * 4 + 2 * SI_QBLOCK * 4 + 128 +
+           (ORBX_GRID_CELLS + 2) * 2 + 4 * (((size_t)cap + 1) / 2 * 4) + ((size_t)cap + 3) / 4 * 4 + 16;
+}
+
+struct SiCtx {
+    SiSmem S;
+    const orbx_keypoint* k1; const orbx_keypoint* k2;
+    const u8* d1; const u8* d2g;
+    const float* prev;
+    GridParams gp;
+    float r;
+    int dkeep, ndescSmem;
+};
+
+__device__ __forceinline__ const uint32_t* si_desc2(const SiCtx& c, int idx)
+{
+    return reinterpret_cast<const uint32_t*>(idx < c.ndescSmem ? c.S.desc + (size_t)idx * 32 : c.d2g + (size_t)idx * 32);
+}
+
+// phase A for the queries qlist[q0 .. q0+nq) into candidate buffer `buf`, warps wfirst..SI_WARPS-1
+__device__ __forceinline__ void si_phase_a(const SiCtx& c, int q0, int nq, int buf, int wfirst, int wid, int lane,
+                                           unsigned long long& ncmp)
+{
+    const SiSmem& S = c.S;
+    for (int qi = wid - wfirst; qi < nq; qi += SI_WARPS - wfirst) {
+        const int i1 = S.qlist[q0 + qi];
+        const float x = c.prev ? c.prev[2 * i1] : c.k1[i1].x, y = c.prev ? c.prev[2 * i1 + 1] : c.k1[i1].y;
+        int cx0, cx1, cy0, cy1;
+        int cnt = 0;
+        if (area_cells(c.gp, x, y, c.r, cx0, cx1, cy0, cy1)) {
+            uint32_t q[8];
+            load_desc(q, c.d1 + (size_t)i1 * 32);
+            const int ncy = cy1 - cy0 + 1;
+            // one lane per grid column: its cells cy0..cy1 are contiguous in the flattened grid
+            for (int cxb = cx0; cxb <= cx1; cxb += 32) {
+                const int ix = cxb + lane;
+                int j = 0, e = 0;
+                if (ix <= cx1) { j = S.gs[ix * ORBX_GRID_ROWS + cy0]; e = S.gs[ix * ORBX_GRID_ROWS + cy0 + ncy]; }
+                while (__any_sync(FULL, j < e)) {
+                    uint32_t ent = 0xffffffffu;
+                    if (j < e) {
+                        const int idx = S.gi[j];
+                        if (fabsf(__fsub_rn(S.kx[idx], x)) < c.r && fabsf(__fsub_rn(S.ky[idx], y)) < c.r) {
+                            const int dist = hamming256(q, si_desc2(c, idx));
+                            ++ncmp;
+                            if (dist <= c.dkeep) ent = ((uint32_t)dist << 16) | (uint32_t)j;
+                        }
+                        ++j;
+                    }
+                    const unsigned m = __ballot_sync(FULL, ent != 0xffffffffu);
+                    if (ent != 0xffffffffu) {
+                        const int p = cnt + __popc(m & ((1u << lane) - 1));
+                        if (p < SI_MAXC) S.cand[(buf * SI_QBLOCK + qi) * SI_MAXC + p] = ent;
+                    }
+                    cnt += __popc(m);
+                }
+            }
+        }
+        if (lane == 0) S.ccount[buf * SI_QBLOCK + qi] = cnt;
+    }
+}
+
+__global__ void __launch_bounds__(SI_WARPS * 32)
 search_init_kernel(FrameStore fs, int firstSlot, int slotStride, GridParams gp, float* prevMatchedBase,
                    int windowSize, float nnratio, int checkOri, int* __restrict__ matches12Base,
-                   int* __restrict__ nmatchesOut, unsigned long long* __restrict__ ncompares)
+                   int* __restrict__ nmatchesOut, unsigned long long* __restrict__ ncompares, int dkeep)
 {
-    extern __shared__ unsigned short sm[];
-    const int lane = threadIdx.x;
+    extern __shared__ __align__(16) unsigned char smraw[];
+    __shared__ int sNq, sCull;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int pair = blockIdx.x;
     const int sA = firstSlot + pair * slotStride, sB = sA + 1;
     const int n1 = min(fs.count[sA], fs.cap), n2 = min(fs.count[sB], fs.cap);
-    unsigned short* md = sm;                   // vMatchedDistance (0xffff = INT_MAX)
-    unsigned short* m21 = sm + fs.cap;         // vnMatches21 (0xffff = -1)
-    u8* binOf = reinterpret_cast<u8*>(sm + 2 * fs.cap);
-    int* hist = reinterpret_cast<int*>(binOf + ((fs.cap + 3) & ~3));
-    for (int i = lane; i < n2; i += 32) { md[i] = 0xffff; m21[i] = 0xffff; }
-    for (int i = lane; i < n1; i += 32) binOf[i] = 0xff;
-    if (lane < ORBX_HISTO_LENGTH) hist[lane] = 0;
+    SiCtx c;
+    c.S = si_carve(smraw, fs.cap);
+    const SiSmem& S = c.S;
+    c.k1 = fs.kps + (size_t)sA * fs.cap; c.k2 = fs.kps + (size_t)sB * fs.cap;
+    c.d1 = fs.desc + (size_t)sA * fs.cap * 32; c.d2g = fs.desc + (size_t)sB * fs.cap * 32;
+    c.prev = prevMatchedBase ? prevMatchedBase + (size_t)pair * fs.cap * 2 : nullptr;
+    c.gp = gp; c.r = (float)windowSize; c.dkeep = dkeep; c.ndescSmem = min(n2, SI_DESC_SMEM);
+    const unsigned short* gsg = fs.gridStart + (size_t)sB * (ORBX_GRID_CELLS + 1);
+    const unsigned short* gig = fs.gridIdx + (size_t)sB * fs.cap;
     int* m12 = matches12Base + (size_t)pair * fs.cap;
-    for (int i = lane; i < n1; i += 32) m12[i] = -1;
-    __syncwarp();
-    const orbx_keypoint* k1 = fs.kps + (size_t)sA * fs.cap;
-    const orbx_keypoint* k2 = fs.kps + (size_t)sB * fs.cap;
-    const u8* d1 = fs.desc + (size_t)sA * fs.cap * 32;
-    const u8* d2 = fs.desc + (size_t)sB * fs.cap * 32;
-    const unsigned short* gs = fs.gridStart + (size_t)sB * (ORBX_GRID_CELLS + 1);
-    const unsigned short* gi = fs.gridIdx + (size_t)sB * fs.cap;
-    const float* prev = prevMatchedBase ? prevMatchedBase + (size_t)pair * fs.cap * 2 : nullptr;
-    const float r = (float)windowSize;
-    int nmatches = 0;
-    unsigned long long ncmp = 0;
-    for (int i1 = 0; i1 < n1; ++i1) {
-        const orbx_keypoint kp1 = k1[i1];
-        if (kp1.octave > 0) continue;
-        const float x = prev ? prev[2 * i1] : kp1.x, y = prev ? prev[2 * i1 + 1] : kp1.y;
-        int cx0, cx1, cy0, cy1;
-        if (!area_cells(gp, x, y, r, cx0, cx1, cy0, cy1)) continue;
-        uint32_t q[8];
-        load_desc(q, d1 + (size_t)i1 * 32);
-        const int ncy = cy1 - cy0 + 1, nc = (cx1 - cx0 + 1) * ncy;
-        int best = 0x7fffffff, second = 0x7fffffff;
-        unsigned key = 0xffffffffu;
-        for (int c = lane; c < nc; c += 32) {
-            const int ix = cx0 + c / ncy, iy = cy0 + c % ncy;
-            const int cell = ix * ORBX_GRID_ROWS + iy;
-            const int s = gs[cell], e = gs[cell + 1];
-            for (int j = s; j < e; ++j) {
-                const int idx = gi[j];
-                const orbx_keypoint kp2 = k2[idx];
-                if (kp2.octave > 0) continue;          // level window [0,0]: bCheckLevels, octave>maxLevel
-                if (!(fabsf(__fsub_rn(kp2.x, x)) < r && fabsf(__fsub_rn(kp2.y, y)) < r)) continue;
-                const int dist = hamming256(q, reinterpret_cast<const uint32_t*>(d2 + (size_t)idx * 32));
-                ++ncmp;
-                if ((int)md[idx] <= dist) continue;    // md = 0xffff never blocks
-                if (dist < best) { second = best; best = dist; key = ((unsigned)cell << 16) | (unsigned)idx; }
-                else if (dist < second) second = dist;
-            }
-        }
-        warp_top2(best, key, second);
-        if (best <= ORBX_TH_LOW && (float)best < __fmul_rn((float)second, nnratio)) {
-            const int bi = (int)(key & 0xffff);
-            const int old = m21[bi];
-            __syncwarp();
-            if (lane == 0) {
-                if (old != 0xffff) m12[old] = -1;
-                m12[i1] = bi;
-                m21[bi] = (unsigned short)i1;
-                md[bi] = (unsigned short)best;
-                if (checkOri) { const int bin = rot_bin(kp1.angle, k2[bi].angle); binOf[i1] = (u8)bin; hist[bin] += 1; }
-            }
-            if (old != 0xffff) --nmatches;
-            ++nmatches;
-            __syncwarp();
-        }
+    // ---- stage F2 -------------------------------------------------------------------------------
+    for (int i = tid; i < n2; i += SI_WARPS * 32) {
+        const orbx_keypoint kp = c.k2[i];
+        S.kx[i] = kp.octave > 0 ? __int_as_float(0x7f800000) : kp.x;     // level window [0,0] (:425)
+        S.ky[i] = kp.y;
+        S.md[i] = 0xffff; S.m21[i] = 0xffff;
+        S.gi[i] = gig[i];
     }
-    __syncwarp();
-    if (checkOri) {
-        int i1a, i2a, i3a;
-        three_maxima(hist, ORBX_HISTO_LENGTH, i1a, i2a, i3a);
-        __threadfence_block();
+    for (int i = tid; i <= ORBX_GRID_CELLS; i += SI_WARPS * 32) S.gs[i] = gsg[i];
+    for (int i = tid; i < c.ndescSmem * 2; i += SI_WARPS * 32)
+        reinterpret_cast<uint4*>(S.desc)[i] = reinterpret_cast<const uint4*>(c.d2g)[i];
+    for (int i = tid; i < n1; i += SI_WARPS * 32) { S.binOf[i] = 0xff; m12[i] = -1; }
+    if (tid < ORBX_HISTO_LENGTH) S.hist[tid] = 0;
+    if (tid == 0) sCull = 0;
+    if (wid == 0) {     // octave-0 keypoints of F1 (src/ORBmatcher.cc:421-423), ascending
+        int nq = 0;
         for (int i0 = 0; i0 < n1; i0 += 32) {
             const int i = i0 + lane;
-            bool cull = false;
-            if (i < n1) {
-                const int b = binOf[i];
-                cull = b != 0xff && b != i1a && b != i2a && b != i3a && m12[i] >= 0;
-                if (cull) m12[i] = -1;
+            const bool isq = i < n1 && c.k1[i].octave <= 0;
+            const unsigned m = __ballot_sync(FULL, isq);
+            if (isq) S.qlist[nq + __popc(m & ((1u << lane) - 1))] = (unsigned short)i;
+            nq += __popc(m);
+        }
+        if (lane == 0) sNq = nq;
+    }
+    __syncthreads();
+    const int nqTotal = sNq;
+    int nmatches = 0;                      // meaningful in warp 0
+    unsigned long long ncmp = 0;
+    si_phase_a(c, 0, min(SI_QBLOCK, nqTotal), 0, 0, wid, lane, ncmp);
+    for (int q0 = 0, buf = 0; q0 < nqTotal; q0 += SI_QBLOCK, buf ^= 1) {
+        __syncthreads();
+        const int nq = min(SI_QBLOCK, nqTotal - q0);
+        if (wid != 0) {
+            // warps 1.. : candidates of the NEXT block while warp 0 replays this one
+            if (q0 + SI_QBLOCK < nqTotal) si_phase_a(c, q0 + SI_QBLOCK, min(SI_QBLOCK, nqTotal - q0 - SI_QBLOCK), buf ^ 1, 1, wid, lane, ncmp);
+        } else {
+            // ---- phase B: replay in i1 order ---------------------------------------------------------
+            for (int qi = 0; qi < nq; ++qi) {
+                const int i1 = S.qlist[q0 + qi];
+                const int cnt = S.ccount[buf * SI_QBLOCK + qi];
+                int best = 0x7fffffff, second = 0x7fffffff;
+                unsigned key = 0xffffffffu;
+                if (cnt <= SI_MAXC) {
+                    if (lane < cnt) {
+                        const uint32_t ent = S.cand[(buf * SI_QBLOCK + qi) * SI_MAXC + lane];
+                        const int dist = (int)(ent >> 16), idx = S.gi[ent & 0xffff];
+                        if ((int)S.md[idx] > dist) { best = dist; key = ent & 0xffff; }
+                    }
+                } else {
+                    // overflow: enumerate again, filtering on the fly (rare)
+                    const float x = c.prev ? c.prev[2 * i1] : c.k1[i1].x, y = c.prev ? c.prev[2 * i1 + 1] : c.k1[i1].y;
+                    int cx0, cx1, cy0, cy1;
+                    area_cells(gp, x, y, c.r, cx0, cx1, cy0, cy1);
+                    uint32_t q[8];
+                    load_desc(q, c.d1 + (size_t)i1 * 32);
+                    const int ncy = cy1 - cy0 + 1;
+                    for (int ix = cx0 + lane; ix <= cx1; ix += 32) {
+                        const int e = S.gs[ix * ORBX_GRID_ROWS + cy0 + ncy];
+                        for (int j = S.gs[ix * ORBX_GRID_ROWS + cy0]; j < e; ++j) {
+                            const int idx = S.gi[j];
+                            if (!(fabsf(__fsub_rn(S.kx[idx], x)) < c.r && fabsf(__fsub_rn(S.ky[idx], y)) < c.r)) continue;
+                            const int dist = hamming256(q, si_desc2(c, idx));
+                            if ((int)S.md[idx] <= dist) continue;
+                            if (dist < best || (dist == best && (unsigned)j < key)) { second = min(second, best); best = dist; key = (unsigned)j; }
+                            else second = min(second, dist);
+                        }
+                    }
+                }
+                warp_top2(best, key, second);
+                if (best <= ORBX_TH_LOW && (float)best < __fmul_rn((float)second, nnratio)) {
+                    const int bi = S.gi[key];
+                    const int old = S.m21[bi];
+                    __syncwarp();
+                    if (lane == 0) {
+                        if (old != 0xffff) m12[old] = -1;
+                        m12[i1] = bi;
+                        S.m21[bi] = (unsigned short)i1;
+                        S.md[bi] = (unsigned short)best;
+                        if (checkOri) { const int bin = rot_bin(c.k1[i1].angle, c.k2[bi].angle); S.binOf[i1] = (u8)bin; S.hist[bin] += 1; }
+                    }
+                    if (old != 0xffff) --nmatches;
+                    ++nmatches;
+                    __syncwarp();
+                }
             }
-            nmatches -= __popc(__ballot_sync(FULL, cull));
         }
     }
+    __threadfence_block();
+    __syncthreads();
+    if (checkOri) {
+        int i1a, i2a, i3a;
+        three_maxima(S.hist, ORBX_HISTO_LENGTH, i1a, i2a, i3a);
+        int culled = 0;
+        for (int i = tid; i < n1; i += SI_WARPS * 32) {
+            const int b = S.binOf[i];
+            if (b != 0xff && b != i1a && b != i2a && b != i3a && m12[i] >= 0) { m12[i] = -1; ++culled; }
+        }
+        for (int d = 16; d > 0; d >>= 1) culled += __shfl_xor_sync(FULL, culled, d);
+        if (lane == 0 && culled) atomicAdd(&sCull, culled);
+    }
+    __syncthreads();
     if (prevMatchedBase) {
         float* pw = prevMatchedBase + (size_t)pair * fs.cap * 2;
-        for (int i = lane; i < n1; i += 32) {
+        for (int i = tid; i < n1; i += SI_WARPS * 32) {
             const int m = m12[i];
-            if (m >= 0) { pw[2 * i] = k2[m].x; pw[2 * i + 1] = k2[m].y; }
+            if (m >= 0) { pw[2 * i] = c.k2[m].x; pw[2 * i + 1] = c.k2[m].y; }
         }
     }
     for (int d = 16; d > 0; d >>= 1) ncmp += __shfl_xor_sync(FULL, ncmp, d);
-    if (lane == 0) {
-        nmatchesOut[pair] = nmatches;
-        if (ncompares) atomicAdd(ncompares, ncmp);
-    }
+    if (lane == 0 && ncompares && ncmp) atomicAdd(ncompares, ncmp);
+    if (tid == 0) nmatchesOut[pair] = nmatches - sCull;
 }
 
 // =============================================================================================
@@ -546,9 +685,13 @@ static int launch_search_init(const FrameStore& fs, int firstSlot, int slotStrid
                               float* prev, int window, float nnratio, int checkOri, int* m12, int* nm,
                               unsigned long long* ncmp, cudaStream_t st)
 {
-    const int smem = fs.cap * 4 + ((fs.cap + 3) & ~3) + ORBX_HISTO_LENGTH * 4 + 16;
-    if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(search_init_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    search_init_kernel<<<npairs, 32, smem, st>>>(fs, firstSlot, slotStride, gp, prev, window, nnratio, checkOri, m12, nm, ncmp);
+    const size_t smem = si_smem_bytes(fs.cap);
+    if (smem > 220 * 1024) { orbx_set_error("frame too large for SearchForInitialization (%d keypoints)", fs.cap); return ORBX_E_CAPACITY; }
+    if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(search_init_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // candidates farther than TH_LOW / nnratio can neither be the match nor make the ratio test fail
+    int dkeep = 256;
+    if (nnratio > 0.f) { const double d = (double)ORBX_TH_LOW / (double)nnratio + 2.0; dkeep = d < 256.0 ? (int)d : 256; }
+    search_init_kernel<<<npairs, SI_WARPS * 32, smem, st>>>(fs, firstSlot, slotStride, gp, prev, window, nnratio, checkOri, m12, nm, ncmp, dkeep);
     return ORBX_OK;
 }
 
