@@ -272,11 +272,15 @@ def main():
     hnp = host.numpy()
     ncmp = C.c_uint64()
 
+    cnt_out = torch.empty((F,), dtype=torch.int32, pin_memory=True).numpy()
+
     def step_e2e():
-        ex.extract_batch(hnp)
+        # host images in -> keypoints / descriptors / counts in host memory (copies overlapped with the kernels
+        # chunk by chunk inside the library), then the matcher with its results copied to the host
+        ex.extract_batch_to_host(hnp, kp_out, de_out, cnt_out)
         capi.check(capi.lib().orbx_search_init_pairs(ex.h, 0, F - 1, WINDOW, NNRATIO, 1, m12_out.ctypes.data_as(C.c_void_p),
                                                      nm_out.ctypes.data_as(C.c_void_p), cap, C.byref(ncmp)))
-        return ex.download(0, F, out=(kp_out, de_out))
+        return kp_out, de_out, cnt_out
 
     _, _, cnts = step_e2e()
     barrier()
@@ -290,7 +294,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = world * F * args.steps / float(t.item())
     h2d = F * W * H
-    d2h = kp_out.nbytes + de_out.nbytes + m12_out.nbytes + nm_out.nbytes + 4 * F + 8
+    d2h = kp_out.nbytes + de_out.nbytes + cnt_out.nbytes + m12_out.nbytes + nm_out.nbytes + 8
 
     # ---- roofline of the dominant kernel ----------------------------------------------------------
     peak, peak_src = measured_peaks()

@@ -95,6 +95,15 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* images, size_t frame_strid
                        size_t row_stride, int width, int height, int nframes,
                        int images_on_device, int first_slot);
 
+/* Same, with the results also delivered to HOST buffers (kps[nframes][capacity],
+ * desc[nframes][capacity][32], counts[nframes]; any may be NULL): the host->device copy of chunk
+ * i+1 and the device->host copy of chunk i-1 overlap the kernels of chunk i (pinned buffers
+ * recommended).  Synchronous when any output pointer is given. */
+int orbx_extract_batch_to_host(orbx_handle* h, const uint8_t* images, size_t frame_stride,
+                               size_t row_stride, int width, int height, int nframes,
+                               int images_on_device, int first_slot, orbx_keypoint* kps,
+                               uint8_t* desc, int32_t* counts, int capacity);
+
 /* Copy results of slots [first_slot, first_slot+nframes) to host: kps[nframes][capacity],
  * desc[nframes][capacity][32], counts[nframes].  Synchronises. Any of kps/desc may be NULL. */
 int orbx_download(orbx_handle* h, int first_slot, int nframes, orbx_keypoint* kps, uint8_t* desc,

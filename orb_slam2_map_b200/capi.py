@@ -56,7 +56,7 @@ STAGES = ["resize", "blur", "fast", "octree", "describe", "grid", "search_init",
 EXPORTS = [
     "orbx_set_profiling", "orbx_get_profile",
     "orbx_last_error", "orbx_device_count", "orbx_create", "orbx_destroy", "orbx_sync", "orbx_get_tables",
-    "orbx_keypoint_capacity", "orbx_extract", "orbx_extract_batch", "orbx_download", "orbx_get_level",
+    "orbx_keypoint_capacity", "orbx_extract", "orbx_extract_batch", "orbx_extract_batch_to_host", "orbx_download", "orbx_get_level",
     "orbx_get_candidates", "orbx_search_init_pairs", "orbx_extract_stereo_batch",
     "orbm_descriptor_distance", "orbm_search_for_initialization", "orbm_search_by_projection",
     "orbm_compute_stereo_matches", "orbm_knn2_device", "orbm_knn2_merge_device", "orbm_knn2_set_variant",
@@ -92,6 +92,8 @@ def lib():
                                    C.c_int, C.POINTER(C.c_int)]
         L.orbx_extract_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int,
                                          C.c_int, C.c_int]
+        L.orbx_extract_batch_to_host.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int,
+                                                 C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.orbx_download.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.orbx_get_level.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_size_t,
                                      C.POINTER(C.c_int), C.POINTER(C.c_int)]
@@ -197,6 +199,15 @@ class Extractor:
             ptr = int(images)
         check(lib().orbx_extract_batch(self.h, C.c_void_p(ptr), frame_stride, row_stride, width, height, nframes,
                                        int(on_device), first_slot))
+
+    def extract_batch_to_host(self, images: np.ndarray, kps: np.ndarray, desc: np.ndarray, counts: np.ndarray,
+                              first_slot=0):
+        """orbx_extract_batch_to_host on host images [n,h,w] with caller-owned (pinned) outputs."""
+        assert images.ndim == 3 and images.dtype == np.uint8 and images.strides[2] == 1
+        n, h, w = images.shape
+        check(lib().orbx_extract_batch_to_host(self.h, C.c_void_p(images.ctypes.data), images.strides[0],
+                                               images.strides[1], w, h, n, 0, first_slot, _p(kps), _p(desc),
+                                               _p(counts), self.cap))
 
     def download(self, first_slot, nframes, want_kps=True, want_desc=True, out=None):
         counts = np.zeros(nframes, np.int32)

@@ -151,6 +151,14 @@ int orbx_create(const orbx_params* params, int max_width, int max_height, int ch
     for (int s = 0; s < ORBX_NSTAGES; ++s) { h->stageMs[s] = 0.0; h->stageLaunches[s] = 0; }
     if (stream) { h->stream = (cudaStream_t)stream; h->ownStream = false; }
     else { ORBX_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)); h->ownStream = true; }
+    ORBX_CUDA(cudaStreamCreateWithFlags(&h->copyStream, cudaStreamNonBlocking));
+    ORBX_CUDA(cudaStreamCreateWithFlags(&h->d2hStream, cudaStreamNonBlocking));
+    ORBX_CUDA(cudaEventCreateWithFlags(&h->evDone, cudaEventDisableTiming));
+    for (int b = 0; b < 2; ++b) {
+        ORBX_CUDA(cudaEventCreateWithFlags(&h->evCopied[b], cudaEventDisableTiming));
+        ORBX_CUDA(cudaEventCreateWithFlags(&h->evFree[b], cudaEventDisableTiming));
+        h->evFreeValid[b] = false;
+    }
     compute_tables(h);
     // per-frame keypoint capacity for the largest shape: sum_l max(N_l+3, 4*nIni)+1, nIni from the
     // aspect ratio of the maximum image (per-level ratios differ by rounding; +8 slack per level)
@@ -188,6 +196,10 @@ int orbx_destroy(orbx_handle* h)
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->hStage) cudaFreeHost(h->hStage);
     for (cudaEvent_t e : h->evPool) cudaEventDestroy(e);
+    for (int b = 0; b < 2; ++b) { cudaEventDestroy(h->evCopied[b]); cudaEventDestroy(h->evFree[b]); }
+    cudaStreamDestroy(h->copyStream);
+    cudaStreamDestroy(h->d2hStream);
+    cudaEventDestroy(h->evDone);
     if (h->ownStream) cudaStreamDestroy(h->stream);
     delete h;
     return ORBX_OK;
@@ -224,21 +236,22 @@ int orbx_get_tables(const orbx_handle* h, float* scale, float* inv_scale, float*
 
 int orbx_keypoint_capacity(const orbx_handle* h) { return h ? h->kpCap : ORBX_E_INVALID; }
 
-static int ensure_stage(orbx_handle* h, size_t bytes)
-{
-    if (h->hStageBytes >= bytes) return ORBX_OK;
-    if (h->hStage) cudaFreeHost(h->hStage);
-    h->hStage = nullptr; h->hStageBytes = 0;
-    ORBX_CUDA(cudaMallocHost(&h->hStage, bytes));
-    h->hStageBytes = bytes;
-    return ORBX_OK;
-}
-
 int orbx_extract_batch(orbx_handle* h, const uint8_t* images, size_t frame_stride,
                        size_t row_stride, int width, int height, int nframes,
                        int images_on_device, int first_slot)
 {
+    return orbx_extract_batch_to_host(h, images, frame_stride, row_stride, width, height, nframes, images_on_device,
+                                      first_slot, nullptr, nullptr, nullptr, 0);
+}
+
+int orbx_extract_batch_to_host(orbx_handle* h, const uint8_t* images, size_t frame_stride,
+                               size_t row_stride, int width, int height, int nframes,
+                               int images_on_device, int first_slot, orbx_keypoint* kps, uint8_t* desc,
+                               int32_t* counts, int capacity)
+{
     if (!h || !images) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
+    const bool toHost = kps || desc || counts;
+    if ((kps || desc) && capacity < h->kpCap) { orbx_set_error("output capacity %d < %d", capacity, h->kpCap); return ORBX_E_CAPACITY; }
     if (width <= 0 || height <= 0 || nframes <= 0) return ORBX_OK;   // empty image: silent return
     if (width < 64 || height < 64) { orbx_set_error("image smaller than 64x64 is outside the extractor's domain"); return ORBX_E_INVALID; }
     if (row_stride < (size_t)width) { orbx_set_error("row_stride < width"); return ORBX_E_INVALID; }
@@ -247,28 +260,62 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* images, size_t frame_strid
     int rc = orbx_setup_shape(h, width, height);
     if (rc) return rc;
     const bool direct = images_on_device && (row_stride % 4 == 0) && (((uintptr_t)images) % 4 == 0) && (frame_stride % 4 == 0);
-    for (int f0 = 0; f0 < nframes; f0 += h->chunkFrames) {
+    // Host (or unaligned device) images: chunk i+1 is copied into the other half of dLevel0 on the
+    // copy stream while the kernels of chunk i run; events order copy -> compute -> buffer reuse.
+    if (!direct) {
+        cudaEvent_t evStart;
+        ORBX_CUDA(cudaEventCreateWithFlags(&evStart, cudaEventDisableTiming));
+        ORBX_CUDA(cudaEventRecord(evStart, h->stream));                 // copies must not overtake earlier work on the handle
+        ORBX_CUDA(cudaStreamWaitEvent(h->copyStream, evStart, 0));
+        ORBX_CUDA(cudaEventDestroy(evStart));
+    }
+    int chunkNo = 0;
+    for (int f0 = 0; f0 < nframes; f0 += h->chunkFrames, ++chunkNo) {
         const int nf = std::min(h->chunkFrames, nframes - f0);
         const uint8_t* src = images + (size_t)f0 * frame_stride;
         Level0 l0;
         l0.base1 = nullptr; l0.stereo = 0;
         if (direct) { l0.base = src; l0.frameStride = (long long)frame_stride; l0.pitch = (int)row_stride; }
         else {
+            const int b = chunkNo & 1;
+            uint8_t* dstBuf = h->dLevel0 + (size_t)b * h->chunkFrames * h->l0FrameBytes;
             const cudaMemcpyKind kind = images_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+            if (h->evFreeValid[b]) ORBX_CUDA(cudaStreamWaitEvent(h->copyStream, h->evFree[b], 0));
             if (frame_stride == row_stride * (size_t)height) {
-                ORBX_CUDA(cudaMemcpy2DAsync(h->dLevel0, h->l0Pitch, src, row_stride, width, (size_t)height * nf, kind, h->stream));
                 // frames are row-contiguous: one tall 2-D copy; workspace frame stride follows
+                ORBX_CUDA(cudaMemcpy2DAsync(dstBuf, h->l0Pitch, src, row_stride, width, (size_t)height * nf, kind, h->copyStream));
                 l0.frameStride = (long long)h->l0Pitch * height;
             } else {
                 for (int f = 0; f < nf; ++f)
-                    ORBX_CUDA(cudaMemcpy2DAsync(h->dLevel0 + (size_t)f * h->l0FrameBytes, h->l0Pitch, src + (size_t)f * frame_stride,
-                                                row_stride, width, height, kind, h->stream));
+                    ORBX_CUDA(cudaMemcpy2DAsync(dstBuf + (size_t)f * h->l0FrameBytes, h->l0Pitch, src + (size_t)f * frame_stride,
+                                                row_stride, width, height, kind, h->copyStream));
                 l0.frameStride = h->l0FrameBytes;
             }
-            l0.base = h->dLevel0; l0.pitch = h->l0Pitch;
+            ORBX_CUDA(cudaEventRecord(h->evCopied[b], h->copyStream));
+            ORBX_CUDA(cudaStreamWaitEvent(h->stream, h->evCopied[b], 0));
+            l0.base = dstBuf; l0.pitch = h->l0Pitch;
         }
         rc = orbx_run_chunk(h, l0, nf, first_slot + f0);
         if (rc) return rc;
+        if (!direct) { ORBX_CUDA(cudaEventRecord(h->evFree[chunkNo & 1], h->stream)); h->evFreeValid[chunkNo & 1] = true; }
+        if (toHost) {
+            // results of this chunk go back on the copy stream while the next chunk computes
+            const int s0 = first_slot + f0;
+            ORBX_CUDA(cudaEventRecord(h->evDone, h->stream));
+            ORBX_CUDA(cudaStreamWaitEvent(h->d2hStream, h->evDone, 0));
+            if (kps)
+                ORBX_CUDA(cudaMemcpy2DAsync(kps + (size_t)f0 * capacity, (size_t)capacity * sizeof(orbx_keypoint), h->dKps + (size_t)s0 * h->kpCap,
+                                            (size_t)h->kpCap * sizeof(orbx_keypoint), (size_t)h->kpCap * sizeof(orbx_keypoint), nf,
+                                            cudaMemcpyDeviceToHost, h->d2hStream));
+            if (desc)
+                ORBX_CUDA(cudaMemcpy2DAsync(desc + (size_t)f0 * capacity * 32, (size_t)capacity * 32, h->dDesc + (size_t)s0 * h->kpCap * 32,
+                                            (size_t)h->kpCap * 32, (size_t)h->kpCap * 32, nf, cudaMemcpyDeviceToHost, h->d2hStream));
+            if (counts) ORBX_CUDA(cudaMemcpyAsync(counts + f0, h->dCount + s0, nf * sizeof(int), cudaMemcpyDeviceToHost, h->d2hStream));
+        }
+    }
+    if (toHost) {
+        ORBX_CUDA(cudaStreamSynchronize(h->d2hStream));
+        return orbx_sync(h);
     }
     return ORBX_OK;
 }

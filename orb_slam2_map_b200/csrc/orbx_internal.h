@@ -94,7 +94,11 @@ struct orbx_handle {
     int nBlurTiles;
     int* dKpMap;        // keypoint-slot -> level map for the describe kernel
     // workspace (chunkFrames deep)
-    uint8_t* dLevel0;   // pitched copy of the input images (when needed)
+    uint8_t* dLevel0;   // pitched copies of the input images (when needed): two chunk-sized buffers
+    cudaStream_t copyStream;        // host->device copies of chunk i+1 overlap the kernels of chunk i
+    cudaStream_t d2hStream;         // device->host copies of chunk i overlap the kernels of chunk i+1
+    cudaEvent_t evCopied[2], evFree[2], evDone;
+    bool evFreeValid[2];
     int l0Pitch;
     long long l0FrameBytes;
     uint8_t* dRaw;      // pyramid levels >= 1

@@ -93,6 +93,26 @@ def test_batch_matches_single_and_oracle():
     ex.close()
 
 
+def test_extract_batch_to_host_overlapped_copies():
+    """host in / host out with chunked, overlapped copies == device-resident results == oracle"""
+    w, h, n = 640, 480, 11
+    frames = synth.frame_sequence(n, w, h, seed=8)
+    ex = capi.Extractor(max_width=w, max_height=h, chunk_frames=3, result_slots=n)
+    kps = np.zeros((n, ex.cap), capi.KP_DTYPE)
+    desc = np.zeros((n, ex.cap, 32), np.uint8)
+    counts = np.zeros(n, np.int32)
+    for _ in range(2):                                   # second call reuses both staging buffers
+        ex.extract_batch_to_host(frames, kps, desc, counts)
+    k2, d2, c2 = ex.download(0, n)
+    assert np.array_equal(counts, c2)
+    orc = O.Extractor()
+    for i in range(n):
+        ko, do = orc.extract(frames[i])
+        _compare_full(kps[i, :counts[i]], desc[i, :counts[i]], ko, do)
+        assert kps[i, :counts[i]].tobytes() == k2[i, :c2[i]].tobytes() and np.array_equal(desc[i, :counts[i]], d2[i, :c2[i]])
+    ex.close()
+
+
 def test_params_variants():
     img = _image(640, 480, seed=11)
     for (nf, sc, nl, it, mt) in [(500, 1.2, 8, 20, 7), (1500, 1.3, 6, 30, 10), (300, 1.5, 4, 15, 5),
