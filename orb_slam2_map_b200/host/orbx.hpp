@@ -1,0 +1,307 @@
+// orbx.hpp — host-side C++ mirror of the reference's ORB front-end classes over the C ABI
+// (include/orbx.h -> liborbx.so).  Header-only.
+//
+// The reference has no plugin/FFI layer: its boundary for this path is the C++ class API
+//   ORB_SLAM2::ORBextractor  (reference include/ORBextractor.h:45-112)
+//   ORB_SLAM2::ORBmatcher    (reference include/ORBmatcher.h:36-101)
+//   Frame::ExtractORB / Frame::ComputeStereoMatches (reference src/Frame.cc:247,466)
+// The classes below keep those names, argument meanings and error behaviour (void/int returns, an
+// empty image returns silently) so the call sites in Frame.cc / Tracking.cc stay as they are.
+//
+// Two flavours of the same classes:
+//   * default: self-contained POD types (orbx::KeyPoint has cv::KeyPoint's 28-byte layout,
+//     orbx::Image is a non-owning 8-bit view).  Used by the tests and the bench here, where no
+//     OpenCV C++ headers exist.
+//   * -DORBX_WITH_OPENCV (after including the OpenCV headers): adds overloads with the reference's
+//     exact signatures on cv::InputArray / cv::OutputArray / cv::KeyPoint / cv::Mat.
+//
+// There is no CPU fallback: a CUDA failure (including "no device") throws std::runtime_error from
+// the constructor or the call — the rest of ORB-SLAM2 cannot continue without features anyway.
+#ifndef ORBX_HPP
+#define ORBX_HPP
+
+#include <cstdint>
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/orbx.h"
+
+namespace orbx {
+
+struct KeyPoint {                      // == cv::KeyPoint, field for field
+    float x = 0, y = 0, size = 0, angle = -1, response = 0;
+    int32_t octave = 0, class_id = -1;
+};
+static_assert(sizeof(KeyPoint) == sizeof(orbx_keypoint), "KeyPoint layout");
+
+struct Point2f { float x, y; };
+
+struct Image {                         // non-owning 8UC1 view (rows x cols, row stride in bytes)
+    const uint8_t* data = nullptr;
+    int rows = 0, cols = 0;
+    size_t step = 0;
+    bool empty() const { return !data || rows <= 0 || cols <= 0; }
+};
+
+struct OwnedImage {                    // one pyramid level copied to the host
+    std::vector<uint8_t> buf;
+    int rows = 0, cols = 0;
+    size_t step = 0;
+    Image view() const { return Image{buf.data(), rows, cols, step}; }
+};
+
+inline void check(int rc, const char* what)
+{
+    if (rc != ORBX_OK) throw std::runtime_error(std::string(what) + ": " + orbx_last_error());
+}
+
+// ---------------------------------------------------------------------------------------------
+// ORBextractor (reference include/ORBextractor.h:45).  One object = one CUDA stream + workspace,
+// to be used by one thread at a time, exactly like the reference object (src/Frame.cc:78-79 runs
+// two objects on two threads).
+// ---------------------------------------------------------------------------------------------
+class ORBextractor {
+public:
+    enum { HARRIS_SCORE = 0, FAST_SCORE = 1 };
+
+    ORBextractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST,
+                 int maxWidth = 1920, int maxHeight = 1080, int device = 0)
+        : nlevels_(nlevels), scaleFactor_(scaleFactor)
+    {
+        orbx_params p{nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST};
+        check(orbx_create(&p, maxWidth, maxHeight, 1, 1, device, nullptr, &h_), "ORBextractor");
+        mvScaleFactor.resize(nlevels); mvInvScaleFactor.resize(nlevels);
+        mvLevelSigma2.resize(nlevels); mvInvLevelSigma2.resize(nlevels);
+        check(orbx_get_tables(h_, mvScaleFactor.data(), mvInvScaleFactor.data(), mvLevelSigma2.data(),
+                              mvInvLevelSigma2.data(), nullptr), "orbx_get_tables");
+        cap_ = orbx_keypoint_capacity(h_);
+        mvImagePyramid.resize(nlevels);
+    }
+    ~ORBextractor() { orbx_destroy(h_); }
+    ORBextractor(const ORBextractor&) = delete;
+    ORBextractor& operator=(const ORBextractor&) = delete;
+
+    // Compute the ORB features and descriptors on an image (reference ORBextractor.h:56-61).
+    // Mask is ignored, as in the reference.  descriptors: N x 32 bytes, row-major.
+    void operator()(const Image& image, const Image& /*mask*/, std::vector<KeyPoint>& keypoints,
+                    std::vector<uint8_t>& descriptors)
+    {
+        if (image.empty()) return;                        // src/ORBextractor.cc:1046-1047
+        kbuf_.resize(cap_); dbuf_.resize((size_t)cap_ * 32);
+        int n = 0;
+        check(orbx_extract(h_, image.data, image.cols, image.rows, image.step,
+                           reinterpret_cast<orbx_keypoint*>(kbuf_.data()), dbuf_.data(), cap_, &n), "ORBextractor::operator()");
+        keypoints.assign(kbuf_.begin(), kbuf_.begin() + n);             // _keypoints.clear(); insert (:1072,:1103)
+        descriptors.assign(dbuf_.begin(), dbuf_.begin() + (size_t)n * 32);   // create(n,32,CV_8U) / release()
+        pyramidValid_ = false;
+    }
+
+    int GetLevels() { return nlevels_; }
+    float GetScaleFactor() { return scaleFactor_; }
+    std::vector<float> GetScaleFactors() { return mvScaleFactor; }
+    std::vector<float> GetInverseScaleFactors() { return mvInvScaleFactor; }
+    std::vector<float> GetScaleSigmaSquares() { return mvLevelSigma2; }
+    std::vector<float> GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
+
+    // The reference exposes the pyramid of the last image as a public member
+    // (ORBextractor.h:85, read by Frame::ComputeStereoMatches).  The device keeps it; it is copied
+    // to the host only when somebody asks (callers that were not moved to the device path).
+    // Each level carries the reference's 19-pixel BORDER_REFLECT_101 margin; view = interior.
+    const std::vector<OwnedImage>& FetchPyramid()
+    {
+        if (!pyramidValid_) {
+            for (int l = 0; l < nlevels_; ++l) {
+                int w = 0, hh = 0;
+                check(orbx_get_level(h_, 0, l, 0, 0, nullptr, 0, &w, &hh), "orbx_get_level");
+                OwnedImage& m = mvImagePyramid[l];
+                m.cols = w; m.rows = hh; m.step = (size_t)w + 38;
+                m.buf.assign(m.step * (size_t)(hh + 38), 0);
+                check(orbx_get_level(h_, 0, l, 0, 19, m.buf.data(), m.step, nullptr, nullptr), "orbx_get_level");
+            }
+            pyramidValid_ = true;
+        }
+        return mvImagePyramid;
+    }
+    std::vector<OwnedImage> mvImagePyramid;   // filled by FetchPyramid(); interior of level l starts at (19,19)
+
+    orbx_handle* handle() { return h_; }
+    int capacity() const { return cap_; }
+
+#ifdef ORBX_WITH_OPENCV
+    // the reference's exact signature (include/ORBextractor.h:59)
+    void operator()(cv::InputArray _image, cv::InputArray _mask, std::vector<cv::KeyPoint>& _keypoints,
+                    cv::OutputArray _descriptors)
+    {
+        (void)_mask;
+        if (_image.empty()) return;
+        cv::Mat image = _image.getMat();
+        kbuf_.resize(cap_); dbuf_.resize((size_t)cap_ * 32);
+        int n = 0;
+        check(orbx_extract(h_, image.data, image.cols, image.rows, (size_t)image.step,
+                           reinterpret_cast<orbx_keypoint*>(kbuf_.data()), dbuf_.data(), cap_, &n), "ORBextractor::operator()");
+        if (n == 0) _descriptors.release();
+        else {
+            _descriptors.create(n, 32, CV_8U);
+            cv::Mat d = _descriptors.getMat();
+            for (int i = 0; i < n; ++i) std::memcpy(d.ptr(i), dbuf_.data() + (size_t)i * 32, 32);
+        }
+        _keypoints.clear();
+        _keypoints.reserve(n);
+        for (int i = 0; i < n; ++i) {
+            const KeyPoint& k = kbuf_[i];
+            _keypoints.push_back(cv::KeyPoint(k.x, k.y, k.size, k.angle, k.response, k.octave, k.class_id));
+        }
+        pyramidValid_ = false;
+    }
+#endif
+
+protected:
+    orbx_handle* h_ = nullptr;
+    int nlevels_, cap_ = 0;
+    float scaleFactor_;
+    bool pyramidValid_ = false;
+    std::vector<KeyPoint> kbuf_;
+    std::vector<uint8_t> dbuf_;
+    std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
+};
+
+// ---------------------------------------------------------------------------------------------
+// What the matchers need from a Frame (reference include/Frame.h:132-189): undistorted
+// keypoints, descriptors, image bounds of the 64x48 grid, optional right coordinates.
+// ---------------------------------------------------------------------------------------------
+struct FrameView {
+    const std::vector<KeyPoint>* mvKeysUn = nullptr;
+    const uint8_t* mDescriptors = nullptr;         // N x 32
+    float mnMinX = 0, mnMaxX = 0, mnMinY = 0, mnMaxY = 0;
+    const std::vector<float>* mvuRight = nullptr;
+    const std::vector<float>* mvScaleFactors = nullptr;
+
+    orbm_frame c() const
+    {
+        orbm_frame f;
+        f.n = mvKeysUn ? (int32_t)mvKeysUn->size() : 0;
+        f.keys_un = mvKeysUn ? reinterpret_cast<const orbx_keypoint*>(mvKeysUn->data()) : nullptr;
+        f.descriptors = mDescriptors;
+        f.min_x = mnMinX; f.max_x = mnMaxX; f.min_y = mnMinY; f.max_y = mnMaxY;
+        f.u_right = mvuRight ? mvuRight->data() : nullptr;
+        f.scale_factors = mvScaleFactors ? mvScaleFactors->data() : nullptr;
+        f.nlevels = mvScaleFactors ? (int32_t)mvScaleFactors->size() : 0;
+        return f;
+    }
+};
+
+// Map points already projected by the caller (the projection itself is scalar host code behind
+// MapPoint mutexes in the reference, src/ORBmatcher.cc:51-76,1340-1376): one query per point.
+struct ProjectionQueries {
+    std::vector<orbm_proj_query> q;
+    std::vector<uint8_t> descriptors;    // q.size() x 32  (MapPoint::GetDescriptor)
+    std::vector<uint8_t> blocks;         // pMP->Observations() > 0
+};
+
+struct ProjectionResult {
+    int nmatches = 0;
+    std::vector<int32_t> assigned;       // per keypoint: query that owns it at the end, or -1
+    std::vector<int32_t> bestIdx, bestDist;   // per query
+};
+
+// ---------------------------------------------------------------------------------------------
+// ORBmatcher (reference include/ORBmatcher.h:36)
+// ---------------------------------------------------------------------------------------------
+class ORBmatcher {
+public:
+    ORBmatcher(float nnratio = 0.6f, bool checkOri = true) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
+
+    static const int TH_LOW = 50, TH_HIGH = 100, HISTO_LENGTH = 30;      // src/ORBmatcher.cc:37-39
+
+    // Hamming distance of two 32-byte descriptors (src/ORBmatcher.cc:1647).  A single pair is host
+    // work (8 popcounts); batches go through DescriptorDistances.
+    static int DescriptorDistance(const uint8_t* a, const uint8_t* b)
+    {
+        int d = 0;
+        for (int i = 0; i < 8; ++i) {
+            uint32_t x, y;
+            std::memcpy(&x, a + 4 * i, 4); std::memcpy(&y, b + 4 * i, 4);
+            d += __builtin_popcount(x ^ y);
+        }
+        return d;
+    }
+    static void DescriptorDistances(const uint8_t* a, const uint8_t* b, int count, int32_t* dist)
+    {
+        check(orbm_descriptor_distance(a, b, count, dist), "DescriptorDistance");
+    }
+
+    // src/ORBmatcher.cc:405 — same arguments, same in/out behaviour of vbPrevMatched / vnMatches12
+    int SearchForInitialization(const FrameView& F1, const FrameView& F2, std::vector<Point2f>& vbPrevMatched,
+                                std::vector<int>& vnMatches12, int windowSize = 10)
+    {
+        const orbm_frame f1 = F1.c(), f2 = F2.c();
+        vnMatches12.assign((size_t)f1.n, -1);
+        if ((int)vbPrevMatched.size() < f1.n) throw std::runtime_error("vbPrevMatched smaller than F1");
+        int32_t n = 0;
+        check(orbm_search_for_initialization(&f1, &f2, reinterpret_cast<float*>(vbPrevMatched.data()), vnMatches12.data(),
+                                             windowSize, mfNNratio, mbCheckOrientation ? 1 : 0, &n), "SearchForInitialization");
+        return n;
+    }
+
+    // The four SearchByProjection overloads (src/ORBmatcher.cc:45,290,1328,1472) on flattened queries.
+    // occupied: in/out, one byte per keypoint of F (it already holds a map point that blocks).
+    ProjectionResult SearchByProjection(int variant, const FrameView& F, const ProjectionQueries& Q,
+                                        std::vector<uint8_t>& occupied, int thDist)
+    {
+        const orbm_frame f = F.c();
+        ProjectionResult r;
+        r.assigned.assign((size_t)f.n, -1);
+        r.bestIdx.assign(Q.q.size(), -1); r.bestDist.assign(Q.q.size(), 256);
+        occupied.resize((size_t)f.n, 0);
+        int32_t n = 0;
+        check(orbm_search_by_projection(variant, &f, Q.q.data(), Q.descriptors.data(), (int)Q.q.size(),
+                                        Q.blocks.empty() ? nullptr : Q.blocks.data(), occupied.data(), r.assigned.data(),
+                                        r.bestIdx.data(), r.bestDist.data(), thDist, mfNNratio, mbCheckOrientation ? 1 : 0, &n),
+              "SearchByProjection");
+        r.nmatches = n;
+        return r;
+    }
+
+protected:
+    float mfNNratio;
+    bool mbCheckOrientation;
+};
+
+// Frame::ComputeStereoMatches (src/Frame.cc:466) for callers that hold both eyes on the host.
+// (The fused path — extraction of both eyes + matching without the pyramids leaving the device —
+// is orbx_extract_stereo_batch.)
+inline void ComputeStereoMatches(const std::vector<KeyPoint>& keysLeft, const uint8_t* descLeft,
+                                 const std::vector<KeyPoint>& keysRight, const uint8_t* descRight,
+                                 const std::vector<Image>& pyrLeft, const std::vector<Image>& pyrRight,
+                                 const std::vector<float>& scaleFactors, const std::vector<float>& invScaleFactors,
+                                 float mbf, float fx, std::vector<float>& mvuRight, std::vector<float>& mvDepth)
+{
+    const int nl = (int)pyrLeft.size();
+    std::vector<const uint8_t*> pl(nl), pr(nl);
+    std::vector<int32_t> lw(nl), lh(nl);
+    std::vector<int64_t> sl(nl), sr(nl);
+    for (int l = 0; l < nl; ++l) {
+        pl[l] = pyrLeft[l].data; pr[l] = pyrRight[l].data;
+        lw[l] = pyrLeft[l].cols; lh[l] = pyrLeft[l].rows;
+        sl[l] = (int64_t)pyrLeft[l].step; sr[l] = (int64_t)pyrRight[l].step;
+    }
+    orbm_stereo_input in;
+    in.n_left = (int32_t)keysLeft.size(); in.n_right = (int32_t)keysRight.size();
+    in.keys_left = reinterpret_cast<const orbx_keypoint*>(keysLeft.data());
+    in.keys_right = reinterpret_cast<const orbx_keypoint*>(keysRight.data());
+    in.desc_left = descLeft; in.desc_right = descRight;
+    in.nlevels = nl;
+    in.scale_factors = scaleFactors.data(); in.inv_scale_factors = invScaleFactors.data();
+    in.pyr_left = pl.data(); in.pyr_right = pr.data();
+    in.level_width = lw.data(); in.level_height = lh.data();
+    in.pyr_stride_left = sl.data(); in.pyr_stride_right = sr.data();
+    in.bf = mbf; in.fx = fx;
+    mvuRight.assign(keysLeft.size(), -1.0f);
+    mvDepth.assign(keysLeft.size(), -1.0f);
+    check(orbm_compute_stereo_matches(&in, mvuRight.data(), mvDepth.data(), nullptr), "ComputeStereoMatches");
+}
+
+} // namespace orbx
+#endif
