@@ -140,7 +140,7 @@ def ref_lib():
     return L
 
 
-def cpu_extract_match(frames: np.ndarray, nthreads: int, use_ref: bool):
+def cpu_extract_match(frames: np.ndarray, nthreads: int, use_ref: bool, window: int | None = None):
     """-> (seconds, kind). frames: [n,h,w] uint8 host."""
     O = oracle_mod()
     p = O.Params(PARAMS["nfeatures"], PARAMS["scale"], PARAMS["nlevels"], PARAMS["ini_th"], PARAMS["min_th"])
@@ -151,7 +151,8 @@ def cpu_extract_match(frames: np.ndarray, nthreads: int, use_ref: bool):
     fn = L.ref_extract_match_many if L is not None else O.lib().oracle_extract_match_many
     t0 = time.perf_counter()
     fn(C.byref(p), frames.ctypes.data_as(C.c_void_p), C.c_size_t(frames.strides[0]), C.c_int(w), C.c_int(h),
-       C.c_size_t(frames.strides[1]), C.c_int(n), C.c_int(nthreads), C.c_int(WINDOW), C.c_float(NNRATIO), C.c_int(1),
+       C.c_size_t(frames.strides[1]), C.c_int(n), C.c_int(nthreads), C.c_int(WINDOW if window is None else window),
+       C.c_float(NNRATIO), C.c_int(1),
        C.byref(tm), C.byref(nc))
     return time.perf_counter() - t0, ("reference" if L is not None else "port")
 
@@ -163,26 +164,217 @@ def run_reference(args):
     from orb_slam2_map_b200 import synth
     cores = os.cpu_count() or 1
     sample = max(2 * cores, 32)
+    hd = args.workload == "hd"
+    if hd:
+        sample = max(cores, 8)
+    win = 0 if hd else None           # window 0: no candidates, i.e. extraction only
     frames = synth.frame_sequence(sample, W, H, seed=0)
     for _ in range(args.warmup):
-        cpu_extract_match(frames[:max(cores, 8)], cores, True)
+        cpu_extract_match(frames[:max(cores, 8)], cores, True, win)
     t, kind = 0.0, "port"
     for _ in range(args.steps):
-        dt, kind = cpu_extract_match(frames, cores, True)
+        dt, kind = cpu_extract_match(frames, cores, True, win)
         t += dt
     fps = sample * args.steps / t
     line = {
         "impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "configs[1]: 640x480 frames, nFeatures 1000, extract + consecutive-frame "
-                               "SearchForInitialization", "frames_per_step": sample},
+        "config": {"workload": (f"configs[3]: {W}x{H} frames, nFeatures {PARAMS['nfeatures']}, extraction only" if hd else
+                                "configs[1]: 640x480 frames, nFeatures 1000, extract + consecutive-frame SearchForInitialization"),
+                   "frames_per_step": sample,
+                   "implementation": "reference src/ORBextractor.cc compiled unmodified (oracle/_ref) + oracle SearchForInitialization"
+                                     if kind == "reference" else "oracle port"},
         "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind,
                          "sample": f"{sample} frames + {sample - 1} pairs per step, one frame per thread"},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line))
+
+
+
+# ---- brute-force 2-NN (BASELINE.json configs[4]) ---------------------------------------------------
+POPC_PER_CLK_PER_SM = 16          # nominal quarter-rate POPC (SURVEY.md §8d [memory]); 5 POPC per compare (carry-save)
+
+
+def knn_rate(dev, nq, ndb, steps, world):
+    """Hamming comparisons/s of knn2_kernel on this GPU: nq x ndb random descriptors, CUDA events."""
+    import torch
+    from orb_slam2_map_b200 import capi, synth
+    q = torch.from_numpy(synth.random_descriptors(nq, 11)).to(dev)
+    db = torch.from_numpy(synth.random_descriptors(ndb, 12)).to(dev)
+    od = torch.empty((nq, 2), dtype=torch.int16, device=dev)
+    oi = torch.empty((nq, 2), dtype=torch.int32, device=dev)
+    st = torch.cuda.current_stream()
+    run = lambda: capi.knn2_device(q.data_ptr(), nq, db.data_ptr(), ndb, 0, od.data_ptr(), oi.data_ptr(), st.cuda_stream)
+    for _ in range(2):
+        run()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record(st)
+    for _ in range(steps):
+        run()
+    e1.record(st)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    rate = nq * ndb / (ms * 1e-3)
+    props = torch.cuda.get_device_properties(dev)
+    peak = props.multi_processor_count * POPC_PER_CLK_PER_SM * 1.965e9 / 5.0
+    return {"metric": "Hamming cmp/s (brute-force 2-NN, 256-bit)", "value": rate * world, "unit": "cmp/s", "per_gpu": rate,
+            "queries": nq, "database_rows": ndb, "ms": ms,
+            "popc_roofline": {"peak": peak, "frac": rate / peak, "how": "nominal 16 POPC/clk/SM x SMs x 1.965 GHz / 5 POPC per compare"}}
+
+
+def run_knn(args):
+    """configs[4]: queries replicated, database rows sharded over the ranks (weak scaling: rows per GPU fixed),
+    local top-2 on every rank, all_gather of 12 B per query and rank over NCCL, device merge."""
+    import torch
+    import torch.distributed as dist
+    from orb_slam2_map_b200 import sharding, synth
+    rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev) if world > 1 else None
+    if world == 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1"); os.environ.setdefault("MASTER_PORT", "29533")
+        dist.init_process_group("nccl", rank=0, world_size=1, device_id=dev)
+    nq, per = args.queries, args.db_per_gpu
+    q = torch.from_numpy(synth.random_descriptors(nq, 1)).to(dev)
+    db = torch.from_numpy(synth.random_descriptors(per, 100 + rank)).to(dev)
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    step = lambda: sharding.knn2_sharded(q, db, rank * per, stream=stream.cuda_stream)
+    for _ in range(max(args.warmup, 1)):
+        step()
+    clocks = ClockSampler(local)
+    dist.barrier(); torch.cuda.synchronize()
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    dist.barrier(); torch.cuda.synchronize()
+    e0.record(stream)
+    for _ in range(args.steps):
+        od, oi = step()
+    e1.record(stream)
+    dist.barrier(); torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    clk = clocks.stop()
+    # e2e: queries from pinned host memory in, merged result to the host out
+    hq = torch.empty((nq, 32), dtype=torch.uint8, pin_memory=True); hq.copy_(q)
+    hod = torch.empty((nq, 2), dtype=torch.int16, pin_memory=True); hoi = torch.empty((nq, 2), dtype=torch.int32, pin_memory=True)
+    def e2e_step():
+        q.copy_(hq, non_blocking=True)
+        d, i = step()
+        hod.copy_(d, non_blocking=True); hoi.copy_(i, non_blocking=True)
+        stream.synchronize()
+    e2e_step(); dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    total = float(nq) * per * world
+    value = total * args.steps / (ms * 1e-3)
+    props = torch.cuda.get_device_properties(dev)
+    peak = props.multi_processor_count * POPC_PER_CLK_PER_SM * 1.965e9 / 5.0
+    line = {"metric": "Hamming cmp/s (brute-force top-2 kNN, 256-bit descriptors)", "value": value, "unit": "cmp/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u32 xor/popc", "data": "synthetic",
+            "config": {"workload": "configs[4]: brute-force Hamming top-2, queries replicated, database sharded by rows, NCCL all_gather of "
+                                   "per-query top-2 + device merge", "queries": nq, "database_rows_per_gpu": per,
+                       "l2_policy": f"database shard {per * 32 / 1e6:.0f} MB streamed once per query tile"},
+            "clocks": clk,
+            "e2e": {"value": total * args.steps / float(dt.item()), "unit": "cmp/s", "h2d_bytes_per_step": nq * 32, "d2h_bytes_per_step": nq * 12},
+            "gpu_launches": 2 * args.steps,
+            "roofline": {"bound": "int-pipe", "kernel": "knn2_kernel", "achieved": value / world, "peak": peak, "unit": "cmp/s",
+                         "frac": value / world / peak, "traffic": None,
+                         "how": "nominal 16 POPC/clk/SM x SMs x 1.965 GHz / 5 POPC per compare (carry-save popcount)"}}
+    if rank == 0:
+        print(json.dumps(line))
+    dist.destroy_process_group()
+
+
+def run_stereo(args):
+    """configs[2]: KITTI-shaped 1241x376 stereo pairs, nFeatures 2000: left+right extraction + ComputeStereoMatches
+    with the pyramids kept on the device; pairs sharded by rank, no collective."""
+    import torch
+    import torch.distributed as dist
+    from orb_slam2_map_b200 import capi, synth
+    rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    w, h, P = 1241, 376, (args.frames if args.frames != 4096 else 1024)
+    bf, fx = 386.1448, 718.856
+    base = [synth.stereo_pair(w, h, seed=1000 * rank + i) for i in range(16)]
+    hl = torch.empty((P, h, w), dtype=torch.uint8, pin_memory=True); hr = torch.empty((P, h, w), dtype=torch.uint8, pin_memory=True)
+    for i in range(P):
+        hl[i] = torch.from_numpy(base[i % 16][0]); hr[i] = torch.from_numpy(base[i % 16][1])
+    dl, dr = hl.to(dev), hr.to(dev)
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    ex = capi.Extractor(nfeatures=2000, max_width=w, max_height=h, chunk_frames=min(args.chunk, 256), result_slots=2 * P, device=local,
+                        stream=stream.cuda_stream)
+    step = lambda: ex.extract_stereo_batch(dl.data_ptr(), dr.data_ptr(), bf, fx, nframes=P, width=w, height=h, frame_stride=w * h,
+                                           row_stride=w, on_device=True, fetch=False)
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    for _ in range(args.warmup):
+        step()
+    ex.sync(); ex.profile(); ex.set_profiling(True)
+    clocks = ClockSampler(local)
+    barrier(); clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    stage_ms, stage_launches = ex.profile(); ex.set_profiling(False)
+    clk = clocks.stop()
+    hln, hrn = hl.numpy(), hr.numpy()
+    ex.extract_stereo_batch(hln, hrn, bf, fx)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ur, dp, ncmp = ex.extract_stereo_batch(hln, hrn, bf, fx)
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    value = world * P * args.steps / (ms * 1e-3)
+    peak, peak_src = measured_peaks()
+    ab = algorithmic_bytes(w, h, 2005)["total"] * 2
+    line = {"metric": "stereo pairs/s (1241x376, 2000 kp, L+R extract + ComputeStereoMatches)", "value": value, "unit": "pairs/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "configs[2]: KITTI-shaped 1241x376 stereo pairs, nFeatures 2000, left/right extraction + ComputeStereoMatches",
+                       "pairs_per_step_per_gpu": P, "l2_policy": f"inputs ({2 * P * w * h / 1e9:.2f} GB per step) larger than L2",
+                       "sharding": "pairs by rank, no collective"},
+            "clocks": clk,
+            "e2e": {"value": world * P * args.steps / float(dt.item()), "unit": "pairs/s", "h2d_bytes_per_step": 2 * P * w * h,
+                    "d2h_bytes_per_step": 2 * P * ex.cap * 4 + 8},
+            "gpu_launches": int(sum(stage_launches.values())),
+            "roofline": {"bound": "hbm", "kernel": "path", "achieved": ab * value / world / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": ab * value / world / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_pair": ab},
+            "stages": {k: {"ms_per_step": v / args.steps, "launches_per_step": stage_launches[k] / args.steps}
+                       for k, v in stage_ms.items() if stage_launches[k]},
+            "hamming_compares_per_step": int(ncmp), "stereo_matches_per_pair": float((ur >= 0).sum() / P)}
+    if rank == 0:
+        print(json.dumps(line))
+    ex.close()
+    if world > 1:
+        dist.destroy_process_group()
 
 
 def main():
@@ -194,9 +386,32 @@ def main():
     ap.add_argument("--frames", type=int, default=4096)
     ap.add_argument("--chunk", type=int, default=512)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--workload", default="frames", choices=["frames", "hd", "stereo", "knn"],
+                    help="frames = BASELINE configs[1] (the graded line); hd = configs[3]; stereo = configs[2]; knn = configs[4]")
+    ap.add_argument("--queries", type=int, default=262144, help="knn: queries per step (config 5 names 1M)")
+    ap.add_argument("--db-per-gpu", type=int, default=2000000, help="knn: database rows per GPU (config 5: 16M over 8)")
     args = ap.parse_args()
+    global W, H, PARAMS, METRIC
+    match = True
+    workload_name = ("configs[1]: batch of 4096 synthetic 640x480 frames, ORBextractor(1000,1.2,8,20,7) + "
+                     "consecutive-frame SearchForInitialization(window 100, nnratio 0.9)")
+    if args.workload == "hd":
+        W, H = 1920, 1080
+        PARAMS = dict(PARAMS, nfeatures=5000)
+        METRIC = "ORB frames/s (1920x1080, 5000 kp, extract)"
+        match = False
+        if args.frames == 4096:
+            args.frames = 512
+        args.chunk = min(args.chunk, 128)
+        workload_name = "configs[3]: 1920x1080 frames, ORBextractor(5000,1.2,8,20,7), extraction only"
     if args.impl == "reference":
         run_reference(args)
+        return
+    if args.workload == "stereo":
+        run_stereo(args)
+        return
+    if args.workload == "knn":
+        run_knn(args)
         return
 
     import torch
@@ -224,7 +439,8 @@ def main():
     def step_device():
         ex.extract_batch(frames.data_ptr(), nframes=F, width=W, height=H, frame_stride=W * H, row_stride=W,
                          on_device=True, first_slot=0)
-        ex.search_init_pairs(0, F - 1, WINDOW, NNRATIO, True, fetch=False)
+        if match:
+            ex.search_init_pairs(0, F - 1, WINDOW, NNRATIO, True, fetch=False)
 
     def barrier():
         if world > 1:
@@ -278,8 +494,9 @@ def main():
         # host images in -> keypoints / descriptors / counts in host memory (copies overlapped with the kernels
         # chunk by chunk inside the library), then the matcher with its results copied to the host
         ex.extract_batch_to_host(hnp, kp_out, de_out, cnt_out)
-        capi.check(capi.lib().orbx_search_init_pairs(ex.h, 0, F - 1, WINDOW, NNRATIO, 1, m12_out.ctypes.data_as(C.c_void_p),
-                                                     nm_out.ctypes.data_as(C.c_void_p), cap, C.byref(ncmp)))
+        if match:
+            capi.check(capi.lib().orbx_search_init_pairs(ex.h, 0, F - 1, WINDOW, NNRATIO, 1, m12_out.ctypes.data_as(C.c_void_p),
+                                                         nm_out.ctypes.data_as(C.c_void_p), cap, C.byref(ncmp)))
         return kp_out, de_out, cnt_out
 
     _, _, cnts = step_e2e()
@@ -318,10 +535,9 @@ def main():
         "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "configs[1]: batch of 4096 synthetic 640x480 frames, ORBextractor(1000,1.2,8,20,7) + "
-                               "consecutive-frame SearchForInitialization(window 100, nnratio 0.9)",
+        "config": {"workload": workload_name,
                    "frames_per_step_per_gpu": F, "chunk_frames": args.chunk, "keypoints_per_frame": nkp,
-                   "l2_policy": "inputs (1.26 GB per step) larger than L2", "sharding": "frames by rank, no collective"},
+                   "l2_policy": f"inputs ({F * W * H / 1e9:.2f} GB per step) larger than L2", "sharding": "frames by rank, no collective"},
         "clocks": clk,
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": int(sum(stage_launches.values())),
@@ -332,13 +548,20 @@ def main():
         "matches_per_pair": float(nm_out.mean()), "hamming_compares_per_step": int(ncmp.value),
     }
 
+    # ---- second half of the metric: Hamming cmp/s of the brute-force 2-NN kernel on this GPU (short run) ----
+    if args.workload == "frames":
+        line["hamming"] = knn_rate(dev, nq=65536, ndb=1 << 20, steps=3, world=world)
+
     # ---- CPU baseline (rank 0, N=1 only): bounded sample of the same frames ----------------------
     if rank == 0 and world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1
         s1 = 16
-        t1, kind = cpu_extract_match(hnp[:s1], 1, False)
         sN = max(2 * cores, 32)
-        tN, _ = cpu_extract_match(hnp[:sN], cores, False)
+        win = WINDOW if match else 0          # window 0: the matcher finds no candidate (extraction-only workloads)
+        if args.workload == "hd":
+            s1, sN = 4, max(cores, 8)
+        tN, kind = cpu_extract_match(hnp[:sN], cores, True, win)
+        t1, _ = cpu_extract_match(hnp[:s1], 1, True, win)
         line["cpu_baseline"] = {"value": sN / tN, "unit": "frames/s", "cores": cores, "kind": kind,
                                 "sample": f"first {sN} frames (+{sN - 1} pairs), one frame per thread on {cores} threads; "
                                           f"single-thread on {s1} frames: {s1 / t1:.2f} frames/s",
