@@ -744,16 +744,17 @@ describe_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, const u8* __r
     const int u = lane - 15;
     int m10 = 0, m01 = 0;
     if (lane < 31) {
-        const u8* center = raw + (long long)py * rp + px;
-        const int au = abs(u);
-#pragma unroll 1
-        for (int v = -15; v <= 15; ++v) {
-            if (au <= c_umax[abs(v)]) {
-                const int val = center[v * rp + u];
-                m10 += u * val;
-                m01 += v * val;
-            }
-        }
+        const u8* center = raw + (long long)py * rp + px + u;
+        // the disc is symmetric: column u holds rows |v| <= umax[|u|].  All 31 loads are issued
+        // before they are consumed (the gather is latency bound otherwise).
+        const int vlim = c_umax[abs(u)];
+        int vals[31];
+#pragma unroll
+        for (int v = -15; v <= 15; ++v) vals[v + 15] = (abs(v) <= vlim) ? (int)center[v * rp] : 0;
+        int colsum = 0;
+#pragma unroll
+        for (int v = -15; v <= 15; ++v) { colsum += vals[v + 15]; m01 += v * vals[v + 15]; }
+        m10 = u * colsum;
     }
     for (int d = 16; d > 0; d >>= 1) { m10 += __shfl_xor_sync(FULL, m10, d); m01 += __shfl_xor_sync(FULL, m01, d); }
     const float angle = fast_atan2_deg((float)m01, (float)m10);
@@ -767,7 +768,9 @@ describe_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, const u8* __r
     int val = 0;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        const float x0 = (float)pat[4 * j], y0 = (float)pat[4 * j + 1], x1 = (float)pat[4 * j + 2], y1 = (float)pat[4 * j + 3];
+        const int pw = reinterpret_cast<const int*>(pat)[j];          // x0, y0, x1, y1 as signed bytes
+        const float x0 = (float)(signed char)(pw & 0xff), y0 = (float)(signed char)((pw >> 8) & 0xff);
+        const float x1 = (float)(signed char)((pw >> 16) & 0xff), y1 = (float)(signed char)(pw >> 24);
         const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sa), __fmul_rn(y0, ca)));
         const int q0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, ca), __fmul_rn(y0, sa)));
         const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, sa), __fmul_rn(y1, ca)));
