@@ -56,6 +56,89 @@ pyr_resize_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long lo
 }
 
 // =============================================================================================
+// K1a (fast path, scale factor <= 2): one warp owns a 128 x RS_TH strip of the destination level;
+// a lane owns 4 adjacent output columns and walks down the output rows.  Everything that depends
+// only on the column (source column, 11-bit coefficients, byte selectors) is hoisted out of the
+// row loop.  A source row contributes 3 aligned 32-bit words per lane; the two taps of a pixel are
+// picked with byte-permutes and combined with one IDP.2A (u16 x u8 dot product).  The horizontal
+// sums of a source row are kept in registers and reused by the next output row (consecutive
+// output rows share a source row when the scale is < 2).  Vertical blend = OpenCV's
+// ((b*(S>>4))>>16 ... +2)>>2 with the >>16 folded into a high multiply.
+// =============================================================================================
+#define RS_TH 32
+#define RS_WARPS 4
+
+struct RsCol { uint32_t coef[4]; uint32_t selA[4], selB[4]; bool useB[4]; int w0idx, w1idx, w2idx; };
+
+__device__ __forceinline__ void rs_hrow(const u8* __restrict__ row, const RsCol& c, uint32_t Hq[4])
+{
+    const uint32_t* r32 = reinterpret_cast<const uint32_t*>(row);
+    const uint32_t w0 = r32[c.w0idx], w1 = r32[c.w1idx], w2 = r32[c.w2idx];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const uint32_t A = __byte_perm(w0, w1, c.selA[i]), B = __byte_perm(w1, w2, c.selB[i]);
+        Hq[i] = __dp2a_lo(c.coef[i], c.useB[i] ? B : A, 0u) >> 4;       // (p0*a0 + p1*a1) >> 4
+    }
+}
+
+__global__ void __launch_bounds__(RS_WARPS * 32)
+pyr_resize4_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long long srcFrameStride, int srcPitch, int sw,
+                   u8* __restrict__ dstBase, long long dstFrameStride, int dstPitch,
+                   int dw, int dh, const int2* __restrict__ cx, const int2* __restrict__ cy)
+{
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int x = (blockIdx.x * 32 + lane) * 4;
+    const int y0 = (blockIdx.y * RS_WARPS + wid) * RS_TH;
+    if (y0 >= dh) return;
+    const u8* src = fromL0 ? l0_frame(l0, blockIdx.z) : srcBase + (long long)blockIdx.z * srcFrameStride;
+    u8* dst = dstBase + (long long)blockIdx.z * dstFrameStride;
+    // ---- per-column constants ------------------------------------------------------------------
+    RsCol c;
+    const int lastWord = (sw - 1) >> 2;
+    {
+        const int2 c0 = cx[min(x, dw - 1)];
+        const int wb = (c0.x & 0xffff) >> 2;
+        c.w0idx = min(wb, lastWord); c.w1idx = min(wb + 1, lastWord); c.w2idx = min(wb + 2, lastWord);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int2 ci = cx[min(x + i, dw - 1)];
+            const int o = (ci.x & 0xffff) - 4 * wb;                 // 0 .. 10 for scale <= 2
+            c.coef[i] = (uint32_t)ci.y;                             // a0 | a1 << 16
+            c.useB[i] = o >= 4;
+            c.selA[i] = (uint32_t)(o & 7) | ((uint32_t)((o + 1) & 7) << 4);
+            c.selB[i] = (uint32_t)((o - 4) & 7) | ((uint32_t)((o - 3) & 7) << 4);
+        }
+    }
+    int ra = -1, rb = -1;                   // source rows whose horizontal sums are in HA / HB
+    uint32_t HA[4], HB[4];
+    const int yend = min(y0 + RS_TH, dh);
+    for (int y = y0; y < yend; ++y) {
+        const int2 cyv = cy[y];
+        const int sy0 = cyv.x & 0xffff, sy1 = cyv.x >> 16;
+        const uint32_t b0 = (uint32_t)(cyv.y & 0xffff) << 16, b1 = (uint32_t)(cyv.y >> 16) << 16;
+        if (sy0 != ra) {
+            if (sy0 == rb) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) HA[i] = HB[i];
+            } else rs_hrow(src + (long long)sy0 * srcPitch, c, HA);
+            ra = sy0;
+        }
+        if (sy1 != rb) {
+            if (sy1 == ra) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) HB[i] = HA[i];
+            } else rs_hrow(src + (long long)sy1 * srcPitch, c, HB);
+            rb = sy1;
+        }
+        uint32_t o[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) o[i] = (__umulhi(b0, HA[i]) + __umulhi(b1, HB[i]) + 2u) >> 2;
+        if (x < dw)
+            *reinterpret_cast<uint32_t*>(dst + (long long)y * dstPitch + x) = o[0] | (o[1] << 8) | (o[2] << 16) | (o[3] << 24);
+    }
+}
+
+// =============================================================================================
 // K1b: 7x7 Gaussian blur, kernel [18 34 48 56 48 34 18]/256 per axis, exact integer, reflect-101
 // of the level itself.  One warp owns a 128 x 32 strip: a lane owns 4 adjacent columns and walks
 // down the rows.  Per row it loads ONE aligned 32-bit word (the warp reads 128 contiguous bytes),
@@ -960,9 +1043,15 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
         const u8* src; long long sfs; int sp;
         if (l == 1) { src = l0.base; sfs = l0.frameStride; sp = l0.pitch; }
         else { src = h->dRaw + S.off; sfs = g.pyrFrameBytes; sp = S.pitch; }
-        dim3 grid((D.w + 127) / 128, (D.h + 7) / 8, nframes), block(32, 8);
-        pyr_resize_kernel<<<grid, block, 0, st>>>(l0, l == 1 ? 1 : 0, src, sfs, sp, h->dRaw + D.off, g.pyrFrameBytes, D.pitch, D.w, D.h,
-                                                  h->dCoef + D.coefX, h->dCoef + D.coefY);
+        if (h->params.scale_factor <= 2.0f) {
+            dim3 grid((D.w + 127) / 128, (D.h + RS_TH * RS_WARPS - 1) / (RS_TH * RS_WARPS), nframes);
+            pyr_resize4_kernel<<<grid, RS_WARPS * 32, 0, st>>>(l0, l == 1 ? 1 : 0, src, sfs, sp, S.w, h->dRaw + D.off, g.pyrFrameBytes,
+                                                               D.pitch, D.w, D.h, h->dCoef + D.coefX, h->dCoef + D.coefY);
+        } else {
+            dim3 grid((D.w + 127) / 128, (D.h + 7) / 8, nframes), block(32, 8);
+            pyr_resize_kernel<<<grid, block, 0, st>>>(l0, l == 1 ? 1 : 0, src, sfs, sp, h->dRaw + D.off, g.pyrFrameBytes, D.pitch, D.w, D.h,
+                                                      h->dCoef + D.coefX, h->dCoef + D.coefY);
+        }
     }
     ORBX_COUNT(h, ORBX_STAGE_RESIZE, nl - 1);
     orbx_prof_mark(h, ORBX_STAGE_RESIZE);
