@@ -70,19 +70,22 @@ pyr_resize_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long lo
 
 struct RsCol { uint32_t coef[4]; uint32_t selA[4], selB[4]; bool useB[4]; int w0idx, w1idx, w2idx; };
 
-__device__ __forceinline__ void rs_hrow(const u8* __restrict__ row, const RsCol& c, uint32_t Hq[4])
+__device__ __forceinline__ void rs_load(const u8* __restrict__ row, const RsCol& c, uint32_t w[3])
 {
     const uint32_t* r32 = reinterpret_cast<const uint32_t*>(row);
-    const uint32_t w0 = r32[c.w0idx], w1 = r32[c.w1idx], w2 = r32[c.w2idx];
+    w[0] = r32[c.w0idx]; w[1] = r32[c.w1idx]; w[2] = r32[c.w2idx];
+}
+__device__ __forceinline__ void rs_hsum(const uint32_t w[3], const RsCol& c, uint32_t Hq[4])
+{
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        const uint32_t A = __byte_perm(w0, w1, c.selA[i]), B = __byte_perm(w1, w2, c.selB[i]);
+        const uint32_t A = __byte_perm(w[0], w[1], c.selA[i]), B = __byte_perm(w[1], w[2], c.selB[i]);
         Hq[i] = __dp2a_lo(c.coef[i], c.useB[i] ? B : A, 0u) >> 4;       // (p0*a0 + p1*a1) >> 4
     }
 }
 
 __global__ void __launch_bounds__(RS_WARPS * 32)
-pyr_resize4_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long long srcFrameStride, int srcPitch, int sw,
+pyr_resize4_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long long srcFrameStride, int srcPitch, int sw, int sh,
                    u8* __restrict__ dstBase, long long dstFrameStride, int dstPitch,
                    int dw, int dh, const int2* __restrict__ cx, const int2* __restrict__ cy)
 {
@@ -112,6 +115,11 @@ pyr_resize4_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long l
     int ra = -1, rb = -1;                   // source rows whose horizontal sums are in HA / HB
     uint32_t HA[4], HB[4];
     const int yend = min(y0 + RS_TH, dh);
+    auto hrow = [&](int r, uint32_t Hq[4]) {
+        uint32_t w[3];
+        rs_load(src + (long long)r * srcPitch, c, w);
+        rs_hsum(w, c, Hq);
+    };
     for (int y = y0; y < yend; ++y) {
         const int2 cyv = cy[y];
         const int sy0 = cyv.x & 0xffff, sy1 = cyv.x >> 16;
@@ -120,14 +128,14 @@ pyr_resize4_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long l
             if (sy0 == rb) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) HA[i] = HB[i];
-            } else rs_hrow(src + (long long)sy0 * srcPitch, c, HA);
+            } else hrow(sy0, HA);
             ra = sy0;
         }
         if (sy1 != rb) {
             if (sy1 == ra) {
 #pragma unroll
                 for (int i = 0; i < 4; ++i) HB[i] = HA[i];
-            } else rs_hrow(src + (long long)sy1 * srcPitch, c, HB);
+            } else hrow(sy1, HB);
             rb = sy1;
         }
         uint32_t o[4];
@@ -797,10 +805,6 @@ describe_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, const u8* __r
                 orbx_keypoint* __restrict__ outKps, u8* __restrict__ outDesc, int* __restrict__ outCount,
                 int* __restrict__ outLevelCount, int firstSlot, int kpCapOut)
 {
-    __shared__ __align__(16) signed char sPat[ORBX_PATTERN_LEN];
-    for (int i = threadIdx.x; i < ORBX_PATTERN_LEN / 4; i += blockDim.x)
-        reinterpret_cast<int*>(sPat)[i] = reinterpret_cast<const int*>(pattern)[i];
-    __syncthreads();
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const long long gw = (long long)blockIdx.x * DESC_WARPS + (threadIdx.x >> 5);
@@ -810,13 +814,15 @@ describe_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, const u8* __r
     const LevelGeom& L = g.L[level];
     const int k = slotk - L.kpOff;
     const int* counts = levelKpCount + frame * g.nlevels;
-    int offset = 0, total = 0;
-    for (int l = 0; l < g.nlevels; ++l) { const int c = counts[l]; if (l < level) offset += c; total += c; }
-    if (slotk == 0 && lane == 0) {
-        outCount[firstSlot + frame] = total;
-        for (int l = 0; l < g.nlevels; ++l) outLevelCount[(firstSlot + frame) * ORBX_MAX_LEVELS + l] = counts[l];
+    // lane l holds the count of level l: output offset = keypoints of the lower levels
+    const int myCount = lane < g.nlevels ? counts[lane] : 0;
+    int offset = lane < level ? myCount : 0, total = myCount;
+    for (int d = 16; d > 0; d >>= 1) { offset += __shfl_xor_sync(FULL, offset, d); total += __shfl_xor_sync(FULL, total, d); }
+    if (slotk == 0) {
+        if (lane == 0) outCount[firstSlot + frame] = total;
+        if (lane < g.nlevels) outLevelCount[(firstSlot + frame) * ORBX_MAX_LEVELS + lane] = myCount;
     }
-    if (k >= counts[level]) return;
+    if (k >= __shfl_sync(FULL, myCount, level)) return;
     const uint32_t packed = levelKps[(size_t)frame * g.kpTotal + slotk];
     const int px = key_x(packed) + 16, py = key_y(packed) + 16;     // + minBorderX/Y (EDGE_THRESHOLD-3)
     const u8* raw;
@@ -847,11 +853,13 @@ describe_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, const u8* __r
     orbx_sincosf(__fmul_rn(angle, factorPI), &sa, &ca);
     const u8* bl = blurBase + (long long)frame * g.pyrFrameBytes + L.off;
     const u8* bc = bl + (long long)py * L.pitch + px;
-    const signed char* pat = sPat + lane * 32;
+    // lane i evaluates the 8 point pairs of descriptor byte i: 32 bytes of the pattern table
+    const int4 patA = __ldg(reinterpret_cast<const int4*>(pattern) + lane * 2), patB = __ldg(reinterpret_cast<const int4*>(pattern) + lane * 2 + 1);
+    const int patw[8] = {patA.x, patA.y, patA.z, patA.w, patB.x, patB.y, patB.z, patB.w};
     int val = 0;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        const int pw = reinterpret_cast<const int*>(pat)[j];          // x0, y0, x1, y1 as signed bytes
+        const int pw = patw[j];                                       // x0, y0, x1, y1 as signed bytes
         const float x0 = (float)(signed char)(pw & 0xff), y0 = (float)(signed char)((pw >> 8) & 0xff);
         const float x1 = (float)(signed char)((pw >> 16) & 0xff), y1 = (float)(signed char)(pw >> 24);
         const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, sa), __fmul_rn(y0, ca)));
@@ -1045,7 +1053,7 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
         else { src = h->dRaw + S.off; sfs = g.pyrFrameBytes; sp = S.pitch; }
         if (h->params.scale_factor <= 2.0f) {
             dim3 grid((D.w + 127) / 128, (D.h + RS_TH * RS_WARPS - 1) / (RS_TH * RS_WARPS), nframes);
-            pyr_resize4_kernel<<<grid, RS_WARPS * 32, 0, st>>>(l0, l == 1 ? 1 : 0, src, sfs, sp, S.w, h->dRaw + D.off, g.pyrFrameBytes,
+            pyr_resize4_kernel<<<grid, RS_WARPS * 32, 0, st>>>(l0, l == 1 ? 1 : 0, src, sfs, sp, S.w, S.h, h->dRaw + D.off, g.pyrFrameBytes,
                                                                D.pitch, D.w, D.h, h->dCoef + D.coefX, h->dCoef + D.coefY);
         } else {
             dim3 grid((D.w + 127) / 128, (D.h + 7) / 8, nframes), block(32, 8);
