@@ -316,7 +316,7 @@ def run_stereo(args):
     dl, dr = hl.to(dev), hr.to(dev)
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
-    ex = capi.Extractor(nfeatures=2000, max_width=w, max_height=h, chunk_frames=min(args.chunk, 256), result_slots=2 * P, device=local,
+    ex = capi.Extractor(nfeatures=2000, max_width=w, max_height=h, chunk_frames=min(args.chunk, 512), result_slots=2 * P, device=local,
                         stream=stream.cuda_stream)
     step = lambda: ex.extract_stereo_batch(dl.data_ptr(), dr.data_ptr(), bf, fx, nframes=P, width=w, height=h, frame_stride=w * h,
                                            row_stride=w, on_device=True, fetch=False)

@@ -73,6 +73,30 @@ void orbx_prof_mark(orbx_handle* h, int stage)
     ++h->evUsed;
 }
 
+// Frames from the caller (host or device) into the pitched workspace.  A 2-D host->device copy
+// with different source and destination pitches runs at a fraction of the link rate (one DMA
+// descriptor per 1-2 KB row), so contiguous host frames are copied LINEARLY into a device landing
+// zone and re-pitched there by a device-to-device 2-D copy.
+int orbx_copy_frames(orbx_handle* h, uint8_t* dst, long long dstFrameBytes, uint8_t* stage, const uint8_t* src, size_t frame_stride,
+                     size_t row_stride, int width, int height, int nf, bool srcOnDevice, cudaStream_t st, long long* frameStrideOut)
+{
+    const cudaMemcpyKind kind = srcOnDevice ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    if (frame_stride == row_stride * (size_t)height) {
+        // row-contiguous frames: one tall image of nf*height rows
+        if (!srcOnDevice && (int)row_stride != h->l0Pitch && (size_t)nf * frame_stride <= (size_t)h->chunkFrames * h->l0FrameBytes) {
+            ORBX_CUDA(cudaMemcpyAsync(stage, src, (size_t)nf * frame_stride, cudaMemcpyHostToDevice, st));
+            ORBX_CUDA(cudaMemcpy2DAsync(dst, h->l0Pitch, stage, row_stride, width, (size_t)height * nf, cudaMemcpyDeviceToDevice, st));
+        } else
+            ORBX_CUDA(cudaMemcpy2DAsync(dst, h->l0Pitch, src, row_stride, width, (size_t)height * nf, kind, st));
+        *frameStrideOut = (long long)h->l0Pitch * height;
+    } else {
+        for (int f = 0; f < nf; ++f)
+            ORBX_CUDA(cudaMemcpy2DAsync(dst + (size_t)f * dstFrameBytes, h->l0Pitch, src + (size_t)f * frame_stride, row_stride, width, height, kind, st));
+        *frameStrideOut = dstFrameBytes;
+    }
+    return ORBX_OK;
+}
+
 extern "C" {
 
 const char* orbx_last_error(void) { return g_err; }
@@ -138,7 +162,7 @@ int orbx_create(const orbx_params* params, int max_width, int max_height, int ch
     h->chunkFrames = chunk_frames; h->resultSlots = result_slots;
     h->curW = h->curH = 0;
     h->dCells = nullptr; h->dCoef = nullptr; h->dBlurTiles = nullptr; h->dKpMap = nullptr; h->nBlurTiles = 0;
-    h->dLevel0 = h->dRaw = h->dBlur = nullptr;
+    h->dLevel0 = h->dStageLin = h->dRaw = h->dBlur = nullptr;
     h->dCand = h->dKeysA = h->dKeysB = nullptr; h->dCellSeg = nullptr; h->dLevelCandCount = nullptr;
     h->dLevelKps = nullptr; h->dLevelKpCount = nullptr; h->dStatus = nullptr;
     h->dKps = nullptr; h->dDesc = nullptr; h->dCount = nullptr; h->dSlotLevelCount = nullptr;
@@ -189,7 +213,7 @@ int orbx_destroy(orbx_handle* h)
     if (!h) return ORBX_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
-    void* ptrs[] = {h->dCells, h->dCoef, h->dBlurTiles, h->dKpMap, h->dLevel0, h->dRaw, h->dBlur, h->dCand, h->dKeysA,
+    void* ptrs[] = {h->dCells, h->dCoef, h->dBlurTiles, h->dKpMap, h->dLevel0, h->dStageLin, h->dRaw, h->dBlur, h->dCand, h->dKeysA,
                     h->dKeysB, h->dCellSeg, h->dLevelCandCount, h->dLevelKps, h->dLevelKpCount, h->dStatus, h->dKps,
                     h->dDesc, h->dCount, h->dSlotLevelCount, h->dGridStart, h->dGridIdx, h->dMatches12, h->dNMatches,
                     h->dNCompares, h->dURight, h->dDepth, h->dMatchScratch};
@@ -279,18 +303,10 @@ int orbx_extract_batch_to_host(orbx_handle* h, const uint8_t* images, size_t fra
         else {
             const int b = chunkNo & 1;
             uint8_t* dstBuf = h->dLevel0 + (size_t)b * h->chunkFrames * h->l0FrameBytes;
-            const cudaMemcpyKind kind = images_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
             if (h->evFreeValid[b]) ORBX_CUDA(cudaStreamWaitEvent(h->copyStream, h->evFree[b], 0));
-            if (frame_stride == row_stride * (size_t)height) {
-                // frames are row-contiguous: one tall 2-D copy; workspace frame stride follows
-                ORBX_CUDA(cudaMemcpy2DAsync(dstBuf, h->l0Pitch, src, row_stride, width, (size_t)height * nf, kind, h->copyStream));
-                l0.frameStride = (long long)h->l0Pitch * height;
-            } else {
-                for (int f = 0; f < nf; ++f)
-                    ORBX_CUDA(cudaMemcpy2DAsync(dstBuf + (size_t)f * h->l0FrameBytes, h->l0Pitch, src + (size_t)f * frame_stride,
-                                                row_stride, width, height, kind, h->copyStream));
-                l0.frameStride = h->l0FrameBytes;
-            }
+            rc = orbx_copy_frames(h, dstBuf, h->l0FrameBytes, h->dStageLin + (size_t)b * h->chunkFrames * h->l0FrameBytes, src, frame_stride,
+                                  row_stride, width, height, nf, images_on_device != 0, h->copyStream, &l0.frameStride);
+            if (rc) return rc;
             ORBX_CUDA(cudaEventRecord(h->evCopied[b], h->copyStream));
             ORBX_CUDA(cudaStreamWaitEvent(h->stream, h->evCopied[b], 0));
             l0.base = dstBuf; l0.pitch = h->l0Pitch;

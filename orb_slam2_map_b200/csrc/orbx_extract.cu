@@ -999,6 +999,7 @@ int orbx_setup_shape(orbx_handle* h, int w, int hgt)
     h->l0Pitch = (w + 15) & ~15;
     h->l0FrameBytes = (((long long)h->l0Pitch * hgt) + 255) & ~255LL;
     ORBX_CUDA(re((void**)&h->dLevel0, 2 * C * h->l0FrameBytes));
+    ORBX_CUDA(re((void**)&h->dStageLin, 2 * C * h->l0FrameBytes));
     h->evFreeValid[0] = h->evFreeValid[1] = false;
     ORBX_CUDA(re((void**)&h->dRaw, C * g.pyrFrameBytes));
     ORBX_CUDA(re((void**)&h->dBlur, C * g.pyrFrameBytes));

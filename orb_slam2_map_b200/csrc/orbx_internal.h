@@ -95,6 +95,7 @@ struct orbx_handle {
     int* dKpMap;        // keypoint-slot -> level map for the describe kernel
     // workspace (chunkFrames deep)
     uint8_t* dLevel0;   // pitched copies of the input images (when needed): two chunk-sized buffers
+    uint8_t* dStageLin; // same size: landing zone for LINEAR host->device copies (then re-pitched on the device)
     cudaStream_t copyStream;        // host->device copies of chunk i+1 overlap the kernels of chunk i
     cudaStream_t d2hStream;         // device->host copies of chunk i overlap the kernels of chunk i+1
     cudaEvent_t evCopied[2], evFree[2], evDone;
@@ -149,6 +150,10 @@ void orbx_prof_mark(orbx_handle* h, int stage);
 // orbx_extract.cu
 int orbx_setup_shape(orbx_handle* h, int w, int hgt);
 int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot);
+
+// orbx_api.cu: frames [nf][height][row_stride] -> pitched workspace frames, on `st`
+int orbx_copy_frames(orbx_handle* h, uint8_t* dst, long long dstFrameBytes, uint8_t* stage, const uint8_t* src, size_t frame_stride,
+                     size_t row_stride, int width, int height, int nf, bool srcOnDevice, cudaStream_t st, long long* frameStrideOut);
 
 // orbx_match.cu
 int orbx_build_grids(orbx_handle* h, int firstSlot, int nframes, int width, int height);

@@ -472,6 +472,7 @@ __device__ __forceinline__ int reflect101i(int i, int n)
 }
 
 #define STEREO_THREADS 256
+#define STEREO_SPLITS 8           // CTAs per pair (left keypoints are split; the median cull is a second kernel)
 __global__ void __launch_bounds__(STEREO_THREADS)
 stereo_match_kernel(FrameStore fs, int firstSlot, PyrView pv, float bf, float fx, int rightCap,
                     float* __restrict__ uRightOut, float* __restrict__ depthOut, int* __restrict__ sadScratch,
@@ -481,10 +482,11 @@ stereo_match_kernel(FrameStore fs, int firstSlot, PyrView pv, float bf, float fx
     int* rRows = reinterpret_cast<int*>(smraw);                 // minr | maxr<<16 (biased by 4096)
     float* rX = reinterpret_cast<float*>(rRows + rightCap);
     u8* rOct = reinterpret_cast<u8*>(rX + rightCap);
-    __shared__ int sCount[2];
-    const int pair = blockIdx.x;
+    const int pair = blockIdx.x, split = blockIdx.y;
     const int sL = firstSlot + 2 * pair, sR = sL + 1;
     const int N = min(fs.count[sL], fs.cap), Nr = min(min(fs.count[sR], fs.cap), rightCap);
+    const int perSplit = (N + STEREO_SPLITS - 1) / STEREO_SPLITS;
+    const int iBeg = split * perSplit, iEnd = min(N, iBeg + perSplit);
     const orbx_keypoint* kL = fs.kps + (size_t)sL * fs.cap;
     const orbx_keypoint* kR = fs.kps + (size_t)sR * fs.cap;
     const u8* dL = fs.desc + (size_t)sL * fs.cap * 32;
@@ -502,13 +504,13 @@ stereo_match_kernel(FrameStore fs, int firstSlot, PyrView pv, float bf, float fx
         rX[i] = kp.x;
         rOct[i] = (u8)kp.octave;
     }
-    if (tid < 2) sCount[tid] = 0;
-    for (int i = N + tid; i < fs.cap; i += STEREO_THREADS) { uOut[i] = -1.f; zOut[i] = -1.f; }   // unused tail
+    if (split == 0)
+        for (int i = N + tid; i < fs.cap; i += STEREO_THREADS) { uOut[i] = -1.f; zOut[i] = -1.f; }   // unused tail
     __syncthreads();
     const float mb = __fdiv_rn(bf, fx);
     const float minD = -3.f, maxD = __fdiv_rn(bf, mb);
     unsigned long long ncmp = 0;
-    for (int iL = wid; iL < N; iL += STEREO_THREADS / 32) {
+    for (int iL = iBeg + wid; iL < iEnd; iL += STEREO_THREADS / 32) {
         const orbx_keypoint kp = kL[iL];
         float uR = -1.f, z = -1.f;
         int bestSad = -1;
@@ -600,8 +602,23 @@ stereo_match_kernel(FrameStore fs, int firstSlot, PyrView pv, float bf, float fx
     }
     for (int d = 16; d > 0; d >>= 1) ncmp += __shfl_xor_sync(FULL, ncmp, d);
     if (lane == 0 && ncompares && ncmp) atomicAdd(ncompares, ncmp);
+}
+
+// phase 3 of Frame::ComputeStereoMatches (src/Frame.cc:624-637): median of the accepted SADs of one
+// pair (k-th smallest with k = size/2, found by bisection on the value), cull SAD >= 1.5*1.4*median.
+__global__ void __launch_bounds__(STEREO_THREADS)
+stereo_cull_kernel(FrameStore fs, int firstSlot, float* __restrict__ uRightOut, float* __restrict__ depthOut,
+                   const int* __restrict__ sadScratch)
+{
+    __shared__ int sCount[2];
+    const int pair = blockIdx.x;
+    const int N = min(fs.count[firstSlot + 2 * pair], fs.cap);
+    float* uOut = uRightOut + (size_t)pair * fs.cap;
+    float* zOut = depthOut + (size_t)pair * fs.cap;
+    const int* sad = sadScratch + (size_t)pair * fs.cap;
+    const int tid = threadIdx.x, lane = tid & 31;
+    if (tid < 2) sCount[tid] = 0;
     __syncthreads();
-    // ---- median of accepted SADs: k-th smallest, k = size/2 -----------------------------------------
     int cnt = 0;
     for (int i = tid; i < N; i += STEREO_THREADS) cnt += sad[i] >= 0;
     for (int d = 16; d > 0; d >>= 1) cnt += __shfl_xor_sync(FULL, cnt, d);
@@ -709,7 +726,8 @@ static int launch_stereo(const FrameStore& fs, int firstSlot, int npairs, const 
     const int smem = rightCap * 9 + 16;
     if (smem > 200 * 1024) { orbx_set_error("more than %d right keypoints per frame unsupported by the stereo matcher", 200 * 1024 / 9); return ORBX_E_CAPACITY; }
     if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(stereo_match_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    stereo_match_kernel<<<npairs, STEREO_THREADS, smem, st>>>(fs, firstSlot, pv, bf, fx, rightCap, uRight, depth, sadScratch, ncmp);
+    stereo_match_kernel<<<dim3(npairs, STEREO_SPLITS), STEREO_THREADS, smem, st>>>(fs, firstSlot, pv, bf, fx, rightCap, uRight, depth, sadScratch, ncmp);
+    stereo_cull_kernel<<<npairs, STEREO_THREADS, 0, st>>>(fs, firstSlot, uRight, depth, sadScratch);
     return ORBX_OK;
 }
 
@@ -988,7 +1006,15 @@ int orbx_extract_stereo_batch(orbx_handle* h, const uint8_t* left, const uint8_t
                         (((uintptr_t)left) % 4 == 0) && (((uintptr_t)right) % 4 == 0);
     const int pairsPerChunk = h->chunkFrames / 2;
     if (ncompares) ORBX_CUDA(cudaMemsetAsync(h->dNCompares, 0, sizeof(unsigned long long), h->stream));
-    for (int p0 = 0; p0 < npairs; p0 += pairsPerChunk) {
+    if (!direct) {
+        cudaEvent_t evStart;                                            // copies must not overtake earlier work on the handle
+        ORBX_CUDA(cudaEventCreateWithFlags(&evStart, cudaEventDisableTiming));
+        ORBX_CUDA(cudaEventRecord(evStart, h->stream));
+        ORBX_CUDA(cudaStreamWaitEvent(h->copyStream, evStart, 0));
+        ORBX_CUDA(cudaEventDestroy(evStart));
+    }
+    int chunkNo = 0;
+    for (int p0 = 0; p0 < npairs; p0 += pairsPerChunk, ++chunkNo) {
         const int np = std::min(pairsPerChunk, npairs - p0);
         Level0 l0;
         l0.stereo = 1;
@@ -996,14 +1022,22 @@ int orbx_extract_stereo_batch(orbx_handle* h, const uint8_t* left, const uint8_t
             l0.base = left + (size_t)p0 * frame_stride; l0.base1 = right + (size_t)p0 * frame_stride;
             l0.frameStride = (long long)frame_stride; l0.pitch = (int)row_stride;
         } else {
-            const cudaMemcpyKind kind = images_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
-            uint8_t* dl = h->dLevel0;
-            uint8_t* dr = h->dLevel0 + (size_t)pairsPerChunk * h->l0FrameBytes;
-            for (int f = 0; f < np; ++f) {
-                ORBX_CUDA(cudaMemcpy2DAsync(dl + (size_t)f * h->l0FrameBytes, h->l0Pitch, left + (size_t)(p0 + f) * frame_stride, row_stride, width, height, kind, h->stream));
-                ORBX_CUDA(cudaMemcpy2DAsync(dr + (size_t)f * h->l0FrameBytes, h->l0Pitch, right + (size_t)(p0 + f) * frame_stride, row_stride, width, height, kind, h->stream));
-            }
-            l0.base = dl; l0.base1 = dr; l0.frameStride = h->l0FrameBytes; l0.pitch = h->l0Pitch;
+            // chunk i+1 is copied on the copy stream into the other half of dLevel0 while chunk i computes
+            const int b = chunkNo & 1;
+            uint8_t* dl = h->dLevel0 + (size_t)b * h->chunkFrames * h->l0FrameBytes;
+            uint8_t* dr = dl + (size_t)pairsPerChunk * h->l0FrameBytes;
+            if (h->evFreeValid[b]) ORBX_CUDA(cudaStreamWaitEvent(h->copyStream, h->evFree[b], 0));
+            uint8_t* sl = h->dStageLin + (size_t)b * h->chunkFrames * h->l0FrameBytes;
+            uint8_t* sr = sl + (size_t)pairsPerChunk * h->l0FrameBytes;
+            rc = orbx_copy_frames(h, dl, h->l0FrameBytes, sl, left + (size_t)p0 * frame_stride, frame_stride, row_stride, width, height, np,
+                                  images_on_device != 0, h->copyStream, &l0.frameStride);
+            if (rc) return rc;
+            rc = orbx_copy_frames(h, dr, h->l0FrameBytes, sr, right + (size_t)p0 * frame_stride, frame_stride, row_stride, width, height, np,
+                                  images_on_device != 0, h->copyStream, &l0.frameStride);
+            if (rc) return rc;
+            ORBX_CUDA(cudaEventRecord(h->evCopied[b], h->copyStream));
+            ORBX_CUDA(cudaStreamWaitEvent(h->stream, h->evCopied[b], 0));
+            l0.base = dl; l0.base1 = dr; l0.pitch = h->l0Pitch;
         }
         const int slot0 = first_slot + 2 * p0;
         rc = orbx_run_chunk(h, l0, 2 * np, slot0); if (rc) return rc;
@@ -1026,8 +1060,9 @@ int orbx_extract_stereo_batch(orbx_handle* h, const uint8_t* left, const uint8_t
         rc = launch_stereo(fs, slot0, np, pv, bf, fx, h->kpCap, h->dURight + row0, h->dDepth + row0,
                            reinterpret_cast<int*>(h->dMatches12) + row0, ncompares ? h->dNCompares : nullptr, h->stream);
         if (rc) return rc;
-        ORBX_COUNT(h, ORBX_STAGE_STEREO, 1);
+        ORBX_COUNT(h, ORBX_STAGE_STEREO, 2);
         orbx_prof_mark(h, ORBX_STAGE_STEREO);
+        if (!direct) { ORBX_CUDA(cudaEventRecord(h->evFree[chunkNo & 1], h->stream)); h->evFreeValid[chunkNo & 1] = true; }
     }
     ORBX_CUDA(cudaGetLastError());
     const size_t row0 = (size_t)(first_slot / 2) * h->kpCap;
