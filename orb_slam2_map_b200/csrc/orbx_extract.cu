@@ -18,6 +18,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstring>
+#include <cstdlib>
 
 typedef uint8_t u8;
 
@@ -316,7 +317,7 @@ __device__ __forceinline__ int fast_strength(const u8* p, int tp)
 
 __global__ void __launch_bounds__(FAST_WARPS * 32)
 fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* __restrict__ rawBase,
-                  int nframes, int minTh, int iniTh, uint32_t* __restrict__ cand,
+                  int nframes, int minThArg, int iniThArg, uint32_t* __restrict__ cand,
                   int2* __restrict__ cellSeg, unsigned* __restrict__ levelCandCount,
                   int tilePitch, int scorePitch, int warpSmem)
 {
@@ -334,7 +335,8 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
 
     u8* tile = smem + (size_t)wid * warpSmem;
     u8* score = tile + (size_t)tilePitch * g.chMax;
-    unsigned short* list = reinterpret_cast<unsigned short*>(score + (size_t)scorePitch * (g.chMax - 4));
+    uint32_t* rowMask = reinterpret_cast<uint32_t*>(score + (size_t)scorePitch * (g.chMax - 4));    // 64 bits per detectable row
+    unsigned short* list = reinterpret_cast<unsigned short*>(rowMask + 2 * (g.chMax - 6));
 
     const int cw = c.cw, ch = c.ch;
     const int dw = cw - 6, dh = ch - 6;               // detectable interior
@@ -342,67 +344,91 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
     int nOut = 0;
     unsigned base = 0;
     if (dw > 0 && dh > 0) {
-        // ---- load the sub-image with aligned 32-bit words; lanes = (row, word) -----------------
-        const int xa = c.x0 & ~3, shift = c.x0 - xa;
-        const int nw = (shift + cw + 3) >> 2;
+        // ---- load the sub-image so that its column 0 lands on byte 0 of a tile row: two aligned
+        // 32-bit loads + funnel shift per word; lanes = (row, word) --------------------------------
         const int tw = tilePitch >> 2;
         {
+            const int xa = c.x0 & ~3, sh8 = 8 * (c.x0 - xa);
+            const int nw = (cw + 3) >> 2;
             const int wshift = nw <= 8 ? 3 : (nw <= 16 ? 4 : 5);
             const int lw = lane & ((1 << wshift) - 1), lr = lane >> wshift, rstep = 32 >> wshift;
             const u8* gp = img + (long long)(c.y0 + lr) * pitch + xa + 4 * lw;
             for (int y = lr; y < ch; y += rstep, gp += (long long)rstep * pitch)
-                if (lw < nw) reinterpret_cast<uint32_t*>(tile)[y * tw + lw] = *reinterpret_cast<const uint32_t*>(gp);
+                if (lw < nw) {
+                    const uint32_t lo = reinterpret_cast<const uint32_t*>(gp)[0], hi = reinterpret_cast<const uint32_t*>(gp)[1];
+                    reinterpret_cast<uint32_t*>(tile)[y * tw + lw] = __funnelshift_r(lo, hi, sh8);
+                }
         }
         // zero the score tile ((dh+2) x scorePitch)
         for (int i = lane; i < ((dh + 2) * scorePitch) >> 2; i += 32) reinterpret_cast<uint32_t*>(score)[i] = 0;
+        for (int i = lane; i < 2 * dh; i += 32) rowMask[i] = 0;
         __syncwarp();
-        // ---- stage 1a: compass pre-test on 4 pixels per lane (byte-packed).  A 9-arc contains two
-        // adjacent compass points, so |v - r| > minTh must hold for one of {N,S} and one of {E,W}.
-        // |v-r| per byte = VABSDIFF4; "> t" per byte via the 7-bit carry trick (t < 127).
+        // The reference calls cv::FAST(iniThFAST) and, only when that returns nothing, cv::FAST(minThFAST)
+        // (ORBextractor.cc:809-816).  Same here: most cells are done after the cheap high-threshold pass.
+        int n3 = 0;
+#pragma unroll 1
+        for (int attempt = 0; attempt < 2 && n3 == 0; ++attempt) {
+        const int minTh = attempt == 0 ? iniThArg : minThArg;
+        // ---- stage 1a: compass pre-test on 8 pixels per lane (byte-packed).  A 9-arc contains two
+        // adjacent compass points, so |v - r| > th must hold for one of {N,S} and one of {E,W}.
+        // |v-r| per byte = VABSDIFF4; "> t" per byte via the 7-bit carry trick (t < 127).  Each lane
+        // drops its 8 flags as ONE byte of the row's 64-bit mask; the ordered candidate list is then
+        // expanded from the masks once per cell (lanes = rows), not once per iteration.
         int n1 = 0;
         {
-            const int ng = (dw + 3) >> 2;                       // 4-pixel groups per row
-            const int gshift = ng <= 8 ? 3 : (ng <= 16 ? 4 : 5);
+            const int ng = (dw + 7) >> 3;                       // 8-pixel groups per row (<= 8: dw < 64)
+            const int gshift = ng <= 4 ? 2 : 3;
             const int lg = lane & ((1 << gshift) - 1), ly = lane >> gshift, rstep = 32 >> gshift;
             const uint32_t T = (uint32_t)(0x7f - min(minTh, 0x7e)) * 0x01010101u;
             const bool packedOk = minTh < 0x7f;
-            // byte column of pixel 0 of the group inside the tile: shift + 3 + 4*lg  -> word lg, byte (shift+3)
-            const int i1 = (shift + 3) >> 2, s1 = ((shift + 3) & 3) * 8;      // centre / N / S window
-            const int i4 = (shift + 6) >> 2, s4 = ((shift + 6) & 3) * 8;      // E window (x+3)
-            const int s12 = shift * 8;                                        // W window (x-3), word lg
-            uint32_t vmask = 0;                                               // valid pixels of this group
+            uint32_t vmask0 = 0, vmask1 = 0;                    // valid pixels of this group
 #pragma unroll
-            for (int j = 0; j < 4; ++j) if (4 * lg + j < dw) vmask |= 0x80u << (8 * j);
+            for (int j = 0; j < 4; ++j) {
+                if (8 * lg + j < dw) vmask0 |= 0x80u << (8 * j);
+                if (8 * lg + 4 + j < dw) vmask1 |= 0x80u << (8 * j);
+            }
+            u8* maskBytes = reinterpret_cast<u8*>(rowMask);
             for (int y0 = 0; y0 < dh; y0 += rstep) {
                 const int y = y0 + ly;
-                uint32_t pass = 0;
-                if (y < dh && lg < ng) {
-                    const uint32_t* rc = reinterpret_cast<const uint32_t*>(tile) + (y + 3) * tw + lg;
-                    const uint32_t t0 = rc[0], t1 = rc[1], t2 = rc[2], t3 = rc[3];
-                    const uint32_t* rn = rc + 3 * tw + i1;
-                    const uint32_t* rs = rc - 3 * tw + i1;
-                    const uint32_t V = __funnelshift_r(i1 ? t1 : t0, i1 ? t2 : t1, s1);
-                    const uint32_t R4 = __funnelshift_r(i4 == 1 ? t1 : t2, i4 == 1 ? t2 : t3, s4);
-                    const uint32_t R12 = __funnelshift_r(t0, t1, s12);
-                    const uint32_t R0 = __funnelshift_r(rn[0], rn[1], s1);
-                    const uint32_t R8 = __funnelshift_r(rs[0], rs[1], s1);
+                if (y < dh) {
+                    // pixel x of the group has its centre at byte 8*lg + 3 + x of tile row y+3
+                    const uint32_t* rc = reinterpret_cast<const uint32_t*>(tile) + (y + 3) * tw + 2 * lg;
+                    const uint2 ta = *reinterpret_cast<const uint2*>(rc), tb = *reinterpret_cast<const uint2*>(rc + 2);
+                    const uint2 na = *reinterpret_cast<const uint2*>(rc + 3 * tw), sa = *reinterpret_cast<const uint2*>(rc - 3 * tw);
+                    const uint32_t nb2 = rc[3 * tw + 2], sb2 = rc[-3 * tw + 2];
+                    const uint32_t V0 = __byte_perm(ta.x, ta.y, 0x6543), V1 = __byte_perm(ta.y, tb.x, 0x6543);
+                    const uint32_t E0 = __byte_perm(ta.y, tb.x, 0x5432), E1 = __byte_perm(tb.x, tb.y, 0x5432);
+                    const uint32_t N0 = __byte_perm(na.x, na.y, 0x6543), N1 = __byte_perm(na.y, nb2, 0x6543);
+                    const uint32_t S0 = __byte_perm(sa.x, sa.y, 0x6543), S1 = __byte_perm(sa.y, sb2, 0x6543);
+                    uint32_t p0 = vmask0, p1 = vmask1;
                     if (packedOk) {
-                        const uint32_t d0 = __vabsdiffu4(R0, V), d4 = __vabsdiffu4(R4, V);
-                        const uint32_t d8 = __vabsdiffu4(R8, V), d12 = __vabsdiffu4(R12, V);
-                        const uint32_t e0 = ((d0 & 0x7f7f7f7fu) + T) | d0, e4 = ((d4 & 0x7f7f7f7fu) + T) | d4;
-                        const uint32_t e8 = ((d8 & 0x7f7f7f7fu) + T) | d8, e12 = ((d12 & 0x7f7f7f7fu) + T) | d12;
-                        pass = (e0 | e8) & (e4 | e12) & vmask;
-                    } else pass = vmask;
+                        const uint32_t dn0 = __vabsdiffu4(N0, V0), de0 = __vabsdiffu4(E0, V0), ds0 = __vabsdiffu4(S0, V0), dw0 = __vabsdiffu4(ta.x, V0);
+                        const uint32_t dn1 = __vabsdiffu4(N1, V1), de1 = __vabsdiffu4(E1, V1), ds1 = __vabsdiffu4(S1, V1), dw1 = __vabsdiffu4(ta.y, V1);
+                        const uint32_t en0 = ((dn0 & 0x7f7f7f7fu) + T) | dn0, ee0 = ((de0 & 0x7f7f7f7fu) + T) | de0;
+                        const uint32_t es0 = ((ds0 & 0x7f7f7f7fu) + T) | ds0, ew0 = ((dw0 & 0x7f7f7f7fu) + T) | dw0;
+                        const uint32_t en1 = ((dn1 & 0x7f7f7f7fu) + T) | dn1, ee1 = ((de1 & 0x7f7f7f7fu) + T) | de1;
+                        const uint32_t es1 = ((ds1 & 0x7f7f7f7fu) + T) | ds1, ew1 = ((dw1 & 0x7f7f7f7fu) + T) | dw1;
+                        p0 &= (en0 | es0) & (ee0 | ew0);
+                        p1 &= (en1 | es1) & (ee1 | ew1);
+                    }
+                    // gather the four 0x80 flags of each word into a nibble (multiply trick: no carries collide)
+                    const uint32_t m8 = (((p0 >> 7) * 0x01020408u) >> 24) | ((((p1 >> 7) * 0x01020408u) >> 20) & 0xf0u);
+                    maskBytes[y * 8 + lg] = (u8)m8;
                 }
-                // append in (row, x) order: lanes are (ly, lg)-major, pixels of a lane ascending
-                const int cnt = __popc(pass);
+            }
+            __syncwarp();
+            // expand: lane = row (two rows per lane when the cell is taller than 32), row-major order
+            for (int yb = 0; yb < dh; yb += 32) {
+                const int y = yb + lane;
+                uint32_t m0 = 0, m1 = 0;
+                if (y < dh) { m0 = rowMask[2 * y]; m1 = rowMask[2 * y + 1]; }
+                const int cnt = __popc(m0) + __popc(m1);
                 int incl = cnt;
 #pragma unroll
                 for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += v; }
                 int pos = n1 + incl - cnt;
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    if (pass & (0x80u << (8 * j))) list[pos++] = (unsigned short)((y << 8) | (4 * lg + j));
+                while (m0) { const int b = __ffs(m0) - 1; m0 &= m0 - 1; list[pos++] = (unsigned short)((y << 8) | b); }
+                while (m1) { const int b = __ffs(m1) - 1; m1 &= m1 - 1; list[pos++] = (unsigned short)((y << 8) | (32 + b)); }
                 n1 += __shfl_sync(FULL, incl, 31);
             }
         }
@@ -418,7 +444,7 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
                 if (i < n1) {
                     e = list[i];
                     const int y = e >> 8, x = e & 0xff;
-                    const u8* p = tile + (y + 3) * tilePitch + shift + x + 3;
+                    const u8* p = tile + (y + 3) * tilePitch + x + 3;
                     const int tp = tilePitch;
                     const int v = p[0];
                     const uint32_t a0 = p[3 * tp] | (p[3 * tp + 1] << 16), b0 = p[-3 * tp] | (p[-3 * tp - 1] << 16);
@@ -448,7 +474,7 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
             if (i < n1) {
                 e = list[i];
                 const int y = e >> 8, x = e & 0xff;
-                const int S = fast_strength(tile + (y + 3) * tilePitch + shift + x + 3, tilePitch);
+                const int S = fast_strength(tile + (y + 3) * tilePitch + x + 3, tilePitch);
                 if (S > minTh) { corner = true; score[(y + 1) * scorePitch + x + 1] = (u8)S; }
             }
             __syncwarp();
@@ -458,10 +484,9 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
         }
         __syncwarp();
         // ---- stage 3: 3x3 non-max suppression inside the cell --------------------------------
-        int n3 = 0, nStrong = 0;
         for (int i0 = 0; i0 < n2; i0 += 32) {
             const int i = i0 + lane;
-            bool keep = false, strong = false;
+            bool keep = false;
             unsigned short e = 0;
             if (i < n2) {
                 e = list[i];
@@ -471,17 +496,16 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
                 keep = v > s[-1] && v > s[1] && v > s[-scorePitch - 1] && v > s[-scorePitch] &&
                        v > s[-scorePitch + 1] && v > s[scorePitch - 1] && v > s[scorePitch] &&
                        v > s[scorePitch + 1];
-                strong = keep && v > iniTh;
             }
             __syncwarp();
             const unsigned m = __ballot_sync(FULL, keep);
             if (keep) list[n3 + __popc(m & ((1u << lane) - 1))] = e;
             n3 += __popc(m);
-            nStrong += __popc(__ballot_sync(FULL, strong));
         }
         __syncwarp();
-        // ---- stage 4: emit (strong ones if any, else all), order = row-major ----------------
-        nOut = nStrong > 0 ? nStrong : n3;
+        }   // attempt
+        // ---- stage 4: emit, order = row-major --------------------------------------------------
+        nOut = n3;
         if (nOut > 0) {
             if (lane == 0) base = atomicAdd(&levelCandCount[frame * g.nlevels + c.level], (unsigned)nOut);
             base = __shfl_sync(FULL, base, 0);
@@ -495,7 +519,7 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
                     const unsigned short e = list[i];
                     const int y = e >> 8, x = e & 0xff;
                     const int S = score[(y + 1) * scorePitch + x + 1];
-                    emit = nStrong > 0 ? (S > iniTh) : true;
+                    emit = true;
                     packed = (uint32_t)(x + 3 + c.offx) | ((uint32_t)(y + 3 + c.offy) << 12) | ((uint32_t)(S - 1) << 24);
                 }
                 const unsigned m = __ballot_sync(FULL, emit);
@@ -945,6 +969,7 @@ int orbx_setup_shape(orbx_handle* h, int w, int hgt)
         const int nCols = (int)(width / 30.f), nRows = (int)(height / 30.f);
         if (L.winW > 0 && L.winH > 0 && nCols > 0 && nRows > 0) {
             const int wCell = (int)ceilf(width / nCols), hCell = (int)ceilf(height / nRows);
+            L.wCell = wCell; L.hCell = hCell;
             for (int i = 0; i < nRows; ++i) {
                 const float iniY = (float)(minBY + i * hCell);
                 float maxY = iniY + hCell + 6;
@@ -960,7 +985,7 @@ int orbx_setup_shape(orbx_handle* h, int w, int hgt)
                     c.cw = (unsigned short)((int)maxX - (int)iniX); c.ch = (unsigned short)((int)maxY - (int)iniY);
                     c.offx = (unsigned short)(j * wCell); c.offy = (unsigned short)(i * hCell);
                     c.level = (unsigned short)l; c.pad = 0;
-                    if (c.cw > 250 || c.ch > 250) { orbx_set_error("FAST cell too large (%dx%d)", c.cw, c.ch); return ORBX_E_INVALID; }
+                    if (c.cw > 66 || c.ch > 66) { orbx_set_error("FAST cell too large (%dx%d)", c.cw, c.ch); return ORBX_E_INVALID; }
                     cells.push_back(c);
                     g.cwMax = std::max<int>(g.cwMax, c.cw); g.chMax = std::max<int>(g.chMax, c.ch);
                     const int dw = c.cw - 6, dh = c.ch - 6;
@@ -1071,9 +1096,10 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
     // K2: FAST
     ORBX_CUDA(cudaMemsetAsync(h->dLevelCandCount, 0, (size_t)nframes * nl * sizeof(unsigned), st));
     {
-        const int tilePitch = ((g.cwMax + 3 + 3) & ~3) + 16;    // +16: the packed pre-test reads whole words past the cell
+        const int tilePitch = ((g.cwMax + 6 + 7) & ~7) + 16;    // rows 8-byte aligned; +16: the packed pre-test reads whole words past the cell
         const int scorePitch = (g.cwMax - 4 + 3) & ~3;
-        int warpSmem = tilePitch * g.chMax + scorePitch * (g.chMax - 4) + 2 * (g.cwMax - 6) * (g.chMax - 6);
+        const int maskBytes = 8 * (g.chMax - 6);                // one 64-bit pre-test mask per detectable row
+        int warpSmem = tilePitch * g.chMax + scorePitch * (g.chMax - 4) + maskBytes + 2 * (g.cwMax - 6) * (g.chMax - 6);
         warpSmem = (warpSmem + 15) & ~15;
         const int smem = warpSmem * FAST_WARPS;
         if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

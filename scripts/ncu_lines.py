@@ -83,7 +83,8 @@ def main():
         src = {i + 1: l.rstrip() for i, l in enumerate(open(f))}
     print(f"kernel {kre}: {tot_i} warp instructions, {tot_s} stall samples, {n} SASS instructions")
     print(f"{'inst%':>6} {'smp%':>6} {'lanes':>5}  line  source")
-    for ln, (i, s, t) in sorted(per.items(), key=lambda kv: -kv[1][0])[:top]:
+    items = sorted(per.items()) if "--by-line" in sys.argv else sorted(per.items(), key=lambda kv: -kv[1][0])[:top]
+    for ln, (i, s, t) in items:
         print(f"{100 * i / max(tot_i, 1):6.2f} {100 * s / max(tot_s, 1):6.2f} {t / max(i, 1):5.1f}  {ln:4d}  {src.get(ln, '')[:110]}")
 
 
