@@ -532,266 +532,292 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
 }
 
 // =============================================================================================
-// K3: DistributeOctTree.  One warp per (frame, level) replays the reference's list algorithm:
-// the node list is kept REVERSED in shared memory (push_front == append), keys of a node are a
-// contiguous, order-preserving segment of a ping-pong key buffer.  Equal-size ties in the
-// "careful" phase are ordered by creation (array index) — DEVIATION-1 of the oracle.
+// K3: DistributeOctTree, re-expressed as deterministic parallel quadtree splitting.  One CTA per
+// (frame, level).  The reference's std::list is kept as a REVERSED array of alive nodes
+// (push_front == append), rebuilt once per pass:  [survivors in order | children in split order].
+// Keys never move: every key carries the index of its node; a pass is
+//   count   key-parallel: quadrant of the key inside its (splitting) node -> 4 counters per node
+//   order   node-parallel: which nodes split and where their children go.  Breadth-first pass:
+//           every node with > 1 key, list order (= descending array index).  "Careful" pass
+//           (ORBextractor.cc:673-738): nodes sorted by (nKeys, creation index) descending, split
+//           until the node count reaches N — the cut-off is a prefix sum over the sorted order.
+//   rebuild node-parallel: write the new array (bounds as DivideNode computes them :481-537)
+//   relabel key-parallel: new node index of every key
+// Equal-size ties in the careful phase are ordered by creation (array index) — DEVIATION-1 of the
+// oracle.  The retained key of a node is its max-response key, first in reference order on ties:
+// a 32-bit atomicMax over (response << 24 | ~original index).
+// Keys and labels live in shared memory when the level has at most `keyCap` candidates, otherwise
+// in the (L2-resident) key buffers.
 // =============================================================================================
-struct QNodes {
-    short* ulx; short* uly; short* urx; short* bry;
-    int* beg;            // bit31 = which key buffer
-    unsigned short* cnt; // 0 = dead
-};
+#define OT_THREADS 128
+#define OT_NOSPLIT 0xffffffffu
 
 __device__ __forceinline__ int key_x(uint32_t k) { return k & 0xfff; }
 __device__ __forceinline__ int key_y(uint32_t k) { return (k >> 12) & 0xfff; }
 
-// Split node `ni` into up to four children appended at *top; returns growth (children - 1).
-__device__ int octree_split(QNodes q, int ni, int* top, uint32_t* keysA, uint32_t* keysB, int lane)
+// inclusive scan over the block (all threads call it); total = block sum
+__device__ __forceinline__ uint32_t block_scan_incl(uint32_t v, uint32_t* wsum, uint32_t& total)
 {
-    const unsigned FULL = 0xffffffffu;
-    const int ulx = q.ulx[ni], uly = q.uly[ni], urx = q.urx[ni], bry = q.bry[ni];
-    const int begw = q.beg[ni];
-    const int beg = begw & 0x7fffffff, n = q.cnt[ni];
-    const uint32_t* src = (begw < 0) ? keysB : keysA;
-    uint32_t* dst = (begw < 0) ? keysA : keysB;
-    const int halfX = (urx - ulx + 1) >> 1;      // ceil((float)(UR.x-UL.x)/2), widths >= 0
-    const int halfY = (bry - uly + 1) >> 1;
-    const int mx = ulx + halfX, my = uly + halfY;
-    int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
-    if (n <= 32) {
-        uint32_t k = 0;
-        int qd = 4;
-        if (lane < n) { k = src[beg + lane]; qd = (key_x(k) >= mx ? 1 : 0) | (key_y(k) >= my ? 2 : 0); }
-        const unsigned m0 = __ballot_sync(FULL, qd == 0), m1 = __ballot_sync(FULL, qd == 1);
-        const unsigned m2 = __ballot_sync(FULL, qd == 2), m3 = __ballot_sync(FULL, qd == 3);
-        c0 = __popc(m0); c1 = __popc(m1); c2 = __popc(m2); c3 = __popc(m3);
-        if (lane < n) {
-            const unsigned lt = (1u << lane) - 1;
-            int pos;
-            if (qd == 0) pos = __popc(m0 & lt);
-            else if (qd == 1) pos = c0 + __popc(m1 & lt);
-            else if (qd == 2) pos = c0 + c1 + __popc(m2 & lt);
-            else pos = c0 + c1 + c2 + __popc(m3 & lt);
-            dst[beg + pos] = k;
-        }
-    } else {
-        for (int i0 = 0; i0 < n; i0 += 32) {
-            int qd = 4;
-            if (i0 + lane < n) { const uint32_t k = src[beg + i0 + lane]; qd = (key_x(k) >= mx ? 1 : 0) | (key_y(k) >= my ? 2 : 0); }
-            c0 += __popc(__ballot_sync(FULL, qd == 0)); c1 += __popc(__ballot_sync(FULL, qd == 1));
-            c2 += __popc(__ballot_sync(FULL, qd == 2)); c3 += __popc(__ballot_sync(FULL, qd == 3));
-        }
-        int o0 = 0, o1 = c0, o2 = c0 + c1, o3 = c0 + c1 + c2;
-        for (int i0 = 0; i0 < n; i0 += 32) {
-            int qd = 4;
-            uint32_t k = 0;
-            if (i0 + lane < n) { k = src[beg + i0 + lane]; qd = (key_x(k) >= mx ? 1 : 0) | (key_y(k) >= my ? 2 : 0); }
-            const unsigned m0 = __ballot_sync(FULL, qd == 0), m1 = __ballot_sync(FULL, qd == 1);
-            const unsigned m2 = __ballot_sync(FULL, qd == 2), m3 = __ballot_sync(FULL, qd == 3);
-            const unsigned lt = (1u << lane) - 1;
-            if (qd == 0) dst[beg + o0 + __popc(m0 & lt)] = k;
-            else if (qd == 1) dst[beg + o1 + __popc(m1 & lt)] = k;
-            else if (qd == 2) dst[beg + o2 + __popc(m2 & lt)] = k;
-            else if (qd == 3) dst[beg + o3 + __popc(m3 & lt)] = k;
-            o0 += __popc(m0); o1 += __popc(m1); o2 += __popc(m2); o3 += __popc(m3);
-        }
-    }
-    __syncwarp();
-    // children in creation order n1 (UL), n2 (UR), n3 (BL), n4 (BR)
-    const int t = *top;
-    const int flip = (begw < 0) ? 0 : (int)0x80000000;
-    int nch = 0;
-    if (lane == 0) {
-        int o = beg, w = t;
-        if (c0) { q.ulx[w] = ulx; q.uly[w] = uly; q.urx[w] = mx;  q.bry[w] = my;  q.beg[w] = o | flip; q.cnt[w] = c0; ++w; } o += c0;
-        if (c1) { q.ulx[w] = mx;  q.uly[w] = uly; q.urx[w] = urx; q.bry[w] = my;  q.beg[w] = o | flip; q.cnt[w] = c1; ++w; } o += c1;
-        if (c2) { q.ulx[w] = ulx; q.uly[w] = my;  q.urx[w] = mx;  q.bry[w] = bry; q.beg[w] = o | flip; q.cnt[w] = c2; ++w; } o += c2;
-        if (c3) { q.ulx[w] = mx;  q.uly[w] = my;  q.urx[w] = urx; q.bry[w] = bry; q.beg[w] = o | flip; q.cnt[w] = c3; ++w; }
-        q.cnt[ni] = 0;   // parent erased
-    }
-    nch = (c0 != 0) + (c1 != 0) + (c2 != 0) + (c3 != 0);
-    *top = t + nch;
-    __syncwarp();
-    return nch - 1;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, v, d); if (lane >= d) v += u; }
+    if (lane == 31) wsum[wid] = v;
+    __syncthreads();
+    uint32_t off = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < OT_THREADS / 32; ++w) { const uint32_t sx = wsum[w]; if (w < wid) off += sx; tot += sx; }
+    __syncthreads();
+    total = tot;
+    return v + off;
 }
 
-// remove dead nodes, keep order; returns new length
-__device__ int octree_compact(QNodes q, int len, int lane)
+__device__ __forceinline__ int ot_quadrant(uint2 b, uint32_t key, int& mx, int& my)
 {
-    const unsigned FULL = 0xffffffffu;
-    int w = 0;
-    for (int i0 = 0; i0 < len; i0 += 32) {
-        const int i = i0 + lane;
-        short a = 0, b = 0, c = 0, d = 0; int bg = 0; unsigned short cn = 0;
-        if (i < len) { cn = q.cnt[i]; a = q.ulx[i]; b = q.uly[i]; c = q.urx[i]; d = q.bry[i]; bg = q.beg[i]; }
-        const unsigned m = __ballot_sync(FULL, cn != 0);
-        __syncwarp();
-        if (cn != 0) {
-            const int p = w + __popc(m & ((1u << lane) - 1));
-            q.cnt[p] = cn; q.ulx[p] = a; q.uly[p] = b; q.urx[p] = c; q.bry[p] = d; q.beg[p] = bg;
-        }
-        w += __popc(m);
-        __syncwarp();
-    }
-    return w;
+    const int ulx = b.x & 0xffff, uly = b.x >> 16, urx = b.y & 0xffff, bry = b.y >> 16;
+    mx = ulx + ((urx - ulx + 1) >> 1);          // UL.x + ceil((UR.x-UL.x)/2), ORBextractor.cc:483
+    my = uly + ((bry - uly + 1) >> 1);
+    return (key_x(key) >= mx ? 1 : 0) | (key_y(key) >= my ? 2 : 0);
 }
 
-// warp bitonic sort (ascending) of n (<= cap, cap power of two) 32-bit keys in shared memory
-__device__ void warp_bitonic_sort(uint32_t* a, int n, int cap, int lane)
-{
-    for (int i = n + lane; i < cap; i += 32) a[i] = 0xffffffffu;
-    __syncwarp();
-    for (int k = 2; k <= cap; k <<= 1)
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int i = lane; i < cap; i += 32) {
-                const int l = i ^ j;
-                if (l > i) {
-                    const uint32_t x = a[i], y = a[l];
-                    const bool up = (i & k) == 0;
-                    if ((x > y) == up) { a[i] = y; a[l] = x; }
-                }
-            }
-            __syncwarp();
-        }
-}
-
-__global__ void __launch_bounds__(32)
+__global__ void __launch_bounds__(OT_THREADS)
 octree_kernel(Geom g, int nframes, const uint32_t* __restrict__ cand, const int2* __restrict__ cellSeg,
-              const unsigned* __restrict__ levelCandCount, uint32_t* __restrict__ keysAbase,
-              uint32_t* __restrict__ keysBbase, uint32_t* __restrict__ levelKps,
-              int* __restrict__ levelKpCount, int nodeCap, int sortCap, int* __restrict__ status)
+              uint32_t* __restrict__ keysAbase, uint32_t* __restrict__ keysBbase, uint32_t* __restrict__ levelKps,
+              int* __restrict__ levelKpCount, int NC, int P2, int cellWords, int keyCap, int* __restrict__ status)
 {
     extern __shared__ __align__(16) u8 smem[];
     const unsigned FULL = 0xffffffffu;
-    const int lane = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31;
     const int level = blockIdx.x % g.nlevels, frame = blockIdx.x / g.nlevels;
     const LevelGeom& L = g.L[level];
-    QNodes q;
-    q.beg = reinterpret_cast<int*>(smem);
-    q.ulx = reinterpret_cast<short*>(q.beg + nodeCap);
-    q.uly = q.ulx + nodeCap; q.urx = q.uly + nodeCap; q.bry = q.urx + nodeCap;
-    q.cnt = reinterpret_cast<unsigned short*>(q.bry + nodeCap);
-    uint32_t* sortbuf = reinterpret_cast<uint32_t*>(q.cnt + nodeCap + (nodeCap & 1));
+    // ---- shared memory carve-up (the cell tables of the gather alias everything up to cntB) ----
+    unsigned long long* sortbuf = reinterpret_cast<unsigned long long*>(smem);
+    uint2* bndA = reinterpret_cast<uint2*>(sortbuf + P2);
+    uint2* bndB = bndA + NC;
+    uint32_t* cc = reinterpret_cast<uint32_t*>(bndB + NC);
+    uint32_t* rel = cc + 4 * NC;
+    uint32_t* tmp = rel + NC;
+    uint32_t* cntA = tmp + NC;
+    uint32_t* aliasEnd = cntA + NC;
+    uint32_t* segStart = reinterpret_cast<uint32_t*>(smem);
+    {
+        const int have = (int)(aliasEnd - segStart);
+        if (cellWords > have) aliasEnd = segStart + cellWords;
+    }
+    uint32_t* cntB = aliasEnd;
+    uint32_t* wsum = cntB + NC;
+    uint32_t* misc = wsum + 32;
+    uint32_t* keysS = misc + 8;
+    unsigned short* nidS = reinterpret_cast<unsigned short*>(keysS + keyCap);
 
-    const int n = (int)levelCandCount[frame * g.nlevels + level];
-    uint32_t* keysA = keysAbase + (size_t)frame * g.candTotal + L.candOff;
-    uint32_t* keysB = keysBbase + (size_t)frame * g.candTotal + L.candOff;
-    const uint32_t* csrc = cand + (size_t)frame * g.candTotal + L.candOff;
     uint32_t* outKps = levelKps + (size_t)frame * g.kpTotal + L.kpOff;
     int* outCount = levelKpCount + frame * g.nlevels + level;
-    if (n == 0 || L.nIni <= 0) { if (lane == 0) *outCount = 0; return; }
+    if (L.nIni <= 0 || L.nCells <= 0) { if (tid == 0) *outCount = 0; return; }
 
-    // ---- gather the per-cell segments into reference order (cell-row-major) into keysB --------
+    // ---- gather the per-cell segments into reference order (cell-row-major) --------------------
+    uint32_t* segSrc = segStart + L.nCells + 1;
+    uint32_t carry = 0;
     {
-        int pos = 0;
         const int2* seg = cellSeg + (size_t)frame * g.ncells + L.cellBeg;
-        for (int c0 = 0; c0 < L.nCells; c0 += 32) {
-            int2 s = make_int2(0, 0);
-            if (c0 + lane < L.nCells) s = seg[c0 + lane];
-            int incl = s.y;
-            for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += v; }
-            const int excl = incl - s.y;
-            const int m = min(32, L.nCells - c0);
-            for (int j = 0; j < m; ++j) {
-                const int so = __shfl_sync(FULL, s.x, j), sc = __shfl_sync(FULL, s.y, j);
-                const int dp = pos + __shfl_sync(FULL, excl, j);
-                for (int i = lane; i < sc; i += 32) keysB[dp + i] = csrc[so + i];
-            }
-            pos += __shfl_sync(FULL, incl, 31);
+        for (int c0 = 0; c0 < L.nCells; c0 += OT_THREADS) {
+            const int c = c0 + tid;
+            int2 sg = make_int2(0, 0);
+            if (c < L.nCells) sg = seg[c];
+            uint32_t tot;
+            const uint32_t incl = block_scan_incl((uint32_t)sg.y, wsum, tot);
+            if (c < L.nCells) { segStart[c] = carry + incl - (uint32_t)sg.y; segSrc[c] = (uint32_t)sg.x; }
+            carry += tot;
         }
+        if (tid == 0) segStart[L.nCells] = carry;
+        for (int r = tid; r < L.nIni; r += OT_THREADS) cntB[r] = 0;
     }
-    __syncwarp();
-    // ---- roots: vpIniNodes[kp.pt.x / hX], stable partition keysB -> keysA ----------------------
-    int top = 0;
+    const int n = (int)carry;
+    if (n == 0) { if (tid == 0) *outCount = 0; return; }
+    __syncthreads();
+    const bool inShared = n <= keyCap;
+    uint32_t* keys = inShared ? keysS : keysAbase + (size_t)frame * g.candTotal + L.candOff;
+    unsigned short* nid = inShared ? nidS : reinterpret_cast<unsigned short*>(keysBbase + (size_t)frame * g.candTotal + L.candOff);
     {
-        int o = 0;
-        // reversed list: root nIni-1 first ... root 0 last
+        const uint32_t* csrc = cand + (size_t)frame * g.candTotal + L.candOff;
+        for (int k0 = 0; k0 < n; k0 += OT_THREADS) {
+            const int k = k0 + tid;
+            uint32_t r = 0xffffffffu;
+            if (k < n) {
+                int lo = 0, hi = L.nCells;                  // last cell with segStart <= k
+                while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (segStart[mid] <= (uint32_t)k) lo = mid; else hi = mid; }
+                const uint32_t key = csrc[segSrc[lo] + ((uint32_t)k - segStart[lo])];
+                keys[k] = key;
+                r = (uint32_t)__float2int_rz(__fdiv_rn((float)key_x(key), L.hX));     // vpIniNodes[kp.pt.x / hX], :557
+                nid[k] = (unsigned short)r;
+            }
+            const unsigned peers = __match_any_sync(FULL, r);
+            if (r != 0xffffffffu && lane == __ffs(peers) - 1) atomicAdd(&cntB[r], (uint32_t)__popc(peers));
+        }
+    }
+    __syncthreads();
+    // ---- roots (reversed list: root nIni-1 first), empty roots are erased (:565-578) ------------
+    if (tid == 0) {
+        int top = 0;
         for (int r = L.nIni - 1; r >= 0; --r) {
-            const int rb = o;
-            for (int i0 = 0; i0 < n; i0 += 32) {
-                bool sel = false; uint32_t k = 0;
-                if (i0 + lane < n) { k = keysB[i0 + lane]; sel = __float2int_rz(__fdiv_rn((float)key_x(k), L.hX)) == r; }
-                const unsigned m = __ballot_sync(FULL, sel);
-                if (sel) keysA[o + __popc(m & ((1u << lane) - 1))] = k;
-                o += __popc(m);
-            }
-            const int cnt = o - rb;
-            if (cnt > 0) {
-                if (lane == 0) {
-                    q.ulx[top] = (short)__float2int_rz(__fmul_rn(L.hX, (float)r));
-                    q.urx[top] = (short)__float2int_rz(__fmul_rn(L.hX, (float)(r + 1)));
-                    q.uly[top] = 0; q.bry[top] = (short)L.winH;
-                    q.beg[top] = rb; q.cnt[top] = (unsigned short)cnt;
-                }
-                ++top;
-            }
+            const uint32_t c = cntB[r];
+            if (c == 0) continue;
+            const int ulx = __float2int_rz(__fmul_rn(L.hX, (float)r)), urx = __float2int_rz(__fmul_rn(L.hX, (float)(r + 1)));
+            bndA[top] = make_uint2((uint32_t)ulx, (uint32_t)urx | ((uint32_t)L.winH << 16));
+            cntA[top] = c;
+            rel[r] = (uint32_t)top;
+            ++top;
         }
+        misc[5] = (uint32_t)top;
     }
-    __syncwarp();
+    __syncthreads();
+    int len = (int)misc[5];
+    for (int k = tid; k < n; k += OT_THREADS) nid[k] = (unsigned short)rel[nid[k]];
+    __syncthreads();
+
     const int N = L.N;
-    int size = top;
-    bool finish = false;
-    bool overflow = false;
+    bool finish = false, careful = false, overflow = false;
     while (!finish) {
-        // full pass: split every node with more than one key, list order = from the end
-        const int len = octree_compact(q, top, lane);
-        top = len;
-        const int prevSize = size;
-        if (len + 4 * len > nodeCap) { overflow = true; break; }
-        for (int i = len - 1; i >= 0; --i) {
-            if (q.cnt[i] <= 1) continue;
-            size += octree_split(q, i, &top, keysA, keysB, lane);
-        }
-        int nToExpand = 0;
-        for (int i0 = len; i0 < top; i0 += 32) nToExpand += __popc(__ballot_sync(FULL, i0 + lane < top && q.cnt[i0 + lane] > 1));
-        if (size >= N || size == prevSize) { finish = true; }
-        else if (size + nToExpand * 3 > N) {
-            while (!finish) {
-                const int len2 = octree_compact(q, top, lane);
-                top = len2;
-                const int prev2 = size;
-                // candidates: alive nodes with > 1 key; sort by (nKeys, creation index)
-                int nc = 0;
-                for (int i0 = 0; i0 < len2; i0 += 32) {
-                    const int i = i0 + lane;
-                    const bool e = i < len2 && q.cnt[i] > 1;
-                    const unsigned m = __ballot_sync(FULL, e);
-                    if (e) {
-                        const int p = nc + __popc(m & ((1u << lane) - 1));
-                        if (p < sortCap) sortbuf[p] = ((uint32_t)q.cnt[i] << 16) | (uint32_t)i;
-                    }
-                    nc += __popc(m);
-                }
-                if (nc > sortCap || len2 + 4 * nc > nodeCap || len2 > 0xffff) { overflow = true; finish = true; break; }
-                __syncwarp();
-                int cap2 = 32; while (cap2 < nc) cap2 <<= 1;
-                warp_bitonic_sort(sortbuf, nc, cap2, lane);
-                for (int j = nc - 1; j >= 0; --j) {
-                    const int ni = (int)(sortbuf[j] & 0xffff);
-                    size += octree_split(q, ni, &top, keysA, keysB, lane);
-                    if (size >= N) break;
-                }
-                if (size >= N || size == prev2) finish = true;
+        const int prev = len;
+        // ---- count: keys per quadrant of every node that may split ------------------------------
+        for (int i = tid; i < 4 * len; i += OT_THREADS) cc[i] = 0;
+        if (tid == 0) { misc[0] = 0; misc[2] = 0; misc[3] = 0; misc[4] = 0; }
+        __syncthreads();
+        for (int k0 = 0; k0 < n; k0 += OT_THREADS) {
+            const int k = k0 + tid;
+            uint32_t idx = 0xffffffffu;
+            if (k < n) {
+                const int ni = nid[k];
+                if (cntA[ni] > 1) { int mx, my; idx = 4u * ni + ot_quadrant(bndA[ni], keys[k], mx, my); }
             }
+            const unsigned peers = __match_any_sync(FULL, idx);
+            if (idx != 0xffffffffu && lane == __ffs(peers) - 1) atomicAdd(&cc[idx], (uint32_t)__popc(peers));
         }
-    }
-    if (overflow) { if (lane == 0) { atomicOr(status, 1); *outCount = 0; } return; }
-    // ---- retain the best key of every node, list order = reversed array -----------------------
-    const int len = octree_compact(q, top, lane);
-    if (len > L.kpCap) { if (lane == 0) { atomicOr(status, 2); *outCount = 0; } return; }
-    for (int i0 = 0; i0 < len; i0 += 32) {
-        const int i = i0 + lane;
-        if (i < len) {
-            const int begw = q.beg[i];
-            const uint32_t* src = (begw < 0) ? keysB : keysA;
-            const int b = begw & 0x7fffffff, c = q.cnt[i];
-            uint32_t best = src[b];
-            for (int k = 1; k < c; ++k) { const uint32_t kk = src[b + k]; if ((kk >> 24) > (best >> 24)) best = kk; }
-            outKps[len - 1 - i] = best;
+        __syncthreads();
+        // ---- order ------------------------------------------------------------------------------
+        uint32_t sTotal, cTotal;
+        if (!careful) {
+            // every node with > 1 key splits; children of node len-1 come first
+            uint32_t run = 0;
+            for (int i0 = 0; i0 < len; i0 += OT_THREADS) {
+                const int i = i0 + tid;
+                uint32_t v = 0;
+                if (i < len) {
+                    if (cntA[i] > 1) v = (uint32_t)((cc[4 * i] != 0) + (cc[4 * i + 1] != 0) + (cc[4 * i + 2] != 0) + (cc[4 * i + 3] != 0)) << 16;
+                    else v = 1;
+                }
+                uint32_t tot;
+                const uint32_t incl = block_scan_incl(v, wsum, tot);
+                if (i < len) tmp[i] = run + incl;
+                run += tot;
+            }
+            sTotal = run & 0xffff; cTotal = run >> 16;
+            for (int i = tid; i < len; i += OT_THREADS) {
+                const uint32_t t = tmp[i];
+                if (cntA[i] > 1) rel[i] = cTotal - (t >> 16);
+                else { rel[i] = OT_NOSPLIT; tmp[i] = (t & 0xffff) - 1; }
+            }
+        } else {
+            // candidates = nodes with > 1 key, sorted ascending by (nKeys, array index), processed from the back
+            for (int i = tid; i < len; i += OT_THREADS) {
+                rel[i] = OT_NOSPLIT;
+                if (cntA[i] > 1) { const uint32_t p = atomicAdd(&misc[0], 1u); sortbuf[p] = ((unsigned long long)cntA[i] << 32) | (uint32_t)i; }
+            }
+            __syncthreads();
+            const int nc = (int)misc[0];
+            int cap2 = 1; while (cap2 < nc) cap2 <<= 1;
+            for (int i = nc + tid; i < cap2; i += OT_THREADS) sortbuf[i] = ~0ull;
+            __syncthreads();
+            for (int kk = 2; kk <= cap2; kk <<= 1)
+                for (int j = kk >> 1; j > 0; j >>= 1) {
+                    for (int i = tid; i < cap2; i += OT_THREADS) {
+                        const int l = i ^ j;
+                        if (l > i) {
+                            const unsigned long long x = sortbuf[i], y = sortbuf[l];
+                            if ((x > y) == ((i & kk) == 0)) { sortbuf[i] = y; sortbuf[l] = x; }
+                        }
+                    }
+                    __syncthreads();
+                }
+            // prefix sums in processing order: node p is split iff the node count is still < N before it (:736)
+            uint32_t run = 0;
+            for (int p0 = 0; p0 < nc; p0 += OT_THREADS) {
+                const int p = p0 + tid;
+                uint32_t v = 0, ni = 0;
+                if (p < nc) {
+                    ni = (uint32_t)sortbuf[nc - 1 - p];
+                    const uint32_t nch = (uint32_t)((cc[4 * ni] != 0) + (cc[4 * ni + 1] != 0) + (cc[4 * ni + 2] != 0) + (cc[4 * ni + 3] != 0));
+                    v = (nch - 1) | (nch << 16);
+                }
+                uint32_t tot;
+                const uint32_t incl = block_scan_incl(v, wsum, tot);
+                if (p < nc) {
+                    const uint32_t inc = run + incl, exc = inc - v;
+                    if (len + (int)(exc & 0xffff) < N) {
+                        rel[ni] = exc >> 16;
+                        if (p == nc - 1 || len + (int)(inc & 0xffff) >= N) { misc[2] = inc & 0xffff; misc[3] = inc >> 16; }
+                    }
+                }
+                run += tot;
+            }
+            __syncthreads();
+            uint32_t srun = 0;
+            for (int i0 = 0; i0 < len; i0 += OT_THREADS) {
+                const int i = i0 + tid;
+                const uint32_t v = (i < len && rel[i] == OT_NOSPLIT) ? 1u : 0u;
+                uint32_t tot;
+                const uint32_t incl = block_scan_incl(v, wsum, tot);
+                if (i < len) tmp[i] = srun + incl - 1;
+                srun += tot;
+            }
+            sTotal = srun; cTotal = misc[3];
         }
+        if ((int)(sTotal + cTotal) > NC) { overflow = true; break; }
+        // ---- rebuild: survivors keep their order, children follow in split order ----------------
+        {
+            uint32_t nExp = 0;
+            for (int i = tid; i < len; i += OT_THREADS) {
+                const uint2 b = bndA[i];
+                if (rel[i] == OT_NOSPLIT) {
+                    const uint32_t j = tmp[i];
+                    bndB[j] = b; cntB[j] = cntA[i]; cc[4 * i] = j;
+                } else {
+                    uint32_t w = sTotal + rel[i];
+                    const int ulx = b.x & 0xffff, uly = b.x >> 16, urx = b.y & 0xffff, bry = b.y >> 16;
+                    const int mx = ulx + ((urx - ulx + 1) >> 1), my = uly + ((bry - uly + 1) >> 1);
+                    // creation order n1 (UL), n2 (UR), n3 (BL), n4 (BR), :618-661
+                    const uint32_t c0 = cc[4 * i], c1 = cc[4 * i + 1], c2 = cc[4 * i + 2], c3 = cc[4 * i + 3];
+                    if (c0) { bndB[w] = make_uint2(ulx | (uly << 16), mx | (my << 16));  cntB[w] = c0; cc[4 * i] = w;     nExp += c0 > 1; ++w; }
+                    if (c1) { bndB[w] = make_uint2(mx | (uly << 16), urx | (my << 16));  cntB[w] = c1; cc[4 * i + 1] = w; nExp += c1 > 1; ++w; }
+                    if (c2) { bndB[w] = make_uint2(ulx | (my << 16), mx | (bry << 16));  cntB[w] = c2; cc[4 * i + 2] = w; nExp += c2 > 1; ++w; }
+                    if (c3) { bndB[w] = make_uint2(mx | (my << 16), urx | (bry << 16));  cntB[w] = c3; cc[4 * i + 3] = w; nExp += c3 > 1; ++w; }
+                }
+            }
+            if (nExp) atomicAdd(&misc[4], nExp);
+        }
+        __syncthreads();
+        // ---- relabel the keys ---------------------------------------------------------------------
+        for (int k = tid; k < n; k += OT_THREADS) {
+            const int ni = nid[k];
+            uint32_t j;
+            if (rel[ni] == OT_NOSPLIT) j = cc[4 * ni];
+            else { int mx, my; j = cc[4 * ni + ot_quadrant(bndA[ni], keys[k], mx, my)]; }
+            nid[k] = (unsigned short)j;
+        }
+        const int nToExpand = (int)misc[4];
+        __syncthreads();
+        { uint2* tb = bndA; bndA = bndB; bndB = tb; uint32_t* tc = cntA; cntA = cntB; cntB = tc; }
+        len = (int)(sTotal + cTotal);
+        if (len >= N || len == prev) finish = true;
+        else if (!careful && len + nToExpand * 3 > N) careful = true;      // :667-673
     }
-    if (lane == 0) *outCount = len;
+    if (overflow) { if (tid == 0) { atomicOr(status, 1); *outCount = 0; } return; }
+    if (len > L.kpCap) { if (tid == 0) { atomicOr(status, 2); *outCount = 0; } return; }
+    // ---- retain the best key of every node (:741-760); list order = reversed array ----------------
+    for (int i = tid; i < len; i += OT_THREADS) cc[i] = 0;
+    __syncthreads();
+    for (int k = tid; k < n; k += OT_THREADS) atomicMax(&cc[nid[k]], (keys[k] & 0xff000000u) | (0xffffffu - (uint32_t)k));
+    __syncthreads();
+    for (int i = tid; i < len; i += OT_THREADS) outKps[len - 1 - i] = keys[0xffffffu - (cc[i] & 0xffffffu)];
+    if (tid == 0) *outCount = len;
 }
 
 // =============================================================================================
@@ -1113,14 +1139,25 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
     }
     // K3: quadtree
     {
-        int maxN = 1;
-        for (int l = 0; l < nl; ++l) maxN = std::max(maxN, std::max(g.L[l].N, 4 * g.L[l].nIni));
-        const int nodeCap = 5 * (maxN + 4) + 32;
-        int sortCap = 32; while (sortCap < maxN + 4) sortCap <<= 1;
-        const int smem = nodeCap * (4 + 8 + 2) + 4 + sortCap * 4;
-        if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        octree_kernel<<<nframes * nl, 32, smem, st>>>(g, nframes, h->dCand, h->dCellSeg, h->dLevelCandCount, h->dKeysA, h->dKeysB,
-                                                       h->dLevelKps, h->dLevelKpCount, nodeCap, sortCap, h->dStatus);
+        int NC = 8, cellsMax = 1, candMax = 1;
+        for (int l = 0; l < nl; ++l) { NC = std::max(NC, g.L[l].kpCap); cellsMax = std::max(cellsMax, g.L[l].nCells); candMax = std::max(candMax, g.L[l].candCap); }
+        if (NC > 16383 || candMax >= (1 << 24)) { orbx_set_error("quadtree: %d nodes / %d candidates per level exceed the kernel's index width", NC, candMax); return ORBX_E_CAPACITY; }
+        int P2 = 32; while (P2 < NC) P2 <<= 1;
+        const int cellWords = 2 * cellsMax + 2;
+        const int aliasWords = std::max(2 * P2 + 11 * NC, cellWords);
+        const int fixedBytes = 4 * (aliasWords + NC + 32 + 8);
+        // keys + labels of a level stay in shared memory up to keyCap candidates (6 bytes each); beyond that
+        // the level runs out of the global key buffers
+        int keyCap = std::min((candMax + 63) & ~63, 4096);
+        if (fixedBytes + 6 * keyCap > 200 * 1024) keyCap = std::max(0, (200 * 1024 - fixedBytes) / 6) & ~63;
+        const int smem = fixedBytes + 6 * keyCap;
+        static int smemSet[16] = {0};
+        if (smem > 48 * 1024 && smem > smemSet[h->device]) {
+            ORBX_CUDA(cudaFuncSetAttribute(octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            smemSet[h->device] = smem;
+        }
+        octree_kernel<<<nframes * nl, OT_THREADS, smem, st>>>(g, nframes, h->dCand, h->dCellSeg, h->dKeysA, h->dKeysB,
+                                                               h->dLevelKps, h->dLevelKpCount, NC, P2, cellWords, keyCap, h->dStatus);
         ORBX_COUNT(h, ORBX_STAGE_OCTREE, 1);
         orbx_prof_mark(h, ORBX_STAGE_OCTREE);
     }
