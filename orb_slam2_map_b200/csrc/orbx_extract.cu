@@ -823,7 +823,6 @@ octree_kernel(Geom g, int nframes, const uint32_t* __restrict__ cand, const int2
 // =============================================================================================
 // K4: orientation (IC_Angle) + rotated BRIEF + final keypoint record.  One warp per keypoint.
 // =============================================================================================
-__constant__ int c_umax[16];
 
 __device__ __forceinline__ float fast_atan2_deg(float y, float x)
 {
@@ -851,15 +850,14 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x)
 __global__ void __launch_bounds__(DESC_WARPS * 32)
 describe_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, const u8* __restrict__ blurBase,
                 int nframes, const uint32_t* __restrict__ levelKps, const int* __restrict__ levelKpCount,
-                const int* __restrict__ kpMap, const signed char* __restrict__ pattern,
+                const int* __restrict__ kpMap, const signed char* __restrict__ pattern, const uint32_t* __restrict__ discMask,
                 orbx_keypoint* __restrict__ outKps, u8* __restrict__ outDesc, int* __restrict__ outCount,
                 int* __restrict__ outLevelCount, int firstSlot, int kpCapOut)
 {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    const long long gw = (long long)blockIdx.x * DESC_WARPS + (threadIdx.x >> 5);
-    if (gw >= (long long)nframes * g.kpTotal) return;
-    const int frame = (int)(gw / g.kpTotal), slotk = (int)(gw - (long long)frame * g.kpTotal);
+    const int frame = blockIdx.y, slotk = blockIdx.x * DESC_WARPS + (threadIdx.x >> 5);
+    if (slotk >= g.kpTotal) return;
     const int level = kpMap[slotk];
     const LevelGeom& L = g.L[level];
     const int k = slotk - L.kpOff;
@@ -879,21 +877,34 @@ describe_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, const u8* __r
     int rp;
     if (level == 0) { raw = l0_frame(l0, frame); rp = l0.pitch; }
     else { raw = rawBase + (long long)frame * g.pyrFrameBytes + L.off; rp = L.pitch; }
-    // ---- IC_Angle: lanes = u in [-15,15], loop over the 31 rows of the disc --------------------
-    const int u = lane - 15;
+    // ---- IC_Angle: the 31x31 window as 8 words x 32 rows; lane = (row r of a group of 4, word w), 8 groups.
+    // The window is re-aligned to the keypoint with a funnel shift, so byte j of lane w is column
+    // u = 4w + j - 15 for every keypoint: the disc mask of (lane, group) is a table word and the column
+    // weights are a per-lane constant.  m10 = sum u*I and the row sums come from two IDP.4A per word.
     int m10 = 0, m01 = 0;
-    if (lane < 31) {
-        const u8* center = raw + (long long)py * rp + px + u;
-        // the disc is symmetric: column u holds rows |v| <= umax[|u|].  All 31 loads are issued
-        // before they are consumed (the gather is latency bound otherwise).
-        const int vlim = c_umax[abs(u)];
-        int vals[31];
+    {
+        const int r = lane >> 3, wq = lane & 7;
+        const u8* win = raw + (long long)(py - 15) * rp + (px - 15);
+        const int a = (int)(reinterpret_cast<uintptr_t>(win) & 3);
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(win - a) + wq;
+        const int rpw = rp >> 2, a8 = 8 * a;
+        const int u0 = 4 * wq - 15;
+        const uint32_t Uw = (uint32_t)(u0 & 0xff) | ((uint32_t)((u0 + 1) & 0xff) << 8) | ((uint32_t)((u0 + 2) & 0xff) << 16) | ((uint32_t)((u0 + 3) & 0xff) << 24);
+        uint32_t lo[8], hi[8], M[8];
 #pragma unroll
-        for (int v = -15; v <= 15; ++v) vals[v + 15] = (abs(v) <= vlim) ? (int)center[v * rp] : 0;
-        int colsum = 0;
+        for (int i = 0; i < 8; ++i) {
+            const int row = min(4 * i + r, 30);                 // row 31 does not exist (its mask is 0)
+            const uint32_t* q = wp + row * rpw;
+            lo[i] = q[0]; hi[i] = q[1];
+            M[i] = __ldg(discMask + i * 32 + lane);
+        }
 #pragma unroll
-        for (int v = -15; v <= 15; ++v) { colsum += vals[v + 15]; m01 += v * vals[v + 15]; }
-        m10 = u * colsum;
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t Iw = __funnelshift_r(lo[i], hi[i], a8) & M[i];
+            const int cs = (int)__dp4a(Iw, 0x01010101u, 0u);
+            asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(m10) : "r"(Iw), "r"(Uw));
+            m01 += (4 * i + r - 15) * cs;
+        }
     }
     for (int d = 16; d > 0; d >>= 1) { m10 += __shfl_xor_sync(FULL, m10, d); m01 += __shfl_xor_sync(FULL, m01, d); }
     const float angle = fast_atan2_deg((float)m01, (float)m10);
@@ -1066,7 +1077,6 @@ int orbx_setup_shape(orbx_handle* h, int w, int hgt)
     if (!coef.empty()) ORBX_CUDA(cudaMemcpyAsync(h->dCoef, coef.data(), coef.size() * sizeof(int2), cudaMemcpyHostToDevice, st));
     ORBX_CUDA(cudaMemcpyAsync(h->dBlurTiles, tiles.data(), tiles.size() * sizeof(int), cudaMemcpyHostToDevice, st));
     ORBX_CUDA(cudaMemcpyAsync(h->dKpMap, kpMap.data(), kpMap.size() * sizeof(int), cudaMemcpyHostToDevice, st));
-    ORBX_CUDA(cudaMemcpyToSymbolAsync(c_umax, h->umax, sizeof(int) * 16, 0, cudaMemcpyHostToDevice, st));
     ORBX_CUDA(cudaStreamSynchronize(st));
     h->curW = w; h->curH = hgt;
     h->lastChunkFrames = 0;
@@ -1074,8 +1084,11 @@ int orbx_setup_shape(orbx_handle* h, int w, int hgt)
 }
 
 static signed char* g_dPattern[16] = {nullptr};
+static uint32_t* g_dDiscMask[16] = {nullptr};
 
-static int get_pattern(int device, const signed char** out)
+// device copies of the BRIEF pattern and of the IC_Angle disc masks (per device, shared by all handles:
+// both depend only on PATCH_SIZE = 31)
+static int get_pattern(int device, const int* umax, const signed char** out, const uint32_t** maskOut)
 {
     if (device < 0 || device >= 16) { orbx_set_error("device index %d unsupported", device); return ORBX_E_INVALID; }
     if (!g_dPattern[device]) {
@@ -1083,7 +1096,25 @@ static int get_pattern(int device, const signed char** out)
         ORBX_CUDA(cudaMalloc((void**)&g_dPattern[device], ORBX_PATTERN_LEN));
         ORBX_CUDA(cudaMemcpy(g_dPattern[device], pat, ORBX_PATTERN_LEN, cudaMemcpyHostToDevice));
     }
+    if (!g_dDiscMask[device]) {
+        // word (group i, lane): rows v = 4i + (lane>>3) - 15, columns u = 4*(lane&7) + j - 15;
+        // a pixel is inside the disc iff |v| <= umax[|u|] (IC_Angle, src/ORBextractor.cc:86-100)
+        uint32_t tab[256];
+        for (int i = 0; i < 8; ++i)
+            for (int lane = 0; lane < 32; ++lane) {
+                const int v = 4 * i + (lane >> 3) - 15;
+                uint32_t m = 0;
+                for (int j = 0; j < 4; ++j) {
+                    const int u = 4 * (lane & 7) + j - 15;
+                    if (abs(u) <= 15 && abs(v) <= 15 && abs(v) <= umax[abs(u)]) m |= 0xffu << (8 * j);
+                }
+                tab[i * 32 + lane] = m;
+            }
+        ORBX_CUDA(cudaMalloc((void**)&g_dDiscMask[device], sizeof(tab)));
+        ORBX_CUDA(cudaMemcpy(g_dDiscMask[device], tab, sizeof(tab), cudaMemcpyHostToDevice));
+    }
     *out = g_dPattern[device];
+    *maskOut = g_dDiscMask[device];
     return ORBX_OK;
 }
 
@@ -1093,7 +1124,8 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
     cudaStream_t st = h->stream;
     const int nl = g.nlevels;
     const signed char* dPat = nullptr;
-    int rc = get_pattern(h->device, &dPat);
+    const uint32_t* dDisc = nullptr;
+    int rc = get_pattern(h->device, h->umax, &dPat, &dDisc);
     if (rc) return rc;
     orbx_prof_mark(h, -1);
     // K1a: levels 1..n-1, each from the previous one
@@ -1163,11 +1195,9 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
     }
     // K4: orientation + descriptors + output records
     {
-        const long long warps = (long long)nframes * g.kpTotal;
-        const int blocks = (int)((warps + DESC_WARPS - 1) / DESC_WARPS);
-        describe_kernel<<<blocks, DESC_WARPS * 32, 0, st>>>(g, l0, h->dRaw, h->dBlur, nframes, h->dLevelKps, h->dLevelKpCount,
-                                                             h->dKpMap, dPat, h->dKps, h->dDesc, h->dCount, h->dSlotLevelCount,
-                                                             firstSlot, h->kpCap);
+        describe_kernel<<<dim3((g.kpTotal + DESC_WARPS - 1) / DESC_WARPS, nframes), DESC_WARPS * 32, 0, st>>>(
+            g, l0, h->dRaw, h->dBlur, nframes, h->dLevelKps, h->dLevelKpCount, h->dKpMap, dPat, dDisc, h->dKps, h->dDesc, h->dCount,
+            h->dSlotLevelCount, firstSlot, h->kpCap);
         ORBX_COUNT(h, ORBX_STAGE_DESCRIBE, 1);
         orbx_prof_mark(h, ORBX_STAGE_DESCRIBE);
     }
