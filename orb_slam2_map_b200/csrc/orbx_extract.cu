@@ -353,11 +353,21 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
             const int wshift = nw <= 8 ? 3 : (nw <= 16 ? 4 : 5);
             const int lw = lane & ((1 << wshift) - 1), lr = lane >> wshift, rstep = 32 >> wshift;
             const u8* gp = img + (long long)(c.y0 + lr) * pitch + xa + 4 * lw;
-            for (int y = lr; y < ch; y += rstep, gp += (long long)rstep * pitch)
-                if (lw < nw) {
-                    const uint32_t lo = reinterpret_cast<const uint32_t*>(gp)[0], hi = reinterpret_cast<const uint32_t*>(gp)[1];
-                    reinterpret_cast<uint32_t*>(tile)[y * tw + lw] = __funnelshift_r(lo, hi, sh8);
-                }
+            const long long gstep = (long long)rstep * pitch;
+            // four rows per lane in flight: the loads of a batch are all issued before the first store
+            for (int y = lr; y < ch; y += 4 * rstep, gp += 4 * gstep) {
+                uint32_t lo[4], hi[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (lw < nw && y + k * rstep < ch) {
+                        const uint32_t* q = reinterpret_cast<const uint32_t*>(gp + k * gstep);
+                        lo[k] = __ldg(q); hi[k] = __ldg(q + 1);
+                    }
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (lw < nw && y + k * rstep < ch)
+                        reinterpret_cast<uint32_t*>(tile)[(y + k * rstep) * tw + lw] = __funnelshift_r(lo[k], hi[k], sh8);
+            }
         }
         // zero the score tile ((dh+2) x scorePitch)
         for (int i = lane; i < ((dh + 2) * scorePitch) >> 2; i += 32) reinterpret_cast<uint32_t*>(score)[i] = 0;
@@ -1154,7 +1164,7 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
     // K2: FAST
     ORBX_CUDA(cudaMemsetAsync(h->dLevelCandCount, 0, (size_t)nframes * nl * sizeof(unsigned), st));
     {
-        const int tilePitch = ((g.cwMax + 6 + 7) & ~7) + 16;    // rows 8-byte aligned; +16: the packed pre-test reads whole words past the cell
+        const int tilePitch = (g.cwMax + 9 + 7) & ~7;          // rows 8-byte aligned; the packed pre-test reads whole words up to byte cw+8
         const int scorePitch = (g.cwMax - 4 + 3) & ~3;
         const int maskBytes = 8 * (g.chMax - 6);                // one 64-bit pre-test mask per detectable row
         int warpSmem = tilePitch * g.chMax + scorePitch * (g.chMax - 4) + maskBytes + 2 * (g.cwMax - 6) * (g.chMax - 6);
