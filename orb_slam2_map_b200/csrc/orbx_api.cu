@@ -142,9 +142,9 @@ int orbx_create(const orbx_params* params, int max_width, int max_height, int ch
 {
     if (!params || !out) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
     if (params->nlevels < 1 || params->nlevels > ORBX_MAX_LEVELS || params->nfeatures < 1 ||
-        params->scale_factor <= 1.0f || params->min_th_fast < 1 || params->ini_th_fast < params->min_th_fast ||
-        params->ini_th_fast > 254) {
-        orbx_set_error("unsupported ORBextractor parameters (nlevels 1..%d, scale>1, 1<=minTh<=iniTh<255)", ORBX_MAX_LEVELS);
+        params->scale_factor <= 1.0f || params->min_th_fast < 1 || params->min_th_fast > 254 ||
+        params->ini_th_fast < 1 || params->ini_th_fast > 254) {
+        orbx_set_error("unsupported ORBextractor parameters (nlevels 1..%d, scale>1, 1<=minTh,iniTh<255)", ORBX_MAX_LEVELS);
         return ORBX_E_INVALID;
     }
     if (max_width < 64 || max_height < 64 || max_width > 4000 || max_height > 4000 || chunk_frames < 1 || result_slots < 1) {

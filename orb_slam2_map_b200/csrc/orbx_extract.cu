@@ -1192,6 +1192,7 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
         // the level runs out of the global key buffers
         int keyCap = std::min((candMax + 63) & ~63, 4096);
         if (fixedBytes + 6 * keyCap > 200 * 1024) keyCap = std::max(0, (200 * 1024 - fixedBytes) / 6) & ~63;
+        if (const char* e = getenv("ORBX_OCTREE_KEYCAP")) keyCap = std::max(0, std::min(keyCap, atoi(e)));   // tests: force the global-memory path
         const int smem = fixedBytes + 6 * keyCap;
         static int smemSet[16] = {0};
         if (smem > 48 * 1024 && smem > smemSet[h->device]) {

@@ -125,6 +125,48 @@ def test_params_variants():
         ex.close()
 
 
+def test_threshold_order_variants():
+    """cv::FAST(iniThFAST) first, cv::FAST(minThFAST) only for empty cells (ORBextractor.cc:809-816) — also when
+    ini <= min, and above the 7-bit range of the byte-packed pre-test"""
+    img = _image(640, 480, seed=21)
+    for (it, mt) in [(5, 7), (7, 7), (60, 3), (126, 100), (140, 130)]:
+        ex = capi.Extractor(1000, 1.2, 8, it, mt, max_width=640, max_height=480)
+        orc = O.Extractor(1000, 1.2, 8, it, mt)
+        ko, do = orc.extract(img)
+        kg, dg = ex.extract(img)
+        for l in range(8):
+            assert np.array_equal(ex.candidates(0, l), orc.candidates(l)), f"candidates level {l} ini={it} min={mt}"
+        _compare_full(kg, dg, ko, do)
+        ex.close()
+
+
+def test_octree_global_key_path(monkeypatch):
+    """levels with more candidates than the shared-memory key capacity run out of the global key buffers"""
+    monkeypatch.setenv("ORBX_OCTREE_KEYCAP", "64")
+    rng = np.random.default_rng(9)
+    for img in (_image(640, 480, seed=31), rng.integers(0, 256, (480, 640), dtype=np.uint8)):
+        ex = capi.Extractor(max_width=640, max_height=480)
+        orc = O.Extractor()
+        ko, do = orc.extract(img)
+        kg, dg = ex.extract(img)
+        _compare_full(kg, dg, ko, do)
+        ex.close()
+
+
+def test_tall_and_wide_images():
+    """several quadtree roots (wide) / a single root with tall cells (tall), small levels vanish"""
+    for (w, h, nf) in [(1200, 160, 800), (160, 900, 600), (97, 83, 200)]:
+        img = _image(w, h, seed=w * 3 + h)
+        ex = capi.Extractor(nfeatures=nf, max_width=w, max_height=h)
+        orc = O.Extractor(nfeatures=nf)
+        ko, do = orc.extract(img)
+        kg, dg = ex.extract(img)
+        for l in range(8):
+            assert np.array_equal(ex.candidates(0, l), orc.candidates(l)), f"candidates level {l} {w}x{h}"
+        _compare_full(kg, dg, ko, do)
+        ex.close()
+
+
 def test_empty_image_is_silent():
     ex = capi.Extractor()
     n = C.c_int(-7)
