@@ -522,6 +522,17 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = world * F * args.steps / float(t.item())
     h2d = F * W * H
+    # the same pinned input copied alone: the PCIe bound of the end-to-end number (images are the input, they must cross)
+    pcie_dst = torch.empty((F, H, W), dtype=torch.uint8, device=dev)
+    pcie_dst.copy_(host, non_blocking=True)
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    pcie_dst.copy_(host, non_blocking=True)
+    ev1.record()
+    torch.cuda.synchronize()
+    h2d_gbs = h2d / (ev0.elapsed_time(ev1) * 1e-3) / 1e9
+    del pcie_dst
     d2h = kp_out.nbytes + de_out.nbytes + cnt_out.nbytes + m12_out.nbytes + nm_out.nbytes + 8
 
     # ---- roofline of the dominant kernel ----------------------------------------------------------
@@ -559,7 +570,8 @@ def main():
                    "frames_per_step_per_gpu": F, "chunk_frames": args.chunk, "keypoints_per_frame": nkp,
                    "l2_policy": f"inputs ({F * W * H / 1e9:.2f} GB per step) larger than L2", "sharding": "frames by rank, no collective"},
         "clocks": clk,
-        "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "h2d_gbs_measured": h2d_gbs, "pcie_bound_frames_s": world * h2d_gbs * 1e9 / (W * H)},
         "gpu_launches": int(sum(stage_launches.values())),
         "roofline": roofline,
         "path_roofline": {"algorithmic_bytes_per_frame": ab["total"], "achieved": path_gbs, "peak": peak,

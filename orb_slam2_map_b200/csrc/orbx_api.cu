@@ -294,8 +294,12 @@ int orbx_extract_batch_to_host(orbx_handle* h, const uint8_t* images, size_t fra
         ORBX_CUDA(cudaEventDestroy(evStart));
     }
     int chunkNo = 0;
-    for (int f0 = 0; f0 < nframes; f0 += h->chunkFrames, ++chunkNo) {
-        const int nf = std::min(h->chunkFrames, nframes - f0);
+    for (int f0 = 0, nf = 0; f0 < nframes; f0 += nf, ++chunkNo) {
+        // host images: ramp the first two chunks (1/4, 1/2 of a chunk) so that less of the first
+        // host->device copy is exposed before the kernels start
+        int cf = h->chunkFrames;
+        if (!direct && nframes > h->chunkFrames) cf = chunkNo == 0 ? std::max(1, cf / 4) : (chunkNo == 1 ? std::max(1, cf / 2) : cf);
+        nf = std::min(cf, nframes - f0);
         const uint8_t* src = images + (size_t)f0 * frame_stride;
         Level0 l0;
         l0.base1 = nullptr; l0.stereo = 0;
