@@ -559,13 +559,13 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
 // Keys and labels live in shared memory when the level has at most `keyCap` candidates, otherwise
 // in the (L2-resident) key buffers.
 // =============================================================================================
-#define OT_THREADS 128
 #define OT_NOSPLIT 0xffffffffu
 
 __device__ __forceinline__ int key_x(uint32_t k) { return k & 0xfff; }
 __device__ __forceinline__ int key_y(uint32_t k) { return (k >> 12) & 0xfff; }
 
 // inclusive scan over the block (all threads call it); total = block sum
+template <int OT_THREADS>
 __device__ __forceinline__ uint32_t block_scan_incl(uint32_t v, uint32_t* wsum, uint32_t& total)
 {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -589,6 +589,7 @@ __device__ __forceinline__ int ot_quadrant(uint2 b, uint32_t key, int& mx, int& 
     return (key_x(key) >= mx ? 1 : 0) | (key_y(key) >= my ? 2 : 0);
 }
 
+template <int OT_THREADS>
 __global__ void __launch_bounds__(OT_THREADS)
 octree_kernel(Geom g, int nframes, const uint32_t* __restrict__ cand, const int2* __restrict__ cellSeg,
               uint32_t* __restrict__ keysAbase, uint32_t* __restrict__ keysBbase, uint32_t* __restrict__ levelKps,
@@ -633,7 +634,7 @@ octree_kernel(Geom g, int nframes, const uint32_t* __restrict__ cand, const int2
             int2 sg = make_int2(0, 0);
             if (c < L.nCells) sg = seg[c];
             uint32_t tot;
-            const uint32_t incl = block_scan_incl((uint32_t)sg.y, wsum, tot);
+            const uint32_t incl = block_scan_incl<OT_THREADS>((uint32_t)sg.y, wsum, tot);
             if (c < L.nCells) { segStart[c] = carry + incl - (uint32_t)sg.y; segSrc[c] = (uint32_t)sg.x; }
             carry += tot;
         }
@@ -715,7 +716,7 @@ octree_kernel(Geom g, int nframes, const uint32_t* __restrict__ cand, const int2
                     else v = 1;
                 }
                 uint32_t tot;
-                const uint32_t incl = block_scan_incl(v, wsum, tot);
+                const uint32_t incl = block_scan_incl<OT_THREADS>(v, wsum, tot);
                 if (i < len) tmp[i] = run + incl;
                 run += tot;
             }
@@ -758,7 +759,7 @@ octree_kernel(Geom g, int nframes, const uint32_t* __restrict__ cand, const int2
                     v = (nch - 1) | (nch << 16);
                 }
                 uint32_t tot;
-                const uint32_t incl = block_scan_incl(v, wsum, tot);
+                const uint32_t incl = block_scan_incl<OT_THREADS>(v, wsum, tot);
                 if (p < nc) {
                     const uint32_t inc = run + incl, exc = inc - v;
                     if (len + (int)(exc & 0xffff) < N) {
@@ -774,7 +775,7 @@ octree_kernel(Geom g, int nframes, const uint32_t* __restrict__ cand, const int2
                 const int i = i0 + tid;
                 const uint32_t v = (i < len && rel[i] == OT_NOSPLIT) ? 1u : 0u;
                 uint32_t tot;
-                const uint32_t incl = block_scan_incl(v, wsum, tot);
+                const uint32_t incl = block_scan_incl<OT_THREADS>(v, wsum, tot);
                 if (i < len) tmp[i] = srun + incl - 1;
                 srun += tot;
             }
@@ -1190,17 +1191,21 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
         const int fixedBytes = 4 * (aliasWords + NC + 32 + 8);
         // keys + labels of a level stay in shared memory up to keyCap candidates (6 bytes each); beyond that
         // the level runs out of the global key buffers
-        int keyCap = std::min((candMax + 63) & ~63, 4096);
+        // CTA width and shared-memory key capacity follow the per-level quota: more features per level means
+        // more candidates per level (640x480/1000: ~2.5 k at level 0; 1920x1080/5000: ~18 k)
+        const int threads = NC <= 256 ? 128 : (NC <= 512 ? 256 : 512);
+        int keyCap = std::min((candMax + 63) & ~63, threads == 128 ? 4096 : (threads == 256 ? 8192 : 24576));
         if (fixedBytes + 6 * keyCap > 200 * 1024) keyCap = std::max(0, (200 * 1024 - fixedBytes) / 6) & ~63;
         if (const char* e = getenv("ORBX_OCTREE_KEYCAP")) keyCap = std::max(0, std::min(keyCap, atoi(e)));   // tests: force the global-memory path
         const int smem = fixedBytes + 6 * keyCap;
-        static int smemSet[16] = {0};
-        if (smem > 48 * 1024 && smem > smemSet[h->device]) {
-            ORBX_CUDA(cudaFuncSetAttribute(octree_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-            smemSet[h->device] = smem;
-        }
-        octree_kernel<<<nframes * nl, OT_THREADS, smem, st>>>(g, nframes, h->dCand, h->dCellSeg, h->dKeysA, h->dKeysB,
-                                                               h->dLevelKps, h->dLevelKpCount, NC, P2, cellWords, keyCap, h->dStatus);
+        auto launch = [&](auto kern) -> int {
+            if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+            kern<<<nframes * nl, threads, smem, st>>>(g, nframes, h->dCand, h->dCellSeg, h->dKeysA, h->dKeysB, h->dLevelKps,
+                                                      h->dLevelKpCount, NC, P2, cellWords, keyCap, h->dStatus);
+            return ORBX_OK;
+        };
+        rc = threads == 128 ? launch(octree_kernel<128>) : (threads == 256 ? launch(octree_kernel<256>) : launch(octree_kernel<512>));
+        if (rc) return rc;
         ORBX_COUNT(h, ORBX_STAGE_OCTREE, 1);
         orbx_prof_mark(h, ORBX_STAGE_OCTREE);
     }
