@@ -474,14 +474,18 @@ __device__ __forceinline__ int reflect101i(int i, int n)
 #define STEREO_THREADS 256
 #define STEREO_SPLITS 8           // CTAs per pair (left keypoints are split; the median cull is a second kernel)
 __global__ void __launch_bounds__(STEREO_THREADS)
-stereo_match_kernel(FrameStore fs, int firstSlot, PyrView pv, float bf, float fx, int rightCap,
+stereo_match_kernel(FrameStore fs, int firstSlot, PyrView pv, float bf, float fx, int rightCap, int listCap,
                     float* __restrict__ uRightOut, float* __restrict__ depthOut, int* __restrict__ sadScratch,
                     unsigned long long* __restrict__ ncompares)
 {
     extern __shared__ __align__(16) unsigned char smraw[];
-    int* rRows = reinterpret_cast<int*>(smraw);                 // minr | maxr<<16 (biased by 4096)
-    float* rX = reinterpret_cast<float*>(rRows + rightCap);
-    u8* rOct = reinterpret_cast<u8*>(rX + rightCap);
+    __shared__ int sPart[STEREO_THREADS / 32], sTotal;
+    const int nRows = pv.h[0];
+    // vRowIndices (src/Frame.cc:478-492) as a CSR table in shared memory: rowEnd[r] = end of row r's list
+    int* rowEnd = reinterpret_cast<int*>(smraw);
+    float* rX = reinterpret_cast<float*>(rowEnd + ((nRows + 4) & ~3));
+    unsigned short* rowList = reinterpret_cast<unsigned short*>(rX + rightCap);
+    u8* rOct = reinterpret_cast<u8*>(rowList + listCap);
     const int pair = blockIdx.x, split = blockIdx.y;
     const int sL = firstSlot + 2 * pair, sR = sL + 1;
     const int N = min(fs.count[sL], fs.cap), Nr = min(min(fs.count[sR], fs.cap), rightCap);
@@ -495,17 +499,48 @@ stereo_match_kernel(FrameStore fs, int firstSlot, PyrView pv, float bf, float fx
     float* zOut = depthOut + (size_t)pair * fs.cap;
     int* sad = sadScratch + (size_t)pair * fs.cap;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int nRows = pv.h[0];
+    for (int r = tid; r < nRows; r += STEREO_THREADS) rowEnd[r] = 0;
+    if (split == 0)
+        for (int i = N + tid; i < fs.cap; i += STEREO_THREADS) { uOut[i] = -1.f; zOut[i] = -1.f; }   // unused tail
+    __syncthreads();
+    // rows minr..maxr of every right keypoint (clipped to the image), r = 2 * scale[octave]
+    auto row_range = [&](const orbx_keypoint& kp, int& minr, int& maxr) {
+        const float r = __fmul_rn(2.0f, pv.scale[kp.octave]);
+        maxr = min((int)ceilf(__fadd_rn(kp.y, r)), nRows - 1);
+        minr = max((int)floorf(__fsub_rn(kp.y, r)), 0);
+    };
     for (int i = tid; i < Nr; i += STEREO_THREADS) {
         const orbx_keypoint kp = kR[i];
-        const float r = __fmul_rn(2.0f, pv.scale[kp.octave]);
-        const int maxr = (int)ceilf(__fadd_rn(kp.y, r)), minr = (int)floorf(__fsub_rn(kp.y, r));
-        rRows[i] = (min(max(minr, -4096), 28000) + 4096) | ((min(max(maxr, -4096), 28000) + 4096) << 16);
+        int minr, maxr;
+        row_range(kp, minr, maxr);
+        for (int r = minr; r <= maxr; ++r) atomicAdd(&rowEnd[r], 1);
         rX[i] = kp.x;
         rOct[i] = (u8)kp.octave;
     }
-    if (split == 0)
-        for (int i = N + tid; i < fs.cap; i += STEREO_THREADS) { uOut[i] = -1.f; zOut[i] = -1.f; }   // unused tail
+    __syncthreads();
+    {   // exclusive scan of the row counts: thread t owns a contiguous run of rows
+        const int per = (nRows + STEREO_THREADS - 1) / STEREO_THREADS;
+        const int r0 = min(tid * per, nRows), r1 = min(r0 + per, nRows);
+        int sum = 0;
+        for (int r = r0; r < r1; ++r) sum += rowEnd[r];
+        int incl = sum;
+        for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += v; }
+        if (lane == 31) sPart[wid] = incl;
+        __syncthreads();
+        int off = 0, tot = 0;
+        for (int w = 0; w < STEREO_THREADS / 32; ++w) { const int v = sPart[w]; if (w < wid) off += v; tot += v; }
+        if (tid == 0) sTotal = tot;
+        int run = off + incl - sum;
+        for (int r = r0; r < r1; ++r) { const int c = rowEnd[r]; rowEnd[r] = run; run += c; }
+    }
+    __syncthreads();
+    const bool useRows = sTotal <= listCap;          // otherwise (pathological scales) every right keypoint is scanned
+    if (useRows)
+        for (int i = tid; i < Nr; i += STEREO_THREADS) {
+            int minr, maxr;
+            row_range(kR[i], minr, maxr);
+            for (int r = minr; r <= maxr; ++r) rowList[atomicAdd(&rowEnd[r], 1)] = (unsigned short)i;   // cursor ends at the row's end
+        }
     __syncthreads();
     const float mb = __fdiv_rn(bf, fx);
     const float minD = -3.f, maxD = __fdiv_rn(bf, mb);
@@ -520,10 +555,11 @@ stereo_match_kernel(FrameStore fs, int firstSlot, PyrView pv, float bf, float fx
             uint32_t q[8];
             load_desc(q, dL + (size_t)iL * 32);
             unsigned best = ((unsigned)ORBX_TH_HIGH << 16);
-            const int rowb = row + 4096;
-            for (int iR = lane; iR < Nr; iR += 32) {
-                const int rr = rRows[iR];
-                if (rowb < (rr & 0xffff) || rowb > (rr >> 16)) continue;
+            const int jBeg = useRows ? (row > 0 ? rowEnd[row - 1] : 0) : 0, jEnd = useRows ? rowEnd[row] : Nr;
+            for (int j = jBeg + lane; j < jEnd; j += 32) {
+                int iR = j;
+                if (useRows) iR = rowList[j];
+                else { int minr, maxr; row_range(kR[iR], minr, maxr); if (row < minr || row > maxr) continue; }
                 const int o = rOct[iR];
                 if (o < kp.octave - 1 || o > kp.octave + 1) continue;
                 const float x = rX[iR];
@@ -550,22 +586,40 @@ stereo_match_kernel(FrameStore fs, int firstSlot, PyrView pv, float bf, float fx
                     const u8* pl = pv.base[0][lvl] + (long long)pair * pv.pairStride[0][lvl];
                     const u8* pr = pv.base[1][lvl] + (long long)pair * pv.pairStride[1][lvl];
                     const int pitL = pv.pitch[0][lvl], pitR = pv.pitch[1][lvl];
-                    const int cL = pl[(long long)reflect101i(cvL, lh) * pitL + reflect101i(cuL, lw)];
-                    int cR[11];
-#pragma unroll
-                    for (int s = 0; s < 11; ++s) cR[s] = pr[(long long)reflect101i(cvL, lh) * pitR + reflect101i(cuR + s - L, lw)];
                     int acc[11];
 #pragma unroll
                     for (int s = 0; s < 11; ++s) acc[s] = 0;
-                    for (int p = lane; p < 121; p += 32) {
-                        const int dy = p / 11 - w, dx = p % 11 - w;
-                        const int yy = reflect101i(cvL + dy, lh);
-                        const int a = (int)pl[(long long)yy * pitL + reflect101i(cuL + dx, lw)] - cL;
-                        const u8* rrow = pr + (long long)yy * pitR;
+                    if (cuL >= w && cuL + w < lw && cvL >= w && cvL + w < lh && cuR >= w + L && cuR + w + L < lw) {
+                        // both windows inside the level (always, for keypoints the extractor produced): plain
+                        // addressing, |(a - cL) - (b - cR_s)| = |(a + (cR_s - cL)) - b| as one add + one SAD
+                        const u8* lc = pl + (long long)cvL * pitL + cuL;
+                        const u8* rc = pr + (long long)cvL * pitR + cuR - L;
+                        const int cL = lc[0];
+                        int kS[11];
 #pragma unroll
-                        for (int s = 0; s < 11; ++s) {
-                            const int b = (int)rrow[reflect101i(cuR + s - L + dx, lw)] - cR[s];
-                            acc[s] += abs(a - b);
+                        for (int s = 0; s < 11; ++s) kS[s] = (int)rc[s] - cL;
+                        for (int p = lane; p < 121; p += 32) {
+                            const int dy = p / 11 - w, dx = p - (dy + w) * 11 - w;
+                            const int a = lc[dy * pitL + dx];
+                            const u8* rq = rc + dy * pitR + dx;
+#pragma unroll
+                            for (int s = 0; s < 11; ++s) acc[s] = (int)__sad(a + kS[s], (int)rq[s], (unsigned)acc[s]);
+                        }
+                    } else {
+                        const int cL = pl[(long long)reflect101i(cvL, lh) * pitL + reflect101i(cuL, lw)];
+                        int cR[11];
+#pragma unroll
+                        for (int s = 0; s < 11; ++s) cR[s] = pr[(long long)reflect101i(cvL, lh) * pitR + reflect101i(cuR + s - L, lw)];
+                        for (int p = lane; p < 121; p += 32) {
+                            const int dy = p / 11 - w, dx = p % 11 - w;
+                            const int yy = reflect101i(cvL + dy, lh);
+                            const int a = (int)pl[(long long)yy * pitL + reflect101i(cuL + dx, lw)] - cL;
+                            const u8* rrow = pr + (long long)yy * pitR;
+#pragma unroll
+                            for (int s = 0; s < 11; ++s) {
+                                const int b = (int)rrow[reflect101i(cuR + s - L + dx, lw)] - cR[s];
+                                acc[s] += abs(a - b);
+                            }
                         }
                     }
 #pragma unroll
@@ -723,10 +777,14 @@ static int launch_stereo(const FrameStore& fs, int firstSlot, int npairs, const 
                          int rightCap, float* uRight, float* depth, int* sadScratch, unsigned long long* ncmp,
                          cudaStream_t st)
 {
-    const int smem = rightCap * 9 + 16;
-    if (smem > 200 * 1024) { orbx_set_error("more than %d right keypoints per frame unsupported by the stereo matcher", 200 * 1024 / 9); return ORBX_E_CAPACITY; }
+    // row table: (rows + 4) ints, then per right keypoint x (4 B), octave (1 B) and room for 10 row entries (2 B each;
+    // the standard 8-level pyramid needs 7.8 on average) — beyond that the kernel falls back to scanning every keypoint
+    int listCap = rightCap * 10;
+    int smem = ((pv.h[0] + 4) & ~3) * 4 + rightCap * 5 + listCap * 2 + 16;
+    if (smem > 200 * 1024) { listCap = 0; smem = ((pv.h[0] + 4) & ~3) * 4 + rightCap * 5 + 16; }
+    if (smem > 200 * 1024) { orbx_set_error("more than %d right keypoints per frame unsupported by the stereo matcher", 180 * 1024 / 5); return ORBX_E_CAPACITY; }
     if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(stereo_match_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    stereo_match_kernel<<<dim3(npairs, STEREO_SPLITS), STEREO_THREADS, smem, st>>>(fs, firstSlot, pv, bf, fx, rightCap, uRight, depth, sadScratch, ncmp);
+    stereo_match_kernel<<<dim3(npairs, STEREO_SPLITS), STEREO_THREADS, smem, st>>>(fs, firstSlot, pv, bf, fx, rightCap, listCap, uRight, depth, sadScratch, ncmp);
     stereo_cull_kernel<<<npairs, STEREO_THREADS, 0, st>>>(fs, firstSlot, uRight, depth, sadScratch);
     return ORBX_OK;
 }
