@@ -323,9 +323,8 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
 {
     extern __shared__ __align__(16) u8 smem[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const long long gw = (long long)blockIdx.x * FAST_WARPS + wid;
-    if (gw >= (long long)nframes * g.ncells) return;
-    const int frame = (int)(gw / g.ncells), ci = (int)(gw - (long long)frame * g.ncells);
+    const int frame = blockIdx.y, ci = blockIdx.x * FAST_WARPS + wid;
+    if (ci >= g.ncells) return;
     const Cell c = cells[ci];
     const LevelGeom& L = g.L[c.level];
     const u8* img;
@@ -334,9 +333,11 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
     else { img = rawBase + (long long)frame * g.pyrFrameBytes + L.off; pitch = L.pitch; }
 
     u8* tile = smem + (size_t)wid * warpSmem;
-    u8* score = tile + (size_t)tilePitch * g.chMax;
-    uint32_t* rowMask = reinterpret_cast<uint32_t*>(score + (size_t)scorePitch * (g.chMax - 4));    // 64 bits per detectable row
-    unsigned short* list = reinterpret_cast<unsigned short*>(rowMask + 2 * (g.chMax - 6));
+    u8* score = tile + (((size_t)tilePitch * g.chMax + 15) & ~(size_t)15);
+    const int scoreBytes = (scorePitch * (g.chMax - 4) + 15) & ~15;
+    uint32_t* rowMask = reinterpret_cast<uint32_t*>(score + scoreBytes);    // 64 bits per detectable row
+    const int zeroVecs = (scoreBytes + 8 * (g.chMax - 6) + 15) >> 4;
+    unsigned short* list = reinterpret_cast<unsigned short*>(score + 16 * zeroVecs);
 
     const int cw = c.cw, ch = c.ch;
     const int dw = cw - 6, dh = ch - 6;               // detectable interior
@@ -350,28 +351,32 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
         {
             const int xa = c.x0 & ~3, sh8 = 8 * (c.x0 - xa);
             const int nw = (cw + 3) >> 2;
-            const int wshift = nw <= 8 ? 3 : (nw <= 16 ? 4 : 5);
-            const int lw = lane & ((1 << wshift) - 1), lr = lane >> wshift, rstep = 32 >> wshift;
-            const u8* gp = img + (long long)(c.y0 + lr) * pitch + xa + 4 * lw;
-            const long long gstep = (long long)rstep * pitch;
-            // four rows per lane in flight: the loads of a batch are all issued before the first store
-            for (int y = lr; y < ch; y += 4 * rstep, gp += 4 * gstep) {
+            // (row, word) pairs flattened over the lanes; row = idx / nw by a 16-bit reciprocal (exact for idx < 3855)
+            const uint32_t inv = (65536u + nw - 1) / nw;
+            const u8* g0 = img + (long long)c.y0 * pitch + xa;
+            const int total = nw * ch;
+            // four words per lane in flight: the loads of a batch are all issued before the first store
+            for (int i0 = lane; i0 < total; i0 += 128) {
                 uint32_t lo[4], hi[4];
+                int dst[4];
 #pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    if (lw < nw && y + k * rstep < ch) {
-                        const uint32_t* q = reinterpret_cast<const uint32_t*>(gp + k * gstep);
+                for (int k = 0; k < 4; ++k) {
+                    const int idx = i0 + 32 * k;
+                    if (idx < total) {
+                        const int y = (int)((idx * inv) >> 16), lw = idx - y * nw;
+                        const uint32_t* q = reinterpret_cast<const uint32_t*>(g0 + y * pitch) + lw;
                         lo[k] = __ldg(q); hi[k] = __ldg(q + 1);
+                        dst[k] = y * tw + lw;
                     }
+                }
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
-                    if (lw < nw && y + k * rstep < ch)
-                        reinterpret_cast<uint32_t*>(tile)[(y + k * rstep) * tw + lw] = __funnelshift_r(lo[k], hi[k], sh8);
+                    if (i0 + 32 * k < total) reinterpret_cast<uint32_t*>(tile)[dst[k]] = __funnelshift_r(lo[k], hi[k], sh8);
             }
         }
         // zero the score tile ((dh+2) x scorePitch)
-        for (int i = lane; i < ((dh + 2) * scorePitch) >> 2; i += 32) reinterpret_cast<uint32_t*>(score)[i] = 0;
-        for (int i = lane; i < 2 * dh; i += 32) rowMask[i] = 0;
+        // (score and rowMask are contiguous and 16-byte aligned: one run of 16-byte stores covers both)
+        for (int i = lane; i < zeroVecs; i += 32) reinterpret_cast<uint4*>(score)[i] = make_uint4(0, 0, 0, 0);
         __syncwarp();
         // The reference calls cv::FAST(iniThFAST) and, only when that returns nothing, cv::FAST(minThFAST)
         // (ORBextractor.cc:809-816).  Same here: most cells are done after the cheap high-threshold pass.
@@ -1168,13 +1173,12 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
         const int tilePitch = (g.cwMax + 9 + 7) & ~7;          // rows 8-byte aligned; the packed pre-test reads whole words up to byte cw+8
         const int scorePitch = (g.cwMax - 4 + 3) & ~3;
         const int maskBytes = 8 * (g.chMax - 6);                // one 64-bit pre-test mask per detectable row
-        int warpSmem = tilePitch * g.chMax + scorePitch * (g.chMax - 4) + maskBytes + 2 * (g.cwMax - 6) * (g.chMax - 6);
+        int warpSmem = ((tilePitch * g.chMax + 15) & ~15) + ((((scorePitch * (g.chMax - 4) + 15) & ~15) + maskBytes + 15) & ~15) +
+                       2 * (g.cwMax - 6) * (g.chMax - 6);
         warpSmem = (warpSmem + 15) & ~15;
         const int smem = warpSmem * FAST_WARPS;
         if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        const long long warps = (long long)nframes * g.ncells;
-        const int blocks = (int)((warps + FAST_WARPS - 1) / FAST_WARPS);
-        fast_cells_kernel<<<blocks, FAST_WARPS * 32, smem, st>>>(g, h->dCells, l0, h->dRaw, nframes, h->params.min_th_fast,
+        fast_cells_kernel<<<dim3((g.ncells + FAST_WARPS - 1) / FAST_WARPS, nframes), FAST_WARPS * 32, smem, st>>>(g, h->dCells, l0, h->dRaw, nframes, h->params.min_th_fast,
                                                                   h->params.ini_th_fast, h->dCand, h->dCellSeg, h->dLevelCandCount,
                                                                   tilePitch, scorePitch, warpSmem);
         ORBX_COUNT(h, ORBX_STAGE_FAST, 1);
