@@ -238,6 +238,53 @@ int orbm_knn2_set_variant(int variant);
 int orbm_knn2_merge_device(const uint16_t* part_dist, const int32_t* part_idx, int nparts,
                            int64_t nq, uint16_t* out_dist, int32_t* out_idx, void* stream);
 
+/* ================================================================================================
+ * RGB-D frame front: the steps of Tracking::GrabImageRGBD / Frame::Frame(RGB-D)
+ * either side of ORBextractor::operator().  Arithmetic = OpenCV 4.13 (oracle/frame_oracle.cpp).
+ * ================================================================================================ */
+
+/* mK (fx, fy, cx, cy) and mDistCoef (k1, k2, p1, p2, k3) as CV_32F (src/Tracking.cc:60-80), mbf */
+typedef struct orbx_camera {
+    float fx, fy, cx, cy;
+    float k1, k2, p1, p2, k3;
+    float bf;
+} orbx_camera;
+
+/* cv::cvtColor(RGB|BGR|RGBA|BGRA -> GRAY) of src/Tracking.cc:308-321 (and :265-290), 8-bit, batched.
+ * channels 3 or 4; rgb_order != 0 for RGB(A) (mbRGB), 0 for BGR(A).  color/gray are host pointers, or device
+ * pointers when on_device != 0.  Strides in bytes. */
+int orbx_cvt_gray(orbx_handle* h, const uint8_t* color, int channels, int rgb_order, size_t frame_stride,
+                  size_t row_stride, int width, int height, int nframes, int on_device, uint8_t* gray,
+                  size_t gray_frame_stride, size_t gray_row_stride);
+
+/* imDepth.convertTo(imDepth, CV_32F, mDepthMapFactor) of src/Tracking.cc:324-327 for a 16-bit depth map
+ * (strides in ELEMENTS); host pointers, or device pointers when on_device != 0. */
+int orbx_depth_to_float(orbx_handle* h, const uint16_t* depth, size_t row_stride, int width, int height, float factor,
+                        int on_device, float* out, size_t out_row_stride);
+
+/* cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK) as Frame::UndistortKeyPoints calls it
+ * (src/Frame.cc:404-434): n points (x, y) in, n points out; host arrays, computed on the device. */
+int orbx_undistort_points(orbx_handle* h, const float* xy, int n, const orbx_camera* cam, float* xy_out);
+
+/* Frame::ComputeImageBounds (src/Frame.cc:436-464): bounds = mnMinX, mnMaxX, mnMinY, mnMaxY */
+int orbx_image_bounds(orbx_handle* h, int cols, int rows, const orbx_camera* cam, float bounds[4]);
+
+/* Batched Frame::Frame(imGray, imDepth, ...) front (src/Frame.cc:136-189) with GrabImageRGBD's conversions:
+ * colour -> gray (channels 1 = already gray), ExtractORB, UndistortKeyPoints, ComputeStereoFromRGBD (depth sampled at
+ * the distorted keypoint, scaled by depth_factor; depth_is_u16 selects 16-bit or float input), ComputeImageBounds,
+ * AssignFeaturesToGrid.  Results stay in slots first_slot ..: mvKeys/descriptors as after orbx_extract_batch, plus
+ * mvKeysUn, mvuRight, mvDepth and the grid; the matchers of this library then run on mvKeysUn and these bounds.
+ * Images are host pointers, or device pointers when on_device != 0.  Strides in bytes. */
+int orbx_frames_rgbd(orbx_handle* h, const uint8_t* color, int channels, int rgb_order, size_t color_frame_stride,
+                     size_t color_row_stride, const void* depth, int depth_is_u16, float depth_factor,
+                     size_t depth_frame_stride, size_t depth_row_stride, int width, int height, int nframes,
+                     int on_device, const orbx_camera* cam, int first_slot);
+
+/* mvKeysUn (full KeyPoint records), mvuRight, mvDepth of slots first_slot ..; each output may be NULL.
+ * keys_un: nframes*capacity records, u_right/depth: nframes*capacity floats, bounds: 4 floats. */
+int orbx_download_frame_front(orbx_handle* h, int first_slot, int nframes, orbx_keypoint* keys_un, float* u_right,
+                              float* depth, int capacity, float bounds[4]);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,103 @@
+// frame_oracle.cpp — CPU restatement of the steps of the reference's RGB-D Frame construction that sit
+// either side of ORBextractor::operator().  TEST INFRASTRUCTURE ONLY: loaded by
+// tests/, __graft_entry__.smoke() and bench.py's CPU legs; the product (liborbx.so) never links it.
+//
+//   oracle_cvt_gray            cv::cvtColor(RGB/BGR/RGBA/BGRA -> GRAY), Tracking.cc:308-321 (and :265-290 stereo)
+//   oracle_depth_to_float      imDepth.convertTo(CV_32F, mDepthMapFactor), Tracking.cc:324-327
+//   oracle_undistort_points    cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK), Frame.cc:404-434, 436-464
+//   oracle_image_bounds        Frame::ComputeImageBounds, Frame.cc:436-464
+//   oracle_stereo_from_rgbd    Frame::ComputeStereoFromRGBD, Frame.cc:641-662
+//
+// The OpenCV arithmetic is that of 4.13.0, pinned by tests/golden/frame_front.npz (generated with the cv2
+// wheel by tests/golden/make_golden_frame.py): 15-bit luma coefficients with round-half-up for 8U cvtColor;
+// five fixed-point iterations in double for undistortPoints (default TermCriteria(COUNT, 5)); float(src) * float(alpha)
+// for 16U -> 32F convertTo (restated from the OpenCV sources: the cv2 Python module has no Mat::convertTo).
+// Compile with -ffp-contract=off: every double operation below is separately rounded.
+
+#include <cmath>
+#include <cstddef>
+#include <cstdint>
+
+extern "C" {
+
+// cv::cvtColor(src, dst, CV_{RGB,BGR,RGBA,BGRA}2GRAY) for 8U: (R*9798 + G*19235 + B*3735 + 2^14) >> 15
+void oracle_cvt_gray(const uint8_t* src, int w, int h, size_t sstride, int channels, int rgb_order,
+                     uint8_t* dst, size_t dstride)
+{
+    const int RY = 9798, GY = 19235, BY = 3735;
+    for (int y = 0; y < h; ++y) {
+        const uint8_t* s = src + (size_t)y * sstride;
+        uint8_t* d = dst + (size_t)y * dstride;
+        for (int x = 0; x < w; ++x, s += channels) {
+            const int c0 = s[0], c1 = s[1], c2 = s[2];
+            const int r = rgb_order ? c0 : c2, b = rgb_order ? c2 : c0;
+            d[x] = (uint8_t)((r * RY + c1 * GY + b * BY + (1 << 14)) >> 15);
+        }
+    }
+}
+
+// imDepth.convertTo(imDepth, CV_32F, factor) for a 16U depth map (a 32F map with factor 1 is left alone by the reference)
+void oracle_depth_to_float(const uint16_t* src, int w, int h, size_t sstride_elems, float factor, float* dst, size_t dstride_elems)
+{
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x) dst[(size_t)y * dstride_elems + x] = (float)src[(size_t)y * sstride_elems + x] * factor;
+}
+
+// cv::undistortPoints with R = I and P = K: cam = (fx, fy, cx, cy), dist = (k1, k2, p1, p2, k3) as floats
+// (mK / mDistCoef are CV_32F, Tracking.cc:60-80; OpenCV widens them to double)
+void oracle_undistort_points(const float* xy_in, int n, const float* cam, const float* dist, float* xy_out)
+{
+    const double fx = cam[0], fy = cam[1], cx = cam[2], cy = cam[3];
+    const double ifx = 1. / fx, ify = 1. / fy;
+    const double k1 = dist[0], k2 = dist[1], p1 = dist[2], p2 = dist[3], k3 = dist[4];
+    for (int i = 0; i < n; ++i) {
+        const double u = xy_in[2 * i], v = xy_in[2 * i + 1];
+        double x = (u - cx) * ifx, y = (v - cy) * ify;
+        const double x0 = x, y0 = y;
+        for (int j = 0; j < 5; ++j) {
+            const double r2 = x * x + y * y;
+            // k[5..7] (k4..k6) and the thin-prism terms k[8..11] are zero for a 5-coefficient model
+            const double icdist = (1 + ((0 * r2 + 0) * r2 + 0) * r2) / (1 + ((k3 * r2 + k2) * r2 + k1) * r2);
+            if (icdist < 0) { x = (u - cx) * ifx; y = (v - cy) * ify; break; }
+            const double deltaX = 2 * p1 * x * y + p2 * (r2 + 2 * x * x) + 0 * r2 + 0 * r2 * r2;
+            const double deltaY = p1 * (r2 + 2 * y * y) + 2 * p2 * x * y + 0 * r2 + 0 * r2 * r2;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+        }
+        // P = K: xx = fx*x + 0*y + cx, yy = 0*x + fy*y + cy, ww = 1 / (0*x + 0*y + 1)
+        const double xx = fx * x + 0 * y + cx, yy = 0 * x + fy * y + cy, ww = 1. / (0 * x + 0 * y + 1);
+        xy_out[2 * i] = (float)(xx * ww);
+        xy_out[2 * i + 1] = (float)(yy * ww);
+    }
+}
+
+// Frame::ComputeImageBounds: bounds = (minX, maxX, minY, maxY)
+void oracle_image_bounds(int cols, int rows, const float* cam, const float* dist, float* bounds)
+{
+    if (dist[0] != 0.0f) {
+        const float c[8] = {0.f, 0.f, (float)cols, 0.f, 0.f, (float)rows, (float)cols, (float)rows};
+        float u[8];
+        oracle_undistort_points(c, 4, cam, dist, u);
+        bounds[0] = std::fmin(u[0], u[4]);
+        bounds[1] = std::fmax(u[2], u[6]);
+        bounds[2] = std::fmin(u[1], u[3]);
+        bounds[3] = std::fmax(u[5], u[7]);
+    } else {
+        bounds[0] = 0.0f; bounds[1] = (float)cols; bounds[2] = 0.0f; bounds[3] = (float)rows;
+    }
+}
+
+// Frame::ComputeStereoFromRGBD: keys = distorted keypoint positions, keys_un = undistorted; depth is CV_32F
+void oracle_stereo_from_rgbd(const float* keys_xy, const float* keys_un_xy, int n, const float* depth, int w, int h,
+                             size_t dstride_elems, float bf, float* u_right, float* z)
+{
+    (void)w; (void)h;
+    for (int i = 0; i < n; ++i) {
+        u_right[i] = -1.f; z[i] = -1.f;
+        const int v = (int)keys_xy[2 * i + 1], u = (int)keys_xy[2 * i];     // imDepth.at<float>(v, u) with float -> int conversion
+        const float d = depth[(size_t)v * dstride_elems + u];
+        if (d > 0) { z[i] = d; u_right[i] = keys_un_xy[2 * i] - bf / d; }
+    }
+}
+
+} // extern "C"

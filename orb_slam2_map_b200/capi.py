@@ -60,7 +60,16 @@ EXPORTS = [
     "orbx_get_candidates", "orbx_search_init_pairs", "orbx_extract_stereo_batch",
     "orbm_descriptor_distance", "orbm_search_for_initialization", "orbm_search_by_projection",
     "orbm_compute_stereo_matches", "orbm_knn2_device", "orbm_knn2_merge_device", "orbm_knn2_set_variant",
+    "orbx_cvt_gray", "orbx_depth_to_float", "orbx_undistort_points", "orbx_image_bounds", "orbx_frames_rgbd",
+    "orbx_download_frame_front",
 ]
+
+
+class Camera(C.Structure):
+    """orbx_camera: mK, mDistCoef (CV_32F) and mbf"""
+    _fields_ = [("fx", C.c_float), ("fy", C.c_float), ("cx", C.c_float), ("cy", C.c_float),
+                ("k1", C.c_float), ("k2", C.c_float), ("p1", C.c_float), ("p2", C.c_float), ("k3", C.c_float),
+                ("bf", C.c_float)]
 
 _LIB = None
 
@@ -233,6 +242,57 @@ class Extractor:
         check(lib().orbx_get_candidates(self.h, frame, level, _p(out), cap, C.byref(n)))
         assert n.value <= cap
         return out[:n.value].copy()
+
+    # ---- RGB-D frame front (orbx_frame.cu) ------------------------------------------------------
+    def cvt_gray(self, color: np.ndarray, rgb_order: bool) -> np.ndarray:
+        color = np.ascontiguousarray(color, np.uint8)
+        if color.ndim == 3:
+            color = color[None]
+        n, h, w, ch = color.shape
+        gray = np.empty((n, h, w), np.uint8)
+        check(lib().orbx_cvt_gray(self.h, color.ctypes.data_as(C.c_void_p), ch, int(rgb_order), C.c_size_t(h * w * ch),
+                                  C.c_size_t(w * ch), w, h, n, 0, gray.ctypes.data_as(C.c_void_p), C.c_size_t(h * w), C.c_size_t(w)))
+        return gray
+
+    def depth_to_float(self, depth: np.ndarray, factor: float) -> np.ndarray:
+        depth = np.ascontiguousarray(depth, np.uint16)
+        h, w = depth.shape
+        out = np.empty((h, w), np.float32)
+        check(lib().orbx_depth_to_float(self.h, depth.ctypes.data_as(C.c_void_p), C.c_size_t(w), w, h, C.c_float(factor), 0,
+                                        out.ctypes.data_as(C.c_void_p), C.c_size_t(w)))
+        return out
+
+    def undistort_points(self, xy: np.ndarray, cam: "Camera") -> np.ndarray:
+        xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+        out = np.empty_like(xy)
+        check(lib().orbx_undistort_points(self.h, xy.ctypes.data_as(C.c_void_p), len(xy), C.byref(cam), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def image_bounds(self, cols: int, rows: int, cam: "Camera") -> np.ndarray:
+        out = np.empty(4, np.float32)
+        check(lib().orbx_image_bounds(self.h, cols, rows, C.byref(cam), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def frames_rgbd(self, color: np.ndarray, depth: np.ndarray, cam: "Camera", rgb_order=True, depth_factor=1.0, first_slot=0):
+        """color [n,h,w,c] or [n,h,w] uint8, depth [n,h,w] uint16 or float32 (host arrays)"""
+        color = np.ascontiguousarray(color, np.uint8)
+        ch = 1 if color.ndim == 3 else color.shape[3]
+        n, h, w = color.shape[:3]
+        is16 = depth.dtype == np.uint16
+        depth = np.ascontiguousarray(depth, np.uint16 if is16 else np.float32)
+        es = 2 if is16 else 4
+        check(lib().orbx_frames_rgbd(self.h, color.ctypes.data_as(C.c_void_p), ch, int(rgb_order), C.c_size_t(h * w * ch), C.c_size_t(w * ch),
+                                     depth.ctypes.data_as(C.c_void_p), int(is16), C.c_float(depth_factor), C.c_size_t(h * w * es),
+                                     C.c_size_t(w * es), w, h, n, 0, C.byref(cam), first_slot))
+
+    def download_frame_front(self, first_slot, nframes):
+        kun = np.zeros((nframes, self.cap), KP_DTYPE)
+        ur = np.zeros((nframes, self.cap), np.float32)
+        z = np.zeros((nframes, self.cap), np.float32)
+        b = np.zeros(4, np.float32)
+        check(lib().orbx_download_frame_front(self.h, first_slot, nframes, kun.ctypes.data_as(C.c_void_p), ur.ctypes.data_as(C.c_void_p),
+                                              z.ctypes.data_as(C.c_void_p), self.cap, b.ctypes.data_as(C.c_void_p)))
+        return kun, ur, z, b
 
     def search_init_pairs(self, first_slot, npairs, window=100, nnratio=0.9, check_ori=True, fetch=True):
         ncmp = C.c_uint64()

@@ -165,6 +165,7 @@ int orbx_create(const orbx_params* params, int max_width, int max_height, int ch
     h->dLevel0 = h->dStageLin = h->dRaw = h->dBlur = nullptr;
     h->dCand = h->dKeysA = h->dKeysB = nullptr; h->dCellSeg = nullptr; h->dLevelCandCount = nullptr;
     h->dLevelKps = nullptr; h->dLevelKpCount = nullptr; h->dStatus = nullptr;
+    h->dKpsUn = nullptr; h->storeUndistorted = false; h->bounds[0] = h->bounds[1] = h->bounds[2] = h->bounds[3] = 0.f;
     h->dKps = nullptr; h->dDesc = nullptr; h->dCount = nullptr; h->dSlotLevelCount = nullptr;
     h->dGridStart = nullptr; h->dGridIdx = nullptr; h->dMatches12 = nullptr; h->dNMatches = nullptr;
     h->dNCompares = nullptr; h->dURight = nullptr; h->dDepth = nullptr; h->dMatchScratch = nullptr;
@@ -213,7 +214,7 @@ int orbx_destroy(orbx_handle* h)
     if (!h) return ORBX_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
-    void* ptrs[] = {h->dCells, h->dCoef, h->dBlurTiles, h->dKpMap, h->dLevel0, h->dStageLin, h->dRaw, h->dBlur, h->dCand, h->dKeysA,
+    void* ptrs[] = {h->dCells, h->dCoef, h->dBlurTiles, h->dKpMap, h->dKpsUn, h->dLevel0, h->dStageLin, h->dRaw, h->dBlur, h->dCand, h->dKeysA,
                     h->dKeysB, h->dCellSeg, h->dLevelCandCount, h->dLevelKps, h->dLevelKpCount, h->dStatus, h->dKps,
                     h->dDesc, h->dCount, h->dSlotLevelCount, h->dGridStart, h->dGridIdx, h->dMatches12, h->dNMatches,
                     h->dNCompares, h->dURight, h->dDepth, h->dMatchScratch};
@@ -283,6 +284,7 @@ int orbx_extract_batch_to_host(orbx_handle* h, const uint8_t* images, size_t fra
     ORBX_CUDA(cudaSetDevice(h->device));
     int rc = orbx_setup_shape(h, width, height);
     if (rc) return rc;
+    h->storeUndistorted = false;            // plain extraction: mvKeysUn = mvKeys, bounds = the image (orbx_frames_rgbd sets them after)
     const bool direct = images_on_device && (row_stride % 4 == 0) && (((uintptr_t)images) % 4 == 0) && (frame_stride % 4 == 0);
     // Host (or unaligned device) images: chunk i+1 is copied into the other half of dLevel0 on the
     // copy stream while the kernels of chunk i run; events order copy -> compute -> buffer reuse.

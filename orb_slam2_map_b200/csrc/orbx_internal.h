@@ -121,6 +121,10 @@ struct orbx_handle {
     uint8_t* dDesc;
     int* dCount;
     int* dSlotLevelCount;
+    // RGB-D frame front (orbx_frame.cu): mvKeysUn records; when storeUndistorted the matchers and the grid use them
+    orbx_keypoint* dKpsUn;
+    bool storeUndistorted;
+    float bounds[4];        // mnMinX, mnMaxX, mnMinY, mnMaxY of the undistorted frames
     // frame grid (per slot)
     unsigned short* dGridStart;   // [slot][GRID_CELLS+1]
     unsigned short* dGridIdx;     // [slot][kpCap]

@@ -730,7 +730,7 @@ int orbx_ensure_match_buffers(orbx_handle* h)
 static FrameStore store_of(orbx_handle* h)
 {
     FrameStore fs;
-    fs.kps = h->dKps; fs.desc = h->dDesc; fs.count = h->dCount;
+    fs.kps = h->storeUndistorted ? h->dKpsUn : h->dKps; fs.desc = h->dDesc; fs.count = h->dCount;
     fs.gridStart = h->dGridStart; fs.gridIdx = h->dGridIdx; fs.cap = h->kpCap;
     return fs;
 }
@@ -770,7 +770,9 @@ int orbx_build_grids(orbx_handle* h, int firstSlot, int nframes, int width, int 
 {
     int rc = orbx_ensure_match_buffers(h);
     if (rc) return rc;
-    return launch_grid_build(store_of(h), firstSlot, nframes, grid_params(0.f, (float)width, 0.f, (float)height), h->stream);
+    const GridParams gp = h->storeUndistorted ? grid_params(h->bounds[0], h->bounds[1], h->bounds[2], h->bounds[3])
+                                              : grid_params(0.f, (float)width, 0.f, (float)height);
+    return launch_grid_build(store_of(h), firstSlot, nframes, gp, h->stream);
 }
 
 static int launch_stereo(const FrameStore& fs, int firstSlot, int npairs, const PyrView& pv, float bf, float fx,
@@ -812,7 +814,8 @@ int orbx_search_init_pairs(orbx_handle* h, int first_slot, int npairs, int windo
     int rc = orbx_ensure_match_buffers(h);
     if (rc) return rc;
     const FrameStore fs = store_of(h);
-    const GridParams gp = grid_params(0.f, (float)h->curW, 0.f, (float)h->curH);
+    const GridParams gp = h->storeUndistorted ? grid_params(h->bounds[0], h->bounds[1], h->bounds[2], h->bounds[3])
+                                              : grid_params(0.f, (float)h->curW, 0.f, (float)h->curH);
     orbx_prof_mark(h, -1);
     rc = launch_grid_build(fs, first_slot, npairs + 1, gp, h->stream);
     if (rc) return rc;
@@ -1058,6 +1061,7 @@ int orbx_extract_stereo_batch(orbx_handle* h, const uint8_t* left, const uint8_t
     if (!(fx > 0) || !(bf > 0)) { orbx_set_error("bf and fx must be positive"); return ORBX_E_INVALID; }
     ORBX_CUDA(cudaSetDevice(h->device));
     int rc = orbx_setup_shape(h, width, height); if (rc) return rc;
+    h->storeUndistorted = false;
     rc = orbx_ensure_match_buffers(h); if (rc) return rc;
     const Geom& g = h->geom;
     const bool direct = images_on_device && (row_stride % 4 == 0) && (frame_stride % 4 == 0) &&

@@ -56,7 +56,8 @@ class StereoInput(C.Structure):
 def build_oracle(force: bool = False) -> str:
     so = os.path.join(ORACLE_DIR, "liborb_oracle.so")
     src = os.path.join(ORACLE_DIR, "orb_oracle.cpp")
-    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+    src2 = os.path.join(ORACLE_DIR, "frame_oracle.cpp")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(src), os.path.getmtime(src2)):
         subprocess.check_call(["make", "-C", ORACLE_DIR, "liborb_oracle.so"], stdout=subprocess.DEVNULL)
     return so
 
@@ -297,3 +298,47 @@ def extract_match_many(params: Params, imgs: np.ndarray, nthreads: int, window=1
                                          C.c_size_t(imgs.strides[1]), C.c_int(n), C.c_int(nthreads), C.c_int(window),
                                          C.c_float(nnratio), C.c_int(int(check_ori)), C.byref(tm), C.byref(nc))
     return int(tk), tm.value, nc.value
+
+
+# ---- RGB-D frame front (oracle/frame_oracle.cpp) -----------------------------------------------------
+def cvt_gray(img: np.ndarray, rgb_order: bool) -> np.ndarray:
+    """cv::cvtColor(RGB|BGR|RGBA|BGRA -> GRAY), 8U"""
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w, ch = img.shape
+    out = np.empty((h, w), np.uint8)
+    lib().oracle_cvt_gray(_p(img), w, h, C.c_size_t(w * ch), ch, int(rgb_order), _p(out), C.c_size_t(w))
+    return out
+
+
+def depth_to_float(depth: np.ndarray, factor: float) -> np.ndarray:
+    depth = np.ascontiguousarray(depth, np.uint16)
+    h, w = depth.shape
+    out = np.empty((h, w), np.float32)
+    lib().oracle_depth_to_float(_p(depth), w, h, C.c_size_t(w), C.c_float(factor), _p(out), C.c_size_t(w))
+    return out
+
+
+def undistort_points(xy: np.ndarray, cam, dist) -> np.ndarray:
+    xy = np.ascontiguousarray(xy, np.float32).reshape(-1, 2)
+    cam = np.asarray(cam, np.float32); dist = np.asarray(dist, np.float32)
+    out = np.empty_like(xy)
+    lib().oracle_undistort_points(_p(xy), len(xy), _p(cam), _p(dist), _p(out))
+    return out
+
+
+def image_bounds(cols: int, rows: int, cam, dist) -> np.ndarray:
+    cam = np.asarray(cam, np.float32); dist = np.asarray(dist, np.float32)
+    out = np.empty(4, np.float32)
+    lib().oracle_image_bounds(cols, rows, _p(cam), _p(dist), _p(out))
+    return out
+
+
+def stereo_from_rgbd(keys_xy: np.ndarray, keys_un_xy: np.ndarray, depth: np.ndarray, bf: float):
+    keys_xy = np.ascontiguousarray(keys_xy, np.float32).reshape(-1, 2)
+    keys_un_xy = np.ascontiguousarray(keys_un_xy, np.float32).reshape(-1, 2)
+    depth = np.ascontiguousarray(depth, np.float32)
+    h, w = depth.shape
+    n = len(keys_xy)
+    ur = np.empty(n, np.float32); z = np.empty(n, np.float32)
+    lib().oracle_stereo_from_rgbd(_p(keys_xy), _p(keys_un_xy), n, _p(depth), w, h, C.c_size_t(w), C.c_float(bf), _p(ur), _p(z))
+    return ur, z
