@@ -69,19 +69,18 @@ pyr_resize_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long lo
 #define RS_TH 32
 #define RS_WARPS 4
 
-struct RsCol { uint32_t coef[4]; uint32_t selA[4], selB[4]; bool useB[4]; int w0idx, w1idx, w2idx; };
+// per-lane column constants: the two taps of output pixel i lie at bytes t, t+1 (0 <= t <= 11) of the lane's
+// three-word window.  sel1 picks them out of words 0-1, sel2 replaces those that live in word 2: two PRMTs
+// per pixel, no predicates.
+struct RsCol { uint32_t coef[4]; uint32_t sel1[4], sel2[4]; };
 
-__device__ __forceinline__ void rs_load(const u8* __restrict__ row, const RsCol& c, uint32_t w[3])
+__device__ __forceinline__ void rs_hsum(const uint32_t* __restrict__ p, const RsCol& c, uint32_t Hq[4])
 {
-    const uint32_t* r32 = reinterpret_cast<const uint32_t*>(row);
-    w[0] = r32[c.w0idx]; w[1] = r32[c.w1idx]; w[2] = r32[c.w2idx];
-}
-__device__ __forceinline__ void rs_hsum(const uint32_t w[3], const RsCol& c, uint32_t Hq[4])
-{
+    const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        const uint32_t A = __byte_perm(w[0], w[1], c.selA[i]), B = __byte_perm(w[1], w[2], c.selB[i]);
-        Hq[i] = __dp2a_lo(c.coef[i], c.useB[i] ? B : A, 0u) >> 4;       // (p0*a0 + p1*a1) >> 4
+        const uint32_t taps = __byte_perm(__byte_perm(w0, w1, c.sel1[i]), w2, c.sel2[i]);
+        Hq[i] = __dp2a_lo(c.coef[i], taps, 0u) >> 4;                    // (p0*a0 + p1*a1) >> 4
     }
 }
 
@@ -98,29 +97,26 @@ pyr_resize4_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long l
     u8* dst = dstBase + (long long)blockIdx.z * dstFrameStride;
     // ---- per-column constants ------------------------------------------------------------------
     RsCol c;
-    const int lastWord = (sw - 1) >> 2;
+    const uint32_t* colp;                       // word wb of source row 0: the lane's window is colp[r*rowWords + 0..2]
     {
+        const int lastWord = (sw - 1) >> 2;     // >= 2: levels are at least 12 pixels wide (host check)
         const int2 c0 = cx[min(x, dw - 1)];
-        const int wb = (c0.x & 0xffff) >> 2;
-        c.w0idx = min(wb, lastWord); c.w1idx = min(wb + 1, lastWord); c.w2idx = min(wb + 2, lastWord);
+        const int wb = max(0, min((c0.x & 0xffff) >> 2, lastWord - 2));
+        colp = reinterpret_cast<const uint32_t*>(src) + wb;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             const int2 ci = cx[min(x + i, dw - 1)];
-            const int o = (ci.x & 0xffff) - 4 * wb;                 // 0 .. 10 for scale <= 2
-            c.coef[i] = (uint32_t)ci.y;                             // a0 | a1 << 16
-            c.useB[i] = o >= 4;
-            c.selA[i] = (uint32_t)(o & 7) | ((uint32_t)((o + 1) & 7) << 4);
-            c.selB[i] = (uint32_t)((o - 4) & 7) | ((uint32_t)((o - 3) & 7) << 4);
+            const int t0 = (ci.x & 0xffff) - 4 * wb, t1 = min(t0 + 1, 11);       // 0 .. 11 for scale <= 2
+            c.coef[i] = (uint32_t)ci.y;                                          // a0 | a1 << 16
+            c.sel1[i] = (uint32_t)(t0 & 7) | ((uint32_t)(t1 & 7) << 4);
+            c.sel2[i] = (uint32_t)(t0 < 8 ? 0 : t0 - 4) | ((uint32_t)(t1 < 8 ? 1 : t1 - 4) << 4);
         }
     }
+    const int rowWords = srcPitch >> 2;
     int ra = -1, rb = -1;                   // source rows whose horizontal sums are in HA / HB
     uint32_t HA[4], HB[4];
     const int yend = min(y0 + RS_TH, dh);
-    auto hrow = [&](int r, uint32_t Hq[4]) {
-        uint32_t w[3];
-        rs_load(src + (long long)r * srcPitch, c, w);
-        rs_hsum(w, c, Hq);
-    };
+    auto hrow = [&](int r, uint32_t Hq[4]) { rs_hsum(colp + (long long)r * rowWords, c, Hq); };
     for (int y = y0; y < yend; ++y) {
         const int2 cyv = cy[y];
         const int sy0 = cyv.x & 0xffff, sy1 = cyv.x >> 16;
