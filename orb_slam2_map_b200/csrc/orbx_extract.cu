@@ -188,6 +188,8 @@ __device__ __forceinline__ void edge_mode(int x, int w, int& mode, uint32_t& sel
     }
 }
 
+// INTERIOR: every source row of the strip (y0-3 .. y0-4+7*ngroups) exists, no row reflection needed
+template <bool INTERIOR>
 __device__ __forceinline__ void blur_strip(const u8* __restrict__ src, int sp, u8* __restrict__ dst, int dp,
                                            int w, int h, int x, int y0, int lane)
 {
@@ -201,14 +203,18 @@ __device__ __forceinline__ void blur_strip(const u8* __restrict__ src, int sp, u
     const bool store = lane >= 1 && lane <= 30 && x < w;
     uint32_t H[7][4];
     uint32_t cur[7], nxt[7];
+    const u8* colp = src + (long long)(y0 - 3) * sp + xl;         // row y0-3 of the lane's column (INTERIOR addressing)
 #pragma unroll
-    for (int k = 0; k < 7; ++k) cur[k] = *reinterpret_cast<const uint32_t*>(src + (long long)reflect_row(y0 - 3 + k, h) * sp + xl);
+    for (int k = 0; k < 7; ++k)
+        cur[k] = INTERIOR ? *reinterpret_cast<const uint32_t*>(colp + k * sp)
+                          : *reinterpret_cast<const uint32_t*>(src + (long long)reflect_row(y0 - 3 + k, h) * sp + xl);
 #pragma unroll 1
     for (int gi = 0; gi < ngroups; ++gi) {
         if (gi + 1 < ngroups) {
 #pragma unroll
             for (int k = 0; k < 7; ++k)
-                nxt[k] = *reinterpret_cast<const uint32_t*>(src + (long long)reflect_row(y0 - 3 + (gi + 1) * 7 + k, h) * sp + xl);
+                nxt[k] = INTERIOR ? *reinterpret_cast<const uint32_t*>(colp + ((gi + 1) * 7 + k) * sp)
+                                  : *reinterpret_cast<const uint32_t*>(src + (long long)reflect_row(y0 - 3 + (gi + 1) * 7 + k, h) * sp + xl);
         }
 #pragma unroll
         for (int k = 0; k < 7; ++k) {
@@ -259,7 +265,9 @@ blur7_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, u8* __restrict__
     if (level == 0) { src = l0_frame(l0, frame); sp = l0.pitch; }
     else { src = rawBase + (long long)frame * g.pyrFrameBytes + L.off; sp = L.pitch; }
     u8* dst = blurBase + (long long)frame * g.pyrFrameBytes + L.off;
-    blur_strip(src, sp, dst, L.pitch, L.w, L.h, tx * BL_TW - 4 + lane * 4, ty * BL_TH, lane);
+    const int y0 = ty * BL_TH, ngroups = (min(BL_TH, L.h - y0) + 6 + 6) / 7;
+    if (y0 >= 3 && y0 - 3 + 7 * ngroups <= L.h) blur_strip<true>(src, sp, dst, L.pitch, L.w, L.h, tx * BL_TW - 4 + lane * 4, y0, lane);
+    else blur_strip<false>(src, sp, dst, L.pitch, L.w, L.h, tx * BL_TW - 4 + lane * 4, y0, lane);
 }
 
 // =============================================================================================
