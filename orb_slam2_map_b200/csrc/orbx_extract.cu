@@ -152,8 +152,7 @@ pyr_resize4_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long l
 // vertical pass — no shared memory, every source byte is fetched once per strip (+6 halo rows).
 // =============================================================================================
 #define BL_TW 120                       // output columns per strip: lanes 1..30 (lanes 0, 31 are halo)
-#define BL_GROUPS 9                     // 7-row groups per strip
-#define BL_TH (7 * BL_GROUPS - 6)       // 57 output rows per strip (+6 halo rows)
+#define BL_TARGET 120                   // strips are about this tall (LevelGeom::blurTH = 7g-6 rows, balanced over the level)
 #define BL_WARPS 4
 __device__ __forceinline__ int reflect101(int i, int n)
 {
@@ -191,11 +190,11 @@ __device__ __forceinline__ void edge_mode(int x, int w, int& mode, uint32_t& sel
 // INTERIOR: every source row of the strip (y0-3 .. y0-4+7*ngroups) exists, no row reflection needed
 template <bool INTERIOR>
 __device__ __forceinline__ void blur_strip(const u8* __restrict__ src, int sp, u8* __restrict__ dst, int dp,
-                                           int w, int h, int x, int y0, int lane)
+                                           int w, int h, int x, int y0, int th, int lane)
 {
     const unsigned FULL = 0xffffffffu;
     const uint32_t c0 = 18u | (34u << 8) | (48u << 16) | (56u << 24), c1 = 48u | (34u << 8) | (18u << 16);
-    const int rowsOut = min(BL_TH, h - y0);
+    const int rowsOut = min(th, h - y0);
     const int ngroups = (rowsOut + 6 + 6) / 7;
     const int xl = min(max(x, 0), (w - 1) & ~3);  // every lane loads an aligned word that lies inside the row
     int mode; uint32_t sel;
@@ -265,9 +264,9 @@ blur7_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, u8* __restrict__
     if (level == 0) { src = l0_frame(l0, frame); sp = l0.pitch; }
     else { src = rawBase + (long long)frame * g.pyrFrameBytes + L.off; sp = L.pitch; }
     u8* dst = blurBase + (long long)frame * g.pyrFrameBytes + L.off;
-    const int y0 = ty * BL_TH, ngroups = (min(BL_TH, L.h - y0) + 6 + 6) / 7;
-    if (y0 >= 3 && y0 - 3 + 7 * ngroups <= L.h) blur_strip<true>(src, sp, dst, L.pitch, L.w, L.h, tx * BL_TW - 4 + lane * 4, y0, lane);
-    else blur_strip<false>(src, sp, dst, L.pitch, L.w, L.h, tx * BL_TW - 4 + lane * 4, y0, lane);
+    const int y0 = ty * L.blurTH, ngroups = (min(L.blurTH, L.h - y0) + 6 + 6) / 7;
+    if (y0 >= 3 && y0 - 3 + 7 * ngroups <= L.h) blur_strip<true>(src, sp, dst, L.pitch, L.w, L.h, tx * BL_TW - 4 + lane * 4, y0, L.blurTH, lane);
+    else blur_strip<false>(src, sp, dst, L.pitch, L.w, L.h, tx * BL_TW - 4 + lane * 4, y0, L.blurTH, lane);
 }
 
 // =============================================================================================
@@ -1014,7 +1013,12 @@ int orbx_setup_shape(orbx_handle* h, int w, int hgt)
             L.coefX = (int)coef.size(); linear_coeffs(g.L[l - 1].w, L.w, coef);
             L.coefY = (int)coef.size(); linear_coeffs(g.L[l - 1].h, L.h, coef);
         }
-        for (int ty = 0; ty * BL_TH < L.h; ++ty)
+        {
+            const int nstrips = std::max(1, (L.h + BL_TARGET - 1) / BL_TARGET);
+            const int g7 = ((L.h + nstrips - 1) / nstrips + 6 + 6) / 7;        // 7-row groups covering rows + 6 halo rows
+            L.blurTH = std::max(1, 7 * g7 - 6);
+        }
+        for (int ty = 0; ty * L.blurTH < L.h; ++ty)
             for (int tx = 0; tx * BL_TW < L.w; ++tx) tiles.push_back((l << 24) | (ty << 12) | tx);
         // FAST cell grid (src/ORBextractor.cc:773-806)
         const int minBX = 16, minBY = 16, maxBX = L.w - 16, maxBY = L.h - 16;

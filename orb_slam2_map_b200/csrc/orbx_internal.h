@@ -40,6 +40,7 @@ struct LevelGeom {
     float hX;               // root width (float, as the reference computes it)
     int winW, winH;         // maxBorderX-minBorderX, maxBorderY-minBorderY
     int coefX, coefY;       // offsets into the resize coefficient table (levels >= 1)
+    int blurTH;             // output rows per blur strip (7g-6)
     int wCell, hCell;       // FAST cell stride (reference src/ORBextractor.cc:786-787)
     float scale;            // mvScaleFactor[level]
     float kpSize;           // (float)(int)(31*scale)
