@@ -57,7 +57,7 @@ pyr_resize_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long lo
 }
 
 // =============================================================================================
-// K1a (fast path, scale factor <= 2): one warp owns a 128 x RS_TH strip of the destination level;
+// K1a (fast path, scale factor <= 2): one warp owns a 128 x th strip of the destination level;
 // a lane owns 4 adjacent output columns and walks down the output rows.  Everything that depends
 // only on the column (source column, 11-bit coefficients, byte selectors) is hoisted out of the
 // row loop.  A source row contributes 3 aligned 32-bit words per lane; the two taps of a pixel are
@@ -66,7 +66,8 @@ pyr_resize_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long lo
 // output rows share a source row when the scale is < 2).  Vertical blend = OpenCV's
 // ((b*(S>>4))>>16 ... +2)>>2 with the >>16 folded into a high multiply.
 // =============================================================================================
-#define RS_TH 32
+#define RS_TARGET 12                    // strips are about this tall, balanced over the level (short strips: the row
+                                        // walk is latency bound, more warps in flight beat the amortised column setup)
 #define RS_WARPS 4
 
 // per-lane column constants: the two taps of output pixel i lie at bytes t, t+1 (0 <= t <= 11) of the lane's
@@ -87,11 +88,11 @@ __device__ __forceinline__ void rs_hsum(const uint32_t* __restrict__ p, const Rs
 __global__ void __launch_bounds__(RS_WARPS * 32)
 pyr_resize4_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long long srcFrameStride, int srcPitch, int sw, int sh,
                    u8* __restrict__ dstBase, long long dstFrameStride, int dstPitch,
-                   int dw, int dh, const int2* __restrict__ cx, const int2* __restrict__ cy)
+                   int dw, int dh, int th, const int2* __restrict__ cx, const int2* __restrict__ cy)
 {
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int x = (blockIdx.x * 32 + lane) * 4;
-    const int y0 = (blockIdx.y * RS_WARPS + wid) * RS_TH;
+    const int y0 = (blockIdx.y * RS_WARPS + wid) * th;
     if (y0 >= dh) return;
     const u8* src = fromL0 ? l0_frame(l0, blockIdx.z) : srcBase + (long long)blockIdx.z * srcFrameStride;
     u8* dst = dstBase + (long long)blockIdx.z * dstFrameStride;
@@ -115,7 +116,7 @@ pyr_resize4_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long l
     const int rowWords = srcPitch >> 2;
     int ra = -1, rb = -1;                   // source rows whose horizontal sums are in HA / HB
     uint32_t HA[4], HB[4];
-    const int yend = min(y0 + RS_TH, dh);
+    const int yend = min(y0 + th, dh);
     auto hrow = [&](int r, uint32_t Hq[4]) { rs_hsum(colp + (long long)r * rowWords, c, Hq); };
     for (int y = y0; y < yend; ++y) {
         const int2 cyv = cy[y];
@@ -1160,9 +1161,10 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
         if (l == 1) { src = l0.base; sfs = l0.frameStride; sp = l0.pitch; }
         else { src = h->dRaw + S.off; sfs = g.pyrFrameBytes; sp = S.pitch; }
         if (h->params.scale_factor <= 2.0f) {
-            dim3 grid((D.w + 127) / 128, (D.h + RS_TH * RS_WARPS - 1) / (RS_TH * RS_WARPS), nframes);
+            const int nstrips = std::max(1, (D.h + RS_TARGET - 1) / RS_TARGET), th = (D.h + nstrips - 1) / nstrips;
+            dim3 grid((D.w + 127) / 128, (nstrips + RS_WARPS - 1) / RS_WARPS, nframes);
             pyr_resize4_kernel<<<grid, RS_WARPS * 32, 0, st>>>(l0, l == 1 ? 1 : 0, src, sfs, sp, S.w, S.h, h->dRaw + D.off, g.pyrFrameBytes,
-                                                               D.pitch, D.w, D.h, h->dCoef + D.coefX, h->dCoef + D.coefY);
+                                                               D.pitch, D.w, D.h, th, h->dCoef + D.coefX, h->dCoef + D.coefY);
         } else {
             dim3 grid((D.w + 127) / 128, (D.h + 7) / 8, nframes), block(32, 8);
             pyr_resize_kernel<<<grid, block, 0, st>>>(l0, l == 1 ? 1 : 0, src, sfs, sp, h->dRaw + D.off, g.pyrFrameBytes, D.pitch, D.w, D.h,
