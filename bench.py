@@ -64,14 +64,14 @@ def algorithmic_bytes(w, h, nkp):
                 total=b_pyr + b_fast + b_desc)
 
 
-# measured DRAM bytes per 640x480 frame (read + write) of each extractor kernel, from the r01h `ncu --set full`
-# capture of a 64-frame launch (profiles/r01h_ncu_full_chunk64_summary.txt); resize = sum over the 7 levels
+# measured DRAM bytes per 640x480 frame (read + write) of each extractor kernel, from the r01i `ncu --set full`
+# capture of a 64-frame launch (profiles/r01i_ncu_full_chunk64_summary.txt); resize = sum over the 7 levels
 NCU_DRAM_BYTES_PER_FRAME = {
-    "fast": (55.878912e6 + 1.043968e6) / 64,
-    "blur": (63.857152e6 + 16.974592e6) / 64,
-    "describe": (118.298624e6 + 5.328384e6) / 64,
+    "fast": (55.875328e6 + 1.419520e6) / 64,
+    "blur": (63.966976e6 + 15.665920e6) / 64,
+    "describe": (118.267136e6 + 5.597696e6) / 64,
     "resize": (19.685632e6 + 13.945344e6 + 9.565184e6 + 6.846208e6 + 4.746752e6 + 3.375872e6 + 2.319360e6 + 0.03e6) / 64,
-    "octree": 1.814528e6 / 64,
+    "octree": 1.813504e6 / 64,
 }
 
 
@@ -546,14 +546,14 @@ def main():
     dom_ms = stage_ms.get(dom, 0.0)
     achieved = (dom_bytes * frames_total / dom_launches) / (dom_ms / dom_launches * 1e-3) / 1e9 if dom_ms > 0 else 0.0
     # DRAM traffic of the dominant kernel: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full`
-    # capture (profiles/r01h_ncu_full_chunk64_summary.txt, a 64-frame launch of the 640x480 workload), scaled to
+    # capture (profiles/r01i_ncu_full_chunk64_summary.txt, a 64-frame launch of the 640x480 workload), scaled to
     # the frames one launch of this run processes.  Other image shapes have no capture: null.
     traffic = None
     if (W, H) == (640, 480) and dom in NCU_DRAM_BYTES_PER_FRAME:
         traffic = NCU_DRAM_BYTES_PER_FRAME[dom] * frames_total / dom_launches
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic,
-                "traffic_source": "ncu --set full, profiles/r01h_ncu_full_chunk64_summary.txt, per-frame bytes x frames per launch" if traffic else None,
+                "traffic_source": "ncu --set full, profiles/r01i_ncu_full_chunk64_summary.txt, per-frame bytes x frames per launch" if traffic else None,
                 "algorithmic_bytes_per_launch": dom_bytes * frames_total / dom_launches,
                 "peak_source": peak_src,
                 "algorithmic_bytes_per_frame": dom_bytes,
