@@ -388,6 +388,66 @@ def run_stereo(args):
         dist.destroy_process_group()
 
 
+def run_rgbd(args):
+    """Side line for SURVEY 8(f) rank 1: the RGB-D frame front (colour -> gray, ORB, mvKeysUn, mvuRight/mvDepth, grid)
+    on TUM-shaped input: 640x480 RGB + 16-bit depth, TUM1 calibration (Examples/RGB-D/TUM1.yaml)."""
+    import torch
+    from orb_slam2_map_b200 import capi, synth
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
+    F = args.frames if args.frames != 4096 else 2048
+    gray = synth.frame_sequence_torch(F, W, H, seed=0, device=dev)
+    g = torch.Generator(device=dev); g.manual_seed(1)
+    color = torch.stack([(gray.to(torch.int16) + torch.randint(-12, 13, gray.shape, generator=g, device=dev, dtype=torch.int16)).clamp(0, 255).to(torch.uint8)
+                         for _ in range(3)], dim=-1).contiguous()
+    depth = torch.randint(500, 30000, (F, H, W), generator=g, device=dev, dtype=torch.int32).to(torch.uint16)
+    cam = capi.Camera(517.306408, 516.469215, 318.643040, 255.313989, 0.262383, -0.953104, -0.005358, 0.002628, 1.163314, 40.0)
+    factor = 1.0 / 5000.0
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    ex = capi.Extractor(**PARAMS, max_width=W, max_height=H, chunk_frames=args.chunk, result_slots=F, device=0, stream=stream.cuda_stream)
+    step = lambda: ex.frames_rgbd_ptr(color.data_ptr(), 3, depth.data_ptr(), True, F, W, H, cam, True, factor, True, 0)
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    clocks = ClockSampler(0); clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop()
+    hc = torch.empty(color.shape, dtype=torch.uint8, pin_memory=True); hc.copy_(color)
+    hd = torch.empty(depth.shape, dtype=torch.uint16, pin_memory=True); hd.copy_(depth)
+    torch.cuda.synchronize()
+    def e2e():
+        ex.frames_rgbd_ptr(hc.data_ptr(), 3, hd.data_ptr(), True, F, W, H, cam, True, factor, False, 0)
+        ex.download(0, F); ex.download_frame_front(0, F)
+    e2e()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e()
+    dt = time.perf_counter() - t0
+    peak, peak_src = measured_peaks()
+    ab = algorithmic_bytes(W, H, 1005)["total"] + 4 * W * H          # + colour read (3 B/px) and gray write (1 B/px)
+    value = F * args.steps / (ms * 1e-3)
+    line = {"metric": "RGB-D frames/s (640x480 RGB + 16-bit depth, 1000 kp: cvtColor + ORB + UndistortKeyPoints + ComputeStereoFromRGBD + grid)",
+            "value": value, "unit": "frames/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "SURVEY 8(f) rank 1: RGB-D frame front on TUM1-shaped input", "frames_per_step_per_gpu": F,
+                       "chunk_frames": args.chunk, "l2_policy": f"inputs ({F * W * H * 5 / 1e9:.2f} GB per step) larger than L2"},
+            "clocks": clk,
+            "e2e": {"value": F * args.steps / dt, "unit": "frames/s", "h2d_bytes_per_step": F * W * H * 5,
+                    "d2h_bytes_per_step": F * ex.cap * (28 + 32 + 28 + 8) + 4 * F},
+            "gpu_launches": None,
+            "roofline": {"bound": "hbm", "kernel": "path", "achieved": ab * value / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": ab * value / 1e9 / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_frame": ab}}
+    print(json.dumps(line))
+    ex.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -397,7 +457,7 @@ def main():
     ap.add_argument("--frames", type=int, default=4096)
     ap.add_argument("--chunk", type=int, default=512)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--workload", default="frames", choices=["frames", "hd", "stereo", "knn"],
+    ap.add_argument("--workload", default="frames", choices=["frames", "hd", "stereo", "knn", "rgbd"],
                     help="frames = BASELINE configs[1] (the graded line); hd = configs[3]; stereo = configs[2]; knn = configs[4]")
     ap.add_argument("--queries", type=int, default=262144, help="knn: queries per step (config 5 names 1M)")
     ap.add_argument("--db-per-gpu", type=int, default=2000000, help="knn: database rows per GPU (config 5: 16M over 8)")
@@ -423,6 +483,9 @@ def main():
         return
     if args.workload == "knn":
         run_knn(args)
+        return
+    if args.workload == "rgbd":
+        run_rgbd(args)
         return
 
     import torch

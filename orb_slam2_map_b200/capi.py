@@ -285,6 +285,15 @@ class Extractor:
                                      depth.ctypes.data_as(C.c_void_p), int(is16), C.c_float(depth_factor), C.c_size_t(h * w * es),
                                      C.c_size_t(w * es), w, h, n, 0, C.byref(cam), first_slot))
 
+    def frames_rgbd_ptr(self, color_ptr, channels, depth_ptr, depth_is_u16, nframes, width, height, cam, rgb_order=True,
+                        depth_factor=1.0, on_device=True, first_slot=0):
+        """raw-pointer form (device or pinned host memory), dense layouts"""
+        es = 2 if depth_is_u16 else 4
+        check(lib().orbx_frames_rgbd(self.h, C.c_void_p(color_ptr), channels, int(rgb_order), C.c_size_t(height * width * channels),
+                                     C.c_size_t(width * channels), C.c_void_p(depth_ptr), int(depth_is_u16), C.c_float(depth_factor),
+                                     C.c_size_t(height * width * es), C.c_size_t(width * es), width, height, nframes, int(on_device),
+                                     C.byref(cam), first_slot))
+
     def download_frame_front(self, first_slot, nframes):
         kun = np.zeros((nframes, self.cap), KP_DTYPE)
         ur = np.zeros((nframes, self.cap), np.float32)

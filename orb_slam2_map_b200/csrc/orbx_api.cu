@@ -165,7 +165,7 @@ int orbx_create(const orbx_params* params, int max_width, int max_height, int ch
     h->dLevel0 = h->dStageLin = h->dRaw = h->dBlur = nullptr;
     h->dCand = h->dKeysA = h->dKeysB = nullptr; h->dCellSeg = nullptr; h->dLevelCandCount = nullptr;
     h->dLevelKps = nullptr; h->dLevelKpCount = nullptr; h->dStatus = nullptr;
-    h->dKpsUn = nullptr; h->storeUndistorted = false; h->bounds[0] = h->bounds[1] = h->bounds[2] = h->bounds[3] = 0.f;
+    h->dKpsUn = nullptr; h->storeUndistorted = false; h->dFrontStage = nullptr; h->frontStageBytes = 0; h->boundsValid = false; h->bounds[0] = h->bounds[1] = h->bounds[2] = h->bounds[3] = 0.f;
     h->dKps = nullptr; h->dDesc = nullptr; h->dCount = nullptr; h->dSlotLevelCount = nullptr;
     h->dGridStart = nullptr; h->dGridIdx = nullptr; h->dMatches12 = nullptr; h->dNMatches = nullptr;
     h->dNCompares = nullptr; h->dURight = nullptr; h->dDepth = nullptr; h->dMatchScratch = nullptr;
@@ -214,7 +214,7 @@ int orbx_destroy(orbx_handle* h)
     if (!h) return ORBX_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
-    void* ptrs[] = {h->dCells, h->dCoef, h->dBlurTiles, h->dKpMap, h->dKpsUn, h->dLevel0, h->dStageLin, h->dRaw, h->dBlur, h->dCand, h->dKeysA,
+    void* ptrs[] = {h->dCells, h->dCoef, h->dBlurTiles, h->dKpMap, h->dKpsUn, h->dFrontStage, h->dLevel0, h->dStageLin, h->dRaw, h->dBlur, h->dCand, h->dKeysA,
                     h->dKeysB, h->dCellSeg, h->dLevelCandCount, h->dLevelKps, h->dLevelKpCount, h->dStatus, h->dKps,
                     h->dDesc, h->dCount, h->dSlotLevelCount, h->dGridStart, h->dGridIdx, h->dMatches12, h->dNMatches,
                     h->dNCompares, h->dURight, h->dDepth, h->dMatchScratch};

@@ -12,6 +12,7 @@
 #include "orbx_internal.h"
 
 #include <algorithm>
+#include <cstring>
 
 typedef uint8_t u8;
 
@@ -259,22 +260,38 @@ int orbx_frames_rgbd(orbx_handle* h, const uint8_t* color, int channels, int rgb
     rc = orbx_ensure_match_buffers(h); if (rc) return rc;
     const size_t R = (size_t)h->resultSlots;
     if (!h->dKpsUn) ORBX_CUDA(cudaMalloc((void**)&h->dKpsUn, R * h->kpCap * sizeof(orbx_keypoint)));
-    // ComputeImageBounds once per call (the reference does it once per calibration, mbInitialComputations)
+    // ComputeImageBounds once per calibration and image size (mbInitialComputations, Frame.cc:170-186)
     float bounds[4];
-    rc = orbx_image_bounds(h, width, height, cam, bounds); if (rc) return rc;
+    {
+        const float key[11] = {cam->fx, cam->fy, cam->cx, cam->cy, cam->k1, cam->k2, cam->p1, cam->p2, cam->k3, (float)width, (float)height};
+        if (!h->boundsValid || memcmp(key, h->boundsKey, sizeof(key)) != 0) {
+            rc = orbx_image_bounds(h, width, height, cam, bounds); if (rc) return rc;
+            memcpy(h->boundsKey, key, sizeof(key));
+            for (int i = 0; i < 4; ++i) h->bounds[i] = bounds[i];
+            h->boundsValid = true;
+        }
+        for (int i = 0; i < 4; ++i) bounds[i] = h->bounds[i];
+    }
     cudaStream_t st = h->stream;
     const CamD cd = cam_double(cam);
     const int C = h->chunkFrames;
     const size_t gPitch = ((size_t)width + 15) & ~(size_t)15, gFrame = gPitch * height;
-    // staging: gray chunk (always), colour / depth chunks when they arrive from the host
-    FBuf dGray, dColor, dDepth;
+    // staging (kept in the handle): gray chunk, and colour / depth chunks when they arrive from the host
     const bool needGray = channels != 1 || !on_device;
-    if (needGray) { rc = dGray.alloc(gFrame * C); if (rc) return rc; }
     const size_t cRow = (size_t)width * channels, cFrame = cRow * height, zRow = (size_t)width * dElem, zFrame = zRow * height;
-    if (!on_device) {
-        if (channels != 1) { rc = dColor.alloc(cFrame * C); if (rc) return rc; }
-        rc = dDepth.alloc(zFrame * C); if (rc) return rc;
+    const size_t grayBytes = needGray ? ((gFrame * C + 255) & ~(size_t)255) : 0;
+    const size_t colorBytes = (!on_device && channels != 1) ? ((cFrame * C + 255) & ~(size_t)255) : 0;
+    const size_t depthBytes = !on_device ? ((zFrame * C + 255) & ~(size_t)255) : 0;
+    if (grayBytes + colorBytes + depthBytes > h->frontStageBytes) {
+        ORBX_CUDA(cudaStreamSynchronize(st));
+        if (h->dFrontStage) cudaFree(h->dFrontStage);
+        h->dFrontStage = nullptr; h->frontStageBytes = 0;
+        ORBX_CUDA(cudaMalloc((void**)&h->dFrontStage, grayBytes + colorBytes + depthBytes));
+        h->frontStageBytes = grayBytes + colorBytes + depthBytes;
     }
+    struct { u8* p; } dGray{h->dFrontStage}, dColor{h->dFrontStage + grayBytes}, dDepth{h->dFrontStage + grayBytes + colorBytes};
+    const bool denseColor = color_row_stride == cRow && color_frame_stride == cFrame && channels != 1;
+    const bool denseDepth = depth_row_stride == zRow && depth_frame_stride == zFrame;
     for (int f0 = 0; f0 < nframes; f0 += C) {
         const int nf = std::min(C, nframes - f0);
         const u8* csrc = color + (size_t)f0 * color_frame_stride;
@@ -282,10 +299,14 @@ int orbx_frames_rgbd(orbx_handle* h, const uint8_t* color, int channels, int rgb
         const u8* gsrc; size_t gfs, grs;
         const u8* zdev = zsrc; size_t zfs = depth_frame_stride, zrs = depth_row_stride;
         if (!on_device) {
-            for (int f = 0; f < nf; ++f) {
+            if (denseColor) ORBX_CUDA(cudaMemcpyAsync(dColor.p, csrc, cFrame * nf, cudaMemcpyHostToDevice, st));
+            if (denseDepth) ORBX_CUDA(cudaMemcpyAsync(dDepth.p, zsrc, zFrame * nf, cudaMemcpyHostToDevice, st));
+            for (int f = 0; f < nf && !(denseColor && denseDepth); ++f) {
                 u8* cdst = channels == 1 ? (u8*)dGray.p + f * gFrame : (u8*)dColor.p + f * cFrame;
-                ORBX_CUDA(cudaMemcpy2DAsync(cdst, channels == 1 ? gPitch : cRow, csrc + f * color_frame_stride, color_row_stride, cRow, height, cudaMemcpyHostToDevice, st));
-                ORBX_CUDA(cudaMemcpy2DAsync((u8*)dDepth.p + f * zFrame, zRow, zsrc + f * depth_frame_stride, depth_row_stride, zRow, height, cudaMemcpyHostToDevice, st));
+                if (!denseColor)
+                    ORBX_CUDA(cudaMemcpy2DAsync(cdst, channels == 1 ? gPitch : cRow, csrc + f * color_frame_stride, color_row_stride, cRow, height, cudaMemcpyHostToDevice, st));
+                if (!denseDepth)
+                    ORBX_CUDA(cudaMemcpy2DAsync((u8*)dDepth.p + f * zFrame, zRow, zsrc + f * depth_frame_stride, depth_row_stride, zRow, height, cudaMemcpyHostToDevice, st));
             }
             zdev = (const u8*)dDepth.p; zfs = zFrame; zrs = zRow;
         }
@@ -305,11 +326,9 @@ int orbx_frames_rgbd(orbx_handle* h, const uint8_t* color, int channels, int rgb
                                                                               depth_is_u16, depth_factor, depth_factor != 1.0f, (long long)zfs,
                                                                               (long long)zrs, h->dKpsUn, h->dURight, h->dDepth);
         ORBX_CUDA(cudaGetLastError());
-        if (!on_device) ORBX_CUDA(cudaStreamSynchronize(st));      // the staging buffers are reused by the next chunk
     }
     // the store now describes undistorted frames: matchers and the grid use mvKeysUn and these bounds
     h->storeUndistorted = true;
-    for (int i = 0; i < 4; ++i) h->bounds[i] = bounds[i];
     rc = orbx_build_grids(h, first_slot, nframes, width, height);
     if (rc) return rc;
     ORBX_CUDA(cudaStreamSynchronize(st));

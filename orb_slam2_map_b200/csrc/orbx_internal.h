@@ -126,6 +126,10 @@ struct orbx_handle {
     orbx_keypoint* dKpsUn;
     bool storeUndistorted;
     float bounds[4];        // mnMinX, mnMaxX, mnMinY, mnMaxY of the undistorted frames
+    uint8_t* dFrontStage;   // gray / colour / depth staging of orbx_frames_rgbd (grown on demand)
+    size_t frontStageBytes;
+    float boundsKey[11];    // camera + image size the cached bounds belong to
+    bool boundsValid;
     // frame grid (per slot)
     unsigned short* dGridStart;   // [slot][GRID_CELLS+1]
     unsigned short* dGridIdx;     // [slot][kpCap]
