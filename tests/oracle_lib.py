@@ -56,8 +56,8 @@ class StereoInput(C.Structure):
 def build_oracle(force: bool = False) -> str:
     so = os.path.join(ORACLE_DIR, "liborb_oracle.so")
     src = os.path.join(ORACLE_DIR, "orb_oracle.cpp")
-    src2 = os.path.join(ORACLE_DIR, "frame_oracle.cpp")
-    if force or not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(src), os.path.getmtime(src2)):
+    srcs = [src, os.path.join(ORACLE_DIR, "frame_oracle.cpp"), os.path.join(ORACLE_DIR, "bow_oracle.cpp")]
+    if force or not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", ORACLE_DIR, "liborb_oracle.so"], stdout=subprocess.DEVNULL)
     return so
 
@@ -342,3 +342,56 @@ def stereo_from_rgbd(keys_xy: np.ndarray, keys_un_xy: np.ndarray, depth: np.ndar
     ur = np.empty(n, np.float32); z = np.empty(n, np.float32)
     lib().oracle_stereo_from_rgbd(_p(keys_xy), _p(keys_un_xy), n, _p(depth), w, h, C.c_size_t(w), C.c_float(bf), _p(ur), _p(z))
     return ur, z
+
+
+# ---- bag-of-words path (oracle/bow_oracle.cpp) ----------------------------------------------------------
+def make_vocabulary(k=8, depth=3, seed=0, stop_fraction=0.05):
+    """Synthetic DBoW2-shaped vocabulary (the reference's ORBvoc is not shipped): a k-ary tree of the given depth,
+    node descriptors = the parent's with ~40 random bits flipped, leaves numbered as words with positive idf-like
+    weights (a few 0 = stopped words).  Returned flattened, node 0 = root."""
+    rng = np.random.default_rng(seed)
+    desc = [np.zeros(32, np.uint8)]
+    child_begin, child_count, children, level = [0], [0], [], [0]
+    frontier = [0]
+    for lv in range(1, depth + 1):
+        nxt = []
+        for p in frontier:
+            child_begin[p] = len(children); child_count[p] = k
+            for _ in range(k):
+                nid = len(desc)
+                bits = np.unpackbits(desc[p] if p else rng.integers(0, 256, 32, dtype=np.uint8))
+                flip = rng.choice(256, 40, replace=False)
+                bits[flip] ^= 1
+                desc.append(np.packbits(bits))
+                child_begin.append(0); child_count.append(0); level.append(lv)
+                children.append(nid); nxt.append(nid)
+        frontier = nxt
+    n = len(desc)
+    word = np.zeros(n, np.uint32); weight = np.zeros(n, np.float64)
+    for w, nid in enumerate(frontier):
+        word[nid] = w
+        weight[nid] = 0.0 if rng.random() < stop_fraction else float(rng.uniform(0.5, 9.0))
+    return dict(nnodes=n, depth=depth, k=k, child_begin=np.array(child_begin, np.int32), child_count=np.array(child_count, np.int32),
+                children=np.array(children, np.int32), desc=np.ascontiguousarray(np.stack(desc)), word=word, weight=weight)
+
+
+def bow_transform(voc, feats: np.ndarray, levelsup: int):
+    feats = np.ascontiguousarray(feats, np.uint8)
+    n = len(feats)
+    wid = np.zeros(n, np.uint32); w = np.zeros(n, np.float64); nid = np.zeros(n, np.uint32)
+    lib().oracle_bow_transform(voc["nnodes"], _p(voc["child_begin"]), _p(voc["child_count"]), _p(voc["children"]), _p(voc["desc"]),
+                               _p(voc["word"]), _p(voc["weight"]), voc["depth"], _p(feats), n, levelsup, _p(wid), _p(w), _p(nid))
+    return wid, w, nid
+
+
+def search_by_bow(variant, descA, angleA, nodeA, flagsA, descB, angleB, nodeB, flagsB, nnratio=0.7, check_ori=True):
+    descA = np.ascontiguousarray(descA, np.uint8); descB = np.ascontiguousarray(descB, np.uint8)
+    angleA = np.ascontiguousarray(angleA, np.float32); angleB = np.ascontiguousarray(angleB, np.float32)
+    nodeA = np.ascontiguousarray(nodeA, np.uint32); nodeB = np.ascontiguousarray(nodeB, np.uint32)
+    flagsA = np.ascontiguousarray(flagsA, np.uint8); flagsB = np.ascontiguousarray(flagsB, np.uint8)
+    mA = np.empty(len(descA), np.int32); mB = np.empty(len(descB), np.int32)
+    L = lib()
+    L.oracle_search_by_bow.restype = C.c_int
+    n = L.oracle_search_by_bow(int(variant), len(descA), _p(descA), _p(angleA), _p(nodeA), _p(flagsA), len(descB), _p(descB), _p(angleB),
+                               _p(nodeB), _p(flagsB), C.c_float(nnratio), int(check_ori), _p(mA), _p(mB))
+    return n, mA, mB
