@@ -285,6 +285,56 @@ int orbx_frames_rgbd(orbx_handle* h, const uint8_t* color, int channels, int rgb
 int orbx_download_frame_front(orbx_handle* h, int first_slot, int nframes, orbx_keypoint* keys_un, float* u_right,
                               float* depth, int capacity, float bounds[4]);
 
+/* ================================================================================================
+ * Bag-of-words matcher path: DBoW2's per-feature transform and both
+ * ORBmatcher::SearchByBoW variants, flattened to plain arrays.
+ * ================================================================================================ */
+
+/* A DBoW2 vocabulary tree (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h) flattened: node 0 = root, the children of
+ * node i are children[child_begin[i] .. child_begin[i] + child_count[i]), child_count == 0 marks a leaf (word). */
+typedef struct orbm_vocabulary {
+    int nnodes;
+    int depth;                      /* m_L */
+    const int32_t* child_begin;     /* [nnodes] */
+    const int32_t* child_count;     /* [nnodes] */
+    const int32_t* children;        /* node ids */
+    const uint8_t* descriptors;     /* [nnodes][32] */
+    const uint32_t* word_id;        /* [nnodes], meaningful for leaves */
+    const double* weight;           /* [nnodes], WordValue of the leaf (0 = stopped word) */
+} orbm_vocabulary;
+typedef struct orbm_vocab_handle orbm_vocab_handle;
+
+int orbm_vocabulary_upload(const orbm_vocabulary* voc, int device, orbm_vocab_handle** out);
+int orbm_vocabulary_free(orbm_vocab_handle* v);
+
+/* TemplatedVocabulary::transform(feature, word_id, weight, &nid, levelsup) (TemplatedVocabulary.h:1231-1271, distance =
+ * FORB::distance FORB.cpp:81-101) for n features: what ::transform(features, BowVector&, FeatureVector&, levelsup)
+ * (:1140-1218, called from Frame::ComputeBoW src/Frame.cc:394-402) evaluates per feature.  The caller accumulates
+ * BowVector[word_id] += weight and FeatureVector[node_id].push_back(i) for the features with weight > 0.
+ * features: host, n x 32 bytes.  Outputs: host arrays of n. */
+int orbm_bow_transform(orbm_vocab_handle* v, const uint8_t* features, int n, int levelsup, uint32_t* word_id,
+                       double* weight, uint32_t* node_id);
+
+/* One side of SearchByBoW.  flags: bit 0 = the feature is in the FeatureVector (its word weight is > 0),
+ * bit 1 = the feature has a MapPoint that is not bad. */
+typedef struct orbm_bow_frame {
+    int n;
+    const uint8_t* descriptors;     /* n x 32 */
+    const float* angles;            /* mvKeysUn[i].angle */
+    const uint32_t* node_id;        /* FeatureVector node of feature i (orbm_bow_transform) */
+    const uint8_t* flags;
+} orbm_bow_frame;
+
+/* ORBmatcher::SearchByBoW, npairs independent frame pairs per call (one CTA each).
+ * variant 0 = (KeyFrame* pKF, Frame& F, vpMapPointMatches)  src/ORBmatcher.cc:159-288: a = keyframe, b = frame;
+ *             match_b[j] = keyframe feature whose MapPoint goes into vpMapPointMatches[j] (-1 = NULL).
+ * variant 1 = (KeyFrame* pKF1, KeyFrame* pKF2, vpMatches12) src/ORBmatcher.cc:522-655: match_a[i] = feature of KF2
+ *             whose MapPoint goes into vpMatches12[i].
+ * Both arrays are filled in both variants; pair p's entries start at the sum of the earlier pairs' a[].n / b[].n.
+ * nmatches: npairs counts (the function's return value in the reference).  All pointers are host pointers. */
+int orbm_search_by_bow(int variant, const orbm_bow_frame* a, const orbm_bow_frame* b, int npairs, float nnratio,
+                       int check_orientation, int device, int32_t* match_a, int32_t* match_b, int32_t* nmatches);
+
 #ifdef __cplusplus
 }
 #endif

@@ -62,6 +62,7 @@ EXPORTS = [
     "orbm_compute_stereo_matches", "orbm_knn2_device", "orbm_knn2_merge_device", "orbm_knn2_set_variant",
     "orbx_cvt_gray", "orbx_depth_to_float", "orbx_undistort_points", "orbx_image_bounds", "orbx_frames_rgbd",
     "orbx_download_frame_front",
+    "orbm_vocabulary_upload", "orbm_vocabulary_free", "orbm_bow_transform", "orbm_search_by_bow",
 ]
 
 
@@ -420,3 +421,62 @@ def knn2_device(q_ptr, nq, db_ptr, ndb, offset, out_dist_ptr, out_idx_ptr, strea
 def knn2_merge_device(pd_ptr, pi_ptr, nparts, nq, od_ptr, oi_ptr, stream=None):
     check(lib().orbm_knn2_merge_device(C.c_void_p(pd_ptr), C.c_void_p(pi_ptr), nparts, nq, C.c_void_p(od_ptr),
                                        C.c_void_p(oi_ptr), C.c_void_p(stream) if stream else None))
+
+
+# ---- bag-of-words path (orbx_bow.cu) -------------------------------------------------------------------
+class VocabularyStruct(C.Structure):
+    _fields_ = [("nnodes", C.c_int), ("depth", C.c_int), ("child_begin", C.c_void_p), ("child_count", C.c_void_p),
+                ("children", C.c_void_p), ("descriptors", C.c_void_p), ("word_id", C.c_void_p), ("weight", C.c_void_p)]
+
+
+class BowFrameStruct(C.Structure):
+    _fields_ = [("n", C.c_int), ("descriptors", C.c_void_p), ("angles", C.c_void_p), ("node_id", C.c_void_p), ("flags", C.c_void_p)]
+
+
+class Vocabulary:
+    """Device copy of a flattened DBoW2 vocabulary tree (dict of numpy arrays: child_begin, child_count, children,
+    desc, word, weight + nnodes, depth)."""
+
+    def __init__(self, voc: dict, device=0):
+        self._keep = {k: np.ascontiguousarray(voc[k], dt) for k, dt in (("child_begin", np.int32), ("child_count", np.int32),
+                      ("children", np.int32), ("desc", np.uint8), ("word", np.uint32), ("weight", np.float64))}
+        k = self._keep
+        st = VocabularyStruct(int(voc["nnodes"]), int(voc["depth"]), k["child_begin"].ctypes.data, k["child_count"].ctypes.data,
+                              k["children"].ctypes.data, k["desc"].ctypes.data, k["word"].ctypes.data, k["weight"].ctypes.data)
+        self.h = C.c_void_p()
+        check(lib().orbm_vocabulary_upload(C.byref(st), device, C.byref(self.h)))
+
+    def transform(self, feats: np.ndarray, levelsup: int):
+        feats = np.ascontiguousarray(feats, np.uint8)
+        n = len(feats)
+        wid = np.zeros(n, np.uint32); w = np.zeros(n, np.float64); nid = np.zeros(n, np.uint32)
+        check(lib().orbm_bow_transform(self.h, feats.ctypes.data_as(C.c_void_p), n, levelsup, wid.ctypes.data_as(C.c_void_p),
+                                       w.ctypes.data_as(C.c_void_p), nid.ctypes.data_as(C.c_void_p)))
+        return wid, w, nid
+
+    def close(self):
+        if self.h:
+            lib().orbm_vocabulary_free(self.h)
+            self.h = None
+
+
+def search_by_bow(variant, pairs, nnratio=0.7, check_ori=True, device=0):
+    """pairs: list of ((descA, angleA, nodeA, flagsA), (descB, angleB, nodeB, flagsB)); returns per pair (n, matchA, matchB)"""
+    keep = []
+    def frame(t):
+        d, a, nd, fl = (np.ascontiguousarray(t[0], np.uint8), np.ascontiguousarray(t[1], np.float32),
+                        np.ascontiguousarray(t[2], np.uint32), np.ascontiguousarray(t[3], np.uint8))
+        keep.append((d, a, nd, fl))
+        return BowFrameStruct(len(d), d.ctypes.data, a.ctypes.data, nd.ctypes.data, fl.ctypes.data)
+    A = (BowFrameStruct * len(pairs))(*[frame(p[0]) for p in pairs])
+    B = (BowFrameStruct * len(pairs))(*[frame(p[1]) for p in pairs])
+    totA = sum(len(p[0][0]) for p in pairs); totB = sum(len(p[1][0]) for p in pairs)
+    mA = np.zeros(max(totA, 1), np.int32); mB = np.zeros(max(totB, 1), np.int32); nm = np.zeros(len(pairs), np.int32)
+    check(lib().orbm_search_by_bow(int(variant), A, B, len(pairs), C.c_float(nnratio), int(check_ori), device,
+                                   mA.ctypes.data_as(C.c_void_p), mB.ctypes.data_as(C.c_void_p), nm.ctypes.data_as(C.c_void_p)))
+    out, oa, ob = [], 0, 0
+    for i, p in enumerate(pairs):
+        na, nb = len(p[0][0]), len(p[1][0])
+        out.append((int(nm[i]), mA[oa:oa + na].copy(), mB[ob:ob + nb].copy()))
+        oa += na; ob += nb
+    return out

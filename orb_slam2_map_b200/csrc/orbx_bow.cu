@@ -1,0 +1,300 @@
+// orbx_bow.cu — the bag-of-words matcher path as sm_100a kernels behind the C ABI:
+//
+//   K16 bow_transform_kernel   DBoW2 TemplatedVocabulary::transform(feature, word, weight, nid, levelsup)
+//                              Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1231-1271, FORB::distance FORB.cpp:81-101
+//   K17 search_bow_kernel      ORBmatcher::SearchByBoW (KeyFrame, Frame) src/ORBmatcher.cc:159-288 and
+//                              (KeyFrame, KeyFrame) src/ORBmatcher.cc:522-655
+//
+// K16: one warp per feature, lane = child of the current node (first minimum wins, as the reference's scan).
+// K17: one CTA per frame pair.  DBoW2's FeatureVector (std::map node -> ascending feature indices) becomes a block
+// bitonic sort of (node << 32 | index) keys; the reference's merge of the two maps visits exactly the common nodes,
+// and a candidate feature belongs to one node only, so nodes are independent: one warp per node run replays the
+// run's keyframe features in order (the "already matched" skip is sequential inside a node), lanes over the
+// candidates, best / second-best by warp shuffle.  Rotation histogram + ComputeThreeMaxima cull at the end.
+
+#include "orbx_internal.h"
+#include "orbx_match_common.cuh"
+
+#include <algorithm>
+#include <vector>
+
+struct orbm_vocab_handle {
+    int device, nnodes, depth;
+    int32_t* childBegin; int32_t* childCount; int32_t* children;
+    u8* desc; uint32_t* word; double* weight;
+};
+
+__global__ void __launch_bounds__(256)
+bow_transform_kernel(const int32_t* __restrict__ childBegin, const int32_t* __restrict__ childCount,
+                     const int32_t* __restrict__ children, const u8* __restrict__ nodeDesc,
+                     const uint32_t* __restrict__ nodeWord, const double* __restrict__ nodeWeight, int depth,
+                     const u8* __restrict__ feats, int n, int levelsup, uint32_t* __restrict__ wordOut,
+                     double* __restrict__ weightOut, uint32_t* __restrict__ nodeOut)
+{
+    const int lane = threadIdx.x & 31, f = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (f >= n) return;
+    uint32_t q[8];
+    load_desc(q, feats + (size_t)f * 32);
+    const int nidLevel = depth - levelsup;
+    int finalId = 0, level = 0;
+    uint32_t nid = 0;
+    do {
+        ++level;
+        const int beg = childBegin[finalId], cnt = childCount[finalId];
+        unsigned best = 0xffffffffu;                 // (distance << 16 | child position): first minimum wins
+        for (int c = lane; c < cnt; c += 32) {
+            const int id = children[beg + c];
+            const unsigned key = ((unsigned)hamming256(q, reinterpret_cast<const uint32_t*>(nodeDesc + (size_t)id * 32)) << 16) | (unsigned)c;
+            best = min(best, key);
+        }
+        for (int d = 16; d > 0; d >>= 1) best = min(best, __shfl_xor_sync(FULL, best, d));
+        finalId = children[beg + (best & 0xffff)];
+        if (level == nidLevel) nid = (uint32_t)finalId;
+    } while (childCount[finalId] != 0);
+    if (lane == 0) { wordOut[f] = nodeWord[finalId]; weightOut[f] = nodeWeight[finalId]; nodeOut[f] = nid; }
+}
+
+#define BOW_THREADS 256
+struct BowPair { int offA, nA, offB, nB; };
+
+__device__ void block_bitonic_sort64(unsigned long long* a, int cap)
+{
+    for (int k = 2; k <= cap; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < cap; i += BOW_THREADS) {
+                const int l = i ^ j;
+                if (l > i) {
+                    const unsigned long long x = a[i], y = a[l];
+                    if ((x > y) == ((i & k) == 0)) { a[i] = y; a[l] = x; }
+                }
+            }
+            __syncthreads();
+        }
+}
+
+__global__ void __launch_bounds__(BOW_THREADS)
+search_bow_kernel(int variant, const BowPair* __restrict__ pairs, const u8* __restrict__ descA, const float* __restrict__ angA,
+                  const uint32_t* __restrict__ nodeA, const u8* __restrict__ flagA, const u8* __restrict__ descB,
+                  const float* __restrict__ angB, const uint32_t* __restrict__ nodeB, const u8* __restrict__ flagB,
+                  float nnratio, int checkOri, int capA, int capB, int32_t* __restrict__ matchA, int32_t* __restrict__ matchB,
+                  int32_t* __restrict__ nmatchesOut)
+{
+    extern __shared__ __align__(16) unsigned char smraw[];
+    __shared__ int sHist[ORBX_HISTO_LENGTH], sCount, sRuns, sInd[3];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const BowPair P = pairs[blockIdx.x];
+    unsigned long long* keysA = reinterpret_cast<unsigned long long*>(smraw);
+    unsigned long long* keysB = keysA + capA;
+    unsigned short* runs = reinterpret_cast<unsigned short*>(keysB + capB);      // start positions of the node runs of A
+    u8* matchedB = reinterpret_cast<u8*>(runs + capA);
+    u8* binOf = matchedB + capB;
+    descA += (size_t)P.offA * 32; angA += P.offA; nodeA += P.offA; flagA += P.offA; matchA += P.offA;
+    descB += (size_t)P.offB * 32; angB += P.offB; nodeB += P.offB; flagB += P.offB; matchB += P.offB;
+    int pa = 1; while (pa < P.nA) pa <<= 1;
+    int pb = 1; while (pb < P.nB) pb <<= 1;
+    for (int i = tid; i < pa; i += BOW_THREADS)
+        keysA[i] = (i < P.nA && (flagA[i] & 1)) ? (((unsigned long long)nodeA[i] << 32) | (unsigned)i) : ~0ull;
+    for (int i = tid; i < pb; i += BOW_THREADS)
+        keysB[i] = (i < P.nB && (flagB[i] & 1)) ? (((unsigned long long)nodeB[i] << 32) | (unsigned)i) : ~0ull;
+    for (int i = tid; i < P.nA; i += BOW_THREADS) { matchA[i] = -1; binOf[i] = 0xff; }
+    for (int i = tid; i < P.nB; i += BOW_THREADS) { matchB[i] = -1; matchedB[i] = 0; }
+    if (tid < ORBX_HISTO_LENGTH) sHist[tid] = 0;
+    if (tid == 0) { sCount = 0; sRuns = 0; }
+    __syncthreads();
+    block_bitonic_sort64(keysA, pa);
+    block_bitonic_sort64(keysB, pb);
+    // node runs of A (any order: nodes are independent)
+    for (int i = tid; i < P.nA; i += BOW_THREADS) {
+        const unsigned long long k = keysA[i];
+        if (k != ~0ull && (i == 0 || (keysA[i - 1] >> 32) != (k >> 32))) runs[atomicAdd(&sRuns, 1)] = (unsigned short)i;
+    }
+    __syncthreads();
+    const int nRuns = sRuns;
+    int accepted = 0;
+    for (int r = wid; r < nRuns; r += BOW_THREADS / 32) {
+        const int a0 = runs[r];
+        const unsigned node = (unsigned)(keysA[a0] >> 32);
+        // B's run of the same node: [b0, b1)
+        int lo = 0, hi = pb;
+        const unsigned long long target = (unsigned long long)node << 32;
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (keysB[mid] < target) lo = mid + 1; else hi = mid; }
+        const int b0 = lo;
+        int b1 = b0;
+        while (b1 < pb && (unsigned)(keysB[b1] >> 32) == node && keysB[b1] != ~0ull) ++b1;      // runs are short (tens of features)
+        if (b1 == b0) continue;
+        for (int ia = a0; ia < P.nA && keysA[ia] != ~0ull && (unsigned)(keysA[ia] >> 32) == node; ++ia) {
+            const int idxA = (int)(keysA[ia] & 0xffffffffu);
+            if (!(flagA[idxA] & 2)) continue;                     // !pMP || pMP->isBad()
+            uint32_t q[8];
+            load_desc(q, descA + (size_t)idxA * 32);
+            int best = 0x7fffffff, second = 0x7fffffff;
+            unsigned key = 0xffffffffu;
+            for (int jb = b0 + lane; jb < b1; jb += 32) {
+                const int idxB = (int)(keysB[jb] & 0xffffffffu);
+                if (matchedB[idxB]) continue;
+                if (variant == 1 && !(flagB[idxB] & 2)) continue;
+                const int dist = hamming256(q, reinterpret_cast<const uint32_t*>(descB + (size_t)idxB * 32));
+                if (dist < best) { second = best; best = dist; key = (unsigned)jb; }
+                else if (dist < second) second = dist;
+            }
+            warp_top2(best, key, second);
+            best = min(best, 256); second = min(second, 256);     // bestDist1 = bestDist2 = 256 initially; a distance of 256 never wins
+            const bool found = best < 256;
+            const bool close = variant == 0 ? best <= ORBX_TH_LOW : best < ORBX_TH_LOW;
+            if (found && close && (float)best < __fmul_rn(nnratio, (float)second)) {
+                const int idxB = (int)(keysB[key] & 0xffffffffu);
+                if (lane == 0) {
+                    matchedB[idxB] = 1; matchA[idxA] = idxB; matchB[idxB] = idxA;
+                    if (checkOri) { const int bin = rot_bin(angA[idxA], angB[idxB]); binOf[idxA] = (u8)bin; atomicAdd(&sHist[bin], 1); }
+                }
+                ++accepted;
+                __syncwarp();
+            }
+        }
+    }
+    if (lane == 0 && accepted) atomicAdd(&sCount, accepted);
+    __syncthreads();
+    if (checkOri) {
+        if (tid == 0) { int i1, i2, i3; three_maxima(sHist, ORBX_HISTO_LENGTH, i1, i2, i3); sInd[0] = i1; sInd[1] = i2; sInd[2] = i3; }
+        __syncthreads();
+        int culled = 0;
+        for (int i = tid; i < P.nA; i += BOW_THREADS) {
+            const int b = binOf[i];
+            if (b != 0xff && b != sInd[0] && b != sInd[1] && b != sInd[2]) { matchB[matchA[i]] = -1; matchA[i] = -1; ++culled; }
+        }
+        if (culled) atomicSub(&sCount, culled);
+        __syncthreads();
+    }
+    if (tid == 0) nmatchesOut[blockIdx.x] = sCount;
+}
+
+struct BBuf {
+    void* p = nullptr;
+    ~BBuf() { if (p) cudaFree(p); }
+    int alloc(size_t bytes) { ORBX_CUDA(cudaMalloc(&p, bytes ? bytes : 4)); return ORBX_OK; }
+    template <typename T> T* as() { return (T*)p; }
+};
+
+extern "C" {
+
+int orbm_vocabulary_upload(const orbm_vocabulary* voc, int device, orbm_vocab_handle** out)
+{
+    if (!voc || !out || voc->nnodes < 2 || voc->depth < 1) { orbx_set_error("bad vocabulary"); return ORBX_E_INVALID; }
+    int ndev = 0;
+    ORBX_CUDA(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) { orbx_set_error("CUDA device %d not available (%d devices); no CPU fallback", device, ndev); return ORBX_E_CUDA; }
+    ORBX_CUDA(cudaSetDevice(device));
+    long long nchildren = 0;
+    for (int i = 0; i < voc->nnodes; ++i) {
+        if (voc->child_count[i] < 0 || voc->child_begin[i] < 0) { orbx_set_error("bad child table at node %d", i); return ORBX_E_INVALID; }
+        if (voc->child_count[i] > 0xffff) { orbx_set_error("more than 65535 children per node unsupported"); return ORBX_E_INVALID; }
+        nchildren = std::max(nchildren, (long long)voc->child_begin[i] + voc->child_count[i]);
+    }
+    if (voc->child_count[0] == 0) { orbx_set_error("the root has no children"); return ORBX_E_INVALID; }
+    orbm_vocab_handle* v = new orbm_vocab_handle();
+    v->device = device; v->nnodes = voc->nnodes; v->depth = voc->depth;
+    const size_t N = (size_t)voc->nnodes;
+    ORBX_CUDA(cudaMalloc((void**)&v->childBegin, N * 4)); ORBX_CUDA(cudaMalloc((void**)&v->childCount, N * 4));
+    ORBX_CUDA(cudaMalloc((void**)&v->children, std::max<size_t>(nchildren, 1) * 4));
+    ORBX_CUDA(cudaMalloc((void**)&v->desc, N * 32)); ORBX_CUDA(cudaMalloc((void**)&v->word, N * 4)); ORBX_CUDA(cudaMalloc((void**)&v->weight, N * 8));
+    ORBX_CUDA(cudaMemcpy(v->childBegin, voc->child_begin, N * 4, cudaMemcpyHostToDevice));
+    ORBX_CUDA(cudaMemcpy(v->childCount, voc->child_count, N * 4, cudaMemcpyHostToDevice));
+    ORBX_CUDA(cudaMemcpy(v->children, voc->children, (size_t)nchildren * 4, cudaMemcpyHostToDevice));
+    ORBX_CUDA(cudaMemcpy(v->desc, voc->descriptors, N * 32, cudaMemcpyHostToDevice));
+    ORBX_CUDA(cudaMemcpy(v->word, voc->word_id, N * 4, cudaMemcpyHostToDevice));
+    ORBX_CUDA(cudaMemcpy(v->weight, voc->weight, N * 8, cudaMemcpyHostToDevice));
+    *out = v;
+    return ORBX_OK;
+}
+
+int orbm_vocabulary_free(orbm_vocab_handle* v)
+{
+    if (!v) return ORBX_OK;
+    cudaSetDevice(v->device);
+    cudaFree(v->childBegin); cudaFree(v->childCount); cudaFree(v->children); cudaFree(v->desc); cudaFree(v->word); cudaFree(v->weight);
+    delete v;
+    return ORBX_OK;
+}
+
+int orbm_bow_transform(orbm_vocab_handle* v, const uint8_t* features, int n, int levelsup, uint32_t* word_id,
+                       double* weight, uint32_t* node_id)
+{
+    if (!v || !features || !word_id || !weight || !node_id) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
+    if (n <= 0) return ORBX_OK;
+    ORBX_CUDA(cudaSetDevice(v->device));
+    BBuf df, dw, dwt, dn;
+    int rc = df.alloc((size_t)n * 32); if (rc) return rc;
+    rc = dw.alloc((size_t)n * 4); if (rc) return rc;
+    rc = dwt.alloc((size_t)n * 8); if (rc) return rc;
+    rc = dn.alloc((size_t)n * 4); if (rc) return rc;
+    ORBX_CUDA(cudaMemcpy(df.p, features, (size_t)n * 32, cudaMemcpyHostToDevice));
+    bow_transform_kernel<<<(n + 7) / 8, 256>>>(v->childBegin, v->childCount, v->children, v->desc, v->word, v->weight, v->depth,
+                                               df.as<u8>(), n, levelsup, dw.as<uint32_t>(), dwt.as<double>(), dn.as<uint32_t>());
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaMemcpy(word_id, dw.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    ORBX_CUDA(cudaMemcpy(weight, dwt.p, (size_t)n * 8, cudaMemcpyDeviceToHost));
+    ORBX_CUDA(cudaMemcpy(node_id, dn.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    return ORBX_OK;
+}
+
+int orbm_search_by_bow(int variant, const orbm_bow_frame* a, const orbm_bow_frame* b, int npairs, float nnratio,
+                       int check_orientation, int device, int32_t* match_a, int32_t* match_b, int32_t* nmatches)
+{
+    if (!a || !b || !match_a || !match_b || !nmatches) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
+    if (variant != 0 && variant != 1) { orbx_set_error("variant must be 0 (KeyFrame, Frame) or 1 (KeyFrame, KeyFrame)"); return ORBX_E_INVALID; }
+    if (npairs <= 0) return ORBX_OK;
+    int ndev = 0;
+    ORBX_CUDA(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) { orbx_set_error("CUDA device %d not available (%d devices); no CPU fallback", device, ndev); return ORBX_E_CUDA; }
+    ORBX_CUDA(cudaSetDevice(device));
+    std::vector<BowPair> pairs(npairs);
+    long long totA = 0, totB = 0;
+    int maxA = 1, maxB = 1;
+    for (int p = 0; p < npairs; ++p) {
+        if (a[p].n < 0 || b[p].n < 0 || a[p].n > 0xffff || b[p].n > 0xffff) { orbx_set_error("pair %d: 0..65535 features per frame", p); return ORBX_E_INVALID; }
+        pairs[p] = BowPair{(int)totA, a[p].n, (int)totB, b[p].n};
+        totA += a[p].n; totB += b[p].n;
+        maxA = std::max(maxA, a[p].n); maxB = std::max(maxB, b[p].n);
+    }
+    int capA = 1; while (capA < maxA) capA <<= 1;
+    int capB = 1; while (capB < maxB) capB <<= 1;
+    const size_t smem = (size_t)(capA + capB) * 8 + (size_t)capA * 2 + capB + capA + 16;
+    if (smem > 220 * 1024) { orbx_set_error("frames of %d / %d features exceed the shared-memory sort (%zu bytes)", maxA, maxB, smem); return ORBX_E_CAPACITY; }
+    BBuf dPairs, dDescA, dAngA, dNodeA, dFlagA, dDescB, dAngB, dNodeB, dFlagB, dMA, dMB, dNM;
+    int rc;
+#define BOW_ALLOC(buf, bytes) rc = buf.alloc(bytes); if (rc) return rc
+    BOW_ALLOC(dPairs, npairs * sizeof(BowPair));
+    BOW_ALLOC(dDescA, (size_t)totA * 32); BOW_ALLOC(dAngA, (size_t)totA * 4); BOW_ALLOC(dNodeA, (size_t)totA * 4); BOW_ALLOC(dFlagA, (size_t)totA);
+    BOW_ALLOC(dDescB, (size_t)totB * 32); BOW_ALLOC(dAngB, (size_t)totB * 4); BOW_ALLOC(dNodeB, (size_t)totB * 4); BOW_ALLOC(dFlagB, (size_t)totB);
+    BOW_ALLOC(dMA, (size_t)totA * 4); BOW_ALLOC(dMB, (size_t)totB * 4); BOW_ALLOC(dNM, (size_t)npairs * 4);
+#undef BOW_ALLOC
+    ORBX_CUDA(cudaMemcpy(dPairs.p, pairs.data(), npairs * sizeof(BowPair), cudaMemcpyHostToDevice));
+    for (int p = 0; p < npairs; ++p) {
+        const BowPair& P = pairs[p];
+        if (P.nA) {
+            if (!a[p].descriptors || !a[p].angles || !a[p].node_id || !a[p].flags) { orbx_set_error("pair %d: null array in a", p); return ORBX_E_INVALID; }
+            ORBX_CUDA(cudaMemcpy(dDescA.as<u8>() + (size_t)P.offA * 32, a[p].descriptors, (size_t)P.nA * 32, cudaMemcpyHostToDevice));
+            ORBX_CUDA(cudaMemcpy(dAngA.as<float>() + P.offA, a[p].angles, (size_t)P.nA * 4, cudaMemcpyHostToDevice));
+            ORBX_CUDA(cudaMemcpy(dNodeA.as<uint32_t>() + P.offA, a[p].node_id, (size_t)P.nA * 4, cudaMemcpyHostToDevice));
+            ORBX_CUDA(cudaMemcpy(dFlagA.as<u8>() + P.offA, a[p].flags, (size_t)P.nA, cudaMemcpyHostToDevice));
+        }
+        if (P.nB) {
+            if (!b[p].descriptors || !b[p].angles || !b[p].node_id || !b[p].flags) { orbx_set_error("pair %d: null array in b", p); return ORBX_E_INVALID; }
+            ORBX_CUDA(cudaMemcpy(dDescB.as<u8>() + (size_t)P.offB * 32, b[p].descriptors, (size_t)P.nB * 32, cudaMemcpyHostToDevice));
+            ORBX_CUDA(cudaMemcpy(dAngB.as<float>() + P.offB, b[p].angles, (size_t)P.nB * 4, cudaMemcpyHostToDevice));
+            ORBX_CUDA(cudaMemcpy(dNodeB.as<uint32_t>() + P.offB, b[p].node_id, (size_t)P.nB * 4, cudaMemcpyHostToDevice));
+            ORBX_CUDA(cudaMemcpy(dFlagB.as<u8>() + P.offB, b[p].flags, (size_t)P.nB, cudaMemcpyHostToDevice));
+        }
+    }
+    if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(search_bow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    search_bow_kernel<<<npairs, BOW_THREADS, smem>>>(variant, dPairs.as<BowPair>(), dDescA.as<u8>(), dAngA.as<float>(), dNodeA.as<uint32_t>(),
+                                                     dFlagA.as<u8>(), dDescB.as<u8>(), dAngB.as<float>(), dNodeB.as<uint32_t>(), dFlagB.as<u8>(),
+                                                     nnratio, check_orientation, capA, capB, dMA.as<int32_t>(), dMB.as<int32_t>(), dNM.as<int32_t>());
+    ORBX_CUDA(cudaGetLastError());
+    if (totA) ORBX_CUDA(cudaMemcpy(match_a, dMA.p, (size_t)totA * 4, cudaMemcpyDeviceToHost));
+    if (totB) ORBX_CUDA(cudaMemcpy(match_b, dMB.p, (size_t)totB * 4, cudaMemcpyDeviceToHost));
+    ORBX_CUDA(cudaMemcpy(nmatches, dNM.p, (size_t)npairs * 4, cudaMemcpyDeviceToHost));
+    return ORBX_OK;
+}
+
+} // extern "C"
