@@ -335,6 +335,14 @@ typedef struct orbm_bow_frame {
 int orbm_search_by_bow(int variant, const orbm_bow_frame* a, const orbm_bow_frame* b, int npairs, float nnratio,
                        int check_orientation, int device, int32_t* match_a, int32_t* match_b, int32_t* nmatches);
 
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-305) for npoints map points
+ * per call: point p owns descriptors offsets[p] .. offsets[p+1] of `descriptors` (its observations in good keyframes,
+ * in the order the caller walked mObservations).  best_idx[p] = index inside the group of the descriptor with the
+ * least median Hamming distance to the others (first minimum; -1 for an empty group); best_median (may be NULL)
+ * receives that median.  Host pointers. */
+int orbm_distinctive_descriptors(const uint8_t* descriptors, const int32_t* offsets, int npoints, int device,
+                                 int32_t* best_idx, int32_t* best_median);
+
 #ifdef __cplusplus
 }
 #endif

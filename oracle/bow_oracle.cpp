@@ -4,6 +4,7 @@
 //   oracle_bow_transform      DBoW2 TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup)
 //                             Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1231-1271 with FORB::distance
 //                             (FORB.cpp:81-101), per feature, as ::transform(features, v, fv, levelsup) :1140-1218 calls it
+//   oracle_distinctive        MapPoint::ComputeDistinctiveDescriptors                src/MapPoint.cc:242-305
 //   oracle_search_by_bow      ORBmatcher::SearchByBoW(KeyFrame*, Frame&, ...)        src/ORBmatcher.cc:159-288 (variant 0)
 //                             ORBmatcher::SearchByBoW(KeyFrame*, KeyFrame*, ...)     src/ORBmatcher.cc:522-655 (variant 1)
 //
@@ -11,6 +12,8 @@
 // .MISSING_LARGE_BLOBS); the control flow follows the reference line by line with std::map in node order exactly
 // like DBoW2::FeatureVector, and tests/test_oracle_bow.py checks it against an independent Python statement.
 
+#include <algorithm>
+#include <climits>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -142,6 +145,35 @@ int oracle_search_by_bow(int variant, int nA, const uint8_t* descA, const float*
         }
     }
     return nmatches;
+}
+
+// MapPoint::ComputeDistinctiveDescriptors for npoints map points: point p owns descriptors offsets[p] .. offsets[p+1]
+// (its observations in good keyframes, in the std::map order the caller walked); best_idx[p] = index inside the group of
+// the descriptor with the least median distance to the others (-1 for an empty group), best_median[p] = that median.
+void oracle_distinctive(const uint8_t* desc, const int32_t* offsets, int npoints, int32_t* best_idx, int32_t* best_median)
+{
+    for (int p = 0; p < npoints; ++p) {
+        const uint8_t* d = desc + (size_t)offsets[p] * 32;
+        const size_t N = (size_t)(offsets[p + 1] - offsets[p]);
+        if (N == 0) { best_idx[p] = -1; best_median[p] = -1; continue; }
+        std::vector<float> Distances(N * N);
+        for (size_t i = 0; i < N; i++) {
+            Distances[i * N + i] = 0;
+            for (size_t j = i + 1; j < N; j++) {
+                const int distij = distance256(d + i * 32, d + j * 32);
+                Distances[i * N + j] = (float)distij;
+                Distances[j * N + i] = (float)distij;
+            }
+        }
+        int BestMedian = INT_MAX, BestIdx = 0;
+        for (size_t i = 0; i < N; i++) {
+            std::vector<int> vDists(Distances.begin() + i * N, Distances.begin() + (i + 1) * N);
+            std::sort(vDists.begin(), vDists.end());
+            const int median = vDists[(size_t)(0.5 * (N - 1))];
+            if (median < BestMedian) { BestMedian = median; BestIdx = (int)i; }
+        }
+        best_idx[p] = BestIdx; best_median[p] = BestMedian;
+    }
 }
 
 } // extern "C"

@@ -62,7 +62,7 @@ EXPORTS = [
     "orbm_compute_stereo_matches", "orbm_knn2_device", "orbm_knn2_merge_device", "orbm_knn2_set_variant",
     "orbx_cvt_gray", "orbx_depth_to_float", "orbx_undistort_points", "orbx_image_bounds", "orbx_frames_rgbd",
     "orbx_download_frame_front",
-    "orbm_vocabulary_upload", "orbm_vocabulary_free", "orbm_bow_transform", "orbm_search_by_bow",
+    "orbm_vocabulary_upload", "orbm_vocabulary_free", "orbm_bow_transform", "orbm_search_by_bow", "orbm_distinctive_descriptors",
 ]
 
 
@@ -480,3 +480,14 @@ def search_by_bow(variant, pairs, nnratio=0.7, check_ori=True, device=0):
         out.append((int(nm[i]), mA[oa:oa + na].copy(), mB[ob:ob + nb].copy()))
         oa += na; ob += nb
     return out
+
+
+def distinctive_descriptors(desc: np.ndarray, offsets: np.ndarray, device=0):
+    """MapPoint::ComputeDistinctiveDescriptors for len(offsets)-1 groups of descriptors"""
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    offsets = np.ascontiguousarray(offsets, np.int32)
+    n = len(offsets) - 1
+    idx = np.zeros(n, np.int32); med = np.zeros(n, np.int32)
+    check(lib().orbm_distinctive_descriptors(desc.ctypes.data_as(C.c_void_p), offsets.ctypes.data_as(C.c_void_p), n, device,
+                                             idx.ctypes.data_as(C.c_void_p), med.ctypes.data_as(C.c_void_p)))
+    return idx, med

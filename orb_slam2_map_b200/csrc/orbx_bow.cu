@@ -4,6 +4,7 @@
 //                              Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1231-1271, FORB::distance FORB.cpp:81-101
 //   K17 search_bow_kernel      ORBmatcher::SearchByBoW (KeyFrame, Frame) src/ORBmatcher.cc:159-288 and
 //                              (KeyFrame, KeyFrame) src/ORBmatcher.cc:522-655
+//   K18 distinctive_kernel     MapPoint::ComputeDistinctiveDescriptors src/MapPoint.cc:242-305 (rank 4)
 //
 // K16: one warp per feature, lane = child of the current node (first minimum wins, as the reference's scan).
 // K17: one CTA per frame pair.  DBoW2's FeatureVector (std::map node -> ascending feature indices) becomes a block
@@ -168,6 +169,48 @@ search_bow_kernel(int variant, const BowPair* __restrict__ pairs, const u8* __re
     if (tid == 0) nmatchesOut[blockIdx.x] = sCount;
 }
 
+// K18: one CTA per map point.  Thread i owns row i of the N x N distance matrix and finds its median
+// (the element at sorted position int(0.5*(N-1))) by bisection over the value range 0..256 — distances are
+// recomputed per step from the descriptors staged in shared memory, nothing of size N x N is stored.
+#define DD_THREADS 128
+#define DD_SMEM_DESC 2048           // descriptors staged in shared memory (64 KB); larger groups read global memory
+__global__ void __launch_bounds__(DD_THREADS)
+distinctive_kernel(const u8* __restrict__ desc, const int32_t* __restrict__ offsets, int32_t* __restrict__ bestIdx,
+                   int32_t* __restrict__ bestMedian)
+{
+    extern __shared__ __align__(16) unsigned char smraw[];
+    __shared__ unsigned sBest;
+    const int p = blockIdx.x, tid = threadIdx.x;
+    const int o = offsets[p], N = offsets[p + 1] - o;
+    if (N <= 0) { if (tid == 0) { bestIdx[p] = -1; if (bestMedian) bestMedian[p] = -1; } return; }
+    const u8* d = desc + (size_t)o * 32;
+    const bool staged = N <= DD_SMEM_DESC;
+    if (staged) {
+        for (int i = tid; i < N * 2; i += DD_THREADS) reinterpret_cast<uint4*>(smraw)[i] = reinterpret_cast<const uint4*>(d)[i];
+        d = smraw;
+    }
+    if (tid == 0) sBest = 0xffffffffu;
+    __syncthreads();
+    const int m = (int)(0.5 * (double)(N - 1));                 // vDists[0.5*(N-1)]
+    unsigned mine = 0xffffffffu;
+    for (int i = tid; i < N; i += DD_THREADS) {
+        uint32_t q[8];
+        load_desc(q, d + (size_t)i * 32);
+        int lo = 0, hi = 256;                                   // smallest t with #(dist <= t) >= m + 1
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            int cnt = 0;
+            for (int j = 0; j < N; ++j) cnt += hamming256(q, reinterpret_cast<const uint32_t*>(d + (size_t)j * 32)) <= mid;
+            if (cnt >= m + 1) hi = mid; else lo = mid + 1;
+        }
+        mine = min(mine, ((unsigned)lo << 16) | (unsigned)i);   // N <= 65535 (host check); first minimum wins
+    }
+    for (int s = 16; s > 0; s >>= 1) mine = min(mine, __shfl_xor_sync(FULL, mine, s));
+    if ((tid & 31) == 0) atomicMin(&sBest, mine);
+    __syncthreads();
+    if (tid == 0) { bestIdx[p] = (int)(sBest & 0xffff); if (bestMedian) bestMedian[p] = (int)(sBest >> 16); }
+}
+
 struct BBuf {
     void* p = nullptr;
     ~BBuf() { if (p) cudaFree(p); }
@@ -294,6 +337,41 @@ int orbm_search_by_bow(int variant, const orbm_bow_frame* a, const orbm_bow_fram
     if (totA) ORBX_CUDA(cudaMemcpy(match_a, dMA.p, (size_t)totA * 4, cudaMemcpyDeviceToHost));
     if (totB) ORBX_CUDA(cudaMemcpy(match_b, dMB.p, (size_t)totB * 4, cudaMemcpyDeviceToHost));
     ORBX_CUDA(cudaMemcpy(nmatches, dNM.p, (size_t)npairs * 4, cudaMemcpyDeviceToHost));
+    return ORBX_OK;
+}
+
+int orbm_distinctive_descriptors(const uint8_t* descriptors, const int32_t* offsets, int npoints, int device,
+                                 int32_t* best_idx, int32_t* best_median)
+{
+    if (!offsets || !best_idx) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
+    if (npoints <= 0) return ORBX_OK;
+    int ndev = 0;
+    ORBX_CUDA(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) { orbx_set_error("CUDA device %d not available (%d devices); no CPU fallback", device, ndev); return ORBX_E_CUDA; }
+    ORBX_CUDA(cudaSetDevice(device));
+    int maxN = 0;
+    for (int p = 0; p < npoints; ++p) {
+        const int n = offsets[p + 1] - offsets[p];
+        if (n < 0 || n > 0xffff) { orbx_set_error("map point %d: 0..65535 observations", p); return ORBX_E_INVALID; }
+        maxN = std::max(maxN, n);
+    }
+    const size_t total = (size_t)(offsets[npoints] - offsets[0]);
+    if (total && !descriptors) { orbx_set_error("null descriptors"); return ORBX_E_INVALID; }
+    BBuf dDesc, dOff, dIdx, dMed;
+    int rc = dDesc.alloc(total * 32); if (rc) return rc;
+    rc = dOff.alloc((size_t)(npoints + 1) * 4); if (rc) return rc;
+    rc = dIdx.alloc((size_t)npoints * 4); if (rc) return rc;
+    rc = dMed.alloc((size_t)npoints * 4); if (rc) return rc;
+    std::vector<int32_t> rel(npoints + 1);
+    for (int p = 0; p <= npoints; ++p) rel[p] = offsets[p] - offsets[0];
+    if (total) ORBX_CUDA(cudaMemcpy(dDesc.p, descriptors + (size_t)offsets[0] * 32, total * 32, cudaMemcpyHostToDevice));
+    ORBX_CUDA(cudaMemcpy(dOff.p, rel.data(), (size_t)(npoints + 1) * 4, cudaMemcpyHostToDevice));
+    const int smem = std::min(maxN, DD_SMEM_DESC) * 32 + 16;
+    if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(distinctive_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    distinctive_kernel<<<npoints, DD_THREADS, smem>>>(dDesc.as<u8>(), dOff.as<int32_t>(), dIdx.as<int32_t>(), dMed.as<int32_t>());
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaMemcpy(best_idx, dIdx.p, (size_t)npoints * 4, cudaMemcpyDeviceToHost));
+    if (best_median) ORBX_CUDA(cudaMemcpy(best_median, dMed.p, (size_t)npoints * 4, cudaMemcpyDeviceToHost));
     return ORBX_OK;
 }
 

@@ -395,3 +395,12 @@ def search_by_bow(variant, descA, angleA, nodeA, flagsA, descB, angleB, nodeB, f
     n = L.oracle_search_by_bow(int(variant), len(descA), _p(descA), _p(angleA), _p(nodeA), _p(flagsA), len(descB), _p(descB), _p(angleB),
                                _p(nodeB), _p(flagsB), C.c_float(nnratio), int(check_ori), _p(mA), _p(mB))
     return n, mA, mB
+
+
+def distinctive_descriptors(desc: np.ndarray, offsets: np.ndarray):
+    desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+    offsets = np.ascontiguousarray(offsets, np.int32)
+    n = len(offsets) - 1
+    idx = np.zeros(n, np.int32); med = np.zeros(n, np.int32)
+    lib().oracle_distinctive(_p(desc), _p(offsets), n, _p(idx), _p(med))
+    return idx, med

@@ -45,3 +45,15 @@ def test_search_by_bow_batch(variant):
             assert n == n_o and np.array_equal(mA, mA_o) and np.array_equal(mB, mB_o)
             total += n
         assert total > 30
+
+
+def test_distinctive_descriptors():
+    rng = np.random.default_rng(8)
+    sizes = [1, 2, 3, 7, 0, 20, 64, 5, 130, 300, 33, 2500]
+    offsets = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    base = rng.integers(0, 256, (len(sizes), 32), dtype=np.uint8)
+    desc = np.concatenate([np.repeat(base[i][None], n, 0) for i, n in enumerate(sizes)])
+    desc ^= rng.integers(0, 256, desc.shape, dtype=np.uint8) & rng.integers(0, 256, desc.shape, dtype=np.uint8) & rng.integers(0, 256, desc.shape, dtype=np.uint8)
+    ig, mg = capi.distinctive_descriptors(desc, offsets)
+    io, mo = O.distinctive_descriptors(desc, offsets)
+    assert np.array_equal(ig, io) and np.array_equal(mg, mo)

@@ -115,3 +115,21 @@ def test_search_by_bow_matches_python(variant, check_ori):
             assert n == int((mA >= 0).sum()) == int((mB >= 0).sum())
             if seed == 0 and ratio == 0.9:
                 assert n > 20                      # the synthetic pair really matches
+
+
+def test_distinctive_descriptors_matches_numpy():
+    rng = np.random.default_rng(5)
+    sizes = [1, 2, 3, 7, 0, 20, 64, 5]
+    offsets = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    base = rng.integers(0, 256, 32, dtype=np.uint8)
+    desc = np.repeat(base[None], offsets[-1], 0)
+    flips = rng.integers(0, 256, desc.shape, dtype=np.uint8) & rng.integers(0, 256, desc.shape, dtype=np.uint8) & rng.integers(0, 256, desc.shape, dtype=np.uint8)
+    desc ^= flips
+    idx, med = O.distinctive_descriptors(desc, offsets)
+    for p, n in enumerate(sizes):
+        if n == 0:
+            assert idx[p] == -1; continue
+        d = desc[offsets[p]:offsets[p + 1]]
+        D = np.array([[_dist(a, b) for b in d] for a in d])
+        meds = np.sort(D, axis=1)[:, int(0.5 * (n - 1))]       # MapPoint.cc:291-293
+        assert idx[p] == int(np.argmin(meds)) and med[p] == int(meds.min())
