@@ -343,6 +343,53 @@ int orbm_search_by_bow(int variant, const orbm_bow_frame* a, const orbm_bow_fram
 int orbm_distinctive_descriptors(const uint8_t* descriptors, const int32_t* offsets, int npoints, int device,
                                  int32_t* best_idx, int32_t* best_median);
 
+/* ================================================================================================
+ * Keyframe-rate matchers: SearchForTriangulation, Fuse x2, SearchBySim3.
+ * Poses, projections and the MapPoint graph stay on the host (as for SearchByProjection above): the
+ * wrapper flattens what the search loops read, the kernels return indices, the wrapper replays the
+ * side effects (AddObservation / Replace / vpMatches12) in the reference's order.
+ * ================================================================================================ */
+
+/* A KeyFrame as these matchers read it. */
+typedef struct orbm_keyframe {
+    orbm_frame frame;               /* mvKeysUn, mDescriptors, mnMinX.., mvuRight, mvScaleFactors, nlevels */
+    const float* level_sigma2;      /* mvLevelSigma2 [nlevels]    (SearchForTriangulation)              */
+    const float* inv_level_sigma2;  /* mvInvLevelSigma2 [nlevels] (Fuse variant 0)                      */
+    const uint32_t* node_id;        /* FeatureVector node of feature i (SearchForTriangulation), else NULL */
+    const uint8_t* flags;           /* bit 0 = feature is in mFeatVec, bit 1 = GetMapPoint(i) != NULL; NULL = all 0 */
+} orbm_keyframe;
+
+/* ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:657-823; CheckDistEpipolarLine :140-157) for npairs
+ * (KF1, KF2) pairs (LocalMapping::CreateNewMapPoints walks the neighbours of one keyframe, src/LocalMapping.cc:240-268).
+ * f12: npairs x 9 floats (row-major F12); epipole: npairs x 2 floats (ex, ey of :664-670, computed by the caller).
+ * matches12: out, vMatches12 of every pair, pair p starts at the sum of the earlier kf1[].frame.n; the caller builds
+ * vMatchedPairs from it in index order (:812-820).  nmatches: npairs counts.  Host pointers. */
+int orbm_search_for_triangulation(const orbm_keyframe* kf1, const orbm_keyframe* kf2, int npairs, const float* f12,
+                                  const float* epipole, int only_stereo, int check_orientation, int device,
+                                  int32_t* matches12, int32_t* nmatches);
+
+enum {
+    ORBM_FUSE_MAPPOINTS = 0, /* Fuse(pKF, vpMapPoints, th)             src/ORBmatcher.cc:825-973: chi2 gate, <= TH_LOW   */
+    ORBM_FUSE_SIM3 = 1,      /* Fuse(pKF, Scw, vpPoints, th, vpReplace) src/ORBmatcher.cc:975-1100: no gate, <= TH_LOW   */
+    ORBM_FUSE_SIM3_LEG = 2   /* one direction of SearchBySim3            src/ORBmatcher.cc:1146-1220: no gate, <= TH_HIGH */
+};
+
+/* The per-MapPoint search of ORBmatcher::Fuse.  One query per MapPoint that passed the caller's projection tests
+ * (:844-892): (u, v), radius = th * mvScaleFactors[nPredictedLevel], u_right = u - bf*invz, level_lo = nPredictedLevel-1,
+ * level_hi = nPredictedLevel; the other orbm_proj_query fields are ignored.  best_idx[q] = the keypoint of
+ * KeyFrame::GetFeaturesInArea (src/KeyFrame.cc:607-646) order with the first least distance that passes the variant's
+ * gate and threshold, else -1; best_dist[q] = its distance (256 when no candidate).  Queries are independent. */
+int orbm_fuse(int variant, const orbm_keyframe* kf, const orbm_proj_query* queries, const uint8_t* query_desc, int nq,
+              int device, int32_t* best_idx, int32_t* best_dist);
+
+/* ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1102-1326): queries12 = MapPoints of KF1 (feature index index1[q])
+ * projected into KF2, queries21 the other way round, both prepared like orbm_fuse queries.  match12: out [kf1->frame.n],
+ * the KF2 feature whose MapPoint goes into vpMatches12[i1] after the agreement check (:1307-1322), or -1. */
+int orbm_search_by_sim3(const orbm_keyframe* kf1, const orbm_keyframe* kf2, const orbm_proj_query* queries12,
+                        const uint8_t* desc12, const int32_t* index1, int nq12, const orbm_proj_query* queries21,
+                        const uint8_t* desc21, const int32_t* index2, int nq21, int device, int32_t* match12,
+                        int32_t* nfound);
+
 #ifdef __cplusplus
 }
 #endif

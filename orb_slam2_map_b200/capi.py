@@ -63,6 +63,7 @@ EXPORTS = [
     "orbx_cvt_gray", "orbx_depth_to_float", "orbx_undistort_points", "orbx_image_bounds", "orbx_frames_rgbd",
     "orbx_download_frame_front",
     "orbm_vocabulary_upload", "orbm_vocabulary_free", "orbm_bow_transform", "orbm_search_by_bow", "orbm_distinctive_descriptors",
+    "orbm_search_for_triangulation", "orbm_fuse", "orbm_search_by_sim3",
 ]
 
 
@@ -491,3 +492,56 @@ def distinctive_descriptors(desc: np.ndarray, offsets: np.ndarray, device=0):
     check(lib().orbm_distinctive_descriptors(desc.ctypes.data_as(C.c_void_p), offsets.ctypes.data_as(C.c_void_p), n, device,
                                              idx.ctypes.data_as(C.c_void_p), med.ctypes.data_as(C.c_void_p)))
     return idx, med
+
+
+class KeyFrameStruct(C.Structure):
+    _fields_ = [("frame", FrameStruct), ("level_sigma2", C.c_void_p), ("inv_level_sigma2", C.c_void_p),
+                ("node_id", C.c_void_p), ("flags", C.c_void_p)]
+
+
+class KeyFrameData:
+    """numpy arrays behind an orbm_keyframe."""
+
+    def __init__(self, kps, desc, width, height, u_right=None, scale_factors=None, level_sigma2=None, node_id=None,
+                 flags=None, bounds=None):
+        self.fd = FrameData(kps, desc, width, height, u_right, scale_factors, bounds)
+        self.n = self.fd.c.n
+        self.s2 = None if level_sigma2 is None else np.ascontiguousarray(level_sigma2, np.float32)
+        self.is2 = None if self.s2 is None else (np.float32(1.0) / self.s2).astype(np.float32)
+        self.node = None if node_id is None else np.ascontiguousarray(node_id, np.uint32)
+        self.flags = None if flags is None else np.ascontiguousarray(flags, np.uint8)
+        self.c = KeyFrameStruct(self.fd.c, *[None if a is None else a.ctypes.data for a in (self.s2, self.is2, self.node, self.flags)])
+
+
+def fuse(variant, kf: KeyFrameData, queries, qdesc, device=0):
+    """per-MapPoint search of ORBmatcher::Fuse (variant 0 / 1) or of one SearchBySim3 direction (2)"""
+    q = np.ascontiguousarray(queries, PROJ_DTYPE)
+    qd = np.ascontiguousarray(qdesc, np.uint8)
+    bi = np.full(max(len(q), 1), -1, np.int32); bd = np.full(max(len(q), 1), 256, np.int32)
+    check(lib().orbm_fuse(variant, C.byref(kf.c), _p(q), _p(qd), len(q), device, _p(bi), _p(bd)))
+    return bi[:len(q)].copy(), bd[:len(q)].copy()
+
+
+def search_by_sim3(kf1: KeyFrameData, kf2: KeyFrameData, q12, d12, index1, q21, d21, index2, device=0):
+    q12 = np.ascontiguousarray(q12, PROJ_DTYPE); q21 = np.ascontiguousarray(q21, PROJ_DTYPE)
+    d12 = np.ascontiguousarray(d12, np.uint8); d21 = np.ascontiguousarray(d21, np.uint8)
+    i1 = np.ascontiguousarray(index1, np.int32); i2 = np.ascontiguousarray(index2, np.int32)
+    m12 = np.full(max(kf1.n, 1), -1, np.int32)
+    nf = C.c_int32()
+    check(lib().orbm_search_by_sim3(C.byref(kf1.c), C.byref(kf2.c), _p(q12), _p(d12), _p(i1), len(q12), _p(q21), _p(d21),
+                                    _p(i2), len(q21), device, _p(m12), C.byref(nf)))
+    return nf.value, m12[:kf1.n].copy()
+
+
+def search_for_triangulation(pairs, f12, epipoles, only_stereo=False, check_ori=True, device=0):
+    """pairs: list of (KeyFrameData kf1, KeyFrameData kf2); f12: [npairs][9]; epipoles: [npairs][2]"""
+    n = len(pairs)
+    a = (KeyFrameStruct * n)(*[p[0].c for p in pairs]); b = (KeyFrameStruct * n)(*[p[1].c for p in pairs])
+    F = np.ascontiguousarray(f12, np.float32).reshape(n, 9); E = np.ascontiguousarray(epipoles, np.float32).reshape(n, 2)
+    tot = sum(p[0].n for p in pairs)
+    m = np.full(max(tot, 1), -1, np.int32); nm = np.zeros(n, np.int32)
+    check(lib().orbm_search_for_triangulation(a, b, n, _p(F), _p(E), int(only_stereo), int(check_ori), device, _p(m), _p(nm)))
+    out, o = [], 0
+    for p in pairs:
+        out.append(m[o:o + p[0].n].copy()); o += p[0].n
+    return nm, out

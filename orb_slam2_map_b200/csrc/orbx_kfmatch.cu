@@ -1,0 +1,426 @@
+// orbx_kfmatch.cu — the keyframe-rate matchers as sm_100a kernels behind the C ABI:
+//
+//   K19 area_best_kernel       the per-MapPoint search of ORBmatcher::Fuse (src/ORBmatcher.cc:825-973, 975-1100) and of
+//                              either direction of SearchBySim3 (:1102-1326) over KeyFrame::GetFeaturesInArea
+//                              (src/KeyFrame.cc:607-646)
+//   K20 sim3_agree_kernel      SearchBySim3's agreement check (:1307-1322)
+//   K21 triangulation_kernel   ORBmatcher::SearchForTriangulation (:657-823) with CheckDistEpipolarLine (:140-157)
+//
+// None of the three loops carries state from one MapPoint / feature to the next (Fuse's side effects are replayed by the
+// host wrapper; SearchForTriangulation never sets vbMatched2), so every query is one warp's work and the grid is as
+// wide as the query list.  K19: lanes own grid columns of the search window; "first least distance in scan order"
+// (strict '<') = the smallest key dist << 16 | position in the cell-sorted index list.  K21: FeatureVectors as a
+// block bitonic sort of (node << 32 | index) keys like K17; a candidate replaces the best when dist <= bestDist, so the
+// winner is the least distance with the LAST position among equals.
+
+#include "orbx_internal.h"
+#include "orbx_match_common.cuh"
+
+#include <algorithm>
+#include <vector>
+
+#define AB_WARPS 8
+
+struct AreaBestArgs {
+    FrameStore fs;
+    GridParams gp;
+    const float* uRight;        // mvuRight of the keyframe or nullptr (all -1)
+    float invSigma2[ORBX_MAX_LEVELS];
+    int variant, thDist;
+};
+
+__global__ void __launch_bounds__(AB_WARPS * 32)
+area_best_kernel(AreaBestArgs A, const orbm_proj_query* __restrict__ queries, const u8* __restrict__ qdesc, int nq,
+                 int* __restrict__ bestIdxOut, int* __restrict__ bestDistOut)
+{
+    const int lane = threadIdx.x & 31, q = blockIdx.x * AB_WARPS + (threadIdx.x >> 5);
+    if (q >= nq) return;
+    const orbx_keypoint* kps = A.fs.kps;
+    const unsigned short* gs = A.fs.gridStart;
+    const unsigned short* gi = A.fs.gridIdx;
+    const orbm_proj_query Q = queries[q];
+    unsigned best = 0xffffffffu;
+    int cx0, cx1, cy0, cy1;
+    if (area_cells(A.gp, Q.u, Q.v, Q.radius, cx0, cx1, cy0, cy1)) {
+        uint32_t qd[8];
+        load_desc(qd, qdesc + (size_t)q * 32);
+        const int ncy = cy1 - cy0 + 1;
+        for (int ix = cx0 + lane; ix <= cx1; ix += 32) {
+            const int e = gs[ix * ORBX_GRID_ROWS + cy0 + ncy];
+            for (int j = gs[ix * ORBX_GRID_ROWS + cy0]; j < e; ++j) {
+                const int idx = gi[j];
+                const orbx_keypoint kp = kps[idx];
+                if (!(fabsf(__fsub_rn(kp.x, Q.u)) < Q.radius && fabsf(__fsub_rn(kp.y, Q.v)) < Q.radius)) continue;
+                if (kp.octave < Q.level_hi - 1 || kp.octave > Q.level_hi) continue;
+                if (A.variant == ORBM_FUSE_MAPPOINTS) {
+                    const float kpr = A.uRight ? A.uRight[idx] : -1.f;
+                    const float ex = __fsub_rn(Q.u, kp.x), ey = __fsub_rn(Q.v, kp.y);
+                    float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                    double lim = 5.99;
+                    if (kpr >= 0) { const float er = __fsub_rn(Q.u_right, kpr); e2 = __fadd_rn(e2, __fmul_rn(er, er)); lim = 7.8; }
+                    if ((double)__fmul_rn(e2, A.invSigma2[kp.octave]) > lim) continue;
+                }
+                const int dist = hamming256(qd, reinterpret_cast<const uint32_t*>(A.fs.desc + (size_t)idx * 32));
+                best = min(best, ((unsigned)dist << 16) | (unsigned)j);
+            }
+        }
+    }
+    for (int d = 16; d > 0; d >>= 1) best = min(best, __shfl_xor_sync(FULL, best, d));
+    if (lane == 0) {
+        const int dist = best == 0xffffffffu ? 256 : (int)(best >> 16);
+        bestDistOut[q] = dist;
+        bestIdxOut[q] = (best != 0xffffffffu && dist <= A.thDist) ? (int)gi[best & 0xffff] : -1;
+    }
+}
+
+// vnMatch1 / vnMatch2 scatter + agreement.  One CTA.
+__global__ void sim3_agree_kernel(const int* __restrict__ best12, const int* __restrict__ index1, int nq12,
+                                  const int* __restrict__ best21, const int* __restrict__ index2, int nq21, int n1, int n2,
+                                  int* __restrict__ vnMatch1, int* __restrict__ vnMatch2, int* __restrict__ match12,
+                                  int* __restrict__ nfound)
+{
+    __shared__ int cnt;
+    if (threadIdx.x == 0) cnt = 0;
+    for (int i = threadIdx.x; i < n1; i += blockDim.x) vnMatch1[i] = -1;
+    for (int i = threadIdx.x; i < n2; i += blockDim.x) vnMatch2[i] = -1;
+    __syncthreads();
+    for (int q = threadIdx.x; q < nq12; q += blockDim.x) vnMatch1[index1[q]] = best12[q];
+    for (int q = threadIdx.x; q < nq21; q += blockDim.x) vnMatch2[index2[q]] = best21[q];
+    __syncthreads();
+    int mine = 0;
+    for (int i1 = threadIdx.x; i1 < n1; i1 += blockDim.x) {
+        const int idx2 = vnMatch1[i1];
+        const bool ok = idx2 >= 0 && vnMatch2[idx2] == i1;
+        match12[i1] = ok ? idx2 : -1;
+        mine += ok;
+    }
+    atomicAdd(&cnt, mine);
+    __syncthreads();
+    if (threadIdx.x == 0) *nfound = cnt;
+}
+
+#define TRI_THREADS 256
+struct TriPair {
+    int offA, nA, offB, nB;
+    float F[9], ex, ey;
+    float scale[ORBX_MAX_LEVELS], sigma2[ORBX_MAX_LEVELS];
+};
+
+__device__ void tri_bitonic_sort64(unsigned long long* a, int cap)
+{
+    for (int k = 2; k <= cap; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = threadIdx.x; i < cap; i += TRI_THREADS) {
+                const int l = i ^ j;
+                if (l > i) {
+                    const unsigned long long x = a[i], y = a[l];
+                    if ((x > y) == ((i & k) == 0)) { a[i] = y; a[l] = x; }
+                }
+            }
+            __syncthreads();
+        }
+}
+
+__global__ void __launch_bounds__(TRI_THREADS)
+triangulation_kernel(const TriPair* __restrict__ pairs, const orbx_keypoint* __restrict__ kpA, const u8* __restrict__ descA,
+                     const uint32_t* __restrict__ nodeA, const u8* __restrict__ flagA, const float* __restrict__ urA,
+                     const orbx_keypoint* __restrict__ kpB, const u8* __restrict__ descB, const uint32_t* __restrict__ nodeB,
+                     const u8* __restrict__ flagB, const float* __restrict__ urB, int onlyStereo, int checkOri, int capA,
+                     int capB, int32_t* __restrict__ matches12, int32_t* __restrict__ nmatchesOut)
+{
+    extern __shared__ __align__(16) unsigned char smraw[];
+    __shared__ int sHist[ORBX_HISTO_LENGTH], sCount, sInd[3];
+    __shared__ TriPair P;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    if (tid < (int)(sizeof(TriPair) / 4)) reinterpret_cast<int*>(&P)[tid] = reinterpret_cast<const int*>(pairs + blockIdx.x)[tid];
+    if (tid < ORBX_HISTO_LENGTH) sHist[tid] = 0;
+    if (tid == 0) sCount = 0;
+    __syncthreads();
+    unsigned long long* keysA = reinterpret_cast<unsigned long long*>(smraw);
+    unsigned long long* keysB = keysA + capA;
+    u8* binOf = reinterpret_cast<u8*>(keysB + capB);
+    kpA += P.offA; descA += (size_t)P.offA * 32; nodeA += P.offA; flagA += P.offA; urA += P.offA; matches12 += P.offA;
+    kpB += P.offB; descB += (size_t)P.offB * 32; nodeB += P.offB; flagB += P.offB; urB += P.offB;
+    int pa = 1; while (pa < P.nA) pa <<= 1;
+    int pb = 1; while (pb < P.nB) pb <<= 1;
+    // A: only the features the loop does not skip (:699-707); B: every FeatureVector entry (skips are per candidate)
+    for (int i = tid; i < pa; i += TRI_THREADS) {
+        bool use = i < P.nA && (flagA[i] & 1) && !(flagA[i] & 2);
+        if (use && onlyStereo && !(urA[i] >= 0)) use = false;
+        keysA[i] = use ? (((unsigned long long)nodeA[i] << 32) | (unsigned)i) : ~0ull;
+    }
+    for (int i = tid; i < pb; i += TRI_THREADS)
+        keysB[i] = (i < P.nB && (flagB[i] & 1)) ? (((unsigned long long)nodeB[i] << 32) | (unsigned)i) : ~0ull;
+    for (int i = tid; i < P.nA; i += TRI_THREADS) { matches12[i] = -1; binOf[i] = 0xff; }
+    __syncthreads();
+    tri_bitonic_sort64(keysA, pa);
+    tri_bitonic_sort64(keysB, pb);
+    int accepted = 0;
+    for (int ia = wid; ia < pa; ia += TRI_THREADS / 32) {
+        const unsigned long long kA = keysA[ia];
+        if (kA == ~0ull) break;                                    // sorted: the unused entries are at the end
+        const unsigned node = (unsigned)(kA >> 32);
+        const int idx1 = (int)(kA & 0xffffffffu);
+        int lo = 0, hi = pb;
+        const unsigned long long target = (unsigned long long)node << 32;
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (keysB[mid] < target) lo = mid + 1; else hi = mid; }
+        const orbx_keypoint kp1 = kpA[idx1];
+        const bool stereo1 = urA[idx1] >= 0;
+        // epipolar line in the second image l = x1' F12 = [a b c]
+        const float a = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, P.F[0]), __fmul_rn(kp1.y, P.F[3])), P.F[6]);
+        const float b = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, P.F[1]), __fmul_rn(kp1.y, P.F[4])), P.F[7]);
+        const float c = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, P.F[2]), __fmul_rn(kp1.y, P.F[5])), P.F[8]);
+        const float den = __fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b));
+        uint32_t q[8];
+        load_desc(q, descA + (size_t)idx1 * 32);
+        unsigned best = 0xffffffffu;                               // dist << 16 | (0xffff - position): last of the least wins
+        for (int jb0 = lo; jb0 < pb; jb0 += 32) {
+            const int jb = jb0 + lane;
+            const unsigned long long kB = jb < pb ? keysB[jb] : ~0ull;
+            const bool inRun = kB != ~0ull && (unsigned)(kB >> 32) == node;
+            if (inRun) {
+                const int idx2 = (int)(kB & 0xffffffffu);
+                const bool stereo2 = urB[idx2] >= 0;
+                bool ok = !(flagB[idx2] & 2) && !(onlyStereo && !stereo2);
+                int dist = 0;
+                if (ok) { dist = hamming256(q, reinterpret_cast<const uint32_t*>(descB + (size_t)idx2 * 32)); ok = dist <= ORBX_TH_LOW; }
+                if (ok) {
+                    const orbx_keypoint kp2 = kpB[idx2];
+                    if (!stereo1 && !stereo2) {
+                        const float dx = __fsub_rn(P.ex, kp2.x), dy = __fsub_rn(P.ey, kp2.y);
+                        if (__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) < __fmul_rn(100.f, P.scale[kp2.octave])) ok = false;
+                    }
+                    if (ok) {
+                        const float num = __fadd_rn(__fadd_rn(__fmul_rn(a, kp2.x), __fmul_rn(b, kp2.y)), c);
+                        ok = den != 0.f && (double)__fdiv_rn(__fmul_rn(num, num), den) < __dmul_rn(3.84, (double)P.sigma2[kp2.octave]);
+                    }
+                    if (ok) best = min(best, ((unsigned)dist << 16) | (unsigned)(0xffff - (jb - lo)));
+                }
+            }
+            if (!__all_sync(FULL, inRun)) break;
+        }
+        for (int d = 16; d > 0; d >>= 1) best = min(best, __shfl_xor_sync(FULL, best, d));
+        if (best != 0xffffffffu) {
+            const int idx2 = (int)(keysB[lo + (0xffff - (int)(best & 0xffff))] & 0xffffffffu);
+            if (lane == 0) {
+                matches12[idx1] = idx2;
+                if (checkOri) { const int bin = rot_bin(kp1.angle, kpB[idx2].angle); binOf[idx1] = (u8)bin; atomicAdd(&sHist[bin], 1); }
+            }
+            ++accepted;
+        }
+    }
+    if (lane == 0) atomicAdd(&sCount, accepted);
+    __syncthreads();
+    if (checkOri) {
+        if (tid == 0) { int i1, i2, i3; three_maxima(sHist, ORBX_HISTO_LENGTH, i1, i2, i3); sInd[0] = i1; sInd[1] = i2; sInd[2] = i3; }
+        __syncthreads();
+        int culled = 0;
+        for (int i = tid; i < P.nA; i += TRI_THREADS) {
+            const int bnum = binOf[i];
+            if (bnum != 0xff && bnum != sInd[0] && bnum != sInd[1] && bnum != sInd[2]) { matches12[i] = -1; ++culled; }
+        }
+        if (culled) atomicSub(&sCount, culled);
+        __syncthreads();
+    }
+    if (tid == 0) nmatchesOut[blockIdx.x] = sCount;
+}
+
+// ---- host side -------------------------------------------------------------------------------------------------
+static int kf_device(int device)
+{
+    int ndev = 0;
+    ORBX_CUDA(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) { orbx_set_error("CUDA device %d not available (%d devices); no CPU fallback", device, ndev); return ORBX_E_CUDA; }
+    ORBX_CUDA(cudaSetDevice(device));
+    return ORBX_OK;
+}
+
+static int kf_check(const orbm_keyframe* kf)
+{
+    const orbm_frame* f = kf ? &kf->frame : nullptr;
+    if (!f || f->n < 0 || (f->n > 0 && (!f->keys_un || !f->descriptors))) { orbx_set_error("bad orbm_keyframe"); return ORBX_E_INVALID; }
+    if (f->n > 65000) { orbx_set_error("more than 65000 keypoints per keyframe unsupported"); return ORBX_E_CAPACITY; }
+    if (f->nlevels < 0 || f->nlevels > ORBX_MAX_LEVELS) { orbx_set_error("nlevels out of range"); return ORBX_E_INVALID; }
+    return ORBX_OK;
+}
+
+// one uploaded keyframe with its grid, ready for area_best_kernel
+struct DevKeyFrame {
+    TempFrames tf;
+    DevBuf uRight;
+    AreaBestArgs args;
+    int upload(const orbm_keyframe* kf, int variant)
+    {
+        const orbm_frame* f = &kf->frame;
+        if (!(f->max_x > f->min_x) || !(f->max_y > f->min_y)) { orbx_set_error("bad keyframe bounds"); return ORBX_E_INVALID; }
+        int rc = tf.alloc(1, f->n); if (rc) return rc;
+        rc = tf.upload(0, f); if (rc) return rc;
+        args.gp = orbx_grid_params(f->min_x, f->max_x, f->min_y, f->max_y);
+        rc = orbx_launch_grid_build(tf.store(), 0, 1, args.gp, 0); if (rc) return rc;
+        args.fs = tf.store();
+        args.uRight = nullptr;
+        args.variant = variant;
+        args.thDist = variant == ORBM_FUSE_SIM3_LEG ? ORBX_TH_HIGH : ORBX_TH_LOW;
+        for (int l = 0; l < ORBX_MAX_LEVELS; ++l) args.invSigma2[l] = 0.f;
+        if (variant == ORBM_FUSE_MAPPOINTS) {
+            if (!kf->inv_level_sigma2 || f->nlevels <= 0) { orbx_set_error("Fuse variant 0 needs inv_level_sigma2 / nlevels"); return ORBX_E_INVALID; }
+            for (int l = 0; l < f->nlevels; ++l) args.invSigma2[l] = kf->inv_level_sigma2[l];
+            if (f->u_right && f->n > 0) {
+                rc = uRight.alloc((size_t)f->n * 4); if (rc) return rc;
+                ORBX_CUDA(cudaMemcpy(uRight.p, f->u_right, (size_t)f->n * 4, cudaMemcpyHostToDevice));
+                args.uRight = uRight.as<float>();
+            }
+        }
+        return ORBX_OK;
+    }
+};
+
+struct DevQueries {
+    DevBuf q, d, bi, bd;
+    int upload(const orbm_proj_query* queries, const uint8_t* desc, int nq)
+    {
+        int rc;
+        if ((rc = q.alloc((size_t)nq * sizeof(orbm_proj_query))) || (rc = d.alloc((size_t)nq * 32)) ||
+            (rc = bi.alloc((size_t)nq * 4)) || (rc = bd.alloc((size_t)nq * 4))) return rc;
+        if (nq > 0) {
+            ORBX_CUDA(cudaMemcpy(q.p, queries, (size_t)nq * sizeof(orbm_proj_query), cudaMemcpyHostToDevice));
+            ORBX_CUDA(cudaMemcpy(d.p, desc, (size_t)nq * 32, cudaMemcpyHostToDevice));
+        }
+        return ORBX_OK;
+    }
+    void launch(const AreaBestArgs& a, int nq)
+    {
+        if (nq > 0)
+            area_best_kernel<<<(nq + AB_WARPS - 1) / AB_WARPS, AB_WARPS * 32>>>(a, q.as<orbm_proj_query>(), d.as<u8>(), nq, bi.as<int>(), bd.as<int>());
+    }
+};
+
+extern "C" {
+
+int orbm_fuse(int variant, const orbm_keyframe* kf, const orbm_proj_query* queries, const uint8_t* query_desc, int nq,
+              int device, int32_t* best_idx, int32_t* best_dist)
+{
+    int rc = kf_check(kf); if (rc) return rc;
+    if (variant < ORBM_FUSE_MAPPOINTS || variant > ORBM_FUSE_SIM3_LEG) { orbx_set_error("unknown Fuse variant %d", variant); return ORBX_E_INVALID; }
+    if (nq < 0 || (nq > 0 && (!queries || !query_desc || !best_idx))) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
+    if (nq == 0) return ORBX_OK;
+    rc = kf_device(device); if (rc) return rc;
+    DevKeyFrame dk;
+    rc = dk.upload(kf, variant); if (rc) return rc;
+    DevQueries dq;
+    rc = dq.upload(queries, query_desc, nq); if (rc) return rc;
+    dq.launch(dk.args, nq);
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaMemcpy(best_idx, dq.bi.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+    if (best_dist) ORBX_CUDA(cudaMemcpy(best_dist, dq.bd.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+    return ORBX_OK;
+}
+
+int orbm_search_by_sim3(const orbm_keyframe* kf1, const orbm_keyframe* kf2, const orbm_proj_query* queries12,
+                        const uint8_t* desc12, const int32_t* index1, int nq12, const orbm_proj_query* queries21,
+                        const uint8_t* desc21, const int32_t* index2, int nq21, int device, int32_t* match12,
+                        int32_t* nfound)
+{
+    int rc = kf_check(kf1); if (rc) return rc;
+    rc = kf_check(kf2); if (rc) return rc;
+    if (nq12 < 0 || nq21 < 0 || (nq12 > 0 && (!queries12 || !desc12 || !index1)) || (nq21 > 0 && (!queries21 || !desc21 || !index2)) ||
+        (kf1->frame.n > 0 && !match12)) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
+    const int n1 = kf1->frame.n, n2 = kf2->frame.n;
+    for (int q = 0; q < nq12; ++q) if (index1[q] < 0 || index1[q] >= n1) { orbx_set_error("index1[%d] out of range", q); return ORBX_E_INVALID; }
+    for (int q = 0; q < nq21; ++q) if (index2[q] < 0 || index2[q] >= n2) { orbx_set_error("index2[%d] out of range", q); return ORBX_E_INVALID; }
+    rc = kf_device(device); if (rc) return rc;
+    DevKeyFrame d1, d2;
+    rc = d1.upload(kf1, ORBM_FUSE_SIM3_LEG); if (rc) return rc;
+    rc = d2.upload(kf2, ORBM_FUSE_SIM3_LEG); if (rc) return rc;
+    DevQueries q12, q21;
+    rc = q12.upload(queries12, desc12, nq12); if (rc) return rc;
+    rc = q21.upload(queries21, desc21, nq21); if (rc) return rc;
+    DevBuf dI1, dI2, dM1, dM2, dM12, dNf;
+    if ((rc = dI1.alloc((size_t)nq12 * 4)) || (rc = dI2.alloc((size_t)nq21 * 4)) || (rc = dM1.alloc((size_t)n1 * 4)) ||
+        (rc = dM2.alloc((size_t)n2 * 4)) || (rc = dM12.alloc((size_t)n1 * 4)) || (rc = dNf.alloc(4))) return rc;
+    if (nq12) ORBX_CUDA(cudaMemcpy(dI1.p, index1, (size_t)nq12 * 4, cudaMemcpyHostToDevice));
+    if (nq21) ORBX_CUDA(cudaMemcpy(dI2.p, index2, (size_t)nq21 * 4, cudaMemcpyHostToDevice));
+    q12.launch(d2.args, nq12);                 // points of KF1 searched in KF2
+    q21.launch(d1.args, nq21);
+    sim3_agree_kernel<<<1, 256>>>(q12.bi.as<int>(), dI1.as<int>(), nq12, q21.bi.as<int>(), dI2.as<int>(), nq21, n1, n2,
+                                  dM1.as<int>(), dM2.as<int>(), dM12.as<int>(), dNf.as<int>());
+    ORBX_CUDA(cudaGetLastError());
+    if (n1) ORBX_CUDA(cudaMemcpy(match12, dM12.p, (size_t)n1 * 4, cudaMemcpyDeviceToHost));
+    int nf = 0;
+    ORBX_CUDA(cudaMemcpy(&nf, dNf.p, 4, cudaMemcpyDeviceToHost));
+    if (nfound) *nfound = nf;
+    return ORBX_OK;
+}
+
+int orbm_search_for_triangulation(const orbm_keyframe* kf1, const orbm_keyframe* kf2, int npairs, const float* f12,
+                                  const float* epipole, int only_stereo, int check_orientation, int device,
+                                  int32_t* matches12, int32_t* nmatches)
+{
+    if (npairs <= 0) return ORBX_OK;
+    if (!kf1 || !kf2 || !f12 || !epipole || !matches12 || !nmatches) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
+    std::vector<TriPair> pairs(npairs);
+    long long totA = 0, totB = 0;
+    int maxA = 1, maxB = 1;
+    for (int p = 0; p < npairs; ++p) {
+        int rc = kf_check(kf1 + p); if (rc) return rc;
+        rc = kf_check(kf2 + p); if (rc) return rc;
+        const orbm_frame &A = kf1[p].frame, &B = kf2[p].frame;
+        if ((A.n > 0 && (!kf1[p].node_id || !kf1[p].flags)) || (B.n > 0 && (!kf2[p].node_id || !kf2[p].flags)) ||
+            (B.n > 0 && (!B.scale_factors || !kf2[p].level_sigma2 || B.nlevels <= 0))) {
+            orbx_set_error("pair %d: node_id / flags / scale_factors / level_sigma2 required", p); return ORBX_E_INVALID;
+        }
+        TriPair& P = pairs[p];
+        P.offA = (int)totA; P.nA = A.n; P.offB = (int)totB; P.nB = B.n;
+        for (int i = 0; i < 9; ++i) P.F[i] = f12[(size_t)p * 9 + i];
+        P.ex = epipole[2 * p]; P.ey = epipole[2 * p + 1];
+        for (int l = 0; l < ORBX_MAX_LEVELS; ++l) {
+            P.scale[l] = l < B.nlevels ? B.scale_factors[l] : 0.f;
+            P.sigma2[l] = l < B.nlevels ? kf2[p].level_sigma2[l] : 0.f;
+        }
+        totA += A.n; totB += B.n;
+        maxA = std::max(maxA, A.n); maxB = std::max(maxB, B.n);
+    }
+    int capA = 1; while (capA < maxA) capA <<= 1;
+    int capB = 1; while (capB < maxB) capB <<= 1;
+    const size_t smem = (size_t)(capA + capB) * 8 + capA + 16;
+    if (smem > 220 * 1024) { orbx_set_error("keyframes of %d / %d features exceed the shared-memory sort (%zu bytes)", maxA, maxB, smem); return ORBX_E_CAPACITY; }
+    int rc = kf_device(device); if (rc) return rc;
+    DevBuf dPairs, dKA, dDA, dNA, dFA, dUA, dKB, dDB, dNB, dFB, dUB, dM, dNM;
+#define KF_ALLOC(buf, bytes) rc = buf.alloc(bytes); if (rc) return rc
+    KF_ALLOC(dPairs, npairs * sizeof(TriPair));
+    KF_ALLOC(dKA, (size_t)totA * sizeof(orbx_keypoint)); KF_ALLOC(dDA, (size_t)totA * 32); KF_ALLOC(dNA, (size_t)totA * 4);
+    KF_ALLOC(dFA, (size_t)totA); KF_ALLOC(dUA, (size_t)totA * 4);
+    KF_ALLOC(dKB, (size_t)totB * sizeof(orbx_keypoint)); KF_ALLOC(dDB, (size_t)totB * 32); KF_ALLOC(dNB, (size_t)totB * 4);
+    KF_ALLOC(dFB, (size_t)totB); KF_ALLOC(dUB, (size_t)totB * 4);
+    KF_ALLOC(dM, (size_t)totA * 4); KF_ALLOC(dNM, (size_t)npairs * 4);
+#undef KF_ALLOC
+    ORBX_CUDA(cudaMemcpy(dPairs.p, pairs.data(), npairs * sizeof(TriPair), cudaMemcpyHostToDevice));
+    std::vector<float> minus;
+    auto up = [&](const orbm_keyframe& kf, int off, DevBuf& k, DevBuf& d, DevBuf& nd, DevBuf& fl, DevBuf& ur) -> int {
+        const orbm_frame& f = kf.frame;
+        if (f.n <= 0) return ORBX_OK;
+        ORBX_CUDA(cudaMemcpy(k.as<orbx_keypoint>() + off, f.keys_un, (size_t)f.n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice));
+        ORBX_CUDA(cudaMemcpy(d.as<u8>() + (size_t)off * 32, f.descriptors, (size_t)f.n * 32, cudaMemcpyHostToDevice));
+        ORBX_CUDA(cudaMemcpy(nd.as<uint32_t>() + off, kf.node_id, (size_t)f.n * 4, cudaMemcpyHostToDevice));
+        ORBX_CUDA(cudaMemcpy(fl.as<u8>() + off, kf.flags, (size_t)f.n, cudaMemcpyHostToDevice));
+        const float* u = f.u_right;
+        if (!u) { minus.assign((size_t)f.n, -1.f); u = minus.data(); }
+        ORBX_CUDA(cudaMemcpy(ur.as<float>() + off, u, (size_t)f.n * 4, cudaMemcpyHostToDevice));
+        return ORBX_OK;
+    };
+    for (int p = 0; p < npairs; ++p) {
+        rc = up(kf1[p], pairs[p].offA, dKA, dDA, dNA, dFA, dUA); if (rc) return rc;
+        rc = up(kf2[p], pairs[p].offB, dKB, dDB, dNB, dFB, dUB); if (rc) return rc;
+    }
+    if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(triangulation_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    triangulation_kernel<<<npairs, TRI_THREADS, smem>>>(dPairs.as<TriPair>(), dKA.as<orbx_keypoint>(), dDA.as<u8>(), dNA.as<uint32_t>(),
+                                                        dFA.as<u8>(), dUA.as<float>(), dKB.as<orbx_keypoint>(), dDB.as<u8>(),
+                                                        dNB.as<uint32_t>(), dFB.as<u8>(), dUB.as<float>(), only_stereo, check_orientation,
+                                                        capA, capB, dM.as<int32_t>(), dNM.as<int32_t>());
+    ORBX_CUDA(cudaGetLastError());
+    if (totA) ORBX_CUDA(cudaMemcpy(matches12, dM.p, (size_t)totA * 4, cudaMemcpyDeviceToHost));
+    ORBX_CUDA(cudaMemcpy(nmatches, dNM.p, (size_t)npairs * 4, cudaMemcpyDeviceToHost));
+    return ORBX_OK;
+}
+
+} // extern "C"

@@ -735,7 +735,7 @@ static FrameStore store_of(orbx_handle* h)
     return fs;
 }
 
-static GridParams grid_params(float minX, float maxX, float minY, float maxY)
+GridParams orbx_grid_params(float minX, float maxX, float minY, float maxY)
 {
     GridParams gp;
     gp.minX = minX; gp.minY = minY;
@@ -744,7 +744,7 @@ static GridParams grid_params(float minX, float maxX, float minY, float maxY)
     return gp;
 }
 
-static int launch_grid_build(const FrameStore& fs, int firstSlot, int nframes, const GridParams& gp, cudaStream_t st)
+int orbx_launch_grid_build(const FrameStore& fs, int firstSlot, int nframes, const GridParams& gp, cudaStream_t st)
 {
     const int smem = (ORBX_GRID_CELLS + fs.cap) * (int)sizeof(unsigned short);
     if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(grid_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -770,9 +770,9 @@ int orbx_build_grids(orbx_handle* h, int firstSlot, int nframes, int width, int 
 {
     int rc = orbx_ensure_match_buffers(h);
     if (rc) return rc;
-    const GridParams gp = h->storeUndistorted ? grid_params(h->bounds[0], h->bounds[1], h->bounds[2], h->bounds[3])
-                                              : grid_params(0.f, (float)width, 0.f, (float)height);
-    return launch_grid_build(store_of(h), firstSlot, nframes, gp, h->stream);
+    const GridParams gp = h->storeUndistorted ? orbx_grid_params(h->bounds[0], h->bounds[1], h->bounds[2], h->bounds[3])
+                                              : orbx_grid_params(0.f, (float)width, 0.f, (float)height);
+    return orbx_launch_grid_build(store_of(h), firstSlot, nframes, gp, h->stream);
 }
 
 static int launch_stereo(const FrameStore& fs, int firstSlot, int npairs, const PyrView& pv, float bf, float fx,
@@ -791,14 +791,6 @@ static int launch_stereo(const FrameStore& fs, int firstSlot, int npairs, const 
     return ORBX_OK;
 }
 
-// device scratch that frees itself (the stateless entry points allocate per call)
-struct DevBuf {
-    void* p = nullptr;
-    ~DevBuf() { if (p) cudaFree(p); }
-    int alloc(size_t bytes) { ORBX_CUDA(cudaMalloc(&p, bytes ? bytes : 4)); return ORBX_OK; }
-    template <typename T> T* as() { return (T*)p; }
-};
-
 extern "C" {
 
 int orbx_search_init_pairs(orbx_handle* h, int first_slot, int npairs, int window_size, float nnratio,
@@ -814,10 +806,10 @@ int orbx_search_init_pairs(orbx_handle* h, int first_slot, int npairs, int windo
     int rc = orbx_ensure_match_buffers(h);
     if (rc) return rc;
     const FrameStore fs = store_of(h);
-    const GridParams gp = h->storeUndistorted ? grid_params(h->bounds[0], h->bounds[1], h->bounds[2], h->bounds[3])
-                                              : grid_params(0.f, (float)h->curW, 0.f, (float)h->curH);
+    const GridParams gp = h->storeUndistorted ? orbx_grid_params(h->bounds[0], h->bounds[1], h->bounds[2], h->bounds[3])
+                                              : orbx_grid_params(0.f, (float)h->curW, 0.f, (float)h->curH);
     orbx_prof_mark(h, -1);
-    rc = launch_grid_build(fs, first_slot, npairs + 1, gp, h->stream);
+    rc = orbx_launch_grid_build(fs, first_slot, npairs + 1, gp, h->stream);
     if (rc) return rc;
     ORBX_COUNT(h, ORBX_STAGE_GRID, 1);
     orbx_prof_mark(h, ORBX_STAGE_GRID);
@@ -837,38 +829,6 @@ int orbx_search_init_pairs(orbx_handle* h, int first_slot, int npairs, int windo
     if (matches12 || nmatches || ncompares) return orbx_sync(h);
     return ORBX_OK;
 }
-
-// ---- stateless entry points: temporary device frames -----------------------------------------
-struct TempFrames {
-    orbx_keypoint* kps = nullptr; u8* desc = nullptr; int* count = nullptr;
-    unsigned short* gridStart = nullptr; unsigned short* gridIdx = nullptr;
-    int cap = 0, nslots = 0;
-    ~TempFrames() { cudaFree(kps); cudaFree(desc); cudaFree(count); cudaFree(gridStart); cudaFree(gridIdx); }
-    int alloc(int slots, int capacity)
-    {
-        cap = std::max(capacity, 8); nslots = slots;
-        ORBX_CUDA(cudaMalloc((void**)&kps, (size_t)slots * cap * sizeof(orbx_keypoint)));
-        ORBX_CUDA(cudaMalloc((void**)&desc, (size_t)slots * cap * 32));
-        ORBX_CUDA(cudaMalloc((void**)&count, slots * sizeof(int)));
-        ORBX_CUDA(cudaMalloc((void**)&gridStart, (size_t)slots * (ORBX_GRID_CELLS + 1) * sizeof(unsigned short)));
-        ORBX_CUDA(cudaMalloc((void**)&gridIdx, (size_t)slots * cap * sizeof(unsigned short)));
-        return ORBX_OK;
-    }
-    int upload(int slot, const orbm_frame* f)
-    {
-        ORBX_CUDA(cudaMemcpy(count + slot, &f->n, sizeof(int), cudaMemcpyHostToDevice));
-        if (f->n > 0) {
-            ORBX_CUDA(cudaMemcpy(kps + (size_t)slot * cap, f->keys_un, (size_t)f->n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice));
-            ORBX_CUDA(cudaMemcpy(desc + (size_t)slot * cap * 32, f->descriptors, (size_t)f->n * 32, cudaMemcpyHostToDevice));
-        }
-        return ORBX_OK;
-    }
-    FrameStore store() const
-    {
-        FrameStore fs; fs.kps = kps; fs.desc = desc; fs.count = count; fs.gridStart = gridStart; fs.gridIdx = gridIdx; fs.cap = cap;
-        return fs;
-    }
-};
 
 static int check_frame(const orbm_frame* f)
 {
@@ -922,8 +882,8 @@ int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, f
     ORBX_CUDA(cudaMalloc((void**)&dM12, (size_t)tf.cap * sizeof(int)));
     ORBX_CUDA(cudaMalloc((void**)&dNm, sizeof(int)));
     if (f1->n) ORBX_CUDA(cudaMemcpy(dPrev, prev_matched, (size_t)f1->n * 2 * sizeof(float), cudaMemcpyHostToDevice));
-    const GridParams gp = grid_params(f2->min_x, f2->max_x, f2->min_y, f2->max_y);
-    rc = launch_grid_build(tf.store(), 1, 1, gp, 0); if (rc) return rc;
+    const GridParams gp = orbx_grid_params(f2->min_x, f2->max_x, f2->min_y, f2->max_y);
+    rc = orbx_launch_grid_build(tf.store(), 1, 1, gp, 0); if (rc) return rc;
     rc = launch_search_init(tf.store(), 0, 1, 1, gp, dPrev, window_size, nnratio, check_orientation, dM12, dNm, nullptr, 0);
     if (rc) return rc;
     ORBX_CUDA(cudaGetLastError());
@@ -953,8 +913,8 @@ int orbm_search_by_projection(int variant, const orbm_frame* frame, const orbm_p
     TempFrames tf;
     rc = tf.alloc(1, frame->n); if (rc) return rc;
     rc = tf.upload(0, frame); if (rc) return rc;
-    const GridParams gp = grid_params(frame->min_x, frame->max_x, frame->min_y, frame->max_y);
-    rc = launch_grid_build(tf.store(), 0, 1, gp, 0); if (rc) return rc;
+    const GridParams gp = orbx_grid_params(frame->min_x, frame->max_x, frame->min_y, frame->max_y);
+    rc = orbx_launch_grid_build(tf.store(), 0, 1, gp, 0); if (rc) return rc;
     DevBuf dQ, dQD, dQB, dOcc, dAsg, dBI, dBD, dBin, dNm, dUR;
     const size_t n = (size_t)std::max(frame->n, 1), Q = (size_t)std::max(nq, 1);
     if ((rc = dQ.alloc(Q * sizeof(orbm_proj_query))) || (rc = dQD.alloc(Q * 32)) || (rc = dQB.alloc(Q)) ||

@@ -87,4 +87,49 @@ __device__ __forceinline__ int rot_bin(float a1, float a2)
 }
 
 
+// ---- host-side helpers shared by the stateless matcher entry points (orbx_match.cu, orbx_kfmatch.cu) ----
+GridParams orbx_grid_params(float minX, float maxX, float minY, float maxY);
+int orbx_launch_grid_build(const FrameStore& fs, int firstSlot, int nframes, const GridParams& gp, cudaStream_t st);
+
+// device scratch that frees itself (the stateless entry points allocate per call)
+struct DevBuf {
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    int alloc(size_t bytes) { ORBX_CUDA(cudaMalloc(&p, bytes ? bytes : 4)); return ORBX_OK; }
+    template <typename T> T* as() { return (T*)p; }
+};
+
+// temporary device frames of the stateless entry points
+struct TempFrames {
+    orbx_keypoint* kps = nullptr; u8* desc = nullptr; int* count = nullptr;
+    unsigned short* gridStart = nullptr; unsigned short* gridIdx = nullptr;
+    int cap = 0, nslots = 0;
+    ~TempFrames() { cudaFree(kps); cudaFree(desc); cudaFree(count); cudaFree(gridStart); cudaFree(gridIdx); }
+    int alloc(int slots, int capacity)
+    {
+        cap = std::max(capacity, 8); nslots = slots;
+        ORBX_CUDA(cudaMalloc((void**)&kps, (size_t)slots * cap * sizeof(orbx_keypoint)));
+        ORBX_CUDA(cudaMalloc((void**)&desc, (size_t)slots * cap * 32));
+        ORBX_CUDA(cudaMalloc((void**)&count, slots * sizeof(int)));
+        ORBX_CUDA(cudaMalloc((void**)&gridStart, (size_t)slots * (ORBX_GRID_CELLS + 1) * sizeof(unsigned short)));
+        ORBX_CUDA(cudaMalloc((void**)&gridIdx, (size_t)slots * cap * sizeof(unsigned short)));
+        return ORBX_OK;
+    }
+    int upload(int slot, const orbm_frame* f)
+    {
+        ORBX_CUDA(cudaMemcpy(count + slot, &f->n, sizeof(int), cudaMemcpyHostToDevice));
+        if (f->n > 0) {
+            ORBX_CUDA(cudaMemcpy(kps + (size_t)slot * cap, f->keys_un, (size_t)f->n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice));
+            ORBX_CUDA(cudaMemcpy(desc + (size_t)slot * cap * 32, f->descriptors, (size_t)f->n * 32, cudaMemcpyHostToDevice));
+        }
+        return ORBX_OK;
+    }
+    FrameStore store() const
+    {
+        FrameStore fs; fs.kps = kps; fs.desc = desc; fs.count = count; fs.gridStart = gridStart; fs.gridIdx = gridIdx; fs.cap = cap;
+        return fs;
+    }
+};
+
+
 #endif

@@ -56,7 +56,7 @@ class StereoInput(C.Structure):
 def build_oracle(force: bool = False) -> str:
     so = os.path.join(ORACLE_DIR, "liborb_oracle.so")
     src = os.path.join(ORACLE_DIR, "orb_oracle.cpp")
-    srcs = [src, os.path.join(ORACLE_DIR, "frame_oracle.cpp"), os.path.join(ORACLE_DIR, "bow_oracle.cpp")]
+    srcs = [src, os.path.join(ORACLE_DIR, "frame_oracle.cpp"), os.path.join(ORACLE_DIR, "bow_oracle.cpp"), os.path.join(ORACLE_DIR, "kfmatch_oracle.cpp")]
     if force or not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", ORACLE_DIR, "liborb_oracle.so"], stdout=subprocess.DEVNULL)
     return so
@@ -404,3 +404,48 @@ def distinctive_descriptors(desc: np.ndarray, offsets: np.ndarray):
     idx = np.zeros(n, np.int32); med = np.zeros(n, np.int32)
     lib().oracle_distinctive(_p(desc), _p(offsets), n, _p(idx), _p(med))
     return idx, med
+
+
+class KeyFrameStruct(C.Structure):
+    _fields_ = [("frame", Frame), ("level_sigma2", C.c_void_p), ("inv_level_sigma2", C.c_void_p),
+                ("node_id", C.c_void_p), ("flags", C.c_void_p)]
+
+
+class KeyFrameData:
+    """numpy arrays behind an orbm_keyframe."""
+
+    def __init__(self, kps, desc, width, height, u_right=None, scale_factors=None, level_sigma2=None, node_id=None,
+                 flags=None, bounds=None):
+        self.fd = FrameData(kps, desc, width, height, u_right, scale_factors, bounds)
+        self.n = self.fd.c.n
+        self.s2 = None if level_sigma2 is None else np.ascontiguousarray(level_sigma2, np.float32)
+        self.is2 = None if self.s2 is None else (np.float32(1.0) / self.s2).astype(np.float32)
+        self.node = None if node_id is None else np.ascontiguousarray(node_id, np.uint32)
+        self.flags = None if flags is None else np.ascontiguousarray(flags, np.uint8)
+        self.c = KeyFrameStruct(self.fd.c, *[None if a is None else a.ctypes.data for a in (self.s2, self.is2, self.node, self.flags)])
+
+
+def fuse(variant, kf: KeyFrameData, queries, qdesc):
+    q = np.ascontiguousarray(queries, PROJ_DTYPE)
+    qd = np.ascontiguousarray(qdesc, np.uint8)
+    bi = np.full(max(len(q), 1), -1, np.int32); bd = np.full(max(len(q), 1), 256, np.int32)
+    lib().oracle_fuse(C.c_int(variant), C.byref(kf.c), _p(q), _p(qd), C.c_int(len(q)), _p(bi), _p(bd))
+    return bi[:len(q)].copy(), bd[:len(q)].copy()
+
+
+def search_by_sim3(kf1: KeyFrameData, kf2: KeyFrameData, q12, d12, index1, q21, d21, index2):
+    q12 = np.ascontiguousarray(q12, PROJ_DTYPE); q21 = np.ascontiguousarray(q21, PROJ_DTYPE)
+    d12 = np.ascontiguousarray(d12, np.uint8); d21 = np.ascontiguousarray(d21, np.uint8)
+    i1 = np.ascontiguousarray(index1, np.int32); i2 = np.ascontiguousarray(index2, np.int32)
+    m12 = np.full(max(kf1.n, 1), -1, np.int32)
+    nf = lib().oracle_search_by_sim3(C.byref(kf1.c), C.byref(kf2.c), _p(q12), _p(d12), _p(i1), C.c_int(len(q12)), _p(q21),
+                                     _p(d21), _p(i2), C.c_int(len(q21)), _p(m12))
+    return nf, m12[:kf1.n].copy()
+
+
+def search_for_triangulation(kf1: KeyFrameData, kf2: KeyFrameData, f12, epipole, only_stereo=False, check_ori=True):
+    F = np.ascontiguousarray(f12, np.float32).reshape(9)
+    m = np.full(max(kf1.n, 1), -1, np.int32)
+    nm = lib().oracle_search_for_triangulation(C.byref(kf1.c), C.byref(kf2.c), _p(F), C.c_float(epipole[0]), C.c_float(epipole[1]),
+                                               C.c_int(int(only_stereo)), C.c_int(int(check_ori)), _p(m))
+    return nm, m[:kf1.n].copy()
