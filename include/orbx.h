@@ -390,6 +390,31 @@ int orbm_search_by_sim3(const orbm_keyframe* kf1, const orbm_keyframe* kf2, cons
                         const uint8_t* desc21, const int32_t* index2, int nq21, int device, int32_t* match12,
                         int32_t* nfound);
 
+/* ================================================================================================
+ * This fork's dense mapping step: per-keyframe depth back-projection.
+ * ================================================================================================ */
+
+/* x, y, z and the colour bytes of a pcl::PointXYZRGBA (b, g, r, a = 255). */
+typedef struct orbx_cloud_point {
+    float x, y, z;
+    uint8_t b, g, r, a;
+} orbx_cloud_point;
+
+/* PointCloudMapping::generatePointCloud (src/PointCloudMap.cc:78-110) / convertToPointCloud (:112-139) for nframes
+ * keyframes per call: every `step`-th row and column (the reference uses 3) of the CV_32F depth map with
+ * 0.01 <= d <= 10 becomes a point z = d, x = (n - cx) * z / fx, y = (m - cy) * z / fy with the BGR bytes of mImRGB, in
+ * row-major scan order (the push_back order); then pcl::transformPointCloud(tmp, cloud, T.inverse().matrix()) in
+ * double: out = (float)(t00*x + t01*y + t02*z + t03), ...
+ * depth: nframes maps, row stride depth_row_stride floats, frame stride depth_frame_stride floats; bgr: 3-channel
+ * images with byte strides, or NULL (the PointXYZ overload :148-176: colour bytes 0, a = 255).
+ * pose_inv: nframes x 16 doubles, row-major T.inverse().matrix(), or NULL for convertToPointCloud (no transform).
+ * points: out, frame f's points start at f * capacity; counts: out [nframes] (a frame that yields more than
+ * `capacity` points returns ORBX_E_CAPACITY; ceil(w/step)*ceil(h/step) always suffices).  Host pointers. */
+int orbm_generate_point_clouds(const float* depth, size_t depth_row_stride, size_t depth_frame_stride, const uint8_t* bgr,
+                               size_t bgr_row_stride, size_t bgr_frame_stride, int width, int height, int nframes, int step,
+                               const orbx_camera* cam, const double* pose_inv, int device, orbx_cloud_point* points,
+                               int capacity, int32_t* counts);
+
 #ifdef __cplusplus
 }
 #endif

@@ -7,6 +7,9 @@
 //   oracle_undistort_points    cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK), Frame.cc:404-434, 436-464
 //   oracle_image_bounds        Frame::ComputeImageBounds, Frame.cc:436-464
 //   oracle_stereo_from_rgbd    Frame::ComputeStereoFromRGBD, Frame.cc:641-662
+//   oracle_generate_point_cloud  PointCloudMapping::generatePointCloud / convertToPointCloud, PointCloudMap.cc:78-139
+//                              with pcl::transformPointCloud<PointT, double> (PCL >= 1.7, not vendored: its published
+//                              per-point arithmetic is restated; parity unpinned for this function)
 //
 // The OpenCV arithmetic is that of 4.13.0, pinned by tests/golden/frame_front.npz (generated with the cv2
 // wheel by tests/golden/make_golden_frame.py): 15-bit luma coefficients with round-half-up for 8U cvtColor;
@@ -98,6 +101,37 @@ void oracle_stereo_from_rgbd(const float* keys_xy, const float* keys_un_xy, int 
         const float d = depth[(size_t)v * dstride_elems + u];
         if (d > 0) { z[i] = d; u_right[i] = keys_un_xy[2 * i] - bf / d; }
     }
+}
+
+// One keyframe.  pose_inv = T.inverse().matrix() row-major, or NULL (convertToPointCloud).  out: 16-byte records
+// {float x, y, z; u8 b, g, r, a}.  Returns the number of points.
+int oracle_generate_point_cloud(const float* depth, size_t dstride_elems, const uint8_t* bgr, size_t cstride, int cols, int rows,
+                                int step, float fx, float fy, float cx, float cy, const double* pose_inv, uint8_t* out)
+{
+    int count = 0;
+    for (int m = 0; m < rows; m += step)
+        for (int n = 0; n < cols; n += step) {
+            const float d = depth[(size_t)m * dstride_elems + n];
+            if (d < 0.01 || d > 10) continue;
+            float p[3];
+            p[2] = d;
+            p[0] = (n - cx) * p[2] / fx;
+            p[1] = (m - cy) * p[2] / fy;
+            uint8_t c[4] = {0, 0, 0, 255};                 // PointXYZRGBA(): r = g = b = 0, a = 255
+            if (bgr) { c[0] = bgr[(size_t)m * cstride + n * 3]; c[1] = bgr[(size_t)m * cstride + n * 3 + 1]; c[2] = bgr[(size_t)m * cstride + n * 3 + 2]; }
+            float o[3] = {p[0], p[1], p[2]};
+            if (pose_inv) {
+                // pcl::transformPointCloud, Scalar = double: static_cast<float>(tf(r,0)*x + tf(r,1)*y + tf(r,2)*z + tf(r,3))
+                const double* tf = pose_inv;
+                for (int r = 0; r < 3; ++r)
+                    o[r] = static_cast<float>(tf[4 * r + 0] * p[0] + tf[4 * r + 1] * p[1] + tf[4 * r + 2] * p[2] + tf[4 * r + 3]);
+            }
+            uint8_t* rec = out + (size_t)count * 16;
+            for (int k = 0; k < 3; ++k) { const float v = o[k]; const uint8_t* b = reinterpret_cast<const uint8_t*>(&v); for (int t = 0; t < 4; ++t) rec[4 * k + t] = b[t]; }
+            for (int t = 0; t < 4; ++t) rec[12 + t] = c[t];
+            ++count;
+        }
+    return count;
 }
 
 } // extern "C"

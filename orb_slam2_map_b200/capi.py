@@ -63,7 +63,7 @@ EXPORTS = [
     "orbx_cvt_gray", "orbx_depth_to_float", "orbx_undistort_points", "orbx_image_bounds", "orbx_frames_rgbd",
     "orbx_download_frame_front",
     "orbm_vocabulary_upload", "orbm_vocabulary_free", "orbm_bow_transform", "orbm_search_by_bow", "orbm_distinctive_descriptors",
-    "orbm_search_for_triangulation", "orbm_fuse", "orbm_search_by_sim3",
+    "orbm_search_for_triangulation", "orbm_fuse", "orbm_search_by_sim3", "orbm_generate_point_clouds",
 ]
 
 
@@ -545,3 +545,23 @@ def search_for_triangulation(pairs, f12, epipoles, only_stereo=False, check_ori=
     for p in pairs:
         out.append(m[o:o + p[0].n].copy()); o += p[0].n
     return nm, out
+
+
+CLOUD_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("b", "u1"), ("g", "u1"), ("r", "u1"), ("a", "u1")])
+
+
+def generate_point_clouds(depth, bgr, cam: "Camera", pose_inv=None, step=3, device=0, capacity=None):
+    """PointCloudMapping::generatePointCloud for a batch: depth [F][H][W] float32, bgr [F][H][W][3] uint8 or None,
+    pose_inv [F][4][4] float64 (T.inverse().matrix()) or None.  Returns a list of CLOUD_DTYPE arrays."""
+    depth = np.ascontiguousarray(depth, np.float32)
+    F, H, W = depth.shape
+    if bgr is not None:
+        bgr = np.ascontiguousarray(bgr, np.uint8).reshape(F, H, W, 3)
+    if pose_inv is not None:
+        pose_inv = np.ascontiguousarray(pose_inv, np.float64).reshape(F, 16)
+    cap = capacity or (-(-W // step)) * (-(-H // step))
+    pts = np.zeros((F, cap), CLOUD_DTYPE)
+    counts = np.zeros(F, np.int32)
+    check(lib().orbm_generate_point_clouds(_p(depth), C.c_size_t(W), C.c_size_t(W * H), _p(bgr), C.c_size_t(W * 3), C.c_size_t(W * H * 3),
+                                           W, H, F, step, C.byref(cam), _p(pose_inv), device, _p(pts), cap, _p(counts)))
+    return [pts[f, :counts[f]].copy() for f in range(F)]

@@ -449,3 +449,19 @@ def search_for_triangulation(kf1: KeyFrameData, kf2: KeyFrameData, f12, epipole,
     nm = lib().oracle_search_for_triangulation(C.byref(kf1.c), C.byref(kf2.c), _p(F), C.c_float(epipole[0]), C.c_float(epipole[1]),
                                                C.c_int(int(only_stereo)), C.c_int(int(check_ori)), _p(m))
     return nm, m[:kf1.n].copy()
+
+
+CLOUD_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("b", "u1"), ("g", "u1"), ("r", "u1"), ("a", "u1")])
+
+
+def generate_point_cloud(depth, bgr, fx, fy, cx, cy, pose_inv=None, step=3):
+    depth = np.ascontiguousarray(depth, np.float32)
+    H, W = depth.shape
+    if bgr is not None:
+        bgr = np.ascontiguousarray(bgr, np.uint8).reshape(H, W, 3)
+    if pose_inv is not None:
+        pose_inv = np.ascontiguousarray(pose_inv, np.float64).reshape(16)
+    out = np.zeros((-(-W // step)) * (-(-H // step)), CLOUD_DTYPE)
+    n = lib().oracle_generate_point_cloud(_p(depth), C.c_size_t(W), _p(bgr), C.c_size_t(W * 3), C.c_int(W), C.c_int(H), C.c_int(step),
+                                          C.c_float(fx), C.c_float(fy), C.c_float(cx), C.c_float(cy), _p(pose_inv), _p(out))
+    return out[:n].copy()

@@ -103,3 +103,28 @@ def test_frames_rgbd_matches_oracle(channels, rgb, depth16):
         n_o, m_o, _, _ = O.search_for_initialization(f1, f2, prev, 100, 0.9, True)
         assert nm[i] == n_o and np.array_equal(m12[i, :counts[i]], m_o), f"pair {i}"
     ex.close()
+
+
+def test_generate_point_clouds_batch():
+    from test_oracle_frame import make_cloud_case
+    cam = capi.Camera(517.3, 516.5, 318.6, 255.3, 0, 0, 0, 0, 0, 40.0)
+    cases = [make_cloud_case(s) for s in range(5)]
+    depth = np.stack([c[0] for c in cases]); bgr = np.stack([c[1] for c in cases]); pose = np.stack([c[2] for c in cases])
+    depth[4] = 0                                                   # an empty cloud
+    for P, Cc in [(pose, bgr), (None, bgr), (pose, None)]:
+        got = capi.generate_point_clouds(depth, Cc, cam, P)
+        for f in range(len(cases)):
+            exp = O.generate_point_cloud(depth[f], None if Cc is None else Cc[f], 517.3, 516.5, 318.6, 255.3,
+                                         pose_inv=None if P is None else P[f])
+            assert len(got[f]) == len(exp) and got[f].tobytes() == exp.tobytes(), f"frame {f}"
+    assert len(got[4]) == 0 and len(got[0]) > 10000
+    # odd geometry, step 1 and 2, more sampled rows than threads per pass
+    rng = np.random.default_rng(9)
+    d = rng.uniform(0, 11, (2, 1100, 37)).astype(np.float32)
+    for step in (1, 2, 5):
+        got = capi.generate_point_clouds(d, None, cam, pose[:2], step=step)
+        for f in range(2):
+            exp = O.generate_point_cloud(d[f], None, 517.3, 516.5, 318.6, 255.3, pose_inv=pose[f], step=step)
+            assert got[f].tobytes() == exp.tobytes()
+    with pytest.raises(capi.OrbxError):
+        capi.generate_point_clouds(depth, bgr, cam, pose, capacity=100)

@@ -64,3 +64,52 @@ def test_depth_and_stereo_from_rgbd():
             assert z[i] == d and ur[i] == np.float32(keys_un[i, 0] - np.float32(bf / d))
         else:
             assert z[i] == -1 and ur[i] == -1
+
+
+def make_cloud_case(seed, w=640, h=480):
+    rng = np.random.default_rng(seed)
+    depth = rng.uniform(0.3, 9.0, (h, w)).astype(np.float32)
+    depth[rng.random((h, w)) < 0.25] = 0.0                      # holes
+    depth[rng.random((h, w)) < 0.05] = np.float32(12.5)         # beyond 10 m
+    depth[0, 0], depth[0, 3], depth[3, 0], depth[3, 3] = np.float32(0.01), np.float32(0.0099999), np.float32(10.0), np.float32(10.000001)
+    bgr = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+    a = rng.normal(size=(3, 3)); q, _ = np.linalg.qr(a)
+    T = np.eye(4); T[:3, :3] = q * np.sign(np.linalg.det(q)); T[:3, 3] = rng.normal(0, 2, 3)
+    return depth, bgr, np.linalg.inv(T)
+
+
+def cloud_numpy(depth, bgr, fx, fy, cx, cy, pose_inv, step=3):
+    """src/PointCloudMap.cc:78-110 vectorised in float32 / float64 numpy"""
+    f32 = np.float32
+    d = depth[::step, ::step]
+    m, n = np.meshgrid(np.arange(0, depth.shape[0], step), np.arange(0, depth.shape[1], step), indexing="ij")
+    keep = ~((d.astype(np.float64) < 0.01) | (d > f32(10)))
+    z = d[keep]
+    x = ((n[keep].astype(f32) - f32(cx)) * z / f32(fx)).astype(f32)
+    y = ((m[keep].astype(f32) - f32(cy)) * z / f32(fy)).astype(f32)
+    out = np.zeros(len(z), O.CLOUD_DTYPE)
+    if pose_inv is not None:
+        P = np.stack([x, y, z]).astype(np.float64)
+        T = pose_inv
+        for k, name in enumerate("xyz"):
+            out[name] = (((T[k, 0] * P[0] + T[k, 1] * P[1]) + T[k, 2] * P[2]) + T[k, 3]).astype(f32)
+    else:
+        out["x"], out["y"], out["z"] = x, y, z
+    out["a"] = 255
+    if bgr is not None:
+        c = bgr[::step, ::step][keep]
+        out["b"], out["g"], out["r"] = c[:, 0], c[:, 1], c[:, 2]
+    return out
+
+
+def test_generate_point_cloud_vs_numpy():
+    depth, bgr, Tinv = make_cloud_case(3)
+    cam = (517.3, 516.5, 318.6, 255.3)
+    for pose, col in [(Tinv, bgr), (None, bgr), (Tinv, None)]:
+        got = O.generate_point_cloud(depth, col, *cam, pose_inv=pose)
+        exp = cloud_numpy(depth, col, *cam, pose)
+        assert len(got) == len(exp) and got.tobytes() == exp.tobytes()
+    assert 0 < len(got) < 214 * 160
+    pts = O.generate_point_cloud(depth, bgr, *cam)
+    # float(0.01f) < 0.01 in double, so a depth of exactly 0.01f is dropped; 10.0f is kept
+    assert pts["z"][0] != np.float32(0.01) and pts["z"].max() == np.float32(10.0)
