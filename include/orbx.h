@@ -415,6 +415,12 @@ int orbm_generate_point_clouds(const float* depth, size_t depth_row_stride, size
                                const orbx_camera* cam, const double* pose_inv, int device, orbx_cloud_point* points,
                                int capacity, int32_t* counts);
 
+/* The per-feature record of Map::Save's keyframe block (src/Map.cc:160-180): 64 bytes = pt.x, pt.y, size, angle,
+ * response (float), octave (int), the 32 descriptor bytes, and the unsigned long index of the feature's MapPoint
+ * (ULONG_MAX = none).  Packs the features of result slot `slot` (mvKeys, mDescriptors as the extractor left them on
+ * the device) into `out` (host, capacity records); mp_index: host [n] or NULL (all ULONG_MAX).  *n = record count. */
+int orbx_pack_map_records(orbx_handle* h, int slot, const uint64_t* mp_index, uint8_t* out, int capacity, int32_t* n);
+
 #ifdef __cplusplus
 }
 #endif

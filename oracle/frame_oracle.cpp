@@ -19,7 +19,9 @@
 
 #include <cmath>
 #include <cstddef>
+#include <climits>
 #include <cstdint>
+#include <cstring>
 
 extern "C" {
 
@@ -132,6 +134,29 @@ int oracle_generate_point_cloud(const float* depth, size_t dstride_elems, const 
             ++count;
         }
     return count;
+}
+
+// The feature loop of Map::_WriteKeyFrame (src/Map.cc:160-180) into a byte buffer: kps = 28-byte cv::KeyPoint records.
+// has_mp[i] == 0 -> ULONG_MAX.  Returns bytes written.
+size_t oracle_write_keyframe_features(const uint8_t* kps, const uint8_t* desc, const uint64_t* mp_index, const uint8_t* has_mp,
+                                      int N, uint8_t* out)
+{
+    uint8_t* f = out;
+    for (int i = 0; i < N; i++) {
+        const uint8_t* kp = kps + (size_t)i * 28;
+        std::memcpy(f, kp + 0, 4); f += 4;       // pt.x
+        std::memcpy(f, kp + 4, 4); f += 4;       // pt.y
+        std::memcpy(f, kp + 8, 4); f += 4;       // size
+        std::memcpy(f, kp + 12, 4); f += 4;      // angle
+        std::memcpy(f, kp + 16, 4); f += 4;      // response
+        std::memcpy(f, kp + 20, 4); f += 4;      // octave
+        for (int j = 0; j < 32; j++) *f++ = desc[(size_t)i * 32 + j];
+        unsigned long int mpidx;
+        if (!has_mp || !has_mp[i]) mpidx = ULONG_MAX;
+        else mpidx = mp_index[i];
+        std::memcpy(f, &mpidx, sizeof(mpidx)); f += sizeof(mpidx);
+    }
+    return (size_t)(f - out);
 }
 
 } // extern "C"

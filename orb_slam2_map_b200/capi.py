@@ -63,7 +63,7 @@ EXPORTS = [
     "orbx_cvt_gray", "orbx_depth_to_float", "orbx_undistort_points", "orbx_image_bounds", "orbx_frames_rgbd",
     "orbx_download_frame_front",
     "orbm_vocabulary_upload", "orbm_vocabulary_free", "orbm_bow_transform", "orbm_search_by_bow", "orbm_distinctive_descriptors",
-    "orbm_search_for_triangulation", "orbm_fuse", "orbm_search_by_sim3", "orbm_generate_point_clouds",
+    "orbm_search_for_triangulation", "orbm_fuse", "orbm_search_by_sim3", "orbm_generate_point_clouds", "orbx_pack_map_records",
 ]
 
 
@@ -304,6 +304,14 @@ class Extractor:
         check(lib().orbx_download_frame_front(self.h, first_slot, nframes, kun.ctypes.data_as(C.c_void_p), ur.ctypes.data_as(C.c_void_p),
                                               z.ctypes.data_as(C.c_void_p), self.cap, b.ctypes.data_as(C.c_void_p)))
         return kun, ur, z, b
+
+    def pack_map_records(self, slot, mp_index=None):
+        """Map::Save per-feature records (64 bytes each) of result slot `slot`"""
+        out = np.zeros((self.cap, 64), np.uint8)
+        n = C.c_int32()
+        mp = None if mp_index is None else np.ascontiguousarray(mp_index, np.uint64)
+        check(lib().orbx_pack_map_records(self.h, slot, _p(mp), _p(out), self.cap, C.byref(n)))
+        return out[:n.value].copy()
 
     def search_init_pairs(self, first_slot, npairs, window=100, nnratio=0.9, check_ori=True, fetch=True):
         ncmp = C.c_uint64()

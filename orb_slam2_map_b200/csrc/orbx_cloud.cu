@@ -12,6 +12,9 @@
 
 #include "orbx_internal.h"
 
+//   K23 pack_records_kernel  the per-feature record of Map::Save's keyframe block (src/Map.cc:160-180): 16 lanes per
+//                            feature, one 4-byte word each, so the 64-byte records leave as coalesced stores
+
 #include <algorithm>
 #include <vector>
 
@@ -166,4 +169,42 @@ extern "C" int orbm_generate_point_clouds(const float* depth, size_t depth_row_s
                                  (size_t)counts[f] * sizeof(orbx_cloud_point), cudaMemcpyDeviceToHost));
     }
     return ORBX_OK;
+}
+
+__global__ void pack_records_kernel(const orbx_keypoint* __restrict__ kps, const uint8_t* __restrict__ desc,
+                                    const unsigned long long* __restrict__ mpIndex, int n, uint32_t* __restrict__ out)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x, i = t >> 4, w = t & 15;
+    if (i >= n) return;
+    uint32_t v;
+    if (w < 5) v = reinterpret_cast<const uint32_t*>(kps + i)[w];                  // pt.x, pt.y, size, angle, response
+    else if (w == 5) v = (uint32_t)kps[i].octave;
+    else if (w < 14) v = reinterpret_cast<const uint32_t*>(desc + (size_t)i * 32)[w - 6];
+    else { const unsigned long long m = mpIndex ? mpIndex[i] : ~0ull; v = w == 14 ? (uint32_t)m : (uint32_t)(m >> 32); }
+    out[t] = v;
+}
+
+extern "C" int orbx_pack_map_records(orbx_handle* h, int slot, const uint64_t* mp_index, uint8_t* out, int capacity, int32_t* n)
+{
+    if (!h || !out || !n) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
+    if (slot < 0 || slot >= h->resultSlots) { orbx_set_error("slot out of bounds"); return ORBX_E_INVALID; }
+    ORBX_CUDA(cudaSetDevice(h->device));
+    int cnt = 0;
+    ORBX_CUDA(cudaMemcpyAsync(&cnt, h->dCount + slot, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    int rc = orbx_sync(h); if (rc) return rc;
+    cnt = std::min(cnt, h->kpCap);
+    *n = cnt;
+    if (cnt > capacity) { orbx_set_error("capacity %d < %d records", capacity, cnt); return ORBX_E_CAPACITY; }
+    if (cnt == 0) return ORBX_OK;
+    CBuf dOut, dIdx;
+    if ((rc = dOut.alloc((size_t)cnt * 64))) return rc;
+    if (mp_index) {
+        if ((rc = dIdx.alloc((size_t)cnt * 8))) return rc;
+        ORBX_CUDA(cudaMemcpyAsync(dIdx.p, mp_index, (size_t)cnt * 8, cudaMemcpyHostToDevice, h->stream));
+    }
+    pack_records_kernel<<<(cnt * 16 + 255) / 256, 256, 0, h->stream>>>(h->dKps + (size_t)slot * h->kpCap, h->dDesc + (size_t)slot * h->kpCap * 32,
+                                                                      mp_index ? dIdx.as<unsigned long long>() : nullptr, cnt, dOut.as<uint32_t>());
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaMemcpyAsync(out, dOut.p, (size_t)cnt * 64, cudaMemcpyDeviceToHost, h->stream));
+    return orbx_sync(h);
 }

@@ -465,3 +465,15 @@ def generate_point_cloud(depth, bgr, fx, fy, cx, cy, pose_inv=None, step=3):
     n = lib().oracle_generate_point_cloud(_p(depth), C.c_size_t(W), _p(bgr), C.c_size_t(W * 3), C.c_int(W), C.c_int(H), C.c_int(step),
                                           C.c_float(fx), C.c_float(fy), C.c_float(cx), C.c_float(cy), _p(pose_inv), _p(out))
     return out[:n].copy()
+
+
+def write_keyframe_features(kps, desc, mp_index=None):
+    kps = np.ascontiguousarray(kps, KP_DTYPE); desc = np.ascontiguousarray(desc, np.uint8)
+    n = len(kps)
+    out = np.zeros((max(n, 1), 64), np.uint8)
+    has = None if mp_index is None else np.ascontiguousarray(np.asarray(mp_index) != np.uint64(0xFFFFFFFFFFFFFFFF), np.uint8)
+    mp = None if mp_index is None else np.ascontiguousarray(mp_index, np.uint64)
+    lib().oracle_write_keyframe_features.restype = C.c_size_t
+    nb = lib().oracle_write_keyframe_features(_p(kps), _p(desc), _p(mp), _p(has), C.c_int(n), _p(out))
+    assert nb == n * 64
+    return out[:n].copy()

@@ -128,3 +128,16 @@ def test_generate_point_clouds_batch():
             assert got[f].tobytes() == exp.tobytes()
     with pytest.raises(capi.OrbxError):
         capi.generate_point_clouds(depth, bgr, cam, pose, capacity=100)
+
+
+def test_pack_map_records():
+    img = synth.frame_sequence(1, 640, 480, seed=12)[0]
+    ex = capi.Extractor(max_width=640, max_height=480, chunk_frames=2)
+    k, d = ex.extract(img)
+    n = len(k)
+    assert n > 500
+    rng = np.random.default_rng(1)
+    mp = rng.integers(0, 1 << 40, n).astype(np.uint64); mp[::4] = np.uint64(0xFFFFFFFFFFFFFFFF)
+    got = ex.pack_map_records(0, mp)
+    assert got.shape == (n, 64) and got.tobytes() == O.write_keyframe_features(k[:n], d[:n], mp).tobytes()
+    assert ex.pack_map_records(0).tobytes() == O.write_keyframe_features(k[:n], d[:n], None).tobytes()

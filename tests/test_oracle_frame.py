@@ -113,3 +113,23 @@ def test_generate_point_cloud_vs_numpy():
     pts = O.generate_point_cloud(depth, bgr, *cam)
     # float(0.01f) < 0.01 in double, so a depth of exactly 0.01f is dropped; 10.0f is kept
     assert pts["z"][0] != np.float32(0.01) and pts["z"].max() == np.float32(10.0)
+
+
+def test_write_keyframe_features_layout():
+    rng = np.random.default_rng(4)
+    n = 57
+    k = np.zeros(n, O.KP_DTYPE)
+    for name in ("x", "y", "size", "angle", "response"):
+        k[name] = rng.uniform(0, 500, n).astype(np.float32)
+    k["octave"] = rng.integers(0, 8, n); k["class_id"] = -1
+    d = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    mp = rng.integers(0, 1 << 40, n).astype(np.uint64); mp[::3] = np.uint64(0xFFFFFFFFFFFFFFFF)
+    rec = O.write_keyframe_features(k, d, mp)
+    dt = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"), ("octave", "<i4"),
+                   ("desc", "u1", 32), ("mp", "<u8")])
+    assert dt.itemsize == 64
+    r = rec.reshape(-1).view(dt)
+    for name in ("x", "y", "size", "angle", "response", "octave"):
+        assert np.array_equal(r[name], k[name])
+    assert np.array_equal(r["desc"], d) and np.array_equal(r["mp"], mp)
+    assert (O.write_keyframe_features(k, d, None).reshape(-1).view(dt)["mp"] == np.uint64(0xFFFFFFFFFFFFFFFF)).all()
