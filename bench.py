@@ -566,11 +566,12 @@ def main():
 
     def step_e2e():
         # host images in -> keypoints / descriptors / counts in host memory (copies overlapped with the kernels
-        # chunk by chunk inside the library), then the matcher with its results copied to the host
-        ex.extract_batch_to_host(hnp, kp_out, de_out, cnt_out)
+        # chunk by chunk inside the library), the matcher of each chunk's pairs and its result copy in the same pipeline
         if match:
-            capi.check(capi.lib().orbx_search_init_pairs(ex.h, 0, F - 1, WINDOW, NNRATIO, 1, m12_out.ctypes.data_as(C.c_void_p),
-                                                         nm_out.ctypes.data_as(C.c_void_p), cap, C.byref(ncmp)))
+            # one pipelined call: the pairs of a chunk are matched right after its extraction
+            ex.extract_match_to_host(hnp, kp_out, de_out, cnt_out, m12_out, nm_out, WINDOW, NNRATIO, True)
+        else:
+            ex.extract_batch_to_host(hnp, kp_out, de_out, cnt_out)
         return kp_out, de_out, cnt_out
 
     _, _, cnts = step_e2e()

@@ -104,6 +104,17 @@ int orbx_extract_batch_to_host(orbx_handle* h, const uint8_t* images, size_t fra
                                int images_on_device, int first_slot, orbx_keypoint* kps,
                                uint8_t* desc, int32_t* counts, int capacity);
 
+/* orbx_extract_batch_to_host with ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:405-520) of every
+ * consecutive pair (frame f, frame f+1) folded into the same chunk pipeline (BASELINE.json configs[1]): the pairs of a
+ * chunk are matched right after its extraction, so the matcher and its result copy overlap the next chunk's input
+ * copy too.  matches12: host [nframes-1][capacity] (vnMatches12 of pair f at row f), nmatches: host [nframes-1];
+ * the result is what orbx_search_init_pairs(first_slot, nframes-1, ...) returns after a plain batch extraction. */
+int orbx_extract_match_to_host(orbx_handle* h, const uint8_t* images, size_t frame_stride,
+                               size_t row_stride, int width, int height, int nframes,
+                               int images_on_device, int first_slot, orbx_keypoint* kps, uint8_t* desc,
+                               int32_t* counts, int capacity, int window_size, float nnratio,
+                               int check_orientation, int32_t* matches12, int32_t* nmatches);
+
 /* Copy results of slots [first_slot, first_slot+nframes) to host: kps[nframes][capacity],
  * desc[nframes][capacity][32], counts[nframes].  Synchronises. Any of kps/desc may be NULL. */
 int orbx_download(orbx_handle* h, int first_slot, int nframes, orbx_keypoint* kps, uint8_t* desc,

@@ -63,7 +63,7 @@ EXPORTS = [
     "orbx_cvt_gray", "orbx_depth_to_float", "orbx_undistort_points", "orbx_image_bounds", "orbx_frames_rgbd",
     "orbx_download_frame_front",
     "orbm_vocabulary_upload", "orbm_vocabulary_free", "orbm_bow_transform", "orbm_search_by_bow", "orbm_distinctive_descriptors",
-    "orbm_search_for_triangulation", "orbm_fuse", "orbm_search_by_sim3", "orbm_generate_point_clouds", "orbx_pack_map_records",
+    "orbm_search_for_triangulation", "orbm_fuse", "orbm_search_by_sim3", "orbm_generate_point_clouds", "orbx_pack_map_records", "orbx_extract_match_to_host",
 ]
 
 
@@ -219,6 +219,15 @@ class Extractor:
         check(lib().orbx_extract_batch_to_host(self.h, C.c_void_p(images.ctypes.data), images.strides[0],
                                                images.strides[1], w, h, n, 0, first_slot, _p(kps), _p(desc),
                                                _p(counts), self.cap))
+
+    def extract_match_to_host(self, images: np.ndarray, kps, desc, counts, matches12, nmatches, window=100, nnratio=0.9,
+                              check_ori=True, first_slot=0):
+        """orbx_extract_match_to_host: extraction + consecutive-frame SearchForInitialization in one chunk pipeline."""
+        assert images.ndim == 3 and images.dtype == np.uint8 and images.strides[2] == 1
+        n, h, w = images.shape
+        check(lib().orbx_extract_match_to_host(self.h, C.c_void_p(images.ctypes.data), C.c_size_t(images.strides[0]),
+                                               C.c_size_t(images.strides[1]), w, h, n, 0, first_slot, _p(kps), _p(desc), _p(counts),
+                                               self.cap, window, C.c_float(nnratio), int(check_ori), _p(matches12), _p(nmatches)))
 
     def download(self, first_slot, nframes, want_kps=True, want_desc=True, out=None):
         counts = np.zeros(nframes, np.int32)

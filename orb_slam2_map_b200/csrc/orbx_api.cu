@@ -7,7 +7,9 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <vector>
 
 static thread_local char g_err[512] = "";
 
@@ -179,7 +181,7 @@ int orbx_create(const orbx_params* params, int max_width, int max_height, int ch
     ORBX_CUDA(cudaStreamCreateWithFlags(&h->copyStream, cudaStreamNonBlocking));
     ORBX_CUDA(cudaStreamCreateWithFlags(&h->d2hStream, cudaStreamNonBlocking));
     ORBX_CUDA(cudaEventCreateWithFlags(&h->evDone, cudaEventDisableTiming));
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < ORBX_L0_BUFS; ++b) {
         ORBX_CUDA(cudaEventCreateWithFlags(&h->evCopied[b], cudaEventDisableTiming));
         ORBX_CUDA(cudaEventCreateWithFlags(&h->evFree[b], cudaEventDisableTiming));
         h->evFreeValid[b] = false;
@@ -221,7 +223,7 @@ int orbx_destroy(orbx_handle* h)
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->hStage) cudaFreeHost(h->hStage);
     for (cudaEvent_t e : h->evPool) cudaEventDestroy(e);
-    for (int b = 0; b < 2; ++b) { cudaEventDestroy(h->evCopied[b]); cudaEventDestroy(h->evFree[b]); }
+    for (int b = 0; b < ORBX_L0_BUFS; ++b) { cudaEventDestroy(h->evCopied[b]); cudaEventDestroy(h->evFree[b]); }
     cudaStreamDestroy(h->copyStream);
     cudaStreamDestroy(h->d2hStream);
     cudaEventDestroy(h->evDone);
@@ -269,13 +271,18 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* images, size_t frame_strid
                                       first_slot, nullptr, nullptr, nullptr, 0);
 }
 
-int orbx_extract_batch_to_host(orbx_handle* h, const uint8_t* images, size_t frame_stride,
-                               size_t row_stride, int width, int height, int nframes,
-                               int images_on_device, int first_slot, orbx_keypoint* kps, uint8_t* desc,
-                               int32_t* counts, int capacity)
+} // extern "C"
+
+// consecutive-frame SearchForInitialization folded into the chunk pipeline (orbx_extract_match_to_host)
+struct MatchOpts { int window; float nnratio; int checkOri; int32_t* matches12; int32_t* nmatches; };
+
+static int batch_to_host_impl(orbx_handle* h, const uint8_t* images, size_t frame_stride,
+                              size_t row_stride, int width, int height, int nframes,
+                              int images_on_device, int first_slot, orbx_keypoint* kps, uint8_t* desc,
+                              int32_t* counts, int capacity, const MatchOpts* mo)
 {
     if (!h || !images) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
-    const bool toHost = kps || desc || counts;
+    const bool toHost = kps || desc || counts || (mo && (mo->matches12 || mo->nmatches));
     if ((kps || desc) && capacity < h->kpCap) { orbx_set_error("output capacity %d < %d", capacity, h->kpCap); return ORBX_E_CAPACITY; }
     if (width <= 0 || height <= 0 || nframes <= 0) return ORBX_OK;   // empty image: silent return
     if (width < 64 || height < 64) { orbx_set_error("image smaller than 64x64 is outside the extractor's domain"); return ORBX_E_INVALID; }
@@ -285,6 +292,7 @@ int orbx_extract_batch_to_host(orbx_handle* h, const uint8_t* images, size_t fra
     int rc = orbx_setup_shape(h, width, height);
     if (rc) return rc;
     h->storeUndistorted = false;            // plain extraction: mvKeysUn = mvKeys, bounds = the image (orbx_frames_rgbd sets them after)
+    if (mo) { rc = orbx_ensure_match_buffers(h); if (rc) return rc; }
     const bool direct = images_on_device && (row_stride % 4 == 0) && (((uintptr_t)images) % 4 == 0) && (frame_stride % 4 == 0);
     // Host (or unaligned device) images: chunk i+1 is copied into the other half of dLevel0 on the
     // copy stream while the kernels of chunk i run; events order copy -> compute -> buffer reuse.
@@ -295,6 +303,11 @@ int orbx_extract_batch_to_host(orbx_handle* h, const uint8_t* images, size_t fra
         ORBX_CUDA(cudaStreamWaitEvent(h->copyStream, evStart, 0));
         ORBX_CUDA(cudaEventDestroy(evStart));
     }
+    // ORBX_PIPE_TRACE=1: print the chunk timeline (copy / kernels / result copy, ms from the first copy) to stderr
+    const bool trace = !direct && getenv("ORBX_PIPE_TRACE") != nullptr;
+    std::vector<cudaEvent_t> tev;
+    std::vector<int> tnf;
+    auto mark = [&](cudaStream_t st) { if (!trace) return; cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, st); tev.push_back(e); };
     int chunkNo = 0;
     for (int f0 = 0, nf = 0; f0 < nframes; f0 += nf, ++chunkNo) {
         // host images: ramp the first two chunks (1/4, 1/2 of a chunk) so that less of the first
@@ -302,24 +315,38 @@ int orbx_extract_batch_to_host(orbx_handle* h, const uint8_t* images, size_t fra
         int cf = h->chunkFrames;
         if (!direct && nframes > h->chunkFrames) cf = chunkNo == 0 ? std::max(1, cf / 4) : (chunkNo == 1 ? std::max(1, cf / 2) : cf);
         nf = std::min(cf, nframes - f0);
+        // ... and taper the tail the same way: the kernels and the device->host copy of the last chunk are exposed
+        if (!direct && toHost && nframes > h->chunkFrames && nf == nframes - f0 && nf > std::max(1, h->chunkFrames / 4))
+            nf = std::max(std::max(1, h->chunkFrames / 4), (nf + 1) / 2);
         const uint8_t* src = images + (size_t)f0 * frame_stride;
         Level0 l0;
         l0.base1 = nullptr; l0.stereo = 0;
         if (direct) { l0.base = src; l0.frameStride = (long long)frame_stride; l0.pitch = (int)row_stride; }
         else {
-            const int b = chunkNo & 1;
+            const int b = chunkNo % ORBX_L0_BUFS;
             uint8_t* dstBuf = h->dLevel0 + (size_t)b * h->chunkFrames * h->l0FrameBytes;
             if (h->evFreeValid[b]) ORBX_CUDA(cudaStreamWaitEvent(h->copyStream, h->evFree[b], 0));
+            mark(h->copyStream);
             rc = orbx_copy_frames(h, dstBuf, h->l0FrameBytes, h->dStageLin + (size_t)b * h->chunkFrames * h->l0FrameBytes, src, frame_stride,
                                   row_stride, width, height, nf, images_on_device != 0, h->copyStream, &l0.frameStride);
             if (rc) return rc;
             ORBX_CUDA(cudaEventRecord(h->evCopied[b], h->copyStream));
+            mark(h->copyStream);
             ORBX_CUDA(cudaStreamWaitEvent(h->stream, h->evCopied[b], 0));
             l0.base = dstBuf; l0.pitch = h->l0Pitch;
         }
+        mark(h->stream);
         rc = orbx_run_chunk(h, l0, nf, first_slot + f0);
         if (rc) return rc;
-        if (!direct) { ORBX_CUDA(cudaEventRecord(h->evFree[chunkNo & 1], h->stream)); h->evFreeValid[chunkNo & 1] = true; }
+        if (!direct) { ORBX_CUDA(cudaEventRecord(h->evFree[chunkNo % ORBX_L0_BUFS], h->stream)); h->evFreeValid[chunkNo % ORBX_L0_BUFS] = true; }
+        // pairs (f-1, f) for the frames of this chunk; the grid of frame f0-1 was built with the previous chunk
+        const int p0 = std::max(f0 - 1, 0), np = f0 + nf - 1 - p0;
+        if (mo) {
+            rc = orbx_match_chunk(h, first_slot + f0, nf, first_slot + p0, np, mo->window, mo->nnratio, mo->checkOri);
+            if (rc) return rc;
+        }
+        mark(h->stream);
+        tnf.push_back(nf);
         if (toHost) {
             // results of this chunk go back on the copy stream while the next chunk computes
             const int s0 = first_slot + f0;
@@ -333,13 +360,55 @@ int orbx_extract_batch_to_host(orbx_handle* h, const uint8_t* images, size_t fra
                 ORBX_CUDA(cudaMemcpy2DAsync(desc + (size_t)f0 * capacity * 32, (size_t)capacity * 32, h->dDesc + (size_t)s0 * h->kpCap * 32,
                                             (size_t)h->kpCap * 32, (size_t)h->kpCap * 32, nf, cudaMemcpyDeviceToHost, h->d2hStream));
             if (counts) ORBX_CUDA(cudaMemcpyAsync(counts + f0, h->dCount + s0, nf * sizeof(int), cudaMemcpyDeviceToHost, h->d2hStream));
+            if (mo && np > 0) {
+                const int ps = first_slot + p0;
+                if (mo->matches12)
+                    ORBX_CUDA(cudaMemcpy2DAsync(mo->matches12 + (size_t)p0 * capacity, (size_t)capacity * 4, h->dMatches12 + (size_t)ps * h->kpCap,
+                                                (size_t)h->kpCap * 4, (size_t)h->kpCap * 4, np, cudaMemcpyDeviceToHost, h->d2hStream));
+                if (mo->nmatches) ORBX_CUDA(cudaMemcpyAsync(mo->nmatches + p0, h->dNMatches + ps, np * sizeof(int), cudaMemcpyDeviceToHost, h->d2hStream));
+            }
+            mark(h->d2hStream);
         }
     }
     if (toHost) {
         ORBX_CUDA(cudaStreamSynchronize(h->d2hStream));
-        return orbx_sync(h);
+        rc = orbx_sync(h);
+        if (trace && rc == ORBX_OK) {
+            cudaStreamSynchronize(h->copyStream);
+            const size_t per = 5;
+            for (size_t c = 0; c * per + per <= tev.size(); ++c) {
+                float t[5];
+                for (int k = 0; k < 5; ++k) cudaEventElapsedTime(&t[k], tev[0], tev[c * per + k]);
+                fprintf(stderr, "chunk %2zu nf %4d  copy %7.3f-%7.3f  kernels %7.3f-%7.3f  d2h done %7.3f\n", c, tnf[c], t[0], t[1], t[2], t[3], t[4]);
+            }
+        }
+        for (cudaEvent_t e : tev) cudaEventDestroy(e);
+        return rc;
     }
     return ORBX_OK;
+}
+
+extern "C" {
+
+int orbx_extract_batch_to_host(orbx_handle* h, const uint8_t* images, size_t frame_stride,
+                               size_t row_stride, int width, int height, int nframes,
+                               int images_on_device, int first_slot, orbx_keypoint* kps, uint8_t* desc,
+                               int32_t* counts, int capacity)
+{
+    return batch_to_host_impl(h, images, frame_stride, row_stride, width, height, nframes, images_on_device, first_slot, kps, desc,
+                              counts, capacity, nullptr);
+}
+
+int orbx_extract_match_to_host(orbx_handle* h, const uint8_t* images, size_t frame_stride,
+                               size_t row_stride, int width, int height, int nframes,
+                               int images_on_device, int first_slot, orbx_keypoint* kps, uint8_t* desc,
+                               int32_t* counts, int capacity, int window_size, float nnratio,
+                               int check_orientation, int32_t* matches12, int32_t* nmatches)
+{
+    if (matches12 && capacity < (h ? h->kpCap : 0)) { orbx_set_error("matches12 capacity %d < %d", capacity, h->kpCap); return ORBX_E_CAPACITY; }
+    const MatchOpts mo = {window_size, nnratio, check_orientation, matches12, nmatches};
+    return batch_to_host_impl(h, images, frame_stride, row_stride, width, height, nframes, images_on_device, first_slot, kps, desc,
+                              counts, capacity, &mo);
 }
 
 int orbx_download(orbx_handle* h, int first_slot, int nframes, orbx_keypoint* kps, uint8_t* desc,

@@ -1085,9 +1085,9 @@ int orbx_setup_shape(orbx_handle* h, int w, int hgt)
     h->nBlurTiles = (int)tiles.size();
     h->l0Pitch = (w + 15) & ~15;
     h->l0FrameBytes = (((long long)h->l0Pitch * hgt) + 255) & ~255LL;
-    ORBX_CUDA(re((void**)&h->dLevel0, 2 * C * h->l0FrameBytes));
-    ORBX_CUDA(re((void**)&h->dStageLin, 2 * C * h->l0FrameBytes));
-    h->evFreeValid[0] = h->evFreeValid[1] = false;
+    ORBX_CUDA(re((void**)&h->dLevel0, ORBX_L0_BUFS * C * h->l0FrameBytes));
+    ORBX_CUDA(re((void**)&h->dStageLin, ORBX_L0_BUFS * C * h->l0FrameBytes));
+    for (int b = 0; b < ORBX_L0_BUFS; ++b) h->evFreeValid[b] = false;
     ORBX_CUDA(re((void**)&h->dRaw, C * g.pyrFrameBytes));
     ORBX_CUDA(re((void**)&h->dBlur, C * g.pyrFrameBytes));
     ORBX_CUDA(re((void**)&h->dCand, C * g.candTotal * sizeof(uint32_t)));

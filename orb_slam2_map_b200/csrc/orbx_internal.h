@@ -9,6 +9,7 @@
 #include "../../include/orbx.h"
 
 #define ORBX_MAX_LEVELS 16
+#define ORBX_L0_BUFS 2        // chunk-sized input buffers of the host-image pipeline (3 measured no faster: the kernels, not the copies, pace it)
 #define ORBX_GRID_COLS 64     // FRAME_GRID_COLS, reference include/Frame.h:38
 #define ORBX_GRID_ROWS 48     // FRAME_GRID_ROWS, reference include/Frame.h:37
 #define ORBX_GRID_CELLS (ORBX_GRID_COLS * ORBX_GRID_ROWS)
@@ -96,12 +97,12 @@ struct orbx_handle {
     int nBlurTiles;
     int* dKpMap;        // keypoint-slot -> level map for the describe kernel
     // workspace (chunkFrames deep)
-    uint8_t* dLevel0;   // pitched copies of the input images (when needed): two chunk-sized buffers
+    uint8_t* dLevel0;   // pitched copies of the input images (when needed): ORBX_L0_BUFS chunk-sized buffers
     uint8_t* dStageLin; // same size: landing zone for LINEAR host->device copies (then re-pitched on the device)
     cudaStream_t copyStream;        // host->device copies of chunk i+1 overlap the kernels of chunk i
     cudaStream_t d2hStream;         // device->host copies of chunk i overlap the kernels of chunk i+1
-    cudaEvent_t evCopied[2], evFree[2], evDone;
-    bool evFreeValid[2];
+    cudaEvent_t evCopied[ORBX_L0_BUFS], evFree[ORBX_L0_BUFS], evDone;
+    bool evFreeValid[ORBX_L0_BUFS];
     int l0Pitch;
     long long l0FrameBytes;
     uint8_t* dRaw;      // pyramid levels >= 1
@@ -168,5 +169,7 @@ int orbx_copy_frames(orbx_handle* h, uint8_t* dst, long long dstFrameBytes, uint
 // orbx_match.cu
 int orbx_build_grids(orbx_handle* h, int firstSlot, int nframes, int width, int height);
 int orbx_ensure_match_buffers(orbx_handle* h);
+// grids of result slots [gridFirst, +gridCount) then SearchForInitialization for pairs (s, s+1), s in [pairFirst, +npairs); async on h->stream
+int orbx_match_chunk(orbx_handle* h, int gridFirst, int gridCount, int pairFirst, int npairs, int window, float nnratio, int checkOri);
 
 #endif

@@ -791,6 +791,27 @@ static int launch_stereo(const FrameStore& fs, int firstSlot, int npairs, const 
     return ORBX_OK;
 }
 
+int orbx_match_chunk(orbx_handle* h, int gridFirst, int gridCount, int pairFirst, int npairs, int window, float nnratio, int checkOri)
+{
+    const FrameStore fs = store_of(h);
+    const GridParams gp = h->storeUndistorted ? orbx_grid_params(h->bounds[0], h->bounds[1], h->bounds[2], h->bounds[3])
+                                              : orbx_grid_params(0.f, (float)h->curW, 0.f, (float)h->curH);
+    orbx_prof_mark(h, -1);
+    int rc = orbx_launch_grid_build(fs, gridFirst, gridCount, gp, h->stream);
+    if (rc) return rc;
+    ORBX_COUNT(h, ORBX_STAGE_GRID, 1);
+    orbx_prof_mark(h, ORBX_STAGE_GRID);
+    if (npairs > 0) {
+        rc = launch_search_init(fs, pairFirst, 1, npairs, gp, nullptr, window, nnratio, checkOri,
+                                h->dMatches12 + (size_t)pairFirst * h->kpCap, h->dNMatches + pairFirst, nullptr, h->stream);
+        if (rc) return rc;
+        ORBX_COUNT(h, ORBX_STAGE_SEARCH_INIT, 1);
+        orbx_prof_mark(h, ORBX_STAGE_SEARCH_INIT);
+    }
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
 extern "C" {
 
 int orbx_search_init_pairs(orbx_handle* h, int first_slot, int npairs, int window_size, float nnratio,

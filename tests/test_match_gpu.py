@@ -100,3 +100,25 @@ def test_search_init_empty_frames():
     f = capi.FrameData(k, d, 640, 480)
     n_g, m_g, _ = capi.search_for_initialization(f, f, np.zeros((0, 2), np.float32))
     assert n_g == 0 and len(m_g) == 0
+
+
+def test_extract_match_pipeline_equals_separate_calls():
+    """orbx_extract_match_to_host (matcher folded into the chunk pipeline, ramped and tapered chunks) against
+    batch extraction followed by orbx_search_init_pairs."""
+    n = 23
+    frames = synth.frame_sequence(n, 640, 480, seed=5)
+    ex = capi.Extractor(max_width=640, max_height=480, chunk_frames=4, result_slots=n)
+    cap = ex.cap
+    kp = np.zeros((n, cap), capi.KP_DTYPE); de = np.zeros((n, cap, 32), np.uint8); cnt = np.zeros(n, np.int32)
+    m12 = np.full((n - 1, cap), -7, np.int32); nm = np.full(n - 1, -7, np.int32)
+    ex.extract_match_to_host(frames, kp, de, cnt, m12, nm, 100, 0.9, True)
+    ex2 = capi.Extractor(max_width=640, max_height=480, chunk_frames=8, result_slots=n)
+    ex2.extract_batch(frames)
+    k2, d2, c2 = ex2.download(0, n)
+    m2, nm2, _ = ex2.search_init_pairs(0, n - 1, 100, 0.9, True)
+    assert np.array_equal(cnt, c2) and nm.min() > 50
+    for f in range(n):
+        assert kp[f, :cnt[f]].tobytes() == k2[f, :c2[f]].tobytes() and np.array_equal(de[f, :cnt[f]], d2[f, :c2[f]])
+    assert np.array_equal(nm, nm2)
+    for f in range(n - 1):
+        assert np.array_equal(m12[f, :cnt[f]], m2[f, :c2[f]]), f"pair {f}"
