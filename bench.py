@@ -73,6 +73,15 @@ NCU_DRAM_BYTES_PER_FRAME = {
     "resize": (19.685632e6 + 13.945344e6 + 9.565184e6 + 6.846208e6 + 4.746752e6 + 3.375872e6 + 2.319360e6 + 0.03e6) / 64,
     "octree": 1.813504e6 / 64,
 }
+# warp instructions executed per 640x480 frame by each extractor kernel (smsp__inst_executed.sum of the same capture):
+# these kernels are bound by instruction issue (4 warp instructions per clock per SM), not by HBM
+NCU_WARP_INST_PER_FRAME = {
+    "fast": 126475674 / 64,
+    "blur": 57940864 / 64,
+    "describe": 44826992 / 64,
+    "resize": (14293120 + 9487168 + 5967488 + 4954176 + 4143232 + 2305088 + 1924992) / 64,
+    "octree": 8843212 / 64,
+}
 
 
 def measured_peaks():
@@ -622,6 +631,13 @@ def main():
                 "peak_source": peak_src,
                 "algorithmic_bytes_per_frame": dom_bytes,
                 "share_of_device_time": dom_ms / max(sum(stage_ms.values()), 1e-9)}
+    if (W, H) == (640, 480) and dom in NCU_WARP_INST_PER_FRAME and clk.get("sm_mhz") and dom_ms > 0:
+        # the bound that actually limits this kernel: issue slots (148 SMs x 4 schedulers x SM clock under load)
+        ginst = NCU_WARP_INST_PER_FRAME[dom] * (frames_total / dom_launches) / (dom_ms / dom_launches * 1e-3) / 1e9
+        issue_peak = 148 * 4 * clk["sm_mhz"] * 1e6 / 1e9
+        roofline["issue"] = {"achieved": ginst, "peak": issue_peak, "unit": "G warp-inst/s", "frac": ginst / issue_peak,
+                             "warp_inst_per_frame": NCU_WARP_INST_PER_FRAME[dom],
+                             "source": "smsp__inst_executed.sum, profiles/r01i_ncu_full_chunk64_summary.txt"}
     path_gbs = ab["total"] * value / world / 1e9
     stages = {k: {"ms_per_step": v / args.steps, "launches_per_step": stage_launches[k] / args.steps}
               for k, v in stage_ms.items() if stage_launches[k]}

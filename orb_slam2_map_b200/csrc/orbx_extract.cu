@@ -188,22 +188,24 @@ __device__ __forceinline__ void edge_mode(int x, int w, int& mode, uint32_t& sel
     }
 }
 
-// INTERIOR: every source row of the strip (y0-3 .. y0-4+7*ngroups) exists, no row reflection needed
+// INTERIOR: every source row of the strip (y0-3 .. y0-4+7*ngroups) exists, no row reflection needed.
+// EDGE: some lane of the warp holds (or follows) the last column or sits at x = -4 and rebuilds its word from its
+// neighbours; strips that lie inside the row skip those four shuffles.
 template <bool INTERIOR>
 __device__ __forceinline__ void blur_strip(const u8* __restrict__ src, int sp, u8* __restrict__ dst, int dp,
-                                           int w, int h, int x, int y0, int th, int lane)
+                                           int w, int h, int x, int y0, int th, int lane, int mode, uint32_t sel, bool EDGE)
 {
     const unsigned FULL = 0xffffffffu;
     const uint32_t c0 = 18u | (34u << 8) | (48u << 16) | (56u << 24), c1 = 48u | (34u << 8) | (18u << 16);
     const int rowsOut = min(th, h - y0);
     const int ngroups = (rowsOut + 6 + 6) / 7;
     const int xl = min(max(x, 0), (w - 1) & ~3);  // every lane loads an aligned word that lies inside the row
-    int mode; uint32_t sel;
-    edge_mode(x, w, mode, sel);
     const bool store = lane >= 1 && lane <= 30 && x < w;
     uint32_t H[7][4];
     uint32_t cur[7], nxt[7];
     const u8* colp = src + (long long)(y0 - 3) * sp + xl;         // row y0-3 of the lane's column (INTERIOR addressing)
+    u8* dcol = dst + x;                                           // kept in registers: the row address is one IMAD.WIDE
+    asm volatile("" : "+l"(dcol));
 #pragma unroll
     for (int k = 0; k < 7; ++k)
         cur[k] = INTERIOR ? *reinterpret_cast<const uint32_t*>(colp + k * sp)
@@ -216,22 +218,25 @@ __device__ __forceinline__ void blur_strip(const u8* __restrict__ src, int sp, u
                 nxt[k] = INTERIOR ? *reinterpret_cast<const uint32_t*>(colp + ((gi + 1) * 7 + k) * sp)
                                   : *reinterpret_cast<const uint32_t*>(src + (long long)reflect_row(y0 - 3 + (gi + 1) * 7 + k, h) * sp + xl);
         }
+        const bool later = gi > 0;                                // rows r >= 7: a full window exists
 #pragma unroll
         for (int k = 0; k < 7; ++k) {
             const int r = gi * 7 + k;
             uint32_t w1 = cur[k];
-            const uint32_t d1 = __shfl_down_sync(FULL, w1, 1), d2 = __shfl_down_sync(FULL, w1, 2);
-            const uint32_t u1 = __shfl_up_sync(FULL, w1, 1), u2 = __shfl_up_sync(FULL, w1, 2);
-            const uint32_t pa = mode == 3 ? d1 : (mode == 2 ? u2 : u1), pb = mode == 3 ? d2 : (mode == 2 ? u1 : w1);
-            if (mode != 0) w1 = __byte_perm(pa, pb, sel);
+            if (EDGE) {
+                const uint32_t d1 = __shfl_down_sync(FULL, w1, 1), d2 = __shfl_down_sync(FULL, w1, 2);
+                const uint32_t u1 = __shfl_up_sync(FULL, w1, 1), u2 = __shfl_up_sync(FULL, w1, 2);
+                const uint32_t pa = mode == 3 ? d1 : (mode == 2 ? u2 : u1), pb = mode == 3 ? d2 : (mode == 2 ? u1 : w1);
+                if (mode != 0) w1 = __byte_perm(pa, pb, sel);
+            }
             const uint32_t w0 = __shfl_up_sync(FULL, w1, 1), w2 = __shfl_down_sync(FULL, w1, 1);
             H[k][0] = __dp4a(__byte_perm(w0, w1, 0x4321), c0, __dp4a(__byte_perm(w1, w2, 0x4321), c1, 0u));
             H[k][1] = __dp4a(__byte_perm(w0, w1, 0x5432), c0, __dp4a(__byte_perm(w1, w2, 0x5432), c1, 0u));
             H[k][2] = __dp4a(__byte_perm(w0, w1, 0x6543), c0, __dp4a(__byte_perm(w1, w2, 0x6543), c1, 0u));
             H[k][3] = __dp4a(w1, c0, __dp4a(w2, c1, 0u));
-            // rows r-6 .. r are in slots (k+1)%7 .. k ; output row y = y0 + r - 6
+            // rows r-6 .. r are in slots (k+1)%7 .. k ; output row y = y0 + r - 6 (r >= 6 <=> gi > 0 or k == 6)
             const int y = y0 + r - 6;
-            if (r >= 6 && y < h) {
+            if ((later || k == 6) && (INTERIOR || y < h)) {
                 uint32_t o[4];
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
@@ -241,7 +246,7 @@ __device__ __forceinline__ void blur_strip(const u8* __restrict__ src, int sp, u
                     o[j] = 18u * s0 + 34u * s1 + 48u * s2 + 56u * H[(k + 4) % 7][j] + 32768u;   // result in bits 16..23
                 }
                 const uint32_t lo = __byte_perm(o[0], o[1], 0x0062), hi = __byte_perm(o[2], o[3], 0x0062);
-                if (store) *reinterpret_cast<uint32_t*>(dst + (unsigned)(y * dp + x)) = __byte_perm(lo, hi, 0x5410);
+                if (store) *reinterpret_cast<uint32_t*>(dcol + (unsigned long long)(unsigned)y * (unsigned)dp) = __byte_perm(lo, hi, 0x5410);
             }
         }
 #pragma unroll
@@ -266,8 +271,13 @@ blur7_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, u8* __restrict__
     else { src = rawBase + (long long)frame * g.pyrFrameBytes + L.off; sp = L.pitch; }
     u8* dst = blurBase + (long long)frame * g.pyrFrameBytes + L.off;
     const int y0 = ty * L.blurTH, ngroups = (min(L.blurTH, L.h - y0) + 6 + 6) / 7;
-    if (y0 >= 3 && y0 - 3 + 7 * ngroups <= L.h) blur_strip<true>(src, sp, dst, L.pitch, L.w, L.h, tx * BL_TW - 4 + lane * 4, y0, L.blurTH, lane);
-    else blur_strip<false>(src, sp, dst, L.pitch, L.w, L.h, tx * BL_TW - 4 + lane * 4, y0, L.blurTH, lane);
+    const int x = tx * BL_TW - 4 + lane * 4;
+    int mode; uint32_t sel;
+    edge_mode(x, L.w, mode, sel);
+    const bool interior = y0 >= 3 && y0 - 3 + 7 * ngroups <= L.h;
+    const bool edge = __any_sync(0xffffffffu, mode != 0);         // warp-uniform
+    if (interior) blur_strip<true>(src, sp, dst, L.pitch, L.w, L.h, x, y0, L.blurTH, lane, mode, sel, edge);
+    else blur_strip<false>(src, sp, dst, L.pitch, L.w, L.h, x, y0, L.blurTH, lane, mode, sel, edge);
 }
 
 // =============================================================================================
