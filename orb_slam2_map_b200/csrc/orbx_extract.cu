@@ -62,12 +62,13 @@ pyr_resize_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long lo
 // only on the column (source column, 11-bit coefficients, byte selectors) is hoisted out of the
 // row loop.  A source row contributes 3 aligned 32-bit words per lane; the two taps of a pixel are
 // picked with byte-permutes and combined with one IDP.2A (u16 x u8 dot product).  The horizontal
-// sums of a source row are kept in registers and reused by the next output row (consecutive
-// output rows share a source row when the scale is < 2).  Vertical blend = OpenCV's
+// sums of a source row are computed once per strip (consecutive output rows share a source row
+// when the scale is < 2).  Vertical blend = OpenCV's
 // ((b*(S>>4))>>16 ... +2)>>2 with the >>16 folded into a high multiply.
 // =============================================================================================
-#define RS_TARGET 12                    // strips are about this tall, balanced over the level (short strips: the row
-                                        // walk is latency bound, more warps in flight beat the amortised column setup)
+#define RS_TARGET 12                    // strips are about this tall, balanced over the level (measured 8 .. 48: taller
+                                        // strips need more shared memory per warp and lose more to occupancy than the
+                                        // amortised column setup gains)
 #define RS_WARPS 4
 
 // per-lane column constants: the two taps of output pixel i lie at bytes t, t+1 (0 <= t <= 11) of the lane's
@@ -75,21 +76,16 @@ pyr_resize_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long lo
 // per pixel, no predicates.
 struct RsCol { uint32_t coef[4]; uint32_t sel1[4], sel2[4]; };
 
-__device__ __forceinline__ void rs_hsum(const uint32_t* __restrict__ p, const RsCol& c, uint32_t Hq[4])
-{
-    const uint32_t w0 = __ldg(p), w1 = __ldg(p + 1), w2 = __ldg(p + 2);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const uint32_t taps = __byte_perm(__byte_perm(w0, w1, c.sel1[i]), w2, c.sel2[i]);
-        Hq[i] = __dp2a_lo(c.coef[i], taps, 0u) >> 4;                    // (p0*a0 + p1*a1) >> 4
-    }
-}
-
-__global__ void __launch_bounds__(RS_WARPS * 32)
+// The row walk used to be bound by load latency (one source row = 3 words in flight per lane, 60 % of the stall
+// samples on the scoreboard).  Now a strip runs in two phases: (1) the horizontal sums of ALL source rows of the strip,
+// four rows (12 independent loads) at a time, parked in shared memory as 4 x u16 per lane; (2) the vertical blends
+// out of shared memory.  Every source row is still summed once.
+__global__ void __launch_bounds__(RS_WARPS * 32, 12)
 pyr_resize4_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long long srcFrameStride, int srcPitch, int sw, int sh,
                    u8* __restrict__ dstBase, long long dstFrameStride, int dstPitch,
-                   int dw, int dh, int th, const int2* __restrict__ cx, const int2* __restrict__ cy)
+                   int dw, int dh, int th, int nsrcMax, const int2* __restrict__ cx, const int2* __restrict__ cy)
 {
+    extern __shared__ uint2 rsH[];              // [warp][source row of the strip][lane]
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int x = (blockIdx.x * 32 + lane) * 4;
     const int y0 = (blockIdx.y * RS_WARPS + wid) * th;
@@ -114,33 +110,46 @@ pyr_resize4_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long l
         }
     }
     const int rowWords = srcPitch >> 2;
-    int ra = -1, rb = -1;                   // source rows whose horizontal sums are in HA / HB
-    uint32_t HA[4], HB[4];
     const int yend = min(y0 + th, dh);
-    auto hrow = [&](int r, uint32_t Hq[4]) { rs_hsum(colp + (long long)r * rowWords, c, Hq); };
+    const int sFirst = cy[y0].x & 0xffff;
+    const int nsrc = min((cy[yend - 1].x >> 16) - sFirst + 1, nsrcMax);
+    uint2* Hs = rsH + (size_t)wid * nsrcMax * 32 + lane;
+    // ---- phase 1: horizontal sums of the strip's source rows -------------------------------------
+    {
+        const uint32_t* p = colp + (long long)sFirst * rowWords;
+        for (int r = 0; r < nsrc; r += 4) {
+            uint32_t w[4][3];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const uint32_t* q = p + (long long)min(r + u, nsrc - 1) * rowWords;
+                w[u][0] = __ldg(q); w[u][1] = __ldg(q + 1); w[u][2] = __ldg(q + 2);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                uint32_t Hq[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const uint32_t taps = __byte_perm(__byte_perm(w[u][0], w[u][1], c.sel1[i]), w[u][2], c.sel2[i]);
+                    Hq[i] = __dp2a_lo(c.coef[i], taps, 0u) >> 4;                    // (p0*a0 + p1*a1) >> 4 < 2^15
+                }
+                if (r + u < nsrc) Hs[(r + u) * 32] = make_uint2(Hq[0] | (Hq[1] << 16), Hq[2] | (Hq[3] << 16));
+            }
+        }
+    }
+    __syncwarp();
+    // ---- phase 2: vertical blends ((b0*SA >> 16) + (b1*SB >> 16) + 2) >> 2 ------------------------
     for (int y = y0; y < yend; ++y) {
         const int2 cyv = cy[y];
-        const int sy0 = cyv.x & 0xffff, sy1 = cyv.x >> 16;
-        const uint32_t b0 = (uint32_t)(cyv.y & 0xffff) << 16, b1 = (uint32_t)(cyv.y >> 16) << 16;
-        if (sy0 != ra) {
-            if (sy0 == rb) {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) HA[i] = HB[i];
-            } else hrow(sy0, HA);
-            ra = sy0;
-        }
-        if (sy1 != rb) {
-            if (sy1 == ra) {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) HB[i] = HA[i];
-            } else hrow(sy1, HB);
-            rb = sy1;
-        }
-        uint32_t o[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) o[i] = (__umulhi(b0, HA[i]) + __umulhi(b1, HB[i]) + 2u) >> 2;
+        const int ia = min((cyv.x & 0xffff) - sFirst, nsrc - 1), ib = min((cyv.x >> 16) - sFirst, nsrc - 1);
+        const uint32_t b0 = (uint32_t)(cyv.y & 0xffff), b1 = (uint32_t)(cyv.y >> 16);
+        const uint2 A = Hs[ia * 32], B = Hs[ib * 32];
+        // even elements sit in the low half (multiply by b << 16), odd ones in the high half (multiply by b)
+        const uint32_t o0 = (__umulhi(b0 << 16, A.x & 0xffffu) + __umulhi(b1 << 16, B.x & 0xffffu) + 2u) >> 2;
+        const uint32_t o1 = (__umulhi(b0, A.x & 0xffff0000u) + __umulhi(b1, B.x & 0xffff0000u) + 2u) >> 2;
+        const uint32_t o2 = (__umulhi(b0 << 16, A.y & 0xffffu) + __umulhi(b1 << 16, B.y & 0xffffu) + 2u) >> 2;
+        const uint32_t o3 = (__umulhi(b0, A.y & 0xffff0000u) + __umulhi(b1, B.y & 0xffff0000u) + 2u) >> 2;
         if (x < dw)
-            *reinterpret_cast<uint32_t*>(dst + (long long)y * dstPitch + x) = o[0] | (o[1] << 8) | (o[2] << 16) | (o[3] << 24);
+            *reinterpret_cast<uint32_t*>(dst + (long long)y * dstPitch + x) = o0 | (o1 << 8) | (o2 << 16) | (o3 << 24);
     }
 }
 
@@ -888,12 +897,15 @@ describe_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, const u8* __r
     const int lane = threadIdx.x & 31;
     const int frame = blockIdx.y, slotk = blockIdx.x * DESC_WARPS + (threadIdx.x >> 5);
     if (slotk >= g.kpTotal) return;
+    // the three loads below do not depend on each other: issue them together (the warp is short-lived, its
+    // chain of dependent global loads is what it mostly waits for)
     const int level = kpMap[slotk];
-    const LevelGeom& L = g.L[level];
-    const int k = slotk - L.kpOff;
+    const uint32_t packed = levelKps[(size_t)frame * g.kpTotal + slotk];
     const int* counts = levelKpCount + frame * g.nlevels;
     // lane l holds the count of level l: output offset = keypoints of the lower levels
     const int myCount = lane < g.nlevels ? counts[lane] : 0;
+    const LevelGeom& L = g.L[level];
+    const int k = slotk - L.kpOff;
     int offset = lane < level ? myCount : 0, total = myCount;
     for (int d = 16; d > 0; d >>= 1) { offset += __shfl_xor_sync(FULL, offset, d); total += __shfl_xor_sync(FULL, total, d); }
     if (slotk == 0) {
@@ -901,7 +913,6 @@ describe_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, const u8* __r
         if (lane < g.nlevels) outLevelCount[(firstSlot + frame) * ORBX_MAX_LEVELS + lane] = myCount;
     }
     if (k >= __shfl_sync(FULL, myCount, level)) return;
-    const uint32_t packed = levelKps[(size_t)frame * g.kpTotal + slotk];
     const int px = key_x(packed) + 16, py = key_y(packed) + 16;     // + minBorderX/Y (EDGE_THRESHOLD-3)
     const u8* raw;
     int rp;
@@ -1171,10 +1182,15 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
         if (l == 1) { src = l0.base; sfs = l0.frameStride; sp = l0.pitch; }
         else { src = h->dRaw + S.off; sfs = g.pyrFrameBytes; sp = S.pitch; }
         if (h->params.scale_factor <= 2.0f) {
-            const int nstrips = std::max(1, (D.h + RS_TARGET - 1) / RS_TARGET), th = (D.h + nstrips - 1) / nstrips;
+            static const int rsTarget = getenv("ORBX_RS_TARGET") ? std::max(4, atoi(getenv("ORBX_RS_TARGET"))) : RS_TARGET;
+            const int nstrips = std::max(1, (D.h + rsTarget - 1) / rsTarget), th = (D.h + nstrips - 1) / nstrips;
             dim3 grid((D.w + 127) / 128, (nstrips + RS_WARPS - 1) / RS_WARPS, nframes);
-            pyr_resize4_kernel<<<grid, RS_WARPS * 32, 0, st>>>(l0, l == 1 ? 1 : 0, src, sfs, sp, S.w, S.h, h->dRaw + D.off, g.pyrFrameBytes,
-                                                               D.pitch, D.w, D.h, th, h->dCoef + D.coefX, h->dCoef + D.coefY);
+            // source rows a strip of th output rows can touch: th * (S.h / D.h) + 2, with slack for the table's rounding
+            const int nsrcMax = (int)((long long)th * S.h / D.h) + 4;
+            const size_t rsSmem = (size_t)RS_WARPS * nsrcMax * 32 * sizeof(uint2);
+            if (rsSmem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(pyr_resize4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsSmem));
+            pyr_resize4_kernel<<<grid, RS_WARPS * 32, rsSmem, st>>>(l0, l == 1 ? 1 : 0, src, sfs, sp, S.w, S.h, h->dRaw + D.off, g.pyrFrameBytes,
+                                                                    D.pitch, D.w, D.h, th, nsrcMax, h->dCoef + D.coefX, h->dCoef + D.coefY);
         } else {
             dim3 grid((D.w + 127) / 128, (D.h + 7) / 8, nframes), block(32, 8);
             pyr_resize_kernel<<<grid, block, 0, st>>>(l0, l == 1 ? 1 : 0, src, sfs, sp, h->dRaw + D.off, g.pyrFrameBytes, D.pitch, D.w, D.h,
