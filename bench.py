@@ -64,24 +64,52 @@ def algorithmic_bytes(w, h, nkp):
                 total=b_pyr + b_fast + b_desc)
 
 
-# measured DRAM bytes per 640x480 frame (read + write) of each extractor kernel, from the r01i `ncu --set full`
-# capture of a 64-frame launch (profiles/r01i_ncu_full_chunk64_summary.txt); resize = sum over the 7 levels
+# measured DRAM bytes per 640x480 frame (read + write) of each extractor kernel, from the r01j `ncu --set full`
+# capture of a 64-frame launch (profiles/r01j_ncu_full_chunk64_summary.txt); resize = sum over the 7 levels
 NCU_DRAM_BYTES_PER_FRAME = {
-    "fast": (55.875328e6 + 1.419520e6) / 64,
-    "blur": (63.966976e6 + 15.665920e6) / 64,
-    "describe": (118.267136e6 + 5.597696e6) / 64,
-    "resize": (19.685632e6 + 13.945344e6 + 9.565184e6 + 6.846208e6 + 4.746752e6 + 3.375872e6 + 2.319360e6 + 0.03e6) / 64,
-    "octree": 1.813504e6 / 64,
+    "fast": (55.876864e6 + 1.015040e6) / 64,
+    "blur": (64.533760e6 + 15.761408e6) / 64,
+    "describe": (118.259456e6 + 6.653440e6) / 64,
+    "resize": (19.689984e6 + 13.948160e6 + 9.569280e6 + 6.850048e6 + 4.752128e6 + 3.382016e6 + 2.323456e6 + 0.03e6) / 64,
+    "octree": 1.814272e6 / 64,
 }
 # warp instructions executed per 640x480 frame by each extractor kernel (smsp__inst_executed.sum of the same capture):
 # these kernels are bound by instruction issue (4 warp instructions per clock per SM), not by HBM
 NCU_WARP_INST_PER_FRAME = {
     "fast": 126475674 / 64,
-    "blur": 57940864 / 64,
-    "describe": 44826992 / 64,
-    "resize": (14293120 + 9487168 + 5967488 + 4954176 + 4143232 + 2305088 + 1924992) / 64,
+    "blur": 51528832 / 64,
+    "describe": 44842346 / 64,
+    "resize": (16092480 + 10659648 + 6708416 + 5568576 + 4677760 + 2598592 + 2169600) / 64,
     "octree": 8843212 / 64,
 }
+
+
+def bind_to_gpu_numa(local):
+    """Pin this rank to the CPUs next to its GPU (sysfs local_cpulist of the GPU's PCI function) BEFORE any pinned
+    host buffer is allocated, so the end-to-end copies of N ranks do not all cross one socket.  Returns a small
+    dict for the JSON line; silently does nothing where the box exposes no topology."""
+    info = {"bound": False}
+    try:
+        out = subprocess.run(["nvidia-smi", "--query-gpu=pci.bus_id", "--format=csv,noheader", "-i", str(local)],
+                             capture_output=True, text=True, timeout=20).stdout.strip().splitlines()[0].strip().lower()
+        bdf = out[-12:] if len(out) >= 12 else out                  # 00000000:1b:00.0 -> 0000:1b:00.0
+        base = "/sys/bus/pci/devices/" + bdf
+        node = int(open(base + "/numa_node").read().strip())
+        cpus = set()
+        for part in open(base + "/local_cpulist").read().strip().split(","):
+            if not part:
+                continue
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        avail = os.sched_getaffinity(0)
+        cpus &= avail
+        info.update({"gpu_pci": bdf, "numa_node": node, "local_cpus": len(cpus)})
+        if cpus and len(cpus) < len(avail):
+            os.sched_setaffinity(0, cpus)
+            info["bound"] = True
+    except Exception as e:      # no topology in this container / VM
+        info["note"] = type(e).__name__
+    return info
 
 
 def measured_peaks():
@@ -254,6 +282,7 @@ def run_knn(args):
     from orb_slam2_map_b200 import sharding, synth
     rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
     torch.cuda.set_device(local)
+    numa = bind_to_gpu_numa(local) if world > 1 else {"bound": False}
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev) if world > 1 else None
     if world == 1:
@@ -324,6 +353,7 @@ def run_stereo(args):
     from orb_slam2_map_b200 import capi, synth
     rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
     torch.cuda.set_device(local)
+    numa = bind_to_gpu_numa(local) if world > 1 else {"bound": False}
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
@@ -379,7 +409,7 @@ def run_stereo(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": "configs[2]: KITTI-shaped 1241x376 stereo pairs, nFeatures 2000, left/right extraction + ComputeStereoMatches",
                        "pairs_per_step_per_gpu": P, "l2_policy": f"inputs ({2 * P * w * h / 1e9:.2f} GB per step) larger than L2",
-                       "sharding": "pairs by rank, no collective"},
+                       "sharding": "pairs by rank, no collective", "rank_cpu_binding": numa},
             "clocks": clk,
             "e2e": {"value": world * P * args.steps / float(dt.item()), "unit": "pairs/s", "h2d_bytes_per_step": 2 * P * w * h,
                     "d2h_bytes_per_step": 2 * P * ex.cap * 4 + 8},
@@ -450,7 +480,8 @@ def run_rgbd(args):
             "clocks": clk,
             "e2e": {"value": F * args.steps / dt, "unit": "frames/s", "h2d_bytes_per_step": F * W * H * 5,
                     "d2h_bytes_per_step": F * ex.cap * (28 + 32 + 28 + 8) + 4 * F},
-            "gpu_launches": None,
+            # per chunk: cvt_gray, 7 resize, blur, FAST, quadtree, describe, depth convertTo, frame_front (+ grid build)
+            "gpu_launches": args.steps * (-(-F // args.chunk)) * (PARAMS["nlevels"] - 1 + 8),
             "roofline": {"bound": "hbm", "kernel": "path", "achieved": ab * value / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": ab * value / 1e9 / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_frame": ab}}
     print(json.dumps(line))
@@ -507,6 +538,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
     torch.cuda.set_device(local)
+    numa = bind_to_gpu_numa(local) if world > 1 else {"bound": False}
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
@@ -619,14 +651,14 @@ def main():
     dom_ms = stage_ms.get(dom, 0.0)
     achieved = (dom_bytes * frames_total / dom_launches) / (dom_ms / dom_launches * 1e-3) / 1e9 if dom_ms > 0 else 0.0
     # DRAM traffic of the dominant kernel: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full`
-    # capture (profiles/r01i_ncu_full_chunk64_summary.txt, a 64-frame launch of the 640x480 workload), scaled to
+    # capture (profiles/r01j_ncu_full_chunk64_summary.txt, a 64-frame launch of the 640x480 workload), scaled to
     # the frames one launch of this run processes.  Other image shapes have no capture: null.
     traffic = None
     if (W, H) == (640, 480) and dom in NCU_DRAM_BYTES_PER_FRAME:
         traffic = NCU_DRAM_BYTES_PER_FRAME[dom] * frames_total / dom_launches
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic,
-                "traffic_source": "ncu --set full, profiles/r01i_ncu_full_chunk64_summary.txt, per-frame bytes x frames per launch" if traffic else None,
+                "traffic_source": "ncu --set full, profiles/r01j_ncu_full_chunk64_summary.txt, per-frame bytes x frames per launch" if traffic else None,
                 "algorithmic_bytes_per_launch": dom_bytes * frames_total / dom_launches,
                 "peak_source": peak_src,
                 "algorithmic_bytes_per_frame": dom_bytes,
@@ -637,7 +669,7 @@ def main():
         issue_peak = 148 * 4 * clk["sm_mhz"] * 1e6 / 1e9
         roofline["issue"] = {"achieved": ginst, "peak": issue_peak, "unit": "G warp-inst/s", "frac": ginst / issue_peak,
                              "warp_inst_per_frame": NCU_WARP_INST_PER_FRAME[dom],
-                             "source": "smsp__inst_executed.sum, profiles/r01i_ncu_full_chunk64_summary.txt"}
+                             "source": "smsp__inst_executed.sum, profiles/r01j_ncu_full_chunk64_summary.txt"}
     path_gbs = ab["total"] * value / world / 1e9
     stages = {k: {"ms_per_step": v / args.steps, "launches_per_step": stage_launches[k] / args.steps}
               for k, v in stage_ms.items() if stage_launches[k]}
@@ -648,7 +680,7 @@ def main():
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": workload_name,
                    "frames_per_step_per_gpu": F, "chunk_frames": args.chunk, "keypoints_per_frame": nkp,
-                   "l2_policy": f"inputs ({F * W * H / 1e9:.2f} GB per step) larger than L2", "sharding": "frames by rank, no collective"},
+                   "l2_policy": f"inputs ({F * W * H / 1e9:.2f} GB per step) larger than L2", "sharding": "frames by rank, no collective", "rank_cpu_binding": numa},
         "clocks": clk,
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "h2d_gbs_measured": h2d_gbs, "pcie_bound_frames_s": world * h2d_gbs * 1e9 / (W * H)},
