@@ -21,7 +21,9 @@
 #define ORBX_HPP
 
 #include <cstdint>
+#include <algorithm>
 #include <cstring>
+#include <utility>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -206,6 +208,55 @@ struct ProjectionResult {
     std::vector<int32_t> bestIdx, bestDist;   // per query
 };
 
+// What the keyframe-rate matchers read from a KeyFrame (reference include/KeyFrame.h): the Frame data plus the level
+// sigma tables, the FeatureVector node of every feature and two per-feature flags.
+struct KeyFrameView {
+    FrameView frame;
+    const std::vector<float>* mvLevelSigma2 = nullptr;
+    const std::vector<float>* mvInvLevelSigma2 = nullptr;
+    const std::vector<uint32_t>* featNode = nullptr;     // node id of mFeatVec that holds feature i
+    const std::vector<uint8_t>* flags = nullptr;         // bit 0: in mFeatVec, bit 1: GetMapPoint(i) != NULL (SearchByBoW: and not bad)
+
+    orbm_keyframe c() const
+    {
+        orbm_keyframe k;
+        k.frame = frame.c();
+        k.level_sigma2 = mvLevelSigma2 ? mvLevelSigma2->data() : nullptr;
+        k.inv_level_sigma2 = mvInvLevelSigma2 ? mvInvLevelSigma2->data() : nullptr;
+        k.node_id = featNode ? featNode->data() : nullptr;
+        k.flags = flags ? flags->data() : nullptr;
+        return k;
+    }
+};
+
+// ORBVocabulary (DBoW2 TemplatedVocabulary) flattened once and kept on the device.
+class Vocabulary {
+public:
+    Vocabulary(const orbm_vocabulary& flat, int device = 0) { check(orbm_vocabulary_upload(&flat, device, &h_), "Vocabulary"); }
+    ~Vocabulary() { if (h_) orbm_vocabulary_free(h_); }
+    Vocabulary(const Vocabulary&) = delete;
+    Vocabulary& operator=(const Vocabulary&) = delete;
+    // what Frame::ComputeBoW / KeyFrame::ComputeBoW evaluate per feature (levelsup = 4): the caller accumulates
+    // mBowVec[word] += weight and mFeatVec[node].push_back(i) for the features with weight > 0
+    void transform(const uint8_t* descriptors, int n, int levelsup, std::vector<uint32_t>& word, std::vector<double>& weight,
+                   std::vector<uint32_t>& node)
+    {
+        word.assign((size_t)n, 0); weight.assign((size_t)n, 0.0); node.assign((size_t)n, 0);
+        check(orbm_bow_transform(h_, descriptors, n, levelsup, word.data(), weight.data(), node.data()), "Vocabulary::transform");
+    }
+private:
+    orbm_vocab_handle* h_ = nullptr;
+};
+
+struct BowSide {                       // one frame of SearchByBoW
+    int n = 0;
+    const uint8_t* descriptors = nullptr;
+    const float* angles = nullptr;
+    const uint32_t* node = nullptr;
+    const uint8_t* flags = nullptr;
+    orbm_bow_frame c() const { orbm_bow_frame f; f.n = n; f.descriptors = descriptors; f.angles = angles; f.node_id = node; f.flags = flags; return f; }
+};
+
 // ---------------------------------------------------------------------------------------------
 // ORBmatcher (reference include/ORBmatcher.h:36)
 // ---------------------------------------------------------------------------------------------
@@ -264,6 +315,55 @@ public:
         return r;
     }
 
+    // SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) (src/ORBmatcher.cc:159, variant 0) and
+    // SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12) (:522, variant 1).  matchA[i] / matchB[j]: partner feature or -1.
+    int SearchByBoW(int variant, const BowSide& A, const BowSide& B, std::vector<int>& matchA, std::vector<int>& matchB, int device = 0)
+    {
+        const orbm_bow_frame a = A.c(), b = B.c();
+        matchA.assign((size_t)A.n, -1); matchB.assign((size_t)B.n, -1);
+        int32_t n = 0;
+        check(orbm_search_by_bow(variant, &a, &b, 1, mfNNratio, mbCheckOrientation ? 1 : 0, device, matchA.data(), matchB.data(), &n), "SearchByBoW");
+        return n;
+    }
+
+    // SearchForTriangulation (src/ORBmatcher.cc:657): F12 row-major, (ex, ey) the epipole of :664-670
+    int SearchForTriangulation(const KeyFrameView& KF1, const KeyFrameView& KF2, const float F12[9], float ex, float ey,
+                               std::vector<std::pair<size_t, size_t>>& vMatchedPairs, bool bOnlyStereo, int device = 0)
+    {
+        const orbm_keyframe k1 = KF1.c(), k2 = KF2.c();
+        std::vector<int32_t> m((size_t)std::max(k1.frame.n, 1), -1);
+        const float epi[2] = {ex, ey};
+        int32_t n = 0;
+        check(orbm_search_for_triangulation(&k1, &k2, 1, F12, epi, bOnlyStereo ? 1 : 0, mbCheckOrientation ? 1 : 0, device, m.data(), &n),
+              "SearchForTriangulation");
+        vMatchedPairs.clear();
+        vMatchedPairs.reserve((size_t)n);
+        for (int i = 0; i < k1.frame.n; ++i) if (m[i] >= 0) vMatchedPairs.push_back(std::make_pair((size_t)i, (size_t)m[i]));
+        return n;
+    }
+
+    // the per-MapPoint search of Fuse (variant ORBM_FUSE_MAPPOINTS / ORBM_FUSE_SIM3); the caller replays the side effects
+    std::vector<int32_t> Fuse(int variant, const KeyFrameView& KF, const ProjectionQueries& Q, int device = 0)
+    {
+        const orbm_keyframe k = KF.c();
+        std::vector<int32_t> best(Q.q.size(), -1);
+        check(orbm_fuse(variant, &k, Q.q.data(), Q.descriptors.data(), (int)Q.q.size(), device, best.data(), nullptr), "Fuse");
+        return best;
+    }
+
+    // SearchBySim3 (src/ORBmatcher.cc:1102): Q12 = MapPoints of KF1 (features index1) projected into KF2, Q21 the reverse
+    int SearchBySim3(const KeyFrameView& KF1, const KeyFrameView& KF2, const ProjectionQueries& Q12, const std::vector<int32_t>& index1,
+                     const ProjectionQueries& Q21, const std::vector<int32_t>& index2, std::vector<int>& match12, int device = 0)
+    {
+        const orbm_keyframe k1 = KF1.c(), k2 = KF2.c();
+        match12.assign((size_t)std::max(k1.frame.n, 1), -1);
+        int32_t n = 0;
+        check(orbm_search_by_sim3(&k1, &k2, Q12.q.data(), Q12.descriptors.data(), index1.data(), (int)Q12.q.size(), Q21.q.data(),
+                                  Q21.descriptors.data(), index2.data(), (int)Q21.q.size(), device, match12.data(), &n), "SearchBySim3");
+        match12.resize((size_t)k1.frame.n);
+        return n;
+    }
+
 protected:
     float mfNNratio;
     bool mbCheckOrientation;
@@ -301,6 +401,33 @@ inline void ComputeStereoMatches(const std::vector<KeyPoint>& keysLeft, const ui
     mvuRight.assign(keysLeft.size(), -1.0f);
     mvDepth.assign(keysLeft.size(), -1.0f);
     check(orbm_compute_stereo_matches(&in, mvuRight.data(), mvDepth.data(), nullptr), "ComputeStereoMatches");
+}
+
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242) for a batch of map points: descriptors of point p are
+// rows offsets[p] .. offsets[p+1]; returns the index (inside its group) of each point's distinctive descriptor.
+inline std::vector<int32_t> ComputeDistinctiveDescriptors(const uint8_t* descriptors, const std::vector<int32_t>& offsets, int device = 0)
+{
+    const int np = (int)offsets.size() - 1;
+    std::vector<int32_t> best((size_t)std::max(np, 0), -1);
+    if (np > 0) check(orbm_distinctive_descriptors(descriptors, offsets.data(), np, device, best.data(), nullptr), "ComputeDistinctiveDescriptors");
+    return best;
+}
+
+// PointCloudMapping::generatePointCloud (src/PointCloudMap.cc:78) for one keyframe: depth CV_32F, bgr 8UC3 (or NULL),
+// poseInv = toSE3Quat(kf->GetPose()).inverse().matrix() row-major (or NULL: convertToPointCloud)
+inline std::vector<orbx_cloud_point> GeneratePointCloud(const float* depth, size_t depthStepFloats, const uint8_t* bgr, size_t bgrStep,
+                                                        int cols, int rows, float fx, float fy, float cx, float cy,
+                                                        const double* poseInv, int device = 0)
+{
+    orbx_camera cam{};
+    cam.fx = fx; cam.fy = fy; cam.cx = cx; cam.cy = cy;
+    const int cap = ((cols + 2) / 3) * ((rows + 2) / 3);
+    std::vector<orbx_cloud_point> pts((size_t)cap);
+    int32_t n = 0;
+    check(orbm_generate_point_clouds(depth, depthStepFloats, depthStepFloats * rows, bgr, bgrStep, bgrStep * rows, cols, rows, 1, 3, &cam,
+                                     poseInv, device, pts.data(), cap, &n), "generatePointCloud");
+    pts.resize((size_t)n);
+    return pts;
 }
 
 } // namespace orbx

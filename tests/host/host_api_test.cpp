@@ -3,7 +3,10 @@
 //   in.raw : int32 w, h, nframes(=2) followed by nframes*w*h bytes
 //   out.bin: for each frame: int32 n, n*28 bytes keypoints, n*32 bytes descriptors; then the pyramid
 //            level 3 of frame 1 with border (int32 rows, cols, bytes); then int32 nmatches,
-//            int32 n1, n1*int32 vnMatches12, n1*2 floats vbPrevMatched
+//            int32 n1, n1*int32 vnMatches12, n1*2 floats vbPrevMatched; then the keyframe-rate section:
+//            int32 nq, nq*int32 Fuse best index (frame 1 as keyframe, its own keypoints of frame 0 as queries);
+//            int32 npoints, npoints*int32 distinctive-descriptor index (groups of 5 descriptors of frame 0);
+//            int32 ncloud, ncloud*16 bytes point cloud of a synthetic depth map (= pixel value / 32 of frame 0)
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -60,6 +63,41 @@ int main(int argc, char** argv)
         fwrite(vnMatches12.data(), 4, n1, o);
         fwrite(vbPrevMatched.data(), 8, n1, o);
         if (orbx::ORBmatcher::DescriptorDistance(desc[0].data(), desc[0].data()) != 0) return 6;
+        // LocalMapping::SearchInNeighbors-style Fuse: keypoints of frame 0 as already projected MapPoints, searched in
+        // frame 1 used as a keyframe (th = 3)
+        std::vector<float> scale = extractor.GetScaleFactors(), invSigma2 = extractor.GetInverseScaleSigmaSquares(),
+                           sigma2 = extractor.GetScaleSigmaSquares();
+        orbx::KeyFrameView KF;
+        KF.frame = F2; KF.frame.mvScaleFactors = &scale; KF.mvLevelSigma2 = &sigma2; KF.mvInvLevelSigma2 = &invSigma2;
+        orbx::ProjectionQueries Q;
+        for (size_t i = 0; i < keys[0].size(); ++i) {
+            orbm_proj_query q{};
+            q.u = keys[0][i].x; q.v = keys[0][i].y; q.radius = 3.0f * scale[keys[0][i].octave];
+            q.min_level = -1; q.max_level = -1; q.u_right = -1.f; q.max_right_err = -1.f; q.angle = keys[0][i].angle;
+            q.level_lo = keys[0][i].octave - 1; q.level_hi = keys[0][i].octave;
+            Q.q.push_back(q);
+        }
+        Q.descriptors = desc[0];
+        const std::vector<int32_t> fused = matcher.Fuse(ORBM_FUSE_MAPPOINTS, KF, Q);
+        int32_t nq = (int32_t)fused.size();
+        fwrite(&nq, 4, 1, o);
+        fwrite(fused.data(), 4, nq, o);
+        // MapPoint::ComputeDistinctiveDescriptors on groups of 5 consecutive descriptors
+        std::vector<int32_t> offsets;
+        for (int32_t i = 0; i + 5 <= (int32_t)keys[0].size() && offsets.size() < 101; i += 5) offsets.push_back(i);
+        const std::vector<int32_t> dd = orbx::ComputeDistinctiveDescriptors(desc[0].data(), offsets);
+        int32_t np = (int32_t)dd.size();
+        fwrite(&np, 4, 1, o);
+        fwrite(dd.data(), 4, np, o);
+        // PointCloudMapping::generatePointCloud on depth = pixel / 32 (so part of the map is below 0.01 or 0)
+        std::vector<float> depth((size_t)w * h);
+        for (size_t i = 0; i < depth.size(); ++i) depth[i] = (float)img[i] / 32.0f;
+        const double Tinv[16] = {0.36, 0.48, -0.8, 0.1, -0.8, 0.6, 0, -0.2, 0.48, 0.64, 0.6, 0.3, 0, 0, 0, 1};
+        const std::vector<orbx_cloud_point> cloud = orbx::GeneratePointCloud(depth.data(), (size_t)w, nullptr, 0, w, h, 517.3f, 516.5f,
+                                                                            318.6f, 255.3f, Tinv);
+        int32_t nc = (int32_t)cloud.size();
+        fwrite(&nc, 4, 1, o);
+        fwrite(cloud.data(), 16, nc, o);
     } catch (const std::exception& e) {
         fprintf(stderr, "host_api_test: %s\n", e.what());
         fclose(o);

@@ -65,8 +65,34 @@ def test_host_classes_match_oracle(tmp_path):
     assert np.array_equal(lvl, O.border101(orc.level(3), 19))      # mvImagePyramid[3] with its 19-px border
     nm, n1 = struct.unpack_from("<2i", buf, pos); pos += 8
     m12 = np.frombuffer(buf, np.int32, n1, pos); pos += 4 * n1
-    pm = np.frombuffer(buf, np.float32, 2 * n1, pos).reshape(n1, 2)
+    pm = np.frombuffer(buf, np.float32, 2 * n1, pos).reshape(n1, 2); pos += 8 * n1
     f1, f2 = O.FrameData(ref[0][0], ref[0][1], w, h), O.FrameData(ref[1][0], ref[1][1], w, h)
     prev = np.stack([f1.kps["x"], f1.kps["y"]], axis=1)
     n_o, m_o, p_o, _ = O.search_for_initialization(f1, f2, prev, 100, 0.9, True)
     assert nm == n_o and np.array_equal(m12, m_o) and np.array_equal(pm, p_o)
+    # keyframe-rate wrappers: Fuse, ComputeDistinctiveDescriptors, generatePointCloud
+    nq, = struct.unpack_from("<i", buf, pos); pos += 4
+    fused = np.frombuffer(buf, np.int32, nq, pos); pos += 4 * nq
+    tab = orc.tables()
+    kf = O.KeyFrameData(ref[1][0], ref[1][1], w, h, None, tab["scale"], tab["sigma2"])
+    kf.is2 = tab["inv_sigma2"].copy(); kf.c.inv_level_sigma2 = kf.is2.ctypes.data
+    q = np.zeros(nq, O.PROJ_DTYPE)
+    k0 = ref[0][0]
+    q["u"], q["v"] = k0["x"], k0["y"]
+    q["radius"] = np.float32(3.0) * tab["scale"][k0["octave"]]
+    q["min_level"] = -1; q["max_level"] = -1; q["u_right"] = -1; q["max_right_err"] = -1; q["angle"] = k0["angle"]
+    q["level_lo"] = k0["octave"] - 1; q["level_hi"] = k0["octave"]
+    bo, _ = O.fuse(0, kf, q, ref[0][1])
+    assert np.array_equal(fused, bo) and (fused >= 0).sum() > 50
+    npts, = struct.unpack_from("<i", buf, pos); pos += 4
+    dd = np.frombuffer(buf, np.int32, npts, pos); pos += 4 * npts
+    offs = np.arange(0, len(k0) - 4, 5, dtype=np.int32)[:101]
+    io, _ = O.distinctive_descriptors(ref[0][1], offs)
+    assert npts == len(offs) - 1 and np.array_equal(dd, io)
+    nc, = struct.unpack_from("<i", buf, pos); pos += 4
+    cloud = np.frombuffer(buf, O.CLOUD_DTYPE, nc, pos); pos += 16 * nc
+    Tinv = np.array([0.36, 0.48, -0.8, 0.1, -0.8, 0.6, 0, -0.2, 0.48, 0.64, 0.6, 0.3, 0, 0, 0, 1], np.float64)
+    exp = O.generate_point_cloud(frames[0].astype(np.float32) / np.float32(32.0), None, np.float32(517.3), np.float32(516.5),
+                                 np.float32(318.6), np.float32(255.3), pose_inv=Tinv)
+    assert nc == len(exp) and cloud.tobytes() == exp.tobytes()
+    assert pos == len(buf)
