@@ -393,11 +393,13 @@ def run_stereo(args):
     stage_ms, stage_launches = ex.profile(); ex.set_profiling(False)
     clk = clocks.stop()
     hln, hrn = hl.numpy(), hr.numpy()
-    ex.extract_stereo_batch(hln, hrn, bf, fx)
+    outs = (torch.empty((P, ex.cap), dtype=torch.float32, pin_memory=True).numpy(),
+            torch.empty((P, ex.cap), dtype=torch.float32, pin_memory=True).numpy())        # mvuRight, mvDepth in pinned host memory
+    ex.extract_stereo_batch(hln, hrn, bf, fx, out=outs)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        ur, dp, ncmp = ex.extract_stereo_batch(hln, hrn, bf, fx)
+        ur, dp, ncmp = ex.extract_stereo_batch(hln, hrn, bf, fx, out=outs)
     dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(dt, op=dist.ReduceOp.MAX)

@@ -335,7 +335,8 @@ class Extractor:
         return None
 
     def extract_stereo_batch(self, left, right, bf, fx, nframes=None, width=None, height=None, frame_stride=None,
-                             row_stride=None, on_device=False, first_slot=0, fetch=True):
+                             row_stride=None, on_device=False, first_slot=0, fetch=True, out=None):
+        """out: optional caller-owned (pinned) float32 arrays (u_right, depth) of shape [npairs, cap]"""
         if isinstance(left, np.ndarray):
             assert left.shape == right.shape and left.strides == right.strides
             nframes, height, width = left.shape
@@ -345,8 +346,11 @@ class Extractor:
             lp, rp = int(left), int(right)
         ncmp = C.c_uint64()
         if fetch:
-            ur = np.zeros((nframes, self.cap), np.float32)
-            dp = np.zeros((nframes, self.cap), np.float32)
+            if out is not None:
+                ur, dp = out
+            else:
+                ur = np.zeros((nframes, self.cap), np.float32)
+                dp = np.zeros((nframes, self.cap), np.float32)
             check(lib().orbx_extract_stereo_batch(self.h, C.c_void_p(lp), C.c_void_p(rp), frame_stride, row_stride,
                                                   width, height, nframes, int(on_device), first_slot, bf, fx, _p(ur),
                                                   _p(dp), self.cap, C.byref(ncmp)))

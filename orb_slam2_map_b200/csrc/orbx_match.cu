@@ -1057,8 +1057,14 @@ int orbx_extract_stereo_batch(orbx_handle* h, const uint8_t* left, const uint8_t
         ORBX_CUDA(cudaEventDestroy(evStart));
     }
     int chunkNo = 0;
-    for (int p0 = 0; p0 < npairs; p0 += pairsPerChunk, ++chunkNo) {
-        const int np = std::min(pairsPerChunk, npairs - p0);
+    for (int p0 = 0, np = 0; p0 < npairs; p0 += np, ++chunkNo) {
+        // host images: ramp the first two chunks and taper the tail (as orbx_extract_batch_to_host does), so that less
+        // of the first copy and of the last chunk's kernels is exposed
+        int cp = pairsPerChunk;
+        if (!direct && npairs > pairsPerChunk) cp = chunkNo == 0 ? std::max(1, cp / 4) : (chunkNo == 1 ? std::max(1, cp / 2) : cp);
+        np = std::min(cp, npairs - p0);
+        if (!direct && npairs > pairsPerChunk && np == npairs - p0 && np > std::max(1, pairsPerChunk / 4))
+            np = std::max(std::max(1, pairsPerChunk / 4), (np + 1) / 2);
         Level0 l0;
         l0.stereo = 1;
         if (direct) {
