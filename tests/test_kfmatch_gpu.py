@@ -62,3 +62,32 @@ def test_search_for_triangulation_batch(only_stereo, ori):
         assert nm[p] == n_o and np.array_equal(ms[p], m_o), f"pair {p}"
         total += n_o
     assert total > 100
+
+
+def test_keyframe_matchers_empty_and_degenerate_inputs():
+    kf1, kf2, F, epi = make_tri_pair(9, n1=120, n2=150)
+    a, b = _to_capi(kf1), _to_capi(kf2)
+    fd = kf2.fd
+    # KF2 without features / without any FeatureVector entry / F12 == 0 (den == 0 -> CheckDistEpipolarLine false)
+    empty = O.KeyFrameData(fd.kps[:0], fd.desc[:0], 640, 480, fd.u_right[:0], SCALE, SIGMA2, kf2.node[:0], kf2.flags[:0])
+    nofv = O.KeyFrameData(fd.kps, fd.desc, 640, 480, fd.u_right, SCALE, SIGMA2, kf2.node, np.zeros_like(kf2.flags))
+    for other, Fm in [(empty, F), (nofv, F), (kf2, np.zeros(9, np.float32))]:
+        nm, ms = capi.search_for_triangulation([(a, _to_capi(other))], [Fm], [epi])
+        n_o, m_o = O.search_for_triangulation(kf1, other, Fm, epi)
+        assert nm[0] == n_o == 0 and np.array_equal(ms[0], m_o) and (ms[0] == -1).all()
+    nm, ms = capi.search_for_triangulation([(_to_capi(empty), b)], [F], [epi])
+    assert nm[0] == 0 and len(ms[0]) == 0
+    # SearchBySim3 with one empty direction: nothing can agree
+    kfa, kfb, q12, d12, i1, q21, d21, i2 = make_sim3_case(31)
+    nf, m12 = capi.search_by_sim3(_to_capi(kfa), _to_capi(kfb), q12, d12, i1, q21[:0], d21[:0], i2[:0])
+    nf_o, m_o = O.search_by_sim3(kfa, kfb, q12, d12, i1, q21[:0], d21[:0], i2[:0])
+    assert nf == nf_o == 0 and np.array_equal(m12, m_o)
+    # out-of-range feature index is rejected, not read
+    bad = i1.copy(); bad[0] = kfa.n
+    with pytest.raises(capi.OrbxError):
+        capi.search_by_sim3(_to_capi(kfa), _to_capi(kfb), q12, d12, bad, q21, d21, i2)
+    # ComputeDistinctiveDescriptors: no points, and only empty groups
+    i0, _ = capi.distinctive_descriptors(np.zeros((0, 32), np.uint8), np.zeros(1, np.int32))
+    assert len(i0) == 0
+    i3, m3 = capi.distinctive_descriptors(np.zeros((0, 32), np.uint8), np.zeros(4, np.int32))
+    assert (i3 == -1).all() and (m3 == -1).all()
