@@ -95,19 +95,29 @@ grid_build_kernel(FrameStore fs, int firstSlot, GridParams gp)
 //     (src/ORBmatcher.cc:444), take best / second best, steal-back bookkeeping (:463-471).
 // =============================================================================================
 #define SI_WARPS 8
-#define SI_QBLOCK 64
+#define SI_QBLOCK 32
 #define SI_MAXC 32
-#define SI_DESC_SMEM 512            // F2 descriptors staged in shared memory (the octave-0 ones come first)
+#define SI_DESC_SMEM 256            // F2 descriptors staged in shared memory (the octave-0 ones come first)
+#define SI_PEND 64                  // per-warp buffer of window hits waiting for their Hamming distance
 
+// The searches only ever return octave-0 keypoints of F2 (level window [0,0], src/ORBmatcher.cc:425), about a
+// fifth of the frame.  They are compacted once per pair into the list L, in the grid's enumeration order (cell-major,
+// index-minor = the order Frame::GetFeaturesInArea walks), each with its grid cell.  A query then tests all of L
+// with full lanes — cell inside the query's cell window AND |dx| < r AND |dy| < r, exactly the two filters of
+// GetFeaturesInArea — instead of walking the grid with one lane per column (6 of 32 lanes busy, 2.5 in the Hamming
+// code); the hits are compacted by ballot and their Hamming distances computed 32 at a time.  The list position
+// is the tie-break key (it is monotonic in the enumeration order).
 struct SiSmem {
-    float* kx; float* ky;            // F2 positions (+inf for octave > 0: never inside a window)
-    unsigned short* gs; unsigned short* gi;
+    float* lx; float* ly;            // L: positions
+    unsigned short* lidx;            // L: keypoint index in F2
+    unsigned short* lcell;           // L: cell x | cell y << 8
     unsigned short* md; unsigned short* m21;
     unsigned short* qlist;           // octave-0 keypoints of F1 in index order
     u8* binOf;                       // per F1 keypoint
     uint32_t* cand;                  // [2][SI_QBLOCK][SI_MAXC]
     int* ccount;                     // [2][SI_QBLOCK] (> SI_MAXC = overflow)
     int* hist;
+    unsigned short* pend;            // [SI_WARPS][SI_PEND]
     u8* desc;                        // first SI_DESC_SMEM descriptors of F2
 };
 
@@ -117,13 +127,14 @@ __device__ __forceinline__ SiSmem si_carve(unsigned char* base, int cap)
     unsigned char* p = base;
     const size_t h = ((size_t)cap + 1) / 2 * 4;      // bytes of a u16[cap] array, 4-byte granular
     s.desc = p; p += (size_t)min(cap, SI_DESC_SMEM) * 32;
-    s.kx = reinterpret_cast<float*>(p); p += (size_t)cap * 4;
-    s.ky = reinterpret_cast<float*>(p); p += (size_t)cap * 4;
+    s.lx = reinterpret_cast<float*>(p); p += (size_t)cap * 4;
+    s.ly = reinterpret_cast<float*>(p); p += (size_t)cap * 4;
     s.cand = reinterpret_cast<uint32_t*>(p); p += 2 * SI_QBLOCK * SI_MAXC * 4;
     s.ccount = reinterpret_cast<int*>(p); p += 2 * SI_QBLOCK * 4;
     s.hist = reinterpret_cast<int*>(p); p += 32 * 4;
-    s.gs = reinterpret_cast<unsigned short*>(p); p += (ORBX_GRID_CELLS + 2) * 2;
-    s.gi = reinterpret_cast<unsigned short*>(p); p += h;
+    s.pend = reinterpret_cast<unsigned short*>(p); p += SI_WARPS * SI_PEND * 2;
+    s.lidx = reinterpret_cast<unsigned short*>(p); p += h;
+    s.lcell = reinterpret_cast<unsigned short*>(p); p += h;
     s.md = reinterpret_cast<unsigned short*>(p); p += h;
     s.m21 = reinterpret_cast<unsigned short*>(p); p += h;
     s.qlist = reinterpret_cast<unsigned short*>(p); p += h;
@@ -133,7 +144,7 @@ __device__ __forceinline__ SiSmem si_carve(unsigned char* base, int cap)
 static size_t si_smem_bytes(int cap)
 {
     return (size_t)std::min(cap, SI_DESC_SMEM) * 32 + (size_t)cap * 8 + 2 * SI_QBLOCK * SI_MAXC * 4 + 2 * SI_QBLOCK * 4 + 128 +
-           (ORBX_GRID_CELLS + 2) * 2 + 4 * (((size_t)cap + 1) / 2 * 4) + ((size_t)cap + 3) / 4 * 4 + 16;
+           SI_WARPS * SI_PEND * 2 + 5 * (((size_t)cap + 1) / 2 * 4) + ((size_t)cap + 3) / 4 * 4 + 16;
 }
 
 struct SiCtx {
@@ -143,7 +154,7 @@ struct SiCtx {
     const float* prev;
     GridParams gp;
     float r;
-    int dkeep, ndescSmem;
+    int dkeep, ndescSmem, nL;
 };
 
 __device__ __forceinline__ const uint32_t* si_desc2(const SiCtx& c, int idx)
@@ -151,11 +162,20 @@ __device__ __forceinline__ const uint32_t* si_desc2(const SiCtx& c, int idx)
     return reinterpret_cast<const uint32_t*>(idx < c.ndescSmem ? c.S.desc + (size_t)idx * 32 : c.d2g + (size_t)idx * 32);
 }
 
+// is list entry p returned by GetFeaturesInArea(x, y, r, 0, 0)?  (cell window first, then the distance test)
+__device__ __forceinline__ bool si_hit(const SiSmem& S, int p, float x, float y, float r, int cx0, int cx1, int cy0, int cy1)
+{
+    const int cell = S.lcell[p], cx = cell & 0xff, cy = cell >> 8;
+    return cx >= cx0 && cx <= cx1 && cy >= cy0 && cy <= cy1 &&
+           fabsf(__fsub_rn(S.lx[p], x)) < r && fabsf(__fsub_rn(S.ly[p], y)) < r;
+}
+
 // phase A for the queries qlist[q0 .. q0+nq) into candidate buffer `buf`, warps wfirst..SI_WARPS-1
 __device__ __forceinline__ void si_phase_a(const SiCtx& c, int q0, int nq, int buf, int wfirst, int wid, int lane,
                                            unsigned long long& ncmp)
 {
     const SiSmem& S = c.S;
+    unsigned short* pend = S.pend + wid * SI_PEND;
     for (int qi = wid - wfirst; qi < nq; qi += SI_WARPS - wfirst) {
         const int i1 = S.qlist[q0 + qi];
         const float x = c.prev ? c.prev[2 * i1] : c.k1[i1].x, y = c.prev ? c.prev[2 * i1 + 1] : c.k1[i1].y;
@@ -164,43 +184,56 @@ __device__ __forceinline__ void si_phase_a(const SiCtx& c, int q0, int nq, int b
         if (area_cells(c.gp, x, y, c.r, cx0, cx1, cy0, cy1)) {
             uint32_t q[8];
             load_desc(q, c.d1 + (size_t)i1 * 32);
-            const int ncy = cy1 - cy0 + 1;
-            // one lane per grid column: its cells cy0..cy1 are contiguous in the flattened grid
-            for (int cxb = cx0; cxb <= cx1; cxb += 32) {
-                const int ix = cxb + lane;
-                int j = 0, e = 0;
-                if (ix <= cx1) { j = S.gs[ix * ORBX_GRID_ROWS + cy0]; e = S.gs[ix * ORBX_GRID_ROWS + cy0 + ncy]; }
-                while (__any_sync(FULL, j < e)) {
-                    uint32_t ent = 0xffffffffu;
-                    if (j < e) {
-                        const int idx = S.gi[j];
-                        if (fabsf(__fsub_rn(S.kx[idx], x)) < c.r && fabsf(__fsub_rn(S.ky[idx], y)) < c.r) {
-                            const int dist = hamming256(q, si_desc2(c, idx));
-                            ++ncmp;
-                            if (dist <= c.dkeep) ent = ((uint32_t)dist << 16) | (uint32_t)j;
-                        }
-                        ++j;
-                    }
-                    const unsigned m = __ballot_sync(FULL, ent != 0xffffffffu);
-                    if (ent != 0xffffffffu) {
-                        const int p = cnt + __popc(m & ((1u << lane) - 1));
-                        if (p < SI_MAXC) S.cand[(buf * SI_QBLOCK + qi) * SI_MAXC + p] = ent;
-                    }
-                    cnt += __popc(m);
+            uint32_t* out = S.cand + (buf * SI_QBLOCK + qi) * SI_MAXC;
+            // Hamming distances of the first n pending hits, one per lane
+            auto flush = [&](int n) {
+                uint32_t ent = 0xffffffffu;
+                if (lane < n) {
+                    const int p = pend[lane];
+                    const int dist = hamming256(q, si_desc2(c, S.lidx[p]));
+                    ++ncmp;
+                    if (dist <= c.dkeep) ent = ((uint32_t)dist << 16) | (uint32_t)p;
+                }
+                const unsigned m = __ballot_sync(FULL, ent != 0xffffffffu);
+                if (ent != 0xffffffffu) {
+                    const int o = cnt + __popc(m & ((1u << lane) - 1));
+                    if (o < SI_MAXC) out[o] = ent;
+                }
+                cnt += __popc(m);
+            };
+            int npend = 0;
+            for (int p0 = 0; p0 < c.nL; p0 += 32) {
+                const int p = p0 + lane;
+                const bool hit = p < c.nL && si_hit(S, p, x, y, c.r, cx0, cx1, cy0, cy1);
+                const unsigned m = __ballot_sync(FULL, hit);
+                if (hit) pend[npend + __popc(m & ((1u << lane) - 1))] = (unsigned short)p;
+                npend += __popc(m);
+                __syncwarp();
+                if (npend >= 32) {
+                    flush(32);
+                    __syncwarp();
+                    const int rest = npend - 32;
+                    const unsigned short mv = lane < rest ? pend[32 + lane] : (unsigned short)0;
+                    __syncwarp();
+                    if (lane < rest) pend[lane] = mv;
+                    npend = rest;
+                    __syncwarp();
                 }
             }
+            if (npend > 0) flush(npend);
+            __syncwarp();
         }
         if (lane == 0) S.ccount[buf * SI_QBLOCK + qi] = cnt;
     }
 }
 
-__global__ void __launch_bounds__(SI_WARPS * 32)
+__global__ void __launch_bounds__(SI_WARPS * 32, 5)
 search_init_kernel(FrameStore fs, int firstSlot, int slotStride, GridParams gp, float* prevMatchedBase,
                    int windowSize, float nnratio, int checkOri, int* __restrict__ matches12Base,
                    int* __restrict__ nmatchesOut, unsigned long long* __restrict__ ncompares, int dkeep)
 {
     extern __shared__ __align__(16) unsigned char smraw[];
-    __shared__ int sNq, sCull;
+    __shared__ int sNq, sCull, sNL, sWq[SI_WARPS], sWl[SI_WARPS];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int pair = blockIdx.x;
     const int sA = firstSlot + pair * slotStride, sB = sA + 1;
@@ -216,32 +249,59 @@ search_init_kernel(FrameStore fs, int firstSlot, int slotStride, GridParams gp, 
     const unsigned short* gig = fs.gridIdx + (size_t)sB * fs.cap;
     int* m12 = matches12Base + (size_t)pair * fs.cap;
     // ---- stage F2 -------------------------------------------------------------------------------
-    for (int i = tid; i < n2; i += SI_WARPS * 32) {
-        const orbx_keypoint kp = c.k2[i];
-        S.kx[i] = kp.octave > 0 ? __int_as_float(0x7f800000) : kp.x;     // level window [0,0] (:425)
-        S.ky[i] = kp.y;
-        S.md[i] = 0xffff; S.m21[i] = 0xffff;
-        S.gi[i] = gig[i];
-    }
-    for (int i = tid; i <= ORBX_GRID_CELLS; i += SI_WARPS * 32) S.gs[i] = gsg[i];
+    for (int i = tid; i < n2; i += SI_WARPS * 32) { S.md[i] = 0xffff; S.m21[i] = 0xffff; }
     for (int i = tid; i < c.ndescSmem * 2; i += SI_WARPS * 32)
         reinterpret_cast<uint4*>(S.desc)[i] = reinterpret_cast<const uint4*>(c.d2g)[i];
     for (int i = tid; i < n1; i += SI_WARPS * 32) { S.binOf[i] = 0xff; m12[i] = -1; }
     if (tid < ORBX_HISTO_LENGTH) S.hist[tid] = 0;
     if (tid == 0) sCull = 0;
-    if (wid == 0) {     // octave-0 keypoints of F1 (src/ORBmatcher.cc:421-423), ascending
-        int nq = 0;
-        for (int i0 = 0; i0 < n1; i0 += 32) {
+    // Two ordered compactions, spread over all warps (each warp owns a contiguous range; counts, then a prefix over
+    // the warps, then the writes):
+    //   qlist: octave-0 keypoints of F1 (src/ORBmatcher.cc:421-423), ascending index
+    //   L:     octave-0 keypoints of F2 that are in the grid, in enumeration order, with their cell
+    const int nIn = min((int)gsg[ORBX_GRID_CELLS], n2);
+    const int qr = ((n1 + SI_WARPS - 1) / SI_WARPS + 31) & ~31, lr = ((nIn + SI_WARPS - 1) / SI_WARPS + 31) & ~31;
+    const int qa = min(wid * qr, n1), qb = min(qa + qr, n1), la = min(wid * lr, nIn), lb = min(la + lr, nIn);
+    {
+        int cq = 0, cl = 0;
+        for (int i0 = qa; i0 < qb; i0 += 32) { const int i = i0 + lane; cq += __popc(__ballot_sync(FULL, i < qb && c.k1[i].octave <= 0)); }
+        for (int j0 = la; j0 < lb; j0 += 32) { const int j = j0 + lane; cl += __popc(__ballot_sync(FULL, j < lb && c.k2[gig[j]].octave <= 0)); }
+        if (lane == 0) { sWq[wid] = cq; sWl[wid] = cl; }
+    }
+    __syncthreads();
+    {
+        int nq = 0, nl = 0;
+        for (int w = 0; w < wid; ++w) { nq += sWq[w]; nl += sWl[w]; }
+        if (wid == SI_WARPS - 1 && lane == 0) { sNq = nq + sWq[wid]; sNL = nl + sWl[wid]; }
+        for (int i0 = qa; i0 < qb; i0 += 32) {
             const int i = i0 + lane;
-            const bool isq = i < n1 && c.k1[i].octave <= 0;
+            const bool isq = i < qb && c.k1[i].octave <= 0;
             const unsigned m = __ballot_sync(FULL, isq);
             if (isq) S.qlist[nq + __popc(m & ((1u << lane) - 1))] = (unsigned short)i;
             nq += __popc(m);
         }
-        if (lane == 0) sNq = nq;
+        for (int j0 = la; j0 < lb; j0 += 32) {
+            const int j = j0 + lane;
+            bool keep = false;
+            int idx = 0;
+            orbx_keypoint kp;
+            if (j < lb) { idx = gig[j]; kp = c.k2[idx]; keep = kp.octave <= 0; }
+            const unsigned m = __ballot_sync(FULL, keep);
+            if (keep) {
+                const int o = nl + __popc(m & ((1u << lane) - 1));
+                // Frame::PosInGrid (src/Frame.cc:382-392): the cell the grid build filed this keypoint under
+                const int px = (int)roundf(__fmul_rn(__fsub_rn(kp.x, gp.minX), gp.invW));
+                const int py = (int)roundf(__fmul_rn(__fsub_rn(kp.y, gp.minY), gp.invH));
+                S.lx[o] = kp.x; S.ly[o] = kp.y;
+                S.lidx[o] = (unsigned short)idx;
+                S.lcell[o] = (unsigned short)(px | (py << 8));
+            }
+            nl += __popc(m);
+        }
     }
     __syncthreads();
     const int nqTotal = sNq;
+    c.nL = sNL;
     int nmatches = 0;                      // meaningful in warp 0
     unsigned long long ncmp = 0;
     si_phase_a(c, 0, min(SI_QBLOCK, nqTotal), 0, 0, wid, lane, ncmp);
@@ -261,7 +321,7 @@ search_init_kernel(FrameStore fs, int firstSlot, int slotStride, GridParams gp, 
                 if (cnt <= SI_MAXC) {
                     if (lane < cnt) {
                         const uint32_t ent = S.cand[(buf * SI_QBLOCK + qi) * SI_MAXC + lane];
-                        const int dist = (int)(ent >> 16), idx = S.gi[ent & 0xffff];
+                        const int dist = (int)(ent >> 16), idx = S.lidx[ent & 0xffff];
                         if ((int)S.md[idx] > dist) { best = dist; key = ent & 0xffff; }
                     }
                 } else {
@@ -271,22 +331,18 @@ search_init_kernel(FrameStore fs, int firstSlot, int slotStride, GridParams gp, 
                     area_cells(gp, x, y, c.r, cx0, cx1, cy0, cy1);
                     uint32_t q[8];
                     load_desc(q, c.d1 + (size_t)i1 * 32);
-                    const int ncy = cy1 - cy0 + 1;
-                    for (int ix = cx0 + lane; ix <= cx1; ix += 32) {
-                        const int e = S.gs[ix * ORBX_GRID_ROWS + cy0 + ncy];
-                        for (int j = S.gs[ix * ORBX_GRID_ROWS + cy0]; j < e; ++j) {
-                            const int idx = S.gi[j];
-                            if (!(fabsf(__fsub_rn(S.kx[idx], x)) < c.r && fabsf(__fsub_rn(S.ky[idx], y)) < c.r)) continue;
-                            const int dist = hamming256(q, si_desc2(c, idx));
-                            if ((int)S.md[idx] <= dist) continue;
-                            if (dist < best || (dist == best && (unsigned)j < key)) { second = min(second, best); best = dist; key = (unsigned)j; }
-                            else second = min(second, dist);
-                        }
+                    for (int p = lane; p < c.nL; p += 32) {
+                        if (!si_hit(S, p, x, y, c.r, cx0, cx1, cy0, cy1)) continue;
+                        const int idx = S.lidx[p];
+                        const int dist = hamming256(q, si_desc2(c, idx));
+                        if ((int)S.md[idx] <= dist) continue;
+                        if (dist < best || (dist == best && (unsigned)p < key)) { second = min(second, best); best = dist; key = (unsigned)p; }
+                        else second = min(second, dist);
                     }
                 }
                 warp_top2(best, key, second);
                 if (best <= ORBX_TH_LOW && (float)best < __fmul_rn((float)second, nnratio)) {
-                    const int bi = S.gi[key];
+                    const int bi = S.lidx[key];
                     const int old = S.m21[bi];
                     __syncwarp();
                     if (lane == 0) {
