@@ -626,7 +626,8 @@ octree_kernel(Geom g, int nframes, const uint32_t* __restrict__ cand, const int2
     extern __shared__ __align__(16) u8 smem[];
     const unsigned FULL = 0xffffffffu;
     const int tid = threadIdx.x, lane = tid & 31;
-    const int level = blockIdx.x % g.nlevels, frame = blockIdx.x / g.nlevels;
+    // level-major block order: the long level-0 CTAs are dispatched first, the kernel's tail is made of short ones
+    const int level = blockIdx.x / nframes, frame = blockIdx.x % nframes;
     const LevelGeom& L = g.L[level];
     // ---- shared memory carve-up (the cell tables of the gather alias everything up to cntB) ----
     unsigned long long* sortbuf = reinterpret_cast<unsigned long long*>(smem);
