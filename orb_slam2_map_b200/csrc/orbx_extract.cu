@@ -210,7 +210,8 @@ __device__ __forceinline__ void blur_strip(const u8* __restrict__ src, int sp, u
     const int ngroups = (rowsOut + 6 + 6) / 7;
     const int xl = min(max(x, 0), (w - 1) & ~3);  // every lane loads an aligned word that lies inside the row
     const bool store = lane >= 1 && lane <= 30 && x < w;
-    uint32_t H[7][4];
+    // Q[k][j]: horizontal sums of rows (r-1, r) of column j packed as two u16 (each < 2^16), r = the row filed in slot k
+    uint32_t Q[7][4], Hprev[4] = {0u, 0u, 0u, 0u};
     uint32_t cur[7], nxt[7];
     const u8* colp = src + (long long)(y0 - 3) * sp + xl;         // row y0-3 of the lane's column (INTERIOR addressing)
     u8* dcol = dst + x;                                           // kept in registers: the row address is one IMAD.WIDE
@@ -239,21 +240,23 @@ __device__ __forceinline__ void blur_strip(const u8* __restrict__ src, int sp, u
                 if (mode != 0) w1 = __byte_perm(pa, pb, sel);
             }
             const uint32_t w0 = __shfl_up_sync(FULL, w1, 1), w2 = __shfl_down_sync(FULL, w1, 1);
-            H[k][0] = __dp4a(__byte_perm(w0, w1, 0x4321), c0, __dp4a(__byte_perm(w1, w2, 0x4321), c1, 0u));
-            H[k][1] = __dp4a(__byte_perm(w0, w1, 0x5432), c0, __dp4a(__byte_perm(w1, w2, 0x5432), c1, 0u));
-            H[k][2] = __dp4a(__byte_perm(w0, w1, 0x6543), c0, __dp4a(__byte_perm(w1, w2, 0x6543), c1, 0u));
-            H[k][3] = __dp4a(w1, c0, __dp4a(w2, c1, 0u));
-            // rows r-6 .. r are in slots (k+1)%7 .. k ; output row y = y0 + r - 6 (r >= 6 <=> gi > 0 or k == 6)
+            uint32_t Hn[4];
+            Hn[0] = __dp4a(__byte_perm(w0, w1, 0x4321), c0, __dp4a(__byte_perm(w1, w2, 0x4321), c1, 0u));
+            Hn[1] = __dp4a(__byte_perm(w0, w1, 0x5432), c0, __dp4a(__byte_perm(w1, w2, 0x5432), c1, 0u));
+            Hn[2] = __dp4a(__byte_perm(w0, w1, 0x6543), c0, __dp4a(__byte_perm(w1, w2, 0x6543), c1, 0u));
+            Hn[3] = __dp4a(w1, c0, __dp4a(w2, c1, 0u));
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { Q[k][j] = __byte_perm(Hprev[j], Hn[j], 0x5410); Hprev[j] = Hn[j]; }
+            // window rows r-6 .. r: the pairs (r-6,r-5), (r-4,r-3), (r-2,r-1) are in slots (k+2)%7, (k+4)%7, (k+6)%7, row r
+            // is Hn; output row y = y0 + r - 6 (r >= 6 <=> gi > 0 or k == 6).  Three IDP.2A + one IMAD per pixel.
             const int y = y0 + r - 6;
             if ((later || k == 6) && (INTERIOR || y < h)) {
                 uint32_t o[4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const uint32_t s0 = H[(k + 1) % 7][j] + H[k][j];
-                    const uint32_t s1 = H[(k + 2) % 7][j] + H[(k + 6) % 7][j];
-                    const uint32_t s2 = H[(k + 3) % 7][j] + H[(k + 5) % 7][j];
-                    o[j] = 18u * s0 + 34u * s1 + 48u * s2 + 56u * H[(k + 4) % 7][j] + 32768u;   // result in bits 16..23
-                }
+                for (int j = 0; j < 4; ++j)
+                    o[j] = __dp2a_lo(Q[(k + 2) % 7][j], 18u | (34u << 8),
+                           __dp2a_lo(Q[(k + 4) % 7][j], 48u | (56u << 8),
+                           __dp2a_lo(Q[(k + 6) % 7][j], 48u | (34u << 8), 18u * Hn[j] + 32768u)));       // result in bits 16..23
                 const uint32_t lo = __byte_perm(o[0], o[1], 0x0062), hi = __byte_perm(o[2], o[3], 0x0062);
                 if (store) *reinterpret_cast<uint32_t*>(dcol + (unsigned long long)(unsigned)y * (unsigned)dp) = __byte_perm(lo, hi, 0x5410);
             }
