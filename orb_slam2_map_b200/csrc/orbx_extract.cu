@@ -299,7 +299,7 @@ blur7_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, u8* __restrict__
 // and NMS(th=ini) == NMS(th=min) restricted to S>ini, so one pass at minTh
 // serves both calls.  Candidates are packed x:12 | y:12 | (S-1):8 in window coordinates.
 // =============================================================================================
-#define FAST_WARPS 4
+#define FAST_WARPS 1
 
 __device__ __forceinline__ uint32_t vmaxu2(uint32_t a, uint32_t b) { return __vmaxu2(a, b); }
 __device__ __forceinline__ uint32_t vminu2(uint32_t a, uint32_t b) { return __vminu2(a, b); }
