@@ -64,10 +64,10 @@ def algorithmic_bytes(w, h, nkp):
                 total=b_pyr + b_fast + b_desc)
 
 
-# measured DRAM bytes per 640x480 frame (read + write) of each extractor kernel, from the r01k `ncu --set full`
-# capture of a 64-frame launch (profiles/r01k_ncu_full_chunk64_summary.txt); resize = sum over the 7 levels
+# measured DRAM bytes per 640x480 frame (read + write) of each extractor kernel, from the r01l `ncu --set full`
+# capture of a 64-frame launch (profiles/r01l_ncu_full_chunk64_summary.txt); resize = sum over the 7 levels
 NCU_DRAM_BYTES_PER_FRAME = {
-    "fast": (55.879936e6 + 1.160192e6) / 64,
+    "fast": (55.872000e6 + 1.545984e6) / 64,
     "blur": (64.554496e6 + 15.194368e6) / 64,
     "describe": (118.258688e6 + 5.856512e6) / 64,
     "resize": (19.690752e6 + 13.948672e6 + 9.568512e6 + 6.848512e6 + 4.751616e6 + 3.381504e6 + 2.323712e6 + 0.03e6) / 64,
@@ -76,7 +76,7 @@ NCU_DRAM_BYTES_PER_FRAME = {
 # warp instructions executed per 640x480 frame by each extractor kernel (smsp__inst_executed.sum of the same capture):
 # these kernels are bound by instruction issue (4 warp instructions per clock per SM), not by HBM
 NCU_WARP_INST_PER_FRAME = {
-    "fast": 126475674 / 64,
+    "fast": 120985254 / 64,
     "blur": 47649344 / 64,
     "describe": 44842346 / 64,
     "resize": (16092480 + 10659648 + 6708416 + 5568576 + 4677760 + 2598592 + 2169600) / 64,
@@ -653,14 +653,14 @@ def main():
     dom_ms = stage_ms.get(dom, 0.0)
     achieved = (dom_bytes * frames_total / dom_launches) / (dom_ms / dom_launches * 1e-3) / 1e9 if dom_ms > 0 else 0.0
     # DRAM traffic of the dominant kernel: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full`
-    # capture (profiles/r01k_ncu_full_chunk64_summary.txt, a 64-frame launch of the 640x480 workload), scaled to
+    # capture (profiles/r01l_ncu_full_chunk64_summary.txt, a 64-frame launch of the 640x480 workload), scaled to
     # the frames one launch of this run processes.  Other image shapes have no capture: null.
     traffic = None
     if (W, H) == (640, 480) and dom in NCU_DRAM_BYTES_PER_FRAME:
         traffic = NCU_DRAM_BYTES_PER_FRAME[dom] * frames_total / dom_launches
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic,
-                "traffic_source": "ncu --set full, profiles/r01k_ncu_full_chunk64_summary.txt, per-frame bytes x frames per launch" if traffic else None,
+                "traffic_source": "ncu --set full, profiles/r01l_ncu_full_chunk64_summary.txt, per-frame bytes x frames per launch" if traffic else None,
                 "algorithmic_bytes_per_launch": dom_bytes * frames_total / dom_launches,
                 "peak_source": peak_src,
                 "algorithmic_bytes_per_frame": dom_bytes,
@@ -671,7 +671,7 @@ def main():
         issue_peak = 148 * 4 * clk["sm_mhz"] * 1e6 / 1e9
         roofline["issue"] = {"achieved": ginst, "peak": issue_peak, "unit": "G warp-inst/s", "frac": ginst / issue_peak,
                              "warp_inst_per_frame": NCU_WARP_INST_PER_FRAME[dom],
-                             "source": "smsp__inst_executed.sum, profiles/r01k_ncu_full_chunk64_summary.txt"}
+                             "source": "smsp__inst_executed.sum, profiles/r01l_ncu_full_chunk64_summary.txt"}
     path_gbs = ab["total"] * value / world / 1e9
     stages = {k: {"ms_per_step": v / args.steps, "launches_per_step": stage_launches[k] / args.steps}
               for k, v in stage_ms.items() if stage_launches[k]}
