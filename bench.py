@@ -490,6 +490,81 @@ def run_rgbd(args):
     ex.close()
 
 
+def run_single(args):
+    """BASELINE configs[0] / SURVEY 8(d) "Config 1": ONE 640x480 frame per call, the way Tracking uses the extractor
+    (Frame::ExtractORB, src/Frame.cc:247-253): pageable host image in, host keypoints + descriptors out, through
+    orbx_extract.  The library replays a CUDA graph of the frame's kernels; the number is the latency the caller of
+    ORBextractor::operator() sees.  CPU side: the reference's own ORBextractor.cc (oracle/_ref), single-threaded per frame."""
+    import torch
+    from orb_slam2_map_b200 import capi, synth
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    NF = 64
+    frames = synth.frame_sequence_torch(NF, W, H, seed=rank, device=dev).cpu().numpy()     # pageable host memory, like a cv::Mat
+    ex = capi.Extractor(**PARAMS, max_width=W, max_height=H, chunk_frames=1, result_slots=1, device=local)  # own stream -> graph path
+    L = capi.lib()
+    kps = np.zeros(ex.cap, capi.KP_DTYPE); desc = np.zeros((ex.cap, 32), np.uint8); n = C.c_int(0)
+    pk, pd = kps.ctypes.data_as(C.c_void_p), desc.ctypes.data_as(C.c_void_p)
+
+    def one(i):
+        f = frames[i % NF]
+        capi.check(L.orbx_extract(ex.h, f.ctypes.data_as(C.c_void_p), W, H, C.c_size_t(W), pk, pd, ex.cap, C.byref(n)))
+
+    calls = max(args.steps, 1) * 200
+    for i in range(max(args.warmup, 3) * 20):
+        one(i)
+    clocks = ClockSampler(local); clocks.start()
+    lat = np.empty(calls)
+    t_all = time.perf_counter()
+    for i in range(calls):
+        t0 = time.perf_counter()
+        one(i)
+        lat[i] = time.perf_counter() - t0
+    t_all = time.perf_counter() - t_all
+    clk = clocks.stop()
+    nkp = int(n.value)
+    # the same frame's kernels alone (device-resident image, no graph: 12 launches), CUDA events on the launching stream
+    stream = torch.cuda.Stream(device=dev); torch.cuda.set_stream(stream)
+    ex2 = capi.Extractor(**PARAMS, max_width=W, max_height=H, chunk_frames=1, result_slots=1, device=local, stream=stream.cuda_stream)
+    dfr = torch.from_numpy(frames[:8]).to(dev)
+    for i in range(20):
+        ex2.extract_batch(dfr[i % 8].data_ptr(), nframes=1, width=W, height=H, frame_stride=W * H, row_stride=W, on_device=True)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for i in range(200):
+        ex2.extract_batch(dfr[i % 8].data_ptr(), nframes=1, width=W, height=H, frame_stride=W * H, row_stride=W, on_device=True)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    dev_us = e0.elapsed_time(e1) * 1e3 / 200
+    med = float(np.median(lat)) * 1e6
+    nl = PARAMS["nlevels"]
+    line = {"metric": "ORB single-frame latency (640x480, 1000 kp, ORBextractor::operator())", "value": med, "unit": "us/frame",
+            "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_all / calls * 1e3, "higher_is_better": False,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "configs[0]: single synthetic 640x480 frame per call, ORBextractor(1000,1.2,8,20,7), pageable host image in, "
+                                   "host keypoints + descriptors out (orbx_extract, CUDA-graph replay)",
+                       "calls": calls, "distinct_frames": NF, "keypoints": nkp, "l2_policy": "latency line: one frame fits L2 by definition"},
+            "clocks": clk,
+            "latency_us": {"median": med, "p10": float(np.percentile(lat, 10)) * 1e6, "p90": float(np.percentile(lat, 90)) * 1e6,
+                           "p99": float(np.percentile(lat, 99)) * 1e6, "kernels_only_no_graph": dev_us},
+            "e2e": {"value": med, "unit": "us/frame", "h2d_bytes_per_step": W * H, "d2h_bytes_per_step": ex.cap * 60 + 8,
+                    "frames_per_s_one_caller": calls / t_all},
+            "gpu_launches": calls * (nl - 1 + 4)}
+    if rank == 0 and not args.no_cpu:
+        s1 = 24
+        t1, kind = cpu_extract_match(frames[:s1], 1, True, 0)
+        line["cpu_baseline"] = {"value": t1 / s1 * 1e6, "unit": "us/frame", "cores": 1, "kind": kind,
+                                "sample": f"{s1} frames, single-threaded per frame as ORB-SLAM2 runs it (extraction only)"}
+    if rank == 0:
+        print(json.dumps(line))
+    ex.close(); ex2.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -499,7 +574,7 @@ def main():
     ap.add_argument("--frames", type=int, default=4096)
     ap.add_argument("--chunk", type=int, default=512)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--workload", default="frames", choices=["frames", "hd", "stereo", "knn", "rgbd"],
+    ap.add_argument("--workload", default="frames", choices=["frames", "hd", "stereo", "knn", "rgbd", "single"],
                     help="frames = BASELINE configs[1] (the graded line); hd = configs[3]; stereo = configs[2]; knn = configs[4]")
     ap.add_argument("--queries", type=int, default=262144, help="knn: queries per step (config 5 names 1M)")
     ap.add_argument("--db-per-gpu", type=int, default=2000000, help="knn: database rows per GPU (config 5: 16M over 8)")
@@ -528,6 +603,9 @@ def main():
         return
     if args.workload == "rgbd":
         run_rgbd(args)
+        return
+    if args.workload == "single":
+        run_single(args)
         return
 
     import torch

@@ -83,7 +83,11 @@ int orbx_keypoint_capacity(const orbx_handle* h);
 /* ---- ORBextractor::operator() (src/ORBextractor.cc:1043), single frame, host buffers --------
  * image: 8UC1 host pointer.  kps/desc: host buffers with room for `capacity` keypoints
  * (desc = capacity*32 bytes).  *n receives the count.  width*height==0 -> *n untouched (the
- * reference returns silently on an empty image). */
+ * reference returns silently on an empty image).
+ * This is the latency path (one call per tracked frame, Frame::ExtractORB src/Frame.cc:247-253): the image
+ * crosses in one copy through pinned staging, the kernels of the frame are replayed from a CUDA graph captured
+ * on the first call of an image shape (handles created on a caller-supplied stream launch them one by one),
+ * and count, keypoints and descriptors return behind a single stream synchronisation. */
 int orbx_extract(orbx_handle* h, const uint8_t* image, int width, int height, size_t row_stride,
                  orbx_keypoint* kps, uint8_t* desc, int capacity, int* n);
 

@@ -1101,6 +1101,7 @@ int orbx_setup_shape(orbx_handle* h, int w, int hgt)
     // (re)allocate shape-dependent device buffers
     cudaStream_t st = h->stream;
     ORBX_CUDA(cudaStreamSynchronize(st));
+    orbx_drop_graph(h);
     auto re = [&](void** p, size_t bytes) -> cudaError_t { if (*p) cudaFree(*p); *p = nullptr; return cudaMalloc(p, std::max<size_t>(bytes, 256)); };
     const size_t C = (size_t)h->chunkFrames;
     ORBX_CUDA(re((void**)&h->dCells, cells.size() * sizeof(Cell)));

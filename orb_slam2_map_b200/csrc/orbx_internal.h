@@ -145,6 +145,10 @@ struct orbx_handle {
     // pinned staging
     void* hStage;
     size_t hStageBytes;
+    // single-frame call (orbx_extract): the kernels of one frame captured once per image shape
+    cudaGraphExec_t graph1;
+    bool graph1Valid;
+    long long graph1Launches[ORBX_NSTAGES];
     // per-stage device timing (CUDA events on the handle's stream) and launch counting
     bool profiling;
     std::vector<cudaEvent_t> evPool;
@@ -160,6 +164,7 @@ void orbx_prof_mark(orbx_handle* h, int stage);
 
 // orbx_extract.cu
 int orbx_setup_shape(orbx_handle* h, int w, int hgt);
+void orbx_drop_graph(orbx_handle* h);      // the workspace moved: the captured single-frame graph is stale
 int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot);
 
 // orbx_api.cu: frames [nf][height][row_stride] -> pitched workspace frames, on `st`

@@ -173,3 +173,50 @@ def test_empty_image_is_silent():
     rc = capi.lib().orbx_extract(ex.h, None, 0, 0, 0, None, None, 0, C.byref(n))
     assert rc == 0 and n.value == -7
     ex.close()
+
+
+def test_single_frame_graph_replay(monkeypatch):
+    """orbx_extract on ONE handle, call after call (the way Tracking uses ORBextractor::operator()): the first call of a
+    shape captures the frame's kernels into a CUDA graph, later calls replay it.  Every call must equal the oracle bit
+    for bit: different content per call, a strided source, a shape change (the graph is dropped with the workspace) and
+    back, batch calls in between, pyramid levels after a replay, and the plain-launch path (ORBX_NO_GRAPH)."""
+    orc = O.Extractor()
+    ex = capi.Extractor(max_width=752, max_height=480, chunk_frames=4, result_slots=4)
+    seq = synth.frame_sequence(6, 640, 480, seed=11)
+    for i in range(6):                               # call 0 plain + capture, 1.. replays
+        kg, dg = ex.extract(seq[i])
+        ko, do = orc.extract(seq[i])
+        _compare_full(kg, dg, ko, do)
+    for l in (0, 3, 7):                              # mvImagePyramid of the frame the graph just processed
+        assert np.array_equal(ex.level(0, l), orc.level(l))
+        assert np.array_equal(ex.level(0, l, blurred=True), orc.level(l, blurred=True))
+    wide = np.zeros((480, 700), np.uint8)            # row stride != width
+    wide[:, :640] = seq[2]
+    wide[:, 640:] = 255
+    kg, dg = ex.extract(wide[:, :640])
+    ko, do = orc.extract(seq[2])
+    _compare_full(kg, dg, ko, do)
+    other = _image(752, 480, seed=3)                 # another shape: workspace and graph rebuilt
+    for _ in range(2):
+        kg, dg = ex.extract(other)
+        ko, do = orc.extract(other)
+        _compare_full(kg, dg, ko, do)
+    ex.extract_batch(seq[:4])                        # a batch on the same handle, then single frames again
+    kb, db, cb = ex.download(0, 4)
+    for i in range(4):
+        ko, do = orc.extract(seq[i])
+        _compare_full(kb[i][:cb[i]], db[i][:cb[i]], ko, do)
+    for i in (5, 1, 4):
+        kg, dg = ex.extract(seq[i])
+        ko, do = orc.extract(seq[i])
+        _compare_full(kg, dg, ko, do)
+    flat = np.full((480, 640), 9, np.uint8)          # no keypoints at all after a full frame
+    kg, dg = ex.extract(flat)
+    assert len(kg) == 0 and dg.shape == (0, 32)
+    kg, dg = ex.extract(seq[0])
+    ko, do = orc.extract(seq[0])
+    _compare_full(kg, dg, ko, do)
+    monkeypatch.setenv("ORBX_NO_GRAPH", "1")
+    kg2, dg2 = ex.extract(seq[0])
+    _compare_full(kg2, dg2, ko, do)
+    ex.close()
