@@ -231,6 +231,9 @@ int orbx_destroy(orbx_handle* h)
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->hStage) cudaFreeHost(h->hStage);
     orbx_drop_graph(h);
+    for (cudaStream_t x : h->sideStreams) cudaStreamDestroy(x);
+    for (cudaEvent_t e : h->sideEvents) cudaEventDestroy(e);
+    for (cudaEvent_t e : h->levelEvents) cudaEventDestroy(e);
     for (cudaEvent_t e : h->evPool) cudaEventDestroy(e);
     for (int b = 0; b < ORBX_L0_BUFS; ++b) { cudaEventDestroy(h->evCopied[b]); cudaEventDestroy(h->evFree[b]); }
     cudaStreamDestroy(h->copyStream);
@@ -487,13 +490,15 @@ int orbx_extract(orbx_handle* h, const uint8_t* image, int width, int height, si
     if (useGraph && !h->graph1Valid) {
         // first frame of this shape: run once plainly (sets function attributes, uploads the per-device tables),
         // then capture the same launches
+        static const bool forkLevels = !getenv("ORBX_LAT_NOFORK");
         rc = orbx_run_chunk(h, l0, 1, 0);
         if (rc) return rc;
+        if (forkLevels) { rc = orbx_run_frame_forked(h, l0, 0); if (rc) return rc; }    // creates the side streams outside the capture
         long long before[ORBX_NSTAGES];
         for (int s = 0; s < ORBX_NSTAGES; ++s) before[s] = h->stageLaunches[s];
         cudaGraph_t graph = nullptr;
         ORBX_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed));
-        rc = orbx_run_chunk(h, l0, 1, 0);
+        rc = forkLevels ? orbx_run_frame_forked(h, l0, 0) : orbx_run_chunk(h, l0, 1, 0);
         const cudaError_t ce = cudaStreamEndCapture(st, &graph);
         for (int s = 0; s < ORBX_NSTAGES; ++s) { h->graph1Launches[s] = h->stageLaunches[s] - before[s]; h->stageLaunches[s] = before[s]; }
         if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }

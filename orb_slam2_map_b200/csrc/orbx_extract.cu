@@ -345,12 +345,12 @@ __global__ void __launch_bounds__(FAST_WARPS * 32)
 fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* __restrict__ rawBase,
                   int nframes, int minThArg, int iniThArg, uint32_t* __restrict__ cand,
                   int2* __restrict__ cellSeg, unsigned* __restrict__ levelCandCount,
-                  int tilePitch, int scorePitch, int warpSmem)
+                  int tilePitch, int scorePitch, int warpSmem, int cellBeg, int cellEnd)
 {
     extern __shared__ __align__(16) u8 smem[];
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    const int frame = blockIdx.y, ci = blockIdx.x * FAST_WARPS + wid;
-    if (ci >= g.ncells) return;
+    const int frame = blockIdx.y, ci = cellBeg + blockIdx.x * FAST_WARPS + wid;
+    if (ci >= cellEnd) return;
     const Cell c = cells[ci];
     const LevelGeom& L = g.L[c.level];
     const u8* img;
@@ -624,13 +624,13 @@ template <int OT_THREADS>
 __global__ void __launch_bounds__(OT_THREADS)
 octree_kernel(Geom g, int nframes, const uint32_t* __restrict__ cand, const int2* __restrict__ cellSeg,
               uint32_t* __restrict__ keysAbase, uint32_t* __restrict__ keysBbase, uint32_t* __restrict__ levelKps,
-              int* __restrict__ levelKpCount, int NC, int P2, int cellWords, int keyCap, int* __restrict__ status)
+              int* __restrict__ levelKpCount, int NC, int P2, int cellWords, int keyCap, int* __restrict__ status, int levelBase)
 {
     extern __shared__ __align__(16) u8 smem[];
     const unsigned FULL = 0xffffffffu;
     const int tid = threadIdx.x, lane = tid & 31;
     // level-major block order: the long level-0 CTAs are dispatched first, the kernel's tail is made of short ones
-    const int level = blockIdx.x / nframes, frame = blockIdx.x % nframes;
+    const int level = levelBase + blockIdx.x / nframes, frame = blockIdx.x % nframes;
     const LevelGeom& L = g.L[level];
     // ---- shared memory carve-up (the cell tables of the gather alias everything up to cntB) ----
     unsigned long long* sortbuf = reinterpret_cast<unsigned long long*>(smem);
@@ -1044,8 +1044,10 @@ int orbx_setup_shape(orbx_handle* h, int w, int hgt)
             const int g7 = ((L.h + nstrips - 1) / nstrips + 6 + 6) / 7;        // 7-row groups covering rows + 6 halo rows
             L.blurTH = std::max(1, 7 * g7 - 6);
         }
+        h->blurTileBeg[l] = (int)tiles.size();
         for (int ty = 0; ty * L.blurTH < L.h; ++ty)
             for (int tx = 0; tx * BL_TW < L.w; ++tx) tiles.push_back((l << 24) | (ty << 12) | tx);
+        h->blurTileBeg[l + 1] = (int)tiles.size();
         // FAST cell grid (src/ORBextractor.cc:773-806)
         const int minBX = 16, minBY = 16, maxBX = L.w - 16, maxBY = L.h - 16;
         L.winW = maxBX - minBX; L.winH = maxBY - minBY;
@@ -1169,7 +1171,12 @@ static int get_pattern(int device, const int* umax, const signed char** out, con
     return ORBX_OK;
 }
 
-int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
+// Launches of one chunk.  forked = false: one stream, kernels in stage order over all levels (throughput form: every
+// kernel fills the GPU).  forked = true (the single-frame latency path, orbx_extract): a frame leaves most SMs idle, so
+// the dependency graph is what matters: level l's blur and its FAST -> quadtree chain start on side streams as soon as
+// resize has produced level l (level 0 at once), run next to the rest of the resize chain, and join before describe.
+// Under stream capture this becomes the forked CUDA graph that orbx_extract replays.
+static int run_chunk_impl(orbx_handle* h, Level0 l0, int nframes, int firstSlot, bool forked)
 {
     const Geom& g = h->geom;
     cudaStream_t st = h->stream;
@@ -1178,7 +1185,77 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
     const uint32_t* dDisc = nullptr;
     int rc = get_pattern(h->device, h->umax, &dPat, &dDisc);
     if (rc) return rc;
+    if (forked) {
+        while ((int)h->sideStreams.size() < 2 * nl) {
+            cudaStream_t s; ORBX_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking)); h->sideStreams.push_back(s);
+            cudaEvent_t e; ORBX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->sideEvents.push_back(e);
+        }
+        while ((int)h->levelEvents.size() < nl) { cudaEvent_t e; ORBX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->levelEvents.push_back(e); }
+    }
+    // FAST / quadtree launch geometry (same for every level)
+    const int tilePitch = (g.cwMax + 9 + 7) & ~7;          // rows 8-byte aligned; the packed pre-test reads whole words up to byte cw+8
+    const int scorePitch = (g.cwMax - 4 + 3) & ~3;
+    const int maskBytes = 8 * (g.chMax - 6);                // one 64-bit pre-test mask per detectable row
+    int warpSmem = ((tilePitch * g.chMax + 15) & ~15) + ((((scorePitch * (g.chMax - 4) + 15) & ~15) + maskBytes + 15) & ~15) +
+                   2 * (g.cwMax - 6) * (g.chMax - 6);
+    warpSmem = (warpSmem + 15) & ~15;
+    const int fastSmem = warpSmem * FAST_WARPS;
+    if (fastSmem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fastSmem));
+    auto launch_fast = [&](cudaStream_t s, int cellBeg, int cellEnd) {
+        fast_cells_kernel<<<dim3((cellEnd - cellBeg + FAST_WARPS - 1) / FAST_WARPS, nframes), FAST_WARPS * 32, fastSmem, s>>>(
+            g, h->dCells, l0, h->dRaw, nframes, h->params.min_th_fast, h->params.ini_th_fast, h->dCand, h->dCellSeg, h->dLevelCandCount,
+            tilePitch, scorePitch, warpSmem, cellBeg, cellEnd);
+    };
+    int NC = 8, cellsMax = 1, candMax = 1;
+    for (int l = 0; l < nl; ++l) { NC = std::max(NC, g.L[l].kpCap); cellsMax = std::max(cellsMax, g.L[l].nCells); candMax = std::max(candMax, g.L[l].candCap); }
+    if (NC > 16383 || candMax >= (1 << 24)) { orbx_set_error("quadtree: %d nodes / %d candidates per level exceed the kernel's index width", NC, candMax); return ORBX_E_CAPACITY; }
+    int P2 = 32; while (P2 < NC) P2 <<= 1;
+    const int cellWords = 2 * cellsMax + 2;
+    const int aliasWords = std::max(2 * P2 + 11 * NC, cellWords);
+    const int fixedBytes = 4 * (aliasWords + NC + 32 + 8);
+    // keys + labels of a level stay in shared memory up to keyCap candidates (6 bytes each); beyond that
+    // the level runs out of the global key buffers
+    // CTA width and shared-memory key capacity follow the per-level quota: more features per level means
+    // more candidates per level (640x480/1000: ~2.5 k at level 0; 1920x1080/5000: ~18 k)
+    int otThreads = NC <= 256 ? 128 : (NC <= 512 ? 256 : 512);
+    if (forked) { static const int ot = getenv("ORBX_LAT_OT") ? atoi(getenv("ORBX_LAT_OT")) : 0; if (ot == 128 || ot == 256 || ot == 512) otThreads = ot; }
+    int keyCap = std::min((candMax + 63) & ~63, otThreads == 128 ? 4096 : (otThreads == 256 ? 8192 : 24576));
+    if (fixedBytes + 6 * keyCap > 200 * 1024) keyCap = std::max(0, (200 * 1024 - fixedBytes) / 6) & ~63;
+    if (const char* e = getenv("ORBX_OCTREE_KEYCAP")) keyCap = std::max(0, std::min(keyCap, atoi(e)));   // tests: force the global-memory path
+    const int otSmem = fixedBytes + 6 * keyCap;
+    auto launch_octree = [&](cudaStream_t s, int levelBeg, int nLevels) -> int {
+        auto launch = [&](auto kern) -> int {
+            if (otSmem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, otSmem));
+            kern<<<nframes * nLevels, otThreads, otSmem, s>>>(g, nframes, h->dCand, h->dCellSeg, h->dKeysA, h->dKeysB, h->dLevelKps,
+                                                              h->dLevelKpCount, NC, P2, cellWords, keyCap, h->dStatus, levelBeg);
+            return ORBX_OK;
+        };
+        return otThreads == 128 ? launch(octree_kernel<128>) : (otThreads == 256 ? launch(octree_kernel<256>) : launch(octree_kernel<512>));
+    };
+    auto launch_blur = [&](cudaStream_t s, int tileBeg, int tileEnd) {
+        blur7_kernel<<<dim3((tileEnd - tileBeg + BL_WARPS - 1) / BL_WARPS, nframes), BL_WARPS * 32, 0, s>>>(g, l0, h->dRaw, h->dBlur, h->dBlurTiles + tileBeg, tileEnd - tileBeg);
+    };
+    // level l's consumers on their side streams (forked form)
+    auto fork_level = [&](int l) -> int {
+        const LevelGeom& L = g.L[l];
+        cudaStream_t sA = h->sideStreams[2 * l], sB = h->sideStreams[2 * l + 1];
+        ORBX_CUDA(cudaEventRecord(h->levelEvents[l], st));
+        ORBX_CUDA(cudaStreamWaitEvent(sA, h->levelEvents[l], 0));
+        ORBX_CUDA(cudaStreamWaitEvent(sB, h->levelEvents[l], 0));
+        if (L.nCells > 0) launch_fast(sA, L.cellBeg, L.cellBeg + L.nCells);
+        int r = launch_octree(sA, l, 1);
+        if (r) return r;
+        ORBX_CUDA(cudaEventRecord(h->sideEvents[2 * l], sA));
+        launch_blur(sB, h->blurTileBeg[l], h->blurTileBeg[l + 1]);
+        ORBX_CUDA(cudaEventRecord(h->sideEvents[2 * l + 1], sB));
+        return ORBX_OK;
+    };
     orbx_prof_mark(h, -1);
+    if (forked) {
+        ORBX_CUDA(cudaMemsetAsync(h->dLevelCandCount, 0, (size_t)nframes * nl * sizeof(unsigned), st));
+        rc = fork_level(0);
+        if (rc) return rc;
+    }
     // K1a: levels 1..n-1, each from the previous one
     for (int l = 1; l < nl; ++l) {
         const LevelGeom& S = g.L[l - 1];
@@ -1187,7 +1264,9 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
         if (l == 1) { src = l0.base; sfs = l0.frameStride; sp = l0.pitch; }
         else { src = h->dRaw + S.off; sfs = g.pyrFrameBytes; sp = S.pitch; }
         if (h->params.scale_factor <= 2.0f) {
-            static const int rsTarget = getenv("ORBX_RS_TARGET") ? std::max(4, atoi(getenv("ORBX_RS_TARGET"))) : RS_TARGET;
+            static const int rsTargetEnv = getenv("ORBX_RS_TARGET") ? std::max(4, atoi(getenv("ORBX_RS_TARGET"))) : RS_TARGET;
+            static const int rsTargetLat = getenv("ORBX_LAT_RS") ? std::max(2, atoi(getenv("ORBX_LAT_RS"))) : RS_TARGET;
+            const int rsTarget = forked ? rsTargetLat : rsTargetEnv;
             const int nstrips = std::max(1, (D.h + rsTarget - 1) / rsTarget), th = (D.h + nstrips - 1) / nstrips;
             dim3 grid((D.w + 127) / 128, (nstrips + RS_WARPS - 1) / RS_WARPS, nframes);
             // source rows a strip of th output rows can touch: th * (S.h / D.h) + 2, with slack for the table's rounding
@@ -1201,55 +1280,27 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
             pyr_resize_kernel<<<grid, block, 0, st>>>(l0, l == 1 ? 1 : 0, src, sfs, sp, h->dRaw + D.off, g.pyrFrameBytes, D.pitch, D.w, D.h,
                                                       h->dCoef + D.coefX, h->dCoef + D.coefY);
         }
+        if (forked) { rc = fork_level(l); if (rc) return rc; }
     }
     ORBX_COUNT(h, ORBX_STAGE_RESIZE, nl - 1);
     orbx_prof_mark(h, ORBX_STAGE_RESIZE);
-    // K1b: blur of all levels
-    blur7_kernel<<<dim3((h->nBlurTiles + BL_WARPS - 1) / BL_WARPS, nframes), BL_WARPS * 32, 0, st>>>(g, l0, h->dRaw, h->dBlur, h->dBlurTiles, h->nBlurTiles);
-    ORBX_COUNT(h, ORBX_STAGE_BLUR, 1);
-    orbx_prof_mark(h, ORBX_STAGE_BLUR);
-    // K2: FAST
-    ORBX_CUDA(cudaMemsetAsync(h->dLevelCandCount, 0, (size_t)nframes * nl * sizeof(unsigned), st));
-    {
-        const int tilePitch = (g.cwMax + 9 + 7) & ~7;          // rows 8-byte aligned; the packed pre-test reads whole words up to byte cw+8
-        const int scorePitch = (g.cwMax - 4 + 3) & ~3;
-        const int maskBytes = 8 * (g.chMax - 6);                // one 64-bit pre-test mask per detectable row
-        int warpSmem = ((tilePitch * g.chMax + 15) & ~15) + ((((scorePitch * (g.chMax - 4) + 15) & ~15) + maskBytes + 15) & ~15) +
-                       2 * (g.cwMax - 6) * (g.chMax - 6);
-        warpSmem = (warpSmem + 15) & ~15;
-        const int smem = warpSmem * FAST_WARPS;
-        if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        fast_cells_kernel<<<dim3((g.ncells + FAST_WARPS - 1) / FAST_WARPS, nframes), FAST_WARPS * 32, smem, st>>>(g, h->dCells, l0, h->dRaw, nframes, h->params.min_th_fast,
-                                                                  h->params.ini_th_fast, h->dCand, h->dCellSeg, h->dLevelCandCount,
-                                                                  tilePitch, scorePitch, warpSmem);
+    if (forked) {
+        for (int i = 0; i < 2 * nl; ++i) ORBX_CUDA(cudaStreamWaitEvent(st, h->sideEvents[i], 0));
+        ORBX_COUNT(h, ORBX_STAGE_BLUR, nl);
+        ORBX_COUNT(h, ORBX_STAGE_FAST, nl);
+        ORBX_COUNT(h, ORBX_STAGE_OCTREE, nl);
+    } else {
+        // K1b: blur of all levels
+        launch_blur(st, 0, h->nBlurTiles);
+        ORBX_COUNT(h, ORBX_STAGE_BLUR, 1);
+        orbx_prof_mark(h, ORBX_STAGE_BLUR);
+        // K2: FAST
+        ORBX_CUDA(cudaMemsetAsync(h->dLevelCandCount, 0, (size_t)nframes * nl * sizeof(unsigned), st));
+        launch_fast(st, 0, g.ncells);
         ORBX_COUNT(h, ORBX_STAGE_FAST, 1);
         orbx_prof_mark(h, ORBX_STAGE_FAST);
-    }
-    // K3: quadtree
-    {
-        int NC = 8, cellsMax = 1, candMax = 1;
-        for (int l = 0; l < nl; ++l) { NC = std::max(NC, g.L[l].kpCap); cellsMax = std::max(cellsMax, g.L[l].nCells); candMax = std::max(candMax, g.L[l].candCap); }
-        if (NC > 16383 || candMax >= (1 << 24)) { orbx_set_error("quadtree: %d nodes / %d candidates per level exceed the kernel's index width", NC, candMax); return ORBX_E_CAPACITY; }
-        int P2 = 32; while (P2 < NC) P2 <<= 1;
-        const int cellWords = 2 * cellsMax + 2;
-        const int aliasWords = std::max(2 * P2 + 11 * NC, cellWords);
-        const int fixedBytes = 4 * (aliasWords + NC + 32 + 8);
-        // keys + labels of a level stay in shared memory up to keyCap candidates (6 bytes each); beyond that
-        // the level runs out of the global key buffers
-        // CTA width and shared-memory key capacity follow the per-level quota: more features per level means
-        // more candidates per level (640x480/1000: ~2.5 k at level 0; 1920x1080/5000: ~18 k)
-        const int threads = NC <= 256 ? 128 : (NC <= 512 ? 256 : 512);
-        int keyCap = std::min((candMax + 63) & ~63, threads == 128 ? 4096 : (threads == 256 ? 8192 : 24576));
-        if (fixedBytes + 6 * keyCap > 200 * 1024) keyCap = std::max(0, (200 * 1024 - fixedBytes) / 6) & ~63;
-        if (const char* e = getenv("ORBX_OCTREE_KEYCAP")) keyCap = std::max(0, std::min(keyCap, atoi(e)));   // tests: force the global-memory path
-        const int smem = fixedBytes + 6 * keyCap;
-        auto launch = [&](auto kern) -> int {
-            if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-            kern<<<nframes * nl, threads, smem, st>>>(g, nframes, h->dCand, h->dCellSeg, h->dKeysA, h->dKeysB, h->dLevelKps,
-                                                      h->dLevelKpCount, NC, P2, cellWords, keyCap, h->dStatus);
-            return ORBX_OK;
-        };
-        rc = threads == 128 ? launch(octree_kernel<128>) : (threads == 256 ? launch(octree_kernel<256>) : launch(octree_kernel<512>));
+        // K3: quadtree
+        rc = launch_octree(st, 0, nl);
         if (rc) return rc;
         ORBX_COUNT(h, ORBX_STAGE_OCTREE, 1);
         orbx_prof_mark(h, ORBX_STAGE_OCTREE);
@@ -1267,3 +1318,6 @@ int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot)
     h->lastChunkFrames = nframes;
     return ORBX_OK;
 }
+
+int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot) { return run_chunk_impl(h, l0, nframes, firstSlot, false); }
+int orbx_run_frame_forked(orbx_handle* h, Level0 l0, int firstSlot) { return run_chunk_impl(h, l0, 1, firstSlot, true); }

@@ -149,6 +149,10 @@ struct orbx_handle {
     cudaGraphExec_t graph1;
     bool graph1Valid;
     long long graph1Launches[ORBX_NSTAGES];
+    // forked form of one frame (orbx_run_frame_forked): per-level side streams and events, blur tile range per level
+    std::vector<cudaStream_t> sideStreams;
+    std::vector<cudaEvent_t> sideEvents, levelEvents;
+    int blurTileBeg[ORBX_MAX_LEVELS + 1];
     // per-stage device timing (CUDA events on the handle's stream) and launch counting
     bool profiling;
     std::vector<cudaEvent_t> evPool;
@@ -166,6 +170,7 @@ void orbx_prof_mark(orbx_handle* h, int stage);
 int orbx_setup_shape(orbx_handle* h, int w, int hgt);
 void orbx_drop_graph(orbx_handle* h);      // the workspace moved: the captured single-frame graph is stale
 int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot);
+int orbx_run_frame_forked(orbx_handle* h, Level0 l0, int firstSlot);   // one frame, per-level fork/join (latency form)
 
 // orbx_api.cu: frames [nf][height][row_stride] -> pitched workspace frames, on `st`
 int orbx_copy_frames(orbx_handle* h, uint8_t* dst, long long dstFrameBytes, uint8_t* stage, const uint8_t* src, size_t frame_stride,
