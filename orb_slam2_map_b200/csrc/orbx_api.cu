@@ -478,9 +478,19 @@ int orbx_extract(orbx_handle* h, const uint8_t* image, int width, int height, si
         h->hStageBytes = need;
     }
     uint8_t* stage = (uint8_t*)h->hStage;
-    if ((size_t)h->l0Pitch == row_stride) memcpy(stage, image, (size_t)row_stride * (height - 1) + width);
-    else for (int y = 0; y < height; ++y) memcpy(stage + (size_t)y * h->l0Pitch, image + (size_t)y * row_stride, width);
-    ORBX_CUDA(cudaMemcpyAsync(h->dLevel0, stage, imgBytes, cudaMemcpyHostToDevice, st));
+    cudaPointerAttributes pa;
+    const bool srcPinned = cudaPointerGetAttributes(&pa, image) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+    cudaGetLastError();                       // an unregistered host pointer is not an error here
+    if (srcPinned) {
+        // the caller's image is page-locked: the DMA engine reads it in place
+        ORBX_CUDA(cudaMemcpy2DAsync(h->dLevel0, h->l0Pitch, image, row_stride, width, height, cudaMemcpyHostToDevice, st));
+    } else {
+        // pageable image (a cv::Mat): one memcpy into the pinned staging at the workspace pitch, one DMA (row slices
+        // that overlap the two were measured slower: four copy launches cost more than the overlap saves)
+        if ((size_t)h->l0Pitch == row_stride) memcpy(stage, image, (size_t)row_stride * (height - 1) + width);
+        else for (int y = 0; y < height; ++y) memcpy(stage + (size_t)y * h->l0Pitch, image + (size_t)y * row_stride, width);
+        ORBX_CUDA(cudaMemcpyAsync(h->dLevel0, stage, imgBytes, cudaMemcpyHostToDevice, st));
+    }
     h->evFreeValid[0] = false;                // buffer 0 is now ordered by the handle's stream alone
     Level0 l0;
     l0.base = h->dLevel0; l0.base1 = nullptr; l0.stereo = 0; l0.frameStride = h->l0FrameBytes; l0.pitch = h->l0Pitch;

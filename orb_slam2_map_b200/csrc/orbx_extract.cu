@@ -1246,7 +1246,13 @@ static int run_chunk_impl(orbx_handle* h, Level0 l0, int nframes, int firstSlot,
         int r = launch_octree(sA, l, 1);
         if (r) return r;
         ORBX_CUDA(cudaEventRecord(h->sideEvents[2 * l], sA));
-        launch_blur(sB, h->blurTileBeg[l], h->blurTileBeg[l + 1]);
+        // blur: per level (8), or levels grouped into fewer launches that start when their last level exists
+        static const int blurGroups = getenv("ORBX_LAT_BLUR") ? atoi(getenv("ORBX_LAT_BLUR")) : 2;      // 8 / 4 / 2 / 1 groups measured 124 / 121 / 121 / 120 us
+        const int per = std::max(1, (nl + std::max(1, blurGroups) - 1) / std::max(1, blurGroups));
+        if ((l + 1) % per == 0 || l == nl - 1) {
+            const int first = (l / per) * per;
+            launch_blur(sB, h->blurTileBeg[first], h->blurTileBeg[l + 1]);
+        }
         ORBX_CUDA(cudaEventRecord(h->sideEvents[2 * l + 1], sB));
         return ORBX_OK;
     };
@@ -1265,7 +1271,7 @@ static int run_chunk_impl(orbx_handle* h, Level0 l0, int nframes, int firstSlot,
         else { src = h->dRaw + S.off; sfs = g.pyrFrameBytes; sp = S.pitch; }
         if (h->params.scale_factor <= 2.0f) {
             static const int rsTargetEnv = getenv("ORBX_RS_TARGET") ? std::max(4, atoi(getenv("ORBX_RS_TARGET"))) : RS_TARGET;
-            static const int rsTargetLat = getenv("ORBX_LAT_RS") ? std::max(2, atoi(getenv("ORBX_LAT_RS"))) : RS_TARGET;
+            static const int rsTargetLat = getenv("ORBX_LAT_RS") ? std::max(2, atoi(getenv("ORBX_LAT_RS"))) : 2;     // latency form: 2-row strips (120 us vs 144 us at 12 rows)
             const int rsTarget = forked ? rsTargetLat : rsTargetEnv;
             const int nstrips = std::max(1, (D.h + rsTarget - 1) / rsTarget), th = (D.h + nstrips - 1) / nstrips;
             dim3 grid((D.w + 127) / 128, (nstrips + RS_WARPS - 1) / RS_WARPS, nframes);

@@ -210,6 +210,12 @@ def test_single_frame_graph_replay(monkeypatch):
         kg, dg = ex.extract(seq[i])
         ko, do = orc.extract(seq[i])
         _compare_full(kg, dg, ko, do)
+    import torch
+    pin = torch.empty((480, 640), dtype=torch.uint8, pin_memory=True)      # page-locked source: copied in place, no staging
+    pin.copy_(torch.from_numpy(seq[3]))
+    kg, dg = ex.extract(pin.numpy())
+    ko, do = orc.extract(seq[3])
+    _compare_full(kg, dg, ko, do)
     flat = np.full((480, 640), 9, np.uint8)          # no keypoints at all after a full frame
     kg, dg = ex.extract(flat)
     assert len(kg) == 0 and dg.shape == (0, 32)
