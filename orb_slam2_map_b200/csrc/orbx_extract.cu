@@ -86,9 +86,6 @@ pyr_resize4_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long l
                    int dw, int dh, int th, int nsrcMax, const int2* __restrict__ cx, const int2* __restrict__ cy)
 {
     extern __shared__ uint2 rsH[];              // [warp][source row of the strip][lane]
-    // programmatic dependent launch (latency form only; both are no-ops otherwise): the next level's launch may be
-    // scheduled as soon as this one runs, and sets up its column constants while this level is still being written
-    asm volatile("griddepcontrol.launch_dependents;");
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     const int x = (blockIdx.x * 32 + lane) * 4;
     const int y0 = (blockIdx.y * RS_WARPS + wid) * th;
@@ -117,7 +114,6 @@ pyr_resize4_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long l
     const int sFirst = cy[y0].x & 0xffff;
     const int nsrc = min((cy[yend - 1].x >> 16) - sFirst + 1, nsrcMax);
     uint2* Hs = rsH + (size_t)wid * nsrcMax * 32 + lane;
-    asm volatile("griddepcontrol.wait;" ::: "memory");     // the source level is complete and visible from here on
     // ---- phase 1: horizontal sums of the strip's source rows -------------------------------------
     {
         const uint32_t* p = colp + (long long)sFirst * rowWords;
@@ -1283,17 +1279,6 @@ static int run_chunk_impl(orbx_handle* h, Level0 l0, int nframes, int firstSlot,
             const int nsrcMax = (int)((long long)th * S.h / D.h) + 4;
             const size_t rsSmem = (size_t)RS_WARPS * nsrcMax * 32 * sizeof(uint2);
             if (rsSmem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(pyr_resize4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsSmem));
-            static const bool pdl = getenv("ORBX_LAT_PDL") != nullptr;
-            if (forked && pdl && l > 1) {
-                cudaLaunchConfig_t cfg = {};
-                cfg.gridDim = grid; cfg.blockDim = dim3(RS_WARPS * 32); cfg.dynamicSmemBytes = rsSmem; cfg.stream = st;
-                cudaLaunchAttribute at[1];
-                at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-                at[0].val.programmaticStreamSerializationAllowed = 1;
-                cfg.attrs = at; cfg.numAttrs = 1;
-                ORBX_CUDA(cudaLaunchKernelEx(&cfg, pyr_resize4_kernel, l0, 0, src, sfs, sp, S.w, S.h, (u8*)(h->dRaw + D.off), (long long)g.pyrFrameBytes,
-                                             D.pitch, D.w, D.h, th, nsrcMax, (const int2*)(h->dCoef + D.coefX), (const int2*)(h->dCoef + D.coefY)));
-            } else
             pyr_resize4_kernel<<<grid, RS_WARPS * 32, rsSmem, st>>>(l0, l == 1 ? 1 : 0, src, sfs, sp, S.w, S.h, h->dRaw + D.off, g.pyrFrameBytes,
                                                                     D.pitch, D.w, D.h, th, nsrcMax, h->dCoef + D.coefX, h->dCoef + D.coefY);
         } else {
