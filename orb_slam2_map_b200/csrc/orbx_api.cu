@@ -61,6 +61,38 @@ static void compute_tables(orbx_handle* h)
     }
 }
 
+namespace {
+struct ScratchBlock { void* p; size_t size; int dev; bool used; };
+struct ScratchPool {
+    std::vector<ScratchBlock> blocks;
+    ~ScratchPool() { for (ScratchBlock& b : blocks) cudaFree(b.p); }      // thread exit; errors at process teardown are ignored
+};
+thread_local ScratchPool g_scratch;
+}
+
+int orbx_scratch_alloc(void** p, size_t bytes)
+{
+    static const bool pooled = !getenv("ORBX_NO_SCRATCH_POOL");
+    if (!pooled) { ORBX_CUDA(cudaMalloc(p, bytes ? bytes : 4)); return ORBX_OK; }
+    size_t sz = 512;
+    while (sz < bytes) sz <<= 1;
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    for (ScratchBlock& b : g_scratch.blocks)
+        if (!b.used && b.dev == dev && b.size == sz) { b.used = true; *p = b.p; return ORBX_OK; }
+    ORBX_CUDA(cudaMalloc(p, sz));
+    g_scratch.blocks.push_back({*p, sz, dev, true});
+    return ORBX_OK;
+}
+
+void orbx_scratch_free(void* p)
+{
+    if (!p) return;
+    for (ScratchBlock& b : g_scratch.blocks)
+        if (b.p == p) { b.used = false; return; }
+    cudaFree(p);                              // not from this thread's pool (pool disabled, or released on another thread)
+}
+
 void orbx_drop_graph(orbx_handle* h)
 {
     if (h->graph1Valid) cudaGraphExecDestroy(h->graph1);

@@ -213,8 +213,8 @@ distinctive_kernel(const u8* __restrict__ desc, const int32_t* __restrict__ offs
 
 struct BBuf {
     void* p = nullptr;
-    ~BBuf() { if (p) cudaFree(p); }
-    int alloc(size_t bytes) { ORBX_CUDA(cudaMalloc(&p, bytes ? bytes : 4)); return ORBX_OK; }
+    ~BBuf() { orbx_scratch_free(p); }
+    int alloc(size_t bytes) { return orbx_scratch_alloc(&p, bytes); }
     template <typename T> T* as() { return (T*)p; }
 };
 

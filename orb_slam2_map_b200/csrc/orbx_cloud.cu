@@ -113,8 +113,8 @@ backproject_kernel(BackprojectArgs A, orbx_cloud_point* __restrict__ points, int
 
 struct CBuf {
     void* p = nullptr;
-    ~CBuf() { if (p) cudaFree(p); }
-    int alloc(size_t bytes) { ORBX_CUDA(cudaMalloc(&p, bytes ? bytes : 4)); return ORBX_OK; }
+    ~CBuf() { orbx_scratch_free(p); }
+    int alloc(size_t bytes) { return orbx_scratch_alloc(&p, bytes); }
     template <typename T> T* as() { return (T*)p; }
 };
 

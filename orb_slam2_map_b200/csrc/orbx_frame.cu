@@ -136,8 +136,8 @@ frame_front_kernel(CamD c, float bf, const orbx_keypoint* __restrict__ kps, cons
 // ---- small RAII device buffer for the stateless entry points ---------------------------------------
 struct FBuf {
     void* p = nullptr;
-    ~FBuf() { if (p) cudaFree(p); }
-    int alloc(size_t bytes) { ORBX_CUDA(cudaMalloc(&p, bytes ? bytes : 4)); return ORBX_OK; }
+    ~FBuf() { orbx_scratch_free(p); }
+    int alloc(size_t bytes) { return orbx_scratch_alloc(&p, bytes); }
 };
 
 static int check_cam(const orbx_camera* cam)

@@ -167,6 +167,12 @@ void orbx_prof_mark(orbx_handle* h, int stage);
 #define ORBX_COUNT(h, stage, n) ((h)->stageLaunches[stage] += (n))
 
 // orbx_extract.cu
+// Device scratch of the stateless entry points (orbm_*, the frame-front helpers): a per-thread cache of blocks in
+// power-of-two size classes, so a call repeated every frame does no cudaMalloc / cudaFree after its first time.
+// A block is reused only by the thread that released it, on the same (legacy default) stream: stream order makes the
+// reuse safe even if the previous call's kernels were still in flight.
+int orbx_scratch_alloc(void** p, size_t bytes);
+void orbx_scratch_free(void* p);
 int orbx_setup_shape(orbx_handle* h, int w, int hgt);
 void orbx_drop_graph(orbx_handle* h);      // the workspace moved: the captured single-frame graph is stale
 int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot);

@@ -399,66 +399,198 @@ __device__ __forceinline__ void top2_insert(unsigned long long& k1, unsigned lon
     else if (k < k2) k2 = k;
 }
 
+// The PROJ_K smallest candidate keys of one query, ascending (warp-cooperative: lanes over the grid cells of
+// Frame::GetFeaturesInArea, each lane keeps its own PROJ_K smallest, then PROJ_K rounds of warp-minimum extraction;
+// every lane returns the same keys).  LIVE_OCC: read the occupancy flags as they are now (replay) rather than as
+// read-only data (candidate phase).
+#define PROJ_K 6
+struct ProjCtx {
+    const orbx_keypoint* kps; const u8* desc; const unsigned short* gs; const unsigned short* gi;
+    const float* uRight; const u8* occupied; GridParams gp; bool gate;
+};
+template <bool LIVE_OCC>
+__device__ __forceinline__ void proj_topk(const ProjCtx& c, const orbm_proj_query& Q, const u8* qdescRow, int lane,
+                                          unsigned long long (&out)[PROJ_K])
+{
+    const unsigned long long NONE = ~0ull;
+#pragma unroll
+    for (int k = 0; k < PROJ_K; ++k) out[k] = NONE;
+    int cx0, cx1, cy0, cy1;
+    if (!area_cells(c.gp, Q.u, Q.v, Q.radius, cx0, cx1, cy0, cy1)) return;
+    unsigned long long loc[PROJ_K];
+#pragma unroll
+    for (int k = 0; k < PROJ_K; ++k) loc[k] = NONE;
+    uint32_t qd[8];
+    load_desc(qd, qdescRow);
+    const bool checkLevels = (Q.min_level > 0) || (Q.max_level >= 0);
+    const int ncy = cy1 - cy0 + 1, nc = (cx1 - cx0 + 1) * ncy;
+    for (int cc = lane; cc < nc; cc += 32) {
+        const int ix = cx0 + cc / ncy, iy = cy0 + cc % ncy;
+        const int cell = ix * ORBX_GRID_ROWS + iy;
+        const int s = c.gs[cell], e = c.gs[cell + 1];
+        for (int j = s; j < e; ++j) {
+            const int idx = c.gi[j];
+            const orbx_keypoint kp = c.kps[idx];
+            if (checkLevels) {
+                if (kp.octave < Q.min_level) continue;
+                if (Q.max_level >= 0 && kp.octave > Q.max_level) continue;
+            }
+            if (!(fabsf(__fsub_rn(kp.x, Q.u)) < Q.radius && fabsf(__fsub_rn(kp.y, Q.v)) < Q.radius)) continue;
+            if (LIVE_OCC ? *reinterpret_cast<const volatile u8*>(c.occupied + idx) : c.occupied[idx]) continue;
+            if (c.gate) {
+                const float ur = c.uRight[idx];
+                if (ur > 0 && Q.max_right_err >= 0 && fabsf(__fsub_rn(Q.u_right, ur)) > Q.max_right_err) continue;
+            }
+            if (Q.level_lo >= 0 && (kp.octave < Q.level_lo || kp.octave > Q.level_hi)) continue;
+            const int dist = hamming256(qd, reinterpret_cast<const uint32_t*>(c.desc + (size_t)idx * 32));
+            unsigned long long key = ((unsigned long long)dist << 40) | ((unsigned long long)cell << 24) |
+                                     ((unsigned long long)idx << 8) | (unsigned long long)(kp.octave & 0xff);
+#pragma unroll
+            for (int k = 0; k < PROJ_K; ++k)             // sorted insertion (keys are distinct: idx is part of the key)
+                if (key < loc[k]) { const unsigned long long t = loc[k]; loc[k] = key; key = t; }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < PROJ_K; ++k) {
+        unsigned long long m = loc[0];
+        for (int d = 16; d > 0; d >>= 1) { const unsigned long long o = __shfl_xor_sync(FULL, m, d); m = o < m ? o : m; }
+        out[k] = m;
+        if (m != NONE && loc[0] == m) {                  // the owner pops its head
+#pragma unroll
+            for (int j = 0; j + 1 < PROJ_K; ++j) loc[j] = loc[j + 1];
+            loc[PROJ_K - 1] = NONE;
+        }
+    }
+}
+
+// Phase 1 (all SMs, warp per query): the PROJ_K smallest keys of every query under the occupancy the call STARTS with.
+#define PROJ_WARPS 4
+#define PROJ_CLAIMS 1024
+__global__ void __launch_bounds__(PROJ_WARPS * 32)
+search_proj_cand_kernel(FrameStore fs, int slot, GridParams gp, const float* __restrict__ uRight,
+                        const orbm_proj_query* __restrict__ queries, const u8* __restrict__ qdesc, int nq,
+                        const u8* __restrict__ occupied, int variant, unsigned long long* __restrict__ keys)
+{
+    const int lane = threadIdx.x & 31, q = blockIdx.x * PROJ_WARPS + (threadIdx.x >> 5);
+    if (q >= nq) return;
+    ProjCtx c;
+    c.kps = fs.kps + (size_t)slot * fs.cap; c.desc = fs.desc + (size_t)slot * fs.cap * 32;
+    c.gs = fs.gridStart + (size_t)slot * (ORBX_GRID_CELLS + 1); c.gi = fs.gridIdx + (size_t)slot * fs.cap;
+    c.uRight = uRight; c.occupied = occupied; c.gp = gp;
+    c.gate = (variant == ORBM_PROJ_LOCALMAP || variant == ORBM_PROJ_LASTFRAME) && uRight != nullptr;
+    const orbm_proj_query Q = queries[q];
+    unsigned long long K[PROJ_K];
+    proj_topk<false>(c, Q, qdesc + (size_t)q * 32, lane, K);
+    if (lane < PROJ_K) {
+        unsigned long long v = K[0];
+#pragma unroll
+        for (int k = 1; k < PROJ_K; ++k) if (lane == k) v = K[k];
+        keys[(size_t)PROJ_K * q + lane] = v;
+    }
+}
+
+// Phase 2 (one warp): replay of the query order.  Occupancy only grows during a call, so the candidates of query q
+// under the occupancy it actually meets are its phase-1 candidates minus those taken by earlier queries of this
+// call: its best and second best are the first two still-free keys of its phase-1 list.  That is exact whenever the
+// list is complete (fewer than PROJ_K candidates) or still has the free keys the variant needs (two for the ratio
+// test of the local-map variant, one otherwise), because everything beyond the list is larger than all of it; only
+// the remaining queries are searched again (proj_topk under the current occupancy).  32 queries are loaded at a
+// time, one per lane, and handed round by shuffle; the occupancy flags live in shared memory during the replay.
 __global__ void __launch_bounds__(32)
 search_proj_kernel(FrameStore fs, int slot, GridParams gp, const float* __restrict__ uRight,
                    const orbm_proj_query* __restrict__ queries, const u8* __restrict__ qdesc, int nq,
                    const u8* __restrict__ queryBlocks, u8* __restrict__ occupied, int* __restrict__ assigned,
                    int* __restrict__ bestIdxOut, int* __restrict__ bestDistOut, u8* __restrict__ binOf,
-                   int variant, int thDist, float nnratio, int checkOri, int* __restrict__ nmatchesOut)
+                   int variant, int thDist, float nnratio, int checkOri, int* __restrict__ nmatchesOut,
+                   const unsigned long long* __restrict__ keys)
 {
     __shared__ int hist[ORBX_HISTO_LENGTH];
+    __shared__ unsigned claim[PROJ_CLAIMS];
+    extern __shared__ __align__(16) u8 occS[];
     const int lane = threadIdx.x;
     const int n = min(fs.count[slot], fs.cap);
-    const orbx_keypoint* kps = fs.kps + (size_t)slot * fs.cap;
-    const u8* desc = fs.desc + (size_t)slot * fs.cap * 32;
-    const unsigned short* gs = fs.gridStart + (size_t)slot * (ORBX_GRID_CELLS + 1);
-    const unsigned short* gi = fs.gridIdx + (size_t)slot * fs.cap;
+    for (int i = lane; i < PROJ_CLAIMS; i += 32) claim[i] = 0xffffffffu;
+    ProjCtx c;
+    c.kps = fs.kps + (size_t)slot * fs.cap; c.desc = fs.desc + (size_t)slot * fs.cap * 32;
+    c.gs = fs.gridStart + (size_t)slot * (ORBX_GRID_CELLS + 1); c.gi = fs.gridIdx + (size_t)slot * fs.cap;
+    c.uRight = uRight; c.occupied = occS; c.gp = gp;
+    c.gate = (variant == ORBM_PROJ_LOCALMAP || variant == ORBM_PROJ_LASTFRAME) && uRight != nullptr;
+    const orbx_keypoint* kps = c.kps;
     if (lane < ORBX_HISTO_LENGTH) hist[lane] = 0;
-    for (int i = lane; i < n; i += 32) assigned[i] = -1;
+    for (int i = lane; i < n; i += 32) { assigned[i] = -1; occS[i] = occupied[i]; }
     __syncwarp();
     const bool rot = checkOri && (variant == ORBM_PROJ_LASTFRAME || variant == ORBM_PROJ_KEYFRAME);
-    const bool gate = (variant == ORBM_PROJ_LOCALMAP || variant == ORBM_PROJ_LASTFRAME) && uRight != nullptr;
+    const bool alwaysBlocks = variant == ORBM_PROJ_KEYFRAME || variant == ORBM_PROJ_SIM3;
+    const int needFree = variant == ORBM_PROJ_LOCALMAP ? 2 : 1;
     const unsigned long long NONE = ~0ull;
+    volatile u8* occ = occS;
     int nmatches = 0;
-    for (int q = 0; q < nq; ++q) {
-        const orbm_proj_query Q = queries[q];
-        int bIdx = -1, bDist = 256;
-        int cx0, cx1, cy0, cy1;
-        if (area_cells(gp, Q.u, Q.v, Q.radius, cx0, cx1, cy0, cy1)) {
-            uint32_t qd[8];
-            load_desc(qd, qdesc + (size_t)q * 32);
-            const bool checkLevels = (Q.min_level > 0) || (Q.max_level >= 0);
-            const int ncy = cy1 - cy0 + 1, nc = (cx1 - cx0 + 1) * ncy;
+    for (int q0 = 0; q0 < nq; q0 += 32) {
+        const int myq = q0 + lane;
+        unsigned long long K[PROJ_K];
+        float A[PROJ_K];
+#pragma unroll
+        for (int k = 0; k < PROJ_K; ++k) { K[k] = NONE; A[k] = 0.f; }
+        float myAngle = 0.f;
+        bool myBlocks = true;
+        if (myq < nq) {
+#pragma unroll
+            for (int k = 0; k < PROJ_K; ++k) K[k] = keys[(size_t)PROJ_K * myq + k];
+            if (rot) {
+                myAngle = queries[myq].angle;
+#pragma unroll
+                for (int k = 0; k < PROJ_K; ++k) if (K[k] != NONE) A[k] = kps[(int)((K[k] >> 8) & 0xffff)].angle;
+            }
+            myBlocks = alwaysBlocks ? true : (queryBlocks ? queryBlocks[myq] != 0 : true);
+        }
+        int outIdx = -1, outDist = 256, outBin = 0xff;
+        const int cnt = min(32, nq - q0);
+        // The 32 queries of the batch are decided lane-parallel against the current occupancy, then committed in
+        // order as far as that is safe: a lane may commit once every earlier lane has, or when no earlier
+        // uncommitted lane takes a keypoint of its candidate list.  The first lane that cannot (or whose list ran
+        // out of free keys: it is searched again by the whole warp) ends the round; the rest is decided again.
+        unsigned done = cnt < 32 ? ~((1u << cnt) - 1u) : 0u;
+        while (done != FULL) {
+            unsigned freeMask = 0;
+            bool complete = false;
+#pragma unroll
+            for (int k = 0; k < PROJ_K; ++k) {
+                const bool valid = K[k] != NONE;
+                const unsigned o = occ[valid ? (int)((K[k] >> 8) & 0xffff) : 0];
+                freeMask |= (valid && !o) ? (1u << k) : 0u;
+                complete |= !valid;
+            }
+            const int nfree = __popc(freeMask);
+            const int p1 = nfree > 0 ? __ffs(freeMask) - 1 : 0;
+            const unsigned rest = freeMask & (freeMask - 1);
+            const int p2 = nfree > 1 ? __ffs(rest) - 1 : -1;
             unsigned long long k1 = NONE, k2 = NONE;
-            for (int c = lane; c < nc; c += 32) {
-                const int ix = cx0 + c / ncy, iy = cy0 + c % ncy;
-                const int cell = ix * ORBX_GRID_ROWS + iy;
-                const int s = gs[cell], e = gs[cell + 1];
-                for (int j = s; j < e; ++j) {
-                    const int idx = gi[j];
-                    const orbx_keypoint kp = kps[idx];
-                    if (checkLevels) {
-                        if (kp.octave < Q.min_level) continue;
-                        if (Q.max_level >= 0 && kp.octave > Q.max_level) continue;
-                    }
-                    if (!(fabsf(__fsub_rn(kp.x, Q.u)) < Q.radius && fabsf(__fsub_rn(kp.y, Q.v)) < Q.radius)) continue;
-                    if (occupied[idx]) continue;
-                    if (gate) {
-                        const float ur = uRight[idx];
-                        if (ur > 0 && Q.max_right_err >= 0 && fabsf(__fsub_rn(Q.u_right, ur)) > Q.max_right_err) continue;
-                    }
-                    if (Q.level_lo >= 0 && (kp.octave < Q.level_lo || kp.octave > Q.level_hi)) continue;
-                    const int dist = hamming256(qd, reinterpret_cast<const uint32_t*>(desc + (size_t)idx * 32));
-                    const unsigned long long key = ((unsigned long long)dist << 40) | ((unsigned long long)cell << 24) |
-                                                   ((unsigned long long)idx << 8) | (unsigned long long)(kp.octave & 0xff);
-                    top2_insert(k1, k2, key);
-                }
+            float kpAngle = A[0];
+#pragma unroll
+            for (int k = 0; k < PROJ_K; ++k) {
+                if (nfree > 0 && p1 == k) { k1 = K[k]; kpAngle = A[k]; }
+                if (p2 == k) k2 = K[k];
             }
-            for (int d = 16; d > 0; d >>= 1) {
-                const unsigned long long o1 = __shfl_xor_sync(FULL, k1, d), o2 = __shfl_xor_sync(FULL, k2, d);
-                top2_insert(k1, k2, o1);
-                top2_insert(k1, k2, o2);
+            const bool pending = !((done >> lane) & 1u);
+            const bool dirty = pending && !complete && nfree < needFree;
+            const unsigned pendMask = ~done;
+            const int first = __ffs(pendMask) - 1;                       // pendMask != 0 here
+            float qAngle = myAngle;
+            bool blocks = myBlocks;
+            int q = myq;
+            const bool slow = (__ballot_sync(FULL, dirty) >> first) & 1u;
+            if (slow) {
+                // the first uncommitted query has no free key left in a truncated list: search it again (whole warp)
+                q = q0 + first;
+                const orbm_proj_query Q = queries[q];
+                unsigned long long R[PROJ_K];
+                proj_topk<true>(c, Q, qdesc + (size_t)q * 32, lane, R);
+                k1 = R[0]; k2 = R[1];
+                qAngle = Q.angle;
+                blocks = __shfl_sync(FULL, (int)myBlocks, first) != 0;
+                if (rot && k1 != NONE) kpAngle = kps[(int)((k1 >> 8) & 0xffff)].angle;
             }
+            int bIdx = -1, bDist = 256;
             if (k1 != NONE) {
                 const int bestDist = (int)(k1 >> 40), bestLevel = (int)(k1 & 0xff), bestIdx = (int)((k1 >> 8) & 0xffff);
                 // reference initial values: bestDist2 = 256, bestLevel2 = -1 (src/ORBmatcher.cc:73-77)
@@ -469,22 +601,46 @@ search_proj_kernel(FrameStore fs, int slot, GridParams gp, const float* __restri
                     (float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) ok = false;
                 if (ok) { bIdx = bestIdx; bDist = bestDist; }
             }
-        }
-        if (bIdx >= 0) {
-            ++nmatches;
-            if (lane == 0) {
-                assigned[bIdx] = q;
-                const bool blocks = (variant == ORBM_PROJ_KEYFRAME || variant == ORBM_PROJ_SIM3) ? true
-                                    : (queryBlocks ? queryBlocks[q] != 0 : true);
-                occupied[bIdx] = blocks ? 1 : 0;
-                if (rot) { const int bin = rot_bin(Q.angle, kps[bIdx].angle); binOf[q] = (u8)bin; hist[bin] += 1; }
+            const int bin = (rot && bIdx >= 0) ? rot_bin(qAngle, kpAngle) : 0xff;
+            unsigned commit;
+            if (slow) commit = 1u << first;                              // every lane holds query `first`'s decision
+            else {
+                // an earlier uncommitted lane that takes one of my candidates (or is itself undecided) stops me.  Takes are
+                // posted in a small hashed claim table (lowest lane wins); a hash collision only stops a lane that
+                // could have gone on, which costs a round, never exactness.
+                const int take = (pending && !dirty) ? bIdx : -1;
+                if (take >= 0) atomicMin(&claim[take & (PROJ_CLAIMS - 1)], (unsigned)lane);
+                __syncwarp();
+                const unsigned dirtyMask = __ballot_sync(FULL, dirty);
+                bool stop = dirty || (dirtyMask & ((1u << lane) - 1u)) != 0;
+                volatile unsigned* cl = claim;
+#pragma unroll
+                for (int k = 0; k < PROJ_K; ++k)
+                    stop |= K[k] != NONE && cl[(int)((K[k] >> 8) & 0xffff) & (PROJ_CLAIMS - 1)] < (unsigned)lane;
+                __syncwarp();
+                if (take >= 0) cl[take & (PROJ_CLAIMS - 1)] = 0xffffffffu;
+                const unsigned bad = __ballot_sync(FULL, pending && stop);
+                const int f = bad ? __ffs(bad) - 1 : 32;
+                commit = pendMask & (f >= 32 ? FULL : ((1u << f) - 1u));
             }
+            const bool mine = slow ? (lane == first) : (((commit >> lane) & 1u) != 0);
+            if (mine) {
+                outIdx = bIdx; outDist = bDist; outBin = bin;
+                if (bIdx >= 0) {
+                    assigned[bIdx] = q;
+                    occ[bIdx] = blocks ? 1 : 0;
+                    if (rot) atomicAdd(&hist[bin], 1);
+                }
+            }
+            nmatches += __popc(__ballot_sync(FULL, mine && bIdx >= 0));
+            done |= commit;
+            __syncwarp();
         }
-        if (lane == 0) { bestIdxOut[q] = bIdx; bestDistOut[q] = bDist; if (rot && bIdx < 0) binOf[q] = 0xff; }
-        __syncwarp();
+        if (myq < nq) { bestIdxOut[myq] = outIdx; bestDistOut[myq] = outDist; if (rot) binOf[myq] = (u8)outBin; }
     }
     __threadfence_block();
     __syncwarp();
+    for (int i = lane; i < n; i += 32) occupied[i] = occS[i];
     if (rot) {
         int i1, i2, i3;
         three_maxima(hist, ORBX_HISTO_LENGTH, i1, i2, i3);
@@ -929,16 +1085,14 @@ int orbm_descriptor_distance(const uint8_t* a, const uint8_t* b, int count, int3
     if (!a || !b || !dist) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
     int rc = require_device();
     if (rc) return rc;
-    u8 *da = nullptr, *db = nullptr; int* dd = nullptr;
-    ORBX_CUDA(cudaMalloc((void**)&da, (size_t)count * 32));
-    ORBX_CUDA(cudaMalloc((void**)&db, (size_t)count * 32));
-    ORBX_CUDA(cudaMalloc((void**)&dd, (size_t)count * 4));
+    DevBuf bA, bB, bD;
+    if ((rc = bA.alloc((size_t)count * 32)) || (rc = bB.alloc((size_t)count * 32)) || (rc = bD.alloc((size_t)count * 4))) return rc;
+    u8 *da = bA.as<u8>(), *db = bB.as<u8>(); int* dd = bD.as<int>();
     ORBX_CUDA(cudaMemcpy(da, a, (size_t)count * 32, cudaMemcpyHostToDevice));
     ORBX_CUDA(cudaMemcpy(db, b, (size_t)count * 32, cudaMemcpyHostToDevice));
     hamming_pairs_kernel<<<(count + 255) / 256, 256>>>(da, db, count, dd);
     ORBX_CUDA(cudaGetLastError());
     ORBX_CUDA(cudaMemcpy(dist, dd, (size_t)count * 4, cudaMemcpyDeviceToHost));
-    cudaFree(da); cudaFree(db); cudaFree(dd);
     return ORBX_OK;
 }
 
@@ -954,10 +1108,9 @@ int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, f
     rc = tf.alloc(2, std::max(f1->n, f2->n)); if (rc) return rc;
     rc = tf.upload(0, f1); if (rc) return rc;
     rc = tf.upload(1, f2); if (rc) return rc;
-    float* dPrev = nullptr; int* dM12 = nullptr; int* dNm = nullptr;
-    ORBX_CUDA(cudaMalloc((void**)&dPrev, (size_t)tf.cap * 2 * sizeof(float)));
-    ORBX_CUDA(cudaMalloc((void**)&dM12, (size_t)tf.cap * sizeof(int)));
-    ORBX_CUDA(cudaMalloc((void**)&dNm, sizeof(int)));
+    DevBuf bPrev, bM12, bNm;
+    if ((rc = bPrev.alloc((size_t)tf.cap * 2 * sizeof(float))) || (rc = bM12.alloc((size_t)tf.cap * sizeof(int))) || (rc = bNm.alloc(sizeof(int)))) return rc;
+    float* dPrev = bPrev.as<float>(); int* dM12 = bM12.as<int>(); int* dNm = bNm.as<int>();
     if (f1->n) ORBX_CUDA(cudaMemcpy(dPrev, prev_matched, (size_t)f1->n * 2 * sizeof(float), cudaMemcpyHostToDevice));
     const GridParams gp = orbx_grid_params(f2->min_x, f2->max_x, f2->min_y, f2->max_y);
     rc = orbx_launch_grid_build(tf.store(), 1, 1, gp, 0); if (rc) return rc;
@@ -971,7 +1124,6 @@ int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, f
         ORBX_CUDA(cudaMemcpy(prev_matched, dPrev, (size_t)f1->n * 2 * sizeof(float), cudaMemcpyDeviceToHost));
     }
     if (nmatches) *nmatches = nm;
-    cudaFree(dPrev); cudaFree(dM12); cudaFree(dNm);
     return ORBX_OK;
 }
 
@@ -1006,10 +1158,18 @@ int orbm_search_by_projection(int variant, const orbm_frame* frame, const orbm_p
         ORBX_CUDA(cudaMemcpy(dOcc.p, occupied, (size_t)frame->n, cudaMemcpyHostToDevice));
         if (frame->u_right) ORBX_CUDA(cudaMemcpy(dUR.p, frame->u_right, (size_t)frame->n * 4, cudaMemcpyHostToDevice));
     }
-    search_proj_kernel<<<1, 32>>>(tf.store(), 0, gp, frame->u_right ? dUR.as<float>() : nullptr, dQ.as<orbm_proj_query>(),
+    DevBuf dKeys;
+    if ((rc = dKeys.alloc(Q * PROJ_K * 8))) return rc;
+    if (nq > 0)
+        search_proj_cand_kernel<<<(nq + PROJ_WARPS - 1) / PROJ_WARPS, PROJ_WARPS * 32>>>(
+            tf.store(), 0, gp, frame->u_right ? dUR.as<float>() : nullptr, dQ.as<orbm_proj_query>(), dQD.as<u8>(), nq, dOcc.as<u8>(),
+            variant, dKeys.as<unsigned long long>());
+    const int occSmem = (std::max(frame->n, 1) + 15) & ~15;          // n <= 65000 (check_frame)
+    if (occSmem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(search_proj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, occSmem));
+    search_proj_kernel<<<1, 32, occSmem>>>(tf.store(), 0, gp, frame->u_right ? dUR.as<float>() : nullptr, dQ.as<orbm_proj_query>(),
                                   dQD.as<u8>(), nq, query_blocks ? dQB.as<u8>() : nullptr, dOcc.as<u8>(), dAsg.as<int>(),
                                   dBI.as<int>(), dBD.as<int>(), dBin.as<u8>(), variant, th_dist, nnratio,
-                                  check_orientation, dNm.as<int>());
+                                  check_orientation, dNm.as<int>(), dKeys.as<unsigned long long>());
     ORBX_CUDA(cudaGetLastError());
     int nm = 0;
     ORBX_CUDA(cudaMemcpy(&nm, dNm.p, 4, cudaMemcpyDeviceToHost));

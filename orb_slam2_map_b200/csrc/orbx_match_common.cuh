@@ -91,11 +91,11 @@ __device__ __forceinline__ int rot_bin(float a1, float a2)
 GridParams orbx_grid_params(float minX, float maxX, float minY, float maxY);
 int orbx_launch_grid_build(const FrameStore& fs, int firstSlot, int nframes, const GridParams& gp, cudaStream_t st);
 
-// device scratch that frees itself (the stateless entry points allocate per call)
+// device scratch that releases itself (per-thread block cache, orbx_scratch_alloc: no cudaMalloc after the first call)
 struct DevBuf {
     void* p = nullptr;
-    ~DevBuf() { if (p) cudaFree(p); }
-    int alloc(size_t bytes) { ORBX_CUDA(cudaMalloc(&p, bytes ? bytes : 4)); return ORBX_OK; }
+    ~DevBuf() { orbx_scratch_free(p); }
+    int alloc(size_t bytes) { return orbx_scratch_alloc(&p, bytes); }
     template <typename T> T* as() { return (T*)p; }
 };
 
@@ -104,15 +104,16 @@ struct TempFrames {
     orbx_keypoint* kps = nullptr; u8* desc = nullptr; int* count = nullptr;
     unsigned short* gridStart = nullptr; unsigned short* gridIdx = nullptr;
     int cap = 0, nslots = 0;
-    ~TempFrames() { cudaFree(kps); cudaFree(desc); cudaFree(count); cudaFree(gridStart); cudaFree(gridIdx); }
+    ~TempFrames() { orbx_scratch_free(kps); orbx_scratch_free(desc); orbx_scratch_free(count); orbx_scratch_free(gridStart); orbx_scratch_free(gridIdx); }
     int alloc(int slots, int capacity)
     {
         cap = std::max(capacity, 8); nslots = slots;
-        ORBX_CUDA(cudaMalloc((void**)&kps, (size_t)slots * cap * sizeof(orbx_keypoint)));
-        ORBX_CUDA(cudaMalloc((void**)&desc, (size_t)slots * cap * 32));
-        ORBX_CUDA(cudaMalloc((void**)&count, slots * sizeof(int)));
-        ORBX_CUDA(cudaMalloc((void**)&gridStart, (size_t)slots * (ORBX_GRID_CELLS + 1) * sizeof(unsigned short)));
-        ORBX_CUDA(cudaMalloc((void**)&gridIdx, (size_t)slots * cap * sizeof(unsigned short)));
+        int rc;
+        if ((rc = orbx_scratch_alloc((void**)&kps, (size_t)slots * cap * sizeof(orbx_keypoint))) ||
+            (rc = orbx_scratch_alloc((void**)&desc, (size_t)slots * cap * 32)) ||
+            (rc = orbx_scratch_alloc((void**)&count, slots * sizeof(int))) ||
+            (rc = orbx_scratch_alloc((void**)&gridStart, (size_t)slots * (ORBX_GRID_CELLS + 1) * sizeof(unsigned short))) ||
+            (rc = orbx_scratch_alloc((void**)&gridIdx, (size_t)slots * cap * sizeof(unsigned short)))) return rc;
         return ORBX_OK;
     }
     int upload(int slot, const orbm_frame* f)
