@@ -177,3 +177,40 @@ def test_knn2_sharded_merge_equals_whole():
     assert np.array_equal(oi.cpu().numpy(), oi_w) and np.array_equal(od.cpu().numpy().view(np.uint16), od_w)
     od_o, oi_o = O.knn2(q[:200], db, nthreads=8)
     assert np.array_equal(oi_w[:200], oi_o) and np.array_equal(od_w[:200], od_o)
+
+
+def test_stateless_calls_reuse_scratch_across_sizes_and_threads():
+    """The stateless matcher entry points draw device scratch from a per-thread block cache (orbx_scratch_alloc): the same
+    calls repeated with growing and shrinking inputs, interleaved between two threads, must keep returning the oracle's
+    answers (stale contents of a reused block, or a block shared between threads, would show up here)."""
+    import threading
+    cases = []
+    for seed, nq in ((1, 900), (2, 300), (3, 1200), (4, 60)):
+        k, d, q, qd, ur, occ, blk, sf = _frame_with_queries(seed, nq=nq)
+        fo = O.FrameData(k, d, 640, 480, u_right=ur, scale_factors=sf)
+        want = O.search_by_projection(capi.PROJ_LOCALMAP, fo, q, qd, blk, occ, 100, 0.8, False)
+        cases.append((k, d, q, qd, ur, occ, blk, sf, want))
+    errors = []
+
+    def worker(order):
+        try:
+            for rep in range(3):
+                for ci in order:
+                    k, d, q, qd, ur, occ, blk, sf, want = cases[ci]
+                    fg = capi.FrameData(k, d, 640, 480, u_right=ur, scale_factors=sf)
+                    got = capi.search_by_projection(capi.PROJ_LOCALMAP, fg, q, qd, blk, occ, 100, 0.8, False)
+                    assert got[0] == want[0]
+                    for a, b in zip(got[1:], want[1:]):
+                        assert np.array_equal(a, b)
+                    dist = capi.descriptor_distance(d[: 50 + 10 * ci], d[::-1][: 50 + 10 * ci])
+                    ref = np.unpackbits(d[: 50 + 10 * ci] ^ d[::-1][: 50 + 10 * ci], axis=1).sum(axis=1)
+                    assert np.array_equal(dist, ref)
+        except Exception as e:      # surfaced in the main thread
+            errors.append(e)
+
+    ts = [threading.Thread(target=worker, args=(o,)) for o in ([0, 1, 2, 3], [3, 2, 1, 0])]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    assert not errors, errors[0]
