@@ -469,7 +469,8 @@ __device__ __forceinline__ void proj_topk(const ProjCtx& c, const orbm_proj_quer
 __global__ void __launch_bounds__(PROJ_WARPS * 32)
 search_proj_cand_kernel(FrameStore fs, int slot, GridParams gp, const float* __restrict__ uRight,
                         const orbm_proj_query* __restrict__ queries, const u8* __restrict__ qdesc, int nq,
-                        const u8* __restrict__ occupied, int variant, unsigned long long* __restrict__ keys)
+                        const u8* __restrict__ occupied, int variant, unsigned long long* __restrict__ keys,
+                        float* __restrict__ keyAngles)
 {
     const int lane = threadIdx.x & 31, q = blockIdx.x * PROJ_WARPS + (threadIdx.x >> 5);
     if (q >= nq) return;
@@ -486,6 +487,8 @@ search_proj_cand_kernel(FrameStore fs, int slot, GridParams gp, const float* __r
 #pragma unroll
         for (int k = 1; k < PROJ_K; ++k) if (lane == k) v = K[k];
         keys[(size_t)PROJ_K * q + lane] = v;
+        // the candidate's orientation rides along, so the replay needs no dependent keypoint load
+        keyAngles[(size_t)PROJ_K * q + lane] = v != ~0ull ? c.kps[(int)((v >> 8) & 0xffff)].angle : 0.f;
     }
 }
 
@@ -502,7 +505,7 @@ search_proj_kernel(FrameStore fs, int slot, GridParams gp, const float* __restri
                    const u8* __restrict__ queryBlocks, u8* __restrict__ occupied, int* __restrict__ assigned,
                    int* __restrict__ bestIdxOut, int* __restrict__ bestDistOut, u8* __restrict__ binOf,
                    int variant, int thDist, float nnratio, int checkOri, int* __restrict__ nmatchesOut,
-                   const unsigned long long* __restrict__ keys)
+                   const unsigned long long* __restrict__ keys, const float* __restrict__ keyAngles)
 {
     __shared__ int hist[ORBX_HISTO_LENGTH];
     __shared__ unsigned claim[PROJ_CLAIMS];
@@ -525,24 +528,37 @@ search_proj_kernel(FrameStore fs, int slot, GridParams gp, const float* __restri
     const unsigned long long NONE = ~0ull;
     volatile u8* occ = occS;
     int nmatches = 0;
+    // per-lane query state, loaded one batch ahead so the loads of batch b+1 fly while batch b is replayed
+    unsigned long long Kn[PROJ_K];
+    float An[PROJ_K];
+    float angleN = 0.f;
+    bool blocksN = true;
+    auto load_batch = [&](int q0) {
+        const int myq = q0 + lane;
+#pragma unroll
+        for (int k = 0; k < PROJ_K; ++k) { Kn[k] = NONE; An[k] = 0.f; }
+        angleN = 0.f; blocksN = true;
+        if (myq < nq) {
+#pragma unroll
+            for (int k = 0; k < PROJ_K; ++k) Kn[k] = keys[(size_t)PROJ_K * myq + k];
+            if (rot) {
+                angleN = queries[myq].angle;
+#pragma unroll
+                for (int k = 0; k < PROJ_K; ++k) An[k] = keyAngles[(size_t)PROJ_K * myq + k];
+            }
+            blocksN = alwaysBlocks ? true : (queryBlocks ? queryBlocks[myq] != 0 : true);
+        }
+    };
+    load_batch(0);
     for (int q0 = 0; q0 < nq; q0 += 32) {
         const int myq = q0 + lane;
         unsigned long long K[PROJ_K];
         float A[PROJ_K];
 #pragma unroll
-        for (int k = 0; k < PROJ_K; ++k) { K[k] = NONE; A[k] = 0.f; }
-        float myAngle = 0.f;
-        bool myBlocks = true;
-        if (myq < nq) {
-#pragma unroll
-            for (int k = 0; k < PROJ_K; ++k) K[k] = keys[(size_t)PROJ_K * myq + k];
-            if (rot) {
-                myAngle = queries[myq].angle;
-#pragma unroll
-                for (int k = 0; k < PROJ_K; ++k) if (K[k] != NONE) A[k] = kps[(int)((K[k] >> 8) & 0xffff)].angle;
-            }
-            myBlocks = alwaysBlocks ? true : (queryBlocks ? queryBlocks[myq] != 0 : true);
-        }
+        for (int k = 0; k < PROJ_K; ++k) { K[k] = Kn[k]; A[k] = An[k]; }
+        const float myAngle = angleN;
+        const bool myBlocks = blocksN;
+        if (q0 + 32 < nq) load_batch(q0 + 32);
         int outIdx = -1, outDist = 256, outBin = 0xff;
         const int cnt = min(32, nq - q0);
         // The 32 queries of the batch are decided lane-parallel against the current occupancy, then committed in
@@ -605,7 +621,7 @@ search_proj_kernel(FrameStore fs, int slot, GridParams gp, const float* __restri
             unsigned commit;
             if (slow) commit = 1u << first;                              // every lane holds query `first`'s decision
             else {
-                // an earlier uncommitted lane that takes one of my candidates (or is itself undecided) stops me.  Takes are
+                // an earlier uncommitted lane that takes a keypoint my decision depends on (or is itself undecided) stops me.  Takes are
                 // posted in a small hashed claim table (lowest lane wins); a hash collision only stops a lane that
                 // could have gone on, which costs a round, never exactness.
                 const int take = (pending && !dirty) ? bIdx : -1;
@@ -614,9 +630,9 @@ search_proj_kernel(FrameStore fs, int slot, GridParams gp, const float* __restri
                 const unsigned dirtyMask = __ballot_sync(FULL, dirty);
                 bool stop = dirty || (dirtyMask & ((1u << lane) - 1u)) != 0;
                 volatile unsigned* cl = claim;
-#pragma unroll
-                for (int k = 0; k < PROJ_K; ++k)
-                    stop |= K[k] != NONE && cl[(int)((K[k] >> 8) & 0xffff) & (PROJ_CLAIMS - 1)] < (unsigned)lane;
+                // only the keys my decision reads matter: the best one, and the second best where the ratio test uses it
+                stop |= k1 != NONE && cl[(int)((k1 >> 8) & 0xffff) & (PROJ_CLAIMS - 1)] < (unsigned)lane;
+                stop |= needFree == 2 && k2 != NONE && cl[(int)((k2 >> 8) & 0xffff) & (PROJ_CLAIMS - 1)] < (unsigned)lane;
                 __syncwarp();
                 if (take >= 0) cl[take & (PROJ_CLAIMS - 1)] = 0xffffffffu;
                 const unsigned bad = __ballot_sync(FULL, pending && stop);
@@ -1158,18 +1174,18 @@ int orbm_search_by_projection(int variant, const orbm_frame* frame, const orbm_p
         ORBX_CUDA(cudaMemcpy(dOcc.p, occupied, (size_t)frame->n, cudaMemcpyHostToDevice));
         if (frame->u_right) ORBX_CUDA(cudaMemcpy(dUR.p, frame->u_right, (size_t)frame->n * 4, cudaMemcpyHostToDevice));
     }
-    DevBuf dKeys;
-    if ((rc = dKeys.alloc(Q * PROJ_K * 8))) return rc;
+    DevBuf dKeys, dKeyAng;
+    if ((rc = dKeys.alloc(Q * PROJ_K * 8)) || (rc = dKeyAng.alloc(Q * PROJ_K * 4))) return rc;
     if (nq > 0)
         search_proj_cand_kernel<<<(nq + PROJ_WARPS - 1) / PROJ_WARPS, PROJ_WARPS * 32>>>(
             tf.store(), 0, gp, frame->u_right ? dUR.as<float>() : nullptr, dQ.as<orbm_proj_query>(), dQD.as<u8>(), nq, dOcc.as<u8>(),
-            variant, dKeys.as<unsigned long long>());
+            variant, dKeys.as<unsigned long long>(), dKeyAng.as<float>());
     const int occSmem = (std::max(frame->n, 1) + 15) & ~15;          // n <= 65000 (check_frame)
     if (occSmem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(search_proj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, occSmem));
     search_proj_kernel<<<1, 32, occSmem>>>(tf.store(), 0, gp, frame->u_right ? dUR.as<float>() : nullptr, dQ.as<orbm_proj_query>(),
                                   dQD.as<u8>(), nq, query_blocks ? dQB.as<u8>() : nullptr, dOcc.as<u8>(), dAsg.as<int>(),
                                   dBI.as<int>(), dBD.as<int>(), dBin.as<u8>(), variant, th_dist, nnratio,
-                                  check_orientation, dNm.as<int>(), dKeys.as<unsigned long long>());
+                                  check_orientation, dNm.as<int>(), dKeys.as<unsigned long long>(), dKeyAng.as<float>());
     ORBX_CUDA(cudaGetLastError());
     int nm = 0;
     ORBX_CUDA(cudaMemcpy(&nm, dNm.p, 4, cudaMemcpyDeviceToHost));
