@@ -65,7 +65,9 @@ namespace {
 struct ScratchBlock { void* p; size_t size; int dev; bool used; };
 struct ScratchPool {
     std::vector<ScratchBlock> blocks;
-    ~ScratchPool() { for (ScratchBlock& b : blocks) cudaFree(b.p); }      // thread exit; errors at process teardown are ignored
+    void* host = nullptr;
+    size_t hostBytes = 0;
+    ~ScratchPool() { for (ScratchBlock& b : blocks) cudaFree(b.p); if (host) cudaFreeHost(host); }   // thread exit; errors at process teardown are ignored
 };
 thread_local ScratchPool g_scratch;
 }
@@ -82,6 +84,19 @@ int orbx_scratch_alloc(void** p, size_t bytes)
         if (!b.used && b.dev == dev && b.size == sz) { b.used = true; *p = b.p; return ORBX_OK; }
     ORBX_CUDA(cudaMalloc(p, sz));
     g_scratch.blocks.push_back({*p, sz, dev, true});
+    return ORBX_OK;
+}
+
+int orbx_scratch_host(void** p, size_t bytes)
+{
+    if (g_scratch.hostBytes < bytes) {
+        if (g_scratch.host) { cudaDeviceSynchronize(); cudaFreeHost(g_scratch.host); g_scratch.host = nullptr; g_scratch.hostBytes = 0; }
+        size_t sz = 1 << 16;
+        while (sz < bytes) sz <<= 1;
+        ORBX_CUDA(cudaMallocHost(&g_scratch.host, sz));
+        g_scratch.hostBytes = sz;
+    }
+    *p = g_scratch.host;
     return ORBX_OK;
 }
 

@@ -173,6 +173,7 @@ void orbx_prof_mark(orbx_handle* h, int stage);
 // reuse safe even if the previous call's kernels were still in flight.
 int orbx_scratch_alloc(void** p, size_t bytes);
 void orbx_scratch_free(void* p);
+int orbx_scratch_host(void** p, size_t bytes);     // this thread's pinned staging buffer (grown on demand, kept)
 int orbx_setup_shape(orbx_handle* h, int w, int hgt);
 void orbx_drop_graph(orbx_handle* h);      // the workspace moved: the captured single-frame graph is stale
 int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot);

@@ -1223,47 +1223,69 @@ int orbm_search_by_projection(int variant, const orbm_frame* frame, const orbm_p
         orbx_set_error("null argument"); return ORBX_E_INVALID;
     }
     rc = require_device(); if (rc) return rc;
-    TempFrames tf;
-    rc = tf.alloc(1, frame->n); if (rc) return rc;
-    rc = tf.upload(0, frame); if (rc) return rc;
-    const GridParams gp = orbx_grid_params(frame->min_x, frame->max_x, frame->min_y, frame->max_y);
-    rc = orbx_launch_grid_build(tf.store(), 0, 1, gp, 0); if (rc) return rc;
-    DevBuf dQ, dQD, dQB, dOcc, dAsg, dBI, dBD, dBin, dNm, dUR;
+    // One device arena, one pinned staging buffer: [inputs][in/out + outputs][work].  Everything the call uploads goes
+    // up in ONE copy and everything it returns comes back in ONE copy (a dozen small synchronous copies cost ~8 us each).
     const size_t n = (size_t)std::max(frame->n, 1), Q = (size_t)std::max(nq, 1);
-    if ((rc = dQ.alloc(Q * sizeof(orbm_proj_query))) || (rc = dQD.alloc(Q * 32)) || (rc = dQB.alloc(Q)) ||
-        (rc = dOcc.alloc(n)) || (rc = dAsg.alloc(n * 4)) || (rc = dBI.alloc(Q * 4)) || (rc = dBD.alloc(Q * 4)) ||
-        (rc = dBin.alloc(Q)) || (rc = dNm.alloc(4)) || (rc = dUR.alloc(n * 4))) return rc;
-    if (nq > 0) {
-        ORBX_CUDA(cudaMemcpy(dQ.p, queries, (size_t)nq * sizeof(orbm_proj_query), cudaMemcpyHostToDevice));
-        ORBX_CUDA(cudaMemcpy(dQD.p, query_desc, (size_t)nq * 32, cudaMemcpyHostToDevice));
-        if (query_blocks) ORBX_CUDA(cudaMemcpy(dQB.p, query_blocks, (size_t)nq, cudaMemcpyHostToDevice));
-    }
+    size_t off = 0;
+    auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    const size_t oCount = take(4), oKps = take(n * sizeof(orbx_keypoint)), oDesc = take(n * 32), oQ = take(Q * sizeof(orbm_proj_query)),
+                 oQD = take(Q * 32), oQB = take(Q), oUR = take(n * 4);
+    const size_t oOcc = take(n);                       // in/out: last of the upload, first of the download
+    const size_t upBytes = off;
+    const size_t oNm = take(4), oAsg = take(n * 4), oBI = take(Q * 4), oBD = take(Q * 4);
+    const size_t downBytes = off - oOcc;
+    const size_t oGS = take((ORBX_GRID_CELLS + 1) * sizeof(unsigned short)), oGI = take(n * sizeof(unsigned short)),
+                 oKeys = take(Q * PROJ_K * 8), oKA = take(Q * PROJ_K * 4), oBin = take(Q);
+    DevBuf arena;
+    if ((rc = arena.alloc(off))) return rc;
+    u8* host = nullptr;
+    if ((rc = orbx_scratch_host((void**)&host, oOcc + downBytes))) return rc;
+    u8* dev = arena.as<u8>();
+    const int nkp = frame->n;
+    memcpy(host + oCount, &nkp, 4);
     if (frame->n > 0) {
-        ORBX_CUDA(cudaMemcpy(dOcc.p, occupied, (size_t)frame->n, cudaMemcpyHostToDevice));
-        if (frame->u_right) ORBX_CUDA(cudaMemcpy(dUR.p, frame->u_right, (size_t)frame->n * 4, cudaMemcpyHostToDevice));
+        memcpy(host + oKps, frame->keys_un, (size_t)frame->n * sizeof(orbx_keypoint));
+        memcpy(host + oDesc, frame->descriptors, (size_t)frame->n * 32);
+        memcpy(host + oOcc, occupied, (size_t)frame->n);
+        if (frame->u_right) memcpy(host + oUR, frame->u_right, (size_t)frame->n * 4);
     }
-    DevBuf dKeys, dKeyAng;
-    if ((rc = dKeys.alloc(Q * PROJ_K * 8)) || (rc = dKeyAng.alloc(Q * PROJ_K * 4))) return rc;
+    if (nq > 0) {
+        memcpy(host + oQ, queries, (size_t)nq * sizeof(orbm_proj_query));
+        memcpy(host + oQD, query_desc, (size_t)nq * 32);
+        if (query_blocks) memcpy(host + oQB, query_blocks, (size_t)nq);
+    }
+    ORBX_CUDA(cudaMemcpyAsync(dev, host, upBytes, cudaMemcpyHostToDevice, 0));
+    FrameStore fs;
+    fs.kps = reinterpret_cast<orbx_keypoint*>(dev + oKps); fs.desc = dev + oDesc; fs.count = reinterpret_cast<int*>(dev + oCount);
+    fs.gridStart = reinterpret_cast<unsigned short*>(dev + oGS); fs.gridIdx = reinterpret_cast<unsigned short*>(dev + oGI);
+    fs.cap = (int)n;
+    const GridParams gp = orbx_grid_params(frame->min_x, frame->max_x, frame->min_y, frame->max_y);
+    rc = orbx_launch_grid_build(fs, 0, 1, gp, 0); if (rc) return rc;
+    const float* dUR = frame->u_right ? reinterpret_cast<const float*>(dev + oUR) : nullptr;
+    const orbm_proj_query* dQ = reinterpret_cast<const orbm_proj_query*>(dev + oQ);
+    unsigned long long* dKeys = reinterpret_cast<unsigned long long*>(dev + oKeys);
+    float* dKA = reinterpret_cast<float*>(dev + oKA);
     if (nq > 0)
         search_proj_cand_kernel<<<(nq + PROJ_WARPS - 1) / PROJ_WARPS, PROJ_WARPS * 32>>>(
-            tf.store(), 0, gp, frame->u_right ? dUR.as<float>() : nullptr, dQ.as<orbm_proj_query>(), dQD.as<u8>(), nq, dOcc.as<u8>(),
-            variant, dKeys.as<unsigned long long>(), dKeyAng.as<float>());
+            fs, 0, gp, dUR, dQ, dev + oQD, nq, dev + oOcc, variant, dKeys, dKA);
     const int occSmem = (std::max(frame->n, 1) + 15) & ~15;          // n <= 65000 (check_frame)
     if (occSmem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(search_proj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, occSmem));
-    search_proj_kernel<<<1, 32, occSmem>>>(tf.store(), 0, gp, frame->u_right ? dUR.as<float>() : nullptr, dQ.as<orbm_proj_query>(),
-                                  dQD.as<u8>(), nq, query_blocks ? dQB.as<u8>() : nullptr, dOcc.as<u8>(), dAsg.as<int>(),
-                                  dBI.as<int>(), dBD.as<int>(), dBin.as<u8>(), variant, th_dist, nnratio,
-                                  check_orientation, dNm.as<int>(), dKeys.as<unsigned long long>(), dKeyAng.as<float>());
+    search_proj_kernel<<<1, 32, occSmem>>>(fs, 0, gp, dUR, dQ, dev + oQD, nq, query_blocks ? dev + oQB : nullptr, dev + oOcc,
+                                           reinterpret_cast<int*>(dev + oAsg), reinterpret_cast<int*>(dev + oBI),
+                                           reinterpret_cast<int*>(dev + oBD), dev + oBin, variant, th_dist, nnratio,
+                                           check_orientation, reinterpret_cast<int*>(dev + oNm), dKeys, dKA);
     ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaMemcpyAsync(host + oOcc, dev + oOcc, downBytes, cudaMemcpyDeviceToHost, 0));
+    ORBX_CUDA(cudaStreamSynchronize(0));
     int nm = 0;
-    ORBX_CUDA(cudaMemcpy(&nm, dNm.p, 4, cudaMemcpyDeviceToHost));
+    memcpy(&nm, host + oNm, 4);
     if (frame->n > 0) {
-        ORBX_CUDA(cudaMemcpy(occupied, dOcc.p, (size_t)frame->n, cudaMemcpyDeviceToHost));
-        ORBX_CUDA(cudaMemcpy(assigned, dAsg.p, (size_t)frame->n * 4, cudaMemcpyDeviceToHost));
+        memcpy(occupied, host + oOcc, (size_t)frame->n);
+        memcpy(assigned, host + oAsg, (size_t)frame->n * 4);
     }
     if (nq > 0) {
-        ORBX_CUDA(cudaMemcpy(best_idx, dBI.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
-        ORBX_CUDA(cudaMemcpy(best_dist, dBD.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
+        memcpy(best_idx, host + oBI, (size_t)nq * 4);
+        memcpy(best_dist, host + oBD, (size_t)nq * 4);
     }
     if (nmatches) *nmatches = nm;
     return ORBX_OK;
