@@ -1188,24 +1188,50 @@ int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, f
     rc = check_frame(f2); if (rc) return rc;
     if (!prev_matched || !matches12) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
     rc = require_device(); if (rc) return rc;
-    TempFrames tf;
-    rc = tf.alloc(2, std::max(f1->n, f2->n)); if (rc) return rc;
-    rc = tf.upload(0, f1); if (rc) return rc;
-    rc = tf.upload(1, f2); if (rc) return rc;
-    DevBuf bPrev, bM12, bNm;
-    if ((rc = bPrev.alloc((size_t)tf.cap * 2 * sizeof(float))) || (rc = bM12.alloc((size_t)tf.cap * sizeof(int))) || (rc = bNm.alloc(sizeof(int)))) return rc;
-    float* dPrev = bPrev.as<float>(); int* dM12 = bM12.as<int>(); int* dNm = bNm.as<int>();
-    if (f1->n) ORBX_CUDA(cudaMemcpy(dPrev, prev_matched, (size_t)f1->n * 2 * sizeof(float), cudaMemcpyHostToDevice));
+    // one arena, one upload, one download (see orbm_search_by_projection)
+    const size_t cap = (size_t)std::max(std::max(f1->n, f2->n), 8);
+    size_t off = 0;
+    auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    const size_t oCount = take(8), oKps = take(2 * cap * sizeof(orbx_keypoint)), oDesc = take(2 * cap * 32);
+    const size_t oPrev = take(cap * 2 * sizeof(float));          // in/out: last of the upload, first of the download
+    const size_t upBytes = off;
+    const size_t oNm = take(4), oM12 = take(cap * 4);
+    const size_t downBytes = off - oPrev;
+    const size_t oGS = take(2 * (ORBX_GRID_CELLS + 1) * sizeof(unsigned short)), oGI = take(2 * cap * sizeof(unsigned short));
+    DevBuf arena;
+    if ((rc = arena.alloc(off))) return rc;
+    u8* host = nullptr;
+    if ((rc = orbx_scratch_host((void**)&host, oPrev + downBytes))) return rc;
+    u8* dev = arena.as<u8>();
+    const int counts[2] = {f1->n, f2->n};
+    memcpy(host + oCount, counts, 8);
+    if (f1->n) {
+        memcpy(host + oKps, f1->keys_un, (size_t)f1->n * sizeof(orbx_keypoint));
+        memcpy(host + oDesc, f1->descriptors, (size_t)f1->n * 32);
+        memcpy(host + oPrev, prev_matched, (size_t)f1->n * 2 * sizeof(float));
+    }
+    if (f2->n) {
+        memcpy(host + oKps + cap * sizeof(orbx_keypoint), f2->keys_un, (size_t)f2->n * sizeof(orbx_keypoint));
+        memcpy(host + oDesc + cap * 32, f2->descriptors, (size_t)f2->n * 32);
+    }
+    ORBX_CUDA(cudaMemcpyAsync(dev, host, upBytes, cudaMemcpyHostToDevice, 0));
+    FrameStore fs;
+    fs.kps = reinterpret_cast<orbx_keypoint*>(dev + oKps); fs.desc = dev + oDesc; fs.count = reinterpret_cast<int*>(dev + oCount);
+    fs.gridStart = reinterpret_cast<unsigned short*>(dev + oGS); fs.gridIdx = reinterpret_cast<unsigned short*>(dev + oGI);
+    fs.cap = (int)cap;
     const GridParams gp = orbx_grid_params(f2->min_x, f2->max_x, f2->min_y, f2->max_y);
-    rc = orbx_launch_grid_build(tf.store(), 1, 1, gp, 0); if (rc) return rc;
-    rc = launch_search_init(tf.store(), 0, 1, 1, gp, dPrev, window_size, nnratio, check_orientation, dM12, dNm, nullptr, 0);
+    rc = orbx_launch_grid_build(fs, 1, 1, gp, 0); if (rc) return rc;
+    rc = launch_search_init(fs, 0, 1, 1, gp, reinterpret_cast<float*>(dev + oPrev), window_size, nnratio, check_orientation,
+                            reinterpret_cast<int*>(dev + oM12), reinterpret_cast<int*>(dev + oNm), nullptr, 0);
     if (rc) return rc;
     ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaMemcpyAsync(host + oPrev, dev + oPrev, downBytes, cudaMemcpyDeviceToHost, 0));
+    ORBX_CUDA(cudaStreamSynchronize(0));
     int nm = 0;
-    ORBX_CUDA(cudaMemcpy(&nm, dNm, sizeof(int), cudaMemcpyDeviceToHost));
+    memcpy(&nm, host + oNm, 4);
     if (f1->n) {
-        ORBX_CUDA(cudaMemcpy(matches12, dM12, (size_t)f1->n * sizeof(int), cudaMemcpyDeviceToHost));
-        ORBX_CUDA(cudaMemcpy(prev_matched, dPrev, (size_t)f1->n * 2 * sizeof(float), cudaMemcpyDeviceToHost));
+        memcpy(matches12, host + oM12, (size_t)f1->n * sizeof(int));
+        memcpy(prev_matched, host + oPrev, (size_t)f1->n * 2 * sizeof(float));
     }
     if (nmatches) *nmatches = nm;
     return ORBX_OK;
