@@ -16,6 +16,10 @@ frame ORBmatcher::SearchForInitialization (window 100, nnratio 0.9, orientation 
   cpu_baseline  the CPU oracle (restatement of the reference's CPU path) on the box's host cores,
             bounded sample of the same frames.
 
+`--workload single` is BASELINE configs[0]: the latency of ONE frame per orbx_extract call (host image in, host
+keypoints + descriptors out) next to the reference's ORBextractor.cc on one host thread; `--workload hd|stereo|knn|rgbd`
+are configs[3], [2], [4] and the RGB-D frame front.
+
 `--impl reference` times the reference's CPU path (oracle/_ref when built from the reference's own
 ORBextractor.cc, else the oracle port) with all host threads on the same workload.
 Multi-GPU: one process per GPU (torchrun), frames sharded by rank, no data-path collective
