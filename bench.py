@@ -116,6 +116,29 @@ def bind_to_gpu_numa(local):
     return info
 
 
+_SAVED_STDOUT = None
+
+
+def quiet_stdout():
+    """Libraries (NCCL's version banner under torchrun) write to file descriptor 1; the contract is ONE JSON line on
+    stdout.  Everything written to fd 1 before the line goes to stderr instead; emit() restores the descriptor."""
+    global _SAVED_STDOUT
+    if _SAVED_STDOUT is None:
+        sys.stdout.flush()
+        _SAVED_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    global _SAVED_STDOUT
+    sys.stdout.flush()
+    if _SAVED_STDOUT is not None:
+        os.dup2(_SAVED_STDOUT, 1)
+        os.close(_SAVED_STDOUT)
+        _SAVED_STDOUT = None
+    print(json.dumps(line), flush=True)
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -242,7 +265,7 @@ def run_reference(args):
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 
@@ -345,7 +368,7 @@ def run_knn(args):
                          "frac": value / world / peak, "traffic": None,
                          "how": "nominal 16 POPC/clk/SM x SMs x 1.965 GHz / 5 POPC per compare (carry-save popcount)"}}
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
     dist.destroy_process_group()
 
 
@@ -427,7 +450,7 @@ def run_stereo(args):
                        for k, v in stage_ms.items() if stage_launches[k]},
             "hamming_compares_per_step": int(ncmp), "stereo_matches_per_pair": float((ur >= 0).sum() / P)}
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
     ex.close()
     if world > 1:
         dist.destroy_process_group()
@@ -490,7 +513,7 @@ def run_rgbd(args):
             "gpu_launches": args.steps * (-(-F // args.chunk)) * (PARAMS["nlevels"] - 1 + 8),
             "roofline": {"bound": "hbm", "kernel": "path", "achieved": ab * value / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": ab * value / 1e9 / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_frame": ab}}
-    print(json.dumps(line))
+    emit(line)
     ex.close()
 
 
@@ -582,7 +605,7 @@ def run_single(args):
         line["cpu_baseline"] = {"value": t1 / s1 * 1e6, "unit": "us/frame", "cores": 1, "kind": kind,
                                 "sample": f"{s1} frames, single-threaded per frame as ORB-SLAM2 runs it (extraction only)"}
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
     ex.close(); ex2.close()
 
 
@@ -600,6 +623,7 @@ def main():
     ap.add_argument("--queries", type=int, default=262144, help="knn: queries per step (config 5 names 1M)")
     ap.add_argument("--db-per-gpu", type=int, default=2000000, help="knn: database rows per GPU (config 5: 16M over 8)")
     args = ap.parse_args()
+    quiet_stdout()
     global W, H, PARAMS, METRIC
     match = True
     workload_name = ("configs[1]: batch of 4096 synthetic 640x480 frames, ORBextractor(1000,1.2,8,20,7) + "
@@ -812,7 +836,7 @@ def main():
                                           f"single-thread on {s1} frames: {s1 / t1:.2f} frames/s",
                                 "single_thread_value": s1 / t1}
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
     ex.close()
     if world > 1:
         dist.destroy_process_group()
