@@ -77,8 +77,16 @@ int orbx_get_profile(orbx_handle* h, double* stage_ms, int64_t* stage_launches);
  * arrays of nlevels entries, any pointer may be NULL.  Replaces GetScaleFactors & friends. */
 int orbx_get_tables(const orbx_handle* h, float* scale, float* inv_scale, float* sigma2,
                     float* inv_sigma2, int32_t* features_per_level);
-/* upper bound of keypoints per frame (sum over levels of max(N_l+3, 4*nIni)). */
+/* upper bound of keypoints per frame (sum over levels of max(N_l+3, 4*nIni)) for the shapes seen so far.
+ * The value set at creation covers the handle's maximum shape; a smaller image with a wider aspect ratio
+ * (more quadtree roots per level, src/ORBextractor.cc:543-546) can need more: see orbx_reserve_shape. */
 int orbx_keypoint_capacity(const orbx_handle* h);
+/* Prepare the handle for width x height images (geometry, workspace, tensor maps) ahead of the first
+ * extraction of that shape and return the per-frame keypoint capacity output buffers must have (>= 0), or
+ * a negative orbx_status.  When the shape needs more than the current capacity the result store grows and
+ * the slots stored so far are discarded.  Every extraction entry point does the same on a shape change;
+ * callers that size their buffers once call this first (the host ORBextractor does). */
+int orbx_reserve_shape(orbx_handle* h, int width, int height);
 
 /* ---- ORBextractor::operator() (src/ORBextractor.cc:1043), single frame, host buffers --------
  * image: 8UC1 host pointer.  kps/desc: host buffers with room for `capacity` keypoints

@@ -56,7 +56,7 @@ STAGES = ["resize", "blur", "fast", "octree", "describe", "grid", "search_init",
 EXPORTS = [
     "orbx_set_profiling", "orbx_get_profile",
     "orbx_last_error", "orbx_device_count", "orbx_create", "orbx_destroy", "orbx_sync", "orbx_get_tables",
-    "orbx_keypoint_capacity", "orbx_extract", "orbx_extract_batch", "orbx_extract_batch_to_host", "orbx_download", "orbx_get_level",
+    "orbx_keypoint_capacity", "orbx_reserve_shape", "orbx_extract", "orbx_extract_batch", "orbx_extract_batch_to_host", "orbx_download", "orbx_get_level",
     "orbx_get_candidates", "orbx_search_init_pairs", "orbx_extract_stereo_batch",
     "orbm_descriptor_distance", "orbm_search_for_initialization", "orbm_search_by_projection",
     "orbm_compute_stereo_matches", "orbm_knn2_device", "orbm_knn2_merge_device", "orbm_knn2_set_variant",
@@ -99,6 +99,7 @@ def lib():
         L.orbx_get_profile.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.orbx_get_tables.argtypes = [C.c_void_p] + [C.c_void_p] * 5
         L.orbx_keypoint_capacity.argtypes = [C.c_void_p]
+        L.orbx_reserve_shape.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.orbx_extract.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_void_p, C.c_void_p,
                                    C.c_int, C.POINTER(C.c_int)]
         L.orbx_extract_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int,
@@ -154,8 +155,18 @@ class Extractor:
         self.nlevels = nlevels
         check(lib().orbx_create(C.byref(self.params), max_width, max_height, chunk_frames, result_slots, device,
                                 C.c_void_p(stream) if stream else None, C.byref(self.h)))
-        self.cap = lib().orbx_keypoint_capacity(self.h)
         self.result_slots = result_slots
+
+    @property
+    def cap(self):
+        """per-frame keypoint capacity (grows when a shape with more quadtree roots is reserved / seen)"""
+        return lib().orbx_keypoint_capacity(self.h)
+
+    def reserve_shape(self, width, height):
+        """orbx_reserve_shape: lay out the workspace for this shape, -> keypoint capacity output buffers need."""
+        rc = lib().orbx_reserve_shape(self.h, width, height)
+        check(min(rc, 0))
+        return rc
 
     def close(self):
         if getattr(self, "h", None) and self.h.value:
@@ -191,11 +202,12 @@ class Extractor:
     def extract(self, img: np.ndarray):
         """ORBextractor::operator() on one host image -> (keypoints[KP_DTYPE], descriptors[n,32])."""
         img = np.ascontiguousarray(img, np.uint8)
-        kps = np.zeros(self.cap, KP_DTYPE)
-        desc = np.zeros((self.cap, 32), np.uint8)
+        cap = self.reserve_shape(img.shape[1], img.shape[0]) if img.size else self.cap
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
         n = C.c_int(0)
         check(lib().orbx_extract(self.h, _p(img), img.shape[1], img.shape[0], img.strides[0], _p(kps), _p(desc),
-                                 self.cap, C.byref(n)))
+                                 cap, C.byref(n)))
         return kps[:n.value].copy(), desc[:n.value].copy()
 
     def extract_batch(self, images, nframes=None, width=None, height=None, frame_stride=None, row_stride=None,

@@ -133,13 +133,13 @@ void orbx_prof_mark(orbx_handle* h, int stage)
 // with different source and destination pitches runs at a fraction of the link rate (one DMA
 // descriptor per 1-2 KB row), so contiguous host frames are copied LINEARLY into a device landing
 // zone and re-pitched there by a device-to-device 2-D copy.
-int orbx_copy_frames(orbx_handle* h, uint8_t* dst, long long dstFrameBytes, uint8_t* stage, const uint8_t* src, size_t frame_stride,
+int orbx_copy_frames(orbx_handle* h, uint8_t* dst, long long dstFrameBytes, uint8_t* stage, size_t stageBytes, const uint8_t* src, size_t frame_stride,
                      size_t row_stride, int width, int height, int nf, bool srcOnDevice, cudaStream_t st, long long* frameStrideOut)
 {
     const cudaMemcpyKind kind = srcOnDevice ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
     if (frame_stride == row_stride * (size_t)height) {
         // row-contiguous frames: one tall image of nf*height rows
-        if (!srcOnDevice && (int)row_stride != h->l0Pitch && (size_t)nf * frame_stride <= (size_t)h->chunkFrames * h->l0FrameBytes) {
+        if (!srcOnDevice && (int)row_stride != h->l0Pitch && (size_t)nf * frame_stride <= stageBytes) {     // stageBytes: what the caller reserved at `stage`
             ORBX_CUDA(cudaMemcpyAsync(stage, src, (size_t)nf * frame_stride, cudaMemcpyHostToDevice, st));
             ORBX_CUDA(cudaMemcpy2DAsync(dst, h->l0Pitch, stage, row_stride, width, (size_t)height * nf, cudaMemcpyDeviceToDevice, st));
         } else
@@ -193,6 +193,8 @@ int orbx_device_count(void)
     return n;
 }
 
+static int create_impl(orbx_handle* h, const orbx_params* params, int result_slots, void* stream);
+
 int orbx_create(const orbx_params* params, int max_width, int max_height, int chunk_frames,
                 int result_slots, int device, void* stream, orbx_handle** out)
 {
@@ -219,7 +221,7 @@ int orbx_create(const orbx_params* params, int max_width, int max_height, int ch
     h->curW = h->curH = 0;
     h->dCells = nullptr; h->dCoef = nullptr; h->dBlurTiles = nullptr; h->dKpMap = nullptr; h->nBlurTiles = 0;
     h->dLevel0 = h->dStageLin = h->dRaw = h->dBlur = nullptr;
-    h->dCand = h->dKeysA = h->dKeysB = nullptr; h->dCellSeg = nullptr; h->dLevelCandCount = nullptr;
+    h->dCand = h->dKeysA = h->dKeysB = nullptr; h->dCellSeg = nullptr;
     h->dLevelKps = nullptr; h->dLevelKpCount = nullptr; h->dStatus = nullptr;
     h->dKpsUn = nullptr; h->storeUndistorted = false; h->dFrontStage = nullptr; h->frontStageBytes = 0; h->boundsValid = false; h->bounds[0] = h->bounds[1] = h->bounds[2] = h->bounds[3] = 0.f;
     h->dKps = nullptr; h->dDesc = nullptr; h->dCount = nullptr; h->dSlotLevelCount = nullptr;
@@ -231,6 +233,19 @@ int orbx_create(const orbx_params* params, int max_width, int max_height, int ch
     h->lastChunkFrames = 0;
     h->profiling = false; h->evUsed = 0;
     for (int s = 0; s < ORBX_NSTAGES; ++s) { h->stageMs[s] = 0.0; h->stageLaunches[s] = 0; }
+    h->stream = h->copyStream = h->d2hStream = nullptr; h->ownStream = false; h->evDone = nullptr;
+    for (int b = 0; b < ORBX_L0_BUFS; ++b) { h->evCopied[b] = h->evFree[b] = nullptr; h->evFreeValid[b] = false; }
+    h->kpCap = 0;
+    memset(&h->geom, 0, sizeof(h->geom));
+    const int rc = create_impl(h, params, result_slots, stream);
+    if (rc != ORBX_OK) { orbx_destroy(h); return rc; }       // nothing of a half-built handle survives
+    *out = h;
+    return ORBX_OK;
+}
+
+static int create_impl(orbx_handle* h, const orbx_params* params, int result_slots, void* stream)
+{
+    const int max_width = h->maxW, max_height = h->maxH;
     if (stream) { h->stream = (cudaStream_t)stream; h->ownStream = false; }
     else { ORBX_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)); h->ownStream = true; }
     ORBX_CUDA(cudaStreamCreateWithFlags(&h->copyStream, cudaStreamNonBlocking));
@@ -262,17 +277,47 @@ int orbx_create(const orbx_params* params, int max_width, int max_height, int ch
     ORBX_CUDA(cudaMalloc((void**)&h->dStatus, sizeof(int)));
     ORBX_CUDA(cudaMemset(h->dCount, 0, R * sizeof(int)));
     ORBX_CUDA(cudaMemset(h->dStatus, 0, sizeof(int)));
-    *out = h;
     return ORBX_OK;
+}
+
+} // extern "C"
+
+// Everything sized by the per-frame keypoint capacity is released and the two extractor outputs re-allocated;
+// the matcher / frame-front buffers come back lazily (orbx_ensure_match_buffers, orbx_frames_rgbd).
+int orbx_grow_result_store(orbx_handle* h, int newCap)
+{
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    void** ptrs[] = {(void**)&h->dKps, (void**)&h->dDesc, (void**)&h->dKpsUn, (void**)&h->dGridStart, (void**)&h->dGridIdx, (void**)&h->dMatches12,
+                     (void**)&h->dNMatches, (void**)&h->dNCompares, (void**)&h->dURight, (void**)&h->dDepth, (void**)&h->dMatchScratch};
+    for (void** p : ptrs) { if (*p) cudaFree(*p); *p = nullptr; }
+    h->matchScratchPerPair = 0;
+    h->kpCap = 0;
+    const size_t R = (size_t)h->resultSlots;
+    ORBX_CUDA(cudaMalloc((void**)&h->dKps, R * newCap * sizeof(orbx_keypoint)));
+    ORBX_CUDA(cudaMalloc((void**)&h->dDesc, R * newCap * 32));
+    ORBX_CUDA(cudaMemsetAsync(h->dCount, 0, R * sizeof(int), h->stream));
+    h->kpCap = newCap;
+    return ORBX_OK;
+}
+
+extern "C" {
+
+int orbx_reserve_shape(orbx_handle* h, int width, int height)
+{
+    if (!h) { orbx_set_error("null handle"); return ORBX_E_INVALID; }
+    if (width < 64 || height < 64) { orbx_set_error("image smaller than 64x64 is outside the extractor's domain"); return ORBX_E_INVALID; }
+    ORBX_CUDA(cudaSetDevice(h->device));
+    const int rc = orbx_setup_shape(h, width, height);
+    return rc ? rc : h->kpCap;
 }
 
 int orbx_destroy(orbx_handle* h)
 {
     if (!h) return ORBX_OK;
     cudaSetDevice(h->device);
-    cudaStreamSynchronize(h->stream);
+    if (h->stream) cudaStreamSynchronize(h->stream);
     void* ptrs[] = {h->dCells, h->dCoef, h->dBlurTiles, h->dKpMap, h->dKpsUn, h->dFrontStage, h->dLevel0, h->dStageLin, h->dRaw, h->dBlur, h->dCand, h->dKeysA,
-                    h->dKeysB, h->dCellSeg, h->dLevelCandCount, h->dLevelKps, h->dLevelKpCount, h->dStatus, h->dKps,
+                    h->dKeysB, h->dCellSeg, h->dLevelKps, h->dLevelKpCount, h->dStatus, h->dKps,
                     h->dDesc, h->dCount, h->dSlotLevelCount, h->dGridStart, h->dGridIdx, h->dMatches12, h->dNMatches,
                     h->dNCompares, h->dURight, h->dDepth, h->dMatchScratch};
     for (void* p : ptrs) if (p) cudaFree(p);
@@ -282,11 +327,11 @@ int orbx_destroy(orbx_handle* h)
     for (cudaEvent_t e : h->sideEvents) cudaEventDestroy(e);
     for (cudaEvent_t e : h->levelEvents) cudaEventDestroy(e);
     for (cudaEvent_t e : h->evPool) cudaEventDestroy(e);
-    for (int b = 0; b < ORBX_L0_BUFS; ++b) { cudaEventDestroy(h->evCopied[b]); cudaEventDestroy(h->evFree[b]); }
-    cudaStreamDestroy(h->copyStream);
-    cudaStreamDestroy(h->d2hStream);
-    cudaEventDestroy(h->evDone);
-    if (h->ownStream) cudaStreamDestroy(h->stream);
+    for (int b = 0; b < ORBX_L0_BUFS; ++b) { if (h->evCopied[b]) cudaEventDestroy(h->evCopied[b]); if (h->evFree[b]) cudaEventDestroy(h->evFree[b]); }
+    if (h->copyStream) cudaStreamDestroy(h->copyStream);
+    if (h->d2hStream) cudaStreamDestroy(h->d2hStream);
+    if (h->evDone) cudaEventDestroy(h->evDone);
+    if (h->ownStream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return ORBX_OK;
 }
@@ -386,7 +431,7 @@ static int batch_to_host_impl(orbx_handle* h, const uint8_t* images, size_t fram
             uint8_t* dstBuf = h->dLevel0 + (size_t)b * h->chunkFrames * h->l0FrameBytes;
             if (h->evFreeValid[b]) ORBX_CUDA(cudaStreamWaitEvent(h->copyStream, h->evFree[b], 0));
             mark(h->copyStream);
-            rc = orbx_copy_frames(h, dstBuf, h->l0FrameBytes, h->dStageLin + (size_t)b * h->chunkFrames * h->l0FrameBytes, src, frame_stride,
+            rc = orbx_copy_frames(h, dstBuf, h->l0FrameBytes, h->dStageLin + (size_t)b * h->chunkFrames * h->l0FrameBytes, (size_t)h->chunkFrames * h->l0FrameBytes, src, frame_stride,
                                   row_stride, width, height, nf, images_on_device != 0, h->copyStream, &l0.frameStride);
             if (rc) return rc;
             ORBX_CUDA(cudaEventRecord(h->evCopied[b], h->copyStream));
@@ -639,11 +684,10 @@ int orbx_get_candidates(orbx_handle* h, int frame, int level, float* xyr, int ca
     const LevelGeom& L = g.L[level];
     std::vector<int2> seg(L.nCells);
     ORBX_CUDA(cudaMemcpyAsync(seg.data(), h->dCellSeg + (size_t)frame * g.ncells + L.cellBeg, L.nCells * sizeof(int2), cudaMemcpyDeviceToHost, h->stream));
-    unsigned cnt = 0;
-    ORBX_CUDA(cudaMemcpyAsync(&cnt, h->dLevelCandCount + frame * g.nlevels + level, sizeof(unsigned), cudaMemcpyDeviceToHost, h->stream));
     ORBX_CUDA(cudaStreamSynchronize(h->stream));
-    std::vector<uint32_t> c(std::max<unsigned>(cnt, 1));
-    if (cnt) ORBX_CUDA(cudaMemcpy(c.data(), h->dCand + (size_t)frame * g.candTotal + L.candOff, cnt * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    // the level's whole candidate region: every cell owns a fixed segment of it (debug / test entry point)
+    std::vector<uint32_t> c(std::max(L.candCap, 1));
+    if (L.candCap) ORBX_CUDA(cudaMemcpy(c.data(), h->dCand + (size_t)frame * g.candTotal + L.candOff, (size_t)L.candCap * sizeof(uint32_t), cudaMemcpyDeviceToHost));
     int k = 0;
     for (int ci = 0; ci < L.nCells; ++ci)
         for (int i = 0; i < seg[ci].y; ++i, ++k) {

@@ -303,9 +303,14 @@ blur7_kernel(Geom g, Level0 l0, const u8* __restrict__ rawBase, u8* __restrict__
 
 __device__ __forceinline__ uint32_t vmaxu2(uint32_t a, uint32_t b) { return __vmaxu2(a, b); }
 __device__ __forceinline__ uint32_t vminu2(uint32_t a, uint32_t b) { return __vminu2(a, b); }
+// three-input packed min / max: one VIMNMX3.U16x2 each on sm_100a
+__device__ __forceinline__ uint32_t vmax3u2(uint32_t a, uint32_t b, uint32_t c) { return __vimax3_u16x2(a, b, c); }
+__device__ __forceinline__ uint32_t vmin3u2(uint32_t a, uint32_t b, uint32_t c) { return __vimin3_u16x2(a, b, c); }
 
 // S for the pixel at p (row pitch tp): max over the 16 arcs of 9 contiguous ring pixels of
 // max(min(v - r), min(r - v)) = max(v - min_arcs(max r), max_arcs(min r) - v).
+// Ring elements are packed two per register (u16x2: elements 2j, 2j+1); window maxima / minima grow
+// 2 -> 6 -> 9 elements with three-input operations.
 __device__ __forceinline__ int fast_strength(const u8* p, int tp)
 {
     const int v = p[0];
@@ -318,24 +323,27 @@ __device__ __forceinline__ int fast_strength(const u8* p, int tp)
     P[5] = p[-2 * tp - 2] | (p[-tp - 3] << 16);
     P[6] = p[-3]          | (p[tp - 3] << 16);
     P[7] = p[2 * tp - 2]  | (p[3 * tp - 1] << 16);
-    uint32_t mx[8], mn[8];
+    uint32_t mx2[8], mn2[8];                      // windows of 2 starting at elements 2j | 2j+1
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         const uint32_t q = __byte_perm(P[j], P[(j + 1) & 7], 0x5432);   // elements 2j+1, 2j+2
-        mx[j] = vmaxu2(P[j], q);
-        mn[j] = vminu2(P[j], q);
+        mx2[j] = vmaxu2(P[j], q);
+        mn2[j] = vminu2(P[j], q);
     }
-    uint32_t mx4[8], mn4[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { mx4[j] = vmaxu2(mx[j], mx[(j + 1) & 7]); mn4[j] = vminu2(mn[j], mn[(j + 1) & 7]); }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { mx[j] = vmaxu2(mx4[j], mx4[(j + 2) & 7]); mn[j] = vminu2(mn4[j], mn4[(j + 2) & 7]); }
-    uint32_t lo = 0xffffffffu, hi = 0;
+    uint32_t mx6[8], mn6[8];                      // windows of 6
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-        lo = vminu2(lo, vmaxu2(mx[j], P[(j + 4) & 7]));   // min over arcs of (max over arc)
-        hi = vmaxu2(hi, vminu2(mn[j], P[(j + 4) & 7]));   // max over arcs of (min over arc)
+        mx6[j] = vmax3u2(mx2[j], mx2[(j + 1) & 7], mx2[(j + 2) & 7]);
+        mn6[j] = vmin3u2(mn2[j], mn2[(j + 1) & 7], mn2[(j + 2) & 7]);
     }
+    uint32_t mx9[8], mn9[8];                      // windows of 9: six + two + one
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        mx9[j] = vmax3u2(mx6[j], mx2[(j + 3) & 7], P[(j + 4) & 7]);
+        mn9[j] = vmin3u2(mn6[j], mn2[(j + 3) & 7], P[(j + 4) & 7]);
+    }
+    const uint32_t lo = vmin3u2(vmin3u2(mx9[0], mx9[1], mx9[2]), vmin3u2(mx9[3], mx9[4], mx9[5]), vminu2(mx9[6], mx9[7]));   // min over arcs of (max over arc)
+    const uint32_t hi = vmax3u2(vmax3u2(mn9[0], mn9[1], mn9[2]), vmax3u2(mn9[3], mn9[4], mn9[5]), vmaxu2(mn9[6], mn9[7]));   // max over arcs of (min over arc)
     const int minArcMax = min(lo & 0xffff, lo >> 16);
     const int maxArcMin = max(hi & 0xffff, hi >> 16);
     return max(v - minArcMax, maxArcMin - v);
@@ -344,7 +352,7 @@ __device__ __forceinline__ int fast_strength(const u8* p, int tp)
 __global__ void __launch_bounds__(FAST_WARPS * 32)
 fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* __restrict__ rawBase,
                   int nframes, int minThArg, int iniThArg, uint32_t* __restrict__ cand,
-                  int2* __restrict__ cellSeg, unsigned* __restrict__ levelCandCount,
+                  int2* __restrict__ cellSeg,
                   int tilePitch, int scorePitch, int warpSmem, int cellBeg, int cellEnd)
 {
     extern __shared__ __align__(16) u8 smem[];
@@ -371,33 +379,30 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
     int nOut = 0;
     unsigned base = 0;
     if (dw > 0 && dh > 0) {
-        // ---- load the sub-image so that its column 0 lands on byte 0 of a tile row: two aligned
-        // 32-bit loads + funnel shift per word; lanes = (row, word) --------------------------------
+        // ---- load the sub-image so that its column 0 lands on byte 0 of a tile row: two aligned 32-bit loads +
+        // funnel shift per word.  A cell starts at an arbitrary byte (x0 = 16 + j*wCell) and a u8 tensor-map box must
+        // start on a 16-byte boundary (scripts/probes/probe_tma_u8.cu: any other inner coordinate is an illegal
+        // instruction), so TMA cannot deliver the re-aligned tile.  Lanes = (row of a group, word column) with the
+        // split done once; the loop only advances two pointers, four row groups (8 loads per lane) in flight. -----
         const int tw = tilePitch >> 2;
         {
             const int xa = c.x0 & ~3, sh8 = 8 * (c.x0 - xa);
-            const int nw = (cw + 3) >> 2;
-            // (row, word) pairs flattened over the lanes; row = idx / nw by a 16-bit reciprocal (exact for idx < 3855)
-            const uint32_t inv = (65536u + nw - 1) / nw;
-            const u8* g0 = img + (long long)c.y0 * pitch + xa;
-            const int total = nw * ch;
-            // four words per lane in flight: the loads of a batch are all issued before the first store
-            for (int i0 = lane; i0 < total; i0 += 128) {
+            const int nw = (cw + 3) >> 2;                               // words per tile row (<= 17)
+            const int rpg = nw <= 8 ? 4 : (nw <= 10 ? 3 : (nw <= 16 ? 2 : 1));      // rows per group of 32 lanes
+            const int lr = lane / nw, lw = lane - lr * nw;
+            const bool act = lr < rpg;
+            const uint32_t* q = reinterpret_cast<const uint32_t*>(img + (long long)(c.y0 + lr) * pitch + xa) + lw;
+            uint32_t* d = reinterpret_cast<uint32_t*>(tile) + lr * tw + lw;
+            const int qstep = rpg * (pitch >> 2), dstep = rpg * tw;
+            for (int y0 = 0; y0 < ch; y0 += 4 * rpg) {
                 uint32_t lo[4], hi[4];
-                int dst[4];
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const int idx = i0 + 32 * k;
-                    if (idx < total) {
-                        const int y = (int)((idx * inv) >> 16), lw = idx - y * nw;
-                        const uint32_t* q = reinterpret_cast<const uint32_t*>(g0 + y * pitch) + lw;
-                        lo[k] = __ldg(q); hi[k] = __ldg(q + 1);
-                        dst[k] = y * tw + lw;
-                    }
-                }
 #pragma unroll
                 for (int k = 0; k < 4; ++k)
-                    if (i0 + 32 * k < total) reinterpret_cast<uint32_t*>(tile)[dst[k]] = __funnelshift_r(lo[k], hi[k], sh8);
+                    if (act && y0 + k * rpg + lr < ch) { lo[k] = __ldg(q + k * qstep); hi[k] = __ldg(q + k * qstep + 1); }
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (act && y0 + k * rpg + lr < ch) d[k * dstep] = __funnelshift_r(lo[k], hi[k], sh8);
+                q += 4 * qstep; d += 4 * dstep;
             }
         }
         // zero the score tile ((dh+2) x scorePitch)
@@ -492,8 +497,8 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
                     const uint32_t a1 = p[2 * tp + 2] | (p[tp + 3] << 16), b1 = p[-2 * tp - 2] | (p[-tp - 3] << 16);
                     const uint32_t a2 = p[3] | (p[-tp + 3] << 16), b2 = p[-3] | (p[tp - 3] << 16);
                     const uint32_t a3 = p[-2 * tp + 2] | (p[-3 * tp + 1] << 16), b3 = p[2 * tp - 2] | (p[3 * tp - 1] << 16);
-                    const uint32_t mx = vminu2(vminu2(vmaxu2(a0, b0), vmaxu2(a1, b1)), vminu2(vmaxu2(a2, b2), vmaxu2(a3, b3)));
-                    const uint32_t mn = vmaxu2(vmaxu2(vminu2(a0, b0), vminu2(a1, b1)), vmaxu2(vminu2(a2, b2), vminu2(a3, b3)));
+                    const uint32_t mx = vminu2(vmin3u2(vmaxu2(a0, b0), vmaxu2(a1, b1), vmaxu2(a2, b2)), vmaxu2(a3, b3));
+                    const uint32_t mn = vmaxu2(vmax3u2(vminu2(a0, b0), vminu2(a1, b1), vminu2(a2, b2)), vminu2(a3, b3));
                     const int A = min(mx & 0xffff, mx >> 16), B = max(mn & 0xffff, mn >> 16);
                     keep = max(A - v, v - B) > minTh;
                 }
@@ -548,8 +553,9 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
         // ---- stage 4: emit, order = row-major --------------------------------------------------
         nOut = n3;
         if (nOut > 0) {
-            if (lane == 0) base = atomicAdd(&levelCandCount[frame * g.nlevels + c.level], (unsigned)nOut);
-            base = __shfl_sync(FULL, base, 0);
+            // every cell owns a fixed segment of its level's candidate region (cellCap entries: no two NMS survivors are
+            // adjacent, so at most ceil(dw/2)*ceil(dh/2) of them exist): no counter, no atomic, no round trip
+            base = (unsigned)(ci - L.cellBeg) * (unsigned)L.cellCap;
             uint32_t* out = cand + (size_t)frame * g.candTotal + L.candOff + base;
             int pos = 0;
             for (int i0 = 0; i0 < n3; i0 += 32) {
@@ -1011,23 +1017,29 @@ static void linear_coeffs(int sn, int dn, std::vector<int2>& out)
     }
 }
 
+// Geometry, tables and workspace of one image shape.  Everything is computed and validated in locals first; the
+// handle forgets its current shape before the first buffer is touched and learns the new one only after every
+// allocation and upload succeeded, so a failed call can never leave a shape whose buffers are stale.
 int orbx_setup_shape(orbx_handle* h, int w, int hgt)
 {
     if (h->curW == w && h->curH == hgt) return ORBX_OK;
     if (w > h->maxW || hgt > h->maxH) { orbx_set_error("image %dx%d exceeds handle maximum %dx%d", w, hgt, h->maxW, h->maxH); return ORBX_E_CAPACITY; }
+    if (w > 4000 || hgt > 4000) { orbx_set_error("image larger than 4000 px per side is unsupported"); return ORBX_E_INVALID; }
     const int nl = h->params.nlevels;
-    Geom& g = h->geom;
+    Geom g;
     memset(&g, 0, sizeof(g));
     g.nlevels = nl;
     std::vector<Cell> cells;
     std::vector<int2> coef;
     std::vector<int> tiles, kpMap;
+    int blurTileBeg[ORBX_MAX_LEVELS + 1] = {0};
     long long off = 0;
     int candOff = 0, kpOff = 0;
     for (int l = 0; l < nl; ++l) {
         LevelGeom& L = g.L[l];
         L.w = cv_roundf((float)w * h->invScale[l]);
         L.h = cv_roundf((float)hgt * h->invScale[l]);
+        if (L.w < 12 || L.h < 1) { orbx_set_error("level %d of a %dx%d image is %dx%d: too small for the pyramid kernels", l, w, hgt, L.w, L.h); return ORBX_E_INVALID; }
         L.pitch = (L.w + 15) & ~15;
         L.off = (int)off;
         off += (long long)L.pitch * L.h;
@@ -1044,10 +1056,10 @@ int orbx_setup_shape(orbx_handle* h, int w, int hgt)
             const int g7 = ((L.h + nstrips - 1) / nstrips + 6 + 6) / 7;        // 7-row groups covering rows + 6 halo rows
             L.blurTH = std::max(1, 7 * g7 - 6);
         }
-        h->blurTileBeg[l] = (int)tiles.size();
+        blurTileBeg[l] = (int)tiles.size();
         for (int ty = 0; ty * L.blurTH < L.h; ++ty)
             for (int tx = 0; tx * BL_TW < L.w; ++tx) tiles.push_back((l << 24) | (ty << 12) | tx);
-        h->blurTileBeg[l + 1] = (int)tiles.size();
+        blurTileBeg[l + 1] = (int)tiles.size();
         // FAST cell grid (src/ORBextractor.cc:773-806)
         const int minBX = 16, minBY = 16, maxBX = L.w - 16, maxBY = L.h - 16;
         L.winW = maxBX - minBX; L.winH = maxBY - minBY;
@@ -1078,7 +1090,7 @@ int orbx_setup_shape(orbx_handle* h, int w, int hgt)
                     cells.push_back(c);
                     g.cwMax = std::max<int>(g.cwMax, c.cw); g.chMax = std::max<int>(g.chMax, c.ch);
                     const int dw = c.cw - 6, dh = c.ch - 6;
-                    if (dw > 0 && dh > 0) cap += ((dw + 1) / 2) * ((dh + 1) / 2);
+                    if (dw > 0 && dh > 0) cap = std::max(cap, ((dw + 1) / 2) * ((dh + 1) / 2));
                 }
             }
             // quadtree roots (src/ORBextractor.cc:543-546)
@@ -1086,24 +1098,30 @@ int orbx_setup_shape(orbx_handle* h, int w, int hgt)
             L.hX = L.nIni > 0 ? (float)(maxBX - minBX) / L.nIni : 0.f;
         }
         L.nCells = (int)cells.size() - L.cellBeg;
-        L.candCap = (cap + 31) & ~31;
+        L.cellCap = cap;                                        // candidate segment per cell (the largest cell's bound)
+        L.candCap = (L.nCells * cap + 31) & ~31;
         candOff += L.candCap;
         L.kpOff = kpOff;
         L.kpCap = std::max(L.N + 3, 4 * std::max(L.nIni, 1)) + 1;
         for (int k = 0; k < L.kpCap; ++k) kpMap.push_back(l);
         kpOff += L.kpCap;
     }
-    if (w > 4000 || hgt > 4000) { orbx_set_error("image larger than 4000 px per side is unsupported"); return ORBX_E_INVALID; }
     g.ncells = (int)cells.size();
     g.candTotal = candOff;
     g.kpTotal = kpOff;
     g.pyrFrameBytes = off;
     if (g.cwMax < 7) g.cwMax = 7;
     if (g.chMax < 7) g.chMax = 7;
-    // (re)allocate shape-dependent device buffers
+    // ---- from here on the handle is touched: forget the current shape first -----------------------------------
     cudaStream_t st = h->stream;
     ORBX_CUDA(cudaStreamSynchronize(st));
     orbx_drop_graph(h);
+    h->curW = h->curH = 0;
+    h->lastChunkFrames = 0;
+    // the per-frame keypoint capacity was sized at creation for the maximum shape; a smaller image with a wider
+    // aspect ratio has more quadtree roots per level (nIni) and may need more: the result store grows (stored slots
+    // are discarded; orbx_keypoint_capacity / orbx_reserve_shape report the new value)
+    if (g.kpTotal > h->kpCap) { const int rc = orbx_grow_result_store(h, (g.kpTotal + 7) & ~7); if (rc) return rc; }
     auto re = [&](void** p, size_t bytes) -> cudaError_t { if (*p) cudaFree(*p); *p = nullptr; return cudaMalloc(p, std::max<size_t>(bytes, 256)); };
     const size_t C = (size_t)h->chunkFrames;
     ORBX_CUDA(re((void**)&h->dCells, cells.size() * sizeof(Cell)));
@@ -1111,6 +1129,7 @@ int orbx_setup_shape(orbx_handle* h, int w, int hgt)
     ORBX_CUDA(re((void**)&h->dBlurTiles, tiles.size() * sizeof(int)));
     ORBX_CUDA(re((void**)&h->dKpMap, kpMap.size() * sizeof(int)));
     h->nBlurTiles = (int)tiles.size();
+    memcpy(h->blurTileBeg, blurTileBeg, sizeof(blurTileBeg));
     h->l0Pitch = (w + 15) & ~15;
     h->l0FrameBytes = (((long long)h->l0Pitch * hgt) + 255) & ~255LL;
     ORBX_CUDA(re((void**)&h->dLevel0, ORBX_L0_BUFS * C * h->l0FrameBytes));
@@ -1122,17 +1141,15 @@ int orbx_setup_shape(orbx_handle* h, int w, int hgt)
     ORBX_CUDA(re((void**)&h->dKeysA, C * g.candTotal * sizeof(uint32_t)));
     ORBX_CUDA(re((void**)&h->dKeysB, C * g.candTotal * sizeof(uint32_t)));
     ORBX_CUDA(re((void**)&h->dCellSeg, C * g.ncells * sizeof(int2)));
-    ORBX_CUDA(re((void**)&h->dLevelCandCount, C * nl * sizeof(unsigned)));
     ORBX_CUDA(re((void**)&h->dLevelKps, C * g.kpTotal * sizeof(uint32_t)));
     ORBX_CUDA(re((void**)&h->dLevelKpCount, C * nl * sizeof(int)));
-    if (g.kpTotal > h->kpCap) { orbx_set_error("internal: keypoint capacity %d < %d", h->kpCap, g.kpTotal); return ORBX_E_CAPACITY; }
     ORBX_CUDA(cudaMemcpyAsync(h->dCells, cells.data(), cells.size() * sizeof(Cell), cudaMemcpyHostToDevice, st));
     if (!coef.empty()) ORBX_CUDA(cudaMemcpyAsync(h->dCoef, coef.data(), coef.size() * sizeof(int2), cudaMemcpyHostToDevice, st));
     ORBX_CUDA(cudaMemcpyAsync(h->dBlurTiles, tiles.data(), tiles.size() * sizeof(int), cudaMemcpyHostToDevice, st));
     ORBX_CUDA(cudaMemcpyAsync(h->dKpMap, kpMap.data(), kpMap.size() * sizeof(int), cudaMemcpyHostToDevice, st));
     ORBX_CUDA(cudaStreamSynchronize(st));
+    h->geom = g;
     h->curW = w; h->curH = hgt;
-    h->lastChunkFrames = 0;
     return ORBX_OK;
 }
 
@@ -1192,7 +1209,7 @@ static int run_chunk_impl(orbx_handle* h, Level0 l0, int nframes, int firstSlot,
         }
         while ((int)h->levelEvents.size() < nl) { cudaEvent_t e; ORBX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->levelEvents.push_back(e); }
     }
-    // FAST / quadtree launch geometry (same for every level)
+    // FAST launch geometry (same for every level)
     const int tilePitch = (g.cwMax + 9 + 7) & ~7;          // rows 8-byte aligned; the packed pre-test reads whole words up to byte cw+8
     const int scorePitch = (g.cwMax - 4 + 3) & ~3;
     const int maskBytes = 8 * (g.chMax - 6);                // one 64-bit pre-test mask per detectable row
@@ -1203,7 +1220,7 @@ static int run_chunk_impl(orbx_handle* h, Level0 l0, int nframes, int firstSlot,
     if (fastSmem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(fast_cells_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, fastSmem));
     auto launch_fast = [&](cudaStream_t s, int cellBeg, int cellEnd) {
         fast_cells_kernel<<<dim3((cellEnd - cellBeg + FAST_WARPS - 1) / FAST_WARPS, nframes), FAST_WARPS * 32, fastSmem, s>>>(
-            g, h->dCells, l0, h->dRaw, nframes, h->params.min_th_fast, h->params.ini_th_fast, h->dCand, h->dCellSeg, h->dLevelCandCount,
+            g, h->dCells, l0, h->dRaw, nframes, h->params.min_th_fast, h->params.ini_th_fast, h->dCand, h->dCellSeg,
             tilePitch, scorePitch, warpSmem, cellBeg, cellEnd);
     };
     int NC = 8, cellsMax = 1, candMax = 1;
@@ -1258,7 +1275,6 @@ static int run_chunk_impl(orbx_handle* h, Level0 l0, int nframes, int firstSlot,
     };
     orbx_prof_mark(h, -1);
     if (forked) {
-        ORBX_CUDA(cudaMemsetAsync(h->dLevelCandCount, 0, (size_t)nframes * nl * sizeof(unsigned), st));
         rc = fork_level(0);
         if (rc) return rc;
     }
@@ -1301,7 +1317,6 @@ static int run_chunk_impl(orbx_handle* h, Level0 l0, int nframes, int firstSlot,
         ORBX_COUNT(h, ORBX_STAGE_BLUR, 1);
         orbx_prof_mark(h, ORBX_STAGE_BLUR);
         // K2: FAST
-        ORBX_CUDA(cudaMemsetAsync(h->dLevelCandCount, 0, (size_t)nframes * nl * sizeof(unsigned), st));
         launch_fast(st, 0, g.ncells);
         ORBX_COUNT(h, ORBX_STAGE_FAST, 1);
         orbx_prof_mark(h, ORBX_STAGE_FAST);

@@ -35,6 +35,7 @@ struct LevelGeom {
     int off;                // byte offset of the level inside one frame's pyramid block
     int cellBeg, nCells;    // range of this level's FAST cells in the cell table
     int candOff, candCap;   // candidate region (entries) inside one frame's candidate block
+    int cellCap;            // ... of which every FAST cell owns a fixed segment of cellCap entries
     int kpOff, kpCap;       // culled-keypoint region inside one frame's keypoint block
     int N;                  // mnFeaturesPerLevel[level]
     int nIni;               // quadtree roots
@@ -111,7 +112,6 @@ struct orbx_handle {
     uint32_t* dKeysA;   // quadtree key buffers
     uint32_t* dKeysB;
     int2* dCellSeg;
-    unsigned* dLevelCandCount;
     uint32_t* dLevelKps;    // culled keypoints per level (packed)
     int* dLevelKpCount;
     int* dStatus;           // device-side error flags
@@ -175,12 +175,13 @@ int orbx_scratch_alloc(void** p, size_t bytes);
 void orbx_scratch_free(void* p);
 int orbx_scratch_host(void** p, size_t bytes);     // this thread's pinned staging buffer (grown on demand, kept)
 int orbx_setup_shape(orbx_handle* h, int w, int hgt);
+int orbx_grow_result_store(orbx_handle* h, int newCap);   // orbx_api.cu: re-allocates everything sized by kpCap (stored slots are discarded)
 void orbx_drop_graph(orbx_handle* h);      // the workspace moved: the captured single-frame graph is stale
 int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot);
 int orbx_run_frame_forked(orbx_handle* h, Level0 l0, int firstSlot);   // one frame, per-level fork/join (latency form)
 
 // orbx_api.cu: frames [nf][height][row_stride] -> pitched workspace frames, on `st`
-int orbx_copy_frames(orbx_handle* h, uint8_t* dst, long long dstFrameBytes, uint8_t* stage, const uint8_t* src, size_t frame_stride,
+int orbx_copy_frames(orbx_handle* h, uint8_t* dst, long long dstFrameBytes, uint8_t* stage, size_t stageBytes, const uint8_t* src, size_t frame_stride,
                      size_t row_stride, int width, int height, int nf, bool srcOnDevice, cudaStream_t st, long long* frameStrideOut);
 
 // orbx_match.cu

@@ -1426,10 +1426,10 @@ int orbx_extract_stereo_batch(orbx_handle* h, const uint8_t* left, const uint8_t
             if (h->evFreeValid[b]) ORBX_CUDA(cudaStreamWaitEvent(h->copyStream, h->evFree[b], 0));
             uint8_t* sl = h->dStageLin + (size_t)b * h->chunkFrames * h->l0FrameBytes;
             uint8_t* sr = sl + (size_t)pairsPerChunk * h->l0FrameBytes;
-            rc = orbx_copy_frames(h, dl, h->l0FrameBytes, sl, left + (size_t)p0 * frame_stride, frame_stride, row_stride, width, height, np,
+            rc = orbx_copy_frames(h, dl, h->l0FrameBytes, sl, (size_t)pairsPerChunk * h->l0FrameBytes, left + (size_t)p0 * frame_stride, frame_stride, row_stride, width, height, np,
                                   images_on_device != 0, h->copyStream, &l0.frameStride);
             if (rc) return rc;
-            rc = orbx_copy_frames(h, dr, h->l0FrameBytes, sr, right + (size_t)p0 * frame_stride, frame_stride, row_stride, width, height, np,
+            rc = orbx_copy_frames(h, dr, h->l0FrameBytes, sr, (size_t)pairsPerChunk * h->l0FrameBytes, right + (size_t)p0 * frame_stride, frame_stride, row_stride, width, height, np,
                                   images_on_device != 0, h->copyStream, &l0.frameStride);
             if (rc) return rc;
             ORBX_CUDA(cudaEventRecord(h->evCopied[b], h->copyStream));

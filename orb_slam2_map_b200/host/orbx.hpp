@@ -91,6 +91,12 @@ public:
                     std::vector<uint8_t>& descriptors)
     {
         if (image.empty()) return;                        // src/ORBextractor.cc:1046-1047
+        if (image.cols != shapeW_ || image.rows != shapeH_) {
+            // a new shape: the handle lays out its workspace and reports the capacity this shape needs
+            const int cap = orbx_reserve_shape(h_, image.cols, image.rows);
+            check(cap < 0 ? cap : ORBX_OK, "ORBextractor::operator()");
+            cap_ = cap; shapeW_ = image.cols; shapeH_ = image.rows;
+        }
         kbuf_.resize(cap_); dbuf_.resize((size_t)cap_ * 32);
         int n = 0;
         check(orbx_extract(h_, image.data, image.cols, image.rows, image.step,
@@ -139,6 +145,11 @@ public:
         (void)_mask;
         if (_image.empty()) return;
         cv::Mat image = _image.getMat();
+        if (image.cols != shapeW_ || image.rows != shapeH_) {
+            const int cap = orbx_reserve_shape(h_, image.cols, image.rows);
+            check(cap < 0 ? cap : ORBX_OK, "ORBextractor::operator()");
+            cap_ = cap; shapeW_ = image.cols; shapeH_ = image.rows;
+        }
         kbuf_.resize(cap_); dbuf_.resize((size_t)cap_ * 32);
         int n = 0;
         check(orbx_extract(h_, image.data, image.cols, image.rows, (size_t)image.step,
@@ -161,7 +172,7 @@ public:
 
 protected:
     orbx_handle* h_ = nullptr;
-    int nlevels_, cap_ = 0;
+    int nlevels_, cap_ = 0, shapeW_ = 0, shapeH_ = 0;
     float scaleFactor_;
     bool pyramidValid_ = false;
     std::vector<KeyPoint> kbuf_;

@@ -226,3 +226,41 @@ def test_single_frame_graph_replay(monkeypatch):
     kg2, dg2 = ex.extract(seq[0])
     _compare_full(kg2, dg2, ko, do)
     ex.close()
+
+
+def test_wide_image_on_larger_handle_grows_capacity():
+    """a smaller image with a wider aspect ratio than the handle maximum has more quadtree roots per level
+    (nIni, src/ORBextractor.cc:543-546) and so a larger keypoint capacity than the one sized at creation: the result
+    store grows (orbx_reserve_shape reports it) instead of the call failing with ORBX_E_CAPACITY."""
+    ex = capi.Extractor(nfeatures=100, max_width=1920, max_height=1080, chunk_frames=2, result_slots=2)
+    cap0 = ex.cap
+    for (w, h) in [(1241, 100), (640, 480), (1900, 70)]:
+        img = _image(w, h, seed=w + 7 * h)
+        orc = O.Extractor(nfeatures=100)
+        ko, do = orc.extract(img)
+        kg, dg = ex.extract(img)
+        _compare_full(kg, dg, ko, do)
+        ex.extract_batch(np.stack([img, img]))           # the batch path on the grown store
+        kb, db, cb = ex.download(0, 2)
+        for i in range(2):
+            _compare_full(kb[i][:cb[i]], db[i][:cb[i]], ko, do)
+    assert ex.cap > cap0
+    ex.close()
+
+
+def test_failed_shape_does_not_poison_the_handle():
+    """a shape the handle rejects must leave no trace: the next call with the previous shape runs on a
+    workspace laid out for THAT shape (the handle forgets its shape before it touches a buffer)."""
+    ex = capi.Extractor(max_width=640, max_height=480)
+    orc = O.Extractor()
+    img = _image(640, 480, seed=21)
+    ko, do = orc.extract(img)
+    _compare_full(*ex.extract(img), ko, do)
+    with pytest.raises(capi.OrbxError):
+        ex.extract(_image(800, 480, seed=1))             # exceeds the handle maximum
+    _compare_full(*ex.extract(img), ko, do)
+    small = _image(333, 251, seed=2)
+    ks, ds = O.Extractor().extract(small)
+    _compare_full(*ex.extract(small), ks, ds)
+    _compare_full(*ex.extract(img), ko, do)
+    ex.close()

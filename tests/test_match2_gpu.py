@@ -214,3 +214,31 @@ def test_stateless_calls_reuse_scratch_across_sizes_and_threads():
     for t in ts:
         t.join()
     assert not errors, errors[0]
+
+
+def test_extract_stereo_batch_padded_host_rows():
+    """contiguous host frames whose row stride exceeds the workspace pitch (1280 for width 1241): each eye
+    owns half of the landing zone, the linear copy of one eye must not spill into the other."""
+    w, h, nf, npairs, stride = 1241, 376, 2000, 2, 1280
+    bf, fx = 386.1448, 718.856
+    Lp = np.zeros((npairs, h, stride), np.uint8); Rp = np.zeros((npairs, h, stride), np.uint8)
+    for i in range(npairs):
+        l, r = synth.stereo_pair(w, h, seed=40 + i)
+        Lp[i, :, :w] = l; Rp[i, :, :w] = r
+        Lp[i, :, w:] = 255; Rp[i, :, w:] = 7
+    ex = capi.Extractor(nfeatures=nf, max_width=w, max_height=h, chunk_frames=4, result_slots=2 * npairs)
+    ur, dp, _ = ex.extract_stereo_batch(Lp.ctypes.data, Rp.ctypes.data, bf, fx, nframes=npairs, width=w, height=h,
+                                        frame_stride=h * stride, row_stride=stride, on_device=False)
+    kps, desc, counts = ex.download(0, 2 * npairs)
+    for i in range(npairs):
+        el, er = O.Extractor(nf), O.Extractor(nf)
+        kl, dl = el.extract(np.ascontiguousarray(Lp[i, :, :w]))
+        kr, dr = er.extract(np.ascontiguousarray(Rp[i, :, :w]))
+        assert counts[2 * i] == len(kl) and counts[2 * i + 1] == len(kr)
+        assert kps[2 * i, :len(kl)].tobytes() == kl.tobytes() and kps[2 * i + 1, :len(kr)].tobytes() == kr.tobytes()
+        assert np.array_equal(desc[2 * i, :len(kl)], dl) and np.array_equal(desc[2 * i + 1, :len(kr)], dr)
+        t = el.tables()
+        u_o, z_o, _ = O.compute_stereo_matches(kl, dl, kr, dr, [el.level(l) for l in range(8)],
+                                               [er.level(l) for l in range(8)], t["scale"], t["inv_scale"], bf, fx)
+        assert np.array_equal(ur[i, :len(kl)], u_o) and np.array_equal(dp[i, :len(kl)], z_o), i
+    ex.close()
