@@ -1,0 +1,360 @@
+"""Seeded matcher cases in REFERENCE terms (frames, map points with the fields Tracking / LocalMapping leave on them),
+each with two runners:
+
+    run_reference(case)  the reference's own code (oracle/_ref/libref_matchers.so through tests/ref2_lib.py)
+    run_oracle(case)     the oracle (oracle/liborb_oracle.so) on the flat arrays the C ABI takes; the flattening below is
+                         the test-side twin of the host wrapper's (orb_slam2_map_b200/host/orbx.hpp)
+
+Both return a dict of numpy arrays that must be identical.  tests/golden/make_golden_matchers.py freezes the reference's
+outputs into tests/golden/ref_matchers.npz so the oracle stays pinned where the reference library is absent.
+TEST INFRASTRUCTURE ONLY."""
+from __future__ import annotations
+
+import functools
+
+import numpy as np
+
+import oracle_lib as O
+from orb_slam2_map_b200 import synth
+
+F32 = np.float32
+TH_HIGH, TH_LOW = 100, 50
+
+
+@functools.lru_cache(maxsize=None)
+def _extracted(w, h, nf, seed, kind="canvas"):
+    if kind == "canvas":
+        img = synth.textured_canvas(w, h, seed=seed)
+    else:
+        img = synth.frame_sequence(seed + 2, w, h, seed=3)[seed + 1]
+    ex = O.Extractor(nfeatures=nf)
+    k, d = ex.extract(img)
+    return k, d, ex.tables()["scale"].copy()
+
+
+def _noisy(desc, r, flips=12, p=0.6):
+    qd = desc.copy()
+    n = len(qd)
+    pos = r.integers(0, 256, (n, flips))
+    for j in range(flips):
+        use = r.random(n) < p
+        qd[use, pos[use, j] // 8] ^= (1 << (pos[use, j] % 8)).astype(np.uint8)
+    return qd
+
+
+def _frame(case, key="frame"):
+    f = case[key]
+    return O.FrameData(f["kps"], f["desc"], f["w"], f["h"], u_right=f.get("u_right"), scale_factors=f.get("scale"),
+                       bounds=f.get("bounds"))
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# DescriptorDistance
+# ------------------------------------------------------------------------------------------------------------------
+def case_distance(seed=0):
+    r = np.random.default_rng(seed)
+    a = r.integers(0, 256, (260, 32), dtype=np.uint8)
+    b = r.integers(0, 256, (260, 32), dtype=np.uint8)
+    a[0] = 0; b[0] = 0
+    a[1] = 0; b[1] = 255
+    a[2] = 0; b[2] = 0; b[2, 17] = 0x10
+    for i in range(3, 40):                       # every byte position once
+        b[i] = a[i]; b[i, i - 3 if i - 3 < 32 else 0] ^= 0x81
+    return dict(kind="distance", a=a, b=b)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Frame::GetFeaturesInArea (+ AssignFeaturesToGrid / PosInGrid)
+# ------------------------------------------------------------------------------------------------------------------
+def case_area(seed=0, shifted=False):
+    k, d, sf = _extracted(640, 480, 1000, 5 + seed)
+    r = np.random.default_rng(100 + seed)
+    k = k.copy()
+    bounds = None
+    if shifted:
+        # undistortion pushes keypoints outside the image and the bounds are not the image: the "last half cell is not
+        # indexed" quirk (PosInGrid rounds, src/Frame.cc:382-392) and negative coordinates
+        k["x"] = (k["x"] * F32(1.04) - F32(12.5)).astype(F32)
+        k["y"] = (k["y"] * F32(1.03) - F32(7.25)).astype(F32)
+        bounds = (-10.5, 655.25, -6.0, 489.5)
+    nq = 500
+    q = np.zeros((nq, 5), F32)
+    q[:, 0] = r.uniform(-40, 700, nq)
+    q[:, 1] = r.uniform(-40, 520, nq)
+    q[:, 2] = r.choice([3.0, 10.0, 25.5, 100.0, 250.0], nq)
+    lv = [(-1, -1), (0, 0), (0, -1), (-1, 3), (2, -1), (1, 2), (3, 3), (0, 7), (7, 7), (1, -1), (-1, 0), (5, 2)]
+    pick = r.integers(0, len(lv), nq)
+    q[:, 3] = [lv[i][0] for i in pick]
+    q[:, 4] = [lv[i][1] for i in pick]
+    # exact cell borders
+    q[:20, 0] = np.arange(20) * 10.0
+    q[:20, 1] = np.arange(20) * 10.0
+    return dict(kind="area", frame=dict(kps=k, desc=d, w=640, h=480, scale=sf, bounds=bounds), queries=q)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# SearchForInitialization
+# ------------------------------------------------------------------------------------------------------------------
+def case_search_init(seed=0, window=100, nnratio=0.9, ori=True, collide=False):
+    k1, d1, sf = _extracted(640, 480, 1000, seed, kind="seq")
+    k2, d2, _ = _extracted(640, 480, 1000, seed + 1, kind="seq")
+    d1, d2 = d1.copy(), d2.copy()
+    if collide:
+        # many F1 descriptors equal -> several queries want the same F2 keypoint (steal-back, vMatchedDistance skips),
+        # and duplicated F2 descriptors make best == second best
+        r = np.random.default_rng(seed)
+        lvl0 = np.nonzero(k1["octave"] == 0)[0]
+        d1[lvl0[::3]] = d1[lvl0[0]]
+        t0 = np.nonzero(k2["octave"] == 0)[0]
+        d2[t0[::4]] = d2[t0[1]]
+        d2[t0[5]] = d1[lvl0[0]]
+    prev = np.stack([k1["x"], k1["y"]], axis=1).astype(F32)
+    return dict(kind="search_init", f1=dict(kps=k1, desc=d1, w=640, h=480, scale=sf), f2=dict(kps=k2, desc=d2, w=640, h=480, scale=sf),
+                prev=prev, window=window, nnratio=nnratio, ori=ori)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Frame::ComputeStereoMatches
+# ------------------------------------------------------------------------------------------------------------------
+@functools.lru_cache(maxsize=None)
+def _stereo(w, h, nf, seed):
+    left, right = synth.stereo_pair(w, h, seed=seed)
+    el, er = O.Extractor(nf), O.Extractor(nf)
+    kl, dl = el.extract(left)
+    kr, dr = er.extract(right)
+    pl = [el.level(l) for l in range(8)]
+    pr = [er.level(l) for l in range(8)]
+    t = el.tables()
+    return kl, dl, kr, dr, pl, pr, t["scale"].copy(), t["inv_scale"].copy()
+
+
+def case_stereo(w=640, h=240, nf=800, seed=2, bf=386.1448, fx=718.856):
+    kl, dl, kr, dr, pl, pr, sc, isc = _stereo(w, h, nf, seed)
+    return dict(kind="stereo", kl=kl, dl=dl, kr=kr, dr=dr, pl=pl, pr=pr, scale=sc, inv_scale=isc, bf=bf, fx=fx)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# SearchByProjection x4.  A frame + "map points" that project near its own keypoints.
+# ------------------------------------------------------------------------------------------------------------------
+def _proj_base(seed, nq, dup):
+    k, d, sf = _extracted(640, 480, 1000, 20 + seed)
+    r = np.random.default_rng(300 + seed)
+    n = len(k)
+    src = r.integers(0, n, nq)
+    u = (k["x"][src] + r.normal(0, 3, nq)).astype(F32)
+    v = (k["y"][src] + r.normal(0, 3, nq)).astype(F32)
+    # a few outside the image bounds (the reference skips them)
+    u[:6] = [-3.0, 641.5, 100.0, 200.0, 0.0, 640.0]
+    v[:6] = [50.0, 60.0, -0.5, 480.25, 0.0, 480.0]
+    qd = _noisy(d[src], r)
+    if dup:
+        qd[::3] = qd[0]
+    level = k["octave"][src].astype(np.int32)
+    angle = ((k["angle"][src] + r.normal(0, 8, nq)) % 360).astype(F32)
+    u_right = np.where(r.random(n) < 0.6, k["x"] - 20.0 + r.normal(0, 4, n), -1.0).astype(F32)
+    slot_state = r.choice([0, 0, 0, 0, 0, 0, 0, 0, 1, 2], n).astype(np.uint8)
+    nobs = r.choice([0, 1, 3], nq, p=[0.3, 0.3, 0.4]).astype(np.int32)
+    frame = dict(kps=k, desc=d, w=640, h=480, scale=sf, u_right=u_right)
+    return frame, r, src, u, v, qd, level, angle, slot_state, nobs
+
+
+def case_proj_localmap(seed=0, th=1.0, nnratio=0.8, dup=False, nq=900):
+    frame, r, src, u, v, qd, level, angle, slot_state, nobs = _proj_base(seed, nq, dup)
+    view_cos = r.choice([0.9, 0.9985, 0.998, 0.99801, 0.5], nq).astype(F32)
+    in_view = (r.random(nq) < 0.9).astype(np.uint8)
+    proj_xr = (u - F32(20.0) + r.normal(0, 3, nq)).astype(F32)
+    return dict(kind="proj_localmap", frame=frame, slot_state=slot_state, proj_x=u, proj_y=v, proj_xr=proj_xr, level=level,
+                view_cos=view_cos, in_view=in_view, qdesc=qd, nobs=nobs, th=th, nnratio=nnratio)
+
+
+def case_proj_lastframe(seed=0, th=15.0, last_tz=0.0, mono=False, ori=True, dup=False, nq=900, bf=20.0):
+    frame, r, src, u, v, qd, level, angle, slot_state, nobs = _proj_base(seed, nq, dup)
+    outlier = (r.random(nq) < 0.05).astype(np.uint8)
+    return dict(kind="proj_lastframe", frame=frame, slot_state=slot_state, bf=bf, u=u, v=v, octave=level, angle=angle, qdesc=qd,
+                nobs=nobs, outlier=outlier, last_tz=last_tz, th=th, mono=mono, ori=ori)
+
+
+def _max_dist_for_level(u, v, level, sf):
+    """mfMaxDistance that makes MapPoint::PredictScale(dist, log(1.2)) = ceil(log(max/dist)/log(sf)) return `level`"""
+    dist = np.sqrt(u.astype(np.float64) ** 2 + v.astype(np.float64) ** 2 + 1.0).astype(F32)
+    return (dist.astype(np.float64) * float(sf[1]) ** (level - 0.5)).astype(F32)
+
+
+def case_proj_keyframe(seed=0, th=10.0, orb_dist=64, ori=True, dup=False, nq=900):
+    frame, r, src, u, v, qd, level, angle, slot_state, nobs = _proj_base(seed, nq, dup)
+    max_dist = _max_dist_for_level(u, v, level, frame["scale"])
+    found = (r.random(nq) < 0.08).astype(np.uint8)
+    return dict(kind="proj_keyframe", frame=frame, slot_state=slot_state, u=u, v=v, level=level, max_dist=max_dist, angle=angle,
+                qdesc=qd, already_found=found, th=th, orb_dist=orb_dist, ori=ori)
+
+
+def case_proj_sim3(seed=0, th=10, dup=False, nq=900):
+    frame, r, src, u, v, qd, level, angle, slot_state, nobs = _proj_base(seed, nq, dup)
+    frame = dict(frame); frame["u_right"] = None
+    level = np.maximum(level, 0)
+    max_dist = _max_dist_for_level(u, v, level, frame["scale"])
+    return dict(kind="proj_sim3", frame=frame, matched_state=(slot_state != 0).astype(np.uint8), u=u, v=v, level=level,
+                max_dist=max_dist, qdesc=qd, th=th)
+
+
+def _queries(n):
+    q = np.zeros(n, O.PROJ_DTYPE)
+    q["level_lo"] = -1
+    q["level_hi"] = -1
+    q["max_right_err"] = -1.0
+    return q
+
+
+def _remap(assigned, keep):
+    """oracle query indices refer to the flattened (kept) list: map them back to the case's map point indices"""
+    idx = np.nonzero(keep)[0]
+    out = np.full_like(assigned, -1)
+    m = assigned >= 0
+    out[m] = idx[assigned[m]]
+    return out
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def run_reference(c):
+    import ref2_lib as R
+    k = c["kind"]
+    if k == "distance":
+        return dict(dist=np.array([R.descriptor_distance(a, b) for a, b in zip(c["a"], c["b"])], np.int32))
+    if k == "area":
+        f = _frame(c)
+        res = [R.features_in_area(f, *map(float, q[:3]), int(q[3]), int(q[4])) for q in c["queries"]]
+        return dict(counts=np.array([len(x) for x in res], np.int32), idx=np.concatenate(res + [np.zeros(0, np.int32)]).astype(np.int32))
+    if k == "search_init":
+        n, m12, pm = R.search_for_initialization(_frame(c, "f1"), _frame(c, "f2"), c["prev"], c["window"], c["nnratio"], c["ori"])
+        return dict(n=np.int32(n), m12=m12, prev=pm)
+    if k == "stereo":
+        ur, dp = R.compute_stereo_matches(c["kl"], c["dl"], c["kr"], c["dr"], c["pl"], c["pr"], c["scale"], c["inv_scale"], c["bf"], c["fx"])
+        return dict(u_right=ur, depth=dp)
+    if k == "proj_localmap":
+        n, a = R.proj_localmap(_frame(c), c["slot_state"], c["proj_x"], c["proj_y"], c["proj_xr"], c["level"], c["view_cos"],
+                               c["in_view"], c["qdesc"], c["nobs"], c["th"], c["nnratio"], False)
+        return dict(n=np.int32(n), assigned=np.where(a == -2, -1, a).astype(np.int32))
+    if k == "proj_lastframe":
+        n, a = R.proj_lastframe(_frame(c), c["slot_state"], c["bf"], c["u"], c["v"], c["octave"], c["angle"], c["qdesc"], c["nobs"],
+                                c["outlier"], c["last_tz"], c["th"], c["mono"], 0.9, c["ori"])
+        return dict(n=np.int32(n), assigned=np.where(a == -2, -1, a).astype(np.int32))
+    if k == "proj_keyframe":
+        n, a, lv = R.proj_keyframe(_frame(c), c["slot_state"], c["u"], c["v"], c["max_dist"], c["angle"], c["qdesc"], c["already_found"],
+                                   c["th"], c["orb_dist"], 0.9, c["ori"])
+        assert np.array_equal(lv, c["level"]), "MapPoint::PredictScale did not return the level the case asked for"
+        return dict(n=np.int32(n), assigned=np.where(a == -2, -1, a).astype(np.int32))
+    if k == "proj_sim3":
+        n, a, lv = R.proj_sim3(_frame(c), c["matched_state"], c["u"], c["v"], c["max_dist"], c["qdesc"], c["th"])
+        assert np.array_equal(lv, c["level"])
+        return dict(n=np.int32(n), assigned=np.where(a == -2, -1, a).astype(np.int32))
+    raise KeyError(k)
+
+
+def run_oracle(c):
+    k = c["kind"]
+    if k == "distance":
+        return dict(dist=np.array([O.descriptor_distance(a, b) for a, b in zip(c["a"], c["b"])], np.int32))
+    if k == "area":
+        f = _frame(c)
+        res = [O.features_in_area(f, *map(float, q[:3]), int(q[3]), int(q[4])) for q in c["queries"]]
+        return dict(counts=np.array([len(x) for x in res], np.int32), idx=np.concatenate(res + [np.zeros(0, np.int32)]).astype(np.int32))
+    if k == "search_init":
+        n, m12, pm, _ = O.search_for_initialization(_frame(c, "f1"), _frame(c, "f2"), c["prev"], c["window"], c["nnratio"], c["ori"])
+        return dict(n=np.int32(n), m12=m12, prev=pm)
+    if k == "stereo":
+        ur, dp, _ = O.compute_stereo_matches(c["kl"], c["dl"], c["kr"], c["dr"], c["pl"], c["pr"], c["scale"], c["inv_scale"], c["bf"], c["fx"])
+        return dict(u_right=ur, depth=dp)
+    f = _frame(c)
+    sf = c["frame"]["scale"]
+    b = c["frame"].get("bounds") or (0.0, float(c["frame"]["w"]), 0.0, float(c["frame"]["h"]))
+    if k == "proj_localmap":
+        # src/ORBmatcher.cc:45-77: in-view points only; r = RadiusByViewingCos(cos) [* th]; window r * scale[level]
+        keep = c["in_view"].astype(bool)
+        q = _queries(int(keep.sum()))
+        # RadiusByViewingCos compares the float cosine with the DOUBLE literal 0.998 (src/ORBmatcher.cc:131-137)
+        rr = np.where(c["view_cos"].astype(np.float64) > 0.998, F32(2.5), F32(4.0)).astype(F32)
+        if c["th"] != 1.0:
+            rr = (rr * F32(c["th"])).astype(F32)
+        rad = (rr * sf[c["level"]]).astype(F32)[keep]
+        q["u"] = c["proj_x"][keep]; q["v"] = c["proj_y"][keep]; q["radius"] = rad
+        q["min_level"] = c["level"][keep] - 1; q["max_level"] = c["level"][keep]
+        q["u_right"] = c["proj_xr"][keep]; q["max_right_err"] = rad
+        n, a, _, _, _ = O.search_by_projection(0, f, q, c["qdesc"][keep], (c["nobs"][keep] > 0).astype(np.uint8),
+                                               (c["slot_state"] == 1).astype(np.uint8), TH_HIGH, c["nnratio"], False)
+        return dict(n=np.int32(n), assigned=_remap(a, keep))
+    if k == "proj_lastframe":
+        # src/ORBmatcher.cc:1328-1392: outliers and points outside the bounds are skipped; window th * scale[octave];
+        # level window by the motion direction
+        u, v = c["u"], c["v"]
+        keep = (c["outlier"] == 0) & ~((u < b[0]) | (u > b[1])) & ~((v < b[2]) | (v > b[3]))
+        mb = F32(c["bf"]) / F32(1.0)
+        fwd = (F32(c["last_tz"]) > mb) and not c["mono"]
+        bwd = (-F32(c["last_tz"]) > mb) and not c["mono"]
+        q = _queries(int(keep.sum()))
+        octv = c["octave"][keep]
+        q["u"] = u[keep]; q["v"] = v[keep]
+        q["radius"] = (F32(c["th"]) * sf[octv]).astype(F32)
+        if fwd:
+            q["min_level"] = octv; q["max_level"] = -1
+        elif bwd:
+            q["min_level"] = 0; q["max_level"] = octv
+        else:
+            q["min_level"] = octv - 1; q["max_level"] = octv + 1
+        q["u_right"] = (u[keep] - F32(c["bf"])).astype(F32)           # u - mbf * invzc, invzc = 1
+        q["max_right_err"] = q["radius"]
+        q["angle"] = c["angle"][keep]
+        n, a, _, _, _ = O.search_by_projection(1, f, q, c["qdesc"][keep], (c["nobs"][keep] > 0).astype(np.uint8),
+                                               (c["slot_state"] == 1).astype(np.uint8), TH_HIGH, 0.9, c["ori"])
+        return dict(n=np.int32(n), assigned=_remap(a, keep))
+    if k == "proj_keyframe":
+        # src/ORBmatcher.cc:1472-1530: already-found and out-of-bounds points skipped; any non-NULL slot blocks
+        u, v = c["u"], c["v"]
+        keep = (c["already_found"] == 0) & ~((u < b[0]) | (u > b[1])) & ~((v < b[2]) | (v > b[3]))
+        q = _queries(int(keep.sum()))
+        lv = c["level"][keep]
+        q["u"] = u[keep]; q["v"] = v[keep]
+        q["radius"] = (F32(c["th"]) * sf[lv]).astype(F32)
+        q["min_level"] = lv - 1; q["max_level"] = lv + 1
+        q["angle"] = c["angle"][keep]
+        n, a, _, _, _ = O.search_by_projection(2, f, q, c["qdesc"][keep], None, (c["slot_state"] != 0).astype(np.uint8),
+                                               c["orb_dist"], 0.9, c["ori"])
+        return dict(n=np.int32(n), assigned=_remap(a, keep))
+    if k == "proj_sim3":
+        # src/ORBmatcher.cc:290-403: KeyFrame::IsInImage, KeyFrame::GetFeaturesInArea (no level window), octave filter
+        u, v = c["u"], c["v"]
+        keep = (u >= b[0]) & (u < b[1]) & (v >= b[2]) & (v < b[3])
+        q = _queries(int(keep.sum()))
+        lv = c["level"][keep]
+        q["u"] = u[keep]; q["v"] = v[keep]
+        q["radius"] = (F32(c["th"]) * sf[lv]).astype(F32)
+        q["min_level"] = -1; q["max_level"] = -1
+        # kpLevel < nPredictedLevel-1 || kpLevel > nPredictedLevel (:374-377); a negative bound switches the filter off in
+        # the flat form, so level 0 is passed as [0, 0]
+        q["level_lo"] = np.maximum(lv - 1, 0); q["level_hi"] = lv
+        n, a, _, _, _ = O.search_by_projection(3, f, q, c["qdesc"][keep], None, c["matched_state"], TH_LOW, 0.75, False)
+        return dict(n=np.int32(n), assigned=_remap(a, keep))
+    raise KeyError(k)
+
+
+# every case the pinning tests run: name -> builder
+CASES = {
+    "distance": lambda: case_distance(),
+    "area": lambda: case_area(0),
+    "area_shifted_bounds": lambda: case_area(1, shifted=True),
+    "search_init_default": lambda: case_search_init(0, 100, 0.9, True),
+    "search_init_w30_noori": lambda: case_search_init(1, 30, 0.7, False),
+    "search_init_w250": lambda: case_search_init(2, 250, 0.95, True),
+    "search_init_collisions": lambda: case_search_init(0, 100, 0.9, True, collide=True),
+    "stereo_640x240": lambda: case_stereo(640, 240, 800, 2),
+    "stereo_kitti": lambda: case_stereo(1241, 376, 2000, 5),
+    "proj_localmap": lambda: case_proj_localmap(0, 1.0, 0.8),
+    "proj_localmap_th3_dup": lambda: case_proj_localmap(1, 3.0, 0.99, dup=True),
+    "proj_lastframe": lambda: case_proj_lastframe(0, 15.0, 0.0),
+    "proj_lastframe_forward": lambda: case_proj_lastframe(1, 7.0, 50.0, ori=False),
+    "proj_lastframe_backward_dup": lambda: case_proj_lastframe(2, 15.0, -50.0, dup=True),
+    "proj_lastframe_mono": lambda: case_proj_lastframe(0, 15.0, 50.0, mono=True),
+    "proj_keyframe": lambda: case_proj_keyframe(0, 10.0, 64),
+    "proj_keyframe_dup_noori": lambda: case_proj_keyframe(1, 15.0, 100, ori=False, dup=True),
+    "proj_sim3": lambda: case_proj_sim3(0, 10),
+    "proj_sim3_dup": lambda: case_proj_sim3(1, 15, dup=True),
+}
