@@ -68,24 +68,31 @@ def algorithmic_bytes(w, h, nkp):
                 total=b_pyr + b_fast + b_desc)
 
 
-# measured DRAM bytes per 640x480 frame (read + write) of each extractor kernel, from the r01l `ncu --set full`
-# capture of a 64-frame launch (profiles/r01l_ncu_full_chunk64_summary.txt); resize = sum over the 7 levels
-NCU_DRAM_BYTES_PER_FRAME = {
-    "fast": (55.872000e6 + 1.545984e6) / 64,
-    "blur": (64.554496e6 + 15.194368e6) / 64,
-    "describe": (118.258688e6 + 5.856512e6) / 64,
-    "resize": (19.690752e6 + 13.948672e6 + 9.568512e6 + 6.848512e6 + 4.751616e6 + 3.381504e6 + 2.323712e6 + 0.03e6) / 64,
-    "octree": 1.815808e6 / 64,
-}
-# warp instructions executed per 640x480 frame by each extractor kernel (smsp__inst_executed.sum of the same capture):
-# these kernels are bound by instruction issue (4 warp instructions per clock per SM), not by HBM
-NCU_WARP_INST_PER_FRAME = {
-    "fast": 120985254 / 64,
-    "blur": 47649344 / 64,
-    "describe": 44842346 / 64,
-    "resize": (16092480 + 10659648 + 6708416 + 5568576 + 4677760 + 2598592 + 2169600) / 64,
-    "octree": 8956845 / 64,
-}
+def ncu_constants():
+    """Per-kernel dram bytes and warp instructions per 640x480 frame from ONE `ncu --set full` capture of the 512-frame
+    chunk the bench launches (profiles/ncu_constants.json, written by scripts/ncu_constants.py from the .ncu-rep).  The file
+    names the kernel sources it was captured on (sha256 of orb_slam2_map_b200/csrc/*.cu,*.h,*.cuh): when they changed
+    since, the numbers are stale and `traffic` / `issue` are reported as null rather than quoted."""
+    path = os.path.join(ROOT, "profiles", "ncu_constants.json")
+    try:
+        with open(path) as f:
+            c = json.load(f)
+    except Exception:
+        return None, "profiles/ncu_constants.json missing"
+    if c.get("csrc_sha256") != csrc_digest():
+        return None, f"profiles/ncu_constants.json was captured on other kernel sources ({c.get('csrc_sha256', '?')[:12]})"
+    return c, None
+
+
+def csrc_digest():
+    import hashlib
+    d = os.path.join(ROOT, "orb_slam2_map_b200", "csrc")
+    h = hashlib.sha256()
+    for name in sorted(os.listdir(d)):
+        if name.endswith((".cu", ".cuh", ".h")):
+            with open(os.path.join(d, name), "rb") as f:
+                h.update(name.encode()); h.update(f.read())
+    return h.hexdigest()
 
 
 def bind_to_gpu_numa(local):
@@ -130,13 +137,14 @@ def quiet_stdout():
 
 
 def emit(line):
-    global _SAVED_STDOUT
+    """The ONE line goes to the ORIGINAL stdout; descriptor 1 itself stays pointed at stderr for the rest of the process, so
+    that whatever a library still prints afterwards (NCCL's communicator teardown under NCCL_DEBUG=INFO) cannot follow it."""
     sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
     if _SAVED_STDOUT is not None:
-        os.dup2(_SAVED_STDOUT, 1)
-        os.close(_SAVED_STDOUT)
-        _SAVED_STDOUT = None
-    print(json.dumps(line), flush=True)
+        os.write(_SAVED_STDOUT, data)
+    else:
+        os.write(1, data)
 
 
 def measured_peaks():
@@ -270,35 +278,73 @@ def run_reference(args):
 
 
 # ---- brute-force 2-NN (BASELINE.json configs[4]) ---------------------------------------------------
-POPC_PER_CLK_PER_SM = 16          # nominal quarter-rate POPC (SURVEY.md §8d [memory]); 5 POPC per compare (carry-save)
-
-
-def knn_rate(dev, nq, ndb, steps, world):
-    """Hamming comparisons/s of knn2_kernel on this GPU: nq x ndb random descriptors, CUDA events."""
+def int_pipe_roofline(dev):
+    """MEASURED integer-pipe rates of this GPU (orbm_measure_int_rates: register-only popc / lop3 / add loops and K10's
+    inner loop on register operands).  The last one is the roofline of knn2_kernel: what the XOR/CSA/POPC/top-2 mix of one
+    compare costs when no shared-memory load, barrier or tail is in the way."""
     import torch
-    from orb_slam2_map_b200 import capi, synth
-    q = torch.from_numpy(synth.random_descriptors(nq, 11)).to(dev)
-    db = torch.from_numpy(synth.random_descriptors(ndb, 12)).to(dev)
-    od = torch.empty((nq, 2), dtype=torch.int16, device=dev)
-    oi = torch.empty((nq, 2), dtype=torch.int32, device=dev)
-    st = torch.cuda.current_stream()
-    run = lambda: capi.knn2_device(q.data_ptr(), nq, db.data_ptr(), ndb, 0, od.data_ptr(), oi.data_ptr(), st.cuda_stream)
-    for _ in range(2):
-        run()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
-    e0.record(st)
-    for _ in range(steps):
-        run()
-    e1.record(st)
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / steps
-    rate = nq * ndb / (ms * 1e-3)
+    from orb_slam2_map_b200 import capi
     props = torch.cuda.get_device_properties(dev)
-    peak = props.multi_processor_count * POPC_PER_CLK_PER_SM * 1.965e9 / 5.0
-    return {"metric": "Hamming cmp/s (brute-force 2-NN, 256-bit)", "value": rate * world, "unit": "cmp/s", "per_gpu": rate,
-            "queries": nq, "database_rows": ndb, "ms": ms,
-            "popc_roofline": {"peak": peak, "frac": rate / peak, "how": "nominal 16 POPC/clk/SM x SMs x 1.965 GHz / 5 POPC per compare"}}
+    r = capi.measure_int_rates()
+    return {"peak": r["knn_mix"], "unit": "cmp/s", "peak_source": "measured: K10 inner loop on register operands (orbm_measure_int_rates)",
+            "popc_per_s": r["popc"], "lop3_per_s": r["lop3"], "add_per_s": r["add"], "sms": props.multi_processor_count,
+            "popc_per_clk_per_sm_at_1965MHz": r["popc"] / props.multi_processor_count / 1.965e9,
+            "lop3_per_clk_per_sm_at_1965MHz": r["lop3"] / props.multi_processor_count / 1.965e9}
+
+
+def hamming_leg(dev, rank, world, stream, queries=1 << 20, per=2000000):
+    """The cmp/s half of BASELINE.json's metric, MEASURED on the ranks of this run: config 5 as named — 1 048 576 queries
+    replicated, 2 000 000 database rows per GPU (16 M over 8) — through ONE C-ABI call per rank, orbm_knn2_sharded: local
+    scan (K10), ncclAllGather of the 12-byte per-query records, device merge (K11), chunked so that the exchange of a chunk
+    overlaps the scan of the next.  One timed step (2.1e12 compares per rank), CUDA events on the launching stream, max over
+    ranks.  Also timed at N > 1: the exchange alone (empty shards) and the same scan without exchange (the N = 1 workload: weak
+    scaling keeps the per-rank work fixed), whose ratio to the sharded per-GPU rate is the efficiency."""
+    import torch
+    import torch.distributed as dist
+    from orb_slam2_map_b200 import sharding, synth
+    q = torch.from_numpy(synth.random_descriptors(queries, 1)).to(dev)
+    db = torch.from_numpy(synth.random_descriptors(per, 100 + rank)).to(dev)
+    od = torch.empty((queries, 2), dtype=torch.int16, device=dev)
+    oi = torch.empty((queries, 2), dtype=torch.int32, device=dev)
+    comm = sharding.ShardComm(dev) if world > 1 else None
+    st = stream.cuda_stream
+
+    def timed(fn):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    small = 65536
+    for _ in range(2):                                                  # warm-up: same path, 1/16 of the queries
+        sharding.knn2_sharded(q[:small], db, rank * per, comm, stream=st, out=(od[:small], oi[:small]))
+    ms = timed(lambda: sharding.knn2_sharded(q, db, rank * per, comm, stream=st, out=(od, oi)))
+    checksum = int(oi[:, 0].to(torch.int64).sum().item())                # rank 0's view of the merged result
+    ms_exchange = timed(lambda: sharding.knn2_sharded(q, db[:0], rank * per, comm, stream=st, out=(od, oi))) if world > 1 else 0.0
+    # the N = 1 workload on this rank: the same scan without communicator (at N = 1 that IS the step just timed)
+    ms_local = timed(lambda: sharding.knn2_sharded(q, db, rank * per, None, stream=st, out=(od, oi))) if world > 1 else ms
+    if comm is not None:
+        comm.close()
+    value = float(queries) * per * world / (ms * 1e-3)
+    local_rate = float(queries) * per / (ms_local * 1e-3)
+    roof = int_pipe_roofline(dev)
+    roof["achieved"] = value / world
+    roof["frac"] = value / world / roof["peak"]
+    return {"metric": "Hamming cmp/s (brute-force top-2 kNN, 256-bit descriptors)", "value": value, "unit": "cmp/s", "per_gpu": value / world,
+            "measured": True, "nranks": world, "queries": queries, "database_rows_per_gpu": per, "database_rows_total": per * world,
+            "steps": 1, "ms": ms, "exchange_ms_alone": ms_exchange, "local_scan_cmp_s_per_gpu": local_rate,
+            "efficiency_vs_n1": value / world / local_rate,
+            "how": "orbm_knn2_sharded (C ABI): K10 scan of the rank's shard, ncclAllGather of 12 B per query and rank, K11 merge; "
+                   "2 query chunks, the exchange of a chunk overlaps the scan of the next; max over ranks of CUDA-event time",
+            "merged_top1_index_checksum": checksum, "popc_roofline": roof}
 
 
 def run_knn(args):
@@ -320,7 +366,8 @@ def run_knn(args):
     db = torch.from_numpy(synth.random_descriptors(per, 100 + rank)).to(dev)
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
-    step = lambda: sharding.knn2_sharded(q, db, rank * per, stream=stream.cuda_stream)
+    comm = sharding.ShardComm(dev) if world > 1 else None
+    step = lambda: sharding.knn2_sharded(q, db, rank * per, comm, stream=stream.cuda_stream)
     for _ in range(max(args.warmup, 1)):
         step()
     clocks = ClockSampler(local)
@@ -353,8 +400,8 @@ def run_knn(args):
     dist.all_reduce(dt, op=dist.ReduceOp.MAX)
     total = float(nq) * per * world
     value = total * args.steps / (ms * 1e-3)
-    props = torch.cuda.get_device_properties(dev)
-    peak = props.multi_processor_count * POPC_PER_CLK_PER_SM * 1.965e9 / 5.0
+    roof = int_pipe_roofline(dev)
+    peak = roof["peak"]
     line = {"metric": "Hamming cmp/s (brute-force top-2 kNN, 256-bit descriptors)", "value": value, "unit": "cmp/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u32 xor/popc", "data": "synthetic",
@@ -366,7 +413,7 @@ def run_knn(args):
             "gpu_launches": 2 * args.steps,
             "roofline": {"bound": "int-pipe", "kernel": "knn2_kernel", "achieved": value / world, "peak": peak, "unit": "cmp/s",
                          "frac": value / world / peak, "traffic": None,
-                         "how": "nominal 16 POPC/clk/SM x SMs x 1.965 GHz / 5 POPC per compare (carry-save popcount)"}}
+                         "how": roof["peak_source"], "int_rates": roof}}
     if rank == 0:
         emit(line)
     dist.destroy_process_group()
@@ -764,6 +811,9 @@ def main():
     h2d_gbs = h2d / (ev0.elapsed_time(ev1) * 1e-3) / 1e9
     del pcie_dst
     d2h = kp_out.nbytes + de_out.nbytes + cnt_out.nbytes + m12_out.nbytes + nm_out.nbytes + 8
+    # descriptor pairs the guided search of one step evaluates (the kernels count them on request; outside the timed region)
+    if match:
+        ncmp.value = ex.search_init_pairs(0, F - 1, WINDOW, NNRATIO, True, fetch=True)[2]
 
     # ---- roofline of the dominant kernel ----------------------------------------------------------
     peak, peak_src = measured_peaks()
@@ -775,26 +825,27 @@ def main():
     dom_launches = max(1, stage_launches.get(dom, 1))
     dom_ms = stage_ms.get(dom, 0.0)
     achieved = (dom_bytes * frames_total / dom_launches) / (dom_ms / dom_launches * 1e-3) / 1e9 if dom_ms > 0 else 0.0
-    # DRAM traffic of the dominant kernel: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full`
-    # capture (profiles/r01l_ncu_full_chunk64_summary.txt, a 64-frame launch of the 640x480 workload), scaled to
-    # the frames one launch of this run processes.  Other image shapes have no capture: null.
+    # DRAM traffic and executed warp instructions of the dominant kernel: dram__bytes_read.sum + dram__bytes_write.sum
+    # and smsp__inst_executed.sum of one `ncu --set full` capture of the 512-frame chunk this run launches, per frame
+    # (profiles/ncu_constants.json), scaled to the frames of one launch.  null when the capture is stale or absent.
+    consts, why = ncu_constants()
     traffic = None
-    if (W, H) == (640, 480) and dom in NCU_DRAM_BYTES_PER_FRAME:
-        traffic = NCU_DRAM_BYTES_PER_FRAME[dom] * frames_total / dom_launches
+    if consts and (W, H) == (640, 480) and dom in consts["kernels"]:
+        traffic = consts["kernels"][dom]["dram_bytes_per_frame"] * frames_total / dom_launches
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic,
-                "traffic_source": "ncu --set full, profiles/r01l_ncu_full_chunk64_summary.txt, per-frame bytes x frames per launch" if traffic else None,
+                "traffic_source": (f"ncu --set full of a {consts['chunk_frames']}-frame launch, {consts['source']}" if traffic else why),
                 "algorithmic_bytes_per_launch": dom_bytes * frames_total / dom_launches,
                 "peak_source": peak_src,
                 "algorithmic_bytes_per_frame": dom_bytes,
                 "share_of_device_time": dom_ms / max(sum(stage_ms.values()), 1e-9)}
-    if (W, H) == (640, 480) and dom in NCU_WARP_INST_PER_FRAME and clk.get("sm_mhz") and dom_ms > 0:
+    if consts and (W, H) == (640, 480) and dom in consts["kernels"] and clk.get("sm_mhz") and dom_ms > 0:
         # the bound that actually limits this kernel: issue slots (148 SMs x 4 schedulers x SM clock under load)
-        ginst = NCU_WARP_INST_PER_FRAME[dom] * (frames_total / dom_launches) / (dom_ms / dom_launches * 1e-3) / 1e9
+        wi = consts["kernels"][dom]["warp_inst_per_frame"]
+        ginst = wi * (frames_total / dom_launches) / (dom_ms / dom_launches * 1e-3) / 1e9
         issue_peak = 148 * 4 * clk["sm_mhz"] * 1e6 / 1e9
         roofline["issue"] = {"achieved": ginst, "peak": issue_peak, "unit": "G warp-inst/s", "frac": ginst / issue_peak,
-                             "warp_inst_per_frame": NCU_WARP_INST_PER_FRAME[dom],
-                             "source": "smsp__inst_executed.sum, profiles/r01l_ncu_full_chunk64_summary.txt"}
+                             "warp_inst_per_frame": wi, "source": f"smsp__inst_executed.sum, {consts['source']}"}
     path_gbs = ab["total"] * value / world / 1e9
     stages = {k: {"ms_per_step": v / args.steps, "launches_per_step": stage_launches[k] / args.steps}
               for k, v in stage_ms.items() if stage_launches[k]}
@@ -818,8 +869,9 @@ def main():
     }
 
     # ---- second half of the metric: Hamming cmp/s of the brute-force 2-NN kernel on this GPU (short run) ----
+    # measured on every rank of this run through orbm_knn2_sharded (NCCL at N > 1), config 5 as named
     if args.workload == "frames":
-        line["hamming"] = knn_rate(dev, nq=65536, ndb=1 << 20, steps=3, world=world)
+        line["hamming"] = hamming_leg(dev, rank, world, stream)
 
     # ---- CPU baseline (rank 0, N=1 only): bounded sample of the same frames ----------------------
     if rank == 0 and world == 1 and not args.no_cpu:

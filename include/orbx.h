@@ -257,9 +257,31 @@ int orbm_knn2_device(const uint8_t* queries, int64_t nq, const uint8_t* database
 /* Tuning hook: how the 256-bit popcount is evaluated (0 = 8 POPC, 1 = carry-save 5 POPC [default],
  * 2 = Harley-Seal 4 POPC).  Results are identical; only the instruction mix changes. */
 int orbm_knn2_set_variant(int variant);
+/* Measurement hook (bench.py): register-only rate probes of the integer pipes K10 lives on.  rates[0..2] = popc.b32 /
+ * lop3.b32 / add.u32 results per second over all SMs, rates[3] = Hamming compares per second of K10's inner loop on
+ * register operands (current popcount variant): the measured roofline of orbm_knn2_device.  Synchronous, ~10 ms. */
+int orbm_measure_int_rates(double rates[4]);
 /* Merge `nparts` per-shard results (each [nq][2]) into one, same tie rule; device pointers. */
 int orbm_knn2_merge_device(const uint16_t* part_dist, const int32_t* part_idx, int nparts,
                            int64_t nq, uint16_t* out_dist, int32_t* out_idx, void* stream);
+
+/* ---- config 5 across GPUs: database sharded by rows, one rank (process or thread) per GPU ------------------
+ * NCCL is bound at run time (dlopen of libnccl.so.2), so only callers of these four entry points need it.
+ * A communicator is either the caller's own ncclComm_t (passed as void*) or one made here: rank 0 obtains an id,
+ * ships its 128 bytes to the other ranks by any means, every rank calls orbm_nccl_comm_create on its device. */
+#define ORBM_NCCL_ID_BYTES 128
+int orbm_nccl_unique_id(uint8_t id[ORBM_NCCL_ID_BYTES]);
+int orbm_nccl_comm_create(const uint8_t id[ORBM_NCCL_ID_BYTES], int rank, int nranks, void** comm);
+int orbm_nccl_comm_destroy(void* comm);
+/* orbm_knn2_device over a row-sharded database: queries (replicated on every rank) against this rank's shard
+ * [db_index_offset, db_index_offset + ndb_local), ncclAllGather of the per-query (best, second) records, merge under
+ * the (distance, global index) order: every rank ends with the result of the whole database in out_dist / out_idx.
+ * Queries are processed in chunks of query_chunk (0 = half of nq, at least 2 x SMs x 1024; rounded to 1024): the gather and
+ * merge of a chunk run on an internal stream while the next chunk is scanned.  All ranks must call with the same nq and
+ * query_chunk.  comm == NULL (or a communicator of one rank with query_chunk == 0) degenerates to orbm_knn2_device.  Device pointers;
+ * asynchronous on `stream`. */
+int orbm_knn2_sharded(void* comm, const uint8_t* queries, int64_t nq, const uint8_t* db_shard, int64_t ndb_local,
+                      int32_t db_index_offset, int64_t query_chunk, uint16_t* out_dist, int32_t* out_idx, void* stream);
 
 /* ================================================================================================
  * RGB-D frame front: the steps of Tracking::GrabImageRGBD / Frame::Frame(RGB-D)

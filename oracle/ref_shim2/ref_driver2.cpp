@@ -15,6 +15,7 @@
  */
 #include <cmath>
 #include <cstdint>
+#include <cstdio>
 #include <cstring>
 #include <mutex>
 #include <set>
@@ -362,6 +363,242 @@ int ref2_proj_sim3(const orbm_frame* kf, const uint8_t* matched_state, int nq, c
     const int n = matcher.SearchByProjection(K, eye4(), q, matched, th);
     report_assignment(matched, q, assigned);
     return n;
+}
+
+
+/* ================================================================================================================
+ * DBoW2 transform, SearchByBoW x2, SearchForTriangulation, Fuse x2, SearchBySim3,
+ * MapPoint::ComputeDistinctiveDescriptors
+ * ================================================================================================================ */
+
+/* An ORBVocabulary built by the reference's own text loader (TemplatedVocabulary::loadFromTextFile, the format of the
+ * ORBvoc.txt the reference ships instructions for): header "k L scoring weighting", then one line per node
+ * "parent isLeaf d0 .. d31 weight" in node-id order.  Nodes 1 .. nnodes-1 (0 is the root); TF_IDF weighting, L1 scoring. */
+void* ref2_voc_create(int k, int L, int nnodes, const int32_t* parent, const uint8_t* is_leaf, const uint8_t* desc, const double* weight,
+                      const char* tmp_path)
+{
+    FILE* f = std::fopen(tmp_path, "w");
+    if (!f) return nullptr;
+    std::fprintf(f, "%d %d 0 0", k, L);
+    for (int i = 1; i < nnodes; ++i) {
+        std::fprintf(f, "\n%d %d", parent[i], (int)is_leaf[i]);
+        for (int b = 0; b < 32; ++b) std::fprintf(f, " %d", (int)desc[(size_t)i * 32 + b]);
+        std::fprintf(f, " %.17g", weight[i]);                  /* round-trips the double exactly */
+    }
+    std::fclose(f);                                            /* no trailing newline: the loader would read a phantom node */
+    ORBVocabulary* v = new ORBVocabulary();
+    const bool ok = v->loadFromTextFile(tmp_path);
+    std::remove(tmp_path);
+    if (!ok || (int)v->m_nodes.size() != nnodes) { delete v; return nullptr; }
+    return v;
+}
+void ref2_voc_destroy(void* v) { delete static_cast<ORBVocabulary*>(v); }
+
+/* TemplatedVocabulary::transform(feature, word_id, weight, nid, levelsup) (TemplatedVocabulary.h:1231-1271) per feature */
+void ref2_voc_transform(void* voc, const uint8_t* feats, int n, int levelsup, uint32_t* word, double* weight, uint32_t* node)
+{
+    ORBVocabulary* v = static_cast<ORBVocabulary*>(voc);
+    for (int i = 0; i < n; ++i) {
+        cv::Mat d = desc_mat(feats + (size_t)i * 32, 1);
+        DBoW2::WordId w; DBoW2::WordValue val; DBoW2::NodeId nid = 0;
+        v->transform(d, w, val, &nid, levelsup);
+        word[i] = w; weight[i] = val; node[i] = nid;
+    }
+}
+
+/* TemplatedVocabulary::transform(features, BowVector&, FeatureVector&, levelsup) (:1140-1218), what Frame::ComputeBoW
+ * (src/Frame.cc:394-402) calls.  Outputs in std::map order; returns the BowVector size, *nfv = FeatureVector entries. */
+int ref2_voc_transform_all(void* voc, const uint8_t* feats, int n, int levelsup, uint32_t* bow_word, double* bow_value,
+                           uint32_t* fv_node, uint32_t* fv_feat, int* nfv)
+{
+    ORBVocabulary* v = static_cast<ORBVocabulary*>(voc);
+    std::vector<cv::Mat> vd = Converter::toDescriptorVector(desc_mat(feats, n));
+    DBoW2::BowVector bow; DBoW2::FeatureVector fv;
+    v->transform(vd, bow, fv, levelsup);
+    int i = 0;
+    for (auto& e : bow) { bow_word[i] = e.first; bow_value[i] = e.second; ++i; }
+    int j = 0;
+    for (auto& e : fv) for (unsigned int idx : e.second) { fv_node[j] = e.first; fv_feat[j] = idx; ++j; }
+    *nfv = j;
+    return i;
+}
+
+namespace {
+/* mFeatVec as Frame::ComputeBoW leaves it: addFeature(node, i) in feature order for the features whose word has a weight */
+void fill_featvec(DBoW2::FeatureVector& fv, const uint32_t* node, const uint8_t* flags, int n)
+{
+    for (int i = 0; i < n; ++i) if (flags[i] & 1) fv.addFeature(node[i], (unsigned)i);
+}
+/* flags bit 1: the feature holds a good MapPoint, bit 2: it holds a bad one */
+void fill_points(World& w, KeyFrame* K, const orbm_frame* f, const uint8_t* flags, std::vector<MapPoint*>& pts)
+{
+    pts.assign(f->n, static_cast<MapPoint*>(nullptr));
+    for (int i = 0; i < f->n; ++i)
+        if (flags[i] & 6) {
+            pts[i] = w.make_point(0, 0, 1, f->descriptors + (size_t)i * 32, 1);
+            if (flags[i] & 4) pts[i]->mbBad = true;
+            K->mvpMapPoints[i] = pts[i];
+        }
+}
+int index_of(const std::vector<MapPoint*>& pts, MapPoint* p)
+{
+    if (!p) return -1;
+    for (size_t i = 0; i < pts.size(); ++i) if (pts[i] == p) return (int)i;
+    return -2;
+}
+}
+
+/* ORBmatcher::SearchByBoW.  variant 0: (KeyFrame* pKF = a, Frame& F = b, vpMapPointMatches) src/ORBmatcher.cc:159-288;
+ * variant 1: (KeyFrame* pKF1 = a, KeyFrame* pKF2 = b, vpMatches12) :522-655.  match_a[i] / match_b[j]: partner or -1. */
+int ref2_search_by_bow(int variant, const orbm_frame* fa, const uint32_t* node_a, const uint8_t* flags_a, const orbm_frame* fb,
+                       const uint32_t* node_b, const uint8_t* flags_b, float nnratio, int check_orientation, int32_t* match_a, int32_t* match_b)
+{
+    std::lock_guard<std::mutex> g(g_lock);
+    World w;
+    KeyFrame* A = w.make_keyframe(fa, kUnitCam, eye4());
+    fill_featvec(A->mFeatVec, node_a, flags_a, fa->n);
+    std::vector<MapPoint*> pa, pb;
+    fill_points(w, A, fa, flags_a, pa);
+    ORBmatcher matcher(nnratio, check_orientation != 0);
+    for (int i = 0; i < fa->n; ++i) match_a[i] = -1;
+    for (int j = 0; j < fb->n; ++j) match_b[j] = -1;
+    int n;
+    if (variant == 0) {
+        Frame* F = make_frame(fb, kUnitCam);
+        w.frames.push_back(F);
+        fill_featvec(F->mFeatVec, node_b, flags_b, fb->n);
+        std::vector<MapPoint*> m;
+        n = matcher.SearchByBoW(A, *F, m);
+        for (int j = 0; j < fb->n; ++j) { const int i = index_of(pa, m[j]); match_b[j] = i; if (i >= 0) match_a[i] = j; }
+    } else {
+        KeyFrame* B = w.make_keyframe(fb, kUnitCam, eye4());
+        fill_featvec(B->mFeatVec, node_b, flags_b, fb->n);
+        fill_points(w, B, fb, flags_b, pb);
+        std::vector<MapPoint*> m;
+        n = matcher.SearchByBoW(A, B, m);
+        for (int i = 0; i < fa->n; ++i) { const int j = index_of(pb, m[i]); match_a[i] = j; if (j >= 0) match_b[j] = i; }
+    }
+    return n;
+}
+
+/* ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:657-823).  KF2 sits at the origin and KF1's camera centre at
+ * (ex, ey, 1), so the epipole the reference computes (:664-670) is exactly (ex, ey) with the unit camera. */
+int ref2_search_for_triangulation(const orbm_frame* f1, const uint32_t* node1, const uint8_t* flags1, const orbm_frame* f2,
+                                  const uint32_t* node2, const uint8_t* flags2, const float* F12, float ex, float ey, int only_stereo,
+                                  int check_orientation, int32_t* matches12)
+{
+    std::lock_guard<std::mutex> g(g_lock);
+    World w;
+    cv::Mat T1 = eye4();
+    T1.at<float>(0, 3) = -ex; T1.at<float>(1, 3) = -ey; T1.at<float>(2, 3) = -1.f;
+    KeyFrame* K1 = w.make_keyframe(f1, kUnitCam, T1);
+    KeyFrame* K2 = w.make_keyframe(f2, kUnitCam, eye4());
+    fill_featvec(K1->mFeatVec, node1, flags1, f1->n);
+    fill_featvec(K2->mFeatVec, node2, flags2, f2->n);
+    std::vector<MapPoint*> p1, p2;
+    fill_points(w, K1, f1, flags1, p1);
+    fill_points(w, K2, f2, flags2, p2);
+    cv::Mat F(3, 3, CV_32F);
+    for (int i = 0; i < 9; ++i) F.at<float>(i / 3, i % 3) = F12[i];
+    std::vector<std::pair<size_t, size_t>> pairs;
+    ORBmatcher matcher(0.6f, check_orientation != 0);
+    const int n = matcher.SearchForTriangulation(K1, K2, F, pairs, only_stereo != 0);
+    for (int i = 0; i < f1->n; ++i) matches12[i] = -1;
+    for (auto& pr : pairs) matches12[pr.first] = (int32_t)pr.second;
+    return n;
+}
+
+/* ORBmatcher::Fuse.  variant 0: (pKF, vpMapPoints, th) src/ORBmatcher.cc:825-973; variant 1: (pKF, Scw = identity, vpPoints,
+ * th, vpReplacePoint) :975-1100.  The keyframe starts without map points; a query's answer is read back from the side
+ * effects: the slot it was added to, or the slot of the point it was replaced by / reported against. */
+int ref2_fuse(int variant, const orbm_frame* kf, float bf, int nq, const float* u, const float* v, const float* max_dist,
+              const uint8_t* qdesc, const int32_t* nobs, float th, int32_t* best_idx, int32_t* predicted_level)
+{
+    std::lock_guard<std::mutex> g(g_lock);
+    World w;
+    const Cam cam = {1.f, 1.f, 0.f, 0.f, bf};
+    KeyFrame* K = w.make_keyframe(kf, cam, eye4());
+    std::vector<MapPoint*> q(nq);
+    for (int i = 0; i < nq; ++i) {
+        q[i] = w.make_point(u[i], v[i], 1.f, qdesc + (size_t)i * 32, nobs ? nobs[i] : 1, max_dist[i], 0.f);
+        if (predicted_level) {
+            const float d = (float)std::sqrt((double)u[i] * u[i] + (double)v[i] * v[i] + 1.0);
+            predicted_level[i] = q[i]->PredictScale(d, K->mfLogScaleFactor);
+        }
+    }
+    ORBmatcher matcher(0.6f, true);
+    int n;
+    std::vector<MapPoint*> repl(nq, static_cast<MapPoint*>(nullptr));
+    if (variant == 0) n = matcher.Fuse(K, q, th);
+    else n = matcher.Fuse(K, eye4(), q, th, repl);
+    for (int i = 0; i < nq; ++i) {
+        MapPoint* p = variant == 1 && repl[i] ? repl[i] : q[i];
+        for (int hop = 0; hop < nq + 2 && p && p->mbBad && p->mpReplaced; ++hop) p = p->mpReplaced;
+        best_idx[i] = (p && p->mObservations.count(K)) ? (int32_t)p->mObservations[K] : -1;
+    }
+    return n;
+}
+
+/* ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1102-1326) with both keyframes at the origin, s12 = 1, R12 = I, t12 = 0:
+ * map point i of KF1 lies at (u1[i], v1[i], 1) and so projects to (u1[i], v1[i]) in KF2, and the other way round.
+ * has1 / has2: the feature holds a map point; pre12[i] >= 0: vpMatches12[i] already holds the point of KF2 feature pre12[i].
+ * match12[i] (out): KF2 feature newly matched to KF1 feature i, or -1. */
+int ref2_search_by_sim3(const orbm_frame* f1, const orbm_frame* f2, const uint8_t* has1, const float* u1, const float* v1,
+                        const float* maxd1, const uint8_t* has2, const float* u2, const float* v2, const float* maxd2,
+                        const int32_t* pre12, float th, int32_t* match12, int32_t* level1, int32_t* level2)
+{
+    std::lock_guard<std::mutex> g(g_lock);
+    World w;
+    KeyFrame* K1 = w.make_keyframe(f1, kUnitCam, eye4());
+    KeyFrame* K2 = w.make_keyframe(f2, kUnitCam, eye4());
+    std::vector<MapPoint*> p1(f1->n, static_cast<MapPoint*>(nullptr)), p2(f2->n, static_cast<MapPoint*>(nullptr));
+    auto lvl = [](MapPoint* p, float u, float v, KeyFrame* K) {
+        const float d = (float)std::sqrt((double)u * u + (double)v * v + 1.0);
+        return p->PredictScale(d, K->mfLogScaleFactor);
+    };
+    for (int i = 0; i < f1->n; ++i) if (has1[i]) {
+        p1[i] = w.make_point(u1[i], v1[i], 1.f, f1->descriptors + (size_t)i * 32, 1, maxd1[i], 0.f);
+        K1->mvpMapPoints[i] = p1[i];
+        p1[i]->mObservations[K1] = i;
+        if (level1) level1[i] = lvl(p1[i], u1[i], v1[i], K2);
+    }
+    for (int i = 0; i < f2->n; ++i) if (has2[i]) {
+        p2[i] = w.make_point(u2[i], v2[i], 1.f, f2->descriptors + (size_t)i * 32, 1, maxd2[i], 0.f);
+        K2->mvpMapPoints[i] = p2[i];
+        p2[i]->mObservations[K2] = i;
+        if (level2) level2[i] = lvl(p2[i], u2[i], v2[i], K1);
+    }
+    std::vector<MapPoint*> m12(f1->n, static_cast<MapPoint*>(nullptr));
+    for (int i = 0; i < f1->n; ++i) if (pre12[i] >= 0) m12[i] = p2[pre12[i]];
+    cv::Mat R12 = cv::Mat::eye(3, 3, CV_32F), t12 = cv::Mat::zeros(3, 1, CV_32F);
+    ORBmatcher matcher(0.75f, true);
+    const int n = matcher.SearchBySim3(K1, K2, m12, 1.0f, R12, t12, th);
+    for (int i = 0; i < f1->n; ++i) match12[i] = (pre12[i] >= 0 || !m12[i]) ? -1 : index_of(p2, m12[i]);
+    return n;
+}
+
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:242-305): n observations, one keyframe each.  mObservations is
+ * a std::map keyed by KeyFrame*: the keyframes are sorted by address and descriptor j goes to the j-th of them, so the
+ * reference walks the descriptors in the caller's order.  out32 = the descriptor the reference keeps. */
+void ref2_distinctive(const uint8_t* desc, int n, uint8_t* out32)
+{
+    std::lock_guard<std::mutex> g(g_lock);
+    World w;
+    static const uint8_t zero[32] = {0};
+    orbx_keypoint kp; std::memset(&kp, 0, sizeof(kp)); kp.x = 50; kp.y = 50; kp.size = 31; kp.class_id = -1;
+    orbm_frame f; std::memset(&f, 0, sizeof(f));
+    f.n = 1; f.keys_un = &kp; f.descriptors = zero; f.min_x = 0; f.max_x = 640; f.min_y = 0; f.max_y = 480;
+    MapPoint* p = w.make_point(0, 0, 1, zero, 0);
+    std::vector<KeyFrame*> ks;
+    for (int j = 0; j < n; ++j) ks.push_back(w.make_keyframe(&f, kUnitCam, eye4()));
+    std::sort(ks.begin(), ks.end());
+    for (int j = 0; j < n; ++j) {
+        std::memcpy(ks[j]->mDescriptors.data, desc + (size_t)j * 32, 32);      /* the member is const: its pixels are not */
+        p->mObservations[ks[j]] = 0;
+    }
+    p->nObs = n;
+    p->ComputeDistinctiveDescriptors();
+    std::memcpy(out32, p->mDescriptor.data, 32);
 }
 
 } // extern "C"

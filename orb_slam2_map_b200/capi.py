@@ -60,6 +60,7 @@ EXPORTS = [
     "orbx_get_candidates", "orbx_search_init_pairs", "orbx_extract_stereo_batch",
     "orbm_descriptor_distance", "orbm_search_for_initialization", "orbm_search_by_projection",
     "orbm_compute_stereo_matches", "orbm_knn2_device", "orbm_knn2_merge_device", "orbm_knn2_set_variant",
+    "orbm_measure_int_rates", "orbm_nccl_unique_id", "orbm_nccl_comm_create", "orbm_nccl_comm_destroy", "orbm_knn2_sharded",
     "orbx_cvt_gray", "orbx_depth_to_float", "orbx_undistort_points", "orbx_image_bounds", "orbx_frames_rgbd",
     "orbx_download_frame_front",
     "orbm_vocabulary_upload", "orbm_vocabulary_free", "orbm_bow_transform", "orbm_search_by_bow", "orbm_distinctive_descriptors",
@@ -127,6 +128,10 @@ def lib():
                                        C.c_void_p, C.c_void_p]
         L.orbm_knn2_merge_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p,
                                              C.c_void_p]
+        L.orbm_nccl_comm_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
+        L.orbm_nccl_comm_destroy.argtypes = [C.c_void_p]
+        L.orbm_knn2_sharded.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int32, C.c_int64,
+                                        C.c_void_p, C.c_void_p, C.c_void_p]
         _LIB = L
     return _LIB
 
@@ -455,6 +460,39 @@ def knn2_device(q_ptr, nq, db_ptr, ndb, offset, out_dist_ptr, out_idx_ptr, strea
 def knn2_merge_device(pd_ptr, pi_ptr, nparts, nq, od_ptr, oi_ptr, stream=None):
     check(lib().orbm_knn2_merge_device(C.c_void_p(pd_ptr), C.c_void_p(pi_ptr), nparts, nq, C.c_void_p(od_ptr),
                                        C.c_void_p(oi_ptr), C.c_void_p(stream) if stream else None))
+
+
+def measure_int_rates():
+    """orbm_measure_int_rates -> dict(popc, lop3, add: results/s; knn_mix: register-only compares/s)"""
+    r = (C.c_double * 4)()
+    check(lib().orbm_measure_int_rates(r))
+    return dict(popc=r[0], lop3=r[1], add=r[2], knn_mix=r[3])
+
+
+def nccl_unique_id() -> bytes:
+    """orbm_nccl_unique_id: rank 0 makes it, the other ranks receive its 128 bytes"""
+    buf = (C.c_uint8 * 128)()
+    check(lib().orbm_nccl_unique_id(buf))
+    return bytes(buf)
+
+
+def nccl_comm_create(uid: bytes, rank: int, nranks: int) -> int:
+    """orbm_nccl_comm_create on the current CUDA device -> ncclComm_t as an integer handle"""
+    buf = (C.c_uint8 * 128).from_buffer_copy(uid)
+    comm = C.c_void_p()
+    check(lib().orbm_nccl_comm_create(buf, rank, nranks, C.byref(comm)))
+    return comm.value
+
+
+def nccl_comm_destroy(comm: int):
+    check(lib().orbm_nccl_comm_destroy(C.c_void_p(comm)))
+
+
+def knn2_sharded(comm, q_ptr, nq, shard_ptr, ndb_local, offset, out_dist_ptr, out_idx_ptr, stream=None, query_chunk=0):
+    """orbm_knn2_sharded: local scan + ncclAllGather + merge, chunked over the queries; comm None = single GPU"""
+    check(lib().orbm_knn2_sharded(C.c_void_p(comm) if comm else None, C.c_void_p(q_ptr), nq, C.c_void_p(shard_ptr), ndb_local,
+                                  offset, query_chunk, C.c_void_p(out_dist_ptr), C.c_void_p(out_idx_ptr),
+                                  C.c_void_p(stream) if stream else None))
 
 
 # ---- bag-of-words path (orbx_bow.cu) -------------------------------------------------------------------

@@ -184,6 +184,75 @@ knn2_merge_kernel(const uint16_t* __restrict__ partDist, const int* __restrict__
     *reinterpret_cast<int2*>(outIdx + 2 * q) = make_int2(k1 == ~0ull ? -1 : (int)(unsigned)k1, k2 == ~0ull ? -1 : (int)(unsigned)k2);
 }
 
+// =============================================================================================
+// Register-only rate probes ("measure it with a register-only POPC microbenchmark and use the
+// measured value as the denominator").  MB_ILP independent chains per thread, no memory traffic inside the loop:
+//   which 0  popc.b32                 -> POPC results per second
+//   which 1  lop3.b32                 -> LOP3 results per second
+//   which 2  add.u32                  -> integer adds per second
+//   which 3  K10's inner loop on register operands (popc8<V> of 8 XOR words + top-2 update, KNN_QPT queries per thread):
+//            Hamming compares per second when nothing but the integer pipes is in the way — the roofline of knn2_kernel
+// =============================================================================================
+#define MB_ILP 8
+__global__ void __launch_bounds__(256)
+int_rate_kernel(int which, int iters, uint32_t seed, uint32_t* __restrict__ sink)
+{
+    uint32_t a[MB_ILP];
+#pragma unroll
+    for (int i = 0; i < MB_ILP; ++i) a[i] = seed * (threadIdx.x + 1u) + 0x9e3779b9u * i;
+    const uint32_t b = seed ^ 0x5bd1e995u, c = seed * 3u + 1u;
+    if (which == 0) {
+        for (int it = 0; it < iters; ++it)
+#pragma unroll
+            for (int i = 0; i < MB_ILP; ++i) asm volatile("popc.b32 %0, %0;" : "+r"(a[i]));
+    } else if (which == 1) {
+        for (int it = 0; it < iters; ++it)
+#pragma unroll
+            for (int i = 0; i < MB_ILP; ++i) asm volatile("lop3.b32 %0, %0, %1, %2, 0x96;" : "+r"(a[i]) : "r"(b), "r"(c));
+    } else {
+        for (int it = 0; it < iters; ++it)
+#pragma unroll
+            for (int i = 0; i < MB_ILP; ++i) asm volatile("add.u32 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+    }
+    uint32_t r = 0;
+#pragma unroll
+    for (int i = 0; i < MB_ILP; ++i) r ^= a[i];
+    if (r == 0x12345u) sink[0] = r;                 // never true in practice: keeps the chains alive
+}
+
+template <int V>
+__global__ void __launch_bounds__(KNN_THREADS)
+knn_mix_kernel(int rows, uint32_t seed, int* __restrict__ sink)
+{
+    uint32_t qw[KNN_QPT][8];
+    Top2 best[KNN_QPT];
+#pragma unroll
+    for (int k = 0; k < KNN_QPT; ++k) {
+#pragma unroll
+        for (int w = 0; w < 8; ++w) qw[k][w] = seed * (threadIdx.x * 8u + w + 1u) + 0x85ebca6bu * k;
+        best[k].d1 = best[k].d2 = 257; best[k].i1 = best[k].i2 = -1;
+    }
+    uint32_t row[8];
+#pragma unroll
+    for (int w = 0; w < 8; ++w) row[w] = seed + 0x27d4eb2fu * w;
+#pragma unroll 2
+    for (int r = 0; r < rows; ++r) {
+        // the "database row" changes every iteration (one add per word: 2 adds per compare at KNN_QPT = 4) so that nothing hoists
+#pragma unroll
+        for (int w = 0; w < 8; ++w) row[w] += 0x9e3779b9u;
+#pragma unroll
+        for (int k = 0; k < KNN_QPT; ++k) {
+            const int d = popc8<V>(qw[k][0] ^ row[0], qw[k][1] ^ row[1], qw[k][2] ^ row[2], qw[k][3] ^ row[3],
+                                   qw[k][4] ^ row[4], qw[k][5] ^ row[5], qw[k][6] ^ row[6], qw[k][7] ^ row[7]);
+            top2_push(best[k], d, r);
+        }
+    }
+    int acc = 0;
+#pragma unroll
+    for (int k = 0; k < KNN_QPT; ++k) acc ^= best[k].d1 ^ best[k].i1 ^ best[k].d2 ^ best[k].i2;
+    if (acc == 0x7fffffff) sink[0] = acc;
+}
+
 static int g_knn_variant = 1;
 
 extern "C" {
@@ -243,6 +312,41 @@ int orbm_knn2_device(const uint8_t* queries, int64_t nq, const uint8_t* database
         ORBX_CUDA(cudaGetLastError());
         ORBX_CUDA(cudaFreeAsync(scratch, st));
     }
+    return ORBX_OK;
+}
+
+// rates[0..2]: popc / lop3 / add results per second (all SMs), rates[3]: register-only K10 compares per second with the
+// current popcount variant.  Synchronous; a few milliseconds.
+int orbm_measure_int_rates(double rates[4])
+{
+    if (!rates) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
+    int dev = 0, sms = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    ORBX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    uint32_t* sink = nullptr;
+    ORBX_CUDA(cudaMalloc((void**)&sink, 64));
+    cudaEvent_t e0, e1;
+    ORBX_CUDA(cudaEventCreate(&e0)); ORBX_CUDA(cudaEventCreate(&e1));
+    const int ctas = sms * 8, iters = 8192, rows = 16384;
+    for (int which = 0; which < 4; ++which) {
+        float best = 1e30f;
+        for (int rep = 0; rep < 4; ++rep) {                         // rep 0 = warm-up
+            ORBX_CUDA(cudaEventRecord(e0, 0));
+            if (which < 3) int_rate_kernel<<<ctas, 256>>>(which, iters, 12345u + rep, sink);
+            else if (g_knn_variant == 0) knn_mix_kernel<0><<<ctas, KNN_THREADS>>>(rows, 777u + rep, (int*)sink);
+            else if (g_knn_variant == 2) knn_mix_kernel<2><<<ctas, KNN_THREADS>>>(rows, 777u + rep, (int*)sink);
+            else knn_mix_kernel<1><<<ctas, KNN_THREADS>>>(rows, 777u + rep, (int*)sink);
+            ORBX_CUDA(cudaEventRecord(e1, 0));
+            ORBX_CUDA(cudaEventSynchronize(e1));
+            float ms = 0.f;
+            ORBX_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+            if (rep > 0) best = std::min(best, ms);
+        }
+        const double work = which < 3 ? (double)ctas * 256 * iters * MB_ILP : (double)ctas * KNN_THREADS * KNN_QPT * rows;
+        rates[which] = work / (best * 1e-3);
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(sink);
     return ORBX_OK;
 }
 

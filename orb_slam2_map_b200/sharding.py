@@ -51,9 +51,47 @@ def gather_top2(dist, idx, group=None):
     return pd, pi
 
 
-def knn2_sharded(queries, db_shard, shard_offset: int, group=None, stream=None):
-    """Config 5 on one rank: local brute-force top-2 on the CUDA shard, all_gather, device merge.
-    queries [nq,32] uint8 cuda, db_shard [n,32] uint8 cuda -> (dist [nq,2] int16, idx [nq,2] int32)."""
+class ShardComm:
+    """The NCCL communicator orbm_knn2_sharded runs on, made through the C ABI (orbm_nccl_unique_id /
+    orbm_nccl_comm_create): rank 0 draws the id, torch.distributed only carries its 128 bytes to the other ranks."""
+
+    def __init__(self, device, group=None):
+        import torch
+        import torch.distributed as dist_
+        from . import capi
+        self.rank, self.world = dist_.get_rank(group), dist_.get_world_size(group)
+        uid = torch.zeros(128, dtype=torch.uint8, device=device)
+        if self.rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(capi.nccl_unique_id()), dtype=torch.uint8))
+        dist_.broadcast(uid, src=0, group=group)
+        with torch.cuda.device(device):
+            self.comm = capi.nccl_comm_create(bytes(uid.cpu().numpy().tobytes()), self.rank, self.world)
+
+    def close(self):
+        from . import capi
+        if self.comm:
+            capi.nccl_comm_destroy(self.comm)
+            self.comm = None
+
+
+def knn2_sharded(queries, db_shard, shard_offset: int, comm: "ShardComm | None" = None, stream=None, query_chunk=0, out=None):
+    """Config 5 on one rank through ONE C-ABI call (orbm_knn2_sharded): local brute-force top-2 on the CUDA shard,
+    ncclAllGather of the 12-byte records and the device merge, chunked so that the exchange of a chunk overlaps the scan of
+    the next.  queries [nq,32] uint8 cuda, db_shard [n,32] uint8 cuda -> (dist [nq,2] int16, idx [nq,2] int32)."""
+    import torch
+    from . import capi
+    nq = queries.shape[0]
+    st = stream if stream is not None else torch.cuda.current_stream().cuda_stream
+    od, oi = out if out is not None else (torch.empty((nq, 2), dtype=torch.int16, device=queries.device),
+                                          torch.empty((nq, 2), dtype=torch.int32, device=queries.device))
+    capi.knn2_sharded(comm.comm if comm is not None else None, queries.data_ptr(), nq, db_shard.data_ptr(), db_shard.shape[0],
+                      shard_offset, od.data_ptr(), oi.data_ptr(), st, query_chunk)
+    return od, oi
+
+
+def knn2_sharded_torch(queries, db_shard, shard_offset: int, group=None, stream=None):
+    """The same exchange spelled with torch.distributed (any backend): used by the CPU (gloo) tests of the merge order and
+    as the cross-check of orbm_knn2_sharded on GPUs."""
     import torch
     from . import capi
     nq = queries.shape[0]

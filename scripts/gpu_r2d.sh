@@ -1,0 +1,15 @@
+# usage: gpu_r2d.sh <tag> <N>  (N GPUs) — sharded kNN test through the C ABI + torchrun bench at N ranks + host<->device copy topology
+T=${1:-r02d}; N=${2:-2}
+mkdir -p gpurun_out
+nvidia-smi topo -m > gpurun_out/${T}_topo.txt 2>&1
+timeout 600 python -m pytest tests/test_sharded_gpu.py -m gpu -x -q > gpurun_out/${T}_pytest_sharded.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/${T}_pytest_sharded.log
+tail -4 gpurun_out/${T}_pytest_sharded.log
+NCCL_DEBUG=INFO NCCL_DEBUG_SUBSYS=INIT,COLL timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29611 \
+    bench.py --gpus $N --steps 5 --warmup 3 > gpurun_out/${T}_bench_${N}.json 2> gpurun_out/${T}_bench_${N}.err; echo "bench rc=$?"
+grep -c "AllGather" gpurun_out/${T}_bench_${N}.err; grep -m3 "AllGather" gpurun_out/${T}_bench_${N}.err
+python - $T $N <<'PY'
+import json,sys
+d=json.loads(open(f'gpurun_out/{sys.argv[1]}_bench_{sys.argv[2]}.json').read().strip().splitlines()[-1])
+print('value',round(d['value']),'e2e',round(d['e2e']['value']),'ms/step',round(d['ms_per_step'],2), 'h2d', d['e2e'].get('h2d_gbs_measured'))
+h=d['hamming']; print({k:h[k] for k in ('value','per_gpu','nranks','ms','exchange_ms_alone','local_scan_cmp_s_per_gpu','efficiency_vs_n1')})
+PY

@@ -197,6 +197,96 @@ def case_proj_sim3(seed=0, th=10, dup=False, nq=900):
                 max_dist=max_dist, qdesc=qd, th=th)
 
 
+# ------------------------------------------------------------------------------------------------------------------
+# SURVEY §8(f) rows
+# ------------------------------------------------------------------------------------------------------------------
+def case_bow_transform(seed=0, k=6, depth=4, n=600):
+    voc = O.make_vocabulary(k=k, depth=depth, seed=seed)
+    r = np.random.default_rng(400 + seed)
+    pick = r.integers(1, voc["nnodes"], n)
+    feats = _noisy(voc["desc"][pick], r, flips=30, p=0.5)
+    feats[:8] = voc["desc"][pick[:8]]                      # exact node descriptors: distance ties between siblings' subtrees
+    return dict(kind="bow_transform", voc=voc, feats=feats)
+
+
+def _bow_sides(seed, voc, levelsup):
+    k1, d1, sf = _extracted(640, 480, 1000, seed, kind="seq")
+    k2, d2, _ = _extracted(640, 480, 1000, seed + 1, kind="seq")
+    r = np.random.default_rng(500 + seed)
+    out = []
+    for k, d in ((k1, d1), (k2, d2)):
+        _, w, nid = O.bow_transform(voc, d, levelsup)
+        flags = (w > 0).astype(np.uint8)                   # bit 0: the feature's word has a weight -> it is in mFeatVec
+        has = r.random(len(k)) < 0.65
+        bad = has & (r.random(len(k)) < 0.06)
+        flags |= (has & ~bad).astype(np.uint8) << 1
+        flags |= bad.astype(np.uint8) << 2
+        out.append(dict(kps=k, desc=d, w=640, h=480, scale=sf, node=nid, flags=flags))
+    return out
+
+
+def case_search_by_bow(variant, seed=0, nnratio=0.7, ori=True, levelsup=2, dup=False):
+    voc = O.make_vocabulary(k=5, depth=4, seed=7)
+    a, b = _bow_sides(seed, voc, levelsup)
+    if dup:
+        a = dict(a); b = dict(b)
+        a["desc"] = a["desc"].copy(); b["desc"] = b["desc"].copy()
+        a["desc"][::5] = a["desc"][0]; b["desc"][::7] = a["desc"][0]
+    return dict(kind="search_by_bow", variant=variant, a=a, b=b, nnratio=nnratio, ori=ori)
+
+
+def case_triangulation(seed=0, only_stereo=False, ori=True):
+    voc = O.make_vocabulary(k=5, depth=4, seed=7)
+    a, b = _bow_sides(seed, voc, 2)
+    r = np.random.default_rng(600 + seed)
+    for side in (a, b):
+        n = len(side["kps"])
+        side["u_right"] = np.where(r.random(n) < 0.5, side["kps"]["x"] - 20.0, -1.0).astype(F32)
+    # the synthetic sequence translates by (1, 0.5) px per frame: F12 = [t]x, epipolar lines parallel to t
+    f12 = np.array([[0, 0, 0.5], [0, 0, -1.0], [-0.5, 1.0, 0]], F32)
+    return dict(kind="triangulation", a=a, b=b, f12=f12, epipole=(F32(320.5), F32(240.25)), only_stereo=only_stereo, ori=ori)
+
+
+def case_fuse(variant, seed=0, th=3.0, dup=False, nq=900, bf=40.0):
+    frame, r, src, u, v, qd, level, angle, slot_state, nobs = _proj_base(seed, nq, dup)
+    level = np.maximum(level, 0)
+    max_dist = _max_dist_for_level(u, v, level, frame["scale"])
+    return dict(kind="fuse", variant=variant, frame=frame, bf=bf, u=u, v=v, level=level, max_dist=max_dist, qdesc=qd,
+                nobs=np.maximum(nobs, 1), th=th)
+
+
+def case_sim3(seed=0, th=7.5):
+    k1, d1, sf = _extracted(640, 480, 1000, seed, kind="seq")
+    k2, d2, _ = _extracted(640, 480, 1000, seed + 1, kind="seq")
+    r = np.random.default_rng(700 + seed)
+    sides = []
+    for k in (k1, k2):
+        n = len(k)
+        has = (r.random(n) < 0.8).astype(np.uint8)
+        u = (k["x"] + r.normal(0, 1.5, n)).astype(F32)
+        v = (k["y"] + r.normal(0, 1.5, n)).astype(F32)
+        lv = k["octave"].astype(np.int32)
+        sides.append((has, u, v, lv, _max_dist_for_level(u, v, lv, sf)))
+    pre12 = np.full(len(k1), -1, np.int32)
+    cand = np.nonzero(sides[0][0])[0][::15]
+    tgt = np.nonzero(sides[1][0])[0]
+    pre12[cand] = r.choice(tgt, len(cand), replace=False)
+    return dict(kind="sim3", f1=dict(kps=k1, desc=d1, w=640, h=480, scale=sf), f2=dict(kps=k2, desc=d2, w=640, h=480, scale=sf),
+                s1=sides[0], s2=sides[1], pre12=pre12, th=th)
+
+
+def case_distinctive(seed=0):
+    r = np.random.default_rng(800 + seed)
+    groups = []
+    for n in [1, 2, 3, 4, 5, 8, 13, 21, 40, 64]:
+        base = r.integers(0, 256, 32, dtype=np.uint8)
+        g = _noisy(np.repeat(base[None], n, 0), r, flips=40, p=0.5)
+        groups.append(g)
+    groups.append(np.repeat(groups[3][:1], 6, 0))                 # all equal: every median 0, first wins
+    g = groups[5].copy(); g[3] = g[1]; groups.append(g)           # duplicated rows: ties between medians
+    return dict(kind="distinctive", groups=groups)
+
+
 def _queries(n):
     q = np.zeros(n, O.PROJ_DTYPE)
     q["level_lo"] = -1
@@ -247,6 +337,36 @@ def run_reference(c):
         n, a, lv = R.proj_sim3(_frame(c), c["matched_state"], c["u"], c["v"], c["max_dist"], c["qdesc"], c["th"])
         assert np.array_equal(lv, c["level"])
         return dict(n=np.int32(n), assigned=np.where(a == -2, -1, a).astype(np.int32))
+    if k == "bow_transform":
+        import ref2_lib
+        voc = ref2_lib.RefVocabulary(c["voc"])
+        out = {}
+        for ls in range(0, c["voc"]["depth"] + 2):
+            w, val, nid = voc.transform(c["feats"], ls)
+            bw, bv, fn, ff = voc.transform_all(c["feats"], ls)
+            out.update({f"word{ls}": w, f"weight{ls}": val, f"node{ls}": nid, f"bow_word{ls}": bw, f"bow_value{ls}": bv,
+                        f"fv_node{ls}": fn, f"fv_feat{ls}": ff})
+        return out
+    if k == "search_by_bow":
+        a, b = c["a"], c["b"]
+        n, ma, mb = R.search_by_bow(c["variant"], _frame(c, "a"), a["node"], a["flags"], _frame(c, "b"), b["node"], b["flags"], c["nnratio"], c["ori"])
+        return dict(n=np.int32(n), match_a=ma, match_b=mb)
+    if k == "triangulation":
+        a, b = c["a"], c["b"]
+        n, m = R.search_for_triangulation(_frame(c, "a"), a["node"], a["flags"], _frame(c, "b"), b["node"], b["flags"], c["f12"], c["epipole"],
+                                          c["only_stereo"], c["ori"])
+        return dict(n=np.int32(n), matches12=m)
+    if k == "fuse":
+        n, bi, lv = R.fuse(c["variant"], _frame(c), c["bf"], c["u"], c["v"], c["max_dist"], c["qdesc"], c["nobs"], c["th"])
+        assert np.array_equal(lv, c["level"])
+        return dict(n=np.int32(n), best_idx=bi)
+    if k == "sim3":
+        (h1, u1, v1, l1, m1), (h2, u2, v2, l2, m2) = c["s1"], c["s2"]
+        n, m, lv1, lv2 = R.search_by_sim3(_frame(c, "f1"), _frame(c, "f2"), h1, u1, v1, m1, h2, u2, v2, m2, c["pre12"], c["th"])
+        assert np.array_equal(lv1[h1 > 0], l1[h1 > 0]) and np.array_equal(lv2[h2 > 0], l2[h2 > 0])
+        return dict(n=np.int32(n), match12=m)
+    if k == "distinctive":
+        return dict(desc=np.stack([R.distinctive(g) for g in c["groups"]]))
     raise KeyError(k)
 
 
@@ -264,6 +384,80 @@ def run_oracle(c):
     if k == "stereo":
         ur, dp, _ = O.compute_stereo_matches(c["kl"], c["dl"], c["kr"], c["dr"], c["pl"], c["pr"], c["scale"], c["inv_scale"], c["bf"], c["fx"])
         return dict(u_right=ur, depth=dp)
+    if k == "bow_transform":
+        out = {}
+        for ls in range(0, c["voc"]["depth"] + 2):
+            w, val, nid = O.bow_transform(c["voc"], c["feats"], ls)
+            # TemplatedVocabulary::transform (TemplatedVocabulary.h:1140-1218), TF_IDF + L1: BowVector[word] += weight and
+            # FeatureVector[node].push_back(i) for the features whose word has a weight, then the L1 normalisation
+            use = val > 0
+            words = np.unique(w[use])
+            vals = np.zeros(len(words), np.float64)
+            for i in np.nonzero(use)[0]:
+                vals[np.searchsorted(words, w[i])] += val[i]
+            norm = 0.0
+            for x in vals:
+                norm += abs(x)
+            if norm > 0.0:
+                vals = vals / norm
+            order = np.lexsort((np.nonzero(use)[0], nid[use]))
+            out.update({f"word{ls}": w, f"weight{ls}": val, f"node{ls}": nid, f"bow_word{ls}": words.astype(np.uint32), f"bow_value{ls}": vals,
+                        f"fv_node{ls}": nid[use][order].astype(np.uint32), f"fv_feat{ls}": np.nonzero(use)[0][order].astype(np.uint32)})
+        return out
+    if k == "search_by_bow":
+        a, b = c["a"], c["b"]
+        fl = lambda x: (x["flags"] & 3).astype(np.uint8)          # flat form: bit 1 = holds a map point that is NOT bad
+        n, ma, mb = O.search_by_bow(c["variant"], a["desc"], a["kps"]["angle"], a["node"], fl(a), b["desc"], b["kps"]["angle"], b["node"], fl(b),
+                                    c["nnratio"], c["ori"])
+        return dict(n=np.int32(n), match_a=ma, match_b=mb)
+    if k == "triangulation":
+        a, b = c["a"], c["b"]
+        # KeyFrame::GetMapPoint(idx) != NULL is all the reference asks (bad points included)
+        fl = lambda x: ((x["flags"] & 1) | (((x["flags"] & 6) != 0).astype(np.uint8) << 1)).astype(np.uint8)
+        mk = lambda x: O.KeyFrameData(x["kps"], x["desc"], 640, 480, u_right=x["u_right"], scale_factors=x["scale"],
+                                      level_sigma2=(x["scale"] * x["scale"]).astype(F32), node_id=x["node"], flags=fl(x))
+        n, m = O.search_for_triangulation(mk(a), mk(b), c["f12"], c["epipole"], c["only_stereo"], c["ori"])
+        return dict(n=np.int32(n), matches12=m)
+    if k == "fuse":
+        fr = c["frame"]
+        sf = fr["scale"]
+        kf = O.KeyFrameData(fr["kps"], fr["desc"], 640, 480, u_right=fr["u_right"], scale_factors=sf, level_sigma2=(sf * sf).astype(F32))
+        u, v = c["u"], c["v"]
+        keep = (u >= 0) & (u < 640) & (v >= 0) & (v < 480)          # KeyFrame::IsInImage
+        q = _queries(int(keep.sum()))
+        lv = c["level"][keep]
+        q["u"] = u[keep]; q["v"] = v[keep]
+        q["radius"] = (F32(c["th"]) * sf[lv]).astype(F32)
+        q["u_right"] = (u[keep] - F32(c["bf"])).astype(F32)
+        q["level_lo"] = lv - 1; q["level_hi"] = lv
+        bi, bd = O.fuse(c["variant"], kf, q, c["qdesc"][keep])
+        out = np.full(len(u), -1, np.int32)
+        out[keep] = bi
+        return dict(n=np.int32((bi >= 0).sum()), best_idx=out)
+    if k == "sim3":
+        (h1, u1, v1, l1, m1), (h2, u2, v2, l2, m2) = c["s1"], c["s2"]
+        f1, f2 = c["f1"], c["f2"]
+        sf = f1["scale"]
+        mk = lambda x: O.KeyFrameData(x["kps"], x["desc"], 640, 480, scale_factors=sf, level_sigma2=(sf * sf).astype(F32))
+        pre = c["pre12"]
+        done2 = np.zeros(len(h2), bool); done2[pre[pre >= 0]] = True
+        def side(has, u, v, lv, skip):
+            keep = (has > 0) & ~skip & (u >= 0) & (u < 640) & (v >= 0) & (v < 480)
+            idx = np.nonzero(keep)[0].astype(np.int32)
+            q = _queries(len(idx))
+            q["u"] = u[idx]; q["v"] = v[idx]
+            q["radius"] = (F32(c["th"]) * sf[lv[idx]]).astype(F32)
+            q["level_lo"] = lv[idx] - 1; q["level_hi"] = lv[idx]
+            return q, idx
+        q12, i1 = side(h1, u1, v1, l1, pre >= 0)
+        q21, i2 = side(h2, u2, v2, l2, done2)
+        n, m = O.search_by_sim3(mk(f1), mk(f2), q12, f1["desc"][i1], i1, q21, f2["desc"][i2], i2)
+        return dict(n=np.int32(n), match12=m)
+    if k == "distinctive":
+        off = np.cumsum([0] + [len(g) for g in c["groups"]]).astype(np.int32)
+        alld = np.concatenate(c["groups"])
+        idx, _ = O.distinctive_descriptors(alld, off)
+        return dict(desc=np.stack([g[i] for g, i in zip(c["groups"], idx)]))
     f = _frame(c)
     sf = c["frame"]["scale"]
     b = c["frame"].get("bounds") or (0.0, float(c["frame"]["w"]), 0.0, float(c["frame"]["h"]))
@@ -357,4 +551,19 @@ CASES = {
     "proj_keyframe_dup_noori": lambda: case_proj_keyframe(1, 15.0, 100, ori=False, dup=True),
     "proj_sim3": lambda: case_proj_sim3(0, 10),
     "proj_sim3_dup": lambda: case_proj_sim3(1, 15, dup=True),
+    "bow_transform": lambda: case_bow_transform(0),
+    "bow_transform_k9": lambda: case_bow_transform(1, k=9, depth=3),
+    "search_by_bow_kf_frame": lambda: case_search_by_bow(0, 0, 0.7, True),
+    "search_by_bow_kf_frame_dup_noori": lambda: case_search_by_bow(0, 1, 0.9, False, dup=True),
+    "search_by_bow_kf_kf": lambda: case_search_by_bow(1, 0, 0.75, True),
+    "search_by_bow_kf_kf_dup": lambda: case_search_by_bow(1, 2, 0.8, True, levelsup=3, dup=True),
+    "triangulation": lambda: case_triangulation(0),
+    "triangulation_only_stereo_noori": lambda: case_triangulation(1, only_stereo=True, ori=False),
+    "fuse_mappoints": lambda: case_fuse(0, 0, 3.0),
+    "fuse_mappoints_dup": lambda: case_fuse(0, 1, 4.0, dup=True),
+    "fuse_sim3": lambda: case_fuse(1, 0, 4.0),
+    "fuse_sim3_dup": lambda: case_fuse(1, 2, 3.0, dup=True),
+    "search_by_sim3": lambda: case_sim3(0),
+    "search_by_sim3_th12": lambda: case_sim3(2, 12.0),
+    "distinctive": lambda: case_distinctive(0),
 }

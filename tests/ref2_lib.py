@@ -117,3 +117,84 @@ def proj_sim3(kf: O.FrameData, matched_state, u, v, max_dist, qdesc, th):
     n = lib().ref2_proj_sim3(C.byref(kf.c), _p(args[0]), C.c_int(nq), _p(args[1]), _p(args[2]), _p(args[3]),
                              _p(args[4]), C.c_int(th), _p(a), _p(lv))
     return n, a[:kf.c.n].copy(), lv[:nq].copy()
+
+
+# ---- SURVEY §8(f) rows ------------------------------------------------------------------------------------------
+class RefVocabulary:
+    """ORBVocabulary built by the reference's own loadFromTextFile from the flat synthetic tree of oracle_lib.make_vocabulary"""
+
+    def __init__(self, voc, tmp_path="/tmp/orbx_ref2_voc.txt"):
+        n = voc["nnodes"]
+        parent = np.zeros(n, np.int32)
+        for p in range(n):
+            b, c = int(voc["child_begin"][p]), int(voc["child_count"][p])
+            parent[voc["children"][b:b + c]] = p
+        leaf = (voc["child_count"] == 0).astype(np.uint8)
+        L = lib()
+        L.ref2_voc_create.restype = C.c_void_p
+        self.keep = (parent, leaf, _u8(voc["desc"]), np.ascontiguousarray(voc["weight"], np.float64))
+        self.h = C.c_void_p(L.ref2_voc_create(C.c_int(voc["k"]), C.c_int(voc["depth"]), C.c_int(n), _p(parent), _p(leaf), _p(self.keep[2]),
+                                             _p(self.keep[3]), tmp_path.encode()))
+        assert self.h.value, "the reference's loadFromTextFile rejected the vocabulary"
+
+    def __del__(self):
+        if getattr(self, "h", None) and self.h.value:
+            lib().ref2_voc_destroy(self.h)
+            self.h = None
+
+    def transform(self, feats, levelsup):
+        feats = _u8(feats)
+        n = len(feats)
+        w = np.zeros(n, np.uint32); val = np.zeros(n, np.float64); nid = np.zeros(n, np.uint32)
+        lib().ref2_voc_transform(self.h, _p(feats), C.c_int(n), C.c_int(levelsup), _p(w), _p(val), _p(nid))
+        return w, val, nid
+
+    def transform_all(self, feats, levelsup):
+        feats = _u8(feats)
+        n = len(feats)
+        bw = np.zeros(n, np.uint32); bv = np.zeros(n, np.float64); fn = np.zeros(n, np.uint32); ff = np.zeros(n, np.uint32)
+        nfv = C.c_int()
+        nb = lib().ref2_voc_transform_all(self.h, _p(feats), C.c_int(n), C.c_int(levelsup), _p(bw), _p(bv), _p(fn), _p(ff), C.byref(nfv))
+        return bw[:nb].copy(), bv[:nb].copy(), fn[:nfv.value].copy(), ff[:nfv.value].copy()
+
+
+def search_by_bow(variant, fa: O.FrameData, node_a, flags_a, fb: O.FrameData, node_b, flags_b, nnratio, check_ori):
+    ma = np.empty(max(fa.c.n, 1), np.int32); mb = np.empty(max(fb.c.n, 1), np.int32)
+    args = [np.ascontiguousarray(node_a, np.uint32), _u8(flags_a), np.ascontiguousarray(node_b, np.uint32), _u8(flags_b)]
+    n = lib().ref2_search_by_bow(C.c_int(variant), C.byref(fa.c), _p(args[0]), _p(args[1]), C.byref(fb.c), _p(args[2]), _p(args[3]),
+                                 C.c_float(nnratio), C.c_int(int(check_ori)), _p(ma), _p(mb))
+    return n, ma[:fa.c.n].copy(), mb[:fb.c.n].copy()
+
+
+def search_for_triangulation(f1: O.FrameData, node1, flags1, f2: O.FrameData, node2, flags2, f12, epipole, only_stereo, check_ori):
+    m = np.empty(max(f1.c.n, 1), np.int32)
+    F = _f32(f12).reshape(9)
+    args = [np.ascontiguousarray(node1, np.uint32), _u8(flags1), np.ascontiguousarray(node2, np.uint32), _u8(flags2)]
+    n = lib().ref2_search_for_triangulation(C.byref(f1.c), _p(args[0]), _p(args[1]), C.byref(f2.c), _p(args[2]), _p(args[3]), _p(F),
+                                            C.c_float(epipole[0]), C.c_float(epipole[1]), C.c_int(int(only_stereo)),
+                                            C.c_int(int(check_ori)), _p(m))
+    return n, m[:f1.c.n].copy()
+
+
+def fuse(variant, kf: O.FrameData, bf, u, v, max_dist, qdesc, nobs, th):
+    nq = len(u)
+    bi = np.empty(max(nq, 1), np.int32); lv = np.empty(max(nq, 1), np.int32)
+    args = [_f32(u), _f32(v), _f32(max_dist), _u8(qdesc), _i32(nobs)]
+    n = lib().ref2_fuse(C.c_int(variant), C.byref(kf.c), C.c_float(bf), C.c_int(nq), _p(args[0]), _p(args[1]), _p(args[2]), _p(args[3]),
+                        _p(args[4]), C.c_float(th), _p(bi), _p(lv))
+    return n, bi[:nq].copy(), lv[:nq].copy()
+
+
+def search_by_sim3(f1: O.FrameData, f2: O.FrameData, has1, u1, v1, maxd1, has2, u2, v2, maxd2, pre12, th):
+    m = np.empty(max(f1.c.n, 1), np.int32)
+    l1 = np.full(max(f1.c.n, 1), -1, np.int32); l2 = np.full(max(f2.c.n, 1), -1, np.int32)
+    args = [_u8(has1), _f32(u1), _f32(v1), _f32(maxd1), _u8(has2), _f32(u2), _f32(v2), _f32(maxd2), _i32(pre12)]
+    n = lib().ref2_search_by_sim3(C.byref(f1.c), C.byref(f2.c), *[_p(a) for a in args], C.c_float(th), _p(m), _p(l1), _p(l2))
+    return n, m[:f1.c.n].copy(), l1[:f1.c.n].copy(), l2[:f2.c.n].copy()
+
+
+def distinctive(desc):
+    desc = _u8(desc)
+    out = np.zeros(32, np.uint8)
+    lib().ref2_distinctive(_p(desc), C.c_int(len(desc)), _p(out))
+    return out
