@@ -213,21 +213,125 @@ def oracle_mod():
     return oracle_lib
 
 
-def ref_lib():
-    """oracle/_ref: the UNMODIFIED reference ORBextractor.cc over the cv shim, if it was built."""
-    p = os.path.join(ROOT, "oracle", "_ref", "libref_orbextractor.so")
+def cpu_level():
+    """highest x86-64 micro-architecture level of this host among the ones oracle/Makefile builds (v4 = AVX-512, v3 = AVX2+FMA)"""
+    try:
+        flags = set(open("/proc/cpuinfo").read().split("flags", 1)[1].split("\n", 1)[0].split())
+    except Exception:
+        return None
+    if {"avx512f", "avx512bw", "avx512cd", "avx512dq", "avx512vl"} <= flags:
+        return "v4"
+    if {"avx2", "fma", "bmi2", "movbe"} <= flags:
+        return "v3"
+    return None
+
+
+def ref_lib(fast=False):
+    """oracle/_ref: the UNMODIFIED reference ORBextractor.cc over the cv shim, if it was built.  fast: the -O3 -march build
+    ("as the reference compiles it", timing only) for this host's level, else None."""
+    name = "libref_orbextractor.so"
+    if fast:
+        lvl = cpu_level()
+        if lvl is None:
+            return None
+        name = f"libref_orbextractor_o3{lvl}.so"
+    p = os.path.join(ROOT, "oracle", "_ref", name)
     if not os.path.exists(p):
         return None
     L = C.CDLL(p)
     L.ref_extract_match_many.restype = C.c_int64
+    L.ref_extractor_create.restype = C.c_void_p
     return L
 
 
-def cpu_extract_match(frames: np.ndarray, nthreads: int, use_ref: bool, window: int | None = None):
+def cpu_single_thread_ms(frames: np.ndarray, fast=False):
+    """Per-frame times (ms) of ORBextractor::operator() of oracle/_ref on ONE thread, one call per frame — the way ORB-SLAM2
+    runs it (Frame::ExtractORB, src/Frame.cc:247-253)."""
+    L = ref_lib(fast)
+    if L is None:
+        return None
+    O = oracle_mod()
+    p = O.Params(PARAMS["nfeatures"], PARAMS["scale"], PARAMS["nlevels"], PARAMS["ini_th"], PARAMS["min_th"])
+    e = C.c_void_p(L.ref_extractor_create(C.byref(p)))
+    cap = PARAMS["nfeatures"] + 64 * PARAMS["nlevels"] + 64
+    kps = np.zeros(cap, O.KP_DTYPE); desc = np.zeros((cap, 32), np.uint8)
+    out = []
+    for i in range(len(frames)):
+        f = frames[i]
+        t0 = time.perf_counter()
+        L.ref_extract(e, f.ctypes.data_as(C.c_void_p), C.c_int(f.shape[1]), C.c_int(f.shape[0]), C.c_size_t(f.strides[0]),
+                      kps.ctypes.data_as(C.c_void_p), desc.ctypes.data_as(C.c_void_p), C.c_int(cap))
+        out.append((time.perf_counter() - t0) * 1e3)
+    L.ref_extractor_destroy(e)
+    return out
+
+
+def cv2_primitives_ms(frames: np.ndarray):
+    """Single-thread time per frame of the REAL OpenCV primitives the reference calls (SIMD build of the cv2 wheel, cv2.setNumThreads(1)):
+    7 x cv::resize, 8 x GaussianBlur(7x7, 2) and one cv::FAST call per 30-px grid cell at iniThFAST (+ minThFAST on empty cells), on
+    the same frames: the OpenCV-dependent part of ORBextractor::operator() when the reference is linked against OpenCV instead of
+    the scalar models behind oracle/ref_shim.  Excludes the quadtree, IC_Angle and the descriptors (the reference's own C++)."""
+    try:
+        import cv2
+    except Exception:
+        return None
+    cv2.setNumThreads(1)
+    sizes = level_sizes(W, H, PARAMS["nlevels"], PARAMS["scale"])
+    det_ini = cv2.FastFeatureDetector_create(PARAMS["ini_th"], True)
+    det_min = cv2.FastFeatureDetector_create(PARAMS["min_th"], True)
+    out = []
+    for f in frames:
+        t0 = time.perf_counter()
+        levels = [f]
+        for (w, h) in sizes[1:]:
+            levels.append(cv2.resize(levels[-1], (w, h), interpolation=cv2.INTER_LINEAR))
+        t1 = time.perf_counter()
+        for lv in levels:
+            cv2.GaussianBlur(lv, (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101)
+        t2 = time.perf_counter()
+        ncell = 0
+        for lv in levels:
+            h, w = lv.shape
+            minb, maxbx, maxby = 16, w - 16, h - 16
+            ncols, nrows = int((maxbx - minb) / 30), int((maxby - minb) / 30)
+            if ncols <= 0 or nrows <= 0:
+                continue
+            wc, hc = -(-(maxbx - minb) // ncols), -(-(maxby - minb) // nrows)
+            for i in range(nrows):
+                y0 = minb + i * hc
+                if y0 >= maxby - 3:
+                    continue
+                y1 = min(y0 + hc + 6, maxby)
+                for j in range(ncols):
+                    x0 = minb + j * wc
+                    if x0 >= maxbx - 6:
+                        continue
+                    x1 = min(x0 + wc + 6, maxbx)
+                    cell = lv[y0:y1, x0:x1]
+                    ncell += 1
+                    if not det_ini.detect(cell):
+                        det_min.detect(cell)
+        t3 = time.perf_counter()
+        for lv in levels:                       # the same detector on whole levels: FAST's SIMD cost without ~1000 binding calls
+            det_ini.detect(lv[16:-16, 16:-16])
+        t4 = time.perf_counter()
+        out.append(((t1 - t0) * 1e3, (t2 - t1) * 1e3, (t3 - t2) * 1e3, (t4 - t3) * 1e3, ncell))
+    a = np.array(out)
+    med = np.median(a[:, :4], axis=0)
+    return {"resize_ms": float(med[0]), "blur_ms": float(med[1]), "fast_cells_ms": float(med[2]), "fast_whole_levels_ms": float(med[3]),
+            "total_ms": float(np.median(a[:, :3].sum(axis=1))), "total_with_whole_level_fast_ms": float(np.median(a[:, [0, 1, 3]].sum(axis=1))),
+            "fast_cells_per_frame": int(a[0, 4]), "frames": len(frames), "cv2_version": cv2.__version__,
+            "note": "fast_cells_ms goes through the Python binding once per cell (an upper bound of the C++ calls); fast_whole_levels_ms is one "
+                    "iniThFAST call per level (a lower bound: no minThFAST retry, no per-cell NMS borders)"}
+
+
+def cpu_extract_match(frames: np.ndarray, nthreads: int, use_ref: bool, window: int | None = None, fast=False):
     """-> (seconds, kind). frames: [n,h,w] uint8 host."""
     O = oracle_mod()
     p = O.Params(PARAMS["nfeatures"], PARAMS["scale"], PARAMS["nlevels"], PARAMS["ini_th"], PARAMS["min_th"])
-    L = ref_lib() if use_ref else None
+    L = ref_lib(fast) if use_ref else None
+    if fast and L is None:
+        return None, None
     frames = np.ascontiguousarray(frames)
     n, h, w = frames.shape
     tm, nc = C.c_int64(), C.c_uint64()
@@ -252,11 +356,14 @@ def run_reference(args):
         sample = max(cores, 8)
     win = 0 if hd else None           # window 0: no candidates, i.e. extraction only
     frames = synth.frame_sequence(sample, W, H, seed=0)
+    # the build the reference's own CMakeLists asks for (-O3 -march=native, here the host's x86-64 level) when it exists for this
+    # CPU; the -O2 parity build otherwise
+    fast = ref_lib(fast=True) is not None
     for _ in range(args.warmup):
-        cpu_extract_match(frames[:max(cores, 8)], cores, True, win)
+        cpu_extract_match(frames[:max(cores, 8)], cores, True, win, fast=fast)
     t, kind = 0.0, "port"
     for _ in range(args.steps):
-        dt, kind = cpu_extract_match(frames, cores, True, win)
+        dt, kind = cpu_extract_match(frames, cores, True, win, fast=fast)
         t += dt
     fps = sample * args.steps / t
     line = {
@@ -266,8 +373,9 @@ def run_reference(args):
         "config": {"workload": (f"configs[3]: {W}x{H} frames, nFeatures {PARAMS['nfeatures']}, extraction only" if hd else
                                 "configs[1]: 640x480 frames, nFeatures 1000, extract + consecutive-frame SearchForInitialization"),
                    "frames_per_step": sample,
-                   "implementation": "reference src/ORBextractor.cc compiled unmodified (oracle/_ref) + oracle SearchForInitialization"
-                                     if kind == "reference" else "oracle port"},
+                   "implementation": ("reference src/ORBextractor.cc compiled unmodified (oracle/_ref, " +
+                                      (f"-O3 -march=x86-64-{cpu_level()} as CMakeLists.txt:14-15 asks" if fast else "-O2 parity build") +
+                                      ") over the scalar cv models + oracle SearchForInitialization") if kind == "reference" else "oracle port"},
         "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": cores, "kind": kind,
                          "sample": f"{sample} frames + {sample - 1} pairs per step, one frame per thread"},
         "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -564,6 +672,103 @@ def run_rgbd(args):
     ex.close()
 
 
+def run_rgbd_single(args):
+    """The fork's main mode, one frame per call: Tracking::GrabImageRGBD + Frame::Frame(RGB-D) (src/Tracking.cc:300-339,
+    src/Frame.cc:136-189) through orbx_frame_rgbd — pageable RGB + 16-bit depth in, mvKeys / mvKeysUn / descriptors / mvuRight /
+    mvDepth out.  CPU side, one thread: the oracle's cvtColor + the reference's own ORBextractor.cc (oracle/_ref) +
+    undistortPoints + ComputeStereoFromRGBD."""
+    import torch
+    from orb_slam2_map_b200 import capi, synth
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local)
+    NF = 32
+    gray = synth.frame_sequence(NF, W, H, seed=0)
+    rng = np.random.default_rng(3)
+    color = np.stack([np.clip(gray.astype(np.int32) + rng.integers(-20, 21, gray.shape), 0, 255) for _ in range(3)], axis=-1).astype(np.uint8)
+    depth = rng.integers(0, 30000, (NF, H, W), dtype=np.uint16)
+    factor = float(np.float32(1.0) / np.float32(5000.0))
+    tum1 = dict(fx=517.306408, fy=516.469215, cx=318.643040, cy=255.313989, k1=0.262383, k2=-0.953104, p1=-0.005358, p2=0.002628, k3=1.163314, bf=40.0)
+    cam = capi.Camera(**tum1)
+    ex = capi.Extractor(**PARAMS, max_width=W, max_height=H, chunk_frames=1, result_slots=1, device=local)
+    L = capi.lib()
+    cap = ex.reserve_shape(W, H)
+    kps = np.zeros(cap, capi.KP_DTYPE); kun = np.zeros(cap, capi.KP_DTYPE); desc = np.zeros((cap, 32), np.uint8)
+    ur = np.zeros(cap, np.float32); z = np.zeros(cap, np.float32); b = np.zeros(4, np.float32); n = C.c_int(0)
+    P = lambda a: a.ctypes.data_as(C.c_void_p)
+
+    def call(c, d):
+        capi.check(L.orbx_frame_rgbd(ex.h, P(c), 3, 1, C.c_size_t(W * 3), P(d), 1, C.c_float(factor), C.c_size_t(W * 2), W, H, C.byref(cam),
+                                     P(kps), P(kun), P(desc), P(ur), P(z), cap, C.byref(n), P(b)))
+
+    def measure(cs, ds, calls):
+        for i in range(40):
+            call(cs[i % NF], ds[i % NF])
+        lat = np.empty(calls)
+        for i in range(calls):
+            t0 = time.perf_counter()
+            call(cs[i % NF], ds[i % NF])
+            lat[i] = time.perf_counter() - t0
+        return lat
+
+    calls = max(args.steps, 1) * 200
+    clocks = ClockSampler(local); clocks.start()
+    t_all = time.perf_counter()
+    lat = measure(color, depth, calls)
+    t_all = time.perf_counter() - t_all
+    clk = clocks.stop()
+    pc = torch.empty(color.shape, dtype=torch.uint8, pin_memory=True); pc.copy_(torch.from_numpy(color))
+    pd = torch.empty(depth.shape, dtype=torch.uint16, pin_memory=True); pd.copy_(torch.from_numpy(depth))
+    lat_p = measure(pc.numpy(), pd.numpy(), calls)
+    # the batch entry point called with one frame (the round-1 way): plain launches, three downloads
+    def old(i):
+        ex.frames_rgbd(color[i % NF:i % NF + 1], depth[i % NF:i % NF + 1], cam, rgb_order=True, depth_factor=factor)
+        ex.download(0, 1); ex.download_frame_front(0, 1)
+    for i in range(10):
+        old(i)
+    lat_o = np.empty(100)
+    for i in range(100):
+        t0 = time.perf_counter(); old(i); lat_o[i] = time.perf_counter() - t0
+    med = float(np.median(lat)) * 1e6
+    line = {"metric": "RGB-D single-frame latency (640x480 RGB + 16-bit depth, 1000 kp: GrabImageRGBD + Frame front)", "value": med, "unit": "us/frame",
+            "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_all / (calls + 40) * 1e3, "higher_is_better": False,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "one RGB-D frame per call through orbx_frame_rgbd: pageable colour + depth in, mvKeys, mvKeysUn, descriptors, "
+                                   "mvuRight, mvDepth out (CUDA-graph replay of the extractor, one synchronisation)",
+                       "calls": calls, "distinct_frames": NF, "keypoints": int(n.value), "l2_policy": "latency line: one frame fits L2 by definition"},
+            "clocks": clk,
+            "latency_us": {"median": med, "p10": float(np.percentile(lat, 10)) * 1e6, "p90": float(np.percentile(lat, 90)) * 1e6,
+                           "p99": float(np.percentile(lat, 99)) * 1e6, "pinned_source_median": float(np.median(lat_p)) * 1e6,
+                           "batch_entry_point_one_frame_median": float(np.median(lat_o)) * 1e6},
+            "e2e": {"value": med, "unit": "us/frame", "h2d_bytes_per_step": W * H * 5, "d2h_bytes_per_step": cap * (28 + 28 + 32 + 8) + 8},
+            "gpu_launches": (calls + 40) * (1 + PARAMS["nlevels"] - 1 + 3 * PARAMS["nlevels"] + 1 + 2)}
+    if not args.no_cpu:
+        O = oracle_mod()
+        camv = np.array([tum1[k] for k in ("fx", "fy", "cx", "cy")], np.float32)
+        dist = np.array([tum1[k] for k in ("k1", "k2", "p1", "p2", "k3")], np.float32)
+        ts = []
+        for i in range(24):
+            t0 = time.perf_counter()
+            g = O.cvt_gray(color[i % NF], True)
+            t1 = time.perf_counter()
+            ext = cpu_single_thread_ms(g[None], fast=False)[0]
+            t2 = time.perf_counter()
+            ko = kps[:int(n.value)]
+            xy = np.stack([ko["x"], ko["y"]], axis=1).astype(np.float32)
+            xyu = O.undistort_points(xy, camv, dist)
+            dflt = O.depth_to_float(depth[i % NF], factor)
+            O.stereo_from_rgbd(xy, xyu, dflt, tum1["bf"])
+            t3 = time.perf_counter()
+            ts.append(((t1 - t0) * 1e3 + ext + (t3 - t2) * 1e3, ext))
+        a = np.array(ts)
+        line["cpu_baseline"] = {"value": float(np.median(a[:, 0])) * 1e3, "unit": "us/frame", "cores": 1, "kind": "reference",
+                                "sample": "24 frames, one thread: oracle cvtColor + the reference's ORBextractor.cc (oracle/_ref, -O2 parity build: "
+                                          f"{float(np.median(a[:, 1])):.2f} ms of it) + oracle undistortPoints / convertTo / ComputeStereoFromRGBD"}
+    emit(line)
+    ex.close()
+
+
 def run_single(args):
     """BASELINE configs[0] / SURVEY 8(d) "Config 1": ONE 640x480 frame per call, the way Tracking uses the extractor
     (Frame::ExtractORB, src/Frame.cc:247-253): pageable host image in, host keypoints + descriptors out, through
@@ -665,7 +870,8 @@ def main():
     ap.add_argument("--frames", type=int, default=4096)
     ap.add_argument("--chunk", type=int, default=512)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--workload", default="frames", choices=["frames", "hd", "stereo", "knn", "rgbd", "single"],
+    ap.add_argument("--no-hamming", action="store_true", help="skip the config-5 leg of the default line (profiling runs)")
+    ap.add_argument("--workload", default="frames", choices=["frames", "hd", "stereo", "knn", "rgbd", "single", "rgbd_single"],
                     help="frames = BASELINE configs[1] (the graded line); hd = configs[3]; stereo = configs[2]; knn = configs[4]")
     ap.add_argument("--queries", type=int, default=262144, help="knn: queries per step (config 5 names 1M)")
     ap.add_argument("--db-per-gpu", type=int, default=2000000, help="knn: database rows per GPU (config 5: 16M over 8)")
@@ -698,6 +904,9 @@ def main():
         return
     if args.workload == "single":
         run_single(args)
+        return
+    if args.workload == "rgbd_single":
+        run_rgbd_single(args)
         return
 
     import torch
@@ -870,7 +1079,7 @@ def main():
 
     # ---- second half of the metric: Hamming cmp/s of the brute-force 2-NN kernel on this GPU (short run) ----
     # measured on every rank of this run through orbm_knn2_sharded (NCCL at N > 1), config 5 as named
-    if args.workload == "frames":
+    if args.workload == "frames" and not args.no_hamming:
         line["hamming"] = hamming_leg(dev, rank, world, stream)
 
     # ---- CPU baseline (rank 0, N=1 only): bounded sample of the same frames ----------------------
@@ -883,10 +1092,26 @@ def main():
             s1, sN = 4, max(cores, 8)
         tN, kind = cpu_extract_match(hnp[:sN], cores, True, win)
         t1, _ = cpu_extract_match(hnp[:s1], 1, True, win)
-        line["cpu_baseline"] = {"value": sN / tN, "unit": "frames/s", "cores": cores, "kind": kind,
-                                "sample": f"first {sN} frames (+{sN - 1} pairs), one frame per thread on {cores} threads; "
-                                          f"single-thread on {s1} frames: {s1 / t1:.2f} frames/s",
-                                "single_thread_value": s1 / t1}
+        cb = {"value": sN / tN, "unit": "frames/s", "cores": cores, "kind": kind,
+              "sample": f"first {sN} frames (+{sN - 1} pairs), one frame per thread on {cores} threads; "
+                        f"single-thread on {s1} frames: {s1 / t1:.2f} frames/s",
+              "single_thread_value": s1 / t1}
+        # "as the reference compiles it": the same unmodified ORBextractor.cc at -O3 -march=<this host's level> (timing only)
+        tF, _ = cpu_extract_match(hnp[:sN], cores, True, win, fast=True)
+        if tF:
+            cb["value_o3_native"] = sN / tF
+            cb["o3_native_build"] = f"-O3 -march=x86-64-{cpu_level()} (oracle/Makefile ref_fast), {cores} threads, same sample"
+        if args.workload == "frames":
+            # single thread, one operator() call per frame, median over 200 frames
+            n1 = min(200, F)
+            for key, fast in (("single_thread_median_ms", False), ("single_thread_median_ms_o3_native", True)):
+                ts = cpu_single_thread_ms(hnp[:n1], fast)
+                if ts:
+                    cb[key] = float(np.median(ts)); cb[key + "_frames"] = n1
+            prim = cv2_primitives_ms(hnp[:min(100, F)])
+            if prim:
+                cb["cv2_primitives_ms"] = prim
+        line["cpu_baseline"] = cb
     if rank == 0:
         emit(line)
     ex.close()

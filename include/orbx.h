@@ -325,6 +325,18 @@ int orbx_frames_rgbd(orbx_handle* h, const uint8_t* color, int channels, int rgb
                      size_t depth_frame_stride, size_t depth_row_stride, int width, int height, int nframes,
                      int on_device, const orbx_camera* cam, int first_slot);
 
+/* ONE RGB-D frame, host images in, the whole Frame front out — Tracking::GrabImageRGBD + Frame::Frame(RGB-D) for the image pair of
+ * one tracked frame (src/Tracking.cc:300-339, src/Frame.cc:136-189): the fork's main mode, built for latency like orbx_extract
+ * (pinned staging or in-place DMA of page-locked images, cvtColor straight into the extractor's level 0, the frame's captured
+ * CUDA graph, the depth map copied by the host while the GPU extracts, one batch of result copies, one synchronisation).
+ * Outputs (host, room for `capacity` keypoints, each may be NULL): kps = mvKeys, keys_un = mvKeysUn, desc = mDescriptors,
+ * u_right = mvuRight, depth_out = mvDepth, *n = N, bounds = mnMinX, mnMaxX, mnMinY, mnMaxY.  The frame also stays in slot 0 with
+ * its grid, so the matchers of this library can run on it.  Empty image -> outputs untouched. */
+int orbx_frame_rgbd(orbx_handle* h, const uint8_t* color, int channels, int rgb_order, size_t color_row_stride, const void* depth,
+                    int depth_is_u16, float depth_factor, size_t depth_row_stride, int width, int height, const orbx_camera* cam,
+                    orbx_keypoint* kps, orbx_keypoint* keys_un, uint8_t* desc, float* u_right, float* depth_out, int capacity, int* n,
+                    float bounds[4]);
+
 /* mvKeysUn (full KeyPoint records), mvuRight, mvDepth of slots first_slot ..; each output may be NULL.
  * keys_un: nframes*capacity records, u_right/depth: nframes*capacity floats, bounds: 4 floats. */
 int orbx_download_frame_front(orbx_handle* h, int first_slot, int nframes, orbx_keypoint* keys_un, float* u_right,

@@ -61,7 +61,7 @@ EXPORTS = [
     "orbm_descriptor_distance", "orbm_search_for_initialization", "orbm_search_by_projection",
     "orbm_compute_stereo_matches", "orbm_knn2_device", "orbm_knn2_merge_device", "orbm_knn2_set_variant",
     "orbm_measure_int_rates", "orbm_nccl_unique_id", "orbm_nccl_comm_create", "orbm_nccl_comm_destroy", "orbm_knn2_sharded",
-    "orbx_cvt_gray", "orbx_depth_to_float", "orbx_undistort_points", "orbx_image_bounds", "orbx_frames_rgbd",
+    "orbx_cvt_gray", "orbx_depth_to_float", "orbx_undistort_points", "orbx_image_bounds", "orbx_frames_rgbd", "orbx_frame_rgbd",
     "orbx_download_frame_front",
     "orbm_vocabulary_upload", "orbm_vocabulary_free", "orbm_bow_transform", "orbm_search_by_bow", "orbm_distinctive_descriptors",
     "orbm_search_for_triangulation", "orbm_fuse", "orbm_search_by_sim3", "orbm_generate_point_clouds", "orbx_pack_map_records", "orbx_extract_match_to_host",
@@ -312,6 +312,23 @@ class Extractor:
         check(lib().orbx_frames_rgbd(self.h, color.ctypes.data_as(C.c_void_p), ch, int(rgb_order), C.c_size_t(h * w * ch), C.c_size_t(w * ch),
                                      depth.ctypes.data_as(C.c_void_p), int(is16), C.c_float(depth_factor), C.c_size_t(h * w * es),
                                      C.c_size_t(w * es), w, h, n, 0, C.byref(cam), first_slot))
+
+    def frame_rgbd(self, color: np.ndarray, depth: np.ndarray, cam: "Camera", rgb_order=True, depth_factor=1.0):
+        """orbx_frame_rgbd: ONE RGB-D frame (host arrays, any row stride) -> dict(kps, keys_un, desc, u_right, depth, bounds)"""
+        assert color.dtype == np.uint8 and color.strides[-1] == 1 and (color.ndim == 2 or color.strides[-2] == color.shape[-1])
+        ch = 1 if color.ndim == 2 else color.shape[2]
+        h, w = color.shape[:2]
+        is16 = depth.dtype == np.uint16
+        assert depth.dtype in (np.uint16, np.float32) and depth.strides[1] == depth.itemsize
+        cap = self.reserve_shape(w, h)
+        kps = np.zeros(cap, KP_DTYPE); kun = np.zeros(cap, KP_DTYPE); desc = np.zeros((cap, 32), np.uint8)
+        ur = np.zeros(cap, np.float32); z = np.zeros(cap, np.float32); b = np.zeros(4, np.float32)
+        n = C.c_int(0)
+        check(lib().orbx_frame_rgbd(self.h, C.c_void_p(color.ctypes.data), ch, int(rgb_order), C.c_size_t(color.strides[0]),
+                                    C.c_void_p(depth.ctypes.data), int(is16), C.c_float(depth_factor), C.c_size_t(depth.strides[0]), w, h,
+                                    C.byref(cam), _p(kps), _p(kun), _p(desc), _p(ur), _p(z), cap, C.byref(n), _p(b)))
+        c = n.value
+        return dict(kps=kps[:c].copy(), keys_un=kun[:c].copy(), desc=desc[:c].copy(), u_right=ur[:c].copy(), depth=z[:c].copy(), bounds=b)
 
     def frames_rgbd_ptr(self, color_ptr, channels, depth_ptr, depth_is_u16, nframes, width, height, cam, rgb_order=True,
                         depth_factor=1.0, on_device=True, first_slot=0):

@@ -228,7 +228,7 @@ int orbx_create(const orbx_params* params, int max_width, int max_height, int ch
     h->dGridStart = nullptr; h->dGridIdx = nullptr; h->dMatches12 = nullptr; h->dNMatches = nullptr;
     h->dNCompares = nullptr; h->dURight = nullptr; h->dDepth = nullptr; h->dMatchScratch = nullptr;
     h->matchScratchPerPair = 0;
-    h->hStage = nullptr; h->hStageBytes = 0;
+    h->hStage = nullptr; h->hStageBytes = 0; h->hPack = nullptr; h->hPackBytes = 0; h->evPack = nullptr;
     h->graph1 = nullptr; h->graph1Valid = false;
     h->lastChunkFrames = 0;
     h->profiling = false; h->evUsed = 0;
@@ -322,6 +322,8 @@ int orbx_destroy(orbx_handle* h)
                     h->dNCompares, h->dURight, h->dDepth, h->dMatchScratch};
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->hStage) cudaFreeHost(h->hStage);
+    if (h->hPack) cudaFreeHost(h->hPack);
+    if (h->evPack) cudaEventDestroy(h->evPack);
     orbx_drop_graph(h);
     for (cudaStream_t x : h->sideStreams) cudaStreamDestroy(x);
     for (cudaEvent_t e : h->sideEvents) cudaEventDestroy(e);
@@ -385,6 +387,7 @@ static int batch_to_host_impl(orbx_handle* h, const uint8_t* images, size_t fram
                               int images_on_device, int first_slot, orbx_keypoint* kps, uint8_t* desc,
                               int32_t* counts, int capacity, const MatchOpts* mo)
 {
+    ORBX_NVTX("orbx_extract_batch");
     if (!h || !images) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
     const bool toHost = kps || desc || counts || (mo && (mo->matches12 || mo->nmatches));
     if ((kps || desc) && capacity < h->kpCap) { orbx_set_error("output capacity %d < %d", capacity, h->kpCap); return ORBX_E_CAPACITY; }
@@ -541,53 +544,84 @@ int orbx_download(orbx_handle* h, int first_slot, int nframes, orbx_keypoint* kp
     return ORBX_OK;
 }
 
-// Single frame, host buffers: the call Tracking makes once per image (Frame::ExtractORB, src/Frame.cc:247-253).
-// Latency path: the image goes through pinned staging in ONE host->device copy, the kernels of the frame are
-// replayed from a CUDA graph captured once per image shape, and count, status, keypoints and descriptors come
-// back in one batch of copies behind a single stream synchronisation.
-int orbx_extract(orbx_handle* h, const uint8_t* image, int width, int height, size_t row_stride,
-                 orbx_keypoint* kps, uint8_t* desc, int capacity, int* n)
+} // extern "C"
+
+int orbx_ensure_host_stage(orbx_handle* h, size_t need)
 {
-    if (!h) { orbx_set_error("null handle"); return ORBX_E_INVALID; }
-    if (width <= 0 || height <= 0 || !image) return ORBX_OK;     // _image.empty(): return, outputs untouched
-    if (width < 64 || height < 64) { orbx_set_error("image smaller than 64x64 is outside the extractor's domain"); return ORBX_E_INVALID; }
-    if (row_stride < (size_t)width) { orbx_set_error("row_stride < width"); return ORBX_E_INVALID; }
-    ORBX_CUDA(cudaSetDevice(h->device));
-    int rc = orbx_setup_shape(h, width, height);
-    if (rc) return rc;
-    h->storeUndistorted = false;
+    if (h->hStageBytes >= need) return ORBX_OK;
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    if (h->hStage) cudaFreeHost(h->hStage);
+    h->hStage = nullptr; h->hStageBytes = 0;
+    ORBX_CUDA(cudaHostAlloc(&h->hStage, need, cudaHostAllocMapped));       // kernels may read it in place (UVA: same pointer)
+    h->hStageBytes = need;
+    return ORBX_OK;
+}
+
+OrbxPackLayout orbx_pack_layout(int kpCap)
+{
+    const size_t cap = (size_t)kpCap;
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    OrbxPackLayout L;
+    L.kps = 256;
+    L.desc = L.kps + up(cap * sizeof(orbx_keypoint));
+    L.kun = L.desc + up(cap * 32);
+    L.ur = L.kun + up(cap * sizeof(orbx_keypoint));
+    L.z = L.ur + up(cap * 4);
+    L.total = L.z + up(cap * 4);
+    return L;
+}
+
+int orbx_ensure_pack(orbx_handle* h)
+{
+    const size_t need = orbx_pack_layout(h->kpCap).total;
+    if (!h->evPack) ORBX_CUDA(cudaEventCreateWithFlags(&h->evPack, cudaEventDisableTiming));
+    if (h->hPackBytes >= need) return ORBX_OK;
+    ORBX_CUDA(cudaStreamSynchronize(h->stream));
+    orbx_drop_graph(h);                                    // the captured graph writes through the old mapping
+    if (h->hPack) cudaFreeHost(h->hPack);
+    h->hPack = nullptr; h->hPackBytes = 0;
+    ORBX_CUDA(cudaHostAlloc((void**)&h->hPack, need, cudaHostAllocMapped));
+    h->hPackBytes = need;
+    return ORBX_OK;
+}
+
+// Results of slot 0 written straight into the caller-visible (mapped, pinned) pack: count and status word, then the `count`
+// keypoint records and descriptors.  Last node of the single-frame graph: the host only synchronises and reads.
+__global__ void __launch_bounds__(128)
+pack_single_kernel(const orbx_keypoint* __restrict__ kps, const uint8_t* __restrict__ desc, const int* __restrict__ count,
+                   const int* __restrict__ status, int cap, uint8_t* __restrict__ pack, size_t offKps, size_t offDesc)
+{
+    const int k = blockIdx.x * 128 + threadIdx.x, n = min(count[0], cap);
+    if (k == 0) { reinterpret_cast<int*>(pack)[0] = count[0]; reinterpret_cast<int*>(pack)[1] = status[0]; }
+    if (k >= n) return;
+    const uint32_t* s = reinterpret_cast<const uint32_t*>(kps + k);
+    uint32_t* d = reinterpret_cast<uint32_t*>(pack + offKps) + (size_t)k * 7;
+#pragma unroll
+    for (int i = 0; i < 7; ++i) d[i] = s[i];
+    const uint4* ds = reinterpret_cast<const uint4*>(desc + (size_t)k * 32);
+    uint4* dd = reinterpret_cast<uint4*>(pack + offDesc + (size_t)k * 32);
+    dd[0] = ds[0]; dd[1] = ds[1];
+}
+
+static int launch_pack(orbx_handle* h)
+{
+    const OrbxPackLayout L = orbx_pack_layout(h->kpCap);
+    pack_single_kernel<<<(h->kpCap + 127) / 128, 128, 0, h->stream>>>(h->dKps, h->dDesc, h->dCount, h->dStatus, h->kpCap, h->hPack, L.kps, L.desc);
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+// The kernels of ONE frame whose level 0 already sits in h->dLevel0 (ordered on the handle's stream): replayed from a CUDA
+// graph captured on the first call of an image shape; plain launches when stage timing is on, the stream is the caller's
+// (it may be one that cannot be captured) or a test forces kernel parameters through the environment.  Results: slot 0.
+int orbx_launch_single_frame(orbx_handle* h)
+{
     cudaStream_t st = h->stream;
-    // pinned staging: [image at the workspace pitch][count, status][keypoints][descriptors]
-    const size_t imgBytes = (size_t)h->l0Pitch * height;
-    const size_t offHdr = (imgBytes + 255) & ~(size_t)255, offKps = offHdr + 256;
-    const size_t offDesc = offKps + (((size_t)h->kpCap * sizeof(orbx_keypoint) + 255) & ~(size_t)255);
-    const size_t need = offDesc + (size_t)h->kpCap * 32;
-    if (h->hStageBytes < need) {
-        ORBX_CUDA(cudaStreamSynchronize(st));
-        if (h->hStage) cudaFreeHost(h->hStage);
-        h->hStage = nullptr; h->hStageBytes = 0;
-        ORBX_CUDA(cudaMallocHost(&h->hStage, need));
-        h->hStageBytes = need;
-    }
-    uint8_t* stage = (uint8_t*)h->hStage;
-    cudaPointerAttributes pa;
-    const bool srcPinned = cudaPointerGetAttributes(&pa, image) == cudaSuccess && pa.type == cudaMemoryTypeHost;
-    cudaGetLastError();                       // an unregistered host pointer is not an error here
-    if (srcPinned) {
-        // the caller's image is page-locked: the DMA engine reads it in place
-        ORBX_CUDA(cudaMemcpy2DAsync(h->dLevel0, h->l0Pitch, image, row_stride, width, height, cudaMemcpyHostToDevice, st));
-    } else {
-        // pageable image (a cv::Mat): one memcpy into the pinned staging at the workspace pitch, one DMA (row slices
-        // that overlap the two were measured slower: four copy launches cost more than the overlap saves)
-        if ((size_t)h->l0Pitch == row_stride) memcpy(stage, image, (size_t)row_stride * (height - 1) + width);
-        else for (int y = 0; y < height; ++y) memcpy(stage + (size_t)y * h->l0Pitch, image + (size_t)y * row_stride, width);
-        ORBX_CUDA(cudaMemcpyAsync(h->dLevel0, stage, imgBytes, cudaMemcpyHostToDevice, st));
-    }
+    int rc = orbx_ensure_pack(h);
+    if (rc) return rc;
     h->evFreeValid[0] = false;                // buffer 0 is now ordered by the handle's stream alone
     Level0 l0;
     l0.base = h->dLevel0; l0.base1 = nullptr; l0.stereo = 0; l0.frameStride = h->l0FrameBytes; l0.pitch = h->l0Pitch;
-    // graph replay unless stage timing is on, the stream is the caller's (it may be one that cannot be captured)
-    // or a test forces kernel parameters through the environment
     const bool useGraph = !h->profiling && h->ownStream && !getenv("ORBX_NO_GRAPH") && !getenv("ORBX_OCTREE_KEYCAP") && !getenv("ORBX_RS_TARGET");
     if (useGraph && !h->graph1Valid) {
         // first frame of this shape: run once plainly (sets function attributes, uploads the per-device tables),
@@ -596,11 +630,13 @@ int orbx_extract(orbx_handle* h, const uint8_t* image, int width, int height, si
         rc = orbx_run_chunk(h, l0, 1, 0);
         if (rc) return rc;
         if (forkLevels) { rc = orbx_run_frame_forked(h, l0, 0); if (rc) return rc; }    // creates the side streams outside the capture
+        rc = launch_pack(h); if (rc) return rc;
         long long before[ORBX_NSTAGES];
         for (int s = 0; s < ORBX_NSTAGES; ++s) before[s] = h->stageLaunches[s];
         cudaGraph_t graph = nullptr;
         ORBX_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed));
         rc = forkLevels ? orbx_run_frame_forked(h, l0, 0) : orbx_run_chunk(h, l0, 1, 0);
+        if (!rc) rc = launch_pack(h);
         const cudaError_t ce = cudaStreamEndCapture(st, &graph);
         for (int s = 0; s < ORBX_NSTAGES; ++s) { h->graph1Launches[s] = h->stageLaunches[s] - before[s]; h->stageLaunches[s] = before[s]; }
         if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
@@ -617,13 +653,54 @@ int orbx_extract(orbx_handle* h, const uint8_t* image, int width, int height, si
     } else {
         rc = orbx_run_chunk(h, l0, 1, 0);
         if (rc) return rc;
+        rc = launch_pack(h); if (rc) return rc;
     }
-    int32_t* hdr = (int32_t*)(stage + offHdr);
-    ORBX_CUDA(cudaMemcpyAsync(hdr, h->dCount, sizeof(int), cudaMemcpyDeviceToHost, st));
-    ORBX_CUDA(cudaMemcpyAsync(hdr + 1, h->dStatus, sizeof(int), cudaMemcpyDeviceToHost, st));
-    if (kps) ORBX_CUDA(cudaMemcpyAsync(stage + offKps, h->dKps, (size_t)h->kpCap * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, st));
-    if (desc) ORBX_CUDA(cudaMemcpyAsync(stage + offDesc, h->dDesc, (size_t)h->kpCap * 32, cudaMemcpyDeviceToHost, st));
-    ORBX_CUDA(cudaStreamSynchronize(st));
+    return ORBX_OK;
+}
+
+extern "C" {
+
+// Single frame, host buffers: the call Tracking makes once per image (Frame::ExtractORB, src/Frame.cc:247-253).
+// Latency path: the image goes through pinned staging in ONE host->device copy, the kernels of the frame are
+// replayed from a CUDA graph captured once per image shape, and the graph's last node writes count, status, keypoints
+// and descriptors straight into a pinned, device-mapped buffer: no device->host copy commands (four of them cost ~30 us),
+// one stream synchronisation.
+int orbx_extract(orbx_handle* h, const uint8_t* image, int width, int height, size_t row_stride,
+                 orbx_keypoint* kps, uint8_t* desc, int capacity, int* n)
+{
+    ORBX_NVTX("orbx_extract");
+    if (!h) { orbx_set_error("null handle"); return ORBX_E_INVALID; }
+    if (width <= 0 || height <= 0 || !image) return ORBX_OK;     // _image.empty(): return, outputs untouched
+    if (width < 64 || height < 64) { orbx_set_error("image smaller than 64x64 is outside the extractor's domain"); return ORBX_E_INVALID; }
+    if (row_stride < (size_t)width) { orbx_set_error("row_stride < width"); return ORBX_E_INVALID; }
+    ORBX_CUDA(cudaSetDevice(h->device));
+    int rc = orbx_setup_shape(h, width, height);
+    if (rc) return rc;
+    h->storeUndistorted = false;
+    cudaStream_t st = h->stream;
+    // pinned staging for a pageable image (at the workspace pitch); results come back through the mapped pack
+    const size_t imgBytes = (size_t)h->l0Pitch * height;
+    rc = orbx_ensure_host_stage(h, imgBytes);
+    if (rc) return rc;
+    uint8_t* stage = (uint8_t*)h->hStage;
+    cudaPointerAttributes pa;
+    const bool srcPinned = cudaPointerGetAttributes(&pa, image) == cudaSuccess && pa.type == cudaMemoryTypeHost;
+    cudaGetLastError();                       // an unregistered host pointer is not an error here
+    if (srcPinned) {
+        // the caller's image is page-locked: the DMA engine reads it in place
+        ORBX_CUDA(cudaMemcpy2DAsync(h->dLevel0, h->l0Pitch, image, row_stride, width, height, cudaMemcpyHostToDevice, st));
+    } else {
+        // pageable image (a cv::Mat): one memcpy into the pinned staging at the workspace pitch, one DMA (row slices
+        // that overlap the two were measured slower: four copy launches cost more than the overlap saves)
+        if ((size_t)h->l0Pitch == row_stride) memcpy(stage, image, (size_t)row_stride * (height - 1) + width);
+        else for (int y = 0; y < height; ++y) memcpy(stage + (size_t)y * h->l0Pitch, image + (size_t)y * row_stride, width);
+        ORBX_CUDA(cudaMemcpyAsync(h->dLevel0, stage, imgBytes, cudaMemcpyHostToDevice, st));
+    }
+    rc = orbx_launch_single_frame(h);
+    if (rc) return rc;
+    ORBX_CUDA(cudaStreamSynchronize(st));                 // the graph's last node wrote count, status, keypoints and descriptors into hPack
+    const OrbxPackLayout PL = orbx_pack_layout(h->kpCap);
+    const int32_t* hdr = (const int32_t*)h->hPack;
     if (hdr[1]) {
         ORBX_CUDA(cudaMemsetAsync(h->dStatus, 0, sizeof(int), st));
         orbx_set_error("device-side capacity overflow (flags 0x%x): quadtree node/keypoint table too small", hdr[1]);
@@ -631,8 +708,8 @@ int orbx_extract(orbx_handle* h, const uint8_t* image, int width, int height, si
     }
     const int cnt = hdr[0];
     if ((kps || desc) && cnt > capacity) { orbx_set_error("capacity %d < %d keypoints", capacity, cnt); return ORBX_E_CAPACITY; }
-    if (kps && cnt > 0) memcpy(kps, stage + offKps, (size_t)cnt * sizeof(orbx_keypoint));
-    if (desc && cnt > 0) memcpy(desc, stage + offDesc, (size_t)cnt * 32);
+    if (kps && cnt > 0) memcpy(kps, h->hPack + PL.kps, (size_t)cnt * sizeof(orbx_keypoint));
+    if (desc && cnt > 0) memcpy(desc, h->hPack + PL.desc, (size_t)cnt * 32);
     if (n) *n = cnt;
     return ORBX_OK;
 }

@@ -283,6 +283,7 @@ int orbm_bow_transform(orbm_vocab_handle* v, const uint8_t* features, int n, int
 int orbm_search_by_bow(int variant, const orbm_bow_frame* a, const orbm_bow_frame* b, int npairs, float nnratio,
                        int check_orientation, int device, int32_t* match_a, int32_t* match_b, int32_t* nmatches)
 {
+    ORBX_NVTX("orbm_search_by_bow");
     if (!a || !b || !match_a || !match_b || !nmatches) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
     if (variant != 0 && variant != 1) { orbx_set_error("variant must be 0 (KeyFrame, Frame) or 1 (KeyFrame, KeyFrame)"); return ORBX_E_INVALID; }
     if (npairs <= 0) return ORBX_OK;

@@ -1273,12 +1273,14 @@ static int run_chunk_impl(orbx_handle* h, Level0 l0, int nframes, int firstSlot,
         ORBX_CUDA(cudaEventRecord(h->sideEvents[2 * l + 1], sB));
         return ORBX_OK;
     };
+    ORBX_NVTX(forked ? "orbx:frame(forked)" : "orbx:chunk");
     orbx_prof_mark(h, -1);
     if (forked) {
         rc = fork_level(0);
         if (rc) return rc;
     }
     // K1a: levels 1..n-1, each from the previous one
+    nvtxRangePushA("orbx:resize");
     for (int l = 1; l < nl; ++l) {
         const LevelGeom& S = g.L[l - 1];
         const LevelGeom& D = g.L[l];
@@ -1304,6 +1306,7 @@ static int run_chunk_impl(orbx_handle* h, Level0 l0, int nframes, int firstSlot,
         }
         if (forked) { rc = fork_level(l); if (rc) return rc; }
     }
+    nvtxRangePop();
     ORBX_COUNT(h, ORBX_STAGE_RESIZE, nl - 1);
     orbx_prof_mark(h, ORBX_STAGE_RESIZE);
     if (forked) {
@@ -1313,21 +1316,22 @@ static int run_chunk_impl(orbx_handle* h, Level0 l0, int nframes, int firstSlot,
         ORBX_COUNT(h, ORBX_STAGE_OCTREE, nl);
     } else {
         // K1b: blur of all levels
-        launch_blur(st, 0, h->nBlurTiles);
+        { ORBX_NVTX("orbx:blur"); launch_blur(st, 0, h->nBlurTiles); }
         ORBX_COUNT(h, ORBX_STAGE_BLUR, 1);
         orbx_prof_mark(h, ORBX_STAGE_BLUR);
         // K2: FAST
-        launch_fast(st, 0, g.ncells);
+        { ORBX_NVTX("orbx:fast"); launch_fast(st, 0, g.ncells); }
         ORBX_COUNT(h, ORBX_STAGE_FAST, 1);
         orbx_prof_mark(h, ORBX_STAGE_FAST);
         // K3: quadtree
-        rc = launch_octree(st, 0, nl);
+        { ORBX_NVTX("orbx:quadtree"); rc = launch_octree(st, 0, nl); }
         if (rc) return rc;
         ORBX_COUNT(h, ORBX_STAGE_OCTREE, 1);
         orbx_prof_mark(h, ORBX_STAGE_OCTREE);
     }
     // K4: orientation + descriptors + output records
     {
+        ORBX_NVTX("orbx:describe");
         describe_kernel<<<dim3((g.kpTotal + DESC_WARPS - 1) / DESC_WARPS, nframes), DESC_WARPS * 32, 0, st>>>(
             g, l0, h->dRaw, h->dBlur, nframes, h->dLevelKps, h->dLevelKpCount, h->dKpMap, dPat, dDisc, h->dKps, h->dDesc, h->dCount,
             h->dSlotLevelCount, firstSlot, h->kpCap);

@@ -113,7 +113,8 @@ __global__ void __launch_bounds__(128)
 frame_front_kernel(CamD c, float bf, const orbx_keypoint* __restrict__ kps, const int* __restrict__ count, int cap,
                    int firstSlot, const u8* __restrict__ depth, int depthU16, float factor, int scaleDepth,
                    long long dFrame, long long dRow, orbx_keypoint* __restrict__ kpsUn,
-                   float* __restrict__ uRight, float* __restrict__ zOut)
+                   float* __restrict__ uRight, float* __restrict__ zOut,
+                   orbx_keypoint* __restrict__ packUn = nullptr, float* __restrict__ packUR = nullptr, float* __restrict__ packZ = nullptr)
 {
     const int slot = firstSlot + blockIdx.y, k = blockIdx.x * 128 + threadIdx.x;
     if (k >= cap) return;
@@ -131,6 +132,7 @@ frame_front_kernel(CamD c, float bf, const orbx_keypoint* __restrict__ kps, cons
     float ur = -1.f, z = -1.f;
     if (d > 0) { z = d; ur = __fsub_rn(kp.x, __fdiv_rn(bf, d)); }
     uRight[o] = ur; zOut[o] = z;
+    if (packUn) { packUn[k] = kp; packUR[k] = ur; packZ[k] = z; }      // single-frame call: also into the host-mapped result pack
 }
 
 // ---- small RAII device buffer for the stateless entry points ---------------------------------------
@@ -249,6 +251,7 @@ int orbx_frames_rgbd(orbx_handle* h, const uint8_t* color, int channels, int rgb
                      size_t depth_frame_stride, size_t depth_row_stride, int width, int height, int nframes,
                      int on_device, const orbx_camera* cam, int first_slot)
 {
+    ORBX_NVTX("orbx_frames_rgbd");
     if (!h || !color || !depth) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
     int rc = check_cam(cam); if (rc) return rc;
     if (channels != 1 && channels != 3 && channels != 4) { orbx_set_error("colour images have 1, 3 or 4 channels, got %d", channels); return ORBX_E_INVALID; }
@@ -332,6 +335,124 @@ int orbx_frames_rgbd(orbx_handle* h, const uint8_t* color, int channels, int rgb
     rc = orbx_build_grids(h, first_slot, nframes, width, height);
     if (rc) return rc;
     ORBX_CUDA(cudaStreamSynchronize(st));
+    return ORBX_OK;
+}
+
+// One RGB-D frame, host images in, the whole Frame front out: what Tracking::GrabImageRGBD + Frame::Frame(RGB-D) produce for one
+// image pair (src/Tracking.cc:300-339, src/Frame.cc:136-189).  The latency twin of orbx_frames_rgbd, built like orbx_extract and
+// without a single copy command on its path (each small cudaMemcpyAsync costs ~8 us of latency):
+//   colour -> pinned, device-MAPPED staging in row slices; cvtColor reads a slice through the mapping while the host copies the next
+//   and writes gray straight into the extractor's level-0 buffer -> the frame's captured graph, whose last node writes mvKeys and
+//   the descriptors into the mapped result pack; meanwhile the host copies the depth map into the mapped staging; the frame-front
+//   kernel (UndistortKeyPoints, ComputeStereoFromRGBD) reads the ~1000 depth pixels it needs through the mapping and writes
+//   mvKeysUn / mvuRight / mvDepth into the pack; ONE event synchronisation; the grid for later matcher calls is built behind it.
+// Page-locked colour / depth images are read in place.
+int orbx_frame_rgbd(orbx_handle* h, const uint8_t* color, int channels, int rgb_order, size_t color_row_stride, const void* depth,
+                    int depth_is_u16, float depth_factor, size_t depth_row_stride, int width, int height, const orbx_camera* cam,
+                    orbx_keypoint* kps, orbx_keypoint* keys_un, uint8_t* desc, float* u_right, float* depth_out, int capacity, int* n,
+                    float bounds_out[4])
+{
+    ORBX_NVTX("orbx_frame_rgbd");
+    if (!h) { orbx_set_error("null handle"); return ORBX_E_INVALID; }
+    if (width <= 0 || height <= 0 || !color) return ORBX_OK;                 // empty image: outputs untouched, as the extractor does
+    if (!depth) { orbx_set_error("null depth image"); return ORBX_E_INVALID; }
+    int rc = check_cam(cam); if (rc) return rc;
+    if (channels != 1 && channels != 3 && channels != 4) { orbx_set_error("colour images have 1, 3 or 4 channels, got %d", channels); return ORBX_E_INVALID; }
+    if (width < 64 || height < 64) { orbx_set_error("image smaller than 64x64 is outside the extractor's domain"); return ORBX_E_INVALID; }
+    const size_t dElem = depth_is_u16 ? 2 : 4;
+    const size_t cRow = (size_t)width * channels, zRow = (size_t)width * dElem;
+    if (color_row_stride < cRow || depth_row_stride < zRow) { orbx_set_error("row stride smaller than a row"); return ORBX_E_INVALID; }
+    ORBX_CUDA(cudaSetDevice(h->device));
+    rc = orbx_setup_shape(h, width, height); if (rc) return rc;
+    rc = orbx_ensure_match_buffers(h); if (rc) return rc;
+    const size_t R = (size_t)h->resultSlots, cap = (size_t)h->kpCap;
+    if (!h->dKpsUn) ORBX_CUDA(cudaMalloc((void**)&h->dKpsUn, R * cap * sizeof(orbx_keypoint)));
+    {   // ComputeImageBounds once per calibration and image size (mbInitialComputations, Frame.cc:170-186)
+        const float key[11] = {cam->fx, cam->fy, cam->cx, cam->cy, cam->k1, cam->k2, cam->p1, cam->p2, cam->k3, (float)width, (float)height};
+        if (!h->boundsValid || memcmp(key, h->boundsKey, sizeof(key)) != 0) {
+            float b[4];
+            rc = orbx_image_bounds(h, width, height, cam, b); if (rc) return rc;
+            memcpy(h->boundsKey, key, sizeof(key));
+            for (int i = 0; i < 4; ++i) h->bounds[i] = b[i];
+            h->boundsValid = true;
+        }
+    }
+    cudaStream_t st = h->stream;
+    // pinned, device-mapped staging for pageable inputs: [colour or gray][depth].  The kernels read it in place.
+    const size_t grayRow = (size_t)h->l0Pitch;
+    const size_t offDepth = ((channels == 1 ? grayRow : cRow) * height + 255) & ~(size_t)255;
+    rc = orbx_ensure_host_stage(h, offDepth + ((zRow * height + 255) & ~(size_t)255)); if (rc) return rc;
+    rc = orbx_ensure_pack(h); if (rc) return rc;
+    u8* stage = (u8*)h->hStage;
+    // a page-locked caller image: usable in place when the driver hands out a device alias for it
+    auto mapped = [](const void* p) -> const u8* {
+        cudaPointerAttributes pa;
+        const bool host = cudaPointerGetAttributes(&pa, p) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer;
+        cudaGetLastError();
+        return host ? (const u8*)pa.devicePointer : nullptr;
+    };
+    // ---- colour in, gray into the extractor's level-0 buffer ------------------------------------------------------------
+    if (channels == 1) {
+        if (mapped(color)) ORBX_CUDA(cudaMemcpy2DAsync(h->dLevel0, grayRow, color, color_row_stride, width, height, cudaMemcpyHostToDevice, st));
+        else {
+            for (int y = 0; y < height; ++y) memcpy(stage + (size_t)y * grayRow, color + (size_t)y * color_row_stride, width);
+            ORBX_CUDA(cudaMemcpyAsync(h->dLevel0, stage, grayRow * height, cudaMemcpyHostToDevice, st));
+        }
+    } else if (const u8* dc = mapped(color)) {
+        // cvtColor reads the page-locked image over the bus and writes gray into level 0: no copy command at all
+        rc = launch_cvt(dc, color_row_stride * height, color_row_stride, channels, rgb_order, h->dLevel0, (size_t)h->l0FrameBytes, grayRow, width, height, 1, st);
+        if (rc) return rc;
+    } else {
+        // pageable image: the host copies it into the mapped staging in row slices and cvtColor converts a slice while the next
+        // one is being copied (a 640x480 RGB image is 0.9 MB: ~70 us of memcpy that would otherwise all sit in front of the GPU)
+        const int slices = 4, rowsPer = ((height + slices - 1) / slices + 3) & ~3;
+        for (int y0 = 0; y0 < height; y0 += rowsPer) {
+            const int rows = std::min(rowsPer, height - y0);
+            if (color_row_stride == cRow) memcpy(stage + (size_t)y0 * cRow, color + (size_t)y0 * cRow, cRow * rows);
+            else for (int y = y0; y < y0 + rows; ++y) memcpy(stage + (size_t)y * cRow, color + (size_t)y * color_row_stride, cRow);
+            rc = launch_cvt(stage + (size_t)y0 * cRow, cRow * height, cRow, channels, rgb_order, h->dLevel0 + (size_t)y0 * grayRow,
+                            (size_t)h->l0FrameBytes, grayRow, width, rows, 1, st);
+            if (rc) return rc;
+        }
+    }
+    h->storeUndistorted = false;
+    rc = orbx_launch_single_frame(h);                    // the extractor's graph: results in slot 0, mvKeys + descriptors in the pack
+    if (rc) return rc;
+    // ---- depth: only the pixels under the keypoints are read, through the mapping (the host copy of a pageable depth map
+    // overlaps the extractor) --------------------------------------------------------------------------------------------
+    const u8* dz = mapped(depth);
+    size_t dzRow = depth_row_stride;
+    if (!dz) {
+        if (depth_row_stride == zRow) memcpy(stage + offDepth, depth, zRow * height);
+        else for (int y = 0; y < height; ++y) memcpy(stage + offDepth + (size_t)y * zRow, (const u8*)depth + (size_t)y * depth_row_stride, zRow);
+        dz = stage + offDepth; dzRow = zRow;
+    }
+    const OrbxPackLayout PL = orbx_pack_layout(h->kpCap);
+    frame_front_kernel<<<dim3((unsigned)((cap + 127) / 128), 1), 128, 0, st>>>(cam_double(cam), cam->bf, h->dKps, h->dCount, h->kpCap, 0, dz, depth_is_u16,
+                                                                              depth_factor, depth_factor != 1.0f, (long long)(dzRow * height), (long long)dzRow,
+                                                                              h->dKpsUn, h->dURight, h->dDepth, (orbx_keypoint*)(h->hPack + PL.kun),
+                                                                              (float*)(h->hPack + PL.ur), (float*)(h->hPack + PL.z));
+    ORBX_CUDA(cudaGetLastError());
+    ORBX_CUDA(cudaEventRecord(h->evPack, st));           // everything the caller gets is in the pack here
+    h->storeUndistorted = true;                          // the store now describes an undistorted frame (grid, matchers)
+    rc = orbx_build_grids(h, 0, 1, width, height);       // for the matchers that run on slot 0 next: finishes behind the caller's back
+    if (rc) return rc;
+    ORBX_CUDA(cudaEventSynchronize(h->evPack));
+    const int32_t* hdr = (const int32_t*)h->hPack;
+    if (hdr[1]) {
+        ORBX_CUDA(cudaMemsetAsync(h->dStatus, 0, sizeof(int), st));
+        orbx_set_error("device-side capacity overflow (flags 0x%x): quadtree node/keypoint table too small", hdr[1]);
+        return ORBX_E_CAPACITY;
+    }
+    const int cnt = hdr[0];
+    if ((kps || keys_un || desc || u_right || depth_out) && cnt > capacity) { orbx_set_error("capacity %d < %d keypoints", capacity, cnt); return ORBX_E_CAPACITY; }
+    if (kps && cnt > 0) memcpy(kps, h->hPack + PL.kps, (size_t)cnt * sizeof(orbx_keypoint));
+    if (keys_un && cnt > 0) memcpy(keys_un, h->hPack + PL.kun, (size_t)cnt * sizeof(orbx_keypoint));
+    if (desc && cnt > 0) memcpy(desc, h->hPack + PL.desc, (size_t)cnt * 32);
+    if (u_right && cnt > 0) memcpy(u_right, h->hPack + PL.ur, (size_t)cnt * 4);
+    if (depth_out && cnt > 0) memcpy(depth_out, h->hPack + PL.z, (size_t)cnt * 4);
+    if (bounds_out) for (int i = 0; i < 4; ++i) bounds_out[i] = h->bounds[i];
+    if (n) *n = cnt;
     return ORBX_OK;
 }
 

@@ -3,6 +3,7 @@
 #define ORBX_INTERNAL_H
 
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>      // header-only NVTX v3: ranges cost a pointer test when no tool is attached
 #include <stdint.h>
 #include <string>
 #include <vector>
@@ -18,6 +19,15 @@
 #define ORBX_HISTO_LENGTH 30  // reference src/ORBmatcher.cc:39
 
 void orbx_set_error(const char* fmt, ...);
+
+// NVTX range around a stage / entry point (SURVEY.md §5 tooling): ORBX_NVTX("orbx:fast");
+struct OrbxNvtxScope {
+    explicit OrbxNvtxScope(const char* name) { nvtxRangePushA(name); }
+    ~OrbxNvtxScope() { nvtxRangePop(); }
+};
+#define ORBX_NVTX_CAT2(a, b) a##b
+#define ORBX_NVTX_CAT(a, b) ORBX_NVTX_CAT2(a, b)
+#define ORBX_NVTX(name) OrbxNvtxScope ORBX_NVTX_CAT(orbxNvtxScope, __LINE__)(name)
 
 #define ORBX_CUDA(call)                                                                         \
     do {                                                                                        \
@@ -142,9 +152,13 @@ struct orbx_handle {
     float* dDepth;
     uint32_t* dMatchScratch;
     long long matchScratchPerPair;
-    // pinned staging
+    // pinned, device-mapped staging of the single-frame calls: inputs are read and results written by the kernels
+    // THROUGH the mapping (no copy commands: a small cudaMemcpyAsync costs ~8 us of latency each)
     void* hStage;
     size_t hStageBytes;
+    uint8_t* hPack;         // [count, status, pad to 256 B][mvKeys cap x 28][descriptors cap x 32][mvKeysUn cap x 28][mvuRight cap x 4][mvDepth cap x 4]
+    size_t hPackBytes;
+    cudaEvent_t evPack;     // recorded when the results of a single-frame call are in hPack
     // single-frame call (orbx_extract): the kernels of one frame captured once per image shape
     cudaGraphExec_t graph1;
     bool graph1Valid;
@@ -179,6 +193,11 @@ int orbx_grow_result_store(orbx_handle* h, int newCap);   // orbx_api.cu: re-all
 void orbx_drop_graph(orbx_handle* h);      // the workspace moved: the captured single-frame graph is stale
 int orbx_run_chunk(orbx_handle* h, Level0 l0, int nframes, int firstSlot);
 int orbx_run_frame_forked(orbx_handle* h, Level0 l0, int firstSlot);   // one frame, per-level fork/join (latency form)
+int orbx_launch_single_frame(orbx_handle* h);    // orbx_api.cu: graph replay of one frame whose level 0 is in dLevel0 -> slot 0
+int orbx_ensure_host_stage(orbx_handle* h, size_t bytes);   // orbx_api.cu: the handle's pinned staging buffer, grown on demand
+int orbx_ensure_pack(orbx_handle* h);                      // orbx_api.cu: the result pack of the single-frame calls (sized by kpCap)
+struct OrbxPackLayout { size_t kps, desc, kun, ur, z, total; };
+OrbxPackLayout orbx_pack_layout(int kpCap);
 
 // orbx_api.cu: frames [nf][height][row_stride] -> pitched workspace frames, on `st`
 int orbx_copy_frames(orbx_handle* h, uint8_t* dst, long long dstFrameBytes, uint8_t* stage, size_t stageBytes, const uint8_t* src, size_t frame_stride,

@@ -300,6 +300,7 @@ extern "C" {
 int orbm_fuse(int variant, const orbm_keyframe* kf, const orbm_proj_query* queries, const uint8_t* query_desc, int nq,
               int device, int32_t* best_idx, int32_t* best_dist)
 {
+    ORBX_NVTX("orbm_fuse");
     int rc = kf_check(kf); if (rc) return rc;
     if (variant < ORBM_FUSE_MAPPOINTS || variant > ORBM_FUSE_SIM3_LEG) { orbx_set_error("unknown Fuse variant %d", variant); return ORBX_E_INVALID; }
     if (nq < 0 || (nq > 0 && (!queries || !query_desc || !best_idx))) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
@@ -321,6 +322,7 @@ int orbm_search_by_sim3(const orbm_keyframe* kf1, const orbm_keyframe* kf2, cons
                         const uint8_t* desc21, const int32_t* index2, int nq21, int device, int32_t* match12,
                         int32_t* nfound)
 {
+    ORBX_NVTX("orbm_search_by_sim3");
     int rc = kf_check(kf1); if (rc) return rc;
     rc = kf_check(kf2); if (rc) return rc;
     if (nq12 < 0 || nq21 < 0 || (nq12 > 0 && (!queries12 || !desc12 || !index1)) || (nq21 > 0 && (!queries21 || !desc21 || !index2)) ||
@@ -356,6 +358,7 @@ int orbm_search_for_triangulation(const orbm_keyframe* kf1, const orbm_keyframe*
                                   const float* epipole, int only_stereo, int check_orientation, int device,
                                   int32_t* matches12, int32_t* nmatches)
 {
+    ORBX_NVTX("orbm_search_for_triangulation");
     if (npairs <= 0) return ORBX_OK;
     if (!kf1 || !kf2 || !f12 || !epipole || !matches12 || !nmatches) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
     std::vector<TriPair> pairs(npairs);

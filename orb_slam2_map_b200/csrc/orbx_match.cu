@@ -1089,6 +1089,7 @@ static int launch_stereo(const FrameStore& fs, int firstSlot, int npairs, const 
 
 int orbx_match_chunk(orbx_handle* h, int gridFirst, int gridCount, int pairFirst, int npairs, int window, float nnratio, int checkOri)
 {
+    ORBX_NVTX("orbx_match_chunk");
     const FrameStore fs = store_of(h);
     const GridParams gp = h->storeUndistorted ? orbx_grid_params(h->bounds[0], h->bounds[1], h->bounds[2], h->bounds[3])
                                               : orbx_grid_params(0.f, (float)h->curW, 0.f, (float)h->curH);
@@ -1184,6 +1185,7 @@ int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, f
                                    int32_t* matches12, int window_size, float nnratio,
                                    int check_orientation, int32_t* nmatches)
 {
+    ORBX_NVTX("orbm_search_for_initialization");
     int rc = check_frame(f1); if (rc) return rc;
     rc = check_frame(f2); if (rc) return rc;
     if (!prev_matched || !matches12) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
@@ -1243,6 +1245,7 @@ int orbm_search_by_projection(int variant, const orbm_frame* frame, const orbm_p
                               int32_t* best_dist, int th_dist, float nnratio,
                               int check_orientation, int32_t* nmatches)
 {
+    ORBX_NVTX("orbm_search_by_projection");
     int rc = check_frame(frame); if (rc) return rc;
     if (variant < ORBM_PROJ_LOCALMAP || variant > ORBM_PROJ_SIM3) { orbx_set_error("unknown SearchByProjection variant %d", variant); return ORBX_E_INVALID; }
     if (nq < 0 || (nq > 0 && (!queries || !query_desc || !best_idx || !best_dist)) || (frame->n > 0 && (!occupied || !assigned))) {
@@ -1319,6 +1322,7 @@ int orbm_search_by_projection(int variant, const orbm_frame* frame, const orbm_p
 int orbm_compute_stereo_matches(const orbm_stereo_input* in, float* u_right, float* depth,
                                 uint64_t* ncompares)
 {
+    ORBX_NVTX("orbm_compute_stereo_matches");
     if (!in || in->n_left < 0 || in->n_right < 0 || in->nlevels < 1 || in->nlevels > ORBX_MAX_LEVELS ||
         !in->scale_factors || !in->inv_scale_factors || !in->pyr_left || !in->pyr_right || !in->level_width ||
         !in->level_height || !in->pyr_stride_left || !in->pyr_stride_right ||
@@ -1380,6 +1384,7 @@ int orbx_extract_stereo_batch(orbx_handle* h, const uint8_t* left, const uint8_t
                               int npairs, int images_on_device, int first_slot, float bf, float fx,
                               float* u_right, float* depth, int capacity, uint64_t* ncompares)
 {
+    ORBX_NVTX("orbx_extract_stereo_batch");
     if (!h || !left || !right) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
     if (width <= 0 || height <= 0 || npairs <= 0) return ORBX_OK;
     if (width < 64 || height < 64) { orbx_set_error("image smaller than 64x64 is outside the extractor's domain"); return ORBX_E_INVALID; }

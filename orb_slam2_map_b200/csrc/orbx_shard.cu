@@ -103,6 +103,7 @@ int orbm_nccl_comm_destroy(void* comm)
 int orbm_knn2_sharded(void* comm, const uint8_t* queries, int64_t nq, const uint8_t* db_shard, int64_t ndb_local,
                       int32_t db_index_offset, int64_t query_chunk, uint16_t* out_dist, int32_t* out_idx, void* stream)
 {
+    ORBX_NVTX("orbm_knn2_sharded");
     if (nq <= 0) return ORBX_OK;
     if (!comm) return orbm_knn2_device(queries, nq, db_shard, ndb_local, db_index_offset, out_dist, out_idx, stream);
     NcclApi* n; int rc = nccl_api(&n); if (rc) return rc;

@@ -141,3 +141,62 @@ def test_pack_map_records():
     got = ex.pack_map_records(0, mp)
     assert got.shape == (n, 64) and got.tobytes() == O.write_keyframe_features(k[:n], d[:n], mp).tobytes()
     assert ex.pack_map_records(0).tobytes() == O.write_keyframe_features(k[:n], d[:n], None).tobytes()
+
+
+@pytest.mark.parametrize("channels,rgb,depth16", [(3, True, True), (4, False, False), (1, True, True)])
+def test_frame_rgbd_single_call_graph_replay(channels, rgb, depth16):
+    """orbx_frame_rgbd, the one-frame latency form of the RGB-D front (Tracking::GrabImageRGBD + Frame::Frame): call after
+    call on ONE handle — first call of a shape captures the extractor's graph, later calls replay it — every call bit-exact
+    against the oracle chain cvtColor -> ORBextractor -> undistortPoints -> ComputeStereoFromRGBD, with strided sources, a
+    page-locked source, a shape change and back, and the matcher on the frame it leaves in slot 0."""
+    import torch
+    w, h, n = 640, 480, 4
+    rng = np.random.default_rng(21)
+    gray0 = synth.frame_sequence(n, w, h, seed=9)
+    color = gray0 if channels == 1 else np.stack([np.clip(gray0.astype(np.int32) + rng.integers(-20, 21, gray0.shape), 0, 255)
+                                                   for _ in range(channels)], axis=-1).astype(np.uint8)
+    if depth16:
+        depth = rng.integers(0, 30000, (n, h, w), dtype=np.uint16); factor = float(np.float32(1.0) / np.float32(5000.0))
+    else:
+        depth = (rng.random((n, h, w)) * 6).astype(np.float32); factor = 1.0
+    depth[rng.random(depth.shape) < 0.15] = 0
+    cam = _cam(**TUM1)
+    camv = np.array([TUM1[k] for k in ("fx", "fy", "cx", "cy")], np.float32)
+    dist = np.array([TUM1[k] for k in ("k1", "k2", "p1", "p2", "k3")], np.float32)
+    orc = O.Extractor()
+    ex = capi.Extractor(max_width=752, max_height=480, chunk_frames=2, result_slots=2)
+
+    def check_one(col, dep):
+        r = ex.frame_rgbd(col, dep, cam, rgb_order=rgb, depth_factor=factor)
+        hh, ww = col.shape[:2]
+        gray = np.ascontiguousarray(col) if col.ndim == 2 else O.cvt_gray(np.ascontiguousarray(col), rgb)
+        ko, do = orc.extract(gray)
+        assert r["kps"].tobytes() == ko.tobytes() and np.array_equal(r["desc"], do)
+        xy = np.stack([ko["x"], ko["y"]], axis=1)
+        xyu = O.undistort_points(xy, camv, dist)
+        dflt = O.depth_to_float(np.ascontiguousarray(dep), factor) if depth16 else np.ascontiguousarray(dep)
+        ur_o, z_o = O.stereo_from_rgbd(xy, xyu, dflt, TUM1["bf"])
+        assert np.array_equal(r["keys_un"]["x"], xyu[:, 0]) and np.array_equal(r["keys_un"]["y"], xyu[:, 1])
+        for f in ("size", "angle", "response", "octave", "class_id"):
+            assert np.array_equal(r["keys_un"][f], ko[f])
+        assert np.array_equal(r["u_right"], ur_o) and np.array_equal(r["depth"], z_o)
+        assert np.array_equal(r["bounds"], O.image_bounds(ww, hh, camv, dist))
+        return r
+
+    for i in range(n):                                           # call 0 captures, the others replay
+        check_one(color[i], depth[i])
+    wide = np.zeros((h, w + 60) + color.shape[3:], np.uint8); wide[:, :w] = color[1]; wide[:, w:] = 255      # padded rows
+    dwide = np.zeros((h, w + 12), depth.dtype); dwide[:, :w] = depth[1]
+    check_one(wide[:, :w], dwide[:, :w])
+    pc = torch.empty(color[2].shape, dtype=torch.uint8, pin_memory=True); pc.copy_(torch.from_numpy(color[2]))
+    pd = torch.empty(depth[2].shape, dtype=torch.from_numpy(depth[2]).dtype, pin_memory=True); pd.copy_(torch.from_numpy(depth[2]))
+    check_one(pc.numpy(), pd.numpy())                            # page-locked sources: DMA in place
+    oc = synth.textured_canvas(752, 480, seed=4)                 # another shape, then back
+    ocol = oc if channels == 1 else np.stack([oc] * channels, axis=-1)
+    odep = (rng.integers(0, 30000, (480, 752), dtype=np.uint16) if depth16 else (rng.random((480, 752)) * 6).astype(np.float32))
+    check_one(ocol, odep)
+    r = check_one(color[0], depth[0])
+    # the frame is in slot 0 with its grid: a stateless matcher call on the same data must agree with the store's view
+    _, _, cnt = ex.download(0, 1, want_kps=False, want_desc=False)
+    assert cnt[0] == len(r["kps"])
+    ex.close()
