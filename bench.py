@@ -686,7 +686,8 @@ def run_rgbd_single(args):
     NF = 32
     gray = synth.frame_sequence(NF, W, H, seed=0)
     rng = np.random.default_rng(3)
-    color = np.stack([np.clip(gray.astype(np.int32) + rng.integers(-20, 21, gray.shape), 0, 255) for _ in range(3)], axis=-1).astype(np.uint8)
+    # R = G = B = the synthetic frame: cvtColor returns exactly that frame, so the extractor sees the images of the `single` line
+    color = np.ascontiguousarray(np.repeat(gray[..., None], 3, axis=-1))
     depth = rng.integers(0, 30000, (NF, H, W), dtype=np.uint16)
     factor = float(np.float32(1.0) / np.float32(5000.0))
     tum1 = dict(fx=517.306408, fy=516.469215, cx=318.643040, cy=255.313989, k1=0.262383, k2=-0.953104, p1=-0.005358, p2=0.002628, k3=1.163314, bf=40.0)
@@ -698,9 +699,17 @@ def run_rgbd_single(args):
     ur = np.zeros(cap, np.float32); z = np.zeros(cap, np.float32); b = np.zeros(4, np.float32); n = C.c_int(0)
     P = lambda a: a.ctypes.data_as(C.c_void_p)
 
+    # argument objects built once: the call below is what a C++ caller pays, not ctypes marshalling of 20 arguments
+    L.orbx_frame_rgbd.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_int,
+                                  C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+    outs = (kps.ctypes.data, kun.ctypes.data, desc.ctypes.data, ur.ctypes.data, z.ctypes.data)
+    camp, np_, bp = C.addressof(cam), C.addressof(n), b.ctypes.data
+
     def call(c, d):
-        capi.check(L.orbx_frame_rgbd(ex.h, P(c), 3, 1, C.c_size_t(W * 3), P(d), 1, C.c_float(factor), C.c_size_t(W * 2), W, H, C.byref(cam),
-                                     P(kps), P(kun), P(desc), P(ur), P(z), cap, C.byref(n), P(b)))
+        rc = L.orbx_frame_rgbd(ex.h, c.ctypes.data, 3, 1, W * 3, d.ctypes.data, 1, factor, W * 2, W, H, camp, outs[0], outs[1], outs[2], outs[3],
+                               outs[4], cap, np_, bp)
+        if rc:
+            capi.check(rc)
 
     def measure(cs, ds, calls):
         for i in range(40):

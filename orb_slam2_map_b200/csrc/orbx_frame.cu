@@ -12,7 +12,10 @@
 #include "orbx_internal.h"
 
 #include <algorithm>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <ctime>
 
 typedef uint8_t u8;
 
@@ -378,6 +381,15 @@ int orbx_frame_rgbd(orbx_handle* h, const uint8_t* color, int channels, int rgb_
         }
     }
     cudaStream_t st = h->stream;
+    // ORBX_LAT_TRACE=1: host clock at every phase of the call, averaged over 200 calls, to stderr
+    static const bool trace = getenv("ORBX_LAT_TRACE") != nullptr;
+    static double tacc[8] = {0}; static int tcalls = 0;
+    auto now = [] { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3; };
+    const double tt0 = trace ? now() : 0.0;
+    double tt[8] = {0};
+    static cudaEvent_t tev[5] = {nullptr}; static double eacc[4] = {0};
+    if (trace && !tev[0]) for (cudaEvent_t& e : tev) cudaEventCreate(&e);
+    if (trace) cudaEventRecord(tev[0], st);
     // pinned, device-mapped staging for pageable inputs: [colour or gray][depth].  The kernels read it in place.
     const size_t grayRow = (size_t)h->l0Pitch;
     const size_t offDepth = ((channels == 1 ? grayRow : cRow) * height + 255) & ~(size_t)255;
@@ -398,26 +410,43 @@ int orbx_frame_rgbd(orbx_handle* h, const uint8_t* color, int channels, int rgb_
             for (int y = 0; y < height; ++y) memcpy(stage + (size_t)y * grayRow, color + (size_t)y * color_row_stride, width);
             ORBX_CUDA(cudaMemcpyAsync(h->dLevel0, stage, grayRow * height, cudaMemcpyHostToDevice, st));
         }
-    } else if (const u8* dc = mapped(color)) {
-        // cvtColor reads the page-locked image over the bus and writes gray into level 0: no copy command at all
-        rc = launch_cvt(dc, color_row_stride * height, color_row_stride, channels, rgb_order, h->dLevel0, (size_t)h->l0FrameBytes, grayRow, width, height, 1, st);
-        if (rc) return rc;
     } else {
-        // pageable image: the host copies it into the mapped staging in row slices and cvtColor converts a slice while the next
-        // one is being copied (a 640x480 RGB image is 0.9 MB: ~70 us of memcpy that would otherwise all sit in front of the GPU)
-        const int slices = 4, rowsPer = ((height + slices - 1) / slices + 3) & ~3;
-        for (int y0 = 0; y0 < height; y0 += rowsPer) {
-            const int rows = std::min(rowsPer, height - y0);
-            if (color_row_stride == cRow) memcpy(stage + (size_t)y0 * cRow, color + (size_t)y0 * cRow, cRow * rows);
-            else for (int y = y0; y < y0 + rows; ++y) memcpy(stage + (size_t)y * cRow, color + (size_t)y * color_row_stride, cRow);
-            rc = launch_cvt(stage + (size_t)y0 * cRow, cRow * height, cRow, channels, rgb_order, h->dLevel0 + (size_t)y0 * grayRow,
-                            (size_t)h->l0FrameBytes, grayRow, width, rows, 1, st);
+        // colour crosses the bus by DMA (a kernel reading 0.9 MB through the mapping in 4-byte pieces measured ~3x slower than
+        // the copy engine), cvtColor then runs out of device memory
+        const size_t colorDev = (cRow * height + 255) & ~(size_t)255;
+        if (colorDev > h->frontStageBytes) {
+            ORBX_CUDA(cudaStreamSynchronize(st));
+            if (h->dFrontStage) cudaFree(h->dFrontStage);
+            h->dFrontStage = nullptr; h->frontStageBytes = 0;
+            ORBX_CUDA(cudaMalloc((void**)&h->dFrontStage, colorDev));
+            h->frontStageBytes = colorDev;
+        }
+        u8* dColor = h->dFrontStage;
+        if (mapped(color)) {
+            ORBX_CUDA(cudaMemcpy2DAsync(dColor, cRow, color, color_row_stride, cRow, height, cudaMemcpyHostToDevice, st));
+            rc = launch_cvt(dColor, cRow * height, cRow, channels, rgb_order, h->dLevel0, (size_t)h->l0FrameBytes, grayRow, width, height, 1, st);
             if (rc) return rc;
+        } else {
+            // pageable image: the host copies it into the mapped staging in row slices and cvtColor converts a slice THROUGH the
+            // mapping while the next one is being copied (measured: 301 us per call against 328-360 us with a DMA per slice; a
+            // 640x480 RGB image is 0.9 MB: ~70 us of memcpy that would otherwise all sit in front of the GPU)
+            static const int slices = getenv("ORBX_RGBD_SLICES") ? std::max(1, atoi(getenv("ORBX_RGBD_SLICES"))) : 4;
+            const int rowsPer = ((height + slices - 1) / slices + 3) & ~3;
+            for (int y0 = 0; y0 < height; y0 += rowsPer) {
+                const int rows = std::min(rowsPer, height - y0);
+                if (color_row_stride == cRow) memcpy(stage + (size_t)y0 * cRow, color + (size_t)y0 * cRow, cRow * rows);
+                else for (int y = y0; y < y0 + rows; ++y) memcpy(stage + (size_t)y * cRow, color + (size_t)y * color_row_stride, cRow);
+                rc = launch_cvt(stage + (size_t)y0 * cRow, cRow * height, cRow, channels, rgb_order, h->dLevel0 + (size_t)y0 * grayRow,
+                                (size_t)h->l0FrameBytes, grayRow, width, rows, 1, st);
+                if (rc) return rc;
+            }
         }
     }
+    if (trace) { tt[0] = now(); cudaEventRecord(tev[1], st); }
     h->storeUndistorted = false;
     rc = orbx_launch_single_frame(h);                    // the extractor's graph: results in slot 0, mvKeys + descriptors in the pack
     if (rc) return rc;
+    if (trace) { tt[1] = now(); cudaEventRecord(tev[2], st); }
     // ---- depth: only the pixels under the keypoints are read, through the mapping (the host copy of a pageable depth map
     // overlaps the extractor) --------------------------------------------------------------------------------------------
     const u8* dz = mapped(depth);
@@ -427,6 +456,7 @@ int orbx_frame_rgbd(orbx_handle* h, const uint8_t* color, int channels, int rgb_
         else for (int y = 0; y < height; ++y) memcpy(stage + offDepth + (size_t)y * zRow, (const u8*)depth + (size_t)y * depth_row_stride, zRow);
         dz = stage + offDepth; dzRow = zRow;
     }
+    if (trace) tt[2] = now();
     const OrbxPackLayout PL = orbx_pack_layout(h->kpCap);
     frame_front_kernel<<<dim3((unsigned)((cap + 127) / 128), 1), 128, 0, st>>>(cam_double(cam), cam->bf, h->dKps, h->dCount, h->kpCap, 0, dz, depth_is_u16,
                                                                               depth_factor, depth_factor != 1.0f, (long long)(dzRow * height), (long long)dzRow,
@@ -434,10 +464,13 @@ int orbx_frame_rgbd(orbx_handle* h, const uint8_t* color, int channels, int rgb_
                                                                               (float*)(h->hPack + PL.ur), (float*)(h->hPack + PL.z));
     ORBX_CUDA(cudaGetLastError());
     ORBX_CUDA(cudaEventRecord(h->evPack, st));           // everything the caller gets is in the pack here
+    if (trace) cudaEventRecord(tev[3], st);
     h->storeUndistorted = true;                          // the store now describes an undistorted frame (grid, matchers)
     rc = orbx_build_grids(h, 0, 1, width, height);       // for the matchers that run on slot 0 next: finishes behind the caller's back
     if (rc) return rc;
+    if (trace) tt[3] = now();
     ORBX_CUDA(cudaEventSynchronize(h->evPack));
+    if (trace) tt[4] = now();
     const int32_t* hdr = (const int32_t*)h->hPack;
     if (hdr[1]) {
         ORBX_CUDA(cudaMemsetAsync(h->dStatus, 0, sizeof(int), st));
@@ -453,6 +486,20 @@ int orbx_frame_rgbd(orbx_handle* h, const uint8_t* color, int channels, int rgb_
     if (depth_out && cnt > 0) memcpy(depth_out, h->hPack + PL.z, (size_t)cnt * 4);
     if (bounds_out) for (int i = 0; i < 4; ++i) bounds_out[i] = h->bounds[i];
     if (n) *n = cnt;
+    if (trace) {
+        tt[5] = now();
+        cudaEventRecord(tev[4], st); cudaEventSynchronize(tev[4]);
+        for (int i = 0; i < 4; ++i) { float ms = 0; cudaEventElapsedTime(&ms, tev[i], tev[i + 1]); eacc[i] += ms * 1e3; }
+        for (int i = 0; i < 6; ++i) tacc[i] += tt[i] - tt0;
+        if (++tcalls == 200) {
+            fprintf(stderr, "orbx_frame_rgbd trace (us from entry, mean of 200): colour enqueued %.1f, graph launched %.1f, depth staged %.1f, "
+                            "front+grid launched %.1f, synchronised %.1f, outputs copied %.1f\n",
+                    tacc[0] / 200, tacc[1] / 200, tacc[2] / 200, tacc[3] / 200, tacc[4] / 200, tacc[5] / 200);
+            fprintf(stderr, "orbx_frame_rgbd trace, device (us, CUDA events): colour in + cvtColor %.1f, extractor graph + pack %.1f, frame front %.1f, grid %.1f\n",
+                    eacc[0] / 200, eacc[1] / 200, eacc[2] / 200, eacc[3] / 200);
+            tcalls = 0; for (double& a : tacc) a = 0; for (double& a : eacc) a = 0;
+        }
+    }
     return ORBX_OK;
 }
 
