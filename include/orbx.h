@@ -472,6 +472,14 @@ int orbm_generate_point_clouds(const float* depth, size_t depth_row_stride, size
                                const orbx_camera* cam, const double* pose_inv, int device, orbx_cloud_point* points,
                                int capacity, int32_t* counts);
 
+/* pcl::VoxelGrid<pcl::PointXYZRGBA> down-sampling as PointCloudMapping uses it (src/PointCloudMap.cc:41, 240-241, 259-260,
+ * 277-280: leaf = resolution on all three axes, default parameters): one point per occupied voxel, in ascending voxel-index
+ * order, at the centroid of the voxel's points (colour = truncated mean, a = 255).  A voxel's points are summed in input order
+ * (PCL's own order follows an unstable sort: its float sums are not bit-defined; the set of occupied voxels and the colours are).
+ * points: n records (host); out: room for `capacity` records (NULL: only count); *nout = voxels.  ORBX_E_CAPACITY when the grid
+ * would overflow PCL's int voxel index (PCL then returns the cloud unfiltered) or when capacity is too small. */
+int orbm_voxel_grid(const orbx_cloud_point* points, int n, float leaf, int device, orbx_cloud_point* out, int capacity, int32_t* nout);
+
 /* The per-feature record of Map::Save's keyframe block (src/Map.cc:160-180): 64 bytes = pt.x, pt.y, size, angle,
  * response (float), octave (int), the 32 descriptor bytes, and the unsigned long index of the feature's MapPoint
  * (ULONG_MAX = none).  Packs the features of result slot `slot` (mvKeys, mDescriptors as the extractor left them on

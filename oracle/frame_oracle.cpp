@@ -17,11 +17,16 @@
 // for 16U -> 32F convertTo (restated from the OpenCV sources: the cv2 Python module has no Mat::convertTo).
 // Compile with -ffp-contract=off: every double operation below is separately rounded.
 
+#include <cfloat>
+#include <climits>
 #include <cmath>
 #include <cstddef>
 #include <climits>
 #include <cstdint>
 #include <cstring>
+#include <algorithm>
+#include <utility>
+#include <vector>
 
 extern "C" {
 
@@ -134,6 +139,71 @@ int oracle_generate_point_cloud(const float* depth, size_t dstride_elems, const 
             ++count;
         }
     return count;
+}
+
+// pcl::VoxelGrid<pcl::PointXYZRGBA>::applyFilter with its default parameters (downsample_all_data, no field filter, no minimum
+// count), the call at src/PointCloudMap.cc:240-241, 259-260, 277-280 with the leaf size of :41.  PCL (>= 1.7, CMakeLists.txt:39) is
+// not vendored under /root/reference: this restates its published algorithm (pcl/filters/impl/voxel_grid.hpp) — PARITY UNPINNED:
+//   bounds of the finite points; inverse leaf = 1 / leaf; min_b = floor(min * inv), div_b = floor(max * inv) - min_b + 1;
+//   a grid whose cell count would overflow an int is refused (PCL warns and passes the cloud through; here: -2);
+//   idx = i + j * div_x + k * div_x * div_y with i = int(floor(x * inv) - float(min_b.x));
+//   one output point per occupied voxel in ascending idx order: the mean of its points (x, y, z summed as float, r, g, b as
+//   integers then truncated after the float division, a = 255 as PCL >= 1.8 leaves it).
+// DETERMINISATION: PCL sorts (idx, point) pairs with an unstable std::sort and adds a voxel's points in that order, so its float
+// centroids are not bit-defined; here a voxel's points are added in input order (a stable sort), one legitimate execution.
+// points / out: 16-byte records {float x, y, z; u8 b, g, r, a}.  Returns the voxel count (-1: cap too small, -2: index overflow).
+int oracle_voxel_grid(const uint8_t* points, int n, float leaf, uint8_t* out, int cap)
+{
+    struct P { float x, y, z; uint8_t b, g, r, a; };
+    const P* p = reinterpret_cast<const P*>(points);
+    P* o = reinterpret_cast<P*>(out);
+    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (int i = 0; i < n; ++i) {
+        if (!std::isfinite(p[i].x) || !std::isfinite(p[i].y) || !std::isfinite(p[i].z)) continue;
+        const float v[3] = {p[i].x, p[i].y, p[i].z};
+        for (int k = 0; k < 3; ++k) { mn[k] = std::min(mn[k], v[k]); mx[k] = std::max(mx[k], v[k]); }
+    }
+    if (mn[0] > mx[0]) return 0;
+    const float inv = 1.0f / leaf;
+    long long dchk = 1, div[3];
+    int minb[3];
+    for (int k = 0; k < 3; ++k) {
+        dchk *= (long long)((mx[k] - mn[k]) * inv) + 1;
+        if (dchk > INT_MAX) return -2;
+        minb[k] = (int)std::floor(mn[k] * inv);
+        div[k] = (long long)(int)std::floor(mx[k] * inv) - minb[k] + 1;
+    }
+    if (div[0] * div[1] * div[2] > INT_MAX) return -2;
+    const int mul1 = (int)div[0], mul2 = (int)(div[0] * div[1]);
+    std::vector<std::pair<uint32_t, int>> iv;
+    iv.reserve(n);
+    for (int i = 0; i < n; ++i) {
+        if (!std::isfinite(p[i].x) || !std::isfinite(p[i].y) || !std::isfinite(p[i].z)) continue;
+        const int a = (int)(std::floor(p[i].x * inv) - (float)minb[0]);
+        const int b = (int)(std::floor(p[i].y * inv) - (float)minb[1]);
+        const int c = (int)(std::floor(p[i].z * inv) - (float)minb[2]);
+        iv.push_back(std::make_pair((uint32_t)(a + b * mul1 + c * mul2), i));
+    }
+    std::stable_sort(iv.begin(), iv.end(), [](const std::pair<uint32_t, int>& l, const std::pair<uint32_t, int>& r) { return l.first < r.first; });
+    int nv = 0;
+    for (size_t s = 0; s < iv.size();) {
+        size_t e = s;
+        float sx = 0.f, sy = 0.f, sz = 0.f;
+        unsigned sr = 0, sg = 0, sb = 0;
+        while (e < iv.size() && iv[e].first == iv[s].first) {
+            const P& q = p[iv[e].second];
+            sx += q.x; sy += q.y; sz += q.z; sr += q.r; sg += q.g; sb += q.b;
+            ++e;
+        }
+        if (nv >= cap) return -1;
+        const float fc = (float)(e - s);
+        P r;
+        r.x = sx / fc; r.y = sy / fc; r.z = sz / fc;
+        r.r = (uint8_t)(int)((float)sr / fc); r.g = (uint8_t)(int)((float)sg / fc); r.b = (uint8_t)(int)((float)sb / fc); r.a = 255;
+        o[nv++] = r;
+        s = e;
+    }
+    return nv;
 }
 
 // The feature loop of Map::_WriteKeyFrame (src/Map.cc:160-180) into a byte buffer: kps = 28-byte cv::KeyPoint records.

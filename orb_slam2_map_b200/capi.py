@@ -64,7 +64,7 @@ EXPORTS = [
     "orbx_cvt_gray", "orbx_depth_to_float", "orbx_undistort_points", "orbx_image_bounds", "orbx_frames_rgbd", "orbx_frame_rgbd",
     "orbx_download_frame_front",
     "orbm_vocabulary_upload", "orbm_vocabulary_free", "orbm_bow_transform", "orbm_search_by_bow", "orbm_distinctive_descriptors",
-    "orbm_search_for_triangulation", "orbm_fuse", "orbm_search_by_sim3", "orbm_generate_point_clouds", "orbx_pack_map_records", "orbx_extract_match_to_host",
+    "orbm_search_for_triangulation", "orbm_fuse", "orbm_search_by_sim3", "orbm_generate_point_clouds", "orbm_voxel_grid", "orbx_pack_map_records", "orbx_extract_match_to_host",
 ]
 
 
@@ -653,3 +653,15 @@ def generate_point_clouds(depth, bgr, cam: "Camera", pose_inv=None, step=3, devi
     check(lib().orbm_generate_point_clouds(_p(depth), C.c_size_t(W), C.c_size_t(W * H), _p(bgr), C.c_size_t(W * 3), C.c_size_t(W * H * 3),
                                            W, H, F, step, C.byref(cam), _p(pose_inv), device, _p(pts), cap, _p(counts)))
     return [pts[f, :counts[f]].copy() for f in range(F)]
+
+
+def voxel_grid(points: np.ndarray, leaf: float, device=0, capacity=None):
+    """orbm_voxel_grid: points = CLOUD_DTYPE records (host) -> one centroid per occupied voxel, ascending voxel index"""
+    pts = np.ascontiguousarray(points, CLOUD_DTYPE)
+    n = C.c_int32(0)
+    if capacity is None:
+        check(lib().orbm_voxel_grid(C.c_void_p(pts.ctypes.data), len(pts), C.c_float(leaf), device, None, 0, C.byref(n)))
+        capacity = n.value
+    out = np.zeros(max(capacity, 1), CLOUD_DTYPE)
+    check(lib().orbm_voxel_grid(C.c_void_p(pts.ctypes.data), len(pts), C.c_float(leaf), device, C.c_void_p(out.ctypes.data), capacity, C.byref(n)))
+    return out[:n.value].copy()

@@ -308,12 +308,25 @@ int orbm_knn2_device(const uint8_t* queries, int64_t nq, const uint8_t* database
     int dev = 0, sms = 148;
     ORBX_CUDA(cudaGetDevice(&dev));
     ORBX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    // few query tiles: split the database so the grid still fills the machine (2 CTAs per SM)
+    // CTAs of one launch all run the same time, so the launch costs ceil(CTAs / resident slots) waves: the database is split
+    // into s row ranges (grid.y) so that the last wave is full — 1024 query tiles on 444 slots are 2.31 waves of work but 3
+    // waves of time unsplit, 7 thirds of a wave with s = 3 — and so that a few query tiles still fill the machine.  Every
+    // split costs a pipeline prologue and a partial result per query (merged by K11): 0.5 % per split is charged.
+    int occ = 2;
+    switch (g_knn_variant) {
+    case 0: cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, knn2_kernel<0>, KNN_THREADS, 0); break;
+    case 2: cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, knn2_kernel<2>, KNN_THREADS, 0); break;
+    default: cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, knn2_kernel<1>, KNN_THREADS, 0); break;
+    }
+    const long long slots = (long long)std::max(occ, 1) * sms;
     long long splits = 1;
-    if (qtiles < 2LL * sms && ndb > 0) {
-        splits = (2LL * sms + qtiles - 1) / qtiles;
-        const long long maxSplits = std::max<long long>(1, ndb / 4096);
-        splits = std::min(splits, maxSplits);
+    if (ndb > 0) {
+        const long long maxSplits = std::max<long long>(1, std::min<long long>(32, ndb / 16384));
+        double best = 1e300;
+        for (long long c = 1; c <= maxSplits; ++c) {
+            const double cost = (double)((qtiles * c + slots - 1) / slots) / (double)c * (1.0 + 0.005 * (double)(c - 1));
+            if (cost < best - 1e-12) { best = cost; splits = c; }
+        }
     }
     splits = std::max<long long>(splits, (ndb + KNN_MAX_SPLIT_ROWS - 1) / KNN_MAX_SPLIT_ROWS);      // the packed key holds 23 bits of row index
     long long rowsPerSplit = ndb > 0 ? (ndb + splits - 1) / splits : 1;
@@ -355,11 +368,15 @@ int orbm_measure_int_rates(double rates[4])
     ORBX_CUDA(cudaMalloc((void**)&sink, 64));
     cudaEvent_t e0, e1;
     ORBX_CUDA(cudaEventCreate(&e0)); ORBX_CUDA(cudaEventCreate(&e1));
-    const int ctas = sms * 8, iters = 8192, rows = 16384;
+    // whole waves of the probe kernels (256 threads: the rate probes hold 8 CTAs per SM, the K10 mix as many as its registers allow)
+    int occMix = 2;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occMix, knn_mix_kernel<1>, KNN_THREADS, 0);
+    const int iters = 8192, rows = 16384;
     for (int which = 0; which < 4; ++which) {
         float best = 1e30f;
         for (int rep = 0; rep < 4; ++rep) {                         // rep 0 = warm-up
             ORBX_CUDA(cudaEventRecord(e0, 0));
+            const int ctas = which < 3 ? sms * 8 : sms * std::max(occMix, 1) * 2;
             if (which < 3) int_rate_kernel<<<ctas, 256>>>(which, iters, 12345u + rep, sink);
             else if (g_knn_variant == 0) knn_mix_kernel<0><<<ctas, KNN_THREADS>>>(rows, 777u + rep, (int*)sink);
             else if (g_knn_variant == 2) knn_mix_kernel<2><<<ctas, KNN_THREADS>>>(rows, 777u + rep, (int*)sink);
@@ -370,7 +387,7 @@ int orbm_measure_int_rates(double rates[4])
             ORBX_CUDA(cudaEventElapsedTime(&ms, e0, e1));
             if (rep > 0) best = std::min(best, ms);
         }
-        const double work = which < 3 ? (double)ctas * 256 * iters * MB_ILP : (double)ctas * KNN_THREADS * KNN_QPT * rows;
+        const double work = which < 3 ? (double)sms * 8 * 256 * iters * MB_ILP : (double)sms * std::max(occMix, 1) * 2 * KNN_THREADS * KNN_QPT * rows;
         rates[which] = work / (best * 1e-3);
     }
     cudaEventDestroy(e0); cudaEventDestroy(e1);

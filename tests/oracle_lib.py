@@ -477,3 +477,11 @@ def write_keyframe_features(kps, desc, mp_index=None):
     nb = lib().oracle_write_keyframe_features(_p(kps), _p(desc), _p(mp), _p(has), C.c_int(n), _p(out))
     assert nb == n * 64
     return out[:n].copy()
+
+
+def voxel_grid(points: np.ndarray, leaf: float):
+    pts = np.ascontiguousarray(points, CLOUD_DTYPE)
+    out = np.zeros(max(len(pts), 1), CLOUD_DTYPE)
+    n = lib().oracle_voxel_grid(_p(pts), C.c_int(len(pts)), C.c_float(leaf), _p(out), C.c_int(len(out)))
+    assert n >= 0, n
+    return out[:n].copy()
