@@ -113,43 +113,62 @@ pyr_resize4_kernel(Level0 l0, int fromL0, const u8* __restrict__ srcBase, long l
     const int yend = min(y0 + th, dh);
     const int sFirst = cy[y0].x & 0xffff;
     const int nsrc = min((cy[yend - 1].x >> 16) - sFirst + 1, nsrcMax);
-    uint2* Hs = rsH + (size_t)wid * nsrcMax * 32 + lane;
-    // ---- phase 1: horizontal sums of the strip's source rows -------------------------------------
+    // sum table of this warp: [source row][element 0..3][lane] as 16-bit values: a warp's access to one element of one row is 64
+    // contiguous bytes (conflict-free as LDS.U16 / STS.U16; 8-byte records per lane cost two wavefronts per access)
+    unsigned short* Hs = reinterpret_cast<unsigned short*>(rsH + (size_t)wid * nsrcMax * 32) + lane;
+    // ---- phase 1: horizontal sums of the strip's source rows, four rows (12 loads) in flight.  nsrcMax is a multiple of 4: the
+    // rows past nsrc of the last group are computed from a clamped source row and stored, never read -----------------------
     {
         const uint32_t* p = colp + (long long)sFirst * rowWords;
-        for (int r = 0; r < nsrc; r += 4) {
+        const int lim = sh - 1 - sFirst;                     // last source row of the image, relative to the strip
+        unsigned short* hp = Hs;
+        for (int r = 0; r < nsrc; r += 4, hp += 4 * 128) {
             uint32_t w[4][3];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                const uint32_t* q = p + (long long)min(r + u, nsrc - 1) * rowWords;
+                const uint32_t* q = p + min(r + u, lim) * rowWords;
                 w[u][0] = __ldg(q); w[u][1] = __ldg(q + 1); w[u][2] = __ldg(q + 2);
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                uint32_t Hq[4];
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
                     const uint32_t taps = __byte_perm(__byte_perm(w[u][0], w[u][1], c.sel1[i]), w[u][2], c.sel2[i]);
-                    Hq[i] = __dp2a_lo(c.coef[i], taps, 0u) >> 4;                    // (p0*a0 + p1*a1) >> 4 < 2^15
+                    hp[u * 128 + i * 32] = (unsigned short)(__dp2a_lo(c.coef[i], taps, 0u) >> 4);      // (p0*a0 + p1*a1) >> 4 < 2^15
                 }
-                if (r + u < nsrc) Hs[(r + u) * 32] = make_uint2(Hq[0] | (Hq[1] << 16), Hq[2] | (Hq[3] << 16));
             }
         }
     }
     __syncwarp();
-    // ---- phase 2: vertical blends ((b0*SA >> 16) + (b1*SB >> 16) + 2) >> 2 ------------------------
-    for (int y = y0; y < yend; ++y) {
-        const int2 cyv = cy[y];
-        const int ia = min((cyv.x & 0xffff) - sFirst, nsrc - 1), ib = min((cyv.x >> 16) - sFirst, nsrc - 1);
-        const uint32_t b0 = (uint32_t)(cyv.y & 0xffff), b1 = (uint32_t)(cyv.y >> 16);
-        const uint2 A = Hs[ia * 32], B = Hs[ib * 32];
-        // even elements sit in the low half (multiply by b << 16), odd ones in the high half (multiply by b)
-        const uint32_t o0 = (__umulhi(b0 << 16, A.x & 0xffffu) + __umulhi(b1 << 16, B.x & 0xffffu) + 2u) >> 2;
-        const uint32_t o1 = (__umulhi(b0, A.x & 0xffff0000u) + __umulhi(b1, B.x & 0xffff0000u) + 2u) >> 2;
-        const uint32_t o2 = (__umulhi(b0 << 16, A.y & 0xffffu) + __umulhi(b1 << 16, B.y & 0xffffu) + 2u) >> 2;
-        const uint32_t o3 = (__umulhi(b0, A.y & 0xffff0000u) + __umulhi(b1, B.y & 0xffff0000u) + 2u) >> 2;
-        if (x < dw)
-            *reinterpret_cast<uint32_t*>(dst + (long long)y * dstPitch + x) = o0 | (o1 << 8) | (o2 << 16) | (o3 << 24);
+    // ---- phase 2: vertical blends ((b0*SA >> 16) + (b1*SB >> 16) + 2) >> 2.  The row constants (offsets of the two source rows
+    // in the sum table, coefficients) are computed lane-parallel, one output row per lane, and broadcast by shuffle; the sums
+    // are read back as 16-bit values (no masks); each product is one IMAD.HI that also carries the running sum (the +2 rides
+    // in as the first addend); two results are packed by an IMAD, shifted as a pair and byte-selected: 3 ALU-pipe
+    // instructions per 4 pixels, the rest on the FMA and load/store pipes ---------------------------------------------------
+    const unsigned short* Hb = Hs;
+    u8* dp = dst + (long long)y0 * dstPitch + x;
+    for (int yb = y0; yb < yend; yb += 32) {
+        uint32_t offs = 0, coefs = 0;
+        if (yb + lane < yend) {
+            const int2 cyv = cy[yb + lane];
+            const int ia = min((cyv.x & 0xffff) - sFirst, nsrc - 1), ib = min((cyv.x >> 16) - sFirst, nsrc - 1);
+            offs = (uint32_t)(ia * 128) | ((uint32_t)(ib * 128) << 16);             // in 16-bit elements: row * 32 lanes * 4
+            coefs = (uint32_t)cyv.y;                                                // b0 | b1 << 16
+        }
+        const int rows = min(32, yend - yb);
+        for (int j = 0; j < rows; ++j, dp += dstPitch) {
+            const uint32_t o = __shfl_sync(0xffffffffu, offs, j), cf = __shfl_sync(0xffffffffu, coefs, j);
+            const unsigned short* A = Hb + (o & 0xffffu);
+            const unsigned short* B = Hb + (o >> 16);
+            const uint32_t b0 = cf << 16, b1 = cf & 0xffff0000u;                    // coefficient << 16: umulhi gives (b * S) >> 16
+            const uint32_t s0 = __umulhi(b1, B[0]) + (__umulhi(b0, A[0]) + 2u);
+            const uint32_t s1 = __umulhi(b1, B[32]) + (__umulhi(b0, A[32]) + 2u);
+            const uint32_t s2 = __umulhi(b1, B[64]) + (__umulhi(b0, A[64]) + 2u);
+            const uint32_t s3 = __umulhi(b1, B[96]) + (__umulhi(b0, A[96]) + 2u);
+            // s <= 1022: (s >> 2) fits a byte, so the pair shift cannot leak between the halves' result bytes
+            const uint32_t p01 = (s1 * 65536u + s0) >> 2, p23 = (s3 * 65536u + s2) >> 2;
+            if (x < dw) *reinterpret_cast<uint32_t*>(dp) = __byte_perm(p01, p23, 0x6420);
+        }
     }
 }
 
@@ -1294,7 +1313,7 @@ static int run_chunk_impl(orbx_handle* h, Level0 l0, int nframes, int firstSlot,
             const int nstrips = std::max(1, (D.h + rsTarget - 1) / rsTarget), th = (D.h + nstrips - 1) / nstrips;
             dim3 grid((D.w + 127) / 128, (nstrips + RS_WARPS - 1) / RS_WARPS, nframes);
             // source rows a strip of th output rows can touch: th * (S.h / D.h) + 2, with slack for the table's rounding
-            const int nsrcMax = (int)((long long)th * S.h / D.h) + 4;
+            const int nsrcMax = ((int)((long long)th * S.h / D.h) + 4 + 3) & ~3;      // a multiple of 4: phase 1 stores whole groups
             const size_t rsSmem = (size_t)RS_WARPS * nsrcMax * 32 * sizeof(uint2);
             if (rsSmem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(pyr_resize4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rsSmem));
             pyr_resize4_kernel<<<grid, RS_WARPS * 32, rsSmem, st>>>(l0, l == 1 ? 1 : 0, src, sfs, sp, S.w, S.h, h->dRaw + D.off, g.pyrFrameBytes,
