@@ -200,7 +200,8 @@ typedef struct orbm_proj_query {
                              |u_right - mvuRight[idx]| > max_right_err -> skip; <0 = gate off   */
     float angle;          /* keypoint angle of the source observation (rotation histogram)     */
     int32_t level_lo, level_hi; /* extra per-candidate octave filter applied after the area query
-                                   (KeyFrame/Sim3 variant, src/ORBmatcher.cc:374-377); -1 = off */
+                                   (KeyFrame/Sim3 variant, src/ORBmatcher.cc:374-377): kpLevel in [lo, hi].
+                                   level_lo < 0 = filter OFF, so a predicted level 0 is passed as [0, 0] */
 } orbm_proj_query;
 
 enum {
@@ -210,7 +211,14 @@ enum {
     ORBM_PROJ_SIM3 = 3       /* (KeyFrame*, Scw, vpPoints, vpMatched, th) src/ORBmatcher.cc:290-403 */
 };
 
-/* occupied: in/out [frame->n] bytes. in: 1 if the keypoint already holds a map point that blocks
+/* Flattening rules (host/orbx.hpp ProjectionFlatten spells them as code; tests/matcher_cases.py checks them against the
+ * reference's own functions): LOCALMAP radius = RadiusByViewingCos(cos) [* th if th != 1] * scale[level] where the float cosine
+ * is compared with the DOUBLE literal 0.998; levels [level-1, level]; max_right_err = radius.  LASTFRAME radius = th *
+ * scale[last octave]; levels [oct, -1] forward, [0, oct] backward, else [oct-1, oct+1]; u_right = u - mbf*invzc.  KEYFRAME levels
+ * [level-1, level+1].  SIM3 / Fuse: min_level = max_level = -1, level_lo = max(level-1, 0), level_hi = level.  Points the
+ * reference skips before its search (bad, already found, outside the image bounds / IsInImage, out of the distance range, not in
+ * view) are simply not in the query list.
+ * occupied: in/out [frame->n] bytes. in: 1 if the keypoint already holds a map point that blocks
  * new matches (Observations()>0 for LOCALMAP/LASTFRAME, non-NULL for KEYFRAME/SIM3);
  * assigned: out [frame->n], index of the query that finally owns keypoint i, or -1 (the
  * reference overwrites F.mvpMapPoints[bestIdx] in query order; rotation-culled ones are -1).

@@ -213,6 +213,66 @@ struct ProjectionQueries {
     std::vector<uint8_t> blocks;         // pMP->Observations() > 0
 };
 
+// The reference's own expressions that turn one projected MapPoint into a query (what the maintainer's loop computes before it
+// appends to ProjectionQueries::q), float for float.  scale = F.mvScaleFactors.
+struct ProjectionFlatten {
+    // src/ORBmatcher.cc:61-77 — r = RadiusByViewingCos(viewCos) [* th when th != 1]; window r * scale[level]; levels [level-1, level];
+    // stereo gate |mTrackProjXR - mvuRight| <= the same window.  The cosine is compared with the DOUBLE literal 0.998 (:131-137).
+    static orbm_proj_query LocalMap(float projX, float projY, float projXR, int level, float viewCos, float th, const std::vector<float>& scale)
+    {
+        float r = (double)viewCos > 0.998 ? 2.5f : 4.0f;
+        if (th != 1.0f) r *= th;
+        orbm_proj_query q = blank();
+        q.u = projX; q.v = projY; q.radius = r * scale[level];
+        q.min_level = level - 1; q.max_level = level;
+        q.u_right = projXR; q.max_right_err = q.radius;
+        return q;
+    }
+    // src/ORBmatcher.cc:1374-1410 — window th * scale[octave of the last frame's keypoint]; levels by the motion direction
+    // (forward: [octave, any], backward: [0, octave], else [octave-1, octave+1]); ur = u - mbf * invzc, gate = the window.
+    static orbm_proj_query LastFrame(float u, float v, float invzc, int lastOctave, float angle, float th, float mbf, bool forward,
+                                     bool backward, const std::vector<float>& scale)
+    {
+        orbm_proj_query q = blank();
+        q.u = u; q.v = v; q.radius = th * scale[lastOctave];
+        if (forward) { q.min_level = lastOctave; q.max_level = -1; }
+        else if (backward) { q.min_level = 0; q.max_level = lastOctave; }
+        else { q.min_level = lastOctave - 1; q.max_level = lastOctave + 1; }
+        q.u_right = u - mbf * invzc; q.max_right_err = q.radius;
+        q.angle = angle;
+        return q;
+    }
+    // src/ORBmatcher.cc:1524-1529 — window th * scale[nPredictedLevel], levels [level-1, level+1]
+    static orbm_proj_query KeyFrame(float u, float v, int level, float angle, float th, const std::vector<float>& scale)
+    {
+        orbm_proj_query q = blank();
+        q.u = u; q.v = v; q.radius = th * scale[level];
+        q.min_level = level - 1; q.max_level = level + 1;
+        q.angle = angle;
+        return q;
+    }
+    // src/ORBmatcher.cc:357-377, :884-905, :1041-1062, :1196-1215 — KeyFrame::GetFeaturesInArea has no level window; the octave filter
+    // kpLevel in [level-1, level] is applied per candidate.  A NEGATIVE level_lo switches that filter off in the flat form, so a
+    // predicted level 0 is passed as [0, 0].  u_right = u - bf * invz is read by Fuse's chi-square gate only.
+    static orbm_proj_query Sim3OrFuse(float u, float v, float invz, int level, float th, float bf, const std::vector<float>& scale)
+    {
+        orbm_proj_query q = blank();
+        q.u = u; q.v = v; q.radius = th * scale[level];
+        q.level_lo = level > 0 ? level - 1 : 0; q.level_hi = level;
+        q.u_right = u - bf * invz;
+        return q;
+    }
+private:
+    static orbm_proj_query blank()
+    {
+        orbm_proj_query q;
+        std::memset(&q, 0, sizeof(q));
+        q.min_level = q.max_level = q.level_lo = q.level_hi = -1;
+        q.max_right_err = -1.f;
+        return q;
+    }
+};
+
 struct ProjectionResult {
     int nmatches = 0;
     std::vector<int32_t> assigned;       // per keypoint: query that owns it at the end, or -1

@@ -30,6 +30,16 @@ def test_host_classes_compile_and_link(tmp_path):
                            os.path.join(ROOT, "tests", "host", "opencv_flavour_check.cpp")])
 
 
+def test_projection_flatten_rules(tmp_path):
+    """ProjectionFlatten (orbx.hpp) = the reference's query expressions (src/ORBmatcher.cc:61-77, :1374-1410, :1524-1529,
+    :357-377); the same rules tests/matcher_cases.py proves against the compiled reference.  Host arithmetic only."""
+    exe = str(tmp_path / "flatten_check")
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-Werror", "-I", HOST, os.path.join(ROOT, "tests", "host", "flatten_check.cpp"),
+                           "-o", exe, "-L", PKG, "-lorbx", "-Wl,-rpath," + PKG])
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 0 and "flatten check ok" in r.stdout, r.stdout
+
+
 def test_host_classes_fail_loudly_without_gpu(tmp_path):
     if capi.lib().orbx_device_count() > 0:
         pytest.skip("needs a machine without a CUDA device")
