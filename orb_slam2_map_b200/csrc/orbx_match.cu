@@ -675,6 +675,265 @@ search_proj_kernel(FrameStore fs, int slot, GridParams gp, const float* __restri
 }
 
 // =============================================================================================
+// K9, latency form (one frame of at most PROJ_SCAN_MAXN keypoints: the per-frame tracking call).
+//  K9a  proj_list_kernel     warp per query, all SMs.  No grid: the lanes sweep the frame's keypoints (coalesced, no
+//       dependent loads) with the window test AND the cell-range test of Frame::GetFeaturesInArea (a keypoint counts only
+//       if the cell AssignFeaturesToGrid files it under lies in the query's cell window, src/Frame.cc:332-377), compact the
+//       hits, and keep the PROJ_L = 32 smallest keys dist|cell|idx|octave sorted across the lanes (bitonic sort + merge).
+//  K9b  proj_fixpoint_kernel  one CTA.  The reference's loop is "query q takes the first key of its list that no EARLIER
+//       query has blocked".  Iterate that rule for all queries at once from the takes of the previous iteration (owner[k] =
+//       lowest blocking query that takes keypoint k): query q is final once every earlier query is, so the prefix of final
+//       queries grows by at least one per iteration and the fixed point is the sequential result; real frames converge in a
+//       handful of iterations.  A query whose 32-key list is truncated and used up is searched again under the occupancy
+//       it sees (same sweep, by a warp).
+// =============================================================================================
+#define PROJ_L 32
+#define PROJ_SCAN_MAXN 4096
+#define PROJ_FIX_THREADS 1024
+#define PROJ_SCAN_BUF 64
+
+struct ProjScan {
+    const orbx_keypoint* kps; const u8* desc; const float* uRight; GridParams gp; int n; bool gate;
+};
+
+__device__ __forceinline__ unsigned long long min64(unsigned long long a, unsigned long long b) { return a < b ? a : b; }
+__device__ __forceinline__ unsigned long long max64(unsigned long long a, unsigned long long b) { return a < b ? b : a; }
+
+// ascending bitonic sort of one key per lane
+__device__ __forceinline__ unsigned long long warp_sort32(unsigned long long v, int lane)
+{
+#pragma unroll
+    for (int k = 2; k <= 32; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const unsigned long long o = __shfl_xor_sync(FULL, v, j);
+            const bool takeMin = ((lane & j) == 0) == ((lane & k) == 0);
+            v = takeMin ? min64(o, v) : max64(o, v);
+        }
+    }
+    return v;
+}
+
+// the 32 smallest of two ascending 32-key sequences, ascending
+__device__ __forceinline__ unsigned long long warp_merge32(unsigned long long a, unsigned long long b, int lane)
+{
+    unsigned long long v = min64(a, __shfl_sync(FULL, b, 31 - lane));       // bitonic
+#pragma unroll
+    for (int j = 16; j > 0; j >>= 1) {
+        const unsigned long long o = __shfl_xor_sync(FULL, v, j);
+        v = (lane & j) == 0 ? min64(o, v) : max64(o, v);
+    }
+    return v;
+}
+
+// Lane l returns the l-th smallest candidate key of the query (~0 where there are fewer).  isFree(idx): the occupancy
+// the query sees.  buf: PROJ_SCAN_BUF entries of shared memory owned by this warp.
+template <typename Free>
+__device__ __forceinline__ unsigned long long proj_scan_sorted(const ProjScan& c, const orbm_proj_query& Q, const u8* qdescRow,
+                                                                int lane, unsigned long long* buf, Free isFree)
+{
+    const unsigned long long NONE = ~0ull;
+    unsigned long long top = NONE;
+    int cx0, cx1, cy0, cy1;
+    if (!area_cells(c.gp, Q.u, Q.v, Q.radius, cx0, cx1, cy0, cy1)) return top;
+    uint32_t qd[8];
+    load_desc(qd, qdescRow);
+    const bool checkLevels = (Q.min_level > 0) || (Q.max_level >= 0);
+    bool haveTop = false;
+    int nbuf = 0;
+    auto flush = [&](int cnt) {
+        unsigned long long key = NONE;
+        if (lane < cnt) {
+            const unsigned long long part = buf[lane];
+            const int idx = (int)((part >> 8) & 0xffff);
+            const int dist = hamming256(qd, reinterpret_cast<const uint32_t*>(c.desc + (size_t)idx * 32));
+            key = ((unsigned long long)dist << 40) | part;
+        }
+        key = warp_sort32(key, lane);
+        top = haveTop ? warp_merge32(top, key, lane) : key;
+        haveTop = true;
+    };
+    for (int i0 = 0; i0 < c.n; i0 += 32) {
+        const int i = i0 + lane;
+        bool cand = false;
+        unsigned long long part = 0;
+        if (i < c.n) {
+            const float kx = c.kps[i].x, ky = c.kps[i].y;
+            if (fabsf(__fsub_rn(kx, Q.u)) < Q.radius && fabsf(__fsub_rn(ky, Q.v)) < Q.radius) {
+                const int oct = c.kps[i].octave;
+                const int px = (int)roundf(__fmul_rn(__fsub_rn(kx, c.gp.minX), c.gp.invW));
+                const int py = (int)roundf(__fmul_rn(__fsub_rn(ky, c.gp.minY), c.gp.invH));
+                cand = px >= cx0 && px <= cx1 && py >= cy0 && py <= cy1;       // the cell window lies inside the grid
+                if (checkLevels && (oct < Q.min_level || (Q.max_level >= 0 && oct > Q.max_level))) cand = false;
+                if (Q.level_lo >= 0 && (oct < Q.level_lo || oct > Q.level_hi)) cand = false;
+                if (cand && c.gate) {
+                    const float ur = c.uRight[i];
+                    if (ur > 0 && Q.max_right_err >= 0 && fabsf(__fsub_rn(Q.u_right, ur)) > Q.max_right_err) cand = false;
+                }
+                if (cand && !isFree(i)) cand = false;
+                part = ((unsigned long long)(px * ORBX_GRID_ROWS + py) << 24) | ((unsigned long long)i << 8) | (unsigned long long)(oct & 0xff);
+            }
+        }
+        const unsigned m = __ballot_sync(FULL, cand);
+        if (m) {
+            if (cand) buf[nbuf + __popc(m & ((1u << lane) - 1u))] = part;
+            nbuf += __popc(m);
+            __syncwarp();
+            if (nbuf >= 32) {
+                flush(32);
+                const unsigned long long carry = (32 + lane < nbuf) ? buf[32 + lane] : 0ull;
+                __syncwarp();
+                buf[lane] = carry;
+                nbuf -= 32;
+                __syncwarp();
+            }
+        }
+    }
+    if (nbuf > 0) flush(nbuf);
+    return top;
+}
+
+#define PROJ_LIST_WARPS 4
+__global__ void __launch_bounds__(PROJ_LIST_WARPS * 32)
+proj_list_kernel(ProjScan c, const orbm_proj_query* __restrict__ queries, const u8* __restrict__ qdesc, int nq,
+                 const u8* __restrict__ occupied, unsigned long long* __restrict__ keys)
+{
+    __shared__ unsigned long long bufS[PROJ_LIST_WARPS][PROJ_SCAN_BUF];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, q = blockIdx.x * PROJ_LIST_WARPS + w;
+    if (q >= nq) return;
+    const orbm_proj_query Q = queries[q];
+    const unsigned long long k = proj_scan_sorted(c, Q, qdesc + (size_t)q * 32, lane, bufS[w],
+                                                  [&](int i) { return occupied[i] == 0; });
+    keys[(size_t)PROJ_L * q + lane] = k;
+}
+
+// best / second best free key -> the reference's acceptance (src/ORBmatcher.cc:100-127, :1428-1433, :1561-1566, :384-389)
+__device__ __forceinline__ int proj_decide(unsigned long long k1, unsigned long long k2, int variant, int thDist, float nnratio, int& bDist)
+{
+    const unsigned long long NONE = ~0ull;
+    bDist = 256;
+    if (k1 == NONE) return -1;
+    const int bestDist = (int)(k1 >> 40), bestLevel = (int)(k1 & 0xff), bestIdx = (int)((k1 >> 8) & 0xffff);
+    const int bestDist2 = (k2 != NONE && (int)(k2 >> 40) < 256) ? (int)(k2 >> 40) : 256;      // initial values 256 / -1 (:73-77)
+    const int bestLevel2 = (k2 != NONE && (int)(k2 >> 40) < 256) ? (int)(k2 & 0xff) : -1;
+    bool ok = bestDist < 256 && bestDist <= thDist;
+    if (ok && variant == ORBM_PROJ_LOCALMAP && bestLevel == bestLevel2 && (float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) ok = false;
+    if (!ok) return -1;
+    bDist = bestDist;
+    return bestIdx;
+}
+
+__global__ void __launch_bounds__(PROJ_FIX_THREADS)
+proj_fixpoint_kernel(ProjScan c, const orbm_proj_query* __restrict__ queries, const u8* __restrict__ qdesc, int nq,
+                     const u8* __restrict__ queryBlocks, u8* __restrict__ occupied, int* __restrict__ assigned,
+                     int* __restrict__ bestIdxOut, int* __restrict__ bestDistOut, int variant, int thDist, float nnratio,
+                     int checkOri, int* __restrict__ nmatchesOut, const unsigned long long* __restrict__ keys,
+                     int* __restrict__ dirtyList, int* __restrict__ iterationsOut)
+{
+    extern __shared__ __align__(16) u8 fixS[];
+    __shared__ int hist[ORBX_HISTO_LENGTH];
+    __shared__ int sChanged, sDirty, sTakes, sMax[3];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, n = c.n;
+    int* ownerA = reinterpret_cast<int*>(fixS);
+    int* ownerB = ownerA + n;
+    unsigned long long* scanBuf = reinterpret_cast<unsigned long long*>(fixS + (((size_t)2 * n * sizeof(int) + 15) & ~(size_t)15));
+    const unsigned long long NONE = ~0ull;
+    const int INF = 0x7fffffff;
+    const bool rot = checkOri && (variant == ORBM_PROJ_LASTFRAME || variant == ORBM_PROJ_KEYFRAME);
+    const bool alwaysBlocks = variant == ORBM_PROJ_KEYFRAME || variant == ORBM_PROJ_SIM3;
+    const int needFree = variant == ORBM_PROJ_LOCALMAP ? 2 : 1;
+    for (int i = tid; i < n; i += PROJ_FIX_THREADS) { ownerA[i] = INF; assigned[i] = -1; }
+    for (int q = tid; q < nq; q += PROJ_FIX_THREADS) { bestIdxOut[q] = -2; bestDistOut[q] = 256; }   // -2: no decision yet
+    if (tid < ORBX_HISTO_LENGTH) hist[tid] = 0;
+    if (tid == 0) sTakes = 0;
+    __syncthreads();
+    int* prev = ownerA;
+    int* next = ownerB;
+    int iterations = 0;
+    for (;;) {
+        ++iterations;
+        for (int i = tid; i < n; i += PROJ_FIX_THREADS) next[i] = INF;
+        if (tid == 0) { sChanged = 0; sDirty = 0; }
+        __syncthreads();
+        // decisions under the takes of the previous iteration
+        for (int q = tid; q < nq; q += PROJ_FIX_THREADS) {
+            const unsigned long long* K = keys + (size_t)PROJ_L * q;
+            unsigned long long k1 = NONE, k2 = NONE;
+            int nfree = 0;
+            bool complete = false;
+            for (int j = 0; j < PROJ_L; ++j) {
+                const unsigned long long k = K[j];
+                if (k == NONE) { complete = true; break; }
+                if (prev[(int)((k >> 8) & 0xffff)] >= q) {
+                    if (nfree == 0) k1 = k; else k2 = k;
+                    if (++nfree == needFree) break;
+                }
+            }
+            if (!complete && nfree < needFree) dirtyList[atomicAdd(&sDirty, 1)] = q;
+            else {
+                int dist;
+                const int take = proj_decide(k1, k2, variant, thDist, nnratio, dist);
+                if (take != bestIdxOut[q]) sChanged = 1;
+                bestIdxOut[q] = take; bestDistOut[q] = dist;
+            }
+        }
+        __syncthreads();
+        // truncated lists without enough free keys: the sweep again, under the occupancy the query sees now
+        const int nd = sDirty;
+        for (int d = wid; d < nd; d += PROJ_FIX_THREADS / 32) {
+            const int q = dirtyList[d];
+            const orbm_proj_query Q = queries[q];
+            const unsigned long long k = proj_scan_sorted(c, Q, qdesc + (size_t)q * 32, lane, scanBuf + wid * PROJ_SCAN_BUF,
+                                                          [&](int i) { return occupied[i] == 0 && prev[i] >= q; });
+            const unsigned long long k1 = __shfl_sync(FULL, k, 0), k2 = __shfl_sync(FULL, k, 1);
+            if (lane == 0) {
+                int dist;
+                const int take = proj_decide(k1, k2, variant, thDist, nnratio, dist);
+                if (take != bestIdxOut[q]) sChanged = 1;
+                bestIdxOut[q] = take; bestDistOut[q] = dist;
+            }
+        }
+        __syncthreads();
+        if (!sChanged) break;                      // every take repeats: prev already holds exactly these takes
+        for (int q = tid; q < nq; q += PROJ_FIX_THREADS) {
+            const int take = bestIdxOut[q];
+            const bool blocks = alwaysBlocks ? true : (queryBlocks ? queryBlocks[q] != 0 : true);
+            if (take >= 0 && blocks) atomicMin(&next[take], q);
+        }
+        __syncthreads();
+        int* t = prev; prev = next; next = t;
+    }
+    // results: the query that writes a keypoint last owns it; blocked keypoints become occupied
+    int mine = 0;
+    for (int q = tid; q < nq; q += PROJ_FIX_THREADS) {
+        const int take = bestIdxOut[q];
+        if (take >= 0) {
+            ++mine;
+            atomicMax(&assigned[take], q);
+            if (rot) atomicAdd(&hist[rot_bin(queries[q].angle, c.kps[take].angle)], 1);
+        }
+    }
+    for (int i = tid; i < n; i += PROJ_FIX_THREADS) if (prev[i] != INF) occupied[i] = 1;
+    if (mine) atomicAdd(&sTakes, mine);
+    __syncthreads();
+    if (rot) {
+        if (tid == 0) three_maxima(hist, ORBX_HISTO_LENGTH, sMax[0], sMax[1], sMax[2]);
+        __syncthreads();
+        int culled = 0;
+        for (int q = tid; q < nq; q += PROJ_FIX_THREADS) {
+            const int take = bestIdxOut[q];
+            if (take >= 0) {
+                const int b = rot_bin(queries[q].angle, c.kps[take].angle);
+                if (b != sMax[0] && b != sMax[1] && b != sMax[2]) { assigned[take] = -1; ++culled; }
+            }
+        }
+        if (culled) atomicSub(&sTakes, culled);
+        __syncthreads();
+    }
+    if (tid == 0) { *nmatchesOut = sTakes; if (iterationsOut) *iterationsOut = iterations; }
+}
+
+// =============================================================================================
 // K8: Frame::ComputeStereoMatches (src/Frame.cc:466-638).  One CTA per stereo pair.
 //  phase 1  every right keypoint -> (minr, maxr, octave, x): the rows it is filed under (:480-491)
 //  phase 2  warp per left keypoint: lanes scan the right keypoints (ascending index = the order
@@ -1181,6 +1440,25 @@ int orbm_descriptor_distance(const uint8_t* a, const uint8_t* b, int count, int3
     return ORBX_OK;
 }
 
+// ORBX_LAT_TRACE=1: device-side phase times of the stateless calls (events on the legacy stream), averaged over 50 calls, to stderr
+struct PhaseTrace {
+    static const int MAXP = 8;
+    bool on; int np; cudaEvent_t ev[MAXP]; const char* tag[MAXP];
+    explicit PhaseTrace(bool enable) : on(enable), np(0) {}
+    void mark(const char* t) { if (!on || np >= MAXP) return; cudaEventCreate(&ev[np]); cudaEventRecord(ev[np], 0); tag[np++] = t; }
+    void report(const char* name, double* acc, int& calls) {
+        if (!on) return;
+        for (int i = 1; i < np; ++i) { float ms = 0; cudaEventElapsedTime(&ms, ev[i - 1], ev[i]); acc[i] += ms * 1000.0; }
+        for (int i = 0; i < np; ++i) cudaEventDestroy(ev[i]);
+        if (++calls % 50 == 0) {
+            fprintf(stderr, "[orbx lat] %s:", name);
+            for (int i = 1; i < np; ++i) { fprintf(stderr, " %s %.1f us", tag[i], acc[i] / 50.0); acc[i] = 0; }
+            fprintf(stderr, "\n");
+        }
+    }
+};
+static bool lat_trace_on() { static const bool on = getenv("ORBX_LAT_TRACE") != nullptr; return on; }
+
 int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, float* prev_matched,
                                    int32_t* matches12, int window_size, float nnratio,
                                    int check_orientation, int32_t* nmatches)
@@ -1216,19 +1494,26 @@ int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, f
         memcpy(host + oKps + cap * sizeof(orbx_keypoint), f2->keys_un, (size_t)f2->n * sizeof(orbx_keypoint));
         memcpy(host + oDesc + cap * 32, f2->descriptors, (size_t)f2->n * 32);
     }
+    PhaseTrace pt(lat_trace_on());
+    pt.mark("start");
     ORBX_CUDA(cudaMemcpyAsync(dev, host, upBytes, cudaMemcpyHostToDevice, 0));
+    pt.mark("h2d");
     FrameStore fs;
     fs.kps = reinterpret_cast<orbx_keypoint*>(dev + oKps); fs.desc = dev + oDesc; fs.count = reinterpret_cast<int*>(dev + oCount);
     fs.gridStart = reinterpret_cast<unsigned short*>(dev + oGS); fs.gridIdx = reinterpret_cast<unsigned short*>(dev + oGI);
     fs.cap = (int)cap;
     const GridParams gp = orbx_grid_params(f2->min_x, f2->max_x, f2->min_y, f2->max_y);
     rc = orbx_launch_grid_build(fs, 1, 1, gp, 0); if (rc) return rc;
+    pt.mark("grid");
     rc = launch_search_init(fs, 0, 1, 1, gp, reinterpret_cast<float*>(dev + oPrev), window_size, nnratio, check_orientation,
                             reinterpret_cast<int*>(dev + oM12), reinterpret_cast<int*>(dev + oNm), nullptr, 0);
     if (rc) return rc;
+    pt.mark("search");
     ORBX_CUDA(cudaGetLastError());
     ORBX_CUDA(cudaMemcpyAsync(host + oPrev, dev + oPrev, downBytes, cudaMemcpyDeviceToHost, 0));
+    pt.mark("d2h");
     ORBX_CUDA(cudaStreamSynchronize(0));
+    { static double acc[PhaseTrace::MAXP]; static int calls = 0; pt.report("search_for_initialization", acc, calls); }
     int nm = 0;
     memcpy(&nm, host + oNm, 4);
     if (f1->n) {
@@ -1263,8 +1548,10 @@ int orbm_search_by_projection(int variant, const orbm_frame* frame, const orbm_p
     const size_t upBytes = off;
     const size_t oNm = take(4), oAsg = take(n * 4), oBI = take(Q * 4), oBD = take(Q * 4);
     const size_t downBytes = off - oOcc;
+    // per-frame tracking sizes take the latency form (K9a/K9b: no grid, 32-key lists, fixed-point replay)
+    const bool sweep = frame->n <= PROJ_SCAN_MAXN;
     const size_t oGS = take((ORBX_GRID_CELLS + 1) * sizeof(unsigned short)), oGI = take(n * sizeof(unsigned short)),
-                 oKeys = take(Q * PROJ_K * 8), oKA = take(Q * PROJ_K * 4), oBin = take(Q);
+                 oKeys = take(Q * (sweep ? PROJ_L : PROJ_K) * 8), oKA = take(Q * PROJ_K * 4), oBin = take(Q * (sweep ? 4 : 1));
     DevBuf arena;
     if ((rc = arena.alloc(off))) return rc;
     u8* host = nullptr;
@@ -1283,29 +1570,54 @@ int orbm_search_by_projection(int variant, const orbm_frame* frame, const orbm_p
         memcpy(host + oQD, query_desc, (size_t)nq * 32);
         if (query_blocks) memcpy(host + oQB, query_blocks, (size_t)nq);
     }
+    PhaseTrace pt(lat_trace_on());
+    pt.mark("start");
     ORBX_CUDA(cudaMemcpyAsync(dev, host, upBytes, cudaMemcpyHostToDevice, 0));
+    pt.mark("h2d");
     FrameStore fs;
     fs.kps = reinterpret_cast<orbx_keypoint*>(dev + oKps); fs.desc = dev + oDesc; fs.count = reinterpret_cast<int*>(dev + oCount);
     fs.gridStart = reinterpret_cast<unsigned short*>(dev + oGS); fs.gridIdx = reinterpret_cast<unsigned short*>(dev + oGI);
     fs.cap = (int)n;
     const GridParams gp = orbx_grid_params(frame->min_x, frame->max_x, frame->min_y, frame->max_y);
-    rc = orbx_launch_grid_build(fs, 0, 1, gp, 0); if (rc) return rc;
     const float* dUR = frame->u_right ? reinterpret_cast<const float*>(dev + oUR) : nullptr;
     const orbm_proj_query* dQ = reinterpret_cast<const orbm_proj_query*>(dev + oQ);
     unsigned long long* dKeys = reinterpret_cast<unsigned long long*>(dev + oKeys);
     float* dKA = reinterpret_cast<float*>(dev + oKA);
-    if (nq > 0)
-        search_proj_cand_kernel<<<(nq + PROJ_WARPS - 1) / PROJ_WARPS, PROJ_WARPS * 32>>>(
-            fs, 0, gp, dUR, dQ, dev + oQD, nq, dev + oOcc, variant, dKeys, dKA);
-    const int occSmem = (std::max(frame->n, 1) + 15) & ~15;          // n <= 65000 (check_frame)
-    if (occSmem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(search_proj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, occSmem));
-    search_proj_kernel<<<1, 32, occSmem>>>(fs, 0, gp, dUR, dQ, dev + oQD, nq, query_blocks ? dev + oQB : nullptr, dev + oOcc,
-                                           reinterpret_cast<int*>(dev + oAsg), reinterpret_cast<int*>(dev + oBI),
-                                           reinterpret_cast<int*>(dev + oBD), dev + oBin, variant, th_dist, nnratio,
-                                           check_orientation, reinterpret_cast<int*>(dev + oNm), dKeys, dKA);
+    if (sweep) {
+        ProjScan ps;
+        ps.kps = fs.kps; ps.desc = fs.desc; ps.uRight = dUR; ps.gp = gp; ps.n = frame->n;
+        ps.gate = (variant == ORBM_PROJ_LOCALMAP || variant == ORBM_PROJ_LASTFRAME) && dUR != nullptr;
+        if (nq > 0)
+            proj_list_kernel<<<(nq + PROJ_LIST_WARPS - 1) / PROJ_LIST_WARPS, PROJ_LIST_WARPS * 32>>>(ps, dQ, dev + oQD, nq, dev + oOcc, dKeys);
+        pt.mark("lists");
+        const int fixSmem = (int)((((size_t)2 * frame->n * sizeof(int) + 15) & ~(size_t)15) + (PROJ_FIX_THREADS / 32) * PROJ_SCAN_BUF * 8);
+        static bool attrSet = false;
+        if (!attrSet) { ORBX_CUDA(cudaFuncSetAttribute(proj_fixpoint_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * PROJ_SCAN_MAXN * 4 + 16 + (PROJ_FIX_THREADS / 32) * PROJ_SCAN_BUF * 8)); attrSet = true; }
+        proj_fixpoint_kernel<<<1, PROJ_FIX_THREADS, fixSmem>>>(ps, dQ, dev + oQD, nq, query_blocks ? dev + oQB : nullptr, dev + oOcc,
+                                                               reinterpret_cast<int*>(dev + oAsg), reinterpret_cast<int*>(dev + oBI),
+                                                               reinterpret_cast<int*>(dev + oBD), variant, th_dist, nnratio, check_orientation,
+                                                               reinterpret_cast<int*>(dev + oNm), dKeys, reinterpret_cast<int*>(dev + oBin), nullptr);
+        pt.mark("fixpoint");
+    } else {
+        rc = orbx_launch_grid_build(fs, 0, 1, gp, 0); if (rc) return rc;
+        pt.mark("grid");
+        if (nq > 0)
+            search_proj_cand_kernel<<<(nq + PROJ_WARPS - 1) / PROJ_WARPS, PROJ_WARPS * 32>>>(
+                fs, 0, gp, dUR, dQ, dev + oQD, nq, dev + oOcc, variant, dKeys, dKA);
+        pt.mark("cand");
+        const int occSmem = (std::max(frame->n, 1) + 15) & ~15;          // n <= 65000 (check_frame)
+        if (occSmem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(search_proj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, occSmem));
+        search_proj_kernel<<<1, 32, occSmem>>>(fs, 0, gp, dUR, dQ, dev + oQD, nq, query_blocks ? dev + oQB : nullptr, dev + oOcc,
+                                               reinterpret_cast<int*>(dev + oAsg), reinterpret_cast<int*>(dev + oBI),
+                                               reinterpret_cast<int*>(dev + oBD), dev + oBin, variant, th_dist, nnratio,
+                                               check_orientation, reinterpret_cast<int*>(dev + oNm), dKeys, dKA);
+        pt.mark("replay");
+    }
     ORBX_CUDA(cudaGetLastError());
     ORBX_CUDA(cudaMemcpyAsync(host + oOcc, dev + oOcc, downBytes, cudaMemcpyDeviceToHost, 0));
+    pt.mark("d2h");
     ORBX_CUDA(cudaStreamSynchronize(0));
+    { static double acc[PhaseTrace::MAXP]; static int calls = 0; pt.report("search_by_projection", acc, calls); }
     int nm = 0;
     memcpy(&nm, host + oNm, 4);
     if (frame->n > 0) {

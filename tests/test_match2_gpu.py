@@ -68,6 +68,49 @@ def test_search_by_projection(variant, th, ratio, ori):
         assert n_o > 50
 
 
+def _random_frame(n, seed, w=640, h=480):
+    """n keypoints at random places with random descriptors (nothing extracted: sizes the extractor never returns)"""
+    r = np.random.default_rng(seed)
+    k = np.zeros(n, capi.KP_DTYPE)
+    k["x"] = r.uniform(0, w, n).astype(np.float32); k["y"] = r.uniform(0, h, n).astype(np.float32)
+    k["octave"] = r.integers(0, 8, n); k["angle"] = r.uniform(0, 360, n).astype(np.float32); k["size"] = 31
+    d = r.integers(0, 256, (n, 32), dtype=np.uint8)
+    return k, d
+
+
+def _queries_around(k, d, nq, seed, radius):
+    r = np.random.default_rng(seed + 100)
+    n = len(k)
+    src = r.integers(0, n, nq)
+    q = np.zeros(nq, capi.PROJ_DTYPE)
+    q["u"] = k["x"][src] + r.normal(0, 2, nq).astype(np.float32)
+    q["v"] = k["y"][src] + r.normal(0, 2, nq).astype(np.float32)
+    q["radius"] = radius
+    q["min_level"] = -1; q["max_level"] = -1; q["u_right"] = -1; q["max_right_err"] = -1
+    q["angle"] = (k["angle"][src] + r.normal(0, 8, nq)) % 360
+    q["level_lo"] = -1; q["level_hi"] = -1
+    qd = d[src].copy()
+    qd[:, 0] ^= r.integers(0, 256, nq, dtype=np.uint8)
+    return q, qd, (r.random(n) < 0.1).astype(np.uint8), (r.random(nq) < 0.8).astype(np.uint8)
+
+
+@pytest.mark.parametrize("n,nq,radius,variant,ratio,ori", [
+    (1500, 6000, 70.0, capi.PROJ_LOCALMAP, 0.8, False),     # windows of > 32 keypoints that fill up: truncated lists are searched again
+    (1500, 6000, 70.0, capi.PROJ_LASTFRAME, 0.9, True),
+    (900, 3000, 1000.0, capi.PROJ_KEYFRAME, 0.9, True),     # every query sees the whole frame: long chains of conflicts
+    (5000, 3000, 25.0, capi.PROJ_LOCALMAP, 0.8, False),     # more keypoints than the latency form takes: grid + warp replay
+    (5000, 3000, 25.0, capi.PROJ_LASTFRAME, 0.9, True)])
+def test_search_by_projection_contended(n, nq, radius, variant, ratio, ori):
+    k, d = _random_frame(n, n + nq)
+    q, qd, occ, blk = _queries_around(k, d, nq, n, radius)
+    fo, fg = O.FrameData(k, d, 640, 480), capi.FrameData(k, d, 640, 480)
+    n_o, a_o, bi_o, bd_o, occ_o = O.search_by_projection(variant, fo, q, qd, blk, occ, 100, ratio, ori)
+    n_g, a_g, bi_g, bd_g, occ_g = capi.search_by_projection(variant, fg, q, qd, blk, occ, 100, ratio, ori)
+    assert n_g == n_o and np.array_equal(bi_g, bi_o) and np.array_equal(bd_g, bd_o)
+    assert np.array_equal(a_g, a_o) and np.array_equal(occ_g, occ_o)
+    assert n_o > 100
+
+
 def test_search_by_projection_empty():
     k = np.zeros(0, capi.KP_DTYPE)
     f = capi.FrameData(k, np.zeros((0, 32), np.uint8), 640, 480)
