@@ -778,6 +778,115 @@ def run_rgbd_single(args):
     ex.close()
 
 
+def run_matcher_calls(args):
+    """The stateless per-frame / per-keyframe matcher calls of include/orbx.h as Tracking, LocalMapping and LoopClosing make
+    them: host structs in, host results out, ONE frame or keyframe pair per call.  Each call's median latency next to the
+    CPU oracle's on the same inputs (single thread, as ORB-SLAM2 runs them).  Inputs: the case builders of tests/."""
+    import torch
+    from orb_slam2_map_b200 import capi, synth
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    O = oracle_mod()          # input containers of the case builders + the CPU leg; the frames below come from the GPU extractor
+    import test_match2_gpu as T
+    from test_oracle_kfmatch import make_fuse_case, make_sim3_case, make_tri_pair
+    from test_oracle_bow import make_pair
+    from test_kfmatch_gpu import _to_capi
+
+    def med(fn, n, warm=5):
+        for _ in range(warm):
+            fn()
+        ts = np.empty(n)
+        for i in range(n):
+            t0 = time.perf_counter(); fn(); ts[i] = time.perf_counter() - t0
+        return float(np.median(ts)) * 1e6
+
+    calls = max(args.steps, 1) * 40
+    cpu_calls = 12
+    rows = {}
+
+    def add(name, gpu_fn, cpu_fn, **info):
+        g = med(gpu_fn, calls)
+        row = {"gpu_us": round(g, 1), **info}
+        if not args.no_cpu:
+            c = med(cpu_fn, cpu_calls, warm=2)
+            row.update(cpu_oracle_us=round(c, 1), speedup=round(c / g, 2))
+        rows[name] = row
+
+    ex = capi.Extractor(**PARAMS, max_width=640, max_height=480, chunk_frames=1, result_slots=1, device=local)
+    sf = ex.tables()["scale"]
+    k, d = ex.extract(synth.textured_canvas(640, 480, seed=1))
+    k, d, q, qd, ur, occ, blk, sf = T._queries_from_keypoints(k, d, sf, 1)
+    fo = O.FrameData(k, d, 640, 480, u_right=ur, scale_factors=sf)
+    fg = capi.FrameData(k, d, 640, 480, u_right=ur, scale_factors=sf)
+    for name, variant, th, ratio, ori in (("search_by_projection_localmap", capi.PROJ_LOCALMAP, 100, 0.8, False),
+                                          ("search_by_projection_lastframe", capi.PROJ_LASTFRAME, 100, 0.9, True),
+                                          ("search_by_projection_keyframe", capi.PROJ_KEYFRAME, 64, 0.9, True),
+                                          ("search_by_projection_sim3", capi.PROJ_SIM3, 50, 0.75, False)):
+        qq = q
+        if variant in (capi.PROJ_KEYFRAME, capi.PROJ_SIM3):
+            qq = q.copy(); qq["min_level"] = -1; qq["max_level"] = -1
+            qq["level_lo"] = np.maximum(k["octave"][:len(q)] - 1, 0); qq["level_hi"] = qq["level_lo"] + 1
+        add(name, lambda: capi.search_by_projection(variant, fg, qq, qd, blk, occ, th, ratio, ori),
+            lambda: O.search_by_projection(variant, fo, qq, qd, blk, occ, th, ratio, ori), queries=len(q), keypoints=len(k))
+    frames = synth.frame_sequence(2, 640, 480, seed=3)
+    ka, da = ex.extract(frames[0]); kb, db = ex.extract(frames[1])
+    prev = np.stack([ka["x"], ka["y"]], axis=1)
+    f1o, f2o = O.FrameData(ka, da, 640, 480), O.FrameData(kb, db, 640, 480)
+    f1g, f2g = capi.FrameData(ka, da, 640, 480), capi.FrameData(kb, db, 640, 480)
+    add("search_for_initialization", lambda: capi.search_for_initialization(f1g, f2g, prev, 100, 0.9, True),
+        lambda: O.search_for_initialization(f1o, f2o, prev, 100, 0.9, True), keypoints=[len(ka), len(kb)])
+    left, right = synth.stereo_pair(1241, 376, seed=5)
+    sp_params = dict(PARAMS, nfeatures=2000)
+    exs = capi.Extractor(**sp_params, max_width=1241, max_height=376, chunk_frames=1, result_slots=1, device=local)
+    kl, dl = exs.extract(left); pl = [exs.level(0, l) for l in range(8)]
+    kr, dr = exs.extract(right); pr = [exs.level(0, l) for l in range(8)]
+    tb = exs.tables()
+    st = (kl, dl, kr, dr, pl, pr, tb["scale"], tb["inv_scale"], 386.1448, 718.856)
+    add("compute_stereo_matches_kitti", lambda: capi.compute_stereo_matches(*st), lambda: O.compute_stereo_matches(*st),
+        keypoints=[len(kl), len(kr)])
+    exs.close()
+    voc = O.make_vocabulary(k=10, depth=4, seed=3)
+    A, B = make_pair(voc, n=1000, seed=1, levelsup=2)
+    for v in (0, 1):
+        add(f"search_by_bow_{'frame' if v == 0 else 'keyframes'}", lambda: capi.search_by_bow(v, [(A, B)], nnratio=0.7, check_ori=True),
+            lambda: O.search_by_bow(v, *A, *B, nnratio=0.7, check_ori=True), features=1000)
+    kf, fq, fqd = make_fuse_case(25, n=2000, nq=3000)
+    kfg = _to_capi(kf)
+    add("fuse", lambda: capi.fuse(0, kfg, fq, fqd), lambda: O.fuse(0, kf, fq, fqd), keypoints=2000, queries=3000)
+    s3 = make_sim3_case(21)
+    s3g = (_to_capi(s3[0]), _to_capi(s3[1])) + tuple(s3[2:])
+    add("search_by_sim3", lambda: capi.search_by_sim3(*s3g), lambda: O.search_by_sim3(*s3), queries=[len(s3[2]), len(s3[5])])
+    ta, tb, F12, epi = make_tri_pair(4, n1=2000, n2=1900, mono_frac=0.0)
+    tg = [(_to_capi(ta), _to_capi(tb))]
+    add("search_for_triangulation", lambda: capi.search_for_triangulation(tg, [F12], [epi], False, True),
+        lambda: O.search_for_triangulation(ta, tb, F12, epi, False, True), keypoints=[2000, 1900])
+    rng = np.random.default_rng(8)
+    sizes = rng.integers(2, 40, 300)
+    offs = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int32)
+    dd = rng.integers(0, 256, (int(offs[-1]), 32), dtype=np.uint8)
+    add("distinctive_descriptors_300_points", lambda: capi.distinctive_descriptors(dd, offs), lambda: O.distinctive_descriptors(dd, offs),
+        observations=int(offs[-1]))
+    ex.close()
+    sp = [r["speedup"] for r in rows.values() if "speedup" in r]
+    head = rows["search_by_projection_localmap"]
+    line = {"metric": "stateless matcher call latency (SearchByProjection local map, 900 map points x 1008 keypoints)", "value": head["gpu_us"],
+            "unit": "us/call", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": head["gpu_us"] / 1e3,
+            "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": "stateless orbm_* calls, one frame / keyframe pair per call, host structs in and out (includes the ctypes "
+                                   "marshalling of orb_slam2_map_b200/capi.py on the GPU side and of tests/oracle_lib.py on the CPU side)",
+                       "calls_per_entry": calls, "l2_policy": "latency line: one frame fits L2 by definition"},
+            "calls": rows, "min_speedup_vs_cpu_oracle": min(sp) if sp else None,
+            "e2e": {"value": head["gpu_us"], "unit": "us/call", "h2d_bytes_per_step": int(k.nbytes + d.nbytes + q.nbytes + qd.nbytes + len(k) * 5 + len(q)),
+                    "d2h_bytes_per_step": int(len(k) * 5 + len(q) * 8 + 4)},
+            "gpu_launches": calls * 2}
+    if not args.no_cpu:
+        line["cpu_baseline"] = {"value": head.get("cpu_oracle_us"), "unit": "us/call", "cores": 1, "kind": "port",
+                                "sample": f"{cpu_calls} calls per entry, oracle/ through tests/oracle_lib.py"}
+    emit(line)
+
+
 def run_single(args):
     """BASELINE configs[0] / SURVEY 8(d) "Config 1": ONE 640x480 frame per call, the way Tracking uses the extractor
     (Frame::ExtractORB, src/Frame.cc:247-253): pageable host image in, host keypoints + descriptors out, through
@@ -880,7 +989,7 @@ def main():
     ap.add_argument("--chunk", type=int, default=512)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-hamming", action="store_true", help="skip the config-5 leg of the default line (profiling runs)")
-    ap.add_argument("--workload", default="frames", choices=["frames", "hd", "stereo", "knn", "rgbd", "single", "rgbd_single"],
+    ap.add_argument("--workload", default="frames", choices=["frames", "hd", "stereo", "knn", "rgbd", "single", "rgbd_single", "matcher_calls"],
                     help="frames = BASELINE configs[1] (the graded line); hd = configs[3]; stereo = configs[2]; knn = configs[4]")
     ap.add_argument("--queries", type=int, default=262144, help="knn: queries per step (config 5 names 1M)")
     ap.add_argument("--db-per-gpu", type=int, default=2000000, help="knn: database rows per GPU (config 5: 16M over 8)")
@@ -916,6 +1025,9 @@ def main():
         return
     if args.workload == "rgbd_single":
         run_rgbd_single(args)
+        return
+    if args.workload == "matcher_calls":
+        run_matcher_calls(args)
         return
 
     import torch

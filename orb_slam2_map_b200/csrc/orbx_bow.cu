@@ -265,19 +265,13 @@ int orbm_bow_transform(orbm_vocab_handle* v, const uint8_t* features, int n, int
     if (!v || !features || !word_id || !weight || !node_id) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
     if (n <= 0) return ORBX_OK;
     ORBX_CUDA(cudaSetDevice(v->device));
-    BBuf df, dw, dwt, dn;
-    int rc = df.alloc((size_t)n * 32); if (rc) return rc;
-    rc = dw.alloc((size_t)n * 4); if (rc) return rc;
-    rc = dwt.alloc((size_t)n * 8); if (rc) return rc;
-    rc = dn.alloc((size_t)n * 4); if (rc) return rc;
-    ORBX_CUDA(cudaMemcpy(df.p, features, (size_t)n * 32, cudaMemcpyHostToDevice));
+    CallArena ar;
+    const int sF = ar.in(features, (size_t)n * 32);
+    const int sWt = ar.out(weight, (size_t)n * 8), sW = ar.out(word_id, (size_t)n * 4), sN = ar.out(node_id, (size_t)n * 4);
+    int rc = ar.commit(); if (rc) return rc;
     bow_transform_kernel<<<(n + 7) / 8, 256>>>(v->childBegin, v->childCount, v->children, v->desc, v->word, v->weight, v->depth,
-                                               df.as<u8>(), n, levelsup, dw.as<uint32_t>(), dwt.as<double>(), dn.as<uint32_t>());
-    ORBX_CUDA(cudaGetLastError());
-    ORBX_CUDA(cudaMemcpy(word_id, dw.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
-    ORBX_CUDA(cudaMemcpy(weight, dwt.p, (size_t)n * 8, cudaMemcpyDeviceToHost));
-    ORBX_CUDA(cudaMemcpy(node_id, dn.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
-    return ORBX_OK;
+                                               ar.dev<u8>(sF), n, levelsup, ar.dev<uint32_t>(sW), ar.dev<double>(sWt), ar.dev<uint32_t>(sN));
+    return ar.finish();
 }
 
 int orbm_search_by_bow(int variant, const orbm_bow_frame* a, const orbm_bow_frame* b, int npairs, float nnratio,
@@ -304,41 +298,38 @@ int orbm_search_by_bow(int variant, const orbm_bow_frame* a, const orbm_bow_fram
     int capB = 1; while (capB < maxB) capB <<= 1;
     const size_t smem = (size_t)(capA + capB) * 8 + (size_t)capA * 2 + capB + capA + 16;
     if (smem > 220 * 1024) { orbx_set_error("frames of %d / %d features exceed the shared-memory sort (%zu bytes)", maxA, maxB, smem); return ORBX_E_CAPACITY; }
-    BBuf dPairs, dDescA, dAngA, dNodeA, dFlagA, dDescB, dAngB, dNodeB, dFlagB, dMA, dMB, dNM;
-    int rc;
-#define BOW_ALLOC(buf, bytes) rc = buf.alloc(bytes); if (rc) return rc
-    BOW_ALLOC(dPairs, npairs * sizeof(BowPair));
-    BOW_ALLOC(dDescA, (size_t)totA * 32); BOW_ALLOC(dAngA, (size_t)totA * 4); BOW_ALLOC(dNodeA, (size_t)totA * 4); BOW_ALLOC(dFlagA, (size_t)totA);
-    BOW_ALLOC(dDescB, (size_t)totB * 32); BOW_ALLOC(dAngB, (size_t)totB * 4); BOW_ALLOC(dNodeB, (size_t)totB * 4); BOW_ALLOC(dFlagB, (size_t)totB);
-    BOW_ALLOC(dMA, (size_t)totA * 4); BOW_ALLOC(dMB, (size_t)totB * 4); BOW_ALLOC(dNM, (size_t)npairs * 4);
-#undef BOW_ALLOC
-    ORBX_CUDA(cudaMemcpy(dPairs.p, pairs.data(), npairs * sizeof(BowPair), cudaMemcpyHostToDevice));
+    for (int p = 0; p < npairs; ++p) {
+        if (pairs[p].nA && (!a[p].descriptors || !a[p].angles || !a[p].node_id || !a[p].flags)) { orbx_set_error("pair %d: null array in a", p); return ORBX_E_INVALID; }
+        if (pairs[p].nB && (!b[p].descriptors || !b[p].angles || !b[p].node_id || !b[p].flags)) { orbx_set_error("pair %d: null array in b", p); return ORBX_E_INVALID; }
+    }
+    // one staged upload, one download (CallArena): the pairs' arrays are concatenated in the staging buffer
+    CallArena ar;
+    const int sPairs = ar.in(pairs.data(), npairs * sizeof(BowPair));
+    const int sDescA = ar.in(nullptr, (size_t)totA * 32), sAngA = ar.in(nullptr, (size_t)totA * 4), sNodeA = ar.in(nullptr, (size_t)totA * 4), sFlagA = ar.in(nullptr, (size_t)totA);
+    const int sDescB = ar.in(nullptr, (size_t)totB * 32), sAngB = ar.in(nullptr, (size_t)totB * 4), sNodeB = ar.in(nullptr, (size_t)totB * 4), sFlagB = ar.in(nullptr, (size_t)totB);
+    const int sMA = ar.out(match_a, (size_t)totA * 4), sMB = ar.out(match_b, (size_t)totB * 4), sNM = ar.out(nmatches, (size_t)npairs * 4);
+    int rc = ar.layout(); if (rc) return rc;
     for (int p = 0; p < npairs; ++p) {
         const BowPair& P = pairs[p];
         if (P.nA) {
-            if (!a[p].descriptors || !a[p].angles || !a[p].node_id || !a[p].flags) { orbx_set_error("pair %d: null array in a", p); return ORBX_E_INVALID; }
-            ORBX_CUDA(cudaMemcpy(dDescA.as<u8>() + (size_t)P.offA * 32, a[p].descriptors, (size_t)P.nA * 32, cudaMemcpyHostToDevice));
-            ORBX_CUDA(cudaMemcpy(dAngA.as<float>() + P.offA, a[p].angles, (size_t)P.nA * 4, cudaMemcpyHostToDevice));
-            ORBX_CUDA(cudaMemcpy(dNodeA.as<uint32_t>() + P.offA, a[p].node_id, (size_t)P.nA * 4, cudaMemcpyHostToDevice));
-            ORBX_CUDA(cudaMemcpy(dFlagA.as<u8>() + P.offA, a[p].flags, (size_t)P.nA, cudaMemcpyHostToDevice));
+            memcpy(ar.hostp<u8>(sDescA) + (size_t)P.offA * 32, a[p].descriptors, (size_t)P.nA * 32);
+            memcpy(ar.hostp<float>(sAngA) + P.offA, a[p].angles, (size_t)P.nA * 4);
+            memcpy(ar.hostp<uint32_t>(sNodeA) + P.offA, a[p].node_id, (size_t)P.nA * 4);
+            memcpy(ar.hostp<u8>(sFlagA) + P.offA, a[p].flags, (size_t)P.nA);
         }
         if (P.nB) {
-            if (!b[p].descriptors || !b[p].angles || !b[p].node_id || !b[p].flags) { orbx_set_error("pair %d: null array in b", p); return ORBX_E_INVALID; }
-            ORBX_CUDA(cudaMemcpy(dDescB.as<u8>() + (size_t)P.offB * 32, b[p].descriptors, (size_t)P.nB * 32, cudaMemcpyHostToDevice));
-            ORBX_CUDA(cudaMemcpy(dAngB.as<float>() + P.offB, b[p].angles, (size_t)P.nB * 4, cudaMemcpyHostToDevice));
-            ORBX_CUDA(cudaMemcpy(dNodeB.as<uint32_t>() + P.offB, b[p].node_id, (size_t)P.nB * 4, cudaMemcpyHostToDevice));
-            ORBX_CUDA(cudaMemcpy(dFlagB.as<u8>() + P.offB, b[p].flags, (size_t)P.nB, cudaMemcpyHostToDevice));
+            memcpy(ar.hostp<u8>(sDescB) + (size_t)P.offB * 32, b[p].descriptors, (size_t)P.nB * 32);
+            memcpy(ar.hostp<float>(sAngB) + P.offB, b[p].angles, (size_t)P.nB * 4);
+            memcpy(ar.hostp<uint32_t>(sNodeB) + P.offB, b[p].node_id, (size_t)P.nB * 4);
+            memcpy(ar.hostp<u8>(sFlagB) + P.offB, b[p].flags, (size_t)P.nB);
         }
     }
+    rc = ar.upload(); if (rc) return rc;
     if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(search_bow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    search_bow_kernel<<<npairs, BOW_THREADS, smem>>>(variant, dPairs.as<BowPair>(), dDescA.as<u8>(), dAngA.as<float>(), dNodeA.as<uint32_t>(),
-                                                     dFlagA.as<u8>(), dDescB.as<u8>(), dAngB.as<float>(), dNodeB.as<uint32_t>(), dFlagB.as<u8>(),
-                                                     nnratio, check_orientation, capA, capB, dMA.as<int32_t>(), dMB.as<int32_t>(), dNM.as<int32_t>());
-    ORBX_CUDA(cudaGetLastError());
-    if (totA) ORBX_CUDA(cudaMemcpy(match_a, dMA.p, (size_t)totA * 4, cudaMemcpyDeviceToHost));
-    if (totB) ORBX_CUDA(cudaMemcpy(match_b, dMB.p, (size_t)totB * 4, cudaMemcpyDeviceToHost));
-    ORBX_CUDA(cudaMemcpy(nmatches, dNM.p, (size_t)npairs * 4, cudaMemcpyDeviceToHost));
-    return ORBX_OK;
+    search_bow_kernel<<<npairs, BOW_THREADS, smem>>>(variant, ar.dev<BowPair>(sPairs), ar.dev<u8>(sDescA), ar.dev<float>(sAngA), ar.dev<uint32_t>(sNodeA),
+                                                     ar.dev<u8>(sFlagA), ar.dev<u8>(sDescB), ar.dev<float>(sAngB), ar.dev<uint32_t>(sNodeB), ar.dev<u8>(sFlagB),
+                                                     nnratio, check_orientation, capA, capB, ar.dev<int32_t>(sMA), ar.dev<int32_t>(sMB), ar.dev<int32_t>(sNM));
+    return ar.finish();
 }
 
 int orbm_distinctive_descriptors(const uint8_t* descriptors, const int32_t* offsets, int npoints, int device,
@@ -358,22 +349,16 @@ int orbm_distinctive_descriptors(const uint8_t* descriptors, const int32_t* offs
     }
     const size_t total = (size_t)(offsets[npoints] - offsets[0]);
     if (total && !descriptors) { orbx_set_error("null descriptors"); return ORBX_E_INVALID; }
-    BBuf dDesc, dOff, dIdx, dMed;
-    int rc = dDesc.alloc(total * 32); if (rc) return rc;
-    rc = dOff.alloc((size_t)(npoints + 1) * 4); if (rc) return rc;
-    rc = dIdx.alloc((size_t)npoints * 4); if (rc) return rc;
-    rc = dMed.alloc((size_t)npoints * 4); if (rc) return rc;
     std::vector<int32_t> rel(npoints + 1);
     for (int p = 0; p <= npoints; ++p) rel[p] = offsets[p] - offsets[0];
-    if (total) ORBX_CUDA(cudaMemcpy(dDesc.p, descriptors + (size_t)offsets[0] * 32, total * 32, cudaMemcpyHostToDevice));
-    ORBX_CUDA(cudaMemcpy(dOff.p, rel.data(), (size_t)(npoints + 1) * 4, cudaMemcpyHostToDevice));
+    CallArena ar;
+    const int sDesc = ar.in(total ? descriptors + (size_t)offsets[0] * 32 : nullptr, total * 32), sOff = ar.in(rel.data(), (size_t)(npoints + 1) * 4);
+    const int sIdx = ar.out(best_idx, (size_t)npoints * 4), sMed = ar.out(best_median, (size_t)npoints * 4);
+    int rc = ar.commit(); if (rc) return rc;
     const int smem = std::min(maxN, DD_SMEM_DESC) * 32 + 16;
     if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(distinctive_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    distinctive_kernel<<<npoints, DD_THREADS, smem>>>(dDesc.as<u8>(), dOff.as<int32_t>(), dIdx.as<int32_t>(), dMed.as<int32_t>());
-    ORBX_CUDA(cudaGetLastError());
-    ORBX_CUDA(cudaMemcpy(best_idx, dIdx.p, (size_t)npoints * 4, cudaMemcpyDeviceToHost));
-    if (best_median) ORBX_CUDA(cudaMemcpy(best_median, dMed.p, (size_t)npoints * 4, cudaMemcpyDeviceToHost));
-    return ORBX_OK;
+    distinctive_kernel<<<npoints, DD_THREADS, smem>>>(ar.dev<u8>(sDesc), ar.dev<int32_t>(sOff), ar.dev<int32_t>(sIdx), ar.dev<int32_t>(sMed));
+    return ar.finish();
 }
 
 } // extern "C"

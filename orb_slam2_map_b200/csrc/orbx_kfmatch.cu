@@ -244,54 +244,57 @@ static int kf_check(const orbm_keyframe* kf)
     return ORBX_OK;
 }
 
-// one uploaded keyframe with its grid, ready for area_best_kernel
-struct DevKeyFrame {
-    TempFrames tf;
-    DevBuf uRight;
-    AreaBestArgs args;
-    int upload(const orbm_keyframe* kf, int variant)
+// one keyframe of a call's arena (CallArena): keypoints, descriptors, count and, for Fuse variant 0, mvuRight go up with the
+// call's single upload; the grid is built on the device behind it
+struct ArenaKeyFrame {
+    int sCount = -1, sKps = -1, sDesc = -1, sUR = -1, sGS = -1, sGI = -1, n = 0;
+    int declare(CallArena& ar, const orbm_keyframe* kf, int variant)
     {
         const orbm_frame* f = &kf->frame;
         if (!(f->max_x > f->min_x) || !(f->max_y > f->min_y)) { orbx_set_error("bad keyframe bounds"); return ORBX_E_INVALID; }
-        int rc = tf.alloc(1, f->n); if (rc) return rc;
-        rc = tf.upload(0, f); if (rc) return rc;
+        if (variant == ORBM_FUSE_MAPPOINTS && (!kf->inv_level_sigma2 || f->nlevels <= 0)) { orbx_set_error("Fuse variant 0 needs inv_level_sigma2 / nlevels"); return ORBX_E_INVALID; }
+        n = f->n;
+        const size_t cap = (size_t)std::max(n, 8);
+        sCount = ar.in(&n, 4);
+        sKps = ar.in(n ? f->keys_un : nullptr, (size_t)n * sizeof(orbx_keypoint));
+        sDesc = ar.in(n ? f->descriptors : nullptr, (size_t)n * 32);
+        if (variant == ORBM_FUSE_MAPPOINTS && f->u_right && n > 0) sUR = ar.in(f->u_right, (size_t)n * 4);
+        sGS = ar.work((ORBX_GRID_CELLS + 1) * sizeof(unsigned short));
+        sGI = ar.work(cap * sizeof(unsigned short));
+        return ORBX_OK;
+    }
+    int ready(CallArena& ar, const orbm_keyframe* kf, int variant, AreaBestArgs& args)
+    {
+        const orbm_frame* f = &kf->frame;
+        FrameStore fs;
+        fs.kps = ar.dev<orbx_keypoint>(sKps); fs.desc = ar.dev<u8>(sDesc); fs.count = ar.dev<int>(sCount);
+        fs.gridStart = ar.dev<unsigned short>(sGS); fs.gridIdx = ar.dev<unsigned short>(sGI); fs.cap = std::max(n, 8);
         args.gp = orbx_grid_params(f->min_x, f->max_x, f->min_y, f->max_y);
-        rc = orbx_launch_grid_build(tf.store(), 0, 1, args.gp, 0); if (rc) return rc;
-        args.fs = tf.store();
-        args.uRight = nullptr;
+        const int rc = orbx_launch_grid_build(fs, 0, 1, args.gp, 0); if (rc) return rc;
+        args.fs = fs;
+        args.uRight = sUR >= 0 ? ar.dev<float>(sUR) : nullptr;
         args.variant = variant;
         args.thDist = variant == ORBM_FUSE_SIM3_LEG ? ORBX_TH_HIGH : ORBX_TH_LOW;
         for (int l = 0; l < ORBX_MAX_LEVELS; ++l) args.invSigma2[l] = 0.f;
-        if (variant == ORBM_FUSE_MAPPOINTS) {
-            if (!kf->inv_level_sigma2 || f->nlevels <= 0) { orbx_set_error("Fuse variant 0 needs inv_level_sigma2 / nlevels"); return ORBX_E_INVALID; }
-            for (int l = 0; l < f->nlevels; ++l) args.invSigma2[l] = kf->inv_level_sigma2[l];
-            if (f->u_right && f->n > 0) {
-                rc = uRight.alloc((size_t)f->n * 4); if (rc) return rc;
-                ORBX_CUDA(cudaMemcpy(uRight.p, f->u_right, (size_t)f->n * 4, cudaMemcpyHostToDevice));
-                args.uRight = uRight.as<float>();
-            }
-        }
+        if (variant == ORBM_FUSE_MAPPOINTS) for (int l = 0; l < f->nlevels; ++l) args.invSigma2[l] = kf->inv_level_sigma2[l];
         return ORBX_OK;
     }
 };
 
-struct DevQueries {
-    DevBuf q, d, bi, bd;
-    int upload(const orbm_proj_query* queries, const uint8_t* desc, int nq)
+struct ArenaQueries {
+    int sQ = -1, sD = -1, sBI = -1, sBD = -1;
+    // outIdx / outDist: host destinations (nullptr = the result stays on the device as work space)
+    void declare(CallArena& ar, const orbm_proj_query* queries, const uint8_t* desc, int nq, int32_t* outIdx, int32_t* outDist)
     {
-        int rc;
-        if ((rc = q.alloc((size_t)nq * sizeof(orbm_proj_query))) || (rc = d.alloc((size_t)nq * 32)) ||
-            (rc = bi.alloc((size_t)nq * 4)) || (rc = bd.alloc((size_t)nq * 4))) return rc;
-        if (nq > 0) {
-            ORBX_CUDA(cudaMemcpy(q.p, queries, (size_t)nq * sizeof(orbm_proj_query), cudaMemcpyHostToDevice));
-            ORBX_CUDA(cudaMemcpy(d.p, desc, (size_t)nq * 32, cudaMemcpyHostToDevice));
-        }
-        return ORBX_OK;
+        sQ = ar.in(nq ? queries : nullptr, (size_t)nq * sizeof(orbm_proj_query));
+        sD = ar.in(nq ? desc : nullptr, (size_t)nq * 32);
+        sBI = outIdx ? ar.out(outIdx, (size_t)nq * 4) : ar.work((size_t)nq * 4);
+        sBD = outDist ? ar.out(outDist, (size_t)nq * 4) : ar.work((size_t)nq * 4);
     }
-    void launch(const AreaBestArgs& a, int nq)
+    void launch(CallArena& ar, const AreaBestArgs& a, int nq)
     {
         if (nq > 0)
-            area_best_kernel<<<(nq + AB_WARPS - 1) / AB_WARPS, AB_WARPS * 32>>>(a, q.as<orbm_proj_query>(), d.as<u8>(), nq, bi.as<int>(), bd.as<int>());
+            area_best_kernel<<<(nq + AB_WARPS - 1) / AB_WARPS, AB_WARPS * 32>>>(a, ar.dev<orbm_proj_query>(sQ), ar.dev<u8>(sD), nq, ar.dev<int>(sBI), ar.dev<int>(sBD));
     }
 };
 
@@ -306,15 +309,16 @@ int orbm_fuse(int variant, const orbm_keyframe* kf, const orbm_proj_query* queri
     if (nq < 0 || (nq > 0 && (!queries || !query_desc || !best_idx))) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
     if (nq == 0) return ORBX_OK;
     rc = kf_device(device); if (rc) return rc;
-    DevKeyFrame dk;
-    rc = dk.upload(kf, variant); if (rc) return rc;
-    DevQueries dq;
-    rc = dq.upload(queries, query_desc, nq); if (rc) return rc;
-    dq.launch(dk.args, nq);
-    ORBX_CUDA(cudaGetLastError());
-    ORBX_CUDA(cudaMemcpy(best_idx, dq.bi.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
-    if (best_dist) ORBX_CUDA(cudaMemcpy(best_dist, dq.bd.p, (size_t)nq * 4, cudaMemcpyDeviceToHost));
-    return ORBX_OK;
+    CallArena ar;
+    ArenaKeyFrame dk;
+    ArenaQueries dq;
+    rc = dk.declare(ar, kf, variant); if (rc) return rc;
+    dq.declare(ar, queries, query_desc, nq, best_idx, best_dist);
+    rc = ar.commit(); if (rc) return rc;
+    AreaBestArgs args;
+    rc = dk.ready(ar, kf, variant, args); if (rc) return rc;
+    dq.launch(ar, args, nq);
+    return ar.finish();
 }
 
 int orbm_search_by_sim3(const orbm_keyframe* kf1, const orbm_keyframe* kf2, const orbm_proj_query* queries12,
@@ -331,25 +335,26 @@ int orbm_search_by_sim3(const orbm_keyframe* kf1, const orbm_keyframe* kf2, cons
     for (int q = 0; q < nq12; ++q) if (index1[q] < 0 || index1[q] >= n1) { orbx_set_error("index1[%d] out of range", q); return ORBX_E_INVALID; }
     for (int q = 0; q < nq21; ++q) if (index2[q] < 0 || index2[q] >= n2) { orbx_set_error("index2[%d] out of range", q); return ORBX_E_INVALID; }
     rc = kf_device(device); if (rc) return rc;
-    DevKeyFrame d1, d2;
-    rc = d1.upload(kf1, ORBM_FUSE_SIM3_LEG); if (rc) return rc;
-    rc = d2.upload(kf2, ORBM_FUSE_SIM3_LEG); if (rc) return rc;
-    DevQueries q12, q21;
-    rc = q12.upload(queries12, desc12, nq12); if (rc) return rc;
-    rc = q21.upload(queries21, desc21, nq21); if (rc) return rc;
-    DevBuf dI1, dI2, dM1, dM2, dM12, dNf;
-    if ((rc = dI1.alloc((size_t)nq12 * 4)) || (rc = dI2.alloc((size_t)nq21 * 4)) || (rc = dM1.alloc((size_t)n1 * 4)) ||
-        (rc = dM2.alloc((size_t)n2 * 4)) || (rc = dM12.alloc((size_t)n1 * 4)) || (rc = dNf.alloc(4))) return rc;
-    if (nq12) ORBX_CUDA(cudaMemcpy(dI1.p, index1, (size_t)nq12 * 4, cudaMemcpyHostToDevice));
-    if (nq21) ORBX_CUDA(cudaMemcpy(dI2.p, index2, (size_t)nq21 * 4, cudaMemcpyHostToDevice));
-    q12.launch(d2.args, nq12);                 // points of KF1 searched in KF2
-    q21.launch(d1.args, nq21);
-    sim3_agree_kernel<<<1, 256>>>(q12.bi.as<int>(), dI1.as<int>(), nq12, q21.bi.as<int>(), dI2.as<int>(), nq21, n1, n2,
-                                  dM1.as<int>(), dM2.as<int>(), dM12.as<int>(), dNf.as<int>());
-    ORBX_CUDA(cudaGetLastError());
-    if (n1) ORBX_CUDA(cudaMemcpy(match12, dM12.p, (size_t)n1 * 4, cudaMemcpyDeviceToHost));
+    CallArena ar;
+    ArenaKeyFrame d1, d2;
+    ArenaQueries q12, q21;
+    rc = d1.declare(ar, kf1, ORBM_FUSE_SIM3_LEG); if (rc) return rc;
+    rc = d2.declare(ar, kf2, ORBM_FUSE_SIM3_LEG); if (rc) return rc;
+    q12.declare(ar, queries12, desc12, nq12, nullptr, nullptr);
+    q21.declare(ar, queries21, desc21, nq21, nullptr, nullptr);
+    const int sI1 = ar.in(nq12 ? index1 : nullptr, (size_t)nq12 * 4), sI2 = ar.in(nq21 ? index2 : nullptr, (size_t)nq21 * 4);
     int nf = 0;
-    ORBX_CUDA(cudaMemcpy(&nf, dNf.p, 4, cudaMemcpyDeviceToHost));
+    const int sM12 = ar.out(match12, (size_t)n1 * 4), sNf = ar.out(&nf, 4);
+    const int sM1 = ar.work((size_t)n1 * 4), sM2 = ar.work((size_t)n2 * 4);
+    rc = ar.commit(); if (rc) return rc;
+    AreaBestArgs a1, a2;
+    rc = d1.ready(ar, kf1, ORBM_FUSE_SIM3_LEG, a1); if (rc) return rc;
+    rc = d2.ready(ar, kf2, ORBM_FUSE_SIM3_LEG, a2); if (rc) return rc;
+    q12.launch(ar, a2, nq12);                 // points of KF1 searched in KF2
+    q21.launch(ar, a1, nq21);
+    sim3_agree_kernel<<<1, 256>>>(ar.dev<int>(q12.sBI), ar.dev<int>(sI1), nq12, ar.dev<int>(q21.sBI), ar.dev<int>(sI2), nq21, n1, n2,
+                                  ar.dev<int>(sM1), ar.dev<int>(sM2), ar.dev<int>(sM12), ar.dev<int>(sNf));
+    rc = ar.finish(); if (rc) return rc;
     if (nfound) *nfound = nf;
     return ORBX_OK;
 }
@@ -388,42 +393,36 @@ int orbm_search_for_triangulation(const orbm_keyframe* kf1, const orbm_keyframe*
     const size_t smem = (size_t)(capA + capB) * 8 + capA + 16;
     if (smem > 220 * 1024) { orbx_set_error("keyframes of %d / %d features exceed the shared-memory sort (%zu bytes)", maxA, maxB, smem); return ORBX_E_CAPACITY; }
     int rc = kf_device(device); if (rc) return rc;
-    DevBuf dPairs, dKA, dDA, dNA, dFA, dUA, dKB, dDB, dNB, dFB, dUB, dM, dNM;
-#define KF_ALLOC(buf, bytes) rc = buf.alloc(bytes); if (rc) return rc
-    KF_ALLOC(dPairs, npairs * sizeof(TriPair));
-    KF_ALLOC(dKA, (size_t)totA * sizeof(orbx_keypoint)); KF_ALLOC(dDA, (size_t)totA * 32); KF_ALLOC(dNA, (size_t)totA * 4);
-    KF_ALLOC(dFA, (size_t)totA); KF_ALLOC(dUA, (size_t)totA * 4);
-    KF_ALLOC(dKB, (size_t)totB * sizeof(orbx_keypoint)); KF_ALLOC(dDB, (size_t)totB * 32); KF_ALLOC(dNB, (size_t)totB * 4);
-    KF_ALLOC(dFB, (size_t)totB); KF_ALLOC(dUB, (size_t)totB * 4);
-    KF_ALLOC(dM, (size_t)totA * 4); KF_ALLOC(dNM, (size_t)npairs * 4);
-#undef KF_ALLOC
-    ORBX_CUDA(cudaMemcpy(dPairs.p, pairs.data(), npairs * sizeof(TriPair), cudaMemcpyHostToDevice));
-    std::vector<float> minus;
-    auto up = [&](const orbm_keyframe& kf, int off, DevBuf& k, DevBuf& d, DevBuf& nd, DevBuf& fl, DevBuf& ur) -> int {
+    CallArena ar;
+    const int sPairs = ar.in(pairs.data(), npairs * sizeof(TriPair));
+    const int sKA = ar.in(nullptr, (size_t)totA * sizeof(orbx_keypoint)), sDA = ar.in(nullptr, (size_t)totA * 32), sNA = ar.in(nullptr, (size_t)totA * 4),
+              sFA = ar.in(nullptr, (size_t)totA), sUA = ar.in(nullptr, (size_t)totA * 4);
+    const int sKB = ar.in(nullptr, (size_t)totB * sizeof(orbx_keypoint)), sDB = ar.in(nullptr, (size_t)totB * 32), sNB = ar.in(nullptr, (size_t)totB * 4),
+              sFB = ar.in(nullptr, (size_t)totB), sUB = ar.in(nullptr, (size_t)totB * 4);
+    const int sM = ar.out(matches12, (size_t)totA * 4), sNM = ar.out(nmatches, (size_t)npairs * 4);
+    rc = ar.layout(); if (rc) return rc;
+    auto up = [&](const orbm_keyframe& kf, int off, int k, int d, int nd, int fl, int ur) {
         const orbm_frame& f = kf.frame;
-        if (f.n <= 0) return ORBX_OK;
-        ORBX_CUDA(cudaMemcpy(k.as<orbx_keypoint>() + off, f.keys_un, (size_t)f.n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice));
-        ORBX_CUDA(cudaMemcpy(d.as<u8>() + (size_t)off * 32, f.descriptors, (size_t)f.n * 32, cudaMemcpyHostToDevice));
-        ORBX_CUDA(cudaMemcpy(nd.as<uint32_t>() + off, kf.node_id, (size_t)f.n * 4, cudaMemcpyHostToDevice));
-        ORBX_CUDA(cudaMemcpy(fl.as<u8>() + off, kf.flags, (size_t)f.n, cudaMemcpyHostToDevice));
-        const float* u = f.u_right;
-        if (!u) { minus.assign((size_t)f.n, -1.f); u = minus.data(); }
-        ORBX_CUDA(cudaMemcpy(ur.as<float>() + off, u, (size_t)f.n * 4, cudaMemcpyHostToDevice));
-        return ORBX_OK;
+        if (f.n <= 0) return;
+        memcpy(ar.hostp<orbx_keypoint>(k) + off, f.keys_un, (size_t)f.n * sizeof(orbx_keypoint));
+        memcpy(ar.hostp<u8>(d) + (size_t)off * 32, f.descriptors, (size_t)f.n * 32);
+        memcpy(ar.hostp<uint32_t>(nd) + off, kf.node_id, (size_t)f.n * 4);
+        memcpy(ar.hostp<u8>(fl) + off, kf.flags, (size_t)f.n);
+        float* u = ar.hostp<float>(ur) + off;
+        if (f.u_right) memcpy(u, f.u_right, (size_t)f.n * 4);
+        else for (int i = 0; i < f.n; ++i) u[i] = -1.f;
     };
     for (int p = 0; p < npairs; ++p) {
-        rc = up(kf1[p], pairs[p].offA, dKA, dDA, dNA, dFA, dUA); if (rc) return rc;
-        rc = up(kf2[p], pairs[p].offB, dKB, dDB, dNB, dFB, dUB); if (rc) return rc;
+        up(kf1[p], pairs[p].offA, sKA, sDA, sNA, sFA, sUA);
+        up(kf2[p], pairs[p].offB, sKB, sDB, sNB, sFB, sUB);
     }
+    rc = ar.upload(); if (rc) return rc;
     if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(triangulation_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    triangulation_kernel<<<npairs, TRI_THREADS, smem>>>(dPairs.as<TriPair>(), dKA.as<orbx_keypoint>(), dDA.as<u8>(), dNA.as<uint32_t>(),
-                                                        dFA.as<u8>(), dUA.as<float>(), dKB.as<orbx_keypoint>(), dDB.as<u8>(),
-                                                        dNB.as<uint32_t>(), dFB.as<u8>(), dUB.as<float>(), only_stereo, check_orientation,
-                                                        capA, capB, dM.as<int32_t>(), dNM.as<int32_t>());
-    ORBX_CUDA(cudaGetLastError());
-    if (totA) ORBX_CUDA(cudaMemcpy(matches12, dM.p, (size_t)totA * 4, cudaMemcpyDeviceToHost));
-    ORBX_CUDA(cudaMemcpy(nmatches, dNM.p, (size_t)npairs * 4, cudaMemcpyDeviceToHost));
-    return ORBX_OK;
+    triangulation_kernel<<<npairs, TRI_THREADS, smem>>>(ar.dev<TriPair>(sPairs), ar.dev<orbx_keypoint>(sKA), ar.dev<u8>(sDA), ar.dev<uint32_t>(sNA),
+                                                        ar.dev<u8>(sFA), ar.dev<float>(sUA), ar.dev<orbx_keypoint>(sKB), ar.dev<u8>(sDB),
+                                                        ar.dev<uint32_t>(sNB), ar.dev<u8>(sFB), ar.dev<float>(sUB), only_stereo, check_orientation,
+                                                        capA, capB, ar.dev<int32_t>(sM), ar.dev<int32_t>(sNM));
+    return ar.finish();
 }
 
 } // extern "C"

@@ -959,7 +959,7 @@ __device__ __forceinline__ int reflect101i(int i, int n)
 }
 
 #define STEREO_THREADS 256
-#define STEREO_SPLITS 8           // CTAs per pair (left keypoints are split; the median cull is a second kernel)
+#define STEREO_SPLITS 8           // CTAs per pair in a batch (left keypoints are split; the median cull is a second kernel); one pair: up to 64
 __global__ void __launch_bounds__(STEREO_THREADS)
 stereo_match_kernel(FrameStore fs, int firstSlot, PyrView pv, float bf, float fx, int rightCap, int listCap,
                     float* __restrict__ uRightOut, float* __restrict__ depthOut, int* __restrict__ sadScratch,
@@ -976,7 +976,7 @@ stereo_match_kernel(FrameStore fs, int firstSlot, PyrView pv, float bf, float fx
     const int pair = blockIdx.x, split = blockIdx.y;
     const int sL = firstSlot + 2 * pair, sR = sL + 1;
     const int N = min(fs.count[sL], fs.cap), Nr = min(min(fs.count[sR], fs.cap), rightCap);
-    const int perSplit = (N + STEREO_SPLITS - 1) / STEREO_SPLITS;
+    const int perSplit = (N + (int)gridDim.y - 1) / (int)gridDim.y;
     const int iBeg = split * perSplit, iEnd = min(N, iBeg + perSplit);
     const orbx_keypoint* kL = fs.kps + (size_t)sL * fs.cap;
     const orbx_keypoint* kR = fs.kps + (size_t)sR * fs.cap;
@@ -1341,7 +1341,9 @@ static int launch_stereo(const FrameStore& fs, int firstSlot, int npairs, const 
     if (smem > 200 * 1024) { listCap = 0; smem = ((pv.h[0] + 4) & ~3) * 4 + rightCap * 5 + 16; }
     if (smem > 200 * 1024) { orbx_set_error("more than %d right keypoints per frame unsupported by the stereo matcher", 180 * 1024 / 5); return ORBX_E_CAPACITY; }
     if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(stereo_match_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    stereo_match_kernel<<<dim3(npairs, STEREO_SPLITS), STEREO_THREADS, smem, st>>>(fs, firstSlot, pv, bf, fx, rightCap, listCap, uRight, depth, sadScratch, ncmp);
+    // a batch fills the GPU with 8 CTAs per pair; a single pair (the per-frame call) is spread over more SMs
+    const int splits = npairs >= 16 ? STEREO_SPLITS : std::min(64, std::max(STEREO_SPLITS, 128 / npairs));
+    stereo_match_kernel<<<dim3(npairs, splits), STEREO_THREADS, smem, st>>>(fs, firstSlot, pv, bf, fx, rightCap, listCap, uRight, depth, sadScratch, ncmp);
     stereo_cull_kernel<<<npairs, STEREO_THREADS, 0, st>>>(fs, firstSlot, uRight, depth, sadScratch);
     return ORBX_OK;
 }
@@ -1648,45 +1650,60 @@ int orbm_compute_stereo_matches(const orbm_stereo_input* in, float* u_right, flo
         const orbx_keypoint& k = i < in->n_left ? in->keys_left[i] : in->keys_right[i - in->n_left];
         if (k.octave < 0 || k.octave >= in->nlevels) { orbx_set_error("keypoint octave outside [0,nlevels)"); return ORBX_E_INVALID; }
     }
-    TempFrames tf;
-    rc = tf.alloc(2, std::max(in->n_left, in->n_right)); if (rc) return rc;
-    orbm_frame fl{in->n_left, in->keys_left, in->desc_left, 0.f, 1.f, 0.f, 1.f, nullptr, nullptr, 0};
-    orbm_frame fr{in->n_right, in->keys_right, in->desc_right, 0.f, 1.f, 0.f, 1.f, nullptr, nullptr, 0};
-    rc = tf.upload(0, &fl); if (rc) return rc;
-    rc = tf.upload(1, &fr); if (rc) return rc;
-    PyrView pv;
-    memset(&pv, 0, sizeof(pv));
-    pv.nlevels = in->nlevels;
-    std::vector<DevBuf> lv(2 * in->nlevels);
+    // one arena: both eyes' keypoints, descriptors and pyramids go up in ONE copy (the levels are packed row by row into the
+    // page-locked staging buffer), uRight / depth / the compare count come back in one
     for (int l = 0; l < in->nlevels; ++l) {
-        pv.w[l] = in->level_width[l]; pv.h[l] = in->level_height[l];
-        pv.scale[l] = in->scale_factors[l]; pv.invScale[l] = in->inv_scale_factors[l];
-        if (pv.w[l] <= 0 || pv.h[l] <= 0) { orbx_set_error("empty pyramid level %d", l); return ORBX_E_INVALID; }
+        if (in->level_width[l] <= 0 || in->level_height[l] <= 0) { orbx_set_error("empty pyramid level %d", l); return ORBX_E_INVALID; }
         for (int e = 0; e < 2; ++e) {
             const uint8_t* src = e ? in->pyr_right[l] : in->pyr_left[l];
             const int64_t ss = e ? in->pyr_stride_right[l] : in->pyr_stride_left[l];
-            if (!src || ss < pv.w[l]) { orbx_set_error("bad pyramid level %d", l); return ORBX_E_INVALID; }
-            DevBuf& b = lv[2 * l + e];
-            const int pitch = (pv.w[l] + 15) & ~15;
-            rc = b.alloc((size_t)pitch * pv.h[l]); if (rc) return rc;
-            ORBX_CUDA(cudaMemcpy2D(b.p, pitch, src, (size_t)ss, pv.w[l], pv.h[l], cudaMemcpyHostToDevice));
-            pv.base[e][l] = b.as<u8>(); pv.pitch[e][l] = pitch; pv.pairStride[e][l] = 0;
+            if (!src || ss < in->level_width[l]) { orbx_set_error("bad pyramid level %d", l); return ORBX_E_INVALID; }
         }
     }
-    DevBuf dU, dZ, dS, dC;
-    const size_t n = (size_t)tf.cap;
-    if ((rc = dU.alloc(n * 4)) || (rc = dZ.alloc(n * 4)) || (rc = dS.alloc(n * 4)) || (rc = dC.alloc(8))) return rc;
-    ORBX_CUDA(cudaMemset(dC.p, 0, 8));
-    rc = launch_stereo(tf.store(), 0, 1, pv, in->bf, in->fx, tf.cap, dU.as<float>(), dZ.as<float>(), dS.as<int>(),
-                       dC.as<unsigned long long>(), 0);
-    if (rc) return rc;
-    ORBX_CUDA(cudaGetLastError());
-    if (in->n_left > 0) {
-        ORBX_CUDA(cudaMemcpy(u_right, dU.p, (size_t)in->n_left * 4, cudaMemcpyDeviceToHost));
-        ORBX_CUDA(cudaMemcpy(depth, dZ.p, (size_t)in->n_left * 4, cudaMemcpyDeviceToHost));
-    }
+    const int cap = std::max(std::max(in->n_left, in->n_right), 8);
+    const int counts[2] = {in->n_left, in->n_right};
+    CallArena ar;
+    const int sCount = ar.in(counts, 8), sKps = ar.in(nullptr, (size_t)2 * cap * sizeof(orbx_keypoint)), sDesc = ar.in(nullptr, (size_t)2 * cap * 32);
+    int sLv[2][ORBX_MAX_LEVELS];
+    for (int l = 0; l < in->nlevels; ++l)
+        for (int e = 0; e < 2; ++e) sLv[e][l] = ar.in(nullptr, (size_t)((in->level_width[l] + 15) & ~15) * in->level_height[l]);
     unsigned long long c = 0;
-    ORBX_CUDA(cudaMemcpy(&c, dC.p, 8, cudaMemcpyDeviceToHost));
+    const int sU = ar.out(u_right, (size_t)in->n_left * 4), sZ = ar.out(depth, (size_t)in->n_left * 4), sC = ar.out(&c, 8);
+    const int sS = ar.work((size_t)cap * 4);
+    rc = ar.layout(); if (rc) return rc;
+    if (in->n_left) {
+        memcpy(ar.hostp<orbx_keypoint>(sKps), in->keys_left, (size_t)in->n_left * sizeof(orbx_keypoint));
+        memcpy(ar.hostp<u8>(sDesc), in->desc_left, (size_t)in->n_left * 32);
+    }
+    if (in->n_right) {
+        memcpy(ar.hostp<orbx_keypoint>(sKps) + cap, in->keys_right, (size_t)in->n_right * sizeof(orbx_keypoint));
+        memcpy(ar.hostp<u8>(sDesc) + (size_t)cap * 32, in->desc_right, (size_t)in->n_right * 32);
+    }
+    PyrView pv;
+    memset(&pv, 0, sizeof(pv));
+    pv.nlevels = in->nlevels;
+    for (int l = 0; l < in->nlevels; ++l) {
+        pv.w[l] = in->level_width[l]; pv.h[l] = in->level_height[l];
+        pv.scale[l] = in->scale_factors[l]; pv.invScale[l] = in->inv_scale_factors[l];
+        const int pitch = (pv.w[l] + 15) & ~15;
+        for (int e = 0; e < 2; ++e) {
+            const uint8_t* src = e ? in->pyr_right[l] : in->pyr_left[l];
+            const int64_t ss = e ? in->pyr_stride_right[l] : in->pyr_stride_left[l];
+            u8* dst = ar.hostp<u8>(sLv[e][l]);
+            if (ss == pitch) memcpy(dst, src, (size_t)pitch * pv.h[l] - (pitch - pv.w[l]));
+            else for (int y = 0; y < pv.h[l]; ++y) memcpy(dst + (size_t)y * pitch, src + (size_t)y * ss, (size_t)pv.w[l]);
+            pv.base[e][l] = ar.dev<u8>(sLv[e][l]); pv.pitch[e][l] = pitch; pv.pairStride[e][l] = 0;
+        }
+    }
+    rc = ar.upload(); if (rc) return rc;
+    ORBX_CUDA(cudaMemsetAsync(ar.dev<u8>(sC), 0, 8, 0));
+    FrameStore fs;
+    fs.kps = ar.dev<orbx_keypoint>(sKps); fs.desc = ar.dev<u8>(sDesc); fs.count = ar.dev<int>(sCount);
+    fs.gridStart = nullptr; fs.gridIdx = nullptr; fs.cap = cap;
+    rc = launch_stereo(fs, 0, 1, pv, in->bf, in->fx, cap, ar.dev<float>(sU), ar.dev<float>(sZ), ar.dev<int>(sS),
+                       ar.dev<unsigned long long>(sC), 0);
+    if (rc) return rc;
+    rc = ar.finish(); if (rc) return rc;
     if (ncompares) *ncompares = c;
     return ORBX_OK;
 }

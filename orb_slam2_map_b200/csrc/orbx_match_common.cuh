@@ -4,6 +4,8 @@
 #define ORBX_MATCH_COMMON_CUH
 
 #include "orbx_internal.h"
+#include <vector>
+#include <cstring>
 
 typedef uint8_t u8;
 #define FULL 0xffffffffu
@@ -97,6 +99,55 @@ struct DevBuf {
     ~DevBuf() { orbx_scratch_free(p); }
     int alloc(size_t bytes) { return orbx_scratch_alloc(&p, bytes); }
     template <typename T> T* as() { return (T*)p; }
+};
+
+// One stateless call = one device arena + one page-locked staging buffer laid out [inputs][in/out][outputs][work]: everything the
+// call uploads goes up in ONE copy and everything it returns comes back in ONE copy (a dozen small synchronous copies of
+// pageable memory cost 10-20 us each, more than the kernels of a per-frame call).  Segments are declared first (in / inout /
+// out / work return an id), commit() lays them out, stages and uploads; dev<T>(id) is the segment on the device; finish()
+// downloads, waits and hands the outputs back.  All work on the legacy default stream, like the kernels of these calls.
+struct CallArena {
+    struct Seg { int kind; const void* src; void* dst; size_t bytes, off; };
+    std::vector<Seg> segs;
+    DevBuf arena;
+    u8* host = nullptr; u8* device = nullptr;
+    size_t upBytes = 0, downBegin = 0, downEnd = 0;
+    int add(int kind, const void* src, void* dst, size_t bytes) { segs.push_back({kind, src, dst, bytes, 0}); return (int)segs.size() - 1; }
+    int in(const void* src, size_t bytes) { return add(0, src, nullptr, bytes); }
+    int inout(void* p, size_t bytes) { return add(1, p, p, bytes); }
+    int out(void* dst, size_t bytes) { return add(2, nullptr, dst, bytes); }
+    int work(size_t bytes) { return add(3, nullptr, nullptr, bytes); }
+    int layout()
+    {
+        size_t off = 0;
+        for (int kind = 0; kind < 4; ++kind) {
+            if (kind == 1) downBegin = off;
+            if (kind == 2) upBytes = off;
+            if (kind == 3) downEnd = off;
+            for (Seg& s : segs) if (s.kind == kind) { s.off = off; off += (s.bytes + 255) & ~(size_t)255; }
+        }
+        int rc = arena.alloc(off ? off : 256); if (rc) return rc;
+        if ((rc = orbx_scratch_host((void**)&host, downEnd ? downEnd : 256))) return rc;
+        device = arena.as<u8>();
+        return ORBX_OK;
+    }
+    int upload()
+    {
+        for (const Seg& s : segs) if (s.kind <= 1 && s.bytes && s.src) memcpy(host + s.off, s.src, s.bytes);
+        if (upBytes) ORBX_CUDA(cudaMemcpyAsync(device, host, upBytes, cudaMemcpyHostToDevice, 0));
+        return ORBX_OK;
+    }
+    int commit() { const int rc = layout(); return rc ? rc : upload(); }
+    template <typename T> T* hostp(int id) { return reinterpret_cast<T*>(host + segs[id].off); }   // inputs without a source: fill between layout() and upload()
+    template <typename T> T* dev(int id) { return reinterpret_cast<T*>(device + segs[id].off); }
+    int finish()
+    {
+        ORBX_CUDA(cudaGetLastError());
+        if (downEnd > downBegin) ORBX_CUDA(cudaMemcpyAsync(host + downBegin, device + downBegin, downEnd - downBegin, cudaMemcpyDeviceToHost, 0));
+        ORBX_CUDA(cudaStreamSynchronize(0));
+        for (const Seg& s : segs) if ((s.kind == 1 || s.kind == 2) && s.bytes && s.dst) memcpy(s.dst, host + s.off, s.bytes);
+        return ORBX_OK;
+    }
 };
 
 // temporary device frames of the stateless entry points

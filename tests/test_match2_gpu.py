@@ -17,13 +17,17 @@ def _frame_with_queries(seed, nq=900, dup=False):
     img = synth.textured_canvas(640, 480, seed=seed)
     orc = O.Extractor()
     k, d = orc.extract(img)
+    return _queries_from_keypoints(k, d, orc.tables()["scale"], seed, nq, dup)
+
+
+def _queries_from_keypoints(k, d, scale, seed, nq=900, dup=False):
     r = np.random.default_rng(seed)
     n = len(k)
     src = r.integers(0, n, nq)
     q = np.zeros(nq, capi.PROJ_DTYPE)
     q["u"] = k["x"][src] + r.normal(0, 3, nq).astype(np.float32)
     q["v"] = k["y"][src] + r.normal(0, 3, nq).astype(np.float32)
-    q["radius"] = r.choice([4.0, 7.0, 15.0, 30.0], nq).astype(np.float32) * orc.tables()["scale"][k["octave"][src]]
+    q["radius"] = r.choice([4.0, 7.0, 15.0, 30.0], nq).astype(np.float32) * scale[k["octave"][src]]
     lvl = k["octave"][src]
     q["min_level"] = np.maximum(lvl - 1, 0)
     q["max_level"] = lvl
@@ -42,7 +46,7 @@ def _frame_with_queries(seed, nq=900, dup=False):
     u_right = np.where(r.random(n) < 0.6, k["x"] - 20.0 + r.normal(0, 4, n), -1.0).astype(np.float32)
     occupied = (r.random(n) < 0.1).astype(np.uint8)
     blocks = (r.random(nq) < 0.7).astype(np.uint8)
-    return k, d, q, qd, u_right, occupied, blocks, orc.tables()["scale"]
+    return k, d, q, qd, u_right, occupied, blocks, scale
 
 
 @pytest.mark.parametrize("variant,th,ratio,ori", [
