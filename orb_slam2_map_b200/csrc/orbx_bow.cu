@@ -73,22 +73,30 @@ __device__ void block_bitonic_sort64(unsigned long long* a, int cap)
         }
 }
 
+// gridDim = (pairs, splits).  Nodes are independent (a feature of B belongs to one node, so the "already matched" flags of one
+// node are never read by another), which lets the node runs of a pair be dealt to the warps of `splits` CTAs: one CTA per
+// pair in a batch, many for the single pair of a per-frame call.  Every CTA sorts both key lists for itself; a run belongs to
+// the warp its START POSITION in the sorted list of A maps to, so all CTAs agree on the deal without talking.  Outputs, the
+// per-feature bins and the pair state (histogram, count, ticket: BOW_STATE_INTS ints per pair) live in global memory and are
+// preset to 0xff bytes by the host (match = -1, bin = none, counters = -1); the CTA that draws the last ticket applies
+// ComputeThreeMaxima to the whole pair.
+#define BOW_STATE_INTS 64
 __global__ void __launch_bounds__(BOW_THREADS)
 search_bow_kernel(int variant, const BowPair* __restrict__ pairs, const u8* __restrict__ descA, const float* __restrict__ angA,
                   const uint32_t* __restrict__ nodeA, const u8* __restrict__ flagA, const u8* __restrict__ descB,
                   const float* __restrict__ angB, const uint32_t* __restrict__ nodeB, const u8* __restrict__ flagB,
                   float nnratio, int checkOri, int capA, int capB, int32_t* __restrict__ matchA, int32_t* __restrict__ matchB,
-                  int32_t* __restrict__ nmatchesOut)
+                  int32_t* __restrict__ nmatchesOut, u8* __restrict__ binOfAll, int* __restrict__ pairState)
 {
     extern __shared__ __align__(16) unsigned char smraw[];
-    __shared__ int sHist[ORBX_HISTO_LENGTH], sCount, sRuns, sInd[3];
+    __shared__ int sInd[3], sLast;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const BowPair P = pairs[blockIdx.x];
     unsigned long long* keysA = reinterpret_cast<unsigned long long*>(smraw);
     unsigned long long* keysB = keysA + capA;
-    unsigned short* runs = reinterpret_cast<unsigned short*>(keysB + capB);      // start positions of the node runs of A
-    u8* matchedB = reinterpret_cast<u8*>(runs + capA);
-    u8* binOf = matchedB + capB;
+    u8* matchedB = reinterpret_cast<u8*>(keysB + capB);
+    int* gState = pairState + (size_t)blockIdx.x * BOW_STATE_INTS;        // [0..29] histogram, [32] count, [33] ticket, all starting at -1
+    u8* binOf = binOfAll + P.offA;
     descA += (size_t)P.offA * 32; angA += P.offA; nodeA += P.offA; flagA += P.offA; matchA += P.offA;
     descB += (size_t)P.offB * 32; angB += P.offB; nodeB += P.offB; flagB += P.offB; matchB += P.offB;
     int pa = 1; while (pa < P.nA) pa <<= 1;
@@ -97,24 +105,17 @@ search_bow_kernel(int variant, const BowPair* __restrict__ pairs, const u8* __re
         keysA[i] = (i < P.nA && (flagA[i] & 1)) ? (((unsigned long long)nodeA[i] << 32) | (unsigned)i) : ~0ull;
     for (int i = tid; i < pb; i += BOW_THREADS)
         keysB[i] = (i < P.nB && (flagB[i] & 1)) ? (((unsigned long long)nodeB[i] << 32) | (unsigned)i) : ~0ull;
-    for (int i = tid; i < P.nA; i += BOW_THREADS) { matchA[i] = -1; binOf[i] = 0xff; }
-    for (int i = tid; i < P.nB; i += BOW_THREADS) { matchB[i] = -1; matchedB[i] = 0; }
-    if (tid < ORBX_HISTO_LENGTH) sHist[tid] = 0;
-    if (tid == 0) { sCount = 0; sRuns = 0; }
+    for (int i = tid; i < P.nB; i += BOW_THREADS) matchedB[i] = 0;
     __syncthreads();
     block_bitonic_sort64(keysA, pa);
     block_bitonic_sort64(keysB, pb);
-    // node runs of A (any order: nodes are independent)
-    for (int i = tid; i < P.nA; i += BOW_THREADS) {
-        const unsigned long long k = keysA[i];
-        if (k != ~0ull && (i == 0 || (keysA[i - 1] >> 32) != (k >> 32))) runs[atomicAdd(&sRuns, 1)] = (unsigned short)i;
-    }
-    __syncthreads();
-    const int nRuns = sRuns;
     int accepted = 0;
-    for (int r = wid; r < nRuns; r += BOW_THREADS / 32) {
-        const int a0 = runs[r];
-        const unsigned node = (unsigned)(keysA[a0] >> 32);
+    const int warpsAll = (int)gridDim.y * (BOW_THREADS / 32);
+    for (int a0 = (int)blockIdx.y * (BOW_THREADS / 32) + wid; a0 < P.nA; a0 += warpsAll) {
+        const unsigned long long k0 = keysA[a0];
+        if (k0 == ~0ull) break;                                  // sorted: the unused entries are at the end
+        if (a0 > 0 && (keysA[a0 - 1] >> 32) == (k0 >> 32)) continue;      // not the start of a node run
+        const unsigned node = (unsigned)(k0 >> 32);
         // B's run of the same node: [b0, b1)
         int lo = 0, hi = pb;
         const unsigned long long target = (unsigned long long)node << 32;
@@ -146,27 +147,39 @@ search_bow_kernel(int variant, const BowPair* __restrict__ pairs, const u8* __re
                 const int idxB = (int)(keysB[key] & 0xffffffffu);
                 if (lane == 0) {
                     matchedB[idxB] = 1; matchA[idxA] = idxB; matchB[idxB] = idxA;
-                    if (checkOri) { const int bin = rot_bin(angA[idxA], angB[idxB]); binOf[idxA] = (u8)bin; atomicAdd(&sHist[bin], 1); }
+                    if (checkOri) { const int bin = rot_bin(angA[idxA], angB[idxB]); binOf[idxA] = (u8)bin; atomicAdd(&gState[bin], 1); }
                 }
                 ++accepted;
                 __syncwarp();
             }
         }
     }
-    if (lane == 0 && accepted) atomicAdd(&sCount, accepted);
+    if (lane == 0 && accepted) atomicAdd(&gState[32], accepted);
+    __threadfence();
     __syncthreads();
+    if (tid == 0) sLast = atomicAdd(&gState[33], 1) == (int)gridDim.y - 2;        // tickets run -1, 0, 1, ...
+    __syncthreads();
+    if (!sLast) return;
+    __threadfence();
+    volatile int* vs = gState;
     if (checkOri) {
-        if (tid == 0) { int i1, i2, i3; three_maxima(sHist, ORBX_HISTO_LENGTH, i1, i2, i3); sInd[0] = i1; sInd[1] = i2; sInd[2] = i3; }
+        if (tid == 0) {
+            int h[ORBX_HISTO_LENGTH];
+            for (int i = 0; i < ORBX_HISTO_LENGTH; ++i) h[i] = vs[i] + 1;
+            int i1, i2, i3; three_maxima(h, ORBX_HISTO_LENGTH, i1, i2, i3); sInd[0] = i1; sInd[1] = i2; sInd[2] = i3;
+        }
         __syncthreads();
         int culled = 0;
+        volatile u8* vb = binOf;
+        volatile int32_t* vmA = matchA;
         for (int i = tid; i < P.nA; i += BOW_THREADS) {
-            const int b = binOf[i];
-            if (b != 0xff && b != sInd[0] && b != sInd[1] && b != sInd[2]) { matchB[matchA[i]] = -1; matchA[i] = -1; ++culled; }
+            const int b = vb[i];
+            if (b != 0xff && b != sInd[0] && b != sInd[1] && b != sInd[2]) { matchB[vmA[i]] = -1; matchA[i] = -1; ++culled; }
         }
-        if (culled) atomicSub(&sCount, culled);
+        if (culled) atomicSub(&gState[32], culled);
         __syncthreads();
     }
-    if (tid == 0) nmatchesOut[blockIdx.x] = sCount;
+    if (tid == 0) nmatchesOut[blockIdx.x] = vs[32] + 1;
 }
 
 // K18: one CTA per map point.  Thread i owns row i of the N x N distance matrix and finds its median
@@ -266,6 +279,7 @@ int orbm_bow_transform(orbm_vocab_handle* v, const uint8_t* features, int n, int
     if (n <= 0) return ORBX_OK;
     ORBX_CUDA(cudaSetDevice(v->device));
     CallArena ar;
+    { static double acc[PhaseTrace::MAXP]; static int calls = 0; ar.trace("bow_transform", acc, &calls); }
     const int sF = ar.in(features, (size_t)n * 32);
     const int sWt = ar.out(weight, (size_t)n * 8), sW = ar.out(word_id, (size_t)n * 4), sN = ar.out(node_id, (size_t)n * 4);
     int rc = ar.commit(); if (rc) return rc;
@@ -296,7 +310,7 @@ int orbm_search_by_bow(int variant, const orbm_bow_frame* a, const orbm_bow_fram
     }
     int capA = 1; while (capA < maxA) capA <<= 1;
     int capB = 1; while (capB < maxB) capB <<= 1;
-    const size_t smem = (size_t)(capA + capB) * 8 + (size_t)capA * 2 + capB + capA + 16;
+    const size_t smem = (size_t)(capA + capB) * 8 + capB + 16;
     if (smem > 220 * 1024) { orbx_set_error("frames of %d / %d features exceed the shared-memory sort (%zu bytes)", maxA, maxB, smem); return ORBX_E_CAPACITY; }
     for (int p = 0; p < npairs; ++p) {
         if (pairs[p].nA && (!a[p].descriptors || !a[p].angles || !a[p].node_id || !a[p].flags)) { orbx_set_error("pair %d: null array in a", p); return ORBX_E_INVALID; }
@@ -304,10 +318,12 @@ int orbm_search_by_bow(int variant, const orbm_bow_frame* a, const orbm_bow_fram
     }
     // one staged upload, one download (CallArena): the pairs' arrays are concatenated in the staging buffer
     CallArena ar;
+    { static double acc[PhaseTrace::MAXP]; static int calls = 0; ar.trace("search_by_bow", acc, &calls); }
     const int sPairs = ar.in(pairs.data(), npairs * sizeof(BowPair));
     const int sDescA = ar.in(nullptr, (size_t)totA * 32), sAngA = ar.in(nullptr, (size_t)totA * 4), sNodeA = ar.in(nullptr, (size_t)totA * 4), sFlagA = ar.in(nullptr, (size_t)totA);
     const int sDescB = ar.in(nullptr, (size_t)totB * 32), sAngB = ar.in(nullptr, (size_t)totB * 4), sNodeB = ar.in(nullptr, (size_t)totB * 4), sFlagB = ar.in(nullptr, (size_t)totB);
     const int sMA = ar.out(match_a, (size_t)totA * 4), sMB = ar.out(match_b, (size_t)totB * 4), sNM = ar.out(nmatches, (size_t)npairs * 4);
+    const int sBin = ar.work((size_t)totA), sState = ar.work((size_t)npairs * BOW_STATE_INTS * 4);
     int rc = ar.layout(); if (rc) return rc;
     for (int p = 0; p < npairs; ++p) {
         const BowPair& P = pairs[p];
@@ -325,10 +341,15 @@ int orbm_search_by_bow(int variant, const orbm_bow_frame* a, const orbm_bow_fram
         }
     }
     rc = ar.upload(); if (rc) return rc;
+    // outputs, bins and pair state are consecutive in the arena: one fill presets them (see the kernel's header)
+    ORBX_CUDA(cudaMemsetAsync(ar.dev<u8>(sMA), 0xff, (size_t)(ar.dev<u8>(sState) - ar.dev<u8>(sMA)) + (size_t)npairs * BOW_STATE_INTS * 4, 0));
     if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(search_bow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    search_bow_kernel<<<npairs, BOW_THREADS, smem>>>(variant, ar.dev<BowPair>(sPairs), ar.dev<u8>(sDescA), ar.dev<float>(sAngA), ar.dev<uint32_t>(sNodeA),
+    // a batch fills the GPU with one CTA per pair; the single pair of a per-frame call is spread over up to 32 SMs
+    const int splits = npairs >= 64 ? 1 : std::max(1, std::min(32, std::min(128 / npairs, (maxA + 63) / 64)));
+    search_bow_kernel<<<dim3(npairs, splits), BOW_THREADS, smem>>>(variant, ar.dev<BowPair>(sPairs), ar.dev<u8>(sDescA), ar.dev<float>(sAngA), ar.dev<uint32_t>(sNodeA),
                                                      ar.dev<u8>(sFlagA), ar.dev<u8>(sDescB), ar.dev<float>(sAngB), ar.dev<uint32_t>(sNodeB), ar.dev<u8>(sFlagB),
-                                                     nnratio, check_orientation, capA, capB, ar.dev<int32_t>(sMA), ar.dev<int32_t>(sMB), ar.dev<int32_t>(sNM));
+                                                     nnratio, check_orientation, capA, capB, ar.dev<int32_t>(sMA), ar.dev<int32_t>(sMB), ar.dev<int32_t>(sNM),
+                                                     ar.dev<u8>(sBin), ar.dev<int>(sState));
     return ar.finish();
 }
 
@@ -352,6 +373,7 @@ int orbm_distinctive_descriptors(const uint8_t* descriptors, const int32_t* offs
     std::vector<int32_t> rel(npoints + 1);
     for (int p = 0; p <= npoints; ++p) rel[p] = offsets[p] - offsets[0];
     CallArena ar;
+    { static double acc[PhaseTrace::MAXP]; static int calls = 0; ar.trace("distinctive_descriptors", acc, &calls); }
     const int sDesc = ar.in(total ? descriptors + (size_t)offsets[0] * 32 : nullptr, total * 32), sOff = ar.in(rel.data(), (size_t)(npoints + 1) * 4);
     const int sIdx = ar.out(best_idx, (size_t)npoints * 4), sMed = ar.out(best_median, (size_t)npoints * 4);
     int rc = ar.commit(); if (rc) return rc;

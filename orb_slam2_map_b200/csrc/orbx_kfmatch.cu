@@ -73,6 +73,62 @@ area_best_kernel(AreaBestArgs A, const orbm_proj_query* __restrict__ queries, co
     }
 }
 
+// K20, latency form (keyframes of at most AB_SWEEP_MAXN keypoints, the per-keyframe calls): no grid.  The lanes of a warp sweep
+// the keyframe's keypoints (coalesced, no dependent loads) with the window test AND the cell-window test of
+// KeyFrame::GetFeaturesInArea (a keypoint counts only if the cell it is filed under lies in the query's cell window); ties
+// between equal distances go to the first candidate in the grid's enumeration order = the smallest (cell, index).  Up to two
+// legs (SearchBySim3 searches KF1's points in KF2 and KF2's in KF1) share one launch: blockIdx.y picks the leg.
+#define AB_SWEEP_MAXN 4096
+struct AreaSweepLeg {
+    AreaBestArgs A;
+    const orbm_proj_query* queries; const u8* qdesc; int nq, n;
+    int* bestIdx; int* bestDist;
+};
+struct AreaSweepLegs { AreaSweepLeg leg[2]; };
+
+__global__ void __launch_bounds__(AB_WARPS * 32)
+area_best_sweep_kernel(AreaSweepLegs L)
+{
+    const AreaSweepLeg& G = L.leg[blockIdx.y];
+    const AreaBestArgs& A = G.A;
+    const int lane = threadIdx.x & 31, q = blockIdx.x * AB_WARPS + (threadIdx.x >> 5);
+    if (q >= G.nq) return;
+    const orbx_keypoint* kps = A.fs.kps;
+    const orbm_proj_query Q = G.queries[q];
+    unsigned long long best = ~0ull;
+    int cx0, cx1, cy0, cy1;
+    if (area_cells(A.gp, Q.u, Q.v, Q.radius, cx0, cx1, cy0, cy1)) {
+        uint32_t qd[8];
+        load_desc(qd, G.qdesc + (size_t)q * 32);
+        for (int i = lane; i < G.n; i += 32) {
+            const float kx = kps[i].x, ky = kps[i].y;
+            if (!(fabsf(__fsub_rn(kx, Q.u)) < Q.radius && fabsf(__fsub_rn(ky, Q.v)) < Q.radius)) continue;
+            const int oct = kps[i].octave;
+            if (oct < Q.level_hi - 1 || oct > Q.level_hi) continue;
+            const int px = (int)roundf(__fmul_rn(__fsub_rn(kx, A.gp.minX), A.gp.invW));
+            const int py = (int)roundf(__fmul_rn(__fsub_rn(ky, A.gp.minY), A.gp.invH));
+            if (px < cx0 || px > cx1 || py < cy0 || py > cy1) continue;           // the cell window lies inside the grid
+            if (A.variant == ORBM_FUSE_MAPPOINTS) {
+                const float kpr = A.uRight ? A.uRight[i] : -1.f;
+                const float ex = __fsub_rn(Q.u, kx), ey = __fsub_rn(Q.v, ky);
+                float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                double lim = 5.99;
+                if (kpr >= 0) { const float er = __fsub_rn(Q.u_right, kpr); e2 = __fadd_rn(e2, __fmul_rn(er, er)); lim = 7.8; }
+                if ((double)__fmul_rn(e2, A.invSigma2[oct]) > lim) continue;
+            }
+            const int dist = hamming256(qd, reinterpret_cast<const uint32_t*>(A.fs.desc + (size_t)i * 32));
+            const unsigned long long key = ((unsigned long long)dist << 32) | ((unsigned long long)(px * ORBX_GRID_ROWS + py) << 16) | (unsigned long long)i;
+            best = key < best ? key : best;
+        }
+    }
+    for (int d = 16; d > 0; d >>= 1) { const unsigned long long o = __shfl_xor_sync(FULL, best, d); best = o < best ? o : best; }
+    if (lane == 0) {
+        const int dist = best == ~0ull ? 256 : (int)(best >> 32);
+        G.bestDist[q] = dist;
+        G.bestIdx[q] = (best != ~0ull && dist <= A.thDist) ? (int)(best & 0xffff) : -1;
+    }
+}
+
 // vnMatch1 / vnMatch2 scatter + agreement.  One CTA.
 __global__ void sim3_agree_kernel(const int* __restrict__ best12, const int* __restrict__ index1, int nq12,
                                   const int* __restrict__ best21, const int* __restrict__ index2, int nq21, int n1, int n2,
@@ -121,46 +177,47 @@ __device__ void tri_bitonic_sort64(unsigned long long* a, int cap)
         }
 }
 
+// gridDim = (pairs, splits): the features of KF1 are independent of each other (the reference keeps no "already matched" state
+// on the KF2 side of this search that a later feature reads), so a pair's KF1 features are split over `splits` CTAs -- one for
+// a batch, many for the single pair of a per-keyframe call.  Every CTA sorts KF2's (node, index) keys for itself; the rotation
+// histogram, the count and a ticket live in global memory (pairState: 64 ints per pair, zeroed by the host) and the CTA that
+// draws the last ticket applies ComputeThreeMaxima to the whole pair.
+#define TRI_STATE_INTS 64
 __global__ void __launch_bounds__(TRI_THREADS)
 triangulation_kernel(const TriPair* __restrict__ pairs, const orbx_keypoint* __restrict__ kpA, const u8* __restrict__ descA,
                      const uint32_t* __restrict__ nodeA, const u8* __restrict__ flagA, const float* __restrict__ urA,
                      const orbx_keypoint* __restrict__ kpB, const u8* __restrict__ descB, const uint32_t* __restrict__ nodeB,
-                     const u8* __restrict__ flagB, const float* __restrict__ urB, int onlyStereo, int checkOri, int capA,
-                     int capB, int32_t* __restrict__ matches12, int32_t* __restrict__ nmatchesOut)
+                     const u8* __restrict__ flagB, const float* __restrict__ urB, int onlyStereo, int checkOri,
+                     int capB, int32_t* __restrict__ matches12, int32_t* __restrict__ nmatchesOut, u8* __restrict__ binOfAll,
+                     int* __restrict__ pairState)
 {
     extern __shared__ __align__(16) unsigned char smraw[];
-    __shared__ int sHist[ORBX_HISTO_LENGTH], sCount, sInd[3];
+    __shared__ int sInd[3], sLast;
     __shared__ TriPair P;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     if (tid < (int)(sizeof(TriPair) / 4)) reinterpret_cast<int*>(&P)[tid] = reinterpret_cast<const int*>(pairs + blockIdx.x)[tid];
-    if (tid < ORBX_HISTO_LENGTH) sHist[tid] = 0;
-    if (tid == 0) sCount = 0;
     __syncthreads();
-    unsigned long long* keysA = reinterpret_cast<unsigned long long*>(smraw);
-    unsigned long long* keysB = keysA + capA;
-    u8* binOf = reinterpret_cast<u8*>(keysB + capB);
+    unsigned long long* keysB = reinterpret_cast<unsigned long long*>(smraw);
+    int* gHist = pairState + (size_t)blockIdx.x * TRI_STATE_INTS;         // [0..29] histogram, [32] count, [33] ticket
+    u8* binOf = binOfAll + P.offA;
     kpA += P.offA; descA += (size_t)P.offA * 32; nodeA += P.offA; flagA += P.offA; urA += P.offA; matches12 += P.offA;
     kpB += P.offB; descB += (size_t)P.offB * 32; nodeB += P.offB; flagB += P.offB; urB += P.offB;
-    int pa = 1; while (pa < P.nA) pa <<= 1;
     int pb = 1; while (pb < P.nB) pb <<= 1;
-    // A: only the features the loop does not skip (:699-707); B: every FeatureVector entry (skips are per candidate)
-    for (int i = tid; i < pa; i += TRI_THREADS) {
-        bool use = i < P.nA && (flagA[i] & 1) && !(flagA[i] & 2);
-        if (use && onlyStereo && !(urA[i] >= 0)) use = false;
-        keysA[i] = use ? (((unsigned long long)nodeA[i] << 32) | (unsigned)i) : ~0ull;
-    }
+    const int perSplit = (P.nA + (int)gridDim.y - 1) / (int)gridDim.y;
+    const int aBeg = min(P.nA, (int)blockIdx.y * perSplit), aEnd = min(P.nA, aBeg + perSplit);
+    // B: every FeatureVector entry (skips are per candidate)
     for (int i = tid; i < pb; i += TRI_THREADS)
         keysB[i] = (i < P.nB && (flagB[i] & 1)) ? (((unsigned long long)nodeB[i] << 32) | (unsigned)i) : ~0ull;
-    for (int i = tid; i < P.nA; i += TRI_THREADS) { matches12[i] = -1; binOf[i] = 0xff; }
+    for (int i = aBeg + tid; i < aEnd; i += TRI_THREADS) { matches12[i] = -1; binOf[i] = 0xff; }
     __syncthreads();
-    tri_bitonic_sort64(keysA, pa);
     tri_bitonic_sort64(keysB, pb);
     int accepted = 0;
-    for (int ia = wid; ia < pa; ia += TRI_THREADS / 32) {
-        const unsigned long long kA = keysA[ia];
-        if (kA == ~0ull) break;                                    // sorted: the unused entries are at the end
-        const unsigned node = (unsigned)(kA >> 32);
-        const int idx1 = (int)(kA & 0xffffffffu);
+    for (int idx1 = aBeg + wid; idx1 < aEnd; idx1 += TRI_THREADS / 32) {
+        // A: only the features the loop does not skip (:699-707)
+        bool use = (flagA[idx1] & 1) && !(flagA[idx1] & 2);
+        if (use && onlyStereo && !(urA[idx1] >= 0)) use = false;
+        if (!use) continue;
+        const unsigned node = nodeA[idx1];
         int lo = 0, hi = pb;
         const unsigned long long target = (unsigned long long)node << 32;
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (keysB[mid] < target) lo = mid + 1; else hi = mid; }
@@ -204,25 +261,36 @@ triangulation_kernel(const TriPair* __restrict__ pairs, const orbx_keypoint* __r
             const int idx2 = (int)(keysB[lo + (0xffff - (int)(best & 0xffff))] & 0xffffffffu);
             if (lane == 0) {
                 matches12[idx1] = idx2;
-                if (checkOri) { const int bin = rot_bin(kp1.angle, kpB[idx2].angle); binOf[idx1] = (u8)bin; atomicAdd(&sHist[bin], 1); }
+                if (checkOri) { const int bin = rot_bin(kp1.angle, kpB[idx2].angle); binOf[idx1] = (u8)bin; atomicAdd(&gHist[bin], 1); }
             }
             ++accepted;
         }
     }
-    if (lane == 0) atomicAdd(&sCount, accepted);
+    if (lane == 0 && accepted) atomicAdd(&gHist[32], accepted);
+    __threadfence();
     __syncthreads();
+    if (tid == 0) sLast = atomicAdd(&gHist[33], 1) == (int)gridDim.y - 1;
+    __syncthreads();
+    if (!sLast) return;
+    __threadfence();
+    volatile int* vh = gHist;
     if (checkOri) {
-        if (tid == 0) { int i1, i2, i3; three_maxima(sHist, ORBX_HISTO_LENGTH, i1, i2, i3); sInd[0] = i1; sInd[1] = i2; sInd[2] = i3; }
+        if (tid == 0) {
+            int h[ORBX_HISTO_LENGTH];
+            for (int i = 0; i < ORBX_HISTO_LENGTH; ++i) h[i] = vh[i];
+            int i1, i2, i3; three_maxima(h, ORBX_HISTO_LENGTH, i1, i2, i3); sInd[0] = i1; sInd[1] = i2; sInd[2] = i3;
+        }
         __syncthreads();
         int culled = 0;
+        volatile u8* vb = binOf;
         for (int i = tid; i < P.nA; i += TRI_THREADS) {
-            const int bnum = binOf[i];
+            const int bnum = vb[i];
             if (bnum != 0xff && bnum != sInd[0] && bnum != sInd[1] && bnum != sInd[2]) { matches12[i] = -1; ++culled; }
         }
-        if (culled) atomicSub(&sCount, culled);
+        if (culled) atomicSub(&gHist[32], culled);
         __syncthreads();
     }
-    if (tid == 0) nmatchesOut[blockIdx.x] = sCount;
+    if (tid == 0) nmatchesOut[blockIdx.x] = vh[32];
 }
 
 // ---- host side -------------------------------------------------------------------------------------------------
@@ -263,14 +331,15 @@ struct ArenaKeyFrame {
         sGI = ar.work(cap * sizeof(unsigned short));
         return ORBX_OK;
     }
-    int ready(CallArena& ar, const orbm_keyframe* kf, int variant, AreaBestArgs& args)
+    bool sweep() const { return n <= AB_SWEEP_MAXN; }       // the latency form needs no grid
+    int ready(CallArena& ar, const orbm_keyframe* kf, int variant, AreaBestArgs& args, bool needGrid)
     {
         const orbm_frame* f = &kf->frame;
         FrameStore fs;
         fs.kps = ar.dev<orbx_keypoint>(sKps); fs.desc = ar.dev<u8>(sDesc); fs.count = ar.dev<int>(sCount);
         fs.gridStart = ar.dev<unsigned short>(sGS); fs.gridIdx = ar.dev<unsigned short>(sGI); fs.cap = std::max(n, 8);
         args.gp = orbx_grid_params(f->min_x, f->max_x, f->min_y, f->max_y);
-        const int rc = orbx_launch_grid_build(fs, 0, 1, args.gp, 0); if (rc) return rc;
+        if (needGrid) { const int rc = orbx_launch_grid_build(fs, 0, 1, args.gp, 0); if (rc) return rc; }
         args.fs = fs;
         args.uRight = sUR >= 0 ? ar.dev<float>(sUR) : nullptr;
         args.variant = variant;
@@ -296,7 +365,22 @@ struct ArenaQueries {
         if (nq > 0)
             area_best_kernel<<<(nq + AB_WARPS - 1) / AB_WARPS, AB_WARPS * 32>>>(a, ar.dev<orbm_proj_query>(sQ), ar.dev<u8>(sD), nq, ar.dev<int>(sBI), ar.dev<int>(sBD));
     }
+    AreaSweepLeg leg(CallArena& ar, const AreaBestArgs& a, int nq, int n)
+    {
+        AreaSweepLeg g;
+        g.A = a; g.queries = ar.dev<orbm_proj_query>(sQ); g.qdesc = ar.dev<u8>(sD); g.nq = nq; g.n = n;
+        g.bestIdx = ar.dev<int>(sBI); g.bestDist = ar.dev<int>(sBD);
+        return g;
+    }
 };
+
+static void launch_area_sweep(const AreaSweepLeg& g0, const AreaSweepLeg* g1)
+{
+    AreaSweepLegs L;
+    L.leg[0] = g0; L.leg[1] = g1 ? *g1 : g0;
+    const int nq = std::max(g0.nq, g1 ? g1->nq : 0);
+    if (nq > 0) area_best_sweep_kernel<<<dim3((nq + AB_WARPS - 1) / AB_WARPS, g1 ? 2 : 1), AB_WARPS * 32>>>(L);
+}
 
 extern "C" {
 
@@ -310,14 +394,16 @@ int orbm_fuse(int variant, const orbm_keyframe* kf, const orbm_proj_query* queri
     if (nq == 0) return ORBX_OK;
     rc = kf_device(device); if (rc) return rc;
     CallArena ar;
+    { static double acc[PhaseTrace::MAXP]; static int calls = 0; ar.trace("fuse", acc, &calls); }
     ArenaKeyFrame dk;
     ArenaQueries dq;
     rc = dk.declare(ar, kf, variant); if (rc) return rc;
     dq.declare(ar, queries, query_desc, nq, best_idx, best_dist);
     rc = ar.commit(); if (rc) return rc;
     AreaBestArgs args;
-    rc = dk.ready(ar, kf, variant, args); if (rc) return rc;
-    dq.launch(ar, args, nq);
+    rc = dk.ready(ar, kf, variant, args, !dk.sweep()); if (rc) return rc;
+    if (dk.sweep()) launch_area_sweep(dq.leg(ar, args, nq, dk.n), nullptr);
+    else dq.launch(ar, args, nq);
     return ar.finish();
 }
 
@@ -336,6 +422,7 @@ int orbm_search_by_sim3(const orbm_keyframe* kf1, const orbm_keyframe* kf2, cons
     for (int q = 0; q < nq21; ++q) if (index2[q] < 0 || index2[q] >= n2) { orbx_set_error("index2[%d] out of range", q); return ORBX_E_INVALID; }
     rc = kf_device(device); if (rc) return rc;
     CallArena ar;
+    { static double acc[PhaseTrace::MAXP]; static int calls = 0; ar.trace("search_by_sim3", acc, &calls); }
     ArenaKeyFrame d1, d2;
     ArenaQueries q12, q21;
     rc = d1.declare(ar, kf1, ORBM_FUSE_SIM3_LEG); if (rc) return rc;
@@ -348,10 +435,16 @@ int orbm_search_by_sim3(const orbm_keyframe* kf1, const orbm_keyframe* kf2, cons
     const int sM1 = ar.work((size_t)n1 * 4), sM2 = ar.work((size_t)n2 * 4);
     rc = ar.commit(); if (rc) return rc;
     AreaBestArgs a1, a2;
-    rc = d1.ready(ar, kf1, ORBM_FUSE_SIM3_LEG, a1); if (rc) return rc;
-    rc = d2.ready(ar, kf2, ORBM_FUSE_SIM3_LEG, a2); if (rc) return rc;
-    q12.launch(ar, a2, nq12);                 // points of KF1 searched in KF2
-    q21.launch(ar, a1, nq21);
+    const bool sweep = d1.sweep() && d2.sweep();
+    rc = d1.ready(ar, kf1, ORBM_FUSE_SIM3_LEG, a1, !sweep); if (rc) return rc;
+    rc = d2.ready(ar, kf2, ORBM_FUSE_SIM3_LEG, a2, !sweep); if (rc) return rc;
+    if (sweep) {
+        const AreaSweepLeg g12 = q12.leg(ar, a2, nq12, d2.n), g21 = q21.leg(ar, a1, nq21, d1.n);   // points of KF1 searched in KF2 and back, one launch
+        launch_area_sweep(g12, &g21);
+    } else {
+        q12.launch(ar, a2, nq12);
+        q21.launch(ar, a1, nq21);
+    }
     sim3_agree_kernel<<<1, 256>>>(ar.dev<int>(q12.sBI), ar.dev<int>(sI1), nq12, ar.dev<int>(q21.sBI), ar.dev<int>(sI2), nq21, n1, n2,
                                   ar.dev<int>(sM1), ar.dev<int>(sM2), ar.dev<int>(sM12), ar.dev<int>(sNf));
     rc = ar.finish(); if (rc) return rc;
@@ -388,18 +481,19 @@ int orbm_search_for_triangulation(const orbm_keyframe* kf1, const orbm_keyframe*
         totA += A.n; totB += B.n;
         maxA = std::max(maxA, A.n); maxB = std::max(maxB, B.n);
     }
-    int capA = 1; while (capA < maxA) capA <<= 1;
     int capB = 1; while (capB < maxB) capB <<= 1;
-    const size_t smem = (size_t)(capA + capB) * 8 + capA + 16;
+    const size_t smem = (size_t)capB * 8 + 16;
     if (smem > 220 * 1024) { orbx_set_error("keyframes of %d / %d features exceed the shared-memory sort (%zu bytes)", maxA, maxB, smem); return ORBX_E_CAPACITY; }
     int rc = kf_device(device); if (rc) return rc;
     CallArena ar;
+    { static double acc[PhaseTrace::MAXP]; static int calls = 0; ar.trace("search_for_triangulation", acc, &calls); }
     const int sPairs = ar.in(pairs.data(), npairs * sizeof(TriPair));
     const int sKA = ar.in(nullptr, (size_t)totA * sizeof(orbx_keypoint)), sDA = ar.in(nullptr, (size_t)totA * 32), sNA = ar.in(nullptr, (size_t)totA * 4),
               sFA = ar.in(nullptr, (size_t)totA), sUA = ar.in(nullptr, (size_t)totA * 4);
     const int sKB = ar.in(nullptr, (size_t)totB * sizeof(orbx_keypoint)), sDB = ar.in(nullptr, (size_t)totB * 32), sNB = ar.in(nullptr, (size_t)totB * 4),
               sFB = ar.in(nullptr, (size_t)totB), sUB = ar.in(nullptr, (size_t)totB * 4);
     const int sM = ar.out(matches12, (size_t)totA * 4), sNM = ar.out(nmatches, (size_t)npairs * 4);
+    const int sBin = ar.work((size_t)totA), sState = ar.work((size_t)npairs * TRI_STATE_INTS * 4);
     rc = ar.layout(); if (rc) return rc;
     auto up = [&](const orbm_keyframe& kf, int off, int k, int d, int nd, int fl, int ur) {
         const orbm_frame& f = kf.frame;
@@ -417,11 +511,14 @@ int orbm_search_for_triangulation(const orbm_keyframe* kf1, const orbm_keyframe*
         up(kf2[p], pairs[p].offB, sKB, sDB, sNB, sFB, sUB);
     }
     rc = ar.upload(); if (rc) return rc;
+    ORBX_CUDA(cudaMemsetAsync(ar.dev<int>(sState), 0, (size_t)npairs * TRI_STATE_INTS * 4, 0));
     if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(triangulation_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    triangulation_kernel<<<npairs, TRI_THREADS, smem>>>(ar.dev<TriPair>(sPairs), ar.dev<orbx_keypoint>(sKA), ar.dev<u8>(sDA), ar.dev<uint32_t>(sNA),
+    // a batch fills the GPU with one CTA per pair; the single pair of a per-keyframe call is spread over up to 64 SMs
+    const int splits = npairs >= 64 ? 1 : std::max(1, std::min(64, std::min(128 / npairs, (maxA + 31) / 32)));
+    triangulation_kernel<<<dim3(npairs, splits), TRI_THREADS, smem>>>(ar.dev<TriPair>(sPairs), ar.dev<orbx_keypoint>(sKA), ar.dev<u8>(sDA), ar.dev<uint32_t>(sNA),
                                                         ar.dev<u8>(sFA), ar.dev<float>(sUA), ar.dev<orbx_keypoint>(sKB), ar.dev<u8>(sDB),
                                                         ar.dev<uint32_t>(sNB), ar.dev<u8>(sFB), ar.dev<float>(sUB), only_stereo, check_orientation,
-                                                        capA, capB, ar.dev<int32_t>(sM), ar.dev<int32_t>(sNM));
+                                                        capB, ar.dev<int32_t>(sM), ar.dev<int32_t>(sNM), ar.dev<u8>(sBin), ar.dev<int>(sState));
     return ar.finish();
 }
 

@@ -1442,25 +1442,6 @@ int orbm_descriptor_distance(const uint8_t* a, const uint8_t* b, int count, int3
     return ORBX_OK;
 }
 
-// ORBX_LAT_TRACE=1: device-side phase times of the stateless calls (events on the legacy stream), averaged over 50 calls, to stderr
-struct PhaseTrace {
-    static const int MAXP = 8;
-    bool on; int np; cudaEvent_t ev[MAXP]; const char* tag[MAXP];
-    explicit PhaseTrace(bool enable) : on(enable), np(0) {}
-    void mark(const char* t) { if (!on || np >= MAXP) return; cudaEventCreate(&ev[np]); cudaEventRecord(ev[np], 0); tag[np++] = t; }
-    void report(const char* name, double* acc, int& calls) {
-        if (!on) return;
-        for (int i = 1; i < np; ++i) { float ms = 0; cudaEventElapsedTime(&ms, ev[i - 1], ev[i]); acc[i] += ms * 1000.0; }
-        for (int i = 0; i < np; ++i) cudaEventDestroy(ev[i]);
-        if (++calls % 50 == 0) {
-            fprintf(stderr, "[orbx lat] %s:", name);
-            for (int i = 1; i < np; ++i) { fprintf(stderr, " %s %.1f us", tag[i], acc[i] / 50.0); acc[i] = 0; }
-            fprintf(stderr, "\n");
-        }
-    }
-};
-static bool lat_trace_on() { static const bool on = getenv("ORBX_LAT_TRACE") != nullptr; return on; }
-
 int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, float* prev_matched,
                                    int32_t* matches12, int window_size, float nnratio,
                                    int check_orientation, int32_t* nmatches)
@@ -1496,7 +1477,7 @@ int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, f
         memcpy(host + oKps + cap * sizeof(orbx_keypoint), f2->keys_un, (size_t)f2->n * sizeof(orbx_keypoint));
         memcpy(host + oDesc + cap * 32, f2->descriptors, (size_t)f2->n * 32);
     }
-    PhaseTrace pt(lat_trace_on());
+    PhaseTrace pt(orbx_lat_trace_on());
     pt.mark("start");
     ORBX_CUDA(cudaMemcpyAsync(dev, host, upBytes, cudaMemcpyHostToDevice, 0));
     pt.mark("h2d");
@@ -1572,7 +1553,7 @@ int orbm_search_by_projection(int variant, const orbm_frame* frame, const orbm_p
         memcpy(host + oQD, query_desc, (size_t)nq * 32);
         if (query_blocks) memcpy(host + oQB, query_blocks, (size_t)nq);
     }
-    PhaseTrace pt(lat_trace_on());
+    PhaseTrace pt(orbx_lat_trace_on());
     pt.mark("start");
     ORBX_CUDA(cudaMemcpyAsync(dev, host, upBytes, cudaMemcpyHostToDevice, 0));
     pt.mark("h2d");
@@ -1663,6 +1644,7 @@ int orbm_compute_stereo_matches(const orbm_stereo_input* in, float* u_right, flo
     const int cap = std::max(std::max(in->n_left, in->n_right), 8);
     const int counts[2] = {in->n_left, in->n_right};
     CallArena ar;
+    { static double acc[PhaseTrace::MAXP]; static int calls = 0; ar.trace("compute_stereo_matches", acc, &calls); }
     const int sCount = ar.in(counts, 8), sKps = ar.in(nullptr, (size_t)2 * cap * sizeof(orbx_keypoint)), sDesc = ar.in(nullptr, (size_t)2 * cap * 32);
     int sLv[2][ORBX_MAX_LEVELS];
     for (int l = 0; l < in->nlevels; ++l)

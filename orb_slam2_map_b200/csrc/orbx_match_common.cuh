@@ -5,6 +5,8 @@
 
 #include "orbx_internal.h"
 #include <vector>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 typedef uint8_t u8;
@@ -101,6 +103,25 @@ struct DevBuf {
     template <typename T> T* as() { return (T*)p; }
 };
 
+// ORBX_LAT_TRACE=1: device-side phase times of the stateless calls (events on the legacy stream), averaged over 50 calls, to stderr
+struct PhaseTrace {
+    static const int MAXP = 8;
+    bool on; int np; cudaEvent_t ev[MAXP]; const char* tag[MAXP];
+    explicit PhaseTrace(bool enable) : on(enable), np(0) {}
+    void mark(const char* t) { if (!on || np >= MAXP) return; cudaEventCreate(&ev[np]); cudaEventRecord(ev[np], 0); tag[np++] = t; }
+    void report(const char* name, double* acc, int& calls) {
+        if (!on) return;
+        for (int i = 1; i < np; ++i) { float ms = 0; cudaEventElapsedTime(&ms, ev[i - 1], ev[i]); acc[i] += ms * 1000.0; }
+        for (int i = 0; i < np; ++i) cudaEventDestroy(ev[i]);
+        if (++calls % 50 == 0) {
+            fprintf(stderr, "[orbx lat] %s:", name);
+            for (int i = 1; i < np; ++i) { fprintf(stderr, " %s %.1f us", tag[i], acc[i] / 50.0); acc[i] = 0; }
+            fprintf(stderr, "\n");
+        }
+    }
+};
+inline bool orbx_lat_trace_on() { static const bool on = getenv("ORBX_LAT_TRACE") != nullptr; return on; }
+
 // One stateless call = one device arena + one page-locked staging buffer laid out [inputs][in/out][outputs][work]: everything the
 // call uploads goes up in ONE copy and everything it returns comes back in ONE copy (a dozen small synchronous copies of
 // pageable memory cost 10-20 us each, more than the kernels of a per-frame call).  Segments are declared first (in / inout /
@@ -110,6 +131,10 @@ struct CallArena {
     struct Seg { int kind; const void* src; void* dst; size_t bytes, off; };
     std::vector<Seg> segs;
     DevBuf arena;
+    PhaseTrace pt{orbx_lat_trace_on()};
+    const char* name = "call";          // static storage: keys the ORBX_LAT_TRACE accumulators
+    double* acc = nullptr; int* calls = nullptr;
+    void trace(const char* n, double* a, int* c) { name = n; acc = a; calls = c; }
     u8* host = nullptr; u8* device = nullptr;
     size_t upBytes = 0, downBegin = 0, downEnd = 0;
     int add(int kind, const void* src, void* dst, size_t bytes) { segs.push_back({kind, src, dst, bytes, 0}); return (int)segs.size() - 1; }
@@ -134,7 +159,9 @@ struct CallArena {
     int upload()
     {
         for (const Seg& s : segs) if (s.kind <= 1 && s.bytes && s.src) memcpy(host + s.off, s.src, s.bytes);
+        pt.mark("start");
         if (upBytes) ORBX_CUDA(cudaMemcpyAsync(device, host, upBytes, cudaMemcpyHostToDevice, 0));
+        pt.mark("h2d");
         return ORBX_OK;
     }
     int commit() { const int rc = layout(); return rc ? rc : upload(); }
@@ -143,8 +170,11 @@ struct CallArena {
     int finish()
     {
         ORBX_CUDA(cudaGetLastError());
+        pt.mark("kernels");
         if (downEnd > downBegin) ORBX_CUDA(cudaMemcpyAsync(host + downBegin, device + downBegin, downEnd - downBegin, cudaMemcpyDeviceToHost, 0));
+        pt.mark("d2h");
         ORBX_CUDA(cudaStreamSynchronize(0));
+        if (acc) pt.report(name, acc, *calls);
         for (const Seg& s : segs) if ((s.kind == 1 || s.kind == 2) && s.bytes && s.dst) memcpy(s.dst, host + s.off, s.bytes);
         return ORBX_OK;
     }

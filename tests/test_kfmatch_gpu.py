@@ -27,6 +27,16 @@ def test_fuse_variants(variant):
     assert total > 500
 
 
+def test_fuse_and_sim3_large_keyframes_take_the_grid_path():
+    """more than 4096 keypoints: K20 walks the grid (the latency form sweeps the keypoints instead)"""
+    kf, q, qd = make_fuse_case(5, n=5000, nq=2500)
+    for variant in (0, 1):
+        bo, do = O.fuse(variant, kf, q, qd)
+        bg, dg = capi.fuse(variant, _to_capi(kf), q, qd)
+        assert np.array_equal(bg, bo) and np.array_equal(dg, do)
+    assert (bg >= 0).sum() > 200
+
+
 def test_fuse_empty_and_mono_keyframe():
     kf, q, qd = make_fuse_case(77, n=300, nq=64)
     fd = kf.fd
