@@ -55,7 +55,7 @@ bow_transform_kernel(const int32_t* __restrict__ childBegin, const int32_t* __re
     if (lane == 0) { wordOut[f] = nodeWord[finalId]; weightOut[f] = nodeWeight[finalId]; nodeOut[f] = nid; }
 }
 
-#define BOW_THREADS 256
+#define BOW_THREADS 1024
 struct BowPair { int offA, nA, offB, nB; };
 
 __device__ void block_bitonic_sort64(unsigned long long* a, int cap)
@@ -107,8 +107,8 @@ search_bow_kernel(int variant, const BowPair* __restrict__ pairs, const u8* __re
         keysB[i] = (i < P.nB && (flagB[i] & 1)) ? (((unsigned long long)nodeB[i] << 32) | (unsigned)i) : ~0ull;
     for (int i = tid; i < P.nB; i += BOW_THREADS) matchedB[i] = 0;
     __syncthreads();
-    block_bitonic_sort64(keysA, pa);
-    block_bitonic_sort64(keysB, pb);
+    if (pa <= 4 * BOW_THREADS) block_sort64<BOW_THREADS>(keysA, pa); else block_bitonic_sort64(keysA, pa);
+    if (pb <= 4 * BOW_THREADS) block_sort64<BOW_THREADS>(keysB, pb); else block_bitonic_sort64(keysB, pb);
     int accepted = 0;
     const int warpsAll = (int)gridDim.y * (BOW_THREADS / 32);
     for (int a0 = (int)blockIdx.y * (BOW_THREADS / 32) + wid; a0 < P.nA; a0 += warpsAll) {
@@ -124,33 +124,76 @@ search_bow_kernel(int variant, const BowPair* __restrict__ pairs, const u8* __re
         int b1 = b0;
         while (b1 < pb && (unsigned)(keysB[b1] >> 32) == node && keysB[b1] != ~0ull) ++b1;      // runs are short (tens of features)
         if (b1 == b0) continue;
-        for (int ia = a0; ia < P.nA && keysA[ia] != ~0ull && (unsigned)(keysA[ia] >> 32) == node; ++ia) {
-            const int idxA = (int)(keysA[ia] & 0xffffffffu);
-            if (!(flagA[idxA] & 2)) continue;                     // !pMP || pMP->isBad()
-            uint32_t q[8];
-            load_desc(q, descA + (size_t)idxA * 32);
-            int best = 0x7fffffff, second = 0x7fffffff;
-            unsigned key = 0xffffffffu;
-            for (int jb = b0 + lane; jb < b1; jb += 32) {
-                const int idxB = (int)(keysB[jb] & 0xffffffffu);
-                if (matchedB[idxB]) continue;
-                if (variant == 1 && !(flagB[idxB] & 2)) continue;
-                const int dist = hamming256(q, reinterpret_cast<const uint32_t*>(descB + (size_t)idxB * 32));
-                if (dist < best) { second = best; best = dist; key = (unsigned)jb; }
-                else if (dist < second) second = dist;
+        const bool resident = b1 - b0 <= 32;                       // the usual case: lane j keeps B's j-th feature of the node in registers
+        uint32_t db[8];
+        int myB = -1;
+        bool freeB = false;
+        float myAngB = 0.f;
+        if (resident && b0 + lane < b1) {
+            myB = (int)(keysB[b0 + lane] & 0xffffffffu);
+            freeB = !(variant == 1 && !(flagB[myB] & 2));
+            load_desc(db, descB + (size_t)myB * 32);
+            if (checkOri) myAngB = angB[myB];
+        }
+        // end of A's run (the run's entries are a prefix of every 32-entry window)
+        int aEnd = a0;
+        for (;;) {
+            const int i = aEnd + lane;
+            const unsigned m = __ballot_sync(FULL, i < P.nA && keysA[i] != ~0ull && (unsigned)(keysA[i] >> 32) == node);
+            aEnd += __popc(m);
+            if (m != FULL) break;
+        }
+        // A's features of the node, 32 at a time: every lane fetches one feature (flags, angle, descriptor) so that the loads
+        // of a whole chunk fly together; the features are then replayed in index order from registers (shuffles)
+        for (int c0 = a0; c0 < aEnd; c0 += 32) {
+            const int cnt = min(32, aEnd - c0);
+            int myA = 0, myFlag = 0;
+            float myAngA = 0.f;
+            uint32_t da[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            if (lane < cnt) {
+                myA = (int)(keysA[c0 + lane] & 0xffffffffu);
+                myFlag = flagA[myA];
+                if (checkOri) myAngA = angA[myA];
+                load_desc(da, descA + (size_t)myA * 32);
             }
-            warp_top2(best, key, second);
-            best = min(best, 256); second = min(second, 256);     // bestDist1 = bestDist2 = 256 initially; a distance of 256 never wins
-            const bool found = best < 256;
-            const bool close = variant == 0 ? best <= ORBX_TH_LOW : best < ORBX_TH_LOW;
-            if (found && close && (float)best < __fmul_rn(nnratio, (float)second)) {
-                const int idxB = (int)(keysB[key] & 0xffffffffu);
-                if (lane == 0) {
-                    matchedB[idxB] = 1; matchA[idxA] = idxB; matchB[idxB] = idxA;
-                    if (checkOri) { const int bin = rot_bin(angA[idxA], angB[idxB]); binOf[idxA] = (u8)bin; atomicAdd(&gState[bin], 1); }
+            for (int t = 0; t < cnt; ++t) {
+                if (!(__shfl_sync(FULL, myFlag, t) & 2)) continue;        // !pMP || pMP->isBad()
+                const int idxA = __shfl_sync(FULL, myA, t);
+                uint32_t q[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) q[i] = __shfl_sync(FULL, da[i], t);
+                int best = 0x7fffffff, second = 0x7fffffff;
+                unsigned key = 0xffffffffu;
+                if (resident) {
+                    if (freeB) { best = hamming256_regs(q, db); key = (unsigned)(b0 + lane); }
+                } else {
+                    for (int jb = b0 + lane; jb < b1; jb += 32) {
+                        const int idxB = (int)(keysB[jb] & 0xffffffffu);
+                        if (matchedB[idxB]) continue;
+                        if (variant == 1 && !(flagB[idxB] & 2)) continue;
+                        const int dist = hamming256(q, reinterpret_cast<const uint32_t*>(descB + (size_t)idxB * 32));
+                        if (dist < best) { second = best; best = dist; key = (unsigned)jb; }
+                        else if (dist < second) second = dist;
+                    }
                 }
-                ++accepted;
-                __syncwarp();
+                warp_top2(best, key, second);
+                best = min(best, 256); second = min(second, 256);     // bestDist1 = bestDist2 = 256 initially; a distance of 256 never wins
+                const bool found = best < 256;
+                const bool close = variant == 0 ? best <= ORBX_TH_LOW : best < ORBX_TH_LOW;
+                if (found && close && (float)best < __fmul_rn(nnratio, (float)second)) {
+                    const int idxB = (int)(keysB[key] & 0xffffffffu);
+                    float aB = 0.f;
+                    if (checkOri) aB = resident ? __shfl_sync(FULL, myAngB, (int)key - b0) : angB[idxB];
+                    const float aA = __shfl_sync(FULL, myAngA, t);
+                    if (resident) { if ((int)key == b0 + lane) freeB = false; }
+                    if (lane == 0) {
+                        if (!resident) matchedB[idxB] = 1;
+                        matchA[idxA] = idxB; matchB[idxB] = idxA;
+                        if (checkOri) { const int bin = rot_bin(aA, aB); binOf[idxA] = (u8)bin; atomicAdd(&gState[bin], 1); }
+                    }
+                    ++accepted;
+                    __syncwarp();
+                }
             }
         }
     }
@@ -344,8 +387,8 @@ int orbm_search_by_bow(int variant, const orbm_bow_frame* a, const orbm_bow_fram
     // outputs, bins and pair state are consecutive in the arena: one fill presets them (see the kernel's header)
     ORBX_CUDA(cudaMemsetAsync(ar.dev<u8>(sMA), 0xff, (size_t)(ar.dev<u8>(sState) - ar.dev<u8>(sMA)) + (size_t)npairs * BOW_STATE_INTS * 4, 0));
     if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(search_bow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    // a batch fills the GPU with one CTA per pair; the single pair of a per-frame call is spread over up to 32 SMs
-    const int splits = npairs >= 64 ? 1 : std::max(1, std::min(32, std::min(128 / npairs, (maxA + 63) / 64)));
+    // a batch fills the GPU with one CTA per pair; the single pair of a per-frame call is spread over up to 8 SMs (32 warps each)
+    const int splits = npairs >= 64 ? 1 : std::max(1, std::min(8, std::min(128 / npairs, (maxA + 255) / 256)));
     search_bow_kernel<<<dim3(npairs, splits), BOW_THREADS, smem>>>(variant, ar.dev<BowPair>(sPairs), ar.dev<u8>(sDescA), ar.dev<float>(sAngA), ar.dev<uint32_t>(sNodeA),
                                                      ar.dev<u8>(sFlagA), ar.dev<u8>(sDescB), ar.dev<float>(sAngB), ar.dev<uint32_t>(sNodeB), ar.dev<u8>(sFlagB),
                                                      nnratio, check_orientation, capA, capB, ar.dev<int32_t>(sMA), ar.dev<int32_t>(sMB), ar.dev<int32_t>(sNM),

@@ -155,7 +155,7 @@ __global__ void sim3_agree_kernel(const int* __restrict__ best12, const int* __r
     if (threadIdx.x == 0) *nfound = cnt;
 }
 
-#define TRI_THREADS 256
+#define TRI_THREADS 1024
 struct TriPair {
     int offA, nA, offB, nB;
     float F[9], ex, ey;
@@ -210,7 +210,7 @@ triangulation_kernel(const TriPair* __restrict__ pairs, const orbx_keypoint* __r
         keysB[i] = (i < P.nB && (flagB[i] & 1)) ? (((unsigned long long)nodeB[i] << 32) | (unsigned)i) : ~0ull;
     for (int i = aBeg + tid; i < aEnd; i += TRI_THREADS) { matches12[i] = -1; binOf[i] = 0xff; }
     __syncthreads();
-    tri_bitonic_sort64(keysB, pb);
+    if (pb <= 4 * TRI_THREADS) block_sort64<TRI_THREADS>(keysB, pb); else tri_bitonic_sort64(keysB, pb);
     int accepted = 0;
     for (int idx1 = aBeg + wid; idx1 < aEnd; idx1 += TRI_THREADS / 32) {
         // A: only the features the loop does not skip (:699-707)
@@ -513,8 +513,8 @@ int orbm_search_for_triangulation(const orbm_keyframe* kf1, const orbm_keyframe*
     rc = ar.upload(); if (rc) return rc;
     ORBX_CUDA(cudaMemsetAsync(ar.dev<int>(sState), 0, (size_t)npairs * TRI_STATE_INTS * 4, 0));
     if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(triangulation_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    // a batch fills the GPU with one CTA per pair; the single pair of a per-keyframe call is spread over up to 64 SMs
-    const int splits = npairs >= 64 ? 1 : std::max(1, std::min(64, std::min(128 / npairs, (maxA + 31) / 32)));
+    // a batch fills the GPU with one CTA per pair; the single pair of a per-keyframe call is spread over up to 16 SMs (32 warps each)
+    const int splits = npairs >= 64 ? 1 : std::max(1, std::min(16, std::min(128 / npairs, (maxA + 127) / 128)));
     triangulation_kernel<<<dim3(npairs, splits), TRI_THREADS, smem>>>(ar.dev<TriPair>(sPairs), ar.dev<orbx_keypoint>(sKA), ar.dev<u8>(sDA), ar.dev<uint32_t>(sNA),
                                                         ar.dev<u8>(sFA), ar.dev<float>(sUA), ar.dev<orbx_keypoint>(sKB), ar.dev<u8>(sDB),
                                                         ar.dev<uint32_t>(sNB), ar.dev<u8>(sFB), ar.dev<float>(sUB), only_stereo, check_orientation,

@@ -19,10 +19,76 @@ __device__ __forceinline__ int hamming256(const uint32_t a[8], const uint32_t* _
            __popc(a[4] ^ b1.x) + __popc(a[5] ^ b1.y) + __popc(a[6] ^ b1.z) + __popc(a[7] ^ b1.w);
 }
 
+// both descriptors in registers
+__device__ __forceinline__ int hamming256_regs(const uint32_t a[8], const uint32_t b[8])
+{
+    int d = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) d += __popc(a[i] ^ b[i]);
+    return d;
+}
+
 __device__ __forceinline__ void load_desc(uint32_t a[8], const u8* __restrict__ p)
 {
     const uint4 v0 = *reinterpret_cast<const uint4*>(p), v1 = *reinterpret_cast<const uint4*>(p + 16);
     a[0] = v0.x; a[1] = v0.y; a[2] = v0.z; a[3] = v0.w; a[4] = v1.x; a[5] = v1.y; a[6] = v1.z; a[7] = v1.w;
+}
+
+// Ascending bitonic sort of cap (a power of two, <= 4 * NT) 64-bit keys in shared memory by a block of NT threads (NT a
+// multiple of 32, every thread of the block calls).  Thread t keeps elements t, t + NT, ... in registers: exchanges at
+// distances >= NT stay inside the thread, distances < 32 are warp shuffles, only the ones between go through shared memory --
+// 15 of the 55 steps of a 1024-key sort.  (The plain shared-memory version, a __syncthreads per step, measured 35 us for
+// 1024 keys; this one is the sort of the per-frame BoW / triangulation calls.)
+template <int NT>
+__device__ __forceinline__ void block_sort64(unsigned long long* a, int cap)
+{
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int E = cap > 2 * NT ? 4 : (cap > NT ? 2 : 1);
+    unsigned long long v[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) v[r] = (r < E && r * NT + tid < cap) ? a[r * NT + tid] : ~0ull;
+    for (int k = 2; k <= cap; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            if (j >= NT) {                                   // partners live in the same thread
+                auto cx = [&](unsigned long long& x, unsigned long long& y, int r) {      // x = element r * NT + tid, y its partner above
+                    const bool asc = ((r * NT + tid) & k) == 0;
+                    const unsigned long long lo = x < y ? x : y, hi = x < y ? y : x;
+                    x = asc ? lo : hi; y = asc ? hi : lo;
+                };
+                if (j == NT) { cx(v[0], v[1], 0); if (E == 4) cx(v[2], v[3], 2); }
+                else { cx(v[0], v[2], 0); cx(v[1], v[3], 1); }                         // j == 2 * NT, E == 4
+            } else if (j >= 32) {                            // through shared memory
+                __syncthreads();
+#pragma unroll
+                for (int r = 0; r < 4; ++r) if (r < E && r * NT + tid < cap) a[r * NT + tid] = v[r];
+                __syncthreads();
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const int e = r * NT + tid;
+                    if (r < E && e < cap) {
+                        const unsigned long long o = a[e ^ j];
+                        const bool takeMin = ((e & j) == 0) == ((e & k) == 0);
+                        v[r] = takeMin ? (o < v[r] ? o : v[r]) : (o > v[r] ? o : v[r]);
+                    }
+                }
+            } else {                                         // inside the warp
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    if (r < E) {
+                        const int e = r * NT + tid;
+                        const unsigned long long o = __shfl_xor_sync(FULL, v[r], j);
+                        const bool takeMin = ((e & j) == 0) == ((e & k) == 0);
+                        v[r] = takeMin ? (o < v[r] ? o : v[r]) : (o > v[r] ? o : v[r]);
+                    }
+                }
+            }
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < 4; ++r) if (r < E && r * NT + tid < cap) a[r * NT + tid] = v[r];
+    __syncthreads();
+    (void)lane;
 }
 
 struct GridParams { float minX, minY, invW, invH; };

@@ -1,0 +1,9 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_match2_gpu.py tests/test_kfmatch_gpu.py tests/test_bow_gpu.py tests/test_match_gpu.py tests/test_host_api.py -m gpu -x -q 2>&1 | tail -8 | tee gpurun_out/r2t_pytest.log
+timeout 600 python bench.py --workload matcher_calls --steps 2 > gpurun_out/r2t_matcher_calls.json 2> gpurun_out/r2t_matcher_calls.err
+tail -5 gpurun_out/r2t_matcher_calls.err; python - <<'PY'
+import json
+d=json.load(open('gpurun_out/r2t_matcher_calls.json'))
+for k,v in d['calls'].items(): print(k, v['gpu_us'], v.get('cpu_oracle_us'), v.get('speedup'))
+PY

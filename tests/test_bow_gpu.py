@@ -30,7 +30,7 @@ def test_bow_transform(k, depth):
 def test_search_by_bow_batch(variant):
     voc = O.make_vocabulary(k=6, depth=3, seed=3)
     pairs = []
-    for seed, n, lu in [(0, 220, 1), (1, 1000, 2), (2, 37, 1), (3, 1500, 3), (4, 640, 2)]:
+    for seed, n, lu in [(0, 220, 1), (1, 1000, 2), (2, 37, 1), (3, 1500, 3), (4, 640, 2), (5, 4500, 2)]:   # 4500: beyond the register sort
         pairs.append(make_pair(voc, n=n, seed=seed, levelsup=lu))
     # an empty frame and a pair without common nodes
     e = (np.zeros((0, 32), np.uint8), np.zeros(0, np.float32), np.zeros(0, np.uint32), np.zeros(0, np.uint8))

@@ -74,6 +74,14 @@ def test_search_for_triangulation_batch(only_stereo, ori):
     assert total > 100
 
 
+def test_search_for_triangulation_large_keyframes_take_the_sort_path():
+    """more than 4096 features in KF2: K19 sorts KF2's (node, index) keys instead of sweeping them"""
+    a, b, F, epi = make_tri_pair(6, n1=4400, n2=5000, mono_frac=0.4)
+    nm, ms = capi.search_for_triangulation([(_to_capi(a), _to_capi(b))], [F], [epi], False, True)
+    n_o, m_o = O.search_for_triangulation(a, b, F, epi, False, True)
+    assert nm[0] == n_o and np.array_equal(ms[0], m_o) and n_o > 20
+
+
 def test_keyframe_matchers_empty_and_degenerate_inputs():
     kf1, kf2, F, epi = make_tri_pair(9, n1=120, n2=150)
     a, b = _to_capi(kf1), _to_capi(kf2)
