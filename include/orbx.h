@@ -262,6 +262,17 @@ int orbm_compute_stereo_matches(const orbm_stereo_input* in, float* u_right, flo
  * `stream` (cudaStream_t or NULL = default stream). */
 int orbm_knn2_device(const uint8_t* queries, int64_t nq, const uint8_t* database, int64_t ndb,
                      int32_t db_index_offset, uint16_t* out_dist, int32_t* out_idx, void* stream);
+/* orbm_knn2_device for callers that may not allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments, same
+ * results bit for bit; calls no cudaMalloc / cudaFree / allocating routine.  The per-split partial results live in an
+ * 8 MiB file-scope device array (ORBM_KNN2_NOALLOC_SCRATCH_BYTES) that every GPU loading the library holds until exit.
+ * Limits: at most 8 database splits and splits * nq * 12 bytes <= 8 MiB -- i.e. any nq when ndb <= 8388608 rows (the call
+ * then runs unsplit if it must), nq <= 87381 at 67108864 rows; beyond that ORBX_E_CAPACITY with the sizes in
+ * orbx_last_error().  All calls on a device SHARE the array: calls that overlap on the GPU (two streams, two threads)
+ * race; calls on one stream are safe.  Stale contents of an earlier call are never read. */
+#define ORBM_KNN2_NOALLOC_SCRATCH_BYTES (8u << 20)
+int orbm_knn2_device_noalloc(const uint8_t* queries, int64_t nq, const uint8_t* database, int64_t ndb,
+                             int32_t db_index_offset, uint16_t* out_dist, int32_t* out_idx, void* stream);
 /* Tuning hook: how the 256-bit popcount is evaluated (0 = 8 POPC, 1 = carry-save 5 POPC [default],
  * 2 = Harley-Seal 4 POPC).  Results are identical; only the instruction mix changes. */
 int orbm_knn2_set_variant(int variant);

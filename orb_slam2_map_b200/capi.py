@@ -59,7 +59,7 @@ EXPORTS = [
     "orbx_keypoint_capacity", "orbx_reserve_shape", "orbx_extract", "orbx_extract_batch", "orbx_extract_batch_to_host", "orbx_download", "orbx_get_level",
     "orbx_get_candidates", "orbx_search_init_pairs", "orbx_extract_stereo_batch",
     "orbm_descriptor_distance", "orbm_search_for_initialization", "orbm_search_by_projection",
-    "orbm_compute_stereo_matches", "orbm_knn2_device", "orbm_knn2_merge_device", "orbm_knn2_set_variant",
+    "orbm_compute_stereo_matches", "orbm_knn2_device", "orbm_knn2_device_noalloc", "orbm_knn2_merge_device", "orbm_knn2_set_variant",
     "orbm_measure_int_rates", "orbm_nccl_unique_id", "orbm_nccl_comm_create", "orbm_nccl_comm_destroy", "orbm_knn2_sharded",
     "orbx_cvt_gray", "orbx_depth_to_float", "orbx_undistort_points", "orbx_image_bounds", "orbx_frames_rgbd", "orbx_frame_rgbd",
     "orbx_download_frame_front",
@@ -126,6 +126,7 @@ def lib():
                                                   C.POINTER(C.c_uint64)]
         L.orbm_knn2_device.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p,
                                        C.c_void_p, C.c_void_p]
+        L.orbm_knn2_device_noalloc.argtypes = L.orbm_knn2_device.argtypes
         L.orbm_knn2_merge_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_void_p, C.c_void_p,
                                              C.c_void_p]
         L.orbm_nccl_comm_create.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]
@@ -472,6 +473,12 @@ def compute_stereo_matches(kl, dl, kr, dr, pyr_l, pyr_r, scale, inv_scale, bf, f
 def knn2_device(q_ptr, nq, db_ptr, ndb, offset, out_dist_ptr, out_idx_ptr, stream=None):
     check(lib().orbm_knn2_device(C.c_void_p(q_ptr), nq, C.c_void_p(db_ptr), ndb, offset, C.c_void_p(out_dist_ptr),
                                  C.c_void_p(out_idx_ptr), C.c_void_p(stream) if stream else None))
+
+
+def knn2_device_noalloc(q_ptr, nq, db_ptr, ndb, offset, out_dist_ptr, out_idx_ptr, stream=None):
+    """orbm_knn2_device_noalloc: the same search with its scratch in a built-in device array (no cudaMalloc in the call)"""
+    check(lib().orbm_knn2_device_noalloc(C.c_void_p(q_ptr), nq, C.c_void_p(db_ptr), ndb, offset, C.c_void_p(out_dist_ptr),
+                                         C.c_void_p(out_idx_ptr), C.c_void_p(stream) if stream else None))
 
 
 def knn2_merge_device(pd_ptr, pi_ptr, nparts, nq, od_ptr, oi_ptr, stream=None):

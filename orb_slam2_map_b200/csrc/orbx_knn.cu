@@ -19,6 +19,7 @@
 #include "orbx_internal.h"
 
 #include <algorithm>
+#include <mutex>
 #include <cstdint>
 
 typedef uint8_t u8;
@@ -352,6 +353,99 @@ int orbm_knn2_device(const uint8_t* queries, int64_t nq, const uint8_t* database
         knn2_merge_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(pd, pi, (int)splits, nq, out_dist, out_idx);
         ORBX_CUDA(cudaGetLastError());
         ORBX_CUDA(cudaFreeAsync(scratch, st));
+    }
+    return ORBX_OK;
+}
+
+// ---- orbm_knn2_device for callers that may not allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc) ----
+// The per-split partial results live in a file-scope device array instead of a cudaMallocAsync block.  Every GPU that loads the
+// library holds the array until exit; every call on a device shares it, so calls that overlap on the GPU (two streams, two
+// threads) race.  The kernels write every entry the merge reads, so nothing has to start at zero and stale contents are harmless.
+#define KNN_NOALLOC_SCRATCH_BYTES (8u << 20)
+#define KNN_NOALLOC_MAX_SPLITS 8
+static __device__ __align__(256) unsigned char g_knn_noalloc_scratch[KNN_NOALLOC_SCRATCH_BYTES];
+static void* g_knn_noalloc_ptr[64];          // device address of the array, per device (the name above is only a host-side stand-in)
+static std::mutex g_knn_noalloc_mu;
+
+static int knn_noalloc_scratch(void** out)
+{
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) { orbx_set_error("device ordinal %d unsupported", dev); return ORBX_E_CAPACITY; }
+    std::lock_guard<std::mutex> lk(g_knn_noalloc_mu);
+    if (!g_knn_noalloc_ptr[dev]) {
+        void* p = nullptr;
+        ORBX_CUDA(cudaGetSymbolAddress(&p, g_knn_noalloc_scratch));       // once per device, with that device current
+        g_knn_noalloc_ptr[dev] = p;
+    }
+    *out = g_knn_noalloc_ptr[dev];
+    return ORBX_OK;
+}
+
+int orbm_knn2_device_noalloc(const uint8_t* queries, int64_t nq, const uint8_t* database, int64_t ndb,
+                             int32_t db_index_offset, uint16_t* out_dist, int32_t* out_idx, void* stream)
+{
+    ORBX_NVTX("orbm_knn2_device_noalloc");
+    if (nq <= 0) return ORBX_OK;
+    if (!queries || !out_dist || !out_idx || ndb < 0 || (ndb > 0 && !database)) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
+    if (((uintptr_t)queries | (uintptr_t)database) & 15) { orbx_set_error("descriptor arrays must be 16-byte aligned"); return ORBX_E_INVALID; }
+    if (((uintptr_t)out_dist & 3) || ((uintptr_t)out_idx & 7)) { orbx_set_error("output arrays must be 4/8-byte aligned"); return ORBX_E_INVALID; }
+    if (ndb > 0x7fffffffLL - 1 || (int64_t)db_index_offset + ndb > 0x7fffffffLL) { orbx_set_error("database index exceeds int32"); return ORBX_E_CAPACITY; }
+    int ndev = 0;
+    ORBX_CUDA(cudaGetDeviceCount(&ndev));
+    if (ndev <= 0) { orbx_set_error("no CUDA device; there is no CPU fallback"); return ORBX_E_CUDA; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t perSplit = (size_t)nq * 2 * (sizeof(uint16_t) + sizeof(int));          // 12 bytes per query and split
+    const long long needSplits = std::max<long long>(1, (ndb + KNN_MAX_SPLIT_ROWS - 1) / KNN_MAX_SPLIT_ROWS);
+    if (needSplits > KNN_NOALLOC_MAX_SPLITS || (needSplits > 1 && needSplits * perSplit > KNN_NOALLOC_SCRATCH_BYTES)) {
+        orbx_set_error("orbm_knn2_device_noalloc: %lld queries x %lld rows need %lld splits x %zu bytes of scratch; the built-in array holds %u bytes "
+                       "and %d splits (use orbm_knn2_device)", (long long)nq, (long long)ndb, needSplits, perSplit, KNN_NOALLOC_SCRATCH_BYTES, KNN_NOALLOC_MAX_SPLITS);
+        return ORBX_E_CAPACITY;
+    }
+    const long long qtiles = (nq + KNN_QUERIES_PER_BLOCK - 1) / KNN_QUERIES_PER_BLOCK;
+    if (qtiles > 0x7fffffffLL) { orbx_set_error("grid too large"); return ORBX_E_CAPACITY; }
+    int dev = 0, sms = 148, occ = 2;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    ORBX_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    switch (g_knn_variant) {
+    case 0: cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, knn2_kernel<0>, KNN_THREADS, 0); break;
+    case 2: cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, knn2_kernel<2>, KNN_THREADS, 0); break;
+    default: cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, knn2_kernel<1>, KNN_THREADS, 0); break;
+    }
+    // the wave-aware choice of orbm_knn2_device, bounded by what the array holds
+    const long long slots = (long long)std::max(occ, 1) * sms;
+    const long long fit = std::min<long long>(KNN_NOALLOC_MAX_SPLITS, (long long)(KNN_NOALLOC_SCRATCH_BYTES / perSplit));
+    long long splits = 1;
+    if (ndb > 0 && fit >= 2) {
+        const long long maxSplits = std::max<long long>(1, std::min<long long>(fit, ndb / 16384));
+        double best = 1e300;
+        for (long long c = 1; c <= maxSplits; ++c) {
+            const double cost = (double)((qtiles * c + slots - 1) / slots) / (double)c * (1.0 + 0.005 * (double)(c - 1));
+            if (cost < best - 1e-12) { best = cost; splits = c; }
+        }
+    }
+    splits = std::max(splits, needSplits);
+    long long rowsPerSplit = ndb > 0 ? (ndb + splits - 1) / splits : 1;
+    rowsPerSplit = (rowsPerSplit + KNN_TILE_ROWS - 1) / KNN_TILE_ROWS * KNN_TILE_ROWS;
+    splits = ndb > 0 ? (ndb + rowsPerSplit - 1) / rowsPerSplit : 1;
+    uint16_t* pd = out_dist;
+    int* pi = out_idx;
+    if (splits > 1) {
+        void* scratch = nullptr;
+        const int rc = knn_noalloc_scratch(&scratch); if (rc) return rc;
+        pi = (int*)scratch;
+        pd = (uint16_t*)((char*)scratch + (size_t)splits * nq * 2 * sizeof(int));
+    }
+    const dim3 grid((unsigned)qtiles, (unsigned)splits);
+    switch (g_knn_variant) {
+    case 0: knn2_kernel<0><<<grid, KNN_THREADS, 0, st>>>(queries, nq, database, ndb, rowsPerSplit, db_index_offset, pd, pi); break;
+    case 2: knn2_kernel<2><<<grid, KNN_THREADS, 0, st>>>(queries, nq, database, ndb, rowsPerSplit, db_index_offset, pd, pi); break;
+    default: knn2_kernel<1><<<grid, KNN_THREADS, 0, st>>>(queries, nq, database, ndb, rowsPerSplit, db_index_offset, pd, pi); break;
+    }
+    ORBX_CUDA(cudaGetLastError());
+    if (splits > 1) {
+        knn2_merge_kernel<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(pd, pi, (int)splits, nq, out_dist, out_idx);
+        ORBX_CUDA(cudaGetLastError());
     }
     return ORBX_OK;
 }
