@@ -113,6 +113,7 @@ struct SiSmem {
     unsigned short* lcell;           // L: cell x | cell y << 8
     unsigned short* md; unsigned short* m21;
     unsigned short* qlist;           // octave-0 keypoints of F1 in index order
+    unsigned short* mbi;             // per F1 keypoint: the F2 keypoint it took when its turn came (0xffff = none)
     u8* binOf;                       // per F1 keypoint
     uint32_t* cand;                  // [2][SI_QBLOCK][SI_MAXC]
     int* ccount;                     // [2][SI_QBLOCK] (> SI_MAXC = overflow)
@@ -138,13 +139,14 @@ __device__ __forceinline__ SiSmem si_carve(unsigned char* base, int cap)
     s.md = reinterpret_cast<unsigned short*>(p); p += h;
     s.m21 = reinterpret_cast<unsigned short*>(p); p += h;
     s.qlist = reinterpret_cast<unsigned short*>(p); p += h;
+    s.mbi = reinterpret_cast<unsigned short*>(p); p += h;
     s.binOf = p;
     return s;
 }
 static size_t si_smem_bytes(int cap)
 {
     return (size_t)std::min(cap, SI_DESC_SMEM) * 32 + (size_t)cap * 8 + 2 * SI_QBLOCK * SI_MAXC * 4 + 2 * SI_QBLOCK * 4 + 128 +
-           SI_WARPS * SI_PEND * 2 + 5 * (((size_t)cap + 1) / 2 * 4) + ((size_t)cap + 3) / 4 * 4 + 16;
+           SI_WARPS * SI_PEND * 2 + 6 * (((size_t)cap + 1) / 2 * 4) + ((size_t)cap + 3) / 4 * 4 + 16;
 }
 
 struct SiCtx {
@@ -252,7 +254,7 @@ search_init_kernel(FrameStore fs, int firstSlot, int slotStride, GridParams gp, 
     for (int i = tid; i < n2; i += SI_WARPS * 32) { S.md[i] = 0xffff; S.m21[i] = 0xffff; }
     for (int i = tid; i < c.ndescSmem * 2; i += SI_WARPS * 32)
         reinterpret_cast<uint4*>(S.desc)[i] = reinterpret_cast<const uint4*>(c.d2g)[i];
-    for (int i = tid; i < n1; i += SI_WARPS * 32) { S.binOf[i] = 0xff; m12[i] = -1; }
+    for (int i = tid; i < n1; i += SI_WARPS * 32) { S.binOf[i] = 0xff; S.mbi[i] = 0xffff; m12[i] = -1; }
     if (tid < ORBX_HISTO_LENGTH) S.hist[tid] = 0;
     if (tid == 0) sCull = 0;
     // Two ordered compactions, spread over all warps (each warp owns a contiguous range; counts, then a prefix over
@@ -350,7 +352,7 @@ search_init_kernel(FrameStore fs, int firstSlot, int slotStride, GridParams gp, 
                         m12[i1] = bi;
                         S.m21[bi] = (unsigned short)i1;
                         S.md[bi] = (unsigned short)best;
-                        if (checkOri) { const int bin = rot_bin(c.k1[i1].angle, c.k2[bi].angle); S.binOf[i1] = (u8)bin; S.hist[bin] += 1; }
+                        S.mbi[i1] = (unsigned short)bi;          // its rotation bin is worked out after the replay (two dependent global loads)
                     }
                     if (old != 0xffff) --nmatches;
                     ++nmatches;
@@ -362,6 +364,12 @@ search_init_kernel(FrameStore fs, int firstSlot, int slotStride, GridParams gp, 
     __threadfence_block();
     __syncthreads();
     if (checkOri) {
+        // rotHist[bin].push_back(i1) happened for every accepted query, also for the ones a later query displaced (src/ORBmatcher.cc:470-482)
+        for (int i = tid; i < n1; i += SI_WARPS * 32) {
+            const int bi = S.mbi[i];
+            if (bi != 0xffff) { const int bin = rot_bin(c.k1[i].angle, c.k2[bi].angle); S.binOf[i] = (u8)bin; atomicAdd(&S.hist[bin], 1); }
+        }
+        __syncthreads();
         int i1a, i2a, i3a;
         three_maxima(S.hist, ORBX_HISTO_LENGTH, i1a, i2a, i3a);
         int culled = 0;
@@ -728,9 +736,11 @@ __device__ __forceinline__ unsigned long long warp_merge32(unsigned long long a,
 
 // Lane l returns the l-th smallest candidate key of the query (~0 where there are fewer).  isFree(idx): the occupancy
 // the query sees.  buf: PROJ_SCAN_BUF entries of shared memory owned by this warp.
-template <typename Free>
+struct KeepAll { __device__ __forceinline__ bool operator()(int, int) const { return true; } };
+// keep(idx, dist): a last filter that needs the distance (SearchForInitialization's vMatchedDistance test)
+template <typename Free, typename Keep = KeepAll>
 __device__ __forceinline__ unsigned long long proj_scan_sorted(const ProjScan& c, const orbm_proj_query& Q, const u8* qdescRow,
-                                                                int lane, unsigned long long* buf, Free isFree)
+                                                                int lane, unsigned long long* buf, Free isFree, Keep keep = Keep())
 {
     const unsigned long long NONE = ~0ull;
     unsigned long long top = NONE;
@@ -747,7 +757,7 @@ __device__ __forceinline__ unsigned long long proj_scan_sorted(const ProjScan& c
             const unsigned long long part = buf[lane];
             const int idx = (int)((part >> 8) & 0xffff);
             const int dist = hamming256(qd, reinterpret_cast<const uint32_t*>(c.desc + (size_t)idx * 32));
-            key = ((unsigned long long)dist << 40) | part;
+            if (keep(idx, dist)) key = ((unsigned long long)dist << 40) | part;
         }
         key = warp_sort32(key, lane);
         top = haveTop ? warp_merge32(top, key, lane) : key;
@@ -931,6 +941,145 @@ proj_fixpoint_kernel(ProjScan c, const orbm_proj_query* __restrict__ queries, co
         __syncthreads();
     }
     if (tid == 0) { *nmatchesOut = sTakes; if (iterationsOut) *iterationsOut = iterations; }
+}
+
+// =============================================================================================
+// K7, latency form (one pair of at most PROJ_SCAN_MAXN keypoints per frame: the stateless call of the initializer).
+//  K7a  si_list_kernel      warp per octave-0 keypoint of F1, all SMs: the sweep of K9a over F2 with the level window [0, 0]
+//       (src/ORBmatcher.cc:425) and only the candidates within dkeep = TH_LOW / nnratio + 2 (farther ones can neither win nor
+//       make the ratio test fail): the 32 smallest keys dist|cell|idx, sorted.
+//  K7b  si_fixpoint_kernel  one CTA.  The reference skips a candidate i2 when an EARLIER query took it with a distance <= the
+//       candidate's (vMatchedDistance, :447).  As in K9b the rule is iterated for all queries at once from the takes of the
+//       previous iteration (takers of a keypoint: a linked list head[i2] -> next[q]); the prefix of final queries grows by at
+//       least one per iteration.  Then the reference's bookkeeping in closed form: the LAST taker of a keypoint owns it
+//       (earlier ones were reset to -1, :462-466), nmatches = keypoints taken, every taker votes in the rotation histogram
+//       (displaced ones too, :470-482), the cull only resets owners.
+// =============================================================================================
+__global__ void __launch_bounds__(PROJ_LIST_WARPS * 32)
+si_list_kernel(ProjScan c, const orbx_keypoint* __restrict__ k1, const u8* __restrict__ d1, const float* __restrict__ prev, int n1,
+               float window, int dkeep, unsigned long long* __restrict__ keys)
+{
+    __shared__ unsigned long long bufS[PROJ_LIST_WARPS][PROJ_SCAN_BUF];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, i1 = blockIdx.x * PROJ_LIST_WARPS + w;
+    if (i1 >= n1 || k1[i1].octave > 0) return;
+    orbm_proj_query Q;
+    Q.u = prev[2 * i1]; Q.v = prev[2 * i1 + 1]; Q.radius = window;
+    Q.min_level = 0; Q.max_level = 0; Q.u_right = 0.f; Q.max_right_err = -1.f; Q.angle = 0.f; Q.level_lo = -1; Q.level_hi = -1;
+    const unsigned long long k = proj_scan_sorted(c, Q, d1 + (size_t)i1 * 32, lane, bufS[w], [](int) { return true; },
+                                                  [dkeep](int, int dist) { return dist <= dkeep; });
+    keys[(size_t)PROJ_L * i1 + lane] = k;
+}
+
+__global__ void __launch_bounds__(PROJ_FIX_THREADS)
+si_fixpoint_kernel(ProjScan c, const orbx_keypoint* __restrict__ k1, const u8* __restrict__ d1, float* __restrict__ prev, int n1,
+                   float window, int dkeep, float nnratio, int checkOri, const unsigned long long* __restrict__ keys,
+                   int* __restrict__ m12, int* __restrict__ nmatchesOut, int* __restrict__ dirtyList)
+{
+    extern __shared__ __align__(16) u8 fixS[];
+    __shared__ int hist[ORBX_HISTO_LENGTH];
+    __shared__ int sChanged, sDirty, sCount, sMax[3];
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, n2 = c.n;
+    // take[q]: keypoint of F2 query q takes (-1 none, -2 no decision yet); tdist[q]: its distance; head / next: takers of a keypoint
+    // (tprev: the distances the lists were built with, so that an iteration reads one consistent state)
+    int* take = reinterpret_cast<int*>(fixS);
+    int* tdist = take + n1;
+    int* tprev = tdist + n1;
+    int* next = tprev + n1;
+    int* head = next + n1;
+    unsigned long long* scanBuf = reinterpret_cast<unsigned long long*>(fixS + ((((size_t)4 * n1 + n2) * sizeof(int) + 15) & ~(size_t)15));
+    const unsigned long long NONE = ~0ull;
+    for (int i = tid; i < n1; i += PROJ_FIX_THREADS) { take[i] = -2; tdist[i] = 0; next[i] = -1; }
+    for (int i = tid; i < n2; i += PROJ_FIX_THREADS) head[i] = -1;
+    if (tid < ORBX_HISTO_LENGTH) hist[tid] = 0;
+    if (tid == 0) sCount = 0;
+    __syncthreads();
+    // is candidate (i2, dist) still on offer when query q's turn comes?
+    auto visible = [&](int q, int i2, int dist) {
+        for (int t = head[i2]; t >= 0; t = next[t]) if (t < q && tprev[t] <= dist) return false;
+        return true;
+    };
+    auto decide = [&](int q, unsigned long long ka, unsigned long long kb) {
+        int t = -1, dist = 0;
+        if (ka != NONE) {
+            const int best = (int)(ka >> 40);
+            // bestDist2 starts at INT_MAX (:435): without a second candidate the ratio test passes
+            const bool ratioOk = kb == NONE || (float)best < __fmul_rn((float)(int)(kb >> 40), nnratio);
+            if (best <= ORBX_TH_LOW && ratioOk) { t = (int)((ka >> 8) & 0xffff); dist = best; }
+        }
+        if (t != take[q] || dist != tdist[q]) sChanged = 1;
+        take[q] = t; tdist[q] = dist;
+    };
+    for (;;) {
+        if (tid == 0) { sChanged = 0; sDirty = 0; }
+        __syncthreads();
+        for (int q = tid; q < n1; q += PROJ_FIX_THREADS) {
+            if (k1[q].octave > 0) { take[q] = -1; continue; }
+            const unsigned long long* K = keys + (size_t)PROJ_L * q;
+            unsigned long long ka = NONE, kb = NONE;
+            int nvis = 0;
+            bool complete = false;
+            for (int j = 0; j < PROJ_L; ++j) {
+                const unsigned long long k = K[j];
+                if (k == NONE) { complete = true; break; }
+                if (visible(q, (int)((k >> 8) & 0xffff), (int)(k >> 40))) {
+                    if (nvis == 0) ka = k; else kb = k;
+                    if (++nvis == 2) break;
+                }
+            }
+            if (!complete && nvis < 2) dirtyList[atomicAdd(&sDirty, 1)] = q;       // a full list used up: searched again below
+            else decide(q, ka, kb);
+        }
+        __syncthreads();
+        const int nd = sDirty;
+        for (int d = wid; d < nd; d += PROJ_FIX_THREADS / 32) {
+            const int q = dirtyList[d];
+            orbm_proj_query Q;
+            Q.u = prev[2 * q]; Q.v = prev[2 * q + 1]; Q.radius = window;
+            Q.min_level = 0; Q.max_level = 0; Q.u_right = 0.f; Q.max_right_err = -1.f; Q.angle = 0.f; Q.level_lo = -1; Q.level_hi = -1;
+            const unsigned long long k = proj_scan_sorted(c, Q, d1 + (size_t)q * 32, lane, scanBuf + wid * PROJ_SCAN_BUF, [](int) { return true; },
+                                                          [&](int i2, int dist) { return dist <= dkeep && visible(q, i2, dist); });
+            const unsigned long long ka = __shfl_sync(FULL, k, 0), kb = __shfl_sync(FULL, k, 1);
+            if (lane == 0) decide(q, ka, kb);
+        }
+        __syncthreads();
+        if (!sChanged) break;
+        // takers of the next iteration
+        for (int i = tid; i < n2; i += PROJ_FIX_THREADS) head[i] = -1;
+        __syncthreads();
+        for (int q = tid; q < n1; q += PROJ_FIX_THREADS) if (take[q] >= 0) { tprev[q] = tdist[q]; next[q] = atomicExch(&head[take[q]], q); }
+        __syncthreads();
+    }
+    // the lists hold the final takes (the last iteration changed nothing).  Owner of a keypoint = its last taker.
+    for (int q = tid; q < n1; q += PROJ_FIX_THREADS) {
+        const int t = take[q];
+        int m = -1;
+        if (t >= 0) {
+            int last = q;
+            for (int o = head[t]; o >= 0; o = next[o]) last = max(last, o);
+            if (last == q) { m = t; atomicAdd(&sCount, 1); }
+            if (checkOri) atomicAdd(&hist[rot_bin(k1[q].angle, c.kps[t].angle)], 1);
+        }
+        m12[q] = m;
+    }
+    __syncthreads();
+    if (checkOri) {
+        if (tid == 0) three_maxima(hist, ORBX_HISTO_LENGTH, sMax[0], sMax[1], sMax[2]);
+        __syncthreads();
+        for (int q = tid; q < n1; q += PROJ_FIX_THREADS) {
+            const int t = m12[q];
+            if (t >= 0) {
+                const int b = rot_bin(k1[q].angle, c.kps[t].angle);
+                if (b != sMax[0] && b != sMax[1] && b != sMax[2]) { m12[q] = -1; atomicSub(&sCount, 1); }
+            }
+        }
+        __syncthreads();
+    }
+    // vbPrevMatched[i1] = F2.mvKeysUn[vnMatches12[i1]].pt (:510-513)
+    for (int q = tid; q < n1; q += PROJ_FIX_THREADS) {
+        const int t = m12[q];
+        if (t >= 0) { prev[2 * q] = c.kps[t].x; prev[2 * q + 1] = c.kps[t].y; }
+    }
+    if (tid == 0) *nmatchesOut = sCount;
 }
 
 // =============================================================================================
@@ -1461,6 +1610,8 @@ int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, f
     const size_t oNm = take(4), oM12 = take(cap * 4);
     const size_t downBytes = off - oPrev;
     const size_t oGS = take(2 * (ORBX_GRID_CELLS + 1) * sizeof(unsigned short)), oGI = take(2 * cap * sizeof(unsigned short));
+    const bool sweep = f1->n <= PROJ_SCAN_MAXN && f2->n <= PROJ_SCAN_MAXN;
+    const size_t oKeys = take(sweep ? cap * PROJ_L * 8 : 8), oDirty = take(sweep ? cap * 4 : 4);
     DevBuf arena;
     if ((rc = arena.alloc(off))) return rc;
     u8* host = nullptr;
@@ -1486,12 +1637,31 @@ int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, f
     fs.gridStart = reinterpret_cast<unsigned short*>(dev + oGS); fs.gridIdx = reinterpret_cast<unsigned short*>(dev + oGI);
     fs.cap = (int)cap;
     const GridParams gp = orbx_grid_params(f2->min_x, f2->max_x, f2->min_y, f2->max_y);
-    rc = orbx_launch_grid_build(fs, 1, 1, gp, 0); if (rc) return rc;
-    pt.mark("grid");
-    rc = launch_search_init(fs, 0, 1, 1, gp, reinterpret_cast<float*>(dev + oPrev), window_size, nnratio, check_orientation,
-                            reinterpret_cast<int*>(dev + oM12), reinterpret_cast<int*>(dev + oNm), nullptr, 0);
-    if (rc) return rc;
-    pt.mark("search");
+    if (sweep) {
+        // latency form (K7a / K7b): no grid, sorted candidate lists on all SMs, fixed-point replay in one CTA
+        ProjScan ps;
+        ps.kps = fs.kps + cap; ps.desc = fs.desc + cap * 32; ps.uRight = nullptr; ps.gp = gp; ps.n = f2->n; ps.gate = false;
+        int dkeep = 256;
+        if (nnratio > 0.f) { const double d = (double)ORBX_TH_LOW / (double)nnratio + 2.0; dkeep = d < 256.0 ? (int)d : 256; }
+        unsigned long long* dKeys = reinterpret_cast<unsigned long long*>(dev + oKeys);
+        float* dPrev = reinterpret_cast<float*>(dev + oPrev);
+        if (f1->n > 0)
+            si_list_kernel<<<(f1->n + PROJ_LIST_WARPS - 1) / PROJ_LIST_WARPS, PROJ_LIST_WARPS * 32>>>(ps, fs.kps, fs.desc, dPrev, f1->n, (float)window_size, dkeep, dKeys);
+        pt.mark("lists");
+        const int fixSmem = (int)(((((size_t)4 * f1->n + f2->n) * sizeof(int) + 15) & ~(size_t)15) + (PROJ_FIX_THREADS / 32) * PROJ_SCAN_BUF * 8);
+        static bool attrSet = false;
+        if (!attrSet) { ORBX_CUDA(cudaFuncSetAttribute(si_fixpoint_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 5 * PROJ_SCAN_MAXN * 4 + 16 + (PROJ_FIX_THREADS / 32) * PROJ_SCAN_BUF * 8)); attrSet = true; }
+        si_fixpoint_kernel<<<1, PROJ_FIX_THREADS, fixSmem>>>(ps, fs.kps, fs.desc, dPrev, f1->n, (float)window_size, dkeep, nnratio, check_orientation, dKeys,
+                                                             reinterpret_cast<int*>(dev + oM12), reinterpret_cast<int*>(dev + oNm), reinterpret_cast<int*>(dev + oDirty));
+        pt.mark("fixpoint");
+    } else {
+        rc = orbx_launch_grid_build(fs, 1, 1, gp, 0); if (rc) return rc;
+        pt.mark("grid");
+        rc = launch_search_init(fs, 0, 1, 1, gp, reinterpret_cast<float*>(dev + oPrev), window_size, nnratio, check_orientation,
+                                reinterpret_cast<int*>(dev + oM12), reinterpret_cast<int*>(dev + oNm), nullptr, 0);
+        if (rc) return rc;
+        pt.mark("search");
+    }
     ORBX_CUDA(cudaGetLastError());
     ORBX_CUDA(cudaMemcpyAsync(host + oPrev, dev + oPrev, downBytes, cudaMemcpyDeviceToHost, 0));
     pt.mark("d2h");

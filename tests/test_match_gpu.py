@@ -94,6 +94,34 @@ def test_search_init_collisions_and_duplicates():
         assert n_g == n_o and np.array_equal(m_g, m_o) and np.array_equal(p_g, p_o)
 
 
+@pytest.mark.parametrize("n,window,nnratio", [(3000, 300, 0.99), (1200, 640, 0.9), (5000, 120, 0.99)])
+def test_search_init_contended_and_large_frames(n, window, nnratio):
+    """Thousands of near-identical descriptors inside wide windows: the 32-entry candidate lists of the latency form fill up
+    with ties and are searched again as keypoints are taken; 5000 keypoints take the batch kernel (grid + warp replay)."""
+    w, h = 640, 480
+    base = np.random.default_rng(n).integers(0, 256, (6, 32), dtype=np.uint8)
+    def mk(seed):
+        r = np.random.default_rng(seed)
+        k = np.zeros(n, capi.KP_DTYPE)
+        k["x"] = r.uniform(5, 635, n).astype(np.float32); k["y"] = r.uniform(5, 475, n).astype(np.float32)
+        k["octave"] = r.integers(0, 2, n); k["angle"] = r.uniform(0, 360, n).astype(np.float32)
+        k["size"] = 31; k["class_id"] = -1
+        d = base[r.integers(0, 6, n)].copy()
+        for _ in range(3):
+            d[np.arange(n), r.integers(0, 32, n)] ^= (1 << r.integers(0, 8, n)).astype(np.uint8)
+        return k, d
+    k1, d1 = mk(n + 1)
+    k2, d2 = mk(n + 2)
+    prev = np.stack([k1["x"], k1["y"]], axis=1).astype(np.float32)
+    fo1, fo2 = O.FrameData(k1, d1, w, h), O.FrameData(k2, d2, w, h)
+    fg1, fg2 = capi.FrameData(k1, d1, w, h), capi.FrameData(k2, d2, w, h)
+    for ori in (True, False):
+        n_o, m_o, p_o, _ = O.search_for_initialization(fo1, fo2, prev, window, nnratio, ori)
+        n_g, m_g, p_g = capi.search_for_initialization(fg1, fg2, prev, window, nnratio, ori)
+        assert n_g == n_o and np.array_equal(m_g, m_o) and np.array_equal(p_g, p_o)
+    assert n_o > 20
+
+
 def test_search_init_empty_frames():
     k = np.zeros(0, capi.KP_DTYPE)
     d = np.zeros((0, 32), np.uint8)
