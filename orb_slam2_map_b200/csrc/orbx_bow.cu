@@ -86,15 +86,16 @@ search_bow_kernel(int variant, const BowPair* __restrict__ pairs, const u8* __re
                   const uint32_t* __restrict__ nodeA, const u8* __restrict__ flagA, const u8* __restrict__ descB,
                   const float* __restrict__ angB, const uint32_t* __restrict__ nodeB, const u8* __restrict__ flagB,
                   float nnratio, int checkOri, int capA, int capB, int32_t* __restrict__ matchA, int32_t* __restrict__ matchB,
-                  int32_t* __restrict__ nmatchesOut, u8* __restrict__ binOfAll, int* __restrict__ pairState)
+                  int32_t* __restrict__ nmatchesOut, u8* __restrict__ binOfAll, int* __restrict__ pairState, int stage)
 {
     extern __shared__ __align__(16) unsigned char smraw[];
-    __shared__ int sInd[3], sLast;
+    __shared__ int sInd[3], sLast, sCull, sWarpRuns[BOW_THREADS / 32], sHist[ORBX_HISTO_LENGTH];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const BowPair P = pairs[blockIdx.x];
     unsigned long long* keysA = reinterpret_cast<unsigned long long*>(smraw);
     unsigned long long* keysB = keysA + capA;
-    u8* matchedB = reinterpret_cast<u8*>(keysB + capB);
+    unsigned short* runs = reinterpret_cast<unsigned short*>(keysB + capB);      // start positions of A's node runs, ascending
+    u8* matchedB = reinterpret_cast<u8*>(runs + capA);
     int* gState = pairState + (size_t)blockIdx.x * BOW_STATE_INTS;        // [0..29] histogram, [32] count, [33] ticket, all starting at -1
     u8* binOf = binOfAll + P.offA;
     descA += (size_t)P.offA * 32; angA += P.offA; nodeA += P.offA; flagA += P.offA; matchA += P.offA;
@@ -106,15 +107,54 @@ search_bow_kernel(int variant, const BowPair* __restrict__ pairs, const u8* __re
     for (int i = tid; i < pb; i += BOW_THREADS)
         keysB[i] = (i < P.nB && (flagB[i] & 1)) ? (((unsigned long long)nodeB[i] << 32) | (unsigned)i) : ~0ull;
     for (int i = tid; i < P.nB; i += BOW_THREADS) matchedB[i] = 0;
+    if (stage) {
+        // per-frame sizes: descriptors, angles and flags of both frames are copied into shared memory (coalesced, in flight during
+        // the sort), so that the replay of a node run never waits on a dependent global load
+        u8* sp = reinterpret_cast<u8*>((reinterpret_cast<uintptr_t>(matchedB + capB) + 15) & ~(uintptr_t)15);
+        uint4* sDA = reinterpret_cast<uint4*>(sp); sp += (size_t)P.nA * 32;
+        uint4* sDB = reinterpret_cast<uint4*>(sp); sp += (size_t)P.nB * 32;
+        float* sAA = reinterpret_cast<float*>(sp); sp += (size_t)P.nA * 4;
+        float* sAB = reinterpret_cast<float*>(sp); sp += (size_t)P.nB * 4;
+        u8* sFA = sp; sp += P.nA;
+        u8* sFB = sp;
+        for (int i = tid; i < P.nA * 2; i += BOW_THREADS) sDA[i] = reinterpret_cast<const uint4*>(descA)[i];
+        for (int i = tid; i < P.nB * 2; i += BOW_THREADS) sDB[i] = reinterpret_cast<const uint4*>(descB)[i];
+        for (int i = tid; i < P.nA; i += BOW_THREADS) { sAA[i] = angA[i]; sFA[i] = flagA[i]; }
+        for (int i = tid; i < P.nB; i += BOW_THREADS) { sAB[i] = angB[i]; sFB[i] = flagB[i]; }
+        descA = reinterpret_cast<const u8*>(sDA); descB = reinterpret_cast<const u8*>(sDB);
+        angA = sAA; angB = sAB; flagA = sFA; flagB = sFB;
+    }
     __syncthreads();
-    if (pa <= 4 * BOW_THREADS) block_sort64<BOW_THREADS>(keysA, pa); else block_bitonic_sort64(keysA, pa);
-    if (pb <= 4 * BOW_THREADS) block_sort64<BOW_THREADS>(keysB, pb); else block_bitonic_sort64(keysB, pb);
+    if (pa == pb && pa <= 2 * BOW_THREADS) block_sort64_pair<BOW_THREADS>(keysA, keysB, pa);      // the usual case: both frames of a size
+    else {
+        if (pa <= 4 * BOW_THREADS) block_sort64<BOW_THREADS>(keysA, pa); else block_bitonic_sort64(keysA, pa);
+        if (pb <= 4 * BOW_THREADS) block_sort64<BOW_THREADS>(keysB, pb); else block_bitonic_sort64(keysB, pb);
+    }
+    // A's node runs in ascending order (every CTA builds the same list, so the deal below needs no communication): thread t owns
+    // a contiguous range of positions, counts its run starts, a block scan places them
+    int nRuns;
+    {
+        const int per = (pa + BOW_THREADS - 1) / BOW_THREADS;
+        const int p0 = tid * per, p1 = min(p0 + per, P.nA);
+        auto is_start = [&](int i) { const unsigned long long k = keysA[i]; return k != ~0ull && (i == 0 || (keysA[i - 1] >> 32) != (k >> 32)); };
+        int cnt = 0;
+        for (int i = p0; i < p1; ++i) cnt += is_start(i);
+        int incl = cnt;
+        for (int d = 1; d < 32; d <<= 1) { const int v = __shfl_up_sync(FULL, incl, d); if (lane >= d) incl += v; }
+        if (lane == 31) sWarpRuns[wid] = incl;
+        __syncthreads();
+        int base = 0, total = 0;
+        for (int w = 0; w < BOW_THREADS / 32; ++w) { const int v = sWarpRuns[w]; if (w < wid) base += v; total += v; }
+        int o = base + incl - cnt;
+        for (int i = p0; i < p1; ++i) if (is_start(i)) runs[o++] = (unsigned short)i;
+        nRuns = total;
+        __syncthreads();
+    }
     int accepted = 0;
     const int warpsAll = (int)gridDim.y * (BOW_THREADS / 32);
-    for (int a0 = (int)blockIdx.y * (BOW_THREADS / 32) + wid; a0 < P.nA; a0 += warpsAll) {
+    for (int r = (int)blockIdx.y * (BOW_THREADS / 32) + wid; r < nRuns; r += warpsAll) {
+        const int a0 = runs[r];
         const unsigned long long k0 = keysA[a0];
-        if (k0 == ~0ull) break;                                  // sorted: the unused entries are at the end
-        if (a0 > 0 && (keysA[a0 - 1] >> 32) == (k0 >> 32)) continue;      // not the start of a node run
         const unsigned node = (unsigned)(k0 >> 32);
         // B's run of the same node: [b0, b1)
         int lo = 0, hi = pb;
@@ -165,7 +205,12 @@ search_bow_kernel(int variant, const BowPair* __restrict__ pairs, const u8* __re
                 int best = 0x7fffffff, second = 0x7fffffff;
                 unsigned key = 0xffffffffu;
                 if (resident) {
-                    if (freeB) { best = hamming256_regs(q, db); key = (unsigned)(b0 + lane); }
+                    // one candidate per lane: two warp-wide integer minima (REDUX) instead of a shuffle tree
+                    const unsigned mine = freeB ? ((unsigned)hamming256_regs(q, db) << 8) | (unsigned)lane : 0xffffffffu;
+                    const unsigned w1 = __reduce_min_sync(FULL, mine);
+                    const unsigned w2 = __reduce_min_sync(FULL, mine == w1 ? 0xffffffffu : mine);
+                    if (w1 != 0xffffffffu) { best = (int)(w1 >> 8); key = (unsigned)b0 + (w1 & 0xff); }
+                    if (w2 != 0xffffffffu) second = (int)(w2 >> 8);
                 } else {
                     for (int jb = b0 + lane; jb < b1; jb += 32) {
                         const int idxB = (int)(keysB[jb] & 0xffffffffu);
@@ -176,7 +221,7 @@ search_bow_kernel(int variant, const BowPair* __restrict__ pairs, const u8* __re
                         else if (dist < second) second = dist;
                     }
                 }
-                warp_top2(best, key, second);
+                if (!resident) warp_top2(best, key, second);
                 best = min(best, 256); second = min(second, 256);     // bestDist1 = bestDist2 = 256 initially; a distance of 256 never wins
                 const bool found = best < 256;
                 const bool close = variant == 0 ? best <= ORBX_TH_LOW : best < ORBX_TH_LOW;
@@ -204,25 +249,28 @@ search_bow_kernel(int variant, const BowPair* __restrict__ pairs, const u8* __re
     __syncthreads();
     if (!sLast) return;
     __threadfence();
+    // everything the finish reads is requested at once (histogram, count, this thread's first bin and match): one trip to L2
     volatile int* vs = gState;
+    volatile u8* vb = binOf;
+    volatile int32_t* vmA = matchA;
+    if (tid == 0) sCull = 0;
+    const int count = tid == 0 ? vs[32] + 1 : 0;
+    int b0 = 0xff, m0 = -1;
     if (checkOri) {
-        if (tid == 0) {
-            int h[ORBX_HISTO_LENGTH];
-            for (int i = 0; i < ORBX_HISTO_LENGTH; ++i) h[i] = vs[i] + 1;
-            int i1, i2, i3; three_maxima(h, ORBX_HISTO_LENGTH, i1, i2, i3); sInd[0] = i1; sInd[1] = i2; sInd[2] = i3;
-        }
+        if (tid < ORBX_HISTO_LENGTH) sHist[tid] = vs[tid] + 1;
+        if (tid < P.nA) { b0 = vb[tid]; m0 = vmA[tid]; }
+        __syncthreads();
+        if (tid == 0) { int i1, i2, i3; three_maxima(sHist, ORBX_HISTO_LENGTH, i1, i2, i3); sInd[0] = i1; sInd[1] = i2; sInd[2] = i3; }
         __syncthreads();
         int culled = 0;
-        volatile u8* vb = binOf;
-        volatile int32_t* vmA = matchA;
         for (int i = tid; i < P.nA; i += BOW_THREADS) {
-            const int b = vb[i];
-            if (b != 0xff && b != sInd[0] && b != sInd[1] && b != sInd[2]) { matchB[vmA[i]] = -1; matchA[i] = -1; ++culled; }
+            const int bb = i == tid ? b0 : (int)vb[i];
+            if (bb != 0xff && bb != sInd[0] && bb != sInd[1] && bb != sInd[2]) { matchB[i == tid ? m0 : (int)vmA[i]] = -1; matchA[i] = -1; ++culled; }
         }
-        if (culled) atomicSub(&gState[32], culled);
-        __syncthreads();
+        if (culled) atomicAdd(&sCull, culled);
     }
-    if (tid == 0) nmatchesOut[blockIdx.x] = vs[32] + 1;
+    __syncthreads();
+    if (tid == 0) nmatchesOut[blockIdx.x] = count - sCull;
 }
 
 // K18: one CTA per map point.  Thread i owns row i of the N x N distance matrix and finds its median
@@ -353,7 +401,10 @@ int orbm_search_by_bow(int variant, const orbm_bow_frame* a, const orbm_bow_fram
     }
     int capA = 1; while (capA < maxA) capA <<= 1;
     int capB = 1; while (capB < maxB) capB <<= 1;
-    const size_t smem = (size_t)(capA + capB) * 8 + capB + 16;
+    size_t smem = (size_t)(capA + capB) * 8 + (size_t)capA * 2 + ((capB + 15) & ~15) + 16;
+    const size_t stageBytes = (size_t)(maxA + maxB) * 37 + 64;
+    const int stage = npairs <= 16 && smem + stageBytes <= 200 * 1024;      // per-frame calls; a batch keeps its occupancy instead
+    if (stage) smem += stageBytes;
     if (smem > 220 * 1024) { orbx_set_error("frames of %d / %d features exceed the shared-memory sort (%zu bytes)", maxA, maxB, smem); return ORBX_E_CAPACITY; }
     for (int p = 0; p < npairs; ++p) {
         if (pairs[p].nA && (!a[p].descriptors || !a[p].angles || !a[p].node_id || !a[p].flags)) { orbx_set_error("pair %d: null array in a", p); return ORBX_E_INVALID; }
@@ -365,8 +416,10 @@ int orbm_search_by_bow(int variant, const orbm_bow_frame* a, const orbm_bow_fram
     const int sPairs = ar.in(pairs.data(), npairs * sizeof(BowPair));
     const int sDescA = ar.in(nullptr, (size_t)totA * 32), sAngA = ar.in(nullptr, (size_t)totA * 4), sNodeA = ar.in(nullptr, (size_t)totA * 4), sFlagA = ar.in(nullptr, (size_t)totA);
     const int sDescB = ar.in(nullptr, (size_t)totB * 32), sAngB = ar.in(nullptr, (size_t)totB * 4), sNodeB = ar.in(nullptr, (size_t)totB * 4), sFlagB = ar.in(nullptr, (size_t)totB);
-    const int sMA = ar.out(match_a, (size_t)totA * 4), sMB = ar.out(match_b, (size_t)totB * 4), sNM = ar.out(nmatches, (size_t)npairs * 4);
-    const int sBin = ar.work((size_t)totA), sState = ar.work((size_t)npairs * BOW_STATE_INTS * 4);
+    // outputs, bins and pair state start as 0xff bytes (see the kernel's header): they are in/out segments filled in the staging
+    // buffer, so the preset rides on the call's one upload instead of a memset node
+    const int sMA = ar.inout_fill(match_a, (size_t)totA * 4), sMB = ar.inout_fill(match_b, (size_t)totB * 4), sNM = ar.inout_fill(nmatches, (size_t)npairs * 4);
+    const int sBin = ar.inout_fill(nullptr, (size_t)totA), sState = ar.inout_fill(nullptr, (size_t)npairs * BOW_STATE_INTS * 4);
     int rc = ar.layout(); if (rc) return rc;
     for (int p = 0; p < npairs; ++p) {
         const BowPair& P = pairs[p];
@@ -383,16 +436,16 @@ int orbm_search_by_bow(int variant, const orbm_bow_frame* a, const orbm_bow_fram
             memcpy(ar.hostp<u8>(sFlagB) + P.offB, b[p].flags, (size_t)P.nB);
         }
     }
+    for (int sg : {sMA, sMB, sNM, sBin, sState}) memset(ar.hostp<u8>(sg), 0xff, ar.segs[sg].bytes);
     rc = ar.upload(); if (rc) return rc;
-    // outputs, bins and pair state are consecutive in the arena: one fill presets them (see the kernel's header)
-    ORBX_CUDA(cudaMemsetAsync(ar.dev<u8>(sMA), 0xff, (size_t)(ar.dev<u8>(sState) - ar.dev<u8>(sMA)) + (size_t)npairs * BOW_STATE_INTS * 4, 0));
-    if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(search_bow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    static bool attrSet = false;             // once: the largest size the host checks above allow
+    if (!attrSet) { ORBX_CUDA(cudaFuncSetAttribute(search_bow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024)); attrSet = true; }
     // a batch fills the GPU with one CTA per pair; the single pair of a per-frame call is spread over up to 8 SMs (32 warps each)
     const int splits = npairs >= 64 ? 1 : std::max(1, std::min(8, std::min(128 / npairs, (maxA + 255) / 256)));
     search_bow_kernel<<<dim3(npairs, splits), BOW_THREADS, smem>>>(variant, ar.dev<BowPair>(sPairs), ar.dev<u8>(sDescA), ar.dev<float>(sAngA), ar.dev<uint32_t>(sNodeA),
                                                      ar.dev<u8>(sFlagA), ar.dev<u8>(sDescB), ar.dev<float>(sAngB), ar.dev<uint32_t>(sNodeB), ar.dev<u8>(sFlagB),
                                                      nnratio, check_orientation, capA, capB, ar.dev<int32_t>(sMA), ar.dev<int32_t>(sMB), ar.dev<int32_t>(sNM),
-                                                     ar.dev<u8>(sBin), ar.dev<int>(sState));
+                                                     ar.dev<u8>(sBin), ar.dev<int>(sState), stage);
     return ar.finish();
 }
 

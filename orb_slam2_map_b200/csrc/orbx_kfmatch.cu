@@ -192,7 +192,7 @@ triangulation_kernel(const TriPair* __restrict__ pairs, const orbx_keypoint* __r
                      int* __restrict__ pairState)
 {
     extern __shared__ __align__(16) unsigned char smraw[];
-    __shared__ int sInd[3], sLast;
+    __shared__ int sInd[3], sLast, sHist[ORBX_HISTO_LENGTH];
     __shared__ TriPair P;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     if (tid < (int)(sizeof(TriPair) / 4)) reinterpret_cast<int*>(&P)[tid] = reinterpret_cast<const int*>(pairs + blockIdx.x)[tid];
@@ -275,11 +275,9 @@ triangulation_kernel(const TriPair* __restrict__ pairs, const orbx_keypoint* __r
     __threadfence();
     volatile int* vh = gHist;
     if (checkOri) {
-        if (tid == 0) {
-            int h[ORBX_HISTO_LENGTH];
-            for (int i = 0; i < ORBX_HISTO_LENGTH; ++i) h[i] = vh[i];
-            int i1, i2, i3; three_maxima(h, ORBX_HISTO_LENGTH, i1, i2, i3); sInd[0] = i1; sInd[1] = i2; sInd[2] = i3;
-        }
+        if (tid < ORBX_HISTO_LENGTH) sHist[tid] = vh[tid];                 // 30 loads in flight at once, not one after the other
+        __syncthreads();
+        if (tid == 0) { int i1, i2, i3; three_maxima(sHist, ORBX_HISTO_LENGTH, i1, i2, i3); sInd[0] = i1; sInd[1] = i2; sInd[2] = i3; }
         __syncthreads();
         int culled = 0;
         volatile u8* vb = binOf;
@@ -493,7 +491,7 @@ int orbm_search_for_triangulation(const orbm_keyframe* kf1, const orbm_keyframe*
     const int sKB = ar.in(nullptr, (size_t)totB * sizeof(orbx_keypoint)), sDB = ar.in(nullptr, (size_t)totB * 32), sNB = ar.in(nullptr, (size_t)totB * 4),
               sFB = ar.in(nullptr, (size_t)totB), sUB = ar.in(nullptr, (size_t)totB * 4);
     const int sM = ar.out(matches12, (size_t)totA * 4), sNM = ar.out(nmatches, (size_t)npairs * 4);
-    const int sBin = ar.work((size_t)totA), sState = ar.work((size_t)npairs * TRI_STATE_INTS * 4);
+    const int sBin = ar.work((size_t)totA), sState = ar.inout_fill(nullptr, (size_t)npairs * TRI_STATE_INTS * 4);   // zeroed in the staging buffer: rides on the upload
     rc = ar.layout(); if (rc) return rc;
     auto up = [&](const orbm_keyframe& kf, int off, int k, int d, int nd, int fl, int ur) {
         const orbm_frame& f = kf.frame;
@@ -510,8 +508,8 @@ int orbm_search_for_triangulation(const orbm_keyframe* kf1, const orbm_keyframe*
         up(kf1[p], pairs[p].offA, sKA, sDA, sNA, sFA, sUA);
         up(kf2[p], pairs[p].offB, sKB, sDB, sNB, sFB, sUB);
     }
+    memset(ar.hostp<u8>(sState), 0, ar.segs[sState].bytes);
     rc = ar.upload(); if (rc) return rc;
-    ORBX_CUDA(cudaMemsetAsync(ar.dev<int>(sState), 0, (size_t)npairs * TRI_STATE_INTS * 4, 0));
     if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(triangulation_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // a batch fills the GPU with one CTA per pair; the single pair of a per-keyframe call is spread over up to 16 SMs (32 warps each)
     const int splits = npairs >= 64 ? 1 : std::max(1, std::min(16, std::min(128 / npairs, (maxA + 127) / 128)));

@@ -39,56 +39,80 @@ __device__ __forceinline__ void load_desc(uint32_t a[8], const u8* __restrict__ 
 // distances >= NT stay inside the thread, distances < 32 are warp shuffles, only the ones between go through shared memory --
 // 15 of the 55 steps of a 1024-key sort.  (The plain shared-memory version, a __syncthreads per step, measured 35 us for
 // 1024 keys; this one is the sort of the per-frame BoW / triangulation calls.)
-template <int NT>
-__device__ __forceinline__ void block_sort64(unsigned long long* a, int cap)
+// NA arrays of the same cap are sorted side by side (one set of barriers, independent instruction streams)
+template <int NT, int E, int NA>
+__device__ __forceinline__ void block_sort64_impl(unsigned long long* const (&arr)[NA], int cap)
 {
-    const int tid = threadIdx.x, lane = tid & 31;
-    const int E = cap > 2 * NT ? 4 : (cap > NT ? 2 : 1);
-    unsigned long long v[4];
+    const int tid = threadIdx.x;
+    unsigned long long v[NA][E];
 #pragma unroll
-    for (int r = 0; r < 4; ++r) v[r] = (r < E && r * NT + tid < cap) ? a[r * NT + tid] : ~0ull;
+    for (int s = 0; s < NA; ++s)
+#pragma unroll
+        for (int r = 0; r < E; ++r) v[s][r] = r * NT + tid < cap ? arr[s][r * NT + tid] : ~0ull;
+    // keep the smaller of (mine, other) when takeMin, else the larger (equal keys: either)
+    auto pick = [](unsigned long long mine, unsigned long long other, bool takeMin) { return ((other < mine) == takeMin) ? other : mine; };
     for (int k = 2; k <= cap; k <<= 1) {
         for (int j = k >> 1; j > 0; j >>= 1) {
-            if (j >= NT) {                                   // partners live in the same thread
+            if (j >= NT) {                                   // partners live in the same thread (E > 1 only)
                 auto cx = [&](unsigned long long& x, unsigned long long& y, int r) {      // x = element r * NT + tid, y its partner above
                     const bool asc = ((r * NT + tid) & k) == 0;
                     const unsigned long long lo = x < y ? x : y, hi = x < y ? y : x;
                     x = asc ? lo : hi; y = asc ? hi : lo;
                 };
-                if (j == NT) { cx(v[0], v[1], 0); if (E == 4) cx(v[2], v[3], 2); }
-                else { cx(v[0], v[2], 0); cx(v[1], v[3], 1); }                         // j == 2 * NT, E == 4
+#pragma unroll
+                for (int s = 0; s < NA; ++s) {
+                    if (E >= 2 && j == NT) { cx(v[s][0], v[s][E >= 2 ? 1 : 0], 0); if (E == 4) cx(v[s][E == 4 ? 2 : 0], v[s][E == 4 ? 3 : 0], 2); }
+                    else if (E == 4) { cx(v[s][0], v[s][E == 4 ? 2 : 0], 0); cx(v[s][E == 4 ? 1 : 0], v[s][E == 4 ? 3 : 0], 1); }     // j == 2 * NT
+                }
             } else if (j >= 32) {                            // through shared memory
                 __syncthreads();
 #pragma unroll
-                for (int r = 0; r < 4; ++r) if (r < E && r * NT + tid < cap) a[r * NT + tid] = v[r];
+                for (int s = 0; s < NA; ++s)
+#pragma unroll
+                    for (int r = 0; r < E; ++r) if (r * NT + tid < cap) arr[s][r * NT + tid] = v[s][r];
                 __syncthreads();
 #pragma unroll
-                for (int r = 0; r < 4; ++r) {
-                    const int e = r * NT + tid;
-                    if (r < E && e < cap) {
-                        const unsigned long long o = a[e ^ j];
-                        const bool takeMin = ((e & j) == 0) == ((e & k) == 0);
-                        v[r] = takeMin ? (o < v[r] ? o : v[r]) : (o > v[r] ? o : v[r]);
+                for (int s = 0; s < NA; ++s)
+#pragma unroll
+                    for (int r = 0; r < E; ++r) {
+                        const int e = r * NT + tid;
+                        if (e < cap) v[s][r] = pick(v[s][r], arr[s][e ^ j], ((e & j) == 0) == ((e & k) == 0));
                     }
-                }
             } else {                                         // inside the warp
 #pragma unroll
-                for (int r = 0; r < 4; ++r) {
-                    if (r < E) {
+                for (int s = 0; s < NA; ++s)
+#pragma unroll
+                    for (int r = 0; r < E; ++r) {
                         const int e = r * NT + tid;
-                        const unsigned long long o = __shfl_xor_sync(FULL, v[r], j);
-                        const bool takeMin = ((e & j) == 0) == ((e & k) == 0);
-                        v[r] = takeMin ? (o < v[r] ? o : v[r]) : (o > v[r] ? o : v[r]);
+                        v[s][r] = pick(v[s][r], __shfl_xor_sync(FULL, v[s][r], j), ((e & j) == 0) == ((e & k) == 0));
                     }
-                }
             }
         }
     }
     __syncthreads();
 #pragma unroll
-    for (int r = 0; r < 4; ++r) if (r < E && r * NT + tid < cap) a[r * NT + tid] = v[r];
+    for (int s = 0; s < NA; ++s)
+#pragma unroll
+        for (int r = 0; r < E; ++r) if (r * NT + tid < cap) arr[s][r * NT + tid] = v[s][r];
     __syncthreads();
-    (void)lane;
+}
+
+template <int NT>
+__device__ __forceinline__ void block_sort64(unsigned long long* a, int cap)
+{
+    unsigned long long* const arr[1] = {a};
+    if (cap > 2 * NT) block_sort64_impl<NT, 4, 1>(arr, cap);
+    else if (cap > NT) block_sort64_impl<NT, 2, 1>(arr, cap);
+    else block_sort64_impl<NT, 1, 1>(arr, cap);
+}
+
+// two arrays of the same cap (<= 2 * NT)
+template <int NT>
+__device__ __forceinline__ void block_sort64_pair(unsigned long long* a, unsigned long long* b, int cap)
+{
+    unsigned long long* const arr[2] = {a, b};
+    if (cap > NT) block_sort64_impl<NT, 2, 2>(arr, cap);
+    else block_sort64_impl<NT, 1, 2>(arr, cap);
 }
 
 struct GridParams { float minX, minY, invW, invH; };
@@ -206,6 +230,7 @@ struct CallArena {
     int add(int kind, const void* src, void* dst, size_t bytes) { segs.push_back({kind, src, dst, bytes, 0}); return (int)segs.size() - 1; }
     int in(const void* src, size_t bytes) { return add(0, src, nullptr, bytes); }
     int inout(void* p, size_t bytes) { return add(1, p, p, bytes); }
+    int inout_fill(void* dst, size_t bytes) { return add(1, nullptr, dst, bytes); }    // filled through hostp() before upload(); dst may be null (device-only state)
     int out(void* dst, size_t bytes) { return add(2, nullptr, dst, bytes); }
     int work(size_t bytes) { return add(3, nullptr, nullptr, bytes); }
     int layout()

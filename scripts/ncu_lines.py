@@ -74,18 +74,22 @@ def main():
     per = collections.defaultdict(lambda: [0, 0, 0])
     tot_i = tot_s = 0
     for k in range(n):
-        _, ln, _, _ = lines[k]
+        _, ln, fn, _ = lines[k]
+        ln = (fn, ln)                       # inlined header code keeps its own file
         per[ln][0] += inst[k][1]; per[ln][1] += inst[k][2]; per[ln][2] += inst[k][3]
         tot_i += inst[k][1]; tot_s += inst[k][2]
     src = {}
-    f = lines[0][2] if lines else None
-    if f and os.path.exists(f):
-        src = {i + 1: l.rstrip() for i, l in enumerate(open(f))}
+    for f in {l[2] for l in lines if l[2]}:
+        if os.path.exists(f):
+            for i, l in enumerate(open(f)):
+                src[(f, i + 1)] = l.rstrip()
+    main_file = lines[0][2] if lines else None
     print(f"kernel {kre}: {tot_i} warp instructions, {tot_s} stall samples, {n} SASS instructions")
     print(f"{'inst%':>6} {'smp%':>6} {'lanes':>5}  line  source")
     items = sorted(per.items()) if "--by-line" in sys.argv else sorted(per.items(), key=lambda kv: -kv[1][0])[:top]
     for ln, (i, s, t) in items:
-        print(f"{100 * i / max(tot_i, 1):6.2f} {100 * s / max(tot_s, 1):6.2f} {t / max(i, 1):5.1f}  {ln:4d}  {src.get(ln, '')[:110]}")
+        tag = "" if ln[0] == main_file else "[" + os.path.basename(ln[0] or "?") + "] "
+        print(f"{100 * i / max(tot_i, 1):6.2f} {100 * s / max(tot_s, 1):6.2f} {t / max(i, 1):5.1f}  {ln[1]:4d}  {tag}{src.get(ln, '')[:110]}")
 
 
 if __name__ == "__main__":
