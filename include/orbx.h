@@ -15,6 +15,18 @@
  *    store; it must be used by one thread at a time (same rule as one ORBextractor object,
  *    reference src/Frame.cc:78-79 uses two objects for two threads).
  *  - "slot" = index of a frame inside the handle's device-resident result store.
+ *
+ * Environment variables the library reads (none is needed; results are identical under all of them):
+ *   ORBX_NO_GRAPH=1         orbx_extract / orbx_frame_rgbd launch their kernels plainly instead of replaying the captured graph
+ *   ORBX_LAT_NOFORK=1       single-frame calls: one stream instead of one forked branch per pyramid level
+ *   ORBX_LAT_RS=<rows>, ORBX_LAT_BLUR=<groups>, ORBX_LAT_OT=<128|256|512>
+ *                           single-frame calls: resize strip height, blur launch groups, quadtree CTA size (tuning sweeps)
+ *   ORBX_RS_TARGET=<rows>   batch calls: resize strip height (tuning sweep; disables the graph)
+ *   ORBX_OCTREE_KEYCAP=<n>  force DistributeOctTree onto its global-memory key path above n candidates (test hook)
+ *   ORBX_RGBD_SLICES=<n>    orbx_frame_rgbd: row slices the pageable colour image is staged in (default 4)
+ *   ORBX_NO_SCRATCH_POOL=1  stateless orbm_* calls: cudaMalloc / cudaFree per call instead of the per-thread block cache
+ *   ORBX_PIPE_TRACE=1       batch calls from host memory: chunk timeline (copy / kernels / result copy) to stderr
+ *   ORBX_LAT_TRACE=1        single-frame and stateless matcher calls: phase times (averaged over 50-200 calls) to stderr
  */
 #ifndef ORBX_H
 #define ORBX_H
