@@ -628,7 +628,7 @@ def run_rgbd(args):
     factor = 1.0 / 5000.0
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
-    ex = capi.Extractor(**PARAMS, max_width=W, max_height=H, chunk_frames=args.chunk, result_slots=F, device=0, stream=stream.cuda_stream)
+    ex = capi.Extractor(**PARAMS, max_width=W, max_height=H, chunk_frames=min(args.chunk, 512), result_slots=F, device=0, stream=stream.cuda_stream)
     step = lambda: ex.frames_rgbd_ptr(color.data_ptr(), 3, depth.data_ptr(), True, F, W, H, cam, True, factor, True, 0)
     for _ in range(args.warmup):
         step()
@@ -660,12 +660,12 @@ def run_rgbd(args):
             "value": value, "unit": "frames/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": "SURVEY 8(f) rank 1: RGB-D frame front on TUM1-shaped input", "frames_per_step_per_gpu": F,
-                       "chunk_frames": args.chunk, "l2_policy": f"inputs ({F * W * H * 5 / 1e9:.2f} GB per step) larger than L2"},
+                       "chunk_frames": min(args.chunk, 512), "l2_policy": f"inputs ({F * W * H * 5 / 1e9:.2f} GB per step) larger than L2"},
             "clocks": clk,
             "e2e": {"value": F * args.steps / dt, "unit": "frames/s", "h2d_bytes_per_step": F * W * H * 5,
                     "d2h_bytes_per_step": F * ex.cap * (28 + 32 + 28 + 8) + 4 * F},
             # per chunk: cvt_gray, 7 resize, blur, FAST, quadtree, describe, depth convertTo, frame_front (+ grid build)
-            "gpu_launches": args.steps * (-(-F // args.chunk)) * (PARAMS["nlevels"] - 1 + 8),
+            "gpu_launches": args.steps * (-(-F // min(args.chunk, 512))) * (PARAMS["nlevels"] - 1 + 8),
             "roofline": {"bound": "hbm", "kernel": "path", "achieved": ab * value / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": ab * value / 1e9 / peak, "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_frame": ab}}
     emit(line)
@@ -986,7 +986,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--frames", type=int, default=4096)
-    ap.add_argument("--chunk", type=int, default=512)
+    ap.add_argument("--chunk", type=int, default=2048, help="frames per device-resident chunk (handle capacity); the pipeline from host images runs on 256-frame chunks inside the library (ORBX_HOST_CHUNK)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-hamming", action="store_true", help="skip the config-5 leg of the default line (profiling runs)")
     ap.add_argument("--workload", default="frames", choices=["frames", "hd", "stereo", "knn", "rgbd", "single", "rgbd_single", "matcher_calls"],
@@ -1185,7 +1185,7 @@ def main():
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": workload_name,
-                   "frames_per_step_per_gpu": F, "chunk_frames": args.chunk, "keypoints_per_frame": nkp,
+                   "frames_per_step_per_gpu": F, "chunk_frames": args.chunk, "e2e_chunk_frames": min(args.chunk, int(os.environ.get("ORBX_HOST_CHUNK", "256"))), "keypoints_per_frame": nkp,
                    "l2_policy": f"inputs ({F * W * H / 1e9:.2f} GB per step) larger than L2", "sharding": "frames by rank, no collective", "rank_cpu_binding": numa},
         "clocks": clk,
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

@@ -25,6 +25,7 @@
  *   ORBX_OCTREE_KEYCAP=<n>  force DistributeOctTree onto its global-memory key path above n candidates (test hook)
  *   ORBX_RGBD_SLICES=<n>    orbx_frame_rgbd: row slices the pageable colour image is staged in (default 4)
  *   ORBX_NO_SCRATCH_POOL=1  stateless orbm_* calls: cudaMalloc / cudaFree per call instead of the per-thread block cache
+ *   ORBX_HOST_CHUNK=<n>     batch calls from host memory: frames per pipelined chunk (default 256, at most the handle's chunk_frames)
  *   ORBX_PIPE_TRACE=1       batch calls from host memory: chunk timeline (copy / kernels / result copy) to stderr
  *   ORBX_LAT_TRACE=1        single-frame and stateless matcher calls: phase times (averaged over 50-200 calls) to stderr
  */

@@ -419,12 +419,18 @@ static int batch_to_host_impl(orbx_handle* h, const uint8_t* images, size_t fram
     for (int f0 = 0, nf = 0; f0 < nframes; f0 += nf, ++chunkNo) {
         // host images: ramp the first two chunks (1/4, 1/2 of a chunk) so that less of the first
         // host->device copy is exposed before the kernels start
-        int cf = h->chunkFrames;
-        if (!direct && nframes > h->chunkFrames) cf = chunkNo == 0 ? std::max(1, cf / 4) : (chunkNo == 1 ? std::max(1, cf / 2) : cf);
+        // The pipeline from host images is bound by the copy (55 GB/s = 5.9 us per 640x480 frame against 4.8 us of kernels), and
+        // what it exposes is the first copy and the kernels + result copy of the last chunk: it runs on smaller chunks
+        // (hostChunk, 256 frames unless ORBX_HOST_CHUNK says otherwise) than device-resident batches, which only pay the
+        // per-chunk launch ramps (measured: 256 -> 156 k frames/s end to end, 512 -> 151 k, 1024 -> 140 k).
+        static const int hostChunkEnv = getenv("ORBX_HOST_CHUNK") ? std::max(1, atoi(getenv("ORBX_HOST_CHUNK"))) : 256;
+        const int full = direct ? h->chunkFrames : std::min(h->chunkFrames, hostChunkEnv);
+        int cf = full;
+        if (!direct && nframes > full) cf = chunkNo == 0 ? std::max(1, cf / 4) : (chunkNo == 1 ? std::max(1, cf / 2) : cf);
         nf = std::min(cf, nframes - f0);
         // ... and taper the tail the same way: the kernels and the device->host copy of the last chunk are exposed
-        if (!direct && toHost && nframes > h->chunkFrames && nf == nframes - f0 && nf > std::max(1, h->chunkFrames / 4))
-            nf = std::max(std::max(1, h->chunkFrames / 4), (nf + 1) / 2);
+        if (!direct && toHost && nframes > full && nf == nframes - f0 && nf > std::max(1, full / 4))
+            nf = std::max(std::max(1, full / 4), (nf + 1) / 2);
         const uint8_t* src = images + (size_t)f0 * frame_stride;
         Level0 l0;
         l0.base1 = nullptr; l0.stereo = 0;
