@@ -17,7 +17,7 @@ for w in single rgbd_single matcher_calls; do
   timeout 600 python bench.py --workload $w > gpurun_out/${T}_bench_$w.json 2> gpurun_out/${T}_bench_$w.err; echo "$w rc=$?"; cut -c1-160 gpurun_out/${T}_bench_$w.json
 done
 LCMD="python bench.py --steps 2 --warmup 3 --no-cpu --no-hamming"
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${T}_launches.csv $LCMD > gpurun_out/${T}_launches.log 2>&1; echo "launch list rc=$?"
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"pyr_|blur7|fast_|octree|describe|grid_build|search_init|repitch|knn2" --csv --log-file gpurun_out/${T}_launches.csv $LCMD > gpurun_out/${T}_launches.log 2>&1; echo "launch list rc=$?"
 CMD="python bench.py --frames 2048 --chunk 2048 --steps 1 --warmup 3 --no-cpu --no-hamming"
 $CMD > gpurun_out/${T}_ncu_plain.log 2>&1 || exit 1
 timeout 1500 ncu --set full --clock-control none --import-source on -k regex:'pyr_|blur7|fast_|octree|describe_kernel|grid_build|search_init' -s 39 -c 13 \
