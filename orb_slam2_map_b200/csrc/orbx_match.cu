@@ -1820,7 +1820,8 @@ int orbm_compute_stereo_matches(const orbm_stereo_input* in, float* u_right, flo
     for (int l = 0; l < in->nlevels; ++l)
         for (int e = 0; e < 2; ++e) sLv[e][l] = ar.in(nullptr, (size_t)((in->level_width[l] + 15) & ~15) * in->level_height[l]);
     unsigned long long c = 0;
-    const int sU = ar.out(u_right, (size_t)in->n_left * 4), sZ = ar.out(depth, (size_t)in->n_left * 4), sC = ar.out(&c, 8);
+    // the kernel fills uRight / depth up to the store's capacity (max of both eyes), the caller gets the left keypoints' part
+    const int sU = ar.out(u_right, (size_t)in->n_left * 4, (size_t)cap * 4), sZ = ar.out(depth, (size_t)in->n_left * 4, (size_t)cap * 4), sC = ar.out(&c, 8);
     const int sS = ar.work((size_t)cap * 4);
     rc = ar.layout(); if (rc) return rc;
     if (in->n_left) {

@@ -218,7 +218,7 @@ inline bool orbx_lat_trace_on() { static const bool on = getenv("ORBX_LAT_TRACE"
 // out / work return an id), commit() lays them out, stages and uploads; dev<T>(id) is the segment on the device; finish()
 // downloads, waits and hands the outputs back.  All work on the legacy default stream, like the kernels of these calls.
 struct CallArena {
-    struct Seg { int kind; const void* src; void* dst; size_t bytes, off; };
+    struct Seg { int kind; const void* src; void* dst; size_t bytes, off, room; };    // room: bytes laid out (>= bytes copied)
     std::vector<Seg> segs;
     DevBuf arena;
     PhaseTrace pt{orbx_lat_trace_on()};
@@ -227,11 +227,11 @@ struct CallArena {
     void trace(const char* n, double* a, int* c) { name = n; acc = a; calls = c; }
     u8* host = nullptr; u8* device = nullptr;
     size_t upBytes = 0, downBegin = 0, downEnd = 0;
-    int add(int kind, const void* src, void* dst, size_t bytes) { segs.push_back({kind, src, dst, bytes, 0}); return (int)segs.size() - 1; }
+    int add(int kind, const void* src, void* dst, size_t bytes, size_t room = 0) { segs.push_back({kind, src, dst, bytes, 0, std::max(bytes, room)}); return (int)segs.size() - 1; }
     int in(const void* src, size_t bytes) { return add(0, src, nullptr, bytes); }
     int inout(void* p, size_t bytes) { return add(1, p, p, bytes); }
     int inout_fill(void* dst, size_t bytes) { return add(1, nullptr, dst, bytes); }    // filled through hostp() before upload(); dst may be null (device-only state)
-    int out(void* dst, size_t bytes) { return add(2, nullptr, dst, bytes); }
+    int out(void* dst, size_t bytes, size_t room = 0) { return add(2, nullptr, dst, bytes, room); }    // room: what the kernels may write
     int work(size_t bytes) { return add(3, nullptr, nullptr, bytes); }
     int layout()
     {
@@ -240,7 +240,7 @@ struct CallArena {
             if (kind == 1) downBegin = off;
             if (kind == 2) upBytes = off;
             if (kind == 3) downEnd = off;
-            for (Seg& s : segs) if (s.kind == kind) { s.off = off; off += (s.bytes + 255) & ~(size_t)255; }
+            for (Seg& s : segs) if (s.kind == kind) { s.off = off; off += (s.room + 255) & ~(size_t)255; }
         }
         int rc = arena.alloc(off ? off : 256); if (rc) return rc;
         if ((rc = orbx_scratch_host((void**)&host, downEnd ? downEnd : 256))) return rc;

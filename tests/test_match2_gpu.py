@@ -143,6 +143,14 @@ def test_compute_stereo_matches_stateless(w, h, nf, seed):
     assert c_g == c_o
     assert np.array_equal(u_g, u_o) and np.array_equal(z_g, z_o)
     assert (u_o >= 0).sum() > 100
+    # fewer left than right keypoints (found by the randomised soak: the kernel fills uRight / depth up to the larger count, which
+    # must not spill into what follows them on the device) and the eyes the other way round
+    for a, b in ((slice(0, len(kl) // 2), slice(None)), (slice(None), slice(0, len(kr) // 3))):
+        for swap in (False, True):
+            args = (kr[b], dr[b], kl[a], dl[a], pr, pl) if swap else (kl[a], dl[a], kr[b], dr[b], pl, pr)
+            u_o, z_o, c_o = O.compute_stereo_matches(*args, t["scale"], t["inv_scale"], bf, fx)
+            u_g, z_g, c_g = capi.compute_stereo_matches(*args, t["scale"], t["inv_scale"], bf, fx)
+            assert c_g == c_o and np.array_equal(u_g, u_o) and np.array_equal(z_g, z_o)
 
 
 def test_extract_stereo_batch_fused():
