@@ -72,6 +72,15 @@ struct ScratchPool {
 thread_local ScratchPool g_scratch;
 }
 
+cudaStream_t orbx_call_stream()
+{
+    thread_local cudaStream_t st[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
+    if (!st[dev] && cudaStreamCreateWithFlags(&st[dev], cudaStreamNonBlocking) != cudaSuccess) { st[dev] = 0; cudaGetLastError(); }
+    return st[dev];                              // 0 (the legacy stream) only if no stream could be made
+}
+
 int orbx_scratch_alloc(void** p, size_t bytes)
 {
     static const bool pooled = !getenv("ORBX_NO_SCRATCH_POOL");

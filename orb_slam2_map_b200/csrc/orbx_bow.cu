@@ -374,7 +374,7 @@ int orbm_bow_transform(orbm_vocab_handle* v, const uint8_t* features, int n, int
     const int sF = ar.in(features, (size_t)n * 32);
     const int sWt = ar.out(weight, (size_t)n * 8), sW = ar.out(word_id, (size_t)n * 4), sN = ar.out(node_id, (size_t)n * 4);
     int rc = ar.commit(); if (rc) return rc;
-    bow_transform_kernel<<<(n + 7) / 8, 256>>>(v->childBegin, v->childCount, v->children, v->desc, v->word, v->weight, v->depth,
+    bow_transform_kernel<<<(n + 7) / 8, 256, 0, ar.st>>>(v->childBegin, v->childCount, v->children, v->desc, v->word, v->weight, v->depth,
                                                ar.dev<u8>(sF), n, levelsup, ar.dev<uint32_t>(sW), ar.dev<double>(sWt), ar.dev<uint32_t>(sN));
     return ar.finish();
 }
@@ -442,7 +442,7 @@ int orbm_search_by_bow(int variant, const orbm_bow_frame* a, const orbm_bow_fram
     if (!attrSet) { ORBX_CUDA(cudaFuncSetAttribute(search_bow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024)); attrSet = true; }
     // a batch fills the GPU with one CTA per pair; the single pair of a per-frame call is spread over up to 8 SMs (32 warps each)
     const int splits = npairs >= 64 ? 1 : std::max(1, std::min(8, std::min(128 / npairs, (maxA + 255) / 256)));
-    search_bow_kernel<<<dim3(npairs, splits), BOW_THREADS, smem>>>(variant, ar.dev<BowPair>(sPairs), ar.dev<u8>(sDescA), ar.dev<float>(sAngA), ar.dev<uint32_t>(sNodeA),
+    search_bow_kernel<<<dim3(npairs, splits), BOW_THREADS, smem, ar.st>>>(variant, ar.dev<BowPair>(sPairs), ar.dev<u8>(sDescA), ar.dev<float>(sAngA), ar.dev<uint32_t>(sNodeA),
                                                      ar.dev<u8>(sFlagA), ar.dev<u8>(sDescB), ar.dev<float>(sAngB), ar.dev<uint32_t>(sNodeB), ar.dev<u8>(sFlagB),
                                                      nnratio, check_orientation, capA, capB, ar.dev<int32_t>(sMA), ar.dev<int32_t>(sMB), ar.dev<int32_t>(sNM),
                                                      ar.dev<u8>(sBin), ar.dev<int>(sState), stage);
@@ -475,7 +475,7 @@ int orbm_distinctive_descriptors(const uint8_t* descriptors, const int32_t* offs
     int rc = ar.commit(); if (rc) return rc;
     const int smem = std::min(maxN, DD_SMEM_DESC) * 32 + 16;
     if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(distinctive_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    distinctive_kernel<<<npoints, DD_THREADS, smem>>>(ar.dev<u8>(sDesc), ar.dev<int32_t>(sOff), ar.dev<int32_t>(sIdx), ar.dev<int32_t>(sMed));
+    distinctive_kernel<<<npoints, DD_THREADS, smem, ar.st>>>(ar.dev<u8>(sDesc), ar.dev<int32_t>(sOff), ar.dev<int32_t>(sIdx), ar.dev<int32_t>(sMed));
     return ar.finish();
 }
 

@@ -185,6 +185,10 @@ void orbx_prof_mark(orbx_handle* h, int stage);
 // power-of-two size classes, so a call repeated every frame does no cudaMalloc / cudaFree after its first time.
 // A block is reused only by the thread that released it, on the same (legacy default) stream: stream order makes the
 // reuse safe even if the previous call's kernels were still in flight.
+// The stream of the stateless orbm_* calls: one non-blocking stream per calling thread and device, so that calls from
+// Tracking / LocalMapping / LoopClosing threads neither serialise on the legacy default stream nor wait for the extractor handles'
+// streams.  A thread's scratch blocks are reused by that thread on this stream only (stream order keeps the reuse safe).
+cudaStream_t orbx_call_stream();
 int orbx_scratch_alloc(void** p, size_t bytes);
 void orbx_scratch_free(void* p);
 int orbx_scratch_host(void** p, size_t bytes);     // this thread's pinned staging buffer (grown on demand, kept)

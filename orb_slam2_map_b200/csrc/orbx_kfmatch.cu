@@ -337,7 +337,7 @@ struct ArenaKeyFrame {
         fs.kps = ar.dev<orbx_keypoint>(sKps); fs.desc = ar.dev<u8>(sDesc); fs.count = ar.dev<int>(sCount);
         fs.gridStart = ar.dev<unsigned short>(sGS); fs.gridIdx = ar.dev<unsigned short>(sGI); fs.cap = std::max(n, 8);
         args.gp = orbx_grid_params(f->min_x, f->max_x, f->min_y, f->max_y);
-        if (needGrid) { const int rc = orbx_launch_grid_build(fs, 0, 1, args.gp, 0); if (rc) return rc; }
+        if (needGrid) { const int rc = orbx_launch_grid_build(fs, 0, 1, args.gp, ar.st); if (rc) return rc; }
         args.fs = fs;
         args.uRight = sUR >= 0 ? ar.dev<float>(sUR) : nullptr;
         args.variant = variant;
@@ -361,7 +361,7 @@ struct ArenaQueries {
     void launch(CallArena& ar, const AreaBestArgs& a, int nq)
     {
         if (nq > 0)
-            area_best_kernel<<<(nq + AB_WARPS - 1) / AB_WARPS, AB_WARPS * 32>>>(a, ar.dev<orbm_proj_query>(sQ), ar.dev<u8>(sD), nq, ar.dev<int>(sBI), ar.dev<int>(sBD));
+            area_best_kernel<<<(nq + AB_WARPS - 1) / AB_WARPS, AB_WARPS * 32, 0, ar.st>>>(a, ar.dev<orbm_proj_query>(sQ), ar.dev<u8>(sD), nq, ar.dev<int>(sBI), ar.dev<int>(sBD));
     }
     AreaSweepLeg leg(CallArena& ar, const AreaBestArgs& a, int nq, int n)
     {
@@ -372,12 +372,12 @@ struct ArenaQueries {
     }
 };
 
-static void launch_area_sweep(const AreaSweepLeg& g0, const AreaSweepLeg* g1)
+static void launch_area_sweep(const AreaSweepLeg& g0, const AreaSweepLeg* g1, cudaStream_t st)
 {
     AreaSweepLegs L;
     L.leg[0] = g0; L.leg[1] = g1 ? *g1 : g0;
     const int nq = std::max(g0.nq, g1 ? g1->nq : 0);
-    if (nq > 0) area_best_sweep_kernel<<<dim3((nq + AB_WARPS - 1) / AB_WARPS, g1 ? 2 : 1), AB_WARPS * 32>>>(L);
+    if (nq > 0) area_best_sweep_kernel<<<dim3((nq + AB_WARPS - 1) / AB_WARPS, g1 ? 2 : 1), AB_WARPS * 32, 0, st>>>(L);
 }
 
 extern "C" {
@@ -400,7 +400,7 @@ int orbm_fuse(int variant, const orbm_keyframe* kf, const orbm_proj_query* queri
     rc = ar.commit(); if (rc) return rc;
     AreaBestArgs args;
     rc = dk.ready(ar, kf, variant, args, !dk.sweep()); if (rc) return rc;
-    if (dk.sweep()) launch_area_sweep(dq.leg(ar, args, nq, dk.n), nullptr);
+    if (dk.sweep()) launch_area_sweep(dq.leg(ar, args, nq, dk.n), nullptr, ar.st);
     else dq.launch(ar, args, nq);
     return ar.finish();
 }
@@ -438,12 +438,12 @@ int orbm_search_by_sim3(const orbm_keyframe* kf1, const orbm_keyframe* kf2, cons
     rc = d2.ready(ar, kf2, ORBM_FUSE_SIM3_LEG, a2, !sweep); if (rc) return rc;
     if (sweep) {
         const AreaSweepLeg g12 = q12.leg(ar, a2, nq12, d2.n), g21 = q21.leg(ar, a1, nq21, d1.n);   // points of KF1 searched in KF2 and back, one launch
-        launch_area_sweep(g12, &g21);
+        launch_area_sweep(g12, &g21, ar.st);
     } else {
         q12.launch(ar, a2, nq12);
         q21.launch(ar, a1, nq21);
     }
-    sim3_agree_kernel<<<1, 256>>>(ar.dev<int>(q12.sBI), ar.dev<int>(sI1), nq12, ar.dev<int>(q21.sBI), ar.dev<int>(sI2), nq21, n1, n2,
+    sim3_agree_kernel<<<1, 256, 0, ar.st>>>(ar.dev<int>(q12.sBI), ar.dev<int>(sI1), nq12, ar.dev<int>(q21.sBI), ar.dev<int>(sI2), nq21, n1, n2,
                                   ar.dev<int>(sM1), ar.dev<int>(sM2), ar.dev<int>(sM12), ar.dev<int>(sNf));
     rc = ar.finish(); if (rc) return rc;
     if (nfound) *nfound = nf;
@@ -513,7 +513,7 @@ int orbm_search_for_triangulation(const orbm_keyframe* kf1, const orbm_keyframe*
     if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(triangulation_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // a batch fills the GPU with one CTA per pair; the single pair of a per-keyframe call is spread over up to 16 SMs (32 warps each)
     const int splits = npairs >= 64 ? 1 : std::max(1, std::min(16, std::min(128 / npairs, (maxA + 127) / 128)));
-    triangulation_kernel<<<dim3(npairs, splits), TRI_THREADS, smem>>>(ar.dev<TriPair>(sPairs), ar.dev<orbx_keypoint>(sKA), ar.dev<u8>(sDA), ar.dev<uint32_t>(sNA),
+    triangulation_kernel<<<dim3(npairs, splits), TRI_THREADS, smem, ar.st>>>(ar.dev<TriPair>(sPairs), ar.dev<orbx_keypoint>(sKA), ar.dev<u8>(sDA), ar.dev<uint32_t>(sNA),
                                                         ar.dev<u8>(sFA), ar.dev<float>(sUA), ar.dev<orbx_keypoint>(sKB), ar.dev<u8>(sDB),
                                                         ar.dev<uint32_t>(sNB), ar.dev<u8>(sFB), ar.dev<float>(sUB), only_stereo, check_orientation,
                                                         capB, ar.dev<int32_t>(sM), ar.dev<int32_t>(sNM), ar.dev<u8>(sBin), ar.dev<int>(sState));

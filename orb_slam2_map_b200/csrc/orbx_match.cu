@@ -1629,9 +1629,10 @@ int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, f
         memcpy(host + oDesc + cap * 32, f2->descriptors, (size_t)f2->n * 32);
     }
     PhaseTrace pt(orbx_lat_trace_on());
-    pt.mark("start");
-    ORBX_CUDA(cudaMemcpyAsync(dev, host, upBytes, cudaMemcpyHostToDevice, 0));
-    pt.mark("h2d");
+    cudaStream_t st = orbx_call_stream();
+    pt.mark("start", st);
+    ORBX_CUDA(cudaMemcpyAsync(dev, host, upBytes, cudaMemcpyHostToDevice, st));
+    pt.mark("h2d", st);
     FrameStore fs;
     fs.kps = reinterpret_cast<orbx_keypoint*>(dev + oKps); fs.desc = dev + oDesc; fs.count = reinterpret_cast<int*>(dev + oCount);
     fs.gridStart = reinterpret_cast<unsigned short*>(dev + oGS); fs.gridIdx = reinterpret_cast<unsigned short*>(dev + oGI);
@@ -1646,26 +1647,26 @@ int orbm_search_for_initialization(const orbm_frame* f1, const orbm_frame* f2, f
         unsigned long long* dKeys = reinterpret_cast<unsigned long long*>(dev + oKeys);
         float* dPrev = reinterpret_cast<float*>(dev + oPrev);
         if (f1->n > 0)
-            si_list_kernel<<<(f1->n + PROJ_LIST_WARPS - 1) / PROJ_LIST_WARPS, PROJ_LIST_WARPS * 32>>>(ps, fs.kps, fs.desc, dPrev, f1->n, (float)window_size, dkeep, dKeys);
-        pt.mark("lists");
+            si_list_kernel<<<(f1->n + PROJ_LIST_WARPS - 1) / PROJ_LIST_WARPS, PROJ_LIST_WARPS * 32, 0, st>>>(ps, fs.kps, fs.desc, dPrev, f1->n, (float)window_size, dkeep, dKeys);
+        pt.mark("lists", st);
         const int fixSmem = (int)(((((size_t)4 * f1->n + f2->n) * sizeof(int) + 15) & ~(size_t)15) + (PROJ_FIX_THREADS / 32) * PROJ_SCAN_BUF * 8);
         static bool attrSet = false;
         if (!attrSet) { ORBX_CUDA(cudaFuncSetAttribute(si_fixpoint_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 5 * PROJ_SCAN_MAXN * 4 + 16 + (PROJ_FIX_THREADS / 32) * PROJ_SCAN_BUF * 8)); attrSet = true; }
-        si_fixpoint_kernel<<<1, PROJ_FIX_THREADS, fixSmem>>>(ps, fs.kps, fs.desc, dPrev, f1->n, (float)window_size, dkeep, nnratio, check_orientation, dKeys,
+        si_fixpoint_kernel<<<1, PROJ_FIX_THREADS, fixSmem, st>>>(ps, fs.kps, fs.desc, dPrev, f1->n, (float)window_size, dkeep, nnratio, check_orientation, dKeys,
                                                              reinterpret_cast<int*>(dev + oM12), reinterpret_cast<int*>(dev + oNm), reinterpret_cast<int*>(dev + oDirty));
-        pt.mark("fixpoint");
+        pt.mark("fixpoint", st);
     } else {
-        rc = orbx_launch_grid_build(fs, 1, 1, gp, 0); if (rc) return rc;
-        pt.mark("grid");
+        rc = orbx_launch_grid_build(fs, 1, 1, gp, st); if (rc) return rc;
+        pt.mark("grid", st);
         rc = launch_search_init(fs, 0, 1, 1, gp, reinterpret_cast<float*>(dev + oPrev), window_size, nnratio, check_orientation,
-                                reinterpret_cast<int*>(dev + oM12), reinterpret_cast<int*>(dev + oNm), nullptr, 0);
+                                reinterpret_cast<int*>(dev + oM12), reinterpret_cast<int*>(dev + oNm), nullptr, st);
         if (rc) return rc;
-        pt.mark("search");
+        pt.mark("search", st);
     }
     ORBX_CUDA(cudaGetLastError());
-    ORBX_CUDA(cudaMemcpyAsync(host + oPrev, dev + oPrev, downBytes, cudaMemcpyDeviceToHost, 0));
-    pt.mark("d2h");
-    ORBX_CUDA(cudaStreamSynchronize(0));
+    ORBX_CUDA(cudaMemcpyAsync(host + oPrev, dev + oPrev, downBytes, cudaMemcpyDeviceToHost, st));
+    pt.mark("d2h", st);
+    ORBX_CUDA(cudaStreamSynchronize(st));
     { static double acc[PhaseTrace::MAXP]; static int calls = 0; pt.report("search_for_initialization", acc, calls); }
     int nm = 0;
     memcpy(&nm, host + oNm, 4);
@@ -1724,9 +1725,10 @@ int orbm_search_by_projection(int variant, const orbm_frame* frame, const orbm_p
         if (query_blocks) memcpy(host + oQB, query_blocks, (size_t)nq);
     }
     PhaseTrace pt(orbx_lat_trace_on());
-    pt.mark("start");
-    ORBX_CUDA(cudaMemcpyAsync(dev, host, upBytes, cudaMemcpyHostToDevice, 0));
-    pt.mark("h2d");
+    cudaStream_t st = orbx_call_stream();
+    pt.mark("start", st);
+    ORBX_CUDA(cudaMemcpyAsync(dev, host, upBytes, cudaMemcpyHostToDevice, st));
+    pt.mark("h2d", st);
     FrameStore fs;
     fs.kps = reinterpret_cast<orbx_keypoint*>(dev + oKps); fs.desc = dev + oDesc; fs.count = reinterpret_cast<int*>(dev + oCount);
     fs.gridStart = reinterpret_cast<unsigned short*>(dev + oGS); fs.gridIdx = reinterpret_cast<unsigned short*>(dev + oGI);
@@ -1741,35 +1743,35 @@ int orbm_search_by_projection(int variant, const orbm_frame* frame, const orbm_p
         ps.kps = fs.kps; ps.desc = fs.desc; ps.uRight = dUR; ps.gp = gp; ps.n = frame->n;
         ps.gate = (variant == ORBM_PROJ_LOCALMAP || variant == ORBM_PROJ_LASTFRAME) && dUR != nullptr;
         if (nq > 0)
-            proj_list_kernel<<<(nq + PROJ_LIST_WARPS - 1) / PROJ_LIST_WARPS, PROJ_LIST_WARPS * 32>>>(ps, dQ, dev + oQD, nq, dev + oOcc, dKeys);
-        pt.mark("lists");
+            proj_list_kernel<<<(nq + PROJ_LIST_WARPS - 1) / PROJ_LIST_WARPS, PROJ_LIST_WARPS * 32, 0, st>>>(ps, dQ, dev + oQD, nq, dev + oOcc, dKeys);
+        pt.mark("lists", st);
         const int fixSmem = (int)((((size_t)2 * frame->n * sizeof(int) + 15) & ~(size_t)15) + (PROJ_FIX_THREADS / 32) * PROJ_SCAN_BUF * 8);
         static bool attrSet = false;
         if (!attrSet) { ORBX_CUDA(cudaFuncSetAttribute(proj_fixpoint_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * PROJ_SCAN_MAXN * 4 + 16 + (PROJ_FIX_THREADS / 32) * PROJ_SCAN_BUF * 8)); attrSet = true; }
-        proj_fixpoint_kernel<<<1, PROJ_FIX_THREADS, fixSmem>>>(ps, dQ, dev + oQD, nq, query_blocks ? dev + oQB : nullptr, dev + oOcc,
+        proj_fixpoint_kernel<<<1, PROJ_FIX_THREADS, fixSmem, st>>>(ps, dQ, dev + oQD, nq, query_blocks ? dev + oQB : nullptr, dev + oOcc,
                                                                reinterpret_cast<int*>(dev + oAsg), reinterpret_cast<int*>(dev + oBI),
                                                                reinterpret_cast<int*>(dev + oBD), variant, th_dist, nnratio, check_orientation,
                                                                reinterpret_cast<int*>(dev + oNm), dKeys, reinterpret_cast<int*>(dev + oBin), nullptr);
-        pt.mark("fixpoint");
+        pt.mark("fixpoint", st);
     } else {
-        rc = orbx_launch_grid_build(fs, 0, 1, gp, 0); if (rc) return rc;
-        pt.mark("grid");
+        rc = orbx_launch_grid_build(fs, 0, 1, gp, st); if (rc) return rc;
+        pt.mark("grid", st);
         if (nq > 0)
-            search_proj_cand_kernel<<<(nq + PROJ_WARPS - 1) / PROJ_WARPS, PROJ_WARPS * 32>>>(
+            search_proj_cand_kernel<<<(nq + PROJ_WARPS - 1) / PROJ_WARPS, PROJ_WARPS * 32, 0, st>>>(
                 fs, 0, gp, dUR, dQ, dev + oQD, nq, dev + oOcc, variant, dKeys, dKA);
-        pt.mark("cand");
+        pt.mark("cand", st);
         const int occSmem = (std::max(frame->n, 1) + 15) & ~15;          // n <= 65000 (check_frame)
         if (occSmem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(search_proj_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, occSmem));
-        search_proj_kernel<<<1, 32, occSmem>>>(fs, 0, gp, dUR, dQ, dev + oQD, nq, query_blocks ? dev + oQB : nullptr, dev + oOcc,
+        search_proj_kernel<<<1, 32, occSmem, st>>>(fs, 0, gp, dUR, dQ, dev + oQD, nq, query_blocks ? dev + oQB : nullptr, dev + oOcc,
                                                reinterpret_cast<int*>(dev + oAsg), reinterpret_cast<int*>(dev + oBI),
                                                reinterpret_cast<int*>(dev + oBD), dev + oBin, variant, th_dist, nnratio,
                                                check_orientation, reinterpret_cast<int*>(dev + oNm), dKeys, dKA);
-        pt.mark("replay");
+        pt.mark("replay", st);
     }
     ORBX_CUDA(cudaGetLastError());
-    ORBX_CUDA(cudaMemcpyAsync(host + oOcc, dev + oOcc, downBytes, cudaMemcpyDeviceToHost, 0));
-    pt.mark("d2h");
-    ORBX_CUDA(cudaStreamSynchronize(0));
+    ORBX_CUDA(cudaMemcpyAsync(host + oOcc, dev + oOcc, downBytes, cudaMemcpyDeviceToHost, st));
+    pt.mark("d2h", st);
+    ORBX_CUDA(cudaStreamSynchronize(st));
     { static double acc[PhaseTrace::MAXP]; static int calls = 0; pt.report("search_by_projection", acc, calls); }
     int nm = 0;
     memcpy(&nm, host + oNm, 4);
@@ -1849,12 +1851,12 @@ int orbm_compute_stereo_matches(const orbm_stereo_input* in, float* u_right, flo
         }
     }
     rc = ar.upload(); if (rc) return rc;
-    ORBX_CUDA(cudaMemsetAsync(ar.dev<u8>(sC), 0, 8, 0));
+    ORBX_CUDA(cudaMemsetAsync(ar.dev<u8>(sC), 0, 8, ar.st));
     FrameStore fs;
     fs.kps = ar.dev<orbx_keypoint>(sKps); fs.desc = ar.dev<u8>(sDesc); fs.count = ar.dev<int>(sCount);
     fs.gridStart = nullptr; fs.gridIdx = nullptr; fs.cap = cap;
     rc = launch_stereo(fs, 0, 1, pv, in->bf, in->fx, cap, ar.dev<float>(sU), ar.dev<float>(sZ), ar.dev<int>(sS),
-                       ar.dev<unsigned long long>(sC), 0);
+                       ar.dev<unsigned long long>(sC), ar.st);
     if (rc) return rc;
     rc = ar.finish(); if (rc) return rc;
     if (ncompares) *ncompares = c;

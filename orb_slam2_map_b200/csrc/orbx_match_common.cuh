@@ -198,7 +198,7 @@ struct PhaseTrace {
     static const int MAXP = 8;
     bool on; int np; cudaEvent_t ev[MAXP]; const char* tag[MAXP];
     explicit PhaseTrace(bool enable) : on(enable), np(0) {}
-    void mark(const char* t) { if (!on || np >= MAXP) return; cudaEventCreate(&ev[np]); cudaEventRecord(ev[np], 0); tag[np++] = t; }
+    void mark(const char* t, cudaStream_t st) { if (!on || np >= MAXP) return; cudaEventCreate(&ev[np]); cudaEventRecord(ev[np], st); tag[np++] = t; }
     void report(const char* name, double* acc, int& calls) {
         if (!on) return;
         for (int i = 1; i < np; ++i) { float ms = 0; cudaEventElapsedTime(&ms, ev[i - 1], ev[i]); acc[i] += ms * 1000.0; }
@@ -216,12 +216,13 @@ inline bool orbx_lat_trace_on() { static const bool on = getenv("ORBX_LAT_TRACE"
 // call uploads goes up in ONE copy and everything it returns comes back in ONE copy (a dozen small synchronous copies of
 // pageable memory cost 10-20 us each, more than the kernels of a per-frame call).  Segments are declared first (in / inout /
 // out / work return an id), commit() lays them out, stages and uploads; dev<T>(id) is the segment on the device; finish()
-// downloads, waits and hands the outputs back.  All work on the legacy default stream, like the kernels of these calls.
+// downloads, waits and hands the outputs back.  All work on the calling thread's own stream (orbx_call_stream).
 struct CallArena {
     struct Seg { int kind; const void* src; void* dst; size_t bytes, off, room; };    // room: bytes laid out (>= bytes copied)
     std::vector<Seg> segs;
     DevBuf arena;
     PhaseTrace pt{orbx_lat_trace_on()};
+    cudaStream_t st = orbx_call_stream();          // every copy and kernel of the call
     const char* name = "call";          // static storage: keys the ORBX_LAT_TRACE accumulators
     double* acc = nullptr; int* calls = nullptr;
     void trace(const char* n, double* a, int* c) { name = n; acc = a; calls = c; }
@@ -250,9 +251,9 @@ struct CallArena {
     int upload()
     {
         for (const Seg& s : segs) if (s.kind <= 1 && s.bytes && s.src) memcpy(host + s.off, s.src, s.bytes);
-        pt.mark("start");
-        if (upBytes) ORBX_CUDA(cudaMemcpyAsync(device, host, upBytes, cudaMemcpyHostToDevice, 0));
-        pt.mark("h2d");
+        pt.mark("start", st);
+        if (upBytes) ORBX_CUDA(cudaMemcpyAsync(device, host, upBytes, cudaMemcpyHostToDevice, st));
+        pt.mark("h2d", st);
         return ORBX_OK;
     }
     int commit() { const int rc = layout(); return rc ? rc : upload(); }
@@ -261,10 +262,10 @@ struct CallArena {
     int finish()
     {
         ORBX_CUDA(cudaGetLastError());
-        pt.mark("kernels");
-        if (downEnd > downBegin) ORBX_CUDA(cudaMemcpyAsync(host + downBegin, device + downBegin, downEnd - downBegin, cudaMemcpyDeviceToHost, 0));
-        pt.mark("d2h");
-        ORBX_CUDA(cudaStreamSynchronize(0));
+        pt.mark("kernels", st);
+        if (downEnd > downBegin) ORBX_CUDA(cudaMemcpyAsync(host + downBegin, device + downBegin, downEnd - downBegin, cudaMemcpyDeviceToHost, st));
+        pt.mark("d2h", st);
+        ORBX_CUDA(cudaStreamSynchronize(st));
         if (acc) pt.report(name, acc, *calls);
         for (const Seg& s : segs) if ((s.kind == 1 || s.kind == 2) && s.bytes && s.dst) memcpy(s.dst, host + s.off, s.bytes);
         return ORBX_OK;
