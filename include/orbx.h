@@ -512,6 +512,17 @@ int orbm_generate_point_clouds(const float* depth, size_t depth_row_stride, size
  * would overflow PCL's int voxel index (PCL then returns the cloud unfiltered) or when capacity is too small. */
 int orbm_voxel_grid(const orbx_cloud_point* points, int n, float leaf, int device, orbx_cloud_point* out, int capacity, int32_t* nout);
 
+/* pcl::StatisticalOutlierRemoval<pcl::PointXYZRGBA> as PointCloudMapping applies it to the global map before saving it
+ * (src/PointCloudMap.cc:46-47 setMeanK(50) / setStddevMulThresh(1.0), :284-285 sor.setInputCloud(globalMapRGBD); sor.filter(*tmp)):
+ * every finite point's mean distance to its mean_k nearest neighbours (exact search; squared distances accumulated in float as
+ * FLANN's L2_Simple does, square roots summed in double in ascending order), mean and standard deviation of those distances,
+ * points with distance > mean + stddev_mul * stddev removed, input order kept.  Non-finite points get distance 0 and stay; with
+ * fewer than mean_k + 1 finite points everything stays.  1 <= mean_k <= 127.
+ * points: n records (host); out: room for `capacity` records (NULL: only count); *nout = points kept; mean_dist: NULL or n floats;
+ * stats: NULL or 5 doubles (threshold, mean, stddev, points with a valid distance, fraction of tile pairs the search visited). */
+int orbm_statistical_outlier_removal(const orbx_cloud_point* points, int64_t n, int mean_k, double stddev_mul, int device,
+                                     orbx_cloud_point* out, int64_t capacity, int64_t* nout, float* mean_dist, double* stats);
+
 /* The per-feature record of Map::Save's keyframe block (src/Map.cc:160-180): 64 bytes = pt.x, pt.y, size, angle,
  * response (float), octave (int), the 32 descriptor bytes, and the unsigned long index of the feature's MapPoint
  * (ULONG_MAX = none).  Packs the features of result slot `slot` (mvKeys, mDescriptors as the extractor left them on

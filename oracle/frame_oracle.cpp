@@ -229,4 +229,63 @@ size_t oracle_write_keyframe_features(const uint8_t* kps, const uint8_t* desc, c
     return (size_t)(f - out);
 }
 
+// pcl::StatisticalOutlierRemoval<PointXYZRGBA>::applyFilterIndices as PointCloudMapping uses it on the global map
+// (reference src/PointCloudMap.cc:46-47 setMeanK(50), setStddevMulThresh(1.0); :284-285 sor.setInputCloud / sor.filter).
+// PARITY UNPINNED: PCL is an external dependency that is absent from /root/reference (no version is pinned there either);
+// this restates the published algorithm of PCL 1.7-1.9, filters/impl/statistical_outlier_removal.hpp:
+//   searcher_k = mean_k + 1 nearest neighbours of every finite point (the point itself is result 0); squared distances as FLANN's
+//   L2_Simple<float> accumulates them (result += diff * diff over x, y, z in float); dist_sum += sqrt(nn_dists[k]) in double for
+//   k = 1 .. mean_k in ascending order (plain sqrt on a float argument: the double overload in those versions);
+//   distances[i] = (float)(dist_sum / mean_k); non-finite points and points whose search returns fewer neighbours get 0.0 and are
+//   not counted; sum += d, sq_sum += d * d (float product) serially in double; mean = sum / valid; variance = (sq_sum - sum * sum /
+//   valid) / (valid - 1); threshold = mean + mul * sqrt(variance); a point is removed when distances[i] > threshold.
+// The k nearest neighbours are found by brute force (exact, like the kd-tree with eps = 0; ties at the k-th distance change
+// nothing because equal distances add equal terms).  points / out: 16-byte records.  stats: threshold, mean, stddev, valid.
+long long oracle_statistical_outlier_removal(const uint8_t* points, long long n, int mean_k, double mul, uint8_t* out,
+                                             float* mean_dist, double* stats)
+{
+    struct P { float x, y, z; uint8_t b, g, r, a; };
+    const P* p = reinterpret_cast<const P*>(points);
+    P* o = reinterpret_cast<P*>(out);
+    const int K = mean_k + 1;
+    std::vector<float> distances((size_t)n, 0.0f), heap;
+    long long finite = 0;
+    for (long long i = 0; i < n; ++i) finite += std::isfinite(p[i].x) && std::isfinite(p[i].y) && std::isfinite(p[i].z);
+    long long valid = 0;
+    for (long long i = 0; i < n; ++i) {
+        if (!std::isfinite(p[i].x) || !std::isfinite(p[i].y) || !std::isfinite(p[i].z)) continue;
+        if (finite < K) continue;                                  // nearestKSearch returns fewer than searcher_k results
+        heap.clear();                                              // max-heap of the K smallest squared distances
+        for (long long j = 0; j < n; ++j) {
+            if (!std::isfinite(p[j].x) || !std::isfinite(p[j].y) || !std::isfinite(p[j].z)) continue;
+            float d2 = 0.0f;
+            const float dx = p[i].x - p[j].x; d2 += dx * dx;
+            const float dy = p[i].y - p[j].y; d2 += dy * dy;
+            const float dz = p[i].z - p[j].z; d2 += dz * dz;
+            if ((int)heap.size() < K) { heap.push_back(d2); std::push_heap(heap.begin(), heap.end()); }
+            else if (d2 < heap.front()) { std::pop_heap(heap.begin(), heap.end()); heap.back() = d2; std::push_heap(heap.begin(), heap.end()); }
+        }
+        std::sort(heap.begin(), heap.end());
+        double dist_sum = 0.0;
+        for (int k = 1; k < K; ++k) dist_sum += std::sqrt((double)heap[k]);
+        distances[i] = static_cast<float>(dist_sum / mean_k);
+        ++valid;
+    }
+    double sum = 0, sq_sum = 0;
+    for (long long i = 0; i < n; ++i) { sum += distances[i]; sq_sum += distances[i] * distances[i]; }
+    const double mean = sum / static_cast<double>(valid);
+    const double variance = (sq_sum - sum * sum / static_cast<double>(valid)) / (static_cast<double>(valid) - 1);
+    const double stddev = std::sqrt(variance);
+    const double thr = mean + mul * stddev;
+    long long kept = 0;
+    for (long long i = 0; i < n; ++i) {
+        if (distances[i] > thr) continue;
+        if (o) o[kept] = p[i];
+        ++kept;
+    }
+    if (mean_dist) for (long long i = 0; i < n; ++i) mean_dist[i] = distances[i];
+    if (stats) { stats[0] = thr; stats[1] = mean; stats[2] = stddev; stats[3] = (double)valid; }
+    return kept;
+}
+
 } // extern "C"

@@ -59,7 +59,7 @@ EXPORTS = [
     "orbx_keypoint_capacity", "orbx_reserve_shape", "orbx_extract", "orbx_extract_batch", "orbx_extract_batch_to_host", "orbx_download", "orbx_get_level",
     "orbx_get_candidates", "orbx_search_init_pairs", "orbx_extract_stereo_batch",
     "orbm_descriptor_distance", "orbm_search_for_initialization", "orbm_search_by_projection",
-    "orbm_compute_stereo_matches", "orbm_knn2_device", "orbm_knn2_device_noalloc", "orbm_knn2_merge_device", "orbm_knn2_set_variant",
+    "orbm_compute_stereo_matches", "orbm_knn2_device", "orbm_knn2_device_noalloc", "orbm_statistical_outlier_removal", "orbm_knn2_merge_device", "orbm_knn2_set_variant",
     "orbm_measure_int_rates", "orbm_nccl_unique_id", "orbm_nccl_comm_create", "orbm_nccl_comm_destroy", "orbm_knn2_sharded",
     "orbx_cvt_gray", "orbx_depth_to_float", "orbx_undistort_points", "orbx_image_bounds", "orbx_frames_rgbd", "orbx_frame_rgbd",
     "orbx_download_frame_front",
@@ -672,3 +672,17 @@ def voxel_grid(points: np.ndarray, leaf: float, device=0, capacity=None):
     out = np.zeros(max(capacity, 1), CLOUD_DTYPE)
     check(lib().orbm_voxel_grid(C.c_void_p(pts.ctypes.data), len(pts), C.c_float(leaf), device, C.c_void_p(out.ctypes.data), capacity, C.byref(n)))
     return out[:n.value].copy()
+
+
+def statistical_outlier_removal(points: np.ndarray, mean_k: int = 50, stddev_mul: float = 1.0, device=0):
+    """orbm_statistical_outlier_removal -> (kept points, mean distance per input point, [threshold, mean, stddev, valid, visited])"""
+    pts = np.ascontiguousarray(points, CLOUD_DTYPE)
+    out = np.zeros(max(len(pts), 1), CLOUD_DTYPE)
+    md = np.zeros(max(len(pts), 1), np.float32)
+    st = np.zeros(5, np.float64)
+    n = C.c_int64(0)
+    f = lib().orbm_statistical_outlier_removal
+    f.argtypes = [C.c_void_p, C.c_int64, C.c_int, C.c_double, C.c_int, C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_void_p]
+    check(f(pts.ctypes.data_as(C.c_void_p), len(pts), int(mean_k), float(stddev_mul), device, out.ctypes.data_as(C.c_void_p), len(out),
+            C.byref(n), md.ctypes.data_as(C.c_void_p), st.ctypes.data_as(C.c_void_p)))
+    return out[:n.value].copy(), md[:len(pts)].copy(), st

@@ -485,3 +485,15 @@ def voxel_grid(points: np.ndarray, leaf: float):
     n = lib().oracle_voxel_grid(_p(pts), C.c_int(len(pts)), C.c_float(leaf), _p(out), C.c_int(len(out)))
     assert n >= 0, n
     return out[:n].copy()
+
+
+def statistical_outlier_removal(points: np.ndarray, mean_k: int = 50, stddev_mul: float = 1.0):
+    """-> (kept points, mean distance per input point, [threshold, mean, stddev, valid])"""
+    pts = np.ascontiguousarray(points, CLOUD_DTYPE)
+    out = np.zeros(max(len(pts), 1), CLOUD_DTYPE)
+    md = np.zeros(max(len(pts), 1), np.float32)
+    st = np.zeros(4, np.float64)
+    f = lib().oracle_statistical_outlier_removal
+    f.restype = C.c_longlong
+    n = f(_p(pts), C.c_longlong(len(pts)), C.c_int(mean_k), C.c_double(stddev_mul), _p(out), _p(md), _p(st))
+    return out[:n].copy(), md[:len(pts)].copy(), st
