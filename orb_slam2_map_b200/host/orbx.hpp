@@ -501,5 +501,28 @@ inline std::vector<orbx_cloud_point> GeneratePointCloud(const float* depth, size
     return pts;
 }
 
+// voxel.setInputCloud(cloud); voxel.filter(*tmp) with voxel.setLeafSize(resolution, resolution, resolution)
+// (src/PointCloudMap.cc:41, 240-241, 259-260, 277-280)
+inline std::vector<orbx_cloud_point> VoxelGridFilter(const std::vector<orbx_cloud_point>& cloud, float resolution, int device = 0)
+{
+    std::vector<orbx_cloud_point> out(cloud.size());
+    int32_t n = 0;
+    if (!cloud.empty()) check(orbm_voxel_grid(cloud.data(), (int)cloud.size(), resolution, device, out.data(), (int)out.size(), &n), "VoxelGrid::filter");
+    out.resize((size_t)n);
+    return out;
+}
+
+// sor.setMeanK(meanK); sor.setStddevMulThresh(mul); sor.setInputCloud(globalMap); sor.filter(*tmp)
+// (src/PointCloudMap.cc:46-47, 284-285)
+inline std::vector<orbx_cloud_point> StatisticalOutlierFilter(const std::vector<orbx_cloud_point>& cloud, int meanK = 50, double mul = 1.0, int device = 0)
+{
+    std::vector<orbx_cloud_point> out(cloud.size());
+    int64_t n = 0;
+    if (!cloud.empty()) check(orbm_statistical_outlier_removal(cloud.data(), (int64_t)cloud.size(), meanK, mul, device, out.data(), (int64_t)out.size(),
+                                                               &n, nullptr, nullptr), "StatisticalOutlierRemoval::filter");
+    out.resize((size_t)n);
+    return out;
+}
+
 } // namespace orbx
 #endif

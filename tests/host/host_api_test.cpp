@@ -98,6 +98,14 @@ int main(int argc, char** argv)
         int32_t nc = (int32_t)cloud.size();
         fwrite(&nc, 4, 1, o);
         fwrite(cloud.data(), 16, nc, o);
+        // the rest of PointCloudMapping's chain: voxel.filter at resolution 0.04, then sor.filter (mean_k 50, multiplier 1.0)
+        const std::vector<orbx_cloud_point> vox = orbx::VoxelGridFilter(cloud, 0.04f);
+        const std::vector<orbx_cloud_point> kept = orbx::StatisticalOutlierFilter(vox, 50, 1.0);
+        int32_t nv = (int32_t)vox.size(), nk = (int32_t)kept.size();
+        fwrite(&nv, 4, 1, o);
+        fwrite(vox.data(), 16, nv, o);
+        fwrite(&nk, 4, 1, o);
+        fwrite(kept.data(), 16, nk, o);
     } catch (const std::exception& e) {
         fprintf(stderr, "host_api_test: %s\n", e.what());
         fclose(o);

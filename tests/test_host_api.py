@@ -105,4 +105,12 @@ def test_host_classes_match_oracle(tmp_path):
     exp = O.generate_point_cloud(frames[0].astype(np.float32) / np.float32(32.0), None, np.float32(517.3), np.float32(516.5),
                                  np.float32(318.6), np.float32(255.3), pose_inv=Tinv)
     assert nc == len(exp) and cloud.tobytes() == exp.tobytes()
+    nv, = struct.unpack_from("<i", buf, pos); pos += 4
+    vox = np.frombuffer(buf, O.CLOUD_DTYPE, nv, pos); pos += 16 * nv
+    vo = O.voxel_grid(exp, 0.04)
+    assert nv == len(vo) and vox.tobytes() == vo.tobytes() and nv > 1000
+    nk, = struct.unpack_from("<i", buf, pos); pos += 4
+    kept = np.frombuffer(buf, O.CLOUD_DTYPE, nk, pos); pos += 16 * nk
+    ko, _, _ = O.statistical_outlier_removal(vo, 50, 1.0)
+    assert nk == len(ko) and kept.tobytes() == ko.tobytes() and 0 < nk < nv
     assert pos == len(buf)
