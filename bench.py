@@ -645,9 +645,14 @@ def run_rgbd(args):
     hc = torch.empty(color.shape, dtype=torch.uint8, pin_memory=True); hc.copy_(color)
     hd = torch.empty(depth.shape, dtype=torch.uint16, pin_memory=True); hd.copy_(depth)
     torch.cuda.synchronize()
+    # results land in page-locked buffers that are allocated once (a caller's Frame objects own theirs)
+    pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True).numpy()
+    cap = ex.cap
+    o_kp = pin((F, cap, 28), torch.uint8).view(capi.KP_DTYPE).reshape(F, cap); o_de = pin((F, cap, 32), torch.uint8)
+    o_un = pin((F, cap, 28), torch.uint8).view(capi.KP_DTYPE).reshape(F, cap); o_ur = pin((F, cap), torch.float32); o_z = pin((F, cap), torch.float32)
     def e2e():
         ex.frames_rgbd_ptr(hc.data_ptr(), 3, hd.data_ptr(), True, F, W, H, cam, True, factor, False, 0)
-        ex.download(0, F); ex.download_frame_front(0, F)
+        ex.download(0, F, out=(o_kp, o_de)); ex.download_frame_front(0, F, out=(o_un, o_ur, o_z))
     e2e()
     t0 = time.perf_counter()
     for _ in range(args.steps):

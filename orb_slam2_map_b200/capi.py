@@ -340,10 +340,14 @@ class Extractor:
                                      C.c_size_t(height * width * es), C.c_size_t(width * es), width, height, nframes, int(on_device),
                                      C.byref(cam), first_slot))
 
-    def download_frame_front(self, first_slot, nframes):
-        kun = np.zeros((nframes, self.cap), KP_DTYPE)
-        ur = np.zeros((nframes, self.cap), np.float32)
-        z = np.zeros((nframes, self.cap), np.float32)
+    def download_frame_front(self, first_slot, nframes, out=None):
+        """out: (mvKeysUn [nframes, cap] KP_DTYPE, mvuRight [nframes, cap] f32, mvDepth [nframes, cap] f32) to fill (e.g. page-locked)"""
+        if out is not None:
+            kun, ur, z = out
+        else:
+            kun = np.zeros((nframes, self.cap), KP_DTYPE)
+            ur = np.zeros((nframes, self.cap), np.float32)
+            z = np.zeros((nframes, self.cap), np.float32)
         b = np.zeros(4, np.float32)
         check(lib().orbx_download_frame_front(self.h, first_slot, nframes, kun.ctypes.data_as(C.c_void_p), ur.ctypes.data_as(C.c_void_p),
                                               z.ctypes.data_as(C.c_void_p), self.cap, b.ctypes.data_as(C.c_void_p)))
