@@ -1133,6 +1133,19 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = world * F * args.steps / float(t.item())
+    # the same call on PAGEABLE buffers (what a std::vector<cv::Mat> and the Frame members are): the driver stages every copy through
+    # its own page-locked buffers, so this is the rate a caller sees without cudaHostRegister; rank 0, informational
+    e2e_pageable = None
+    if rank == 0 and match:
+        pg_in = np.array(hnp, copy=True)
+        pg = (np.zeros_like(kp_out), np.zeros_like(de_out), np.zeros_like(cnt_out), np.zeros_like(m12_out), np.zeros_like(nm_out))
+        ex.extract_match_to_host(pg_in, *pg, WINDOW, NNRATIO, True)
+        t0 = time.perf_counter()
+        for _ in range(max(1, args.steps // 2)):
+            ex.extract_match_to_host(pg_in, *pg, WINDOW, NNRATIO, True)
+        torch.cuda.synchronize()
+        e2e_pageable = F * max(1, args.steps // 2) / (time.perf_counter() - t0)
+        del pg_in, pg
     h2d = F * W * H
     # the same pinned input copied alone: the PCIe bound of the end-to-end number (images are the input, they must cross)
     pcie_dst = torch.empty((F, H, W), dtype=torch.uint8, device=dev)
@@ -1194,7 +1207,8 @@ def main():
                    "l2_policy": f"inputs ({F * W * H / 1e9:.2f} GB per step) larger than L2", "sharding": "frames by rank, no collective", "rank_cpu_binding": numa},
         "clocks": clk,
         "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "h2d_gbs_measured": h2d_gbs, "pcie_bound_frames_s": world * h2d_gbs * 1e9 / (W * H)},
+                "h2d_gbs_measured": h2d_gbs, "pcie_bound_frames_s": world * h2d_gbs * 1e9 / (W * H),
+                "pageable_buffers_frames_s_rank0": e2e_pageable},
         "gpu_launches": int(sum(stage_launches.values())),
         "roofline": roofline,
         "path_roofline": {"algorithmic_bytes_per_frame": ab["total"], "achieved": path_gbs, "peak": peak,

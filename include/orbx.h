@@ -122,8 +122,10 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* images, size_t frame_strid
 
 /* Same, with the results also delivered to HOST buffers (kps[nframes][capacity],
  * desc[nframes][capacity][32], counts[nframes]; any may be NULL): the host->device copy of chunk
- * i+1 and the device->host copy of chunk i-1 overlap the kernels of chunk i (pinned buffers
- * recommended).  Synchronous when any output pointer is given. */
+ * i+1 and the device->host copy of chunk i-1 overlap the kernels of chunk i.  Pass PAGE-LOCKED buffers
+ * (cudaHostAlloc, or cudaHostRegister once on buffers that are reused): measured 156 k frames/s (640x480) from
+ * page-locked memory against 25 k frames/s from pageable memory, where the driver stages every copy synchronously.
+ * Synchronous when any output pointer is given. */
 int orbx_extract_batch_to_host(orbx_handle* h, const uint8_t* images, size_t frame_stride,
                                size_t row_stride, int width, int height, int nframes,
                                int images_on_device, int first_slot, orbx_keypoint* kps,

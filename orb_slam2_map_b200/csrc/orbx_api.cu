@@ -99,7 +99,8 @@ int orbx_scratch_alloc(void** p, size_t bytes)
 int orbx_scratch_host(void** p, size_t bytes)
 {
     if (g_scratch.hostBytes < bytes) {
-        if (g_scratch.host) { cudaDeviceSynchronize(); cudaFreeHost(g_scratch.host); g_scratch.host = nullptr; g_scratch.hostBytes = 0; }
+        // the buffer belongs to this thread's calls, which all end with a synchronisation of its stream: nothing else can be using it
+        if (g_scratch.host) { cudaStreamSynchronize(orbx_call_stream()); cudaFreeHost(g_scratch.host); g_scratch.host = nullptr; g_scratch.hostBytes = 0; }
         size_t sz = 1 << 16;
         while (sz < bytes) sz <<= 1;
         ORBX_CUDA(cudaMallocHost(&g_scratch.host, sz));

@@ -1580,14 +1580,11 @@ int orbm_descriptor_distance(const uint8_t* a, const uint8_t* b, int count, int3
     if (!a || !b || !dist) { orbx_set_error("null argument"); return ORBX_E_INVALID; }
     int rc = require_device();
     if (rc) return rc;
-    DevBuf bA, bB, bD;
-    if ((rc = bA.alloc((size_t)count * 32)) || (rc = bB.alloc((size_t)count * 32)) || (rc = bD.alloc((size_t)count * 4))) return rc;
-    u8 *da = bA.as<u8>(), *db = bB.as<u8>(); int* dd = bD.as<int>();
-    ORBX_CUDA(cudaMemcpy(da, a, (size_t)count * 32, cudaMemcpyHostToDevice));
-    ORBX_CUDA(cudaMemcpy(db, b, (size_t)count * 32, cudaMemcpyHostToDevice));
-    hamming_pairs_kernel<<<(count + 255) / 256, 256>>>(da, db, count, dd);
-    ORBX_CUDA(cudaGetLastError());
-    ORBX_CUDA(cudaMemcpy(dist, dd, (size_t)count * 4, cudaMemcpyDeviceToHost));
+    CallArena ar;
+    const int sA = ar.in(a, (size_t)count * 32), sB = ar.in(b, (size_t)count * 32), sD = ar.out(dist, (size_t)count * 4);
+    if ((rc = ar.commit())) return rc;
+    hamming_pairs_kernel<<<(count + 255) / 256, 256, 0, ar.st>>>(ar.dev<u8>(sA), ar.dev<u8>(sB), count, ar.dev<int>(sD));
+    if ((rc = ar.finish())) return rc;
     return ORBX_OK;
 }
 
