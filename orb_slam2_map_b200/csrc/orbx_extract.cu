@@ -446,6 +446,10 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
             const int lg = lane & ((1 << gshift) - 1), ly = lane >> gshift, rstep = 32 >> gshift;
             const uint32_t T = (uint32_t)(0x7f - min(minTh, 0x7e)) * 0x01010101u;
             const bool packedOk = minTh < 0x7f;
+            // low thresholds let a quarter of the pixels through the compass test: two more diameters in the packed test halve that
+            // (an arc of 9 holds one end of EVERY diameter) and with it the per-candidate work behind; at high thresholds the
+            // handful of candidates does not pay for it
+            const bool diag = packedOk && minTh <= 10;
             uint32_t vmask0 = 0, vmask1 = 0;                    // valid pixels of this group
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -475,6 +479,17 @@ fast_cells_kernel(Geom g, const Cell* __restrict__ cells, Level0 l0, const u8* _
                         const uint32_t es1 = ((ds1 & 0x7f7f7f7fu) + T) | ds1, ew1 = ((dw1 & 0x7f7f7f7fu) + T) | dw1;
                         p0 &= (en0 | es0) & (ee0 | ew0);
                         p1 &= (en1 | es1) & (ee1 | ew1);
+                        if (diag) {
+                            // the two diagonal diameters (+-2, +-2) of the ring, same test: rows y+3+-2, bytes centre +- 2.
+                            // (the "-2" word of pixels 4..7 is the "+2" word of pixels 0..3)
+                            const uint2 ua = *reinterpret_cast<const uint2*>(rc + 2 * tw), ub = *reinterpret_cast<const uint2*>(rc + 2 * tw + 2);
+                            const uint2 la = *reinterpret_cast<const uint2*>(rc - 2 * tw), lb = *reinterpret_cast<const uint2*>(rc - 2 * tw + 2);
+                            const uint32_t uM0 = __byte_perm(ua.x, ua.y, 0x4321), uP0 = __byte_perm(ua.y, ub.x, 0x4321), uP1 = __byte_perm(ub.x, ub.y, 0x4321);
+                            const uint32_t lM0 = __byte_perm(la.x, la.y, 0x4321), lP0 = __byte_perm(la.y, lb.x, 0x4321), lP1 = __byte_perm(lb.x, lb.y, 0x4321);
+                            auto far = [T](uint32_t r, uint32_t v) { const uint32_t d = __vabsdiffu4(r, v); return ((d & 0x7f7f7f7fu) + T) | d; };
+                            p0 &= (far(uP0, V0) | far(lM0, V0)) & (far(lP0, V0) | far(uM0, V0));
+                            p1 &= (far(uP1, V1) | far(lP0, V1)) & (far(lP1, V1) | far(uP0, V1));
+                        }
                     }
                     // gather the four 0x80 flags of each word into a nibble (multiply trick: no carries collide)
                     const uint32_t m8 = (((p0 >> 7) * 0x01020408u) >> 24) | ((((p1 >> 7) * 0x01020408u) >> 20) & 0xf0u);
