@@ -26,6 +26,8 @@
  *   ORBX_RGBD_SLICES=<n>    orbx_frame_rgbd: row slices the pageable colour image is staged in (default 4)
  *   ORBX_NO_SCRATCH_POOL=1  stateless orbm_* calls: cudaMalloc / cudaFree per call instead of the per-thread block cache
  *   ORBX_HOST_CHUNK=<n>     batch calls from host memory: frames per pipelined chunk (default 256, at most the handle's chunk_frames)
+ *   ORBX_HOST_THREADS=<n>   batch calls from PAGEABLE host memory: host threads that copy to / from the page-locked pools (default min(8, cores))
+ *   ORBX_NO_HOST_POOL=1     batch calls from PAGEABLE host memory: let the driver stage the copies (no pools)
  *   ORBX_PIPE_TRACE=1       batch calls from host memory: chunk timeline (copy / kernels / result copy) to stderr
  *   ORBX_LAT_TRACE=1        single-frame and stateless matcher calls: phase times (averaged over 50-200 calls) to stderr
  */
@@ -122,10 +124,11 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* images, size_t frame_strid
 
 /* Same, with the results also delivered to HOST buffers (kps[nframes][capacity],
  * desc[nframes][capacity][32], counts[nframes]; any may be NULL): the host->device copy of chunk
- * i+1 and the device->host copy of chunk i-1 overlap the kernels of chunk i.  Pass PAGE-LOCKED buffers
- * (cudaHostAlloc, or cudaHostRegister once on buffers that are reused): measured 156 k frames/s (640x480) from
- * page-locked memory against 25 k frames/s from pageable memory, where the driver stages every copy synchronously.
- * Synchronous when any output pointer is given. */
+ * i+1 and the device->host copy of chunk i-1 overlap the kernels of chunk i.  PAGE-LOCKED buffers (cudaHostAlloc, or
+ * cudaHostRegister once on buffers that are reused) are copied directly: 159 k frames/s at 640x480.  PAGEABLE buffers go
+ * through page-locked pools of the handle (host threads copy the images in, results are handed over one chunk later):
+ * 70 k frames/s (25 k when the driver stages the copies itself, ORBX_NO_HOST_POOL=1).  Records beyond counts[f] of a frame
+ * are unspecified.  Synchronous when any output pointer is given. */
 int orbx_extract_batch_to_host(orbx_handle* h, const uint8_t* images, size_t frame_stride,
                                size_t row_stride, int width, int height, int nframes,
                                int images_on_device, int first_slot, orbx_keypoint* kps,

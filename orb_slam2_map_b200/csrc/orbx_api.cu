@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <vector>
+#include <thread>
 
 static thread_local char g_err[512] = "";
 
@@ -245,6 +246,9 @@ int orbx_create(const orbx_params* params, int max_width, int max_height, int ch
     for (int s = 0; s < ORBX_NSTAGES; ++s) { h->stageMs[s] = 0.0; h->stageLaunches[s] = 0; }
     h->stream = h->copyStream = h->d2hStream = nullptr; h->ownStream = false; h->evDone = nullptr;
     for (int b = 0; b < ORBX_L0_BUFS; ++b) { h->evCopied[b] = h->evFree[b] = nullptr; h->evFreeValid[b] = false; }
+    for (int b = 0; b < ORBX_L0_BUFS; ++b) { h->hInPool[b] = nullptr; h->evInPool[b] = nullptr; h->evInPoolValid[b] = false; }
+    for (int b = 0; b < 2; ++b) { h->hOutPool[b] = nullptr; h->evOutPool[b] = nullptr; }
+    h->hInPoolBytes = h->hOutPoolBytes = 0;
     h->kpCap = 0;
     memset(&h->geom, 0, sizeof(h->geom));
     const int rc = create_impl(h, params, result_slots, stream);
@@ -333,6 +337,8 @@ int orbx_destroy(orbx_handle* h)
     for (void* p : ptrs) if (p) cudaFree(p);
     if (h->hStage) cudaFreeHost(h->hStage);
     if (h->hPack) cudaFreeHost(h->hPack);
+    for (int b = 0; b < ORBX_L0_BUFS; ++b) { if (h->hInPool[b]) cudaFreeHost(h->hInPool[b]); if (h->evInPool[b]) cudaEventDestroy(h->evInPool[b]); }
+    for (int b = 0; b < 2; ++b) { if (h->hOutPool[b]) cudaFreeHost(h->hOutPool[b]); if (h->evOutPool[b]) cudaEventDestroy(h->evOutPool[b]); }
     if (h->evPack) cudaEventDestroy(h->evPack);
     orbx_drop_graph(h);
     for (cudaStream_t x : h->sideStreams) cudaStreamDestroy(x);
@@ -389,6 +395,62 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* images, size_t frame_strid
 
 } // extern "C"
 
+// ---- staging pool of the batch pipeline for pageable caller buffers -------------------------------------------------
+static bool is_pageable(const void* p)
+{
+    if (!p) return false;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return true; }
+    return a.type == cudaMemoryTypeUnregistered;
+}
+
+// f(begin, end) over [0, n) on a few host threads (ORBX_HOST_THREADS, default min(8, cores)); the caller's thread takes a share
+template <class F>
+static void host_parallel_for(int n, F f)
+{
+    static const int maxT = [] {
+        const char* e = getenv("ORBX_HOST_THREADS");
+        const int hw = (int)std::thread::hardware_concurrency();
+        return std::max(1, e ? atoi(e) : std::min(8, hw > 0 ? hw : 1));
+    }();
+    const int T = std::min(n, maxT);
+    if (T <= 1) { if (n > 0) f(0, n); return; }
+    const int per = (n + T - 1) / T;
+    std::vector<std::thread> th;
+    for (int t = 1; t < T; ++t) { const int a = t * per, b = std::min(n, a + per); if (a < b) th.emplace_back([=] { f(a, b); }); }
+    f(0, std::min(per, n));
+    for (std::thread& x : th) x.join();
+}
+
+static int ensure_in_pool(orbx_handle* h, size_t bytes)
+{
+    if (h->hInPoolBytes >= bytes) return ORBX_OK;
+    for (int b = 0; b < ORBX_L0_BUFS; ++b) {
+        if (h->evInPoolValid[b]) { cudaEventSynchronize(h->evInPool[b]); h->evInPoolValid[b] = false; }
+        if (h->hInPool[b]) { cudaFreeHost(h->hInPool[b]); h->hInPool[b] = nullptr; }
+    }
+    h->hInPoolBytes = 0;
+    for (int b = 0; b < ORBX_L0_BUFS; ++b) {
+        ORBX_CUDA(cudaMallocHost((void**)&h->hInPool[b], bytes));
+        if (!h->evInPool[b]) ORBX_CUDA(cudaEventCreateWithFlags(&h->evInPool[b], cudaEventDisableTiming));
+    }
+    h->hInPoolBytes = bytes;
+    return ORBX_OK;
+}
+
+static int ensure_out_pool(orbx_handle* h, size_t bytes)
+{
+    if (h->hOutPoolBytes >= bytes) return ORBX_OK;
+    for (int b = 0; b < 2; ++b) if (h->hOutPool[b]) { cudaFreeHost(h->hOutPool[b]); h->hOutPool[b] = nullptr; }
+    h->hOutPoolBytes = 0;
+    for (int b = 0; b < 2; ++b) {
+        ORBX_CUDA(cudaMallocHost((void**)&h->hOutPool[b], bytes));
+        if (!h->evOutPool[b]) ORBX_CUDA(cudaEventCreateWithFlags(&h->evOutPool[b], cudaEventDisableTiming));
+    }
+    h->hOutPoolBytes = bytes;
+    return ORBX_OK;
+}
+
 // consecutive-frame SearchForInitialization folded into the chunk pipeline (orbx_extract_match_to_host)
 struct MatchOpts { int window; float nnratio; int checkOri; int32_t* matches12; int32_t* nmatches; };
 
@@ -420,6 +482,43 @@ static int batch_to_host_impl(orbx_handle* h, const uint8_t* images, size_t fram
         ORBX_CUDA(cudaStreamWaitEvent(h->copyStream, evStart, 0));
         ORBX_CUDA(cudaEventDestroy(evStart));
     }
+    static const int hostChunkEnv = getenv("ORBX_HOST_CHUNK") ? std::max(1, atoi(getenv("ORBX_HOST_CHUNK"))) : 256;
+    const int full = direct ? h->chunkFrames : std::min(h->chunkFrames, hostChunkEnv);
+    // Pageable caller buffers: a driver-staged copy blocks the host until it is done, which serialises copy / kernels / copy.
+    // They go through the handle's page-locked pools instead: inputs are copied there by a few host threads and uploaded from
+    // there, results land there and are handed over one chunk later (25 k -> [see DESIGN 5] frames/s at 640x480).
+    static const bool noPool = getenv("ORBX_NO_HOST_POOL") != nullptr;
+    const bool stageIn = !noPool && !images_on_device && is_pageable(images);
+    const bool stageOut = !noPool && toHost && (is_pageable(kps) || is_pageable(desc) || is_pageable(counts) ||
+                                                (mo && (is_pageable(mo->matches12) || is_pageable(mo->nmatches))));
+    const size_t tightFrame = (size_t)width * height;
+    if (stageIn) { rc = ensure_in_pool(h, (size_t)full * tightFrame); if (rc) return rc; }
+    // result pool layout of one chunk: [mvKeys][descriptors][counts][matches12][nmatches], each sized for `full` frames
+    const size_t oK = 0, oD = oK + (size_t)full * h->kpCap * sizeof(orbx_keypoint), oC = oD + (size_t)full * h->kpCap * 32,
+                 oM = oC + (((size_t)full * 4 + 15) & ~(size_t)15), oN = oM + (size_t)full * h->kpCap * 4, outBytes = oN + (size_t)full * 4;
+    if (stageOut) { rc = ensure_out_pool(h, outBytes); if (rc) return rc; }
+    struct Pending { bool live; int f0, nf, p0, np, ob; } pend = {false, 0, 0, 0, 0, 0};
+    auto flush = [&](const Pending& P) -> int {       // hand a finished chunk's results from the pool to the caller
+        ORBX_CUDA(cudaEventSynchronize(h->evOutPool[P.ob]));
+        const uint8_t* S = h->hOutPool[P.ob];
+        const int32_t* cnt = reinterpret_cast<const int32_t*>(S + oC);
+        host_parallel_for(P.nf, [&](int a, int b) {
+            for (int f = a; f < b; ++f) {
+                const size_t c = (size_t)std::min(std::max(cnt[f], 0), h->kpCap);     // only the records that exist
+                if (kps) memcpy(kps + (size_t)(P.f0 + f) * capacity, S + oK + (size_t)f * h->kpCap * sizeof(orbx_keypoint), c * sizeof(orbx_keypoint));
+                if (desc) memcpy(desc + (size_t)(P.f0 + f) * capacity * 32, S + oD + (size_t)f * h->kpCap * 32, c * 32);
+            }
+        });
+        if (counts) memcpy(counts + P.f0, cnt, (size_t)P.nf * 4);
+        if (mo && P.np > 0) {
+            if (mo->matches12)
+                host_parallel_for(P.np, [&](int a, int b) {
+                    for (int q = a; q < b; ++q) memcpy(mo->matches12 + (size_t)(P.p0 + q) * capacity, S + oM + (size_t)q * h->kpCap * 4, (size_t)h->kpCap * 4);
+                });
+            if (mo->nmatches) memcpy(mo->nmatches + P.p0, S + oN, (size_t)P.np * 4);
+        }
+        return ORBX_OK;
+    };
     // ORBX_PIPE_TRACE=1: print the chunk timeline (copy / kernels / result copy, ms from the first copy) to stderr
     const bool trace = !direct && getenv("ORBX_PIPE_TRACE") != nullptr;
     std::vector<cudaEvent_t> tev;
@@ -433,8 +532,6 @@ static int batch_to_host_impl(orbx_handle* h, const uint8_t* images, size_t fram
         // what it exposes is the first copy and the kernels + result copy of the last chunk: it runs on smaller chunks
         // (hostChunk, 256 frames unless ORBX_HOST_CHUNK says otherwise) than device-resident batches, which only pay the
         // per-chunk launch ramps (measured: 256 -> 156 k frames/s end to end, 512 -> 151 k, 1024 -> 140 k).
-        static const int hostChunkEnv = getenv("ORBX_HOST_CHUNK") ? std::max(1, atoi(getenv("ORBX_HOST_CHUNK"))) : 256;
-        const int full = direct ? h->chunkFrames : std::min(h->chunkFrames, hostChunkEnv);
         int cf = full;
         if (!direct && nframes > full) cf = chunkNo == 0 ? std::max(1, cf / 4) : (chunkNo == 1 ? std::max(1, cf / 2) : cf);
         nf = std::min(cf, nframes - f0);
@@ -449,10 +546,26 @@ static int batch_to_host_impl(orbx_handle* h, const uint8_t* images, size_t fram
             const int b = chunkNo % ORBX_L0_BUFS;
             uint8_t* dstBuf = h->dLevel0 + (size_t)b * h->chunkFrames * h->l0FrameBytes;
             if (h->evFreeValid[b]) ORBX_CUDA(cudaStreamWaitEvent(h->copyStream, h->evFree[b], 0));
+            const uint8_t* csrc = src;
+            size_t cFrameStride = frame_stride, cRowStride = row_stride;
+            if (stageIn) {
+                // pool buffer b was last read by the upload of chunk chunkNo - ORBX_L0_BUFS
+                if (h->evInPoolValid[b]) ORBX_CUDA(cudaEventSynchronize(h->evInPool[b]));
+                uint8_t* pool = h->hInPool[b];
+                if (row_stride == (size_t)width)
+                    host_parallel_for(nf, [&](int a, int e) { for (int f = a; f < e; ++f) memcpy(pool + (size_t)f * tightFrame, src + (size_t)f * frame_stride, tightFrame); });
+                else
+                    host_parallel_for(nf, [&](int a, int e) {
+                        for (int f = a; f < e; ++f)
+                            for (int y = 0; y < height; ++y) memcpy(pool + (size_t)f * tightFrame + (size_t)y * width, src + (size_t)f * frame_stride + (size_t)y * row_stride, (size_t)width);
+                    });
+                csrc = pool; cFrameStride = tightFrame; cRowStride = (size_t)width;
+            }
             mark(h->copyStream);
-            rc = orbx_copy_frames(h, dstBuf, h->l0FrameBytes, h->dStageLin + (size_t)b * h->chunkFrames * h->l0FrameBytes, (size_t)h->chunkFrames * h->l0FrameBytes, src, frame_stride,
-                                  row_stride, width, height, nf, images_on_device != 0, h->copyStream, &l0.frameStride);
+            rc = orbx_copy_frames(h, dstBuf, h->l0FrameBytes, h->dStageLin + (size_t)b * h->chunkFrames * h->l0FrameBytes, (size_t)h->chunkFrames * h->l0FrameBytes, csrc, cFrameStride,
+                                  cRowStride, width, height, nf, images_on_device != 0, h->copyStream, &l0.frameStride);
             if (rc) return rc;
+            if (stageIn) { ORBX_CUDA(cudaEventRecord(h->evInPool[b], h->copyStream)); h->evInPoolValid[b] = true; }
             ORBX_CUDA(cudaEventRecord(h->evCopied[b], h->copyStream));
             mark(h->copyStream);
             ORBX_CUDA(cudaStreamWaitEvent(h->stream, h->evCopied[b], 0));
@@ -475,6 +588,24 @@ static int batch_to_host_impl(orbx_handle* h, const uint8_t* images, size_t fram
             const int s0 = first_slot + f0;
             ORBX_CUDA(cudaEventRecord(h->evDone, h->stream));
             ORBX_CUDA(cudaStreamWaitEvent(h->d2hStream, h->evDone, 0));
+            if (stageOut) {
+                // into the pool (contiguous copies), handed to the caller after the NEXT chunk has been queued
+                const int ob = chunkNo & 1;
+                uint8_t* S = h->hOutPool[ob];               // free: its previous chunk (chunkNo - 2) was flushed one iteration ago
+                if (kps) ORBX_CUDA(cudaMemcpyAsync(S + oK, h->dKps + (size_t)s0 * h->kpCap, (size_t)nf * h->kpCap * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, h->d2hStream));
+                if (desc) ORBX_CUDA(cudaMemcpyAsync(S + oD, h->dDesc + (size_t)s0 * h->kpCap * 32, (size_t)nf * h->kpCap * 32, cudaMemcpyDeviceToHost, h->d2hStream));
+                ORBX_CUDA(cudaMemcpyAsync(S + oC, h->dCount + s0, (size_t)nf * 4, cudaMemcpyDeviceToHost, h->d2hStream));
+                if (mo && np > 0) {
+                    const int ps = first_slot + p0;
+                    if (mo->matches12) ORBX_CUDA(cudaMemcpyAsync(S + oM, h->dMatches12 + (size_t)ps * h->kpCap, (size_t)np * h->kpCap * 4, cudaMemcpyDeviceToHost, h->d2hStream));
+                    if (mo->nmatches) ORBX_CUDA(cudaMemcpyAsync(S + oN, h->dNMatches + ps, (size_t)np * 4, cudaMemcpyDeviceToHost, h->d2hStream));
+                }
+                ORBX_CUDA(cudaEventRecord(h->evOutPool[ob], h->d2hStream));
+                mark(h->d2hStream);
+                if (pend.live) { rc = flush(pend); if (rc) return rc; }
+                pend = Pending{true, f0, nf, p0, np, ob};
+                continue;
+            }
             if (kps)
                 ORBX_CUDA(cudaMemcpy2DAsync(kps + (size_t)f0 * capacity, (size_t)capacity * sizeof(orbx_keypoint), h->dKps + (size_t)s0 * h->kpCap,
                                             (size_t)h->kpCap * sizeof(orbx_keypoint), (size_t)h->kpCap * sizeof(orbx_keypoint), nf,
@@ -494,6 +625,7 @@ static int batch_to_host_impl(orbx_handle* h, const uint8_t* images, size_t fram
         }
     }
     if (toHost) {
+        if (pend.live) { rc = flush(pend); if (rc) return rc; }
         ORBX_CUDA(cudaStreamSynchronize(h->d2hStream));
         rc = orbx_sync(h);
         if (trace && rc == ORBX_OK) {

@@ -114,6 +114,13 @@ struct orbx_handle {
     cudaStream_t d2hStream;         // device->host copies of chunk i overlap the kernels of chunk i+1
     cudaEvent_t evCopied[ORBX_L0_BUFS], evFree[ORBX_L0_BUFS], evDone;
     bool evFreeValid[ORBX_L0_BUFS];
+    // page-locked staging of the batch pipeline for callers whose buffers are PAGEABLE (a driver-staged copy blocks the host and
+    // serialises the pipeline): inputs are copied here by a few host threads and uploaded from here, results land here and are
+    // handed to the caller one chunk later (orbx_api.cu: batch_to_host_impl)
+    uint8_t* hInPool[ORBX_L0_BUFS]; size_t hInPoolBytes;
+    uint8_t* hOutPool[2]; size_t hOutPoolBytes;
+    cudaEvent_t evInPool[ORBX_L0_BUFS], evOutPool[2];
+    bool evInPoolValid[ORBX_L0_BUFS];
     int l0Pitch;
     long long l0FrameBytes;
     uint8_t* dRaw;      // pyramid levels >= 1

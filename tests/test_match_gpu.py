@@ -150,3 +150,33 @@ def test_extract_match_pipeline_equals_separate_calls():
     assert np.array_equal(nm, nm2)
     for f in range(n - 1):
         assert np.array_equal(m12[f, :cnt[f]], m2[f, :c2[f]]), f"pair {f}"
+
+
+def test_batch_pipeline_pageable_pool_equals_page_locked_buffers():
+    """Pageable caller buffers go through the handle's page-locked pools (inputs copied in by host threads, results handed over a
+    chunk later); page-locked buffers are copied directly.  Same frames, padded rows on the pageable side: identical results."""
+    import torch
+    n, w, h = 37, 640, 480
+    frames = synth.frame_sequence(n, w, h, seed=9)
+    ex = capi.Extractor(max_width=w, max_height=h, chunk_frames=8, result_slots=n)
+    cap = ex.cap
+    def run(pinned):
+        if pinned:
+            pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True).numpy()
+            src = pin((n, h, w), torch.uint8); src[:] = frames
+            kp = pin((n, cap, 28), torch.uint8).view(capi.KP_DTYPE).reshape(n, cap); de = pin((n, cap, 32), torch.uint8)
+            cnt = pin((n,), torch.int32); m12 = pin((n - 1, cap), torch.int32); nm = pin((n - 1,), torch.int32)
+        else:
+            padded = np.zeros((n, h, w + 24), np.uint8); padded[:, :, :w] = frames
+            src = padded[:, :, :w]                                   # row stride 664: the pool copies row by row
+            kp = np.zeros((n, cap), capi.KP_DTYPE); de = np.zeros((n, cap, 32), np.uint8)
+            cnt = np.zeros(n, np.int32); m12 = np.full((n - 1, cap), -7, np.int32); nm = np.full(n - 1, -7, np.int32)
+        ex.extract_match_to_host(src, kp, de, cnt, m12, nm, 100, 0.9, True)
+        return kp, de, cnt, m12, nm
+    a, b = run(True), run(False)
+    assert np.array_equal(a[2], b[2]) and np.array_equal(a[4], b[4]) and a[4].min() > 50
+    for f in range(n):
+        c = a[2][f]
+        assert a[0][f, :c].tobytes() == b[0][f, :c].tobytes() and np.array_equal(a[1][f, :c], b[1][f, :c])
+        if f < n - 1:
+            assert np.array_equal(a[3][f, :c], b[3][f, :c])
