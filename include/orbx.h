@@ -126,8 +126,8 @@ int orbx_extract_batch(orbx_handle* h, const uint8_t* images, size_t frame_strid
  * desc[nframes][capacity][32], counts[nframes]; any may be NULL): the host->device copy of chunk
  * i+1 and the device->host copy of chunk i-1 overlap the kernels of chunk i.  PAGE-LOCKED buffers (cudaHostAlloc, or
  * cudaHostRegister once on buffers that are reused) are copied directly: 159 k frames/s at 640x480.  PAGEABLE buffers go
- * through page-locked pools of the handle (host threads copy the images in, results are handed over one chunk later):
- * 70 k frames/s (25 k when the driver stages the copies itself, ORBX_NO_HOST_POOL=1).  Records beyond counts[f] of a frame
+ * through page-locked pools of the handle (a copy thread fills the next chunk's pool while this one is queued, results are
+ * handed over one chunk later): 82 k frames/s (25 k when the driver stages the copies itself, ORBX_NO_HOST_POOL=1).  Records beyond counts[f] of a frame
  * are unspecified.  Synchronous when any output pointer is given. */
 int orbx_extract_batch_to_host(orbx_handle* h, const uint8_t* images, size_t frame_stride,
                                size_t row_stride, int width, int height, int nframes,

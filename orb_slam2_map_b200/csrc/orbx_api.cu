@@ -524,20 +524,43 @@ static int batch_to_host_impl(orbx_handle* h, const uint8_t* images, size_t fram
     std::vector<cudaEvent_t> tev;
     std::vector<int> tnf;
     auto mark = [&](cudaStream_t st) { if (!trace) return; cudaEvent_t e; cudaEventCreate(&e); cudaEventRecord(e, st); tev.push_back(e); };
-    int chunkNo = 0;
-    for (int f0 = 0, nf = 0; f0 < nframes; f0 += nf, ++chunkNo) {
+    // the chunk schedule (ramped head, tapered tail: see below), known up front so that a copy thread can run one chunk ahead
+    std::vector<std::pair<int, int>> sched;                     // (first frame, frames)
+    for (int f0 = 0, nf = 0, c = 0; f0 < nframes; f0 += nf, ++c) {
+        int cf = full;
+        if (!direct && nframes > full) cf = c == 0 ? std::max(1, cf / 4) : (c == 1 ? std::max(1, cf / 2) : cf);
+        nf = std::min(cf, nframes - f0);
+        if (!direct && toHost && nframes > full && nf == nframes - f0 && nf > std::max(1, full / 4))
+            nf = std::max(std::max(1, full / 4), (nf + 1) / 2);
+        sched.push_back({f0, nf});
+    }
+    // pageable inputs: chunk c is copied into pool buffer c % ORBX_L0_BUFS (last read by the upload of chunk c - ORBX_L0_BUFS) by
+    // a copy thread that runs while the caller's thread queues chunk c - 1 and hands over the results of chunk c - 2
+    auto fill_pool = [&](int c) {
+        cudaSetDevice(h->device);
+        const int b = c % ORBX_L0_BUFS, f0 = sched[c].first, nf = sched[c].second;
+        if (h->evInPoolValid[b]) cudaEventSynchronize(h->evInPool[b]);
+        uint8_t* pool = h->hInPool[b];
+        const uint8_t* src = images + (size_t)f0 * frame_stride;
+        if (row_stride == (size_t)width)
+            host_parallel_for(nf, [&](int a, int e) { for (int f = a; f < e; ++f) memcpy(pool + (size_t)f * tightFrame, src + (size_t)f * frame_stride, tightFrame); });
+        else
+            host_parallel_for(nf, [&](int a, int e) {
+                for (int f = a; f < e; ++f)
+                    for (int y = 0; y < height; ++y) memcpy(pool + (size_t)f * tightFrame + (size_t)y * width, src + (size_t)f * frame_stride + (size_t)y * row_stride, (size_t)width);
+            });
+    };
+    struct Joiner { std::thread t; ~Joiner() { if (t.joinable()) t.join(); } } ahead;      // joins on every exit path
+    if (stageIn) fill_pool(0);
+    for (int chunkNo = 0; chunkNo < (int)sched.size(); ++chunkNo) {
+        const int f0 = sched[chunkNo].first, nf = sched[chunkNo].second;
         // host images: ramp the first two chunks (1/4, 1/2 of a chunk) so that less of the first
         // host->device copy is exposed before the kernels start
         // The pipeline from host images is bound by the copy (55 GB/s = 5.9 us per 640x480 frame against 4.8 us of kernels), and
         // what it exposes is the first copy and the kernels + result copy of the last chunk: it runs on smaller chunks
         // (hostChunk, 256 frames unless ORBX_HOST_CHUNK says otherwise) than device-resident batches, which only pay the
         // per-chunk launch ramps (measured: 256 -> 156 k frames/s end to end, 512 -> 151 k, 1024 -> 140 k).
-        int cf = full;
-        if (!direct && nframes > full) cf = chunkNo == 0 ? std::max(1, cf / 4) : (chunkNo == 1 ? std::max(1, cf / 2) : cf);
-        nf = std::min(cf, nframes - f0);
-        // ... and taper the tail the same way: the kernels and the device->host copy of the last chunk are exposed
-        if (!direct && toHost && nframes > full && nf == nframes - f0 && nf > std::max(1, full / 4))
-            nf = std::max(std::max(1, full / 4), (nf + 1) / 2);
+        // ... and the tail is tapered the same way: the kernels and the device->host copy of the last chunk are exposed
         const uint8_t* src = images + (size_t)f0 * frame_stride;
         Level0 l0;
         l0.base1 = nullptr; l0.stereo = 0;
@@ -549,23 +572,20 @@ static int batch_to_host_impl(orbx_handle* h, const uint8_t* images, size_t fram
             const uint8_t* csrc = src;
             size_t cFrameStride = frame_stride, cRowStride = row_stride;
             if (stageIn) {
-                // pool buffer b was last read by the upload of chunk chunkNo - ORBX_L0_BUFS
-                if (h->evInPoolValid[b]) ORBX_CUDA(cudaEventSynchronize(h->evInPool[b]));
-                uint8_t* pool = h->hInPool[b];
-                if (row_stride == (size_t)width)
-                    host_parallel_for(nf, [&](int a, int e) { for (int f = a; f < e; ++f) memcpy(pool + (size_t)f * tightFrame, src + (size_t)f * frame_stride, tightFrame); });
-                else
-                    host_parallel_for(nf, [&](int a, int e) {
-                        for (int f = a; f < e; ++f)
-                            for (int y = 0; y < height; ++y) memcpy(pool + (size_t)f * tightFrame + (size_t)y * width, src + (size_t)f * frame_stride + (size_t)y * row_stride, (size_t)width);
-                    });
-                csrc = pool; cFrameStride = tightFrame; cRowStride = (size_t)width;
+                if (ahead.t.joinable()) ahead.t.join();              // this chunk's images are in pool buffer b
+                csrc = h->hInPool[b]; cFrameStride = tightFrame; cRowStride = (size_t)width;
             }
             mark(h->copyStream);
             rc = orbx_copy_frames(h, dstBuf, h->l0FrameBytes, h->dStageLin + (size_t)b * h->chunkFrames * h->l0FrameBytes, (size_t)h->chunkFrames * h->l0FrameBytes, csrc, cFrameStride,
                                   cRowStride, width, height, nf, images_on_device != 0, h->copyStream, &l0.frameStride);
             if (rc) return rc;
-            if (stageIn) { ORBX_CUDA(cudaEventRecord(h->evInPool[b], h->copyStream)); h->evInPoolValid[b] = true; }
+            if (stageIn) {
+                ORBX_CUDA(cudaEventRecord(h->evInPool[b], h->copyStream)); h->evInPoolValid[b] = true;
+                if (chunkNo + 1 < (int)sched.size()) {
+                    if (ORBX_L0_BUFS >= 2) ahead.t = std::thread(fill_pool, chunkNo + 1);      // the other buffer: it waits for that buffer's last upload itself
+                    else fill_pool(chunkNo + 1);
+                }
+            }
             ORBX_CUDA(cudaEventRecord(h->evCopied[b], h->copyStream));
             mark(h->copyStream);
             ORBX_CUDA(cudaStreamWaitEvent(h->stream, h->evCopied[b], 0));
