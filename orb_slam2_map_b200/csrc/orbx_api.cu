@@ -486,7 +486,7 @@ static int batch_to_host_impl(orbx_handle* h, const uint8_t* images, size_t fram
     const int full = direct ? h->chunkFrames : std::min(h->chunkFrames, hostChunkEnv);
     // Pageable caller buffers: a driver-staged copy blocks the host until it is done, which serialises copy / kernels / copy.
     // They go through the handle's page-locked pools instead: inputs are copied there by a few host threads and uploaded from
-    // there, results land there and are handed over one chunk later (25 k -> [see DESIGN 5] frames/s at 640x480).
+    // there, results land there and are handed over one chunk later (25 k -> 82 k frames/s at 640x480).
     static const bool noPool = getenv("ORBX_NO_HOST_POOL") != nullptr;
     const bool stageIn = !noPool && !images_on_device && is_pageable(images);
     const bool stageOut = !noPool && toHost && (is_pageable(kps) || is_pageable(desc) || is_pageable(counts) ||

@@ -7,11 +7,12 @@
 //   K18 distinctive_kernel     MapPoint::ComputeDistinctiveDescriptors src/MapPoint.cc:242-305 (rank 4)
 //
 // K16: one warp per feature, lane = child of the current node (first minimum wins, as the reference's scan).
-// K17: one CTA per frame pair.  DBoW2's FeatureVector (std::map node -> ascending feature indices) becomes a block
-// bitonic sort of (node << 32 | index) keys; the reference's merge of the two maps visits exactly the common nodes,
-// and a candidate feature belongs to one node only, so nodes are independent: one warp per node run replays the
-// run's keyframe features in order (the "already matched" skip is sequential inside a node), lanes over the
-// candidates, best / second-best by warp shuffle.  Rotation histogram + ComputeThreeMaxima cull at the end.
+// K17: one CTA per frame pair in a batch, several for the single pair of a per-frame call.  DBoW2's FeatureVector (std::map
+// node -> ascending feature indices) becomes a register/shuffle bitonic sort of (node << 32 | index) keys; the reference's
+// merge of the two maps visits exactly the common nodes, and a candidate feature belongs to one node only, so nodes are
+// independent: one warp per node run replays the run's keyframe features in order (the "already matched" skip is sequential
+// inside a node) with the run's candidates resident in its lanes, best / second best by two warp-wide integer minima.
+// Rotation histogram + ComputeThreeMaxima cull by the CTA that finishes last.
 
 #include "orbx_internal.h"
 #include "orbx_match_common.cuh"
@@ -75,8 +76,8 @@ __device__ void block_bitonic_sort64(unsigned long long* a, int cap)
 
 // gridDim = (pairs, splits).  Nodes are independent (a feature of B belongs to one node, so the "already matched" flags of one
 // node are never read by another), which lets the node runs of a pair be dealt to the warps of `splits` CTAs: one CTA per
-// pair in a batch, many for the single pair of a per-frame call.  Every CTA sorts both key lists for itself; a run belongs to
-// the warp its START POSITION in the sorted list of A maps to, so all CTAs agree on the deal without talking.  Outputs, the
+// pair in a batch, many for the single pair of a per-frame call.  Every CTA sorts both key lists for itself and lists A's node
+// runs in ascending order by a block scan, so all CTAs hold the same list and deal run r to warp r mod (all warps) without talking.  Outputs, the
 // per-feature bins and the pair state (histogram, count, ticket: BOW_STATE_INTS ints per pair) live in global memory and are
 // preset to 0xff bytes by the host (match = -1, bin = none, counters = -1); the CTA that draws the last ticket applies
 // ComputeThreeMaxima to the whole pair.

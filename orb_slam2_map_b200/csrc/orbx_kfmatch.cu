@@ -12,6 +12,9 @@
 // (strict '<') = the smallest key dist << 16 | position in the cell-sorted index list.  K21: FeatureVectors as a
 // block bitonic sort of (node << 32 | index) keys like K17; a candidate replaces the best when dist <= bestDist, so the
 // winner is the least distance with the LAST position among equals.
+// Per-keyframe sizes (the stateless calls): K19 has a grid-free sweep form (area_best_sweep_kernel: the lanes sweep the keyframe's
+// keypoints with the window and cell-window tests, both SearchBySim3 legs in one launch), and K21 splits the single pair of a call
+// over several CTAs of 1024 threads with a last-ticket ComputeThreeMaxima; both forms are bit-identical to the ones above.
 
 #include "orbx_internal.h"
 #include "orbx_match_common.cuh"

@@ -11,6 +11,9 @@
 // later queries may take).  One warp per frame (pair) replays that order; inside one query the
 // candidates are spread over the lanes and "first minimum in GetFeaturesInArea order" becomes a
 // min over (distance, cell, index) — the enumeration order of src/Frame.cc:350-376.
+// The stateless per-frame calls (one frame of <= 4096 keypoints) take the LATENCY forms K7a/K7b and K9a/K9b further down instead:
+// grid-free keypoint sweeps that keep a sorted 32-key candidate list per query on all SMs, then ONE CTA that iterates the
+// reference's sequential rule for all queries at once until nothing changes (the fixed point is the sequential result).
 
 #include "orbx_internal.h"
 
