@@ -128,8 +128,14 @@ def _stereo(w, h, nf, seed):
     return kl, dl, kr, dr, pl, pr, t["scale"].copy(), t["inv_scale"].copy()
 
 
-def case_stereo(w=640, h=240, nf=800, seed=2, bf=386.1448, fx=718.856):
+def case_stereo(w=640, h=240, nf=800, seed=2, bf=386.1448, fx=718.856, left_frac=1.0, right_frac=1.0, swap=False):
+    """left_frac / right_frac keep a prefix of an eye's keypoints (eyes with different keypoint counts); swap: the eyes the other
+    way round (disparities of the wrong sign: almost nothing matches, the search structure is walked all the same)"""
     kl, dl, kr, dr, pl, pr, sc, isc = _stereo(w, h, nf, seed)
+    nl, nr = int(len(kl) * left_frac), int(len(kr) * right_frac)
+    kl, dl, kr, dr = kl[:nl], dl[:nl], kr[:nr], dr[:nr]
+    if swap:
+        kl, dl, kr, dr, pl, pr = kr, dr, kl, dl, pr, pl
     return dict(kind="stereo", kl=kl, dl=dl, kr=kr, dr=dr, pl=pl, pr=pr, scale=sc, inv_scale=isc, bf=bf, fx=fx)
 
 
@@ -541,6 +547,9 @@ CASES = {
     "search_init_collisions": lambda: case_search_init(0, 100, 0.9, True, collide=True),
     "stereo_640x240": lambda: case_stereo(640, 240, 800, 2),
     "stereo_kitti": lambda: case_stereo(1241, 376, 2000, 5),
+    "stereo_fewer_left": lambda: case_stereo(640, 240, 800, 3, left_frac=0.5),
+    "stereo_fewer_right_swapped": lambda: case_stereo(640, 240, 800, 4, right_frac=0.34, swap=True),
+    "search_init_w10": lambda: case_search_init(3, 10, 0.9, True),
     "proj_localmap": lambda: case_proj_localmap(0, 1.0, 0.8),
     "proj_localmap_th3_dup": lambda: case_proj_localmap(1, 3.0, 0.99, dup=True),
     "proj_lastframe": lambda: case_proj_lastframe(0, 15.0, 0.0),
