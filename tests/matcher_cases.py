@@ -575,4 +575,16 @@ CASES = {
     "search_by_sim3": lambda: case_sim3(0),
     "search_by_sim3_th12": lambda: case_sim3(2, 12.0),
     "distinctive": lambda: case_distinctive(0),
+    # further seeds of the rows with the most state (first-come ownership, ratio tests, rotation culls)
+    "proj_localmap_s5": lambda: case_proj_localmap(5, 1.0, 0.8),
+    "proj_lastframe_s6": lambda: case_proj_lastframe(6, 15.0, 0.0),
+    "proj_keyframe_s7": lambda: case_proj_keyframe(7, 10.0, 64),
+    "proj_sim3_s8": lambda: case_proj_sim3(8, 10),
+    "search_init_s9": lambda: case_search_init(9, 100, 0.9, True),
+    "search_by_bow_kf_frame_s3": lambda: case_search_by_bow(0, 3, 0.7, True),
+    "search_by_bow_kf_kf_s4": lambda: case_search_by_bow(1, 4, 0.75, True),
+    "triangulation_s5": lambda: case_triangulation(5),
+    "fuse_mappoints_s6": lambda: case_fuse(0, 6, 3.0),
+    "fuse_sim3_s7": lambda: case_fuse(1, 7, 4.0),
+    "search_by_sim3_s8": lambda: case_sim3(8),
 }
