@@ -42,9 +42,9 @@ def _noisy(desc, r, flips=12, p=0.6):
     return qd
 
 
-def _frame(case, key="frame"):
+def _frame(case, key="frame", B=None):
     f = case[key]
-    return O.FrameData(f["kps"], f["desc"], f["w"], f["h"], u_right=f.get("u_right"), scale_factors=f.get("scale"),
+    return (B or O).FrameData(f["kps"], f["desc"], f["w"], f["h"], u_right=f.get("u_right"), scale_factors=f.get("scale"),
                        bounds=f.get("bounds"))
 
 
@@ -376,24 +376,27 @@ def run_reference(c):
     raise KeyError(k)
 
 
-def run_oracle(c):
+def run_oracle(c, B=None):
+    """The case through the flat interface of include/orbx.h.  B = the implementation behind it: the CPU oracle (default) or an
+    object with the same functions over the CUDA library (tests/test_gpu_vs_reference_golden.py)."""
+    B = B or O
     k = c["kind"]
     if k == "distance":
-        return dict(dist=np.array([O.descriptor_distance(a, b) for a, b in zip(c["a"], c["b"])], np.int32))
+        return dict(dist=np.array([B.descriptor_distance(a, b) for a, b in zip(c["a"], c["b"])], np.int32))
     if k == "area":
-        f = _frame(c)
-        res = [O.features_in_area(f, *map(float, q[:3]), int(q[3]), int(q[4])) for q in c["queries"]]
+        f = _frame(c, B=B)
+        res = [B.features_in_area(f, *map(float, q[:3]), int(q[3]), int(q[4])) for q in c["queries"]]
         return dict(counts=np.array([len(x) for x in res], np.int32), idx=np.concatenate(res + [np.zeros(0, np.int32)]).astype(np.int32))
     if k == "search_init":
-        n, m12, pm, _ = O.search_for_initialization(_frame(c, "f1"), _frame(c, "f2"), c["prev"], c["window"], c["nnratio"], c["ori"])
+        n, m12, pm, _ = B.search_for_initialization(_frame(c, "f1", B=B), _frame(c, "f2", B=B), c["prev"], c["window"], c["nnratio"], c["ori"])
         return dict(n=np.int32(n), m12=m12, prev=pm)
     if k == "stereo":
-        ur, dp, _ = O.compute_stereo_matches(c["kl"], c["dl"], c["kr"], c["dr"], c["pl"], c["pr"], c["scale"], c["inv_scale"], c["bf"], c["fx"])
+        ur, dp, _ = B.compute_stereo_matches(c["kl"], c["dl"], c["kr"], c["dr"], c["pl"], c["pr"], c["scale"], c["inv_scale"], c["bf"], c["fx"])
         return dict(u_right=ur, depth=dp)
     if k == "bow_transform":
         out = {}
         for ls in range(0, c["voc"]["depth"] + 2):
-            w, val, nid = O.bow_transform(c["voc"], c["feats"], ls)
+            w, val, nid = B.bow_transform(c["voc"], c["feats"], ls)
             # TemplatedVocabulary::transform (TemplatedVocabulary.h:1140-1218), TF_IDF + L1: BowVector[word] += weight and
             # FeatureVector[node].push_back(i) for the features whose word has a weight, then the L1 normalisation
             use = val > 0
@@ -413,21 +416,21 @@ def run_oracle(c):
     if k == "search_by_bow":
         a, b = c["a"], c["b"]
         fl = lambda x: (x["flags"] & 3).astype(np.uint8)          # flat form: bit 1 = holds a map point that is NOT bad
-        n, ma, mb = O.search_by_bow(c["variant"], a["desc"], a["kps"]["angle"], a["node"], fl(a), b["desc"], b["kps"]["angle"], b["node"], fl(b),
+        n, ma, mb = B.search_by_bow(c["variant"], a["desc"], a["kps"]["angle"], a["node"], fl(a), b["desc"], b["kps"]["angle"], b["node"], fl(b),
                                     c["nnratio"], c["ori"])
         return dict(n=np.int32(n), match_a=ma, match_b=mb)
     if k == "triangulation":
         a, b = c["a"], c["b"]
         # KeyFrame::GetMapPoint(idx) != NULL is all the reference asks (bad points included)
         fl = lambda x: ((x["flags"] & 1) | (((x["flags"] & 6) != 0).astype(np.uint8) << 1)).astype(np.uint8)
-        mk = lambda x: O.KeyFrameData(x["kps"], x["desc"], 640, 480, u_right=x["u_right"], scale_factors=x["scale"],
+        mk = lambda x: B.KeyFrameData(x["kps"], x["desc"], 640, 480, u_right=x["u_right"], scale_factors=x["scale"],
                                       level_sigma2=(x["scale"] * x["scale"]).astype(F32), node_id=x["node"], flags=fl(x))
-        n, m = O.search_for_triangulation(mk(a), mk(b), c["f12"], c["epipole"], c["only_stereo"], c["ori"])
+        n, m = B.search_for_triangulation(mk(a), mk(b), c["f12"], c["epipole"], c["only_stereo"], c["ori"])
         return dict(n=np.int32(n), matches12=m)
     if k == "fuse":
         fr = c["frame"]
         sf = fr["scale"]
-        kf = O.KeyFrameData(fr["kps"], fr["desc"], 640, 480, u_right=fr["u_right"], scale_factors=sf, level_sigma2=(sf * sf).astype(F32))
+        kf = B.KeyFrameData(fr["kps"], fr["desc"], 640, 480, u_right=fr["u_right"], scale_factors=sf, level_sigma2=(sf * sf).astype(F32))
         u, v = c["u"], c["v"]
         keep = (u >= 0) & (u < 640) & (v >= 0) & (v < 480)          # KeyFrame::IsInImage
         q = _queries(int(keep.sum()))
@@ -436,7 +439,7 @@ def run_oracle(c):
         q["radius"] = (F32(c["th"]) * sf[lv]).astype(F32)
         q["u_right"] = (u[keep] - F32(c["bf"])).astype(F32)
         q["level_lo"] = lv - 1; q["level_hi"] = lv
-        bi, bd = O.fuse(c["variant"], kf, q, c["qdesc"][keep])
+        bi, bd = B.fuse(c["variant"], kf, q, c["qdesc"][keep])
         out = np.full(len(u), -1, np.int32)
         out[keep] = bi
         return dict(n=np.int32((bi >= 0).sum()), best_idx=out)
@@ -444,7 +447,7 @@ def run_oracle(c):
         (h1, u1, v1, l1, m1), (h2, u2, v2, l2, m2) = c["s1"], c["s2"]
         f1, f2 = c["f1"], c["f2"]
         sf = f1["scale"]
-        mk = lambda x: O.KeyFrameData(x["kps"], x["desc"], 640, 480, scale_factors=sf, level_sigma2=(sf * sf).astype(F32))
+        mk = lambda x: B.KeyFrameData(x["kps"], x["desc"], 640, 480, scale_factors=sf, level_sigma2=(sf * sf).astype(F32))
         pre = c["pre12"]
         done2 = np.zeros(len(h2), bool); done2[pre[pre >= 0]] = True
         def side(has, u, v, lv, skip):
@@ -457,14 +460,14 @@ def run_oracle(c):
             return q, idx
         q12, i1 = side(h1, u1, v1, l1, pre >= 0)
         q21, i2 = side(h2, u2, v2, l2, done2)
-        n, m = O.search_by_sim3(mk(f1), mk(f2), q12, f1["desc"][i1], i1, q21, f2["desc"][i2], i2)
+        n, m = B.search_by_sim3(mk(f1), mk(f2), q12, f1["desc"][i1], i1, q21, f2["desc"][i2], i2)
         return dict(n=np.int32(n), match12=m)
     if k == "distinctive":
         off = np.cumsum([0] + [len(g) for g in c["groups"]]).astype(np.int32)
         alld = np.concatenate(c["groups"])
-        idx, _ = O.distinctive_descriptors(alld, off)
+        idx, _ = B.distinctive_descriptors(alld, off)
         return dict(desc=np.stack([g[i] for g, i in zip(c["groups"], idx)]))
-    f = _frame(c)
+    f = _frame(c, B=B)
     sf = c["frame"]["scale"]
     b = c["frame"].get("bounds") or (0.0, float(c["frame"]["w"]), 0.0, float(c["frame"]["h"]))
     if k == "proj_localmap":
@@ -479,7 +482,7 @@ def run_oracle(c):
         q["u"] = c["proj_x"][keep]; q["v"] = c["proj_y"][keep]; q["radius"] = rad
         q["min_level"] = c["level"][keep] - 1; q["max_level"] = c["level"][keep]
         q["u_right"] = c["proj_xr"][keep]; q["max_right_err"] = rad
-        n, a, _, _, _ = O.search_by_projection(0, f, q, c["qdesc"][keep], (c["nobs"][keep] > 0).astype(np.uint8),
+        n, a, _, _, _ = B.search_by_projection(0, f, q, c["qdesc"][keep], (c["nobs"][keep] > 0).astype(np.uint8),
                                                (c["slot_state"] == 1).astype(np.uint8), TH_HIGH, c["nnratio"], False)
         return dict(n=np.int32(n), assigned=_remap(a, keep))
     if k == "proj_lastframe":
@@ -503,7 +506,7 @@ def run_oracle(c):
         q["u_right"] = (u[keep] - F32(c["bf"])).astype(F32)           # u - mbf * invzc, invzc = 1
         q["max_right_err"] = q["radius"]
         q["angle"] = c["angle"][keep]
-        n, a, _, _, _ = O.search_by_projection(1, f, q, c["qdesc"][keep], (c["nobs"][keep] > 0).astype(np.uint8),
+        n, a, _, _, _ = B.search_by_projection(1, f, q, c["qdesc"][keep], (c["nobs"][keep] > 0).astype(np.uint8),
                                                (c["slot_state"] == 1).astype(np.uint8), TH_HIGH, 0.9, c["ori"])
         return dict(n=np.int32(n), assigned=_remap(a, keep))
     if k == "proj_keyframe":
@@ -516,7 +519,7 @@ def run_oracle(c):
         q["radius"] = (F32(c["th"]) * sf[lv]).astype(F32)
         q["min_level"] = lv - 1; q["max_level"] = lv + 1
         q["angle"] = c["angle"][keep]
-        n, a, _, _, _ = O.search_by_projection(2, f, q, c["qdesc"][keep], None, (c["slot_state"] != 0).astype(np.uint8),
+        n, a, _, _, _ = B.search_by_projection(2, f, q, c["qdesc"][keep], None, (c["slot_state"] != 0).astype(np.uint8),
                                                c["orb_dist"], 0.9, c["ori"])
         return dict(n=np.int32(n), assigned=_remap(a, keep))
     if k == "proj_sim3":
@@ -531,7 +534,7 @@ def run_oracle(c):
         # kpLevel < nPredictedLevel-1 || kpLevel > nPredictedLevel (:374-377); a negative bound switches the filter off in
         # the flat form, so level 0 is passed as [0, 0]
         q["level_lo"] = np.maximum(lv - 1, 0); q["level_hi"] = lv
-        n, a, _, _, _ = O.search_by_projection(3, f, q, c["qdesc"][keep], None, c["matched_state"], TH_LOW, 0.75, False)
+        n, a, _, _, _ = B.search_by_projection(3, f, q, c["qdesc"][keep], None, c["matched_state"], TH_LOW, 0.75, False)
         return dict(n=np.int32(n), assigned=_remap(a, keep))
     raise KeyError(k)
 
