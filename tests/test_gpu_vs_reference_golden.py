@@ -68,3 +68,40 @@ def test_cuda_path_equals_frozen_reference_output(name):
             assert np.array_equal(g[f"{name}/{k}#sha256"], digest(v)), f"{name}: {k} differs from the reference's frozen output"
         seen += 1
     assert seen == sum(1 for key in g.files if key.startswith(name + "/"))
+
+
+# ---- the extractor against tests/golden/ref_orbextractor.npz (the unmodified src/ORBextractor.cc, oracle/_ref) ----------------
+import hashlib
+import sys
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+import make_golden as G  # noqa: E402  (input generators + case tables only)
+
+REF = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_orbextractor.npz"))
+
+
+def _sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def test_cuda_extractor_equals_frozen_reference_output_full():
+    for i, (w, h, nf, sc, nl, it, mt, seed) in enumerate(G.EXTRACT_FULL):
+        ex = capi.Extractor(nf, sc, nl, it, mt, max_width=w, max_height=h)
+        k, d = ex.extract(G.extract_input(w, h, seed))
+        assert np.array_equal(k.view(np.uint8).reshape(len(k), 28), REF[f"full_kps_{i}"]), i
+        assert np.array_equal(d, REF[f"full_desc_{i}"]), i
+        assert np.array_equal(ex.level(0, min(3, nl - 1), border=19), REF[f"full_level3_border_{i}"]), i      # mvImagePyramid with its border
+        ex.close()
+
+
+def test_cuda_extractor_equals_frozen_reference_output_hashes():
+    for row, (w, h, nf, sc, nl, it, mt, seed) in zip(REF["hash"], G.EXTRACT_HASH):
+        ex = capi.Extractor(nf, sc, nl, it, mt, max_width=w, max_height=h)
+        k, d = ex.extract(G.extract_input(w, h, seed))
+        assert len(k) == int(row[0])
+        assert _sha(k) == str(row[1]) and _sha(d) == str(row[2])
+        assert _sha(np.concatenate([ex.level(0, l).ravel() for l in range(nl)])) == str(row[3])
+        ex.close()
+    t = capi.Extractor().tables()
+    for key in ("scale", "inv_scale", "sigma2", "inv_sigma2"):
+        assert np.array_equal(t[key], REF["table_" + key]), key
