@@ -1,4 +1,4 @@
-# usage: gpu_r3f.sh <tag> <N> — N-GPU: sharded kNN test + torchrun bench at N (both arms)
+# usage: gpu_multi_both_arms.sh <tag> <N> — N-GPU: sharded kNN test + torchrun bench at N (both arms)
 T=${1:-r02z}; N=${2:-8}
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests/test_sharded_gpu.py -m gpu -x -q > gpurun_out/${T}_pytest_sharded_${N}.log 2>&1; echo "pytest rc=$?"; tail -2 gpurun_out/${T}_pytest_sharded_${N}.log
