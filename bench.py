@@ -400,7 +400,7 @@ def int_pipe_roofline(dev):
             "lop3_per_clk_per_sm_at_1965MHz": r["lop3"] / props.multi_processor_count / 1.965e9}
 
 
-def hamming_leg(dev, rank, world, stream, queries=1 << 20, per=2000000):
+def hamming_leg(dev, rank, world, stream, queries=1 << 20, per=2000000, cpu=False):
     """The cmp/s half of BASELINE.json's metric, MEASURED on the ranks of this run: config 5 as named — 1 048 576 queries
     replicated, 2 000 000 database rows per GPU (16 M over 8) — through ONE C-ABI call per rank, orbm_knn2_sharded: local
     scan (K10), ncclAllGather of the 12-byte per-query records, device merge (K11), chunked so that the exchange of a chunk
@@ -446,7 +446,26 @@ def hamming_leg(dev, rank, world, stream, queries=1 << 20, per=2000000):
     roof = int_pipe_roofline(dev)
     roof["achieved"] = value / world
     roof["frac"] = value / world / roof["peak"]
+    cpu_sample = None
+    if cpu and rank == 0 and world == 1:
+        # config 5 on the host cores: the oracle's brute-force top-2 (__builtin_popcountll, all threads) on a bounded sample of the
+        # same descriptors, its own result checked against the GPU's for those queries
+        cores = os.cpu_count() or 1
+        nq_c, ndb_c = 2048, min(per, 1000000)
+        O = oracle_mod()
+        qc, dbc = q[:nq_c].cpu().numpy(), db[:ndb_c].cpu().numpy()
+        O.knn2(qc[:64], dbc[:65536], 0, cores)
+        t0 = time.perf_counter()
+        od_c, oi_c = O.knn2(qc, dbc, 0, cores)
+        dt_c = time.perf_counter() - t0
+        god = torch.empty((nq_c, 2), dtype=torch.int16, device=dev); goi = torch.empty((nq_c, 2), dtype=torch.int32, device=dev)
+        sharding.knn2_sharded(q[:nq_c], db[:ndb_c], 0, None, stream=st, out=(god, goi))
+        torch.cuda.synchronize()
+        cpu_sample = {"value": float(nq_c) * ndb_c / dt_c, "unit": "cmp/s", "cores": cores, "kind": "port",
+                      "sample": f"{nq_c} queries x {ndb_c} rows of the same data, oracle_knn2 on {cores} threads",
+                      "equals_gpu_result": bool(np.array_equal(goi.cpu().numpy(), oi_c) and np.array_equal(god.cpu().numpy().view(np.uint16), od_c))}
     return {"metric": "Hamming cmp/s (brute-force top-2 kNN, 256-bit descriptors)", "value": value, "unit": "cmp/s", "per_gpu": value / world,
+            "cpu_sample": cpu_sample,
             "measured": True, "nranks": world, "queries": queries, "database_rows_per_gpu": per, "database_rows_total": per * world,
             "steps": 1, "ms": ms, "exchange_ms_alone": ms_exchange, "local_scan_cmp_s_per_gpu": local_rate,
             "efficiency_vs_n1": value / world / local_rate,
@@ -1220,7 +1239,7 @@ def main():
     # ---- second half of the metric: Hamming cmp/s of the brute-force 2-NN kernel on this GPU (short run) ----
     # measured on every rank of this run through orbm_knn2_sharded (NCCL at N > 1), config 5 as named
     if args.workload == "frames" and not args.no_hamming:
-        line["hamming"] = hamming_leg(dev, rank, world, stream)
+        line["hamming"] = hamming_leg(dev, rank, world, stream, cpu=not args.no_cpu)
 
     # ---- CPU baseline (rank 0, N=1 only): bounded sample of the same frames ----------------------
     if rank == 0 and world == 1 and not args.no_cpu:
